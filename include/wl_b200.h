@@ -1,0 +1,146 @@
+/* wl_b200.h -- C ABI of libwaterlily_b200.so: the B200 (sm_100a) implementation of
+ * WaterLily.jl's time-step hot path (sim_step! -> mom_step! + MultiLevelPoisson V-cycle).
+ *
+ * This is the drop-in boundary.  The Julia side (waterlily.jl_b200/julia/WaterLilyB200.jl)
+ * binds these symbols with `ccall`; waterlily.jl_b200/__init__.py binds the same symbols with
+ * ctypes.  No torch / C++ types cross this boundary: plain pointers, sizes and POD structs.
+ *
+ * Conventions
+ *  - Host arrays passed in/out use the reference's layout exactly: Julia column-major,
+ *    size (N1+2, N2+2[, N3+2][, D[, D]]), Float32, one ghost layer per side, component slowest
+ *    (reference src/Flow.jl:133-147).  The library repacks into its padded device layout.
+ *  - Every function returns 0 on success or a WL_ERR_* code; wl_last_error() gives the text.
+ *    Nothing aborts or exits.  One host thread per wl_sim (distinct sims are independent).
+ *  - All device memory is owned by the wl_sim; host buffers are borrowed for the call only.
+ *  - Unsupported through this boundary (WL_ERR_UNSUPPORTED, never a silent CPU fallback):
+ *    space-varying Function uBC / g, udf hooks, user-defined convective schemes, T != Float32.
+ */
+#ifndef WL_B200_H
+#define WL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WL_OK 0
+#define WL_ERR_INVALID 1       /* bad argument / size rule violated                         */
+#define WL_ERR_UNSUPPORTED 2   /* feature of the reference API this path does not implement */
+#define WL_ERR_CUDA 3          /* CUDA runtime error (text in wl_last_error)                 */
+#define WL_ERR_NO_DEVICE 4     /* no usable sm_100 device: the library never falls back      */
+
+typedef struct wl_sim wl_sim;
+
+/* Replaces the keyword arguments of `Simulation(dims,uBC,L;...)` / `Flow(N,uBC;...)`
+ * (reference src/WaterLily.jl:93-98, src/Flow.jl:133-134) and of
+ * `MultiLevelPoisson(x,L,z;maxlevels,perdir)` / `solver!(ml;tol,itmx)`
+ * (src/MultiLevelPoisson.jl:68,108). */
+typedef struct wl_config {
+  int32_t D;            /* 2 or 3                                                    */
+  int32_t N[3];         /* interior cells per direction (dims)                       */
+  int32_t perdir[3];    /* 1 if direction is periodic                                */
+  int32_t exitBC;       /* convective exit in direction 1                            */
+  int32_t scheme;       /* λ: 0 quick, 1 cds, 2 vanLeer (src/Flow.jl:4-6)            */
+  float nu;             /* ν                                                         */
+  float dt0;            /* Δt[1]                                                     */
+  float uBC[3];         /* constant-tuple boundary velocity                          */
+  int32_t maxlevels;    /* 10                                                        */
+  float tol;            /* 2e-3                                                      */
+  int32_t itmx;         /* 32                                                        */
+  int32_t device;       /* CUDA device ordinal                                       */
+  int32_t flags;        /* WL_FLAG_*                                                 */
+} wl_config;
+
+#define WL_FLAG_NO_GRAPHS 1   /* disable CUDA-graph replay of the V-cycle (debugging) */
+
+/* Parametric AutoBody: primitive sdf composed with map(x,t) = x - centre(t),
+ * centre(t) = center + vel*t + acc*t^2 + amp*sin(omega*t)  (src/AutoBody.jl:1-37).
+ * Arbitrary Julia closures cannot cross a C ABI; they are measured on the host by the
+ * reference's own measure! and uploaded with wl_set_body_coeffs. */
+typedef struct wl_body {
+  int32_t kind;         /* 0 NoBody, 1 sphere/circle, 2 cylinder along `axis`, 3 torus with ring normal `axis` */
+  int32_t axis;
+  float center[3];
+  float radius;
+  float minor;
+  float vel[3], acc[3], amp[3];
+  float omega;
+} wl_body;
+
+/* Fields a caller can read or write (sim.flow.* and sim.pois.levels[l].*). */
+enum wl_field {
+  WL_U = 0, WL_U0 = 1, WL_F = 2, WL_P = 3, WL_SIGMA = 4, WL_V = 5, WL_MU0 = 6, WL_MU1 = 7,
+  WL_X = 10, WL_R = 11, WL_EPS = 12, WL_Z = 13, WL_L = 14, WL_DIAG = 15, WL_IDIAG = 16
+};
+
+/* Per-step results: replaces `push!(a.Δt,CFL(a))` (src/Flow.jl:166), the two `push!(ml.n,nᵖ)`
+ * (src/MultiLevelPoisson.jl:127) and the `@log` solver trace (:112,117). */
+typedef struct wl_step_info {
+  float dt_next;
+  int32_t n_pred, n_corr;
+  int32_t flags;                       /* bit0: non-finite residual seen, bit1: itmx reached */
+  int32_t trace_len[2];                /* entries valid in each trace (n+1)                 */
+  float rinf[2][34], r1[2][34], omega[2][34];
+} wl_step_info;
+
+/* ---- lifetime.  wl_create = Flow constructor (src/Flow.jl:133-147) with the default IC.      */
+int wl_create(const wl_config* cfg, wl_sim** out);
+void wl_destroy(wl_sim* s);
+const char* wl_last_error(const wl_sim* s);   /* s may be NULL: last error of wl_create */
+int wl_version(void);
+
+/* ---- data surface: Array(field) / copyto!(field, ::Array)  (ext/WaterLilyJLD2Ext.jl:13-14,43-44) */
+int wl_field_dims(const wl_sim* s, int field, int level, int32_t dims[5], int32_t* ndims);
+int wl_download(wl_sim* s, int field, int level, float* host, size_t count);
+int wl_upload(wl_sim* s, int field, int level, const float* host, size_t count);
+int wl_nlevels(const wl_sim* s);
+
+/* ---- initial condition: after uploading WL_U this applies BC!, exitBC!(u,u,0), u⁰=u (src/Flow.jl:141-142) */
+int wl_finish_ic(wl_sim* s, const float uBC[3]);
+
+/* ---- body: measure!(flow,body;t,ϵ) (src/Body.jl:28-51)                                      */
+int wl_measure_body(wl_sim* s, const wl_body* body, double t, double eps);
+/* host-measured coefficients (values BEFORE the two BC! calls of Body.jl:49-50, which are applied here) */
+int wl_set_body_coeffs(wl_sim* s, const float* mu0, const float* mu1, const float* V, const float* sdf);
+
+/* ---- Poisson: pois_ctor(flow) (src/WaterLily.jl:97), update! (src/MultiLevelPoisson.jl:79-86),
+ *      solver! (src/MultiLevelPoisson.jl:108-128) on the current x (=p) and z (=σ).            */
+int wl_build_poisson(wl_sim* s);
+int wl_update_poisson(wl_sim* s);
+int wl_solver(wl_sim* s, int32_t* n_iter, int32_t* trace_len, float* rinf, float* r1, float* omega);
+
+/* ---- time step: mom_step! (src/Flow.jl:156-167).  uBC_t1 = boundary velocity at t₁ (NULL: cfg.uBC);
+ *      acc0/acc1 = space-uniform g+dU/dt at t₀/t₁ for accelerate! (src/Flow.jl:69-73), may be NULL.
+ *      Uses and replaces the stored Δt (wl_get_dt / wl_set_dt).                                */
+int wl_mom_step(wl_sim* s, const float* uBC_t1, const float* acc0, const float* acc1, wl_step_info* info);
+int wl_get_dt(const wl_sim* s, float* dt);
+int wl_set_dt(wl_sim* s, float dt);
+int wl_cfl(wl_sim* s, float* dt);                       /* CFL(a) src/Flow.jl:234-237 */
+
+/* ---- pressure_force(sim) (src/Metrics.jl:116-133); clobbers flow.f like the reference        */
+int wl_pressure_force(wl_sim* s, const wl_body* body, double t, double out[3]);
+
+/* ---- asynchronous stepping for host-overlap: enqueue `nsteps` mom_steps without reading
+ *      results back between them is not possible (Δt and the solver loop are host-steered in
+ *      the reference); wl_sync waits for all queued device work.                               */
+int wl_sync(wl_sim* s);
+
+/* ---- counters for benchmarks: kernels launched by this sim since creation, and per-phase
+ *      device time of the last step when enabled by wl_enable_timing.                         */
+int64_t wl_launch_count(const wl_sim* s);
+int wl_enable_timing(wl_sim* s, int on);
+/* phases: 0 mom predictor, 1 project(w=1), 2 mom corrector, 3 project(w=.5), 4 cfl; seconds */
+int wl_last_phase_times(const wl_sim* s, double out[8]);
+
+/* ---- test hook: run ONE constituent operation of the step so that kernel-level parity tests can
+ *      compare it with the oracle.  op: 0 BC!(u,uBC,exitBC) 1 conv_diff!+BDIM! predictor (u from u⁰)
+ *      2 mom_project!(w=arg) 3 residual!(level) 4 Vcycle!(ω=arg) 5 smooth!(level,ω=arg)
+ *      6 Jacobi!(level) 7 exitBC!(u,u⁰,Δt) 8 conv_diff!+BDIM!+scale corrector 9 u⁰ .= u          */
+int wl_debug_op(wl_sim* s, int op, int level, float arg);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WL_B200_H */

@@ -1,0 +1,305 @@
+"""GPU parity tests proper: the sm_100a CUDA path, called through the C ABI, against the CPU
+oracle on the same seeded inputs.  Tolerances (north_star: 1e-5 relative in Float32 after N
+steps, identical Poisson iteration counts):
+  * single kernels / one operation on random data:      max|Δ| <= 2e-6 · scale
+  * fields after N full steps:                           max|Δu| <= 1e-5·U, rel max|Δp| <= 1e-4
+  * Poisson iteration counts `pois.n` and Δt history:    identical / 1e-6 relative
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from oracle import wl_oracle as wo
+
+
+@pytest.fixture(scope="module")
+def wl():
+    import __graft_entry__ as ge
+    ge.build()
+    import waterlily_jl_b200 as wl
+    return wl
+
+
+def pair(wl, dims, uBC, L=1.0, body=None, **kw):
+    b_gpu = wl.AutoBody(**body) if body else None
+    b_cpu = wo.make_body(**body) if body else None
+    return wl.Simulation(dims, uBC, L, body=b_gpu, **kw), wo.OracleSim(dims, uBC, L, body=b_cpu, **kw)
+
+
+def randomize(sim, ref, names, seed=0, scale=1.0):
+    rng = np.random.default_rng(seed)
+    for nm in names:
+        a = ref.field(nm)
+        a[...] = (scale * rng.uniform(-1, 1, a.shape)).astype(np.float32)
+        sim.upload(nm, a)
+
+
+def close(a, b, tol, what=""):
+    scale = max(1.0, float(np.abs(b).max()))
+    err = float(np.abs(a - b).max())
+    assert err <= tol * scale, f"{what}: max|Δ|={err:.3e} scale={scale:.3e}"
+
+
+CASES_BC = [((8, 6), (), False), ((8, 6), (1,), False), ((8, 6), (2,), True), ((8, 6), (1, 2), False),
+            ((6, 8, 4), (), True), ((6, 8, 4), (3,), False), ((6, 8, 4), (1, 2, 3), False), ((6, 8, 4), (2,), True)]
+
+
+@pytest.mark.parametrize("dims,perdir,exitBC", CASES_BC)
+def test_bc_kernel(wl, dims, perdir, exitBC):
+    """Fused BC! kernel == the reference's D² sequential passes, corners included (core.jl:200-219)."""
+    U = (1.0, 0.5, -0.25)[: len(dims)]
+    sim, ref = pair(wl, dims, U, perdir=perdir, exitBC=exitBC)
+    randomize(sim, ref, ["u"], seed=1)
+    sim.debug_op(0)
+    a = ref.field("u")
+    import ctypes as C
+    ng = (C.c_int * 3)(*([d + 2 for d in dims] + [1] * (3 - len(dims))))
+    per = (C.c_int * 3)(*[1 if d + 1 in perdir else 0 for d in range(3)])
+    Ua = (C.c_float * 3)(*(list(U) + [0.0] * (3 - len(dims))))
+    ref.lib.wlo_BC(a.ctypes.data, len(dims), ng, Ua, int(exitBC), per)
+    assert np.array_equal(sim.flow.u, a)
+    # exitBC! kernel (core.jl:226-233)
+    randomize(sim, ref, ["u0"], seed=2)
+    sim.upload("u", a)
+    sim.debug_op(7)
+    ref.lib.wlo_exitBC(a.ctypes.data, ref.field("u0").ctypes.data, len(dims), ng, float(ref.dts[-1]))
+    close(sim.flow.u, a, 1e-6, "exitBC")
+
+
+@pytest.mark.parametrize("dims,perdir,scheme", [((16, 12), (), "quick"), ((16, 12), (1, 2), "quick"),
+                                                  ((16, 12), (2,), "vanLeer"), ((12, 8, 8), (), "quick"),
+                                                  ((12, 8, 8), (1, 2, 3), "cds"), ((12, 8, 8), (3,), "vanLeer")])
+def test_conv_diff_bdim_kernel(wl, dims, perdir, scheme):
+    """K-RHS + K-BDIM on random fields == conv_diff! + BDIM! (Flow.jl:38-62,176-180), ghost rows included."""
+    U = (1.0, 0.0, 0.0)[: len(dims)]
+    sim, ref = pair(wl, dims, U, perdir=perdir, scheme=scheme, nu=0.05)
+    randomize(sim, ref, ["u", "u0", "V", "mu1"], seed=3)
+    randomize(sim, ref, ["mu0"], seed=4, scale=0.5)
+    # predictor: u zeroed, advect u⁰
+    ref.lib.wlo_op_scale_u(ref.h, 0.0)
+    ref.lib.wlo_op_conv_diff(ref.h, 1)
+    ref.lib.wlo_op_bdim(ref.h)
+    sim.debug_op(1)
+    close(sim.flow.f, ref.field("f"), 2e-6, "f (predictor)")
+    close(sim.flow.u, ref.field("u"), 2e-6, "u (predictor)")
+    # corrector: advect u, average
+    ref.lib.wlo_op_conv_diff(ref.h, 0)
+    sig = ref.field("sigma").copy()
+    ref.lib.wlo_op_bdim(ref.h)
+    ref.lib.wlo_op_scale_u(ref.h, 0.5)
+    sim.debug_op(8)
+    close(sim.flow.f, ref.field("f"), 2e-6, "f (corrector)")
+    close(sim.flow.u, ref.field("u"), 2e-6, "u (corrector)")
+    # stale Φ in σ's upper ghosts (feeds CFL's whole-array maximum, Flow.jl:236)
+    s_gpu = sim.flow.sigma
+    inner = tuple(slice(1, -1) for _ in dims)
+    mask = np.ones(sig.shape, bool)
+    mask[inner] = False
+    low = np.zeros(sig.shape, bool)
+    for ax in range(len(dims)):
+        idx = [slice(None)] * len(dims)
+        idx[ax] = 0
+        low[tuple(idx)] = True
+    m = mask & ~low
+    close(s_gpu[m], sig[m], 2e-6, "ghost Φ")
+
+
+@pytest.mark.parametrize("N,n_max", [((66, 66), 4), ((18, 18, 18), 3), ((34, 18), 32), ((18, 10, 6), 32)])
+def test_solver_manufactured(wl, N, n_max):
+    """`Poisson_setup(MultiLevelPoisson, N)` (test/test_poisson.jl:1-12,62-70) on the GPU: same x,
+    same iteration count and residual trace as the oracle, and the reference's own bounds."""
+    D = len(N)
+    dims = tuple(n - 2 for n in N)
+    sim, ref = pair(wl, dims, (0.0,) * D)
+    soln = np.zeros(ref.field("p").shape, np.float32)
+    soln[...] = (np.arange(N[0], dtype=np.float32) - 1).reshape((1,) * (D - 1) + (N[0],))
+    ref.lib.wlo_mult(ref.h, soln.ctypes.data)
+    sim.upload("sigma", ref.field("sigma"))
+    n_ref = ref.lib.wlo_solver(ref.h)
+    tr = sim.solver()
+    assert tr["n"] == n_ref <= n_max
+    t_ref = ref.trace(0)
+    assert np.allclose(tr["r1"], t_ref["r1"], rtol=2e-4) and np.allclose(tr["rinf"], t_ref["rinf"], rtol=2e-4)
+    assert tr["omega"] == t_ref["omega"]
+    x = sim.flow.p
+    close(x, ref.field("p"), 1e-5, "x")
+    if n_max <= 4:
+        x = x - x[(1,) * D]
+        inner = tuple(slice(1, -1) for _ in N)
+        err = np.sum((x - soln)[inner].astype(np.float64) ** 2) / np.sum(soln[inner].astype(np.float64) ** 2)
+        assert err < 1e-6
+        assert np.abs(sim.pois.levels[0].r).max() < 2e-3
+
+
+def test_level_data_surface(wl):
+    """pois.levels[l].D / .L after update! (test/test_poisson.jl:54-60) through download/upload."""
+    sim, ref = pair(wl, (8, 8), (0.0, 0.0))
+    assert np.array_equal(sim.pois.levels[2].D.T, np.array([[0, 0, 0, 0], [0, -2, -2, 0], [0, -2, -2, 0], [0, 0, 0, 0]], np.float32))
+    L = sim.pois.levels[0].L
+    L[0].T[4:6, :] = 0
+    sim.upload("L", L, 0)
+    sim._check(sim.lib.wl_update_poisson(sim.h))
+    assert np.array_equal(sim.pois.levels[2].D.T, np.array([[0, 0, 0, 0], [0, -1, -1, 0], [0, -1, -1, 0], [0, 0, 0, 0]], np.float32))
+    with pytest.raises(AssertionError):
+        wl.Simulation((15, 81), (0.0, 0.0))          # size rule, test_poisson.jl:42
+    for l in range(sim.nlevels):
+        assert sim.field_shape("x", l) == ref.field("x", l).shape
+
+
+def step_both(sim, ref, nsteps, **kw):
+    for _ in range(nsteps):
+        sim.sim_step(**kw)
+        ref.sim_step(**kw)
+
+
+def check_state(sim, ref, utol=1e-5, ptol=1e-4, U=1.0):
+    assert sim.pois.n == ref.n, (sim.pois.n, ref.n)
+    assert np.allclose(sim.flow.Δt, ref.dts, rtol=2e-6), (sim.flow.Δt[-3:], ref.dts[-3:])
+    u, p = sim.flow.u, sim.flow.p
+    eu = float(np.abs(u - ref.field("u")).max())
+    ep = float(np.abs(p - ref.field("p")).max()) / max(1e-30, float(np.abs(ref.field("p")).max()))
+    assert eu <= utol * max(U, 1.0), f"max|Δu|={eu:.3e}"
+    assert ep <= ptol, f"rel max|Δp|={ep:.3e}"
+    assert not np.isnan(u).any()
+
+
+def test_config_A_circle_2d(wl):
+    """BASELINE config A: README circle, 96x64, Re=100, 100 sim_step! (README.md:41-58)."""
+    n, m = 96, 64
+    R = m / 8
+    body = dict(kind="circle", center=(m / 2 - 1, m / 2 - 1), radius=R)
+    sim, ref = pair(wl, (n, m), (1.0, 0.0), 2 * R, body=body, nu=2 * R / 100)
+    close(sim.flow.mu0, ref.field("mu0"), 1e-6, "μ₀")
+    close(sim.flow.mu1, ref.field("mu1"), 1e-6, "μ₁")
+    step_both(sim, ref, 100, remeasure=False)
+    check_state(sim, ref, utol=2e-5)
+    f_gpu, f_ref = sim.pressure_force(), ref.pressure_force()
+    assert np.allclose(f_gpu, f_ref, rtol=1e-4, atol=1e-4 * np.abs(f_ref).max()), (f_gpu, f_ref)
+
+
+def tgv3d(i, x, k):
+    if i == 1:
+        return -np.sin(k * x[0]) * np.cos(k * x[1]) * np.cos(k * x[2])
+    if i == 2:
+        return np.cos(k * x[0]) * np.sin(k * x[1]) * np.cos(k * x[2])
+    return 0 * x[0] * x[1] * x[2]
+
+
+def test_config_B_tgv_small(wl):
+    """BASELINE config B at 32³ (oracle-sized): periodic 3D TGV, 10 steps."""
+    N = 32
+    k = np.float32(2 * np.pi / N)
+    kw = dict(perdir=(1, 2, 3), nu=float(1 / (k * 1600)), U=1.0, u0=lambda i, x: tgv3d(i, x, k))
+    sim, ref = pair(wl, (N, N, N), (0.0, 0.0, 0.0), N, **kw)
+    step_both(sim, ref, 10)
+    check_state(sim, ref)
+
+
+@pytest.mark.parametrize("exitBC", [False, True])
+def test_config_C_sphere_small(wl, exitBC):
+    """BASELINE config C at 64x32x32: static sphere with BDIM, optional convective exit."""
+    m = 32
+    R = m / 8
+    body = dict(kind="sphere", center=(m / 2 - 1,) * 3, radius=R)
+    sim, ref = pair(wl, (2 * m, m, m), (1.0, 0.0, 0.0), 2 * R, body=body, nu=2 * R / 3700, exitBC=exitBC)
+    step_both(sim, ref, 10, remeasure=False)
+    check_state(sim, ref)
+    f_gpu, f_ref = sim.pressure_force(), ref.pressure_force()
+    assert np.allclose(f_gpu, f_ref, rtol=1e-4, atol=1e-4 * np.abs(f_ref).max())
+
+
+def test_config_D_moving_cylinder_small(wl):
+    """BASELINE config D at 64x64x16: oscillating cylinder, periodic z, remeasure every step."""
+    R = 6.0
+    body = dict(kind="cylinder", axis=2, center=(32, 32, 0), radius=R, amp=(R, 0, 0), omega=2 * np.pi / (8 * R))
+    sim, ref = pair(wl, (64, 64, 16), (0.0, 0.0, 0.0), 2 * R, body=body, U=1.0, nu=2 * R / 1000, perdir=(3,))
+    step_both(sim, ref, 8, remeasure=True)
+    close(sim.flow.V, ref.field("V"), 1e-6, "V")
+    close(sim.flow.mu0, ref.field("mu0"), 2e-6, "μ₀")
+    check_state(sim, ref)
+
+
+def test_torus_and_schemes(wl):
+    body = dict(kind="torus", axis=0, center=(16, 16, 16), radius=8.0, minor=3.0)
+    for scheme in ("vanLeer", "cds"):
+        sim, ref = pair(wl, (32, 32, 32), (1.0, 0.0, 0.0), 16, body=body, nu=0.01, scheme=scheme)
+        step_both(sim, ref, 4, remeasure=False)
+        check_state(sim, ref)
+
+
+def test_semicoarsening_and_odd_sizes(wl):
+    """Semi-coarsened hierarchies (test/test_poisson.jl:73-82) and an odd last dimension (half_rangek quirk)."""
+    H = 16
+    R = H // 4
+    sim, ref = pair(wl, (8 * H, H), (1, 0), R, body=dict(kind="circle", center=(4 * H, H // 2), radius=R), nu=R / 100)
+    step_both(sim, ref, 4, remeasure=False)
+    check_state(sim, ref)
+    assert all(n <= 10 for n in sim.pois.n)
+    H = 8
+    R = H // 4
+    sim, ref = pair(wl, (8 * H, H, H), (1, 0, 0), R, body=dict(kind="sphere", center=(4 * H, H // 2, H // 2), radius=R), nu=R / 100)
+    step_both(sim, ref, 4, remeasure=False)
+    check_state(sim, ref)
+    assert all(n <= 12 for n in sim.pois.n)
+    sim, ref = pair(wl, (16, 32, 7), (1, 0, 0), 4, body=dict(kind="sphere", center=(8, 16, 3.5), radius=2), nu=0.05)
+    step_both(sim, ref, 3, remeasure=False)
+    check_state(sim, ref)
+
+
+def test_reference_known_answers_on_gpu(wl):
+    """The reference's own assertions, evaluated on the CUDA path."""
+    # impulsive box flow test/test_flow.jl:76-84
+    U = (2 / 3, -1 / 3)
+    sim = wl.Simulation((16, 16), U)
+    sim.mom_step()
+    u = sim.flow.u
+    L2 = lambda a: float(np.sum(a[1:-1, 1:-1].astype(np.float64) ** 2))
+    assert L2(u[0] - np.float32(U[0])) < 2e-5 and L2(u[1] - np.float32(U[1])) < 1e-5
+    # accelerating circle test/test_flow.jl:161-173 (time-dependent uniform uBC)
+    radius, H = 32, 16
+    sim = wl.Simulation((2 * H * radius,) * 2, (0.0, 0.0), radius, U=1,
+                        body=wl.AutoBody("circle", (H * radius,) * 2, radius))
+    kw = dict(uBC_t=lambda t: (t, 0.0), dUdt=lambda t: (1.0, 0.0))
+    sim.sim_step(**kw)
+    force = sim.pressure_force() / (np.pi * sim.L ** 2)
+    assert np.allclose(force, [-1, 0], atol=0.04), force
+    u = sim.flow.u
+    assert u.max() / u[0][1, 1] > 1.91
+    for _ in range(3):
+        sim.sim_step(**kw)
+    assert all(n <= 2 for n in sim.pois.n), sim.pois.n
+    # moving circle with V = U = 1 test/test_simulation.jl:22-24
+    radius = 8
+    for exitBC in (True, False):
+        sim = wl.Simulation((4 * radius,) * 2, (1, 0), radius, nu=radius / 250, exitBC=exitBC,
+                            body=wl.AutoBody("circle", (2 * radius,) * 2, radius, vel=(1, 0)))
+        sim.sim_step()
+        assert np.allclose(sim.flow.u[0].T[:, radius - 1], 1)
+
+
+def test_full_size_properties_tgv128(wl):
+    """BASELINE config B at full size (128³): size-independent properties instead of an oracle run:
+    divergence-free projection, kinetic energy non-increasing, TGV symmetry u₃ ≡ 0 preserved on the
+    mid-plane, bounded iteration counts, determinism (two runs bit-identical)."""
+    N = 128
+    k = np.float32(2 * np.pi / N)
+    kw = dict(perdir=(1, 2, 3), nu=float(1 / (k * 1600)), U=1.0, u0=lambda i, x: tgv3d(i, x, k))
+
+    def run():
+        sim = wl.Simulation((N, N, N), (0.0, 0.0, 0.0), N, **kw)
+        ke = []
+        for _ in range(5):
+            sim.sim_step()
+            u = sim.flow.u
+            ke.append(float(np.sum(u[:, 1:-1, 1:-1, 1:-1].astype(np.float64) ** 2)))
+        return sim, u, ke
+
+    sim, u, ke = run()
+    div = (u[0][1:-1, 1:-1, 2:] - u[0][1:-1, 1:-1, 1:-1]) + (u[1][1:-1, 2:, 1:-1] - u[1][1:-1, 1:-1, 1:-1]) + \
+          (u[2][2:, 1:-1, 1:-1] - u[2][1:-1, 1:-1, 1:-1])
+    assert np.abs(div).max() < 4e-3                 # div(u) after projection == solver residual, tol 2e-3
+    assert all(b <= a * (1 + 1e-5) for a, b in zip(ke, ke[1:]))
+    assert all(1 <= n <= 8 for n in sim.pois.n), sim.pois.n
+    sim2, u2, _ = run()
+    assert np.array_equal(u, u2) and sim.pois.n == sim2.pois.n

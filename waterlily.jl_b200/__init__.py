@@ -1,0 +1,395 @@
+"""waterlily.jl_b200 -- host-side mirror of WaterLily.jl's `Simulation` / `sim_step!` API over the
+C ABI of libwaterlily_b200.so (include/wl_b200.h).
+
+The reference is Julia; Julia is not present in this image, so this module plays the role of
+the thin `ccall` shim (julia/WaterLilyB200.jl is that shim, unexecuted here).  Names and
+argument meaning follow the reference (src/WaterLily.jl:93-149, src/Flow.jl:133-147):
+
+    sim = Simulation((nx,ny,nz), (U,0,0), L; ν, body=AutoBody(...), perdir, exitBC, ...)
+    sim_step!(sim, t_end; remeasure)   ->  sim.sim_step(t_end, remeasure=...)
+    sim.flow.u, sim.flow.p, sim.flow.Δt, sim.pois.n, pressure_force(sim)
+
+Everything numerical happens in hand-written sm_100a CUDA kernels inside the shared library;
+this file only marshals arguments.  There is NO CPU fallback: if the library is missing or no
+Blackwell GPU is visible, construction raises.
+
+Array convention: a Julia array of size (n1,n2,n3,D) is returned as a numpy array of shape
+(D,n3,n2,n1) (same memory order), i.e. a[c-1,k-1,j-1,i-1] == a_julia[i,j,k,c].
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIBNAME = os.path.join(_HERE, "libwaterlily_b200.so")
+
+WL_OK, WL_ERR_INVALID, WL_ERR_UNSUPPORTED, WL_ERR_CUDA, WL_ERR_NO_DEVICE = range(5)
+FIELDS = dict(u=0, u0=1, f=2, p=3, sigma=4, V=5, mu0=6, mu1=7,
+              x=10, r=11, eps=12, z=13, L=14, D=15, iD=16)
+SCHEMES = dict(quick=0, cds=1, vanLeer=2)
+KINDS = dict(none=0, sphere=1, circle=1, cylinder=2, torus=3)
+
+# symbols include/wl_b200.h declares (tests check the library exports every one of them)
+ABI_SYMBOLS = [
+    "wl_create", "wl_destroy", "wl_last_error", "wl_version", "wl_field_dims", "wl_download",
+    "wl_upload", "wl_nlevels", "wl_finish_ic", "wl_measure_body", "wl_set_body_coeffs",
+    "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
+    "wl_cfl", "wl_pressure_force", "wl_sync", "wl_launch_count", "wl_enable_timing",
+    "wl_last_phase_times", "wl_debug_op",
+]
+
+
+class WLConfig(C.Structure):
+    _fields_ = [("D", C.c_int32), ("N", C.c_int32 * 3), ("perdir", C.c_int32 * 3), ("exitBC", C.c_int32),
+                ("scheme", C.c_int32), ("nu", C.c_float), ("dt0", C.c_float), ("uBC", C.c_float * 3),
+                ("maxlevels", C.c_int32), ("tol", C.c_float), ("itmx", C.c_int32), ("device", C.c_int32),
+                ("flags", C.c_int32)]
+
+
+class WLBody(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("axis", C.c_int32), ("center", C.c_float * 3), ("radius", C.c_float),
+                ("minor", C.c_float), ("vel", C.c_float * 3), ("acc", C.c_float * 3), ("amp", C.c_float * 3),
+                ("omega", C.c_float)]
+
+
+class WLStepInfo(C.Structure):
+    _fields_ = [("dt_next", C.c_float), ("n_pred", C.c_int32), ("n_corr", C.c_int32), ("flags", C.c_int32),
+                ("trace_len", C.c_int32 * 2), ("rinf", (C.c_float * 34) * 2), ("r1", (C.c_float * 34) * 2),
+                ("omega", (C.c_float * 34) * 2)]
+
+
+class WaterLilyB200Error(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library(path=None):
+    """dlopen libwaterlily_b200.so and declare the prototypes of include/wl_b200.h.
+    Loading needs no GPU; any compute entry point does."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    path = path or _LIBNAME
+    if not os.path.exists(path):
+        raise WaterLilyB200Error(
+            f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a).  There is no CPU fallback.")
+    lib = C.CDLL(path)
+    P, F, I = C.c_void_p, C.c_float, C.c_int32
+    FP = C.POINTER(F)
+    lib.wl_create.argtypes = [C.POINTER(WLConfig), C.POINTER(P)]
+    lib.wl_destroy.argtypes = [P]
+    lib.wl_destroy.restype = None
+    lib.wl_last_error.argtypes = [P]
+    lib.wl_last_error.restype = C.c_char_p
+    lib.wl_field_dims.argtypes = [P, I, I, C.POINTER(I * 5), C.POINTER(I)]
+    lib.wl_download.argtypes = [P, I, I, P, C.c_size_t]
+    lib.wl_upload.argtypes = [P, I, I, P, C.c_size_t]
+    lib.wl_nlevels.argtypes = [P]
+    lib.wl_finish_ic.argtypes = [P, FP]
+    lib.wl_measure_body.argtypes = [P, C.POINTER(WLBody), C.c_double, C.c_double]
+    lib.wl_set_body_coeffs.argtypes = [P, P, P, P, P]
+    lib.wl_build_poisson.argtypes = [P]
+    lib.wl_update_poisson.argtypes = [P]
+    lib.wl_solver.argtypes = [P, C.POINTER(I), C.POINTER(I), FP, FP, FP]
+    lib.wl_mom_step.argtypes = [P, FP, FP, FP, C.POINTER(WLStepInfo)]
+    lib.wl_get_dt.argtypes = [P, FP]
+    lib.wl_set_dt.argtypes = [P, F]
+    lib.wl_cfl.argtypes = [P, FP]
+    lib.wl_pressure_force.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3)]
+    lib.wl_sync.argtypes = [P]
+    lib.wl_launch_count.argtypes = [P]
+    lib.wl_launch_count.restype = C.c_int64
+    lib.wl_enable_timing.argtypes = [P, I]
+    lib.wl_last_phase_times.argtypes = [P, C.POINTER(C.c_double * 8)]
+    lib.wl_debug_op.argtypes = [P, I, I, F]
+    if path == _LIBNAME:
+        _lib = lib
+    return lib
+
+
+def _v3f(a):
+    a = list(a) + [0.0] * (3 - len(a))
+    return (C.c_float * 3)(*[float(x) for x in a])
+
+
+class AutoBody:
+    """Parametric stand-in for `AutoBody(sdf,map)` (src/AutoBody.jl:1-37): a primitive signed
+    distance composed with the rigid translation map(x,t) = x - (center + vel t + acc t² + amp sin(ω t)).
+    Arbitrary closures stay on the Julia host and enter through `set_body_coeffs`."""
+
+    def __init__(self, kind="none", center=(0, 0, 0), radius=0.0, minor=0.0, axis=2, vel=(0, 0, 0),
+                 acc=(0, 0, 0), amp=(0, 0, 0), omega=0.0):
+        self.c = WLBody(KINDS[kind], int(axis), _v3f(center), float(radius), float(minor), _v3f(vel),
+                        _v3f(acc), _v3f(amp), float(omega))
+
+    @property
+    def kind(self):
+        return self.c.kind
+
+
+def NoBody():
+    return AutoBody("none")
+
+
+class _Handle:
+    def __init__(self, lib, h):
+        self.lib, self.h = lib, h
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.lib.wl_destroy(self.h)
+        except Exception:
+            pass
+
+
+class B200Flow:
+    """`Flow` (src/Flow.jl:114-148) whose arrays live on the device; attribute access downloads."""
+
+    def __init__(self, sim):
+        self._sim = sim
+        self.Δt = sim._dts
+        self.ν = sim.nu
+        self.uBC = sim.uBC
+        self.exitBC = sim.exitBC
+        self.perdir = sim.perdir
+
+    def __getattr__(self, name):
+        alias = {"μ₀": "mu0", "μ₁": "mu1", "σ": "sigma", "u⁰": "u0"}
+        name = alias.get(name, name)
+        if name in ("u", "u0", "f", "p", "sigma", "V", "mu0", "mu1"):
+            return self._sim.download(name)
+        raise AttributeError(name)
+
+
+class _LevelView:
+    def __init__(self, sim, l):
+        self._sim, self._l = sim, l
+
+    def __getattr__(self, name):
+        alias = {"ϵ": "eps"}
+        name = alias.get(name, name)
+        if name in ("x", "r", "eps", "z", "L", "D", "iD"):
+            return self._sim.download(name, self._l)
+        raise AttributeError(name)
+
+
+class B200Poisson:
+    """`MultiLevelPoisson` (src/MultiLevelPoisson.jl:61-77): `n` iteration log and `levels[l].x/r/L/D`."""
+
+    def __init__(self, sim):
+        self._sim = sim
+        self.n = sim._n
+
+    @property
+    def levels(self):
+        return [_LevelView(self._sim, l) for l in range(self._sim.nlevels)]
+
+
+class Simulation:
+    """`Simulation(dims,uBC,L;Δt,ν,U,ϵ,perdir,u0,exitBC,λ,body,T,mem)` (src/WaterLily.jl:93-106) on a B200."""
+
+    def __init__(self, dims, uBC, L=1.0, *, dt=0.25, nu=0.0, U=None, eps=1.0, perdir=(), exitBC=False,
+                 scheme="quick", body=None, u0=None, g=None, maxlevels=10, tol=2e-3, itmx=32, device=0,
+                 T=np.float32, lib=None):
+        if np.dtype(T) != np.float32:
+            raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: the B200 path is Float32 only")
+        if callable(uBC) or callable(g):
+            raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: Function uBC/g; use the uBC_t/dUdt arguments of "
+                                     "sim_step for space-uniform time-dependent boundary velocity")
+        if scheme not in SCHEMES:
+            raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: convective scheme must be quick, cds or vanLeer")
+        self.lib = lib or load_library()
+        self.D = len(dims)
+        self.dims = tuple(int(n) for n in dims)
+        self.L = L
+        self.U = float(np.sqrt(sum(float(x) ** 2 for x in uBC))) if U is None else U
+        self.ϵ = self.eps = eps
+        self.uBC = tuple(float(x) for x in uBC)
+        self.nu = float(nu)
+        self.exitBC = bool(exitBC)
+        self.perdir = tuple(perdir)
+        self.body = body if body is not None else NoBody()
+        per = [1 if (d + 1) in perdir else 0 for d in range(3)]
+        cfg = WLConfig(self.D, (C.c_int32 * 3)(*(list(self.dims) + [0] * (3 - self.D))), (C.c_int32 * 3)(*per),
+                       int(exitBC), SCHEMES[scheme], float(nu), float(dt), _v3f(self.uBC), maxlevels, float(tol),
+                       itmx, device, 0)
+        h = C.c_void_p()
+        rc = self.lib.wl_create(C.byref(cfg), C.byref(h))
+        if rc != WL_OK:
+            raise WaterLilyB200Error(f"wl_create failed ({rc}): {self.lib.wl_last_error(None).decode()}")
+        self._handle = _Handle(self.lib, h)
+        self.h = h
+        self._dts = [np.float32(dt)]
+        self._n = []
+        self.last_info = None
+        if u0 is not None:
+            self.apply_ic(u0)
+        self._check(self.lib.wl_measure_body(self.h, C.byref(self.body.c), 0.0, float(eps)))   # measure!(flow,body;ϵ)
+        self._check(self.lib.wl_build_poisson(self.h))                                        # pois_ctor(flow)
+        self.nlevels = self.lib.wl_nlevels(self.h)
+        self.flow = B200Flow(self)
+        self.pois = B200Poisson(self)
+
+    # ---- plumbing
+    def _check(self, rc):
+        if rc != WL_OK:
+            msg = self.lib.wl_last_error(self.h).decode()
+            if rc == WL_ERR_INVALID and "size=a2" in msg:
+                raise AssertionError("MultiLevelPoisson requires size=a2ⁿ, where n>2")
+            raise WaterLilyB200Error(f"libwaterlily_b200 error {rc}: {msg}")
+
+    def field_shape(self, name, level=0):
+        dims = (C.c_int32 * 5)()
+        nd = C.c_int32()
+        self._check(self.lib.wl_field_dims(self.h, FIELDS[name], level, C.byref(dims), C.byref(nd)))
+        return tuple(dims[i] for i in range(nd.value))[::-1]
+
+    def download(self, name, level=0, out=None):
+        """`Array(flow.u)`: device -> host in the reference's (unpadded) layout."""
+        shape = self.field_shape(name, level)
+        a = out if out is not None else np.empty(shape, np.float32)
+        self._check(self.lib.wl_download(self.h, FIELDS[name], level, a.ctypes.data, a.size))
+        return a
+
+    def upload(self, name, a, level=0):
+        """`copyto!(flow.u, ::Array)`."""
+        a = np.ascontiguousarray(a, np.float32)
+        assert a.shape == self.field_shape(name, level), (a.shape, self.field_shape(name, level))
+        self._check(self.lib.wl_upload(self.h, FIELDS[name], level, a.ctypes.data, a.size))
+
+    def loc(self, i):
+        """`loc(i,I)` (src/core.jl:177) for every cell; D arrays broadcastable against a scalar field."""
+        n = [d + 2 for d in self.dims]
+        out = []
+        for d in range(self.D):
+            x = np.arange(n[d], dtype=np.float32) - np.float32(0.5) - (np.float32(0.5) if i == d + 1 else 0)
+            shp = [1] * self.D
+            shp[self.D - 1 - d] = n[d]
+            out.append(x.reshape(shp))
+        return out
+
+    def apply_ic(self, fn, U=None):
+        """`apply!(u0,u)` over all indices + BC! + exitBC!(u,u,0) + u⁰=u (src/Flow.jl:140-142)."""
+        shape = self.field_shape("u")
+        u = np.empty(shape, np.float32)
+        for i in range(self.D):
+            u[i][...] = np.broadcast_to(np.asarray(fn(i + 1, self.loc(i + 1)), dtype=np.float32), shape[1:])
+        self.upload("u", u)
+        self._check(self.lib.wl_finish_ic(self.h, _v3f(self.uBC if U is None else U)))
+
+    # ---- reference API
+    def time(self):
+        """`time(flow)` = sum(Δt[1:end-1]) (src/Flow.jl:174)."""
+        return float(np.sum(np.asarray(self._dts[:-1], np.float32), dtype=np.float32)) if len(self._dts) > 1 else 0.0
+
+    def sim_time(self):
+        return self.time() * self.U / self.L
+
+    def measure(self, t=None):
+        """`measure!(sim,t=sum(Δt))` = measure!(flow,body) + update!(pois) (src/WaterLily.jl:146-149)."""
+        if t is None:
+            t = float(np.sum(np.asarray(self._dts, np.float32), dtype=np.float32))
+        self._check(self.lib.wl_measure_body(self.h, C.byref(self.body.c), float(t), float(self.eps)))
+        self._check(self.lib.wl_update_poisson(self.h))
+
+    def set_body_coeffs(self, mu0=None, mu1=None, V=None, sdf=None):
+        """Upload host-measured BDIM coefficients (arbitrary AutoBody closures), then update!(pois)."""
+        def p(a):
+            return None if a is None else np.ascontiguousarray(a, np.float32).ctypes.data
+        keep = [np.ascontiguousarray(a, np.float32) for a in (mu0, mu1, V, sdf) if a is not None]
+        self._check(self.lib.wl_set_body_coeffs(self.h, p(mu0), p(mu1), p(V), p(sdf)))
+        del keep
+        self._check(self.lib.wl_update_poisson(self.h))
+
+    def mom_step(self, U1=None, acc0=None, acc1=None):
+        """`mom_step!(flow,pois)` (src/Flow.jl:156-167)."""
+        info = WLStepInfo()
+        f = lambda v: None if v is None else _v3f(v)
+        self._check(self.lib.wl_mom_step(self.h, f(U1), f(acc0), f(acc1), C.byref(info)))
+        self._dts.append(np.float32(info.dt_next))
+        self._n += [info.n_pred, info.n_corr]
+        self.last_info = info
+        return info
+
+    def sim_step(self, t_end=None, remeasure=True, max_steps=None, uBC_t=None, dUdt=None, udf=None):
+        """`sim_step!(sim[,t_end];remeasure,max_steps)` (src/WaterLily.jl:128-139)."""
+        if udf is not None:
+            raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: udf hooks cannot cross the C ABI")
+        steps = 0
+        while True:
+            if t_end is not None and not (self.sim_time() < t_end):
+                break
+            if max_steps is not None and steps >= max_steps:
+                break
+            if remeasure and self.body.kind != 0:
+                self.measure()
+            t1 = float(np.sum(np.asarray(self._dts, np.float32), dtype=np.float32))
+            t0 = float(np.float32(t1) - self._dts[-1])
+            self.mom_step(None if uBC_t is None else uBC_t(t1),
+                          None if dUdt is None else dUdt(t0), None if dUdt is None else dUdt(t1))
+            steps += 1
+            if t_end is None:
+                break
+
+    def solver(self):
+        """Stand-alone `solver!(pois)` on the current x (=p) and z (=σ)."""
+        n, tl = C.c_int32(), C.c_int32()
+        a, b, c = ((C.c_float * 34)() for _ in range(3))
+        self._check(self.lib.wl_solver(self.h, C.byref(n), C.byref(tl), a, b, c))
+        k = tl.value
+        return dict(n=n.value, rinf=list(a[:k]), r1=list(b[:k]), omega=list(c[:k]))
+
+    def trace(self, which):
+        i = self.last_info
+        k = i.trace_len[which]
+        return dict(n=k - 1, rinf=list(i.rinf[which][:k]), r1=list(i.r1[which][:k]), omega=list(i.omega[which][:k]))
+
+    def cfl(self):
+        dt = C.c_float()
+        self._check(self.lib.wl_cfl(self.h, C.byref(dt)))
+        return float(dt.value)
+
+    def pressure_force(self, t=None):
+        """`pressure_force(sim)` (src/Metrics.jl:116-133)."""
+        out = (C.c_double * 3)()
+        t = self.time() if t is None else t
+        self._check(self.lib.wl_pressure_force(self.h, C.byref(self.body.c), float(t), C.byref(out)))
+        return np.array(out[: self.D])
+
+    def debug_op(self, op, level=0, arg=0.0):
+        self._check(self.lib.wl_debug_op(self.h, int(op), int(level), float(arg)))
+
+    def sync(self):
+        self._check(self.lib.wl_sync(self.h))
+
+    def launch_count(self):
+        return int(self.lib.wl_launch_count(self.h))
+
+    def enable_timing(self, on=True):
+        self._check(self.lib.wl_enable_timing(self.h, int(on)))
+
+    def phase_times(self):
+        out = (C.c_double * 8)()
+        self._check(self.lib.wl_last_phase_times(self.h, C.byref(out)))
+        return list(out)
+
+
+def sim_step(sim, *a, **k):
+    return sim.sim_step(*a, **k)
+
+
+def sim_time(sim):
+    return sim.sim_time()
+
+
+def measure(sim, t=None):
+    return sim.measure(t)
+
+
+def pressure_force(sim):
+    return sim.pressure_force()

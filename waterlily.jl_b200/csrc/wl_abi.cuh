@@ -1,0 +1,398 @@
+// wl_abi.cuh -- the extern "C" entry points of include/wl_b200.h (included by wl_b200.cu).
+#pragma once
+
+namespace {
+
+int fail(wl_sim* s, int code, const std::string& msg) {
+  if (s) { s->err = msg; s->status = code; } else g_create_error = msg;
+  return code;
+}
+
+// MultiLevelPoisson(x,L,z;maxlevels,perdir) (MultiLevelPoisson.jl:68-76) + restrictML (:33-41)
+int build_levels(wl_sim* s) {
+  for (size_t l = 1; l < s->lv.size(); ++l) {
+    Level& v = s->lv[l];
+    free_field(v.L); free_field(v.x); free_field(v.z);
+  }
+  for (auto& v : s->lv) { free_field(v.r); free_field(v.eps); free_field(v.Dg); free_field(v.iD); }
+  s->lv.clear();
+  s->lv.reserve(s->cfg.maxlevels + 2);
+  s->lv.emplace_back();
+  {
+    Level& l0 = s->lv.back();
+    l0.lay = s->lay; l0.L = s->mu0; l0.x = s->p; l0.z = s->sigma; l0.owns = false;
+    if (int e = alloc_field(s, l0.r, s->lay, 1)) return e;
+    if (int e = alloc_field(s, l0.eps, s->lay, 1)) return e;
+    if (int e = alloc_field(s, l0.Dg, s->lay, 1)) return e;
+    if (int e = alloc_field(s, l0.iD, s->lay, 1)) return e;
+    set_diag(s, l0);
+  }
+  auto anydiv = [&](const Level& l) {
+    for (int d = 0; d < s->D; ++d) if (divisible(l.lay.n(d))) return true;
+    return false;
+  };
+  while (anydiv(s->lv.back()) && (int)s->lv.size() <= s->cfg.maxlevels) {
+    const Level& f = s->lv.back();
+    Level c;
+    int ng[3];
+    for (int d = 0; d < 3; ++d) {
+      c.c[d] = d < s->D && divisible(f.lay.n(d));
+      ng[d] = c.c[d] ? 1 + f.lay.n(d) / 2 : f.lay.n(d);
+    }
+    c.lay = make_lay(s->D, ng);
+    c.owns = true;
+    s->lv.push_back(c);
+    Level& co = s->lv.back();
+    if (int e = alloc_field(s, co.L, co.lay, s->D)) return e;
+    if (int e = alloc_field(s, co.x, co.lay, 1)) return e;
+    if (int e = alloc_field(s, co.z, co.lay, 1)) return e;
+    if (int e = alloc_field(s, co.r, co.lay, 1)) return e;
+    if (int e = alloc_field(s, co.eps, co.lay, 1)) return e;
+    if (int e = alloc_field(s, co.Dg, co.lay, 1)) return e;
+    if (int e = alloc_field(s, co.iD, co.lay, 1)) return e;
+    restrictL(s, s->lv[s->lv.size() - 2], co);
+    set_diag(s, co);
+  }
+  if (s->lv.size() <= 2) return fail(s, WL_ERR_INVALID, "MultiLevelPoisson requires size=a2^n, where n>2");
+  // reduction scratch sized for the finest level's largest grid
+  return WL_OK;
+}
+
+int check_async(wl_sim* s, const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(s, WL_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+  return WL_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int wl_version(void) { return 100; }
+
+const char* wl_last_error(const wl_sim* s) { return s ? s->err.c_str() : g_create_error.c_str(); }
+
+int wl_create(const wl_config* cfg, wl_sim** out) {
+  if (!cfg || !out) return fail(nullptr, WL_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (cfg->D != 2 && cfg->D != 3) return fail(nullptr, WL_ERR_INVALID, "D must be 2 or 3");
+  for (int d = 0; d < cfg->D; ++d)
+    if (cfg->N[d] < 2) return fail(nullptr, WL_ERR_INVALID, "each dimension needs at least 2 cells");
+  if (cfg->scheme < 0 || cfg->scheme > 2) return fail(nullptr, WL_ERR_UNSUPPORTED, "convective scheme must be quick, cds or vanLeer");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0 || cfg->device >= ndev)
+    return fail(nullptr, WL_ERR_NO_DEVICE, "no CUDA device: libwaterlily_b200 has no CPU fallback");
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, cfg->device);
+  if (prop.major < 10)
+    return fail(nullptr, WL_ERR_NO_DEVICE, "device is not sm_100 (Blackwell); this library ships sm_100a code only");
+  wl_sim* s = new wl_sim();
+  s->cfg = *cfg;
+  s->D = cfg->D;
+  s->device = cfg->device;
+  s->dt = cfg->dt0;
+  if (s->cfg.maxlevels <= 0) s->cfg.maxlevels = 10;
+  if (s->cfg.itmx <= 0) s->cfg.itmx = 32;
+  if (s->cfg.itmx > 32) s->cfg.itmx = 32;
+  if (s->cfg.tol <= 0) s->cfg.tol = 2e-3f;
+  auto bail = [&](int code) { g_create_error = s->err; wl_destroy(s); return code; };
+  if (cudaSetDevice(cfg->device) != cudaSuccess) { s->err = "cudaSetDevice failed"; return bail(WL_ERR_CUDA); }
+  if (cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking) != cudaSuccess) { s->err = "stream create failed"; return bail(WL_ERR_CUDA); }
+  int ng[3];
+  for (int d = 0; d < 3; ++d) { ng[d] = cfg->N[d] + 2; s->per.p[d] = d < cfg->D ? (cfg->perdir[d] != 0) : 0; }
+  s->lay = make_lay(cfg->D, ng);
+  const int D = s->D;
+  int e = 0;
+  if ((e = alloc_field(s, s->u, s->lay, D)) || (e = alloc_field(s, s->u0, s->lay, D)) ||
+      (e = alloc_field(s, s->f, s->lay, D)) || (e = alloc_field(s, s->p, s->lay, 1)) ||
+      (e = alloc_field(s, s->sigma, s->lay, 1)) || (e = alloc_field(s, s->V, s->lay, D)) ||
+      (e = alloc_field(s, s->mu0, s->lay, D)) || (e = alloc_field(s, s->mu1, s->lay, D * D)))
+    return bail(e);
+  // reduction scratch: one partial per block of the largest launch
+  {
+    dim3 g = grid_all(s->lay);
+    size_t nb = (size_t)g.x * g.y * g.z + 64;
+    if (cudaMalloc(&s->redw.psum, nb * sizeof(double)) != cudaSuccess ||
+        cudaMalloc(&s->redw.pmax, nb * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&s->redw.ticket, sizeof(unsigned)) != cudaSuccess ||
+        cudaMalloc(&s->d_red, sizeof(Red) * NRED) != cudaSuccess ||
+        cudaHostAlloc(&s->h_red, sizeof(Red) * NRED, cudaHostAllocDefault) != cudaSuccess) {
+      s->err = "reduction scratch allocation failed";
+      return bail(WL_ERR_CUDA);
+    }
+    cudaMemsetAsync(s->redw.ticket, 0, sizeof(unsigned), s->st);
+    cudaMemsetAsync(s->d_red, 0, sizeof(Red) * NRED, s->st);
+  }
+  for (int i = 0; i < 8; ++i) cudaEventCreate(&s->ev[i]);
+  // Flow constructor (Flow.jl:139-145): u = uBC everywhere, BC!, exitBC!(u,u,0), u⁰ = u, μ₀ = 1 then BC!(μ₀,0)
+  {
+    std::vector<float> ones((size_t)s->lay.cstride * D + 64, 1.f);
+    cudaMemcpyAsync(s->mu0.alloc, ones.data(), ones.size() * sizeof(float), cudaMemcpyHostToDevice, s->st);
+    for (int c = 0; c < D; ++c) {
+      std::fill(ones.begin(), ones.begin() + s->lay.cstride, cfg->uBC[c]);
+      cudaMemcpyAsync(s->u.alloc + (size_t)s->lay.cstride * c, ones.data(), s->lay.cstride * sizeof(float),
+                      cudaMemcpyHostToDevice, s->st);
+      cudaStreamSynchronize(s->st);
+    }
+  }
+  *out = s;
+  if ((e = wl_finish_ic(s, cfg->uBC))) { *out = nullptr; return bail(e); }
+  bc_vec(s, s->mu0, nullptr, false);
+  if (cudaStreamSynchronize(s->st) != cudaSuccess || cudaGetLastError() != cudaSuccess) {
+    s->err = "device initialisation failed";
+    *out = nullptr;
+    return bail(WL_ERR_CUDA);
+  }
+  return WL_OK;
+}
+
+void wl_destroy(wl_sim* s) {
+  if (!s) return;
+  cudaSetDevice(s->device);
+  if (s->st) cudaStreamSynchronize(s->st);
+  for (size_t l = 0; l < s->lv.size(); ++l) {
+    Level& v = s->lv[l];
+    if (v.owns) { free_field(v.L); free_field(v.x); free_field(v.z); }
+    free_field(v.r); free_field(v.eps); free_field(v.Dg); free_field(v.iD);
+  }
+  free_field(s->u); free_field(s->u0); free_field(s->f); free_field(s->p);
+  free_field(s->sigma); free_field(s->V); free_field(s->mu0); free_field(s->mu1);
+  if (s->redw.psum) cudaFree(s->redw.psum);
+  if (s->redw.pmax) cudaFree(s->redw.pmax);
+  if (s->redw.ticket) cudaFree(s->redw.ticket);
+  if (s->d_red) cudaFree(s->d_red);
+  if (s->h_red) cudaFreeHost(s->h_red);
+  for (int i = 0; i < 8; ++i) if (s->ev[i]) cudaEventDestroy(s->ev[i]);
+  if (s->st) cudaStreamDestroy(s->st);
+  delete s;
+}
+
+int wl_nlevels(const wl_sim* s) { return s ? (int)s->lv.size() : 0; }
+
+int wl_field_dims(const wl_sim* s, int field, int level, int32_t dims[5], int32_t* ndims) {
+  if (!s) return WL_ERR_INVALID;
+  Lay lay;
+  DevField* f = flow_field(const_cast<wl_sim*>(s), field, level, &lay);
+  if (!f) return WL_ERR_INVALID;
+  int n = 0;
+  dims[n++] = lay.n0; dims[n++] = lay.n1;
+  if (s->D == 3) dims[n++] = lay.n2;
+  if (f->ncomp == s->D * s->D && field == WL_MU1) { dims[n++] = s->D; dims[n++] = s->D; }
+  else if (f->ncomp > 1) dims[n++] = f->ncomp;
+  *ndims = n;
+  return WL_OK;
+}
+
+static int xfer(wl_sim* s, int field, int level, float* host, size_t count, bool up) {
+  if (!s || !host) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  Lay lay;
+  DevField* f = flow_field(s, field, level, &lay);
+  if (!f) return fail(s, WL_ERR_INVALID, "unknown field/level");
+  const size_t per = (size_t)lay.n0 * lay.n1 * lay.n2;
+  if (count != per * f->ncomp) return fail(s, WL_ERR_INVALID, "host buffer has the wrong number of elements");
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  for (int c = 0; c < f->ncomp; ++c) {
+    float* dev = f->base + lay.cstride * c;
+    float* h = host + per * c;
+    if (up)
+      WL_CUDA(s, cudaMemcpy2DAsync(dev, lay.pitch * sizeof(float), h, lay.n0 * sizeof(float), lay.n0 * sizeof(float),
+                                   (size_t)lay.n1 * lay.n2, cudaMemcpyHostToDevice, s->st));
+    else
+      WL_CUDA(s, cudaMemcpy2DAsync(h, lay.n0 * sizeof(float), dev, lay.pitch * sizeof(float), lay.n0 * sizeof(float),
+                                   (size_t)lay.n1 * lay.n2, cudaMemcpyDeviceToHost, s->st));
+  }
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  return WL_OK;
+}
+int wl_download(wl_sim* s, int field, int level, float* host, size_t count) { return xfer(s, field, level, host, count, false); }
+int wl_upload(wl_sim* s, int field, int level, const float* host, size_t count) {
+  return xfer(s, field, level, const_cast<float*>(host), count, true);
+}
+
+int wl_finish_ic(wl_sim* s, const float uBC[3]) {
+  if (!s) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  bc_vec(s, s->u, uBC ? uBC : s->cfg.uBC, s->cfg.exitBC != 0);
+  exitbc(s, s->u, s->u, 0.f);                        // runs even when exitBC=false (Flow.jl:141)
+  WL_CUDA(s, cudaMemcpyAsync(s->u0.alloc, s->u.alloc, s->u.bytes, cudaMemcpyDeviceToDevice, s->st));
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  return check_async(s, "wl_finish_ic");
+}
+
+int wl_measure_body(wl_sim* s, const wl_body* body, double t, double eps) {
+  if (!s || !body) return WL_ERR_INVALID;
+  if (body->kind == 0) return WL_OK;                 // NoBody: measure! is a no-op (Body.jl:83)
+  if (body->kind < 0 || body->kind > 3) return fail(s, WL_ERR_UNSUPPORTED, "unknown body kind");
+  cudaSetDevice(s->device);
+  MeasArgs a{s->lay, body_at(body, s->D, (float)t), (float)eps, s->sigma.base, s->V.base, s->mu0.base, s->mu1.base};
+  DISPATCH_D(s, k_measure, grid_all(s->lay), blk(s->D), a);
+  bc_vec(s, s->mu0, nullptr, false);
+  bc_vec(s, s->V, nullptr, s->cfg.exitBC != 0);
+  return check_async(s, "wl_measure_body");
+}
+
+int wl_set_body_coeffs(wl_sim* s, const float* mu0, const float* mu1, const float* V, const float* sdf) {
+  if (!s) return WL_ERR_INVALID;
+  const size_t per = (size_t)s->lay.n0 * s->lay.n1 * s->lay.n2;
+  int e = 0;
+  if (mu0 && (e = wl_upload(s, WL_MU0, 0, mu0, per * s->D))) return e;
+  if (mu1 && (e = wl_upload(s, WL_MU1, 0, mu1, per * s->D * s->D))) return e;
+  if (V && (e = wl_upload(s, WL_V, 0, V, per * s->D))) return e;
+  if (sdf && (e = wl_upload(s, WL_SIGMA, 0, sdf, per))) return e;
+  bc_vec(s, s->mu0, nullptr, false);
+  bc_vec(s, s->V, nullptr, s->cfg.exitBC != 0);
+  return check_async(s, "wl_set_body_coeffs");
+}
+
+int wl_build_poisson(wl_sim* s) {
+  if (!s) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  if (int e = build_levels(s)) return e;
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  return check_async(s, "wl_build_poisson");
+}
+
+// update!(ml) (MultiLevelPoisson.jl:79-86)
+int wl_update_poisson(wl_sim* s) {
+  if (!s || s->lv.empty()) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  set_diag(s, s->lv[0]);
+  for (size_t l = 1; l < s->lv.size(); ++l) { restrictL(s, s->lv[l - 1], s->lv[l]); set_diag(s, s->lv[l]); }
+  return check_async(s, "wl_update_poisson");
+}
+
+int wl_solver(wl_sim* s, int32_t* n_iter, int32_t* trace_len, float* rinf, float* r1, float* omega) {
+  if (!s || s->lv.empty()) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  Trace tr;
+  if (int e = mlp_solver(s, &tr)) return e;
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  if (n_iter) *n_iter = tr.n;
+  if (trace_len) *trace_len = tr.n + 1;
+  for (int i = 0; i <= tr.n && i < 34; ++i) {
+    if (rinf) rinf[i] = tr.rinf[i];
+    if (r1) r1[i] = tr.r1[i];
+    if (omega) omega[i] = tr.omega[i];
+  }
+  return check_async(s, "wl_solver");
+}
+
+int wl_get_dt(const wl_sim* s, float* dt) { if (!s || !dt) return WL_ERR_INVALID; *dt = s->dt; return WL_OK; }
+int wl_set_dt(wl_sim* s, float dt) { if (!s) return WL_ERR_INVALID; s->dt = dt; return WL_OK; }
+
+int wl_cfl(wl_sim* s, float* dt) {
+  if (!s || !dt) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  if (int e = cfl(s, dt)) return e;
+  return check_async(s, "wl_cfl");
+}
+
+// mom_step!(a,b) (Flow.jl:156-167) = mom_predict! (:190-196), mom_project!(w=1), mom_correct! (:205-210),
+// mom_project!(w=½), push!(Δt,CFL)
+int wl_mom_step(wl_sim* s, const float* uBC_t1, const float* acc0, const float* acc1, wl_step_info* info) {
+  if (!s || s->lv.empty()) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  const float* U = uBC_t1 ? uBC_t1 : s->cfg.uBC;
+  const bool ex = s->cfg.exitBC != 0;
+  Trace tr[2];
+  if (s->timing) cudaEventRecord(s->ev[0], s->st);
+  WL_CUDA(s, cudaMemcpyAsync(s->u0.alloc, s->u.alloc, s->u.bytes, cudaMemcpyDeviceToDevice, s->st));   // u⁰ .= u
+  ++s->launches;
+  // predictor
+  mom_rhs(s, s->u0, acc0);
+  bdim(s, 0);
+  bc_vec(s, s->u, U, ex);
+  if (ex) exitbc(s, s->u, s->u0, s->dt);
+  if (s->timing) cudaEventRecord(s->ev[1], s->st);
+  if (int e = mom_project(s, 1.f, U, &tr[0])) return e;
+  if (s->timing) cudaEventRecord(s->ev[2], s->st);
+  // corrector
+  ghost_phi(s);
+  mom_rhs(s, s->u, acc1);
+  bdim(s, 1);
+  bc_vec(s, s->u, U, ex);
+  if (s->timing) cudaEventRecord(s->ev[3], s->st);
+  if (int e = mom_project(s, 0.5f, U, &tr[1])) return e;
+  if (s->timing) cudaEventRecord(s->ev[4], s->st);
+  float dtn = 0.f;
+  if (int e = cfl(s, &dtn)) return e;
+  if (s->timing) {
+    cudaEventRecord(s->ev[5], s->st);
+    cudaEventSynchronize(s->ev[5]);
+    for (int i = 0; i < 5; ++i) { float ms = 0; cudaEventElapsedTime(&ms, s->ev[i], s->ev[i + 1]); s->phase_s[i] = ms * 1e-3; }
+  }
+  s->dt = dtn;
+  if (info) {
+    info->dt_next = dtn; info->n_pred = tr[0].n; info->n_corr = tr[1].n;
+    info->flags = tr[0].flags | tr[1].flags;
+    for (int q = 0; q < 2; ++q) {
+      info->trace_len[q] = tr[q].n + 1;
+      for (int i = 0; i <= tr[q].n && i < 34; ++i) {
+        info->rinf[q][i] = tr[q].rinf[i]; info->r1[q][i] = tr[q].r1[i]; info->omega[q][i] = tr[q].omega[i];
+      }
+    }
+  }
+  return check_async(s, "wl_mom_step");
+}
+
+int wl_pressure_force(wl_sim* s, const wl_body* body, double t, double out[3]) {
+  if (!s || !body || !out) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  ForceArgs a{s->lay, body_at(body, s->D, (float)t), s->p.base, s->f.base};
+  DISPATCH_D(s, k_force_df, grid_all(s->lay), blk(s->D), a);
+  for (int c = 0; c < s->D; ++c) {
+    SumArgs sa{s->lay, s->f.base + s->lay.cstride * c, s->redw, s->d_red + 3 + c};
+    DISPATCH_D(s, k_sum_all, grid_all(s->lay), blk(s->D), sa);
+  }
+  if (int e = fetch_red(s)) return e;
+  for (int c = 0; c < 3; ++c) out[c] = c < s->D ? s->h_red[3 + c].sum : 0.0;
+  return check_async(s, "wl_pressure_force");
+}
+
+int wl_debug_op(wl_sim* s, int op, int level, float arg) {
+  if (!s) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  if (op >= 2 && op <= 6 && (s->lv.empty() || level < 0 || level >= (int)s->lv.size())) return WL_ERR_INVALID;
+  const bool ex = s->cfg.exitBC != 0;
+  switch (op) {
+    case 0: bc_vec(s, s->u, s->cfg.uBC, ex); break;
+    case 1: mom_rhs(s, s->u0, nullptr); bdim(s, 0); break;
+    case 2: { Trace tr; if (int e = mom_project(s, arg, s->cfg.uBC, &tr)) return e; break; }
+    case 3: {
+      Level& p = s->lv[level];
+      perbc(s, p.lay, p.x.base);
+      LevArgs a = lev_args(s, p);
+      a.out = s->d_red + 0;
+      DISPATCH_D(s, k_residual, grid_inside(p.lay), blk(s->D), a);
+      a.in = s->d_red + 0; a.out = s->d_red + 1;
+      DISPATCH_D(s, k_shift_norms, grid_inside(p.lay), blk(s->D), a);
+      break;
+    }
+    case 4: vcycle(s, 0, arg); break;
+    case 5: smooth(s, s->lv[level], arg, nullptr); break;
+    case 6: jacobi(s, s->lv[level]); break;
+    case 7: exitbc(s, s->u, s->u0, s->dt); break;
+    case 8: ghost_phi(s); mom_rhs(s, s->u, nullptr); bdim(s, 1); break;
+    case 9: cudaMemcpyAsync(s->u0.alloc, s->u.alloc, s->u.bytes, cudaMemcpyDeviceToDevice, s->st); break;
+    default: return fail(s, WL_ERR_INVALID, "unknown debug op");
+  }
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  return check_async(s, "wl_debug_op");
+}
+
+int wl_sync(wl_sim* s) {
+  if (!s) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  return WL_OK;
+}
+int64_t wl_launch_count(const wl_sim* s) { return s ? s->launches : 0; }
+int wl_enable_timing(wl_sim* s, int on) { if (!s) return WL_ERR_INVALID; s->timing = on != 0; return WL_OK; }
+int wl_last_phase_times(const wl_sim* s, double out[8]) {
+  if (!s || !out) return WL_ERR_INVALID;
+  for (int i = 0; i < 8; ++i) out[i] = s->phase_s[i];
+  return WL_OK;
+}
+
+}  // extern "C"

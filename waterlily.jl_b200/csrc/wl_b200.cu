@@ -1,0 +1,343 @@
+// wl_b200.cu -- host side of libwaterlily_b200.so: device state, kernel orchestration of
+// mom_step! / solver! / update! / measure!, and the C ABI declared in include/wl_b200.h.
+// There is no CPU fallback anywhere in this file: without an sm_100 device wl_create fails.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/wl_b200.h"
+#include "wl_common.cuh"
+#include "wl_kernels_body.cuh"
+#include "wl_kernels_mg.cuh"
+#include "wl_kernels_mom.cuh"
+
+using namespace wl;
+
+namespace {
+
+std::string g_create_error;
+
+struct DevField {
+  float* alloc = nullptr;
+  float* base = nullptr;   // element (0,0,0) of component 0
+  Lay lay{};
+  int ncomp = 0;
+  size_t bytes = 0;
+};
+
+struct Level {
+  Lay lay{};
+  DevField L, x, z, r, eps, Dg, iD;
+  bool owns = false;
+  int c[3] = {0, 0, 0};
+};
+
+constexpr int NRED = 8;
+
+}  // namespace
+
+struct wl_sim {
+  wl_config cfg{};
+  int D = 3;
+  Lay lay{};
+  Per per{};
+  DevField u, u0, f, p, sigma, V, mu0, mu1;
+  std::vector<Level> lv;
+  cudaStream_t st = nullptr;
+  RedWork redw{};
+  Red* d_red = nullptr;
+  Red* h_red = nullptr;
+  float dt = 0.25f;
+  std::string err;
+  int64_t launches = 0;
+  int device = 0;
+  bool timing = false;
+  cudaEvent_t ev[8] = {};
+  double phase_s[8] = {};
+  int status = WL_OK;
+};
+
+namespace {
+
+#define WL_CUDA(s, call)                                                                   \
+  do {                                                                                     \
+    cudaError_t e_ = (call);                                                               \
+    if (e_ != cudaSuccess) {                                                               \
+      (s)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                       \
+      (s)->status = WL_ERR_CUDA;                                                           \
+      return WL_ERR_CUDA;                                                                  \
+    }                                                                                      \
+  } while (0)
+
+int alloc_field(wl_sim* s, DevField& f, const Lay& lay, int ncomp) {
+  f.lay = lay; f.ncomp = ncomp;
+  f.bytes = (size_t)lay.cstride * ncomp * sizeof(float) + 256;
+  WL_CUDA(s, cudaMalloc(&f.alloc, f.bytes));
+  WL_CUDA(s, cudaMemsetAsync(f.alloc, 0, f.bytes, s->st));
+  f.base = f.alloc + LPAD;
+  return WL_OK;
+}
+void free_field(DevField& f) { if (f.alloc) cudaFree(f.alloc); f.alloc = f.base = nullptr; }
+
+dim3 blk(int D) { return D == 3 ? dim3(32, 4, 2) : dim3(32, 8, 1); }
+dim3 grid_inside(const Lay& l) {
+  dim3 b = blk(l.D);
+  return dim3((l.n0 - 2 + 31) / 32, (l.n1 - 2 + b.y - 1) / b.y, l.D == 3 ? (l.n2 - 2 + b.z - 1) / b.z : 1);
+}
+dim3 grid_all(const Lay& l) {
+  dim3 b = blk(l.D);
+  return dim3((l.n0 + LPAD + 31) / 32, (l.n1 + b.y - 1) / b.y, l.D == 3 ? (l.n2 + b.z - 1) / b.z : 1);
+}
+// plane kernels: threads over (fast in-plane dim, slow in-plane dim); sized for the largest plane
+void plane_launch(const Lay& l, dim3& g, dim3& b) {
+  int m = l.n0 > l.n1 ? l.n0 : l.n1;
+  int m2 = l.D == 3 ? (l.n1 > l.n2 ? l.n1 : l.n2) : 1;
+  b = l.D == 3 ? dim3(32, 8, 1) : dim3(128, 1, 1);
+  g = dim3((m + b.x - 1) / b.x, (m2 + b.y - 1) / b.y, 1);
+}
+
+#define LAUNCH(s, kern, g, b, ...)                 \
+  do {                                             \
+    kern<<<g, b, 0, (s)->st>>>(__VA_ARGS__);       \
+    ++(s)->launches;                               \
+  } while (0)
+
+#define DISPATCH_D(s, kern, g, b, ...)                                    \
+  do {                                                                    \
+    if ((s)->D == 3) LAUNCH(s, kern<3>, g, b, __VA_ARGS__);               \
+    else LAUNCH(s, kern<2>, g, b, __VA_ARGS__);                           \
+  } while (0)
+
+#define DISPATCH_DS(s, kern, g, b, ...)                                                   \
+  do {                                                                                    \
+    const int sc_ = (s)->cfg.scheme;                                                      \
+    if ((s)->D == 3) {                                                                    \
+      if (sc_ == 0) LAUNCH(s, (kern<3, 0>), g, b, __VA_ARGS__);                           \
+      else if (sc_ == 1) LAUNCH(s, (kern<3, 1>), g, b, __VA_ARGS__);                      \
+      else LAUNCH(s, (kern<3, 2>), g, b, __VA_ARGS__);                                    \
+    } else {                                                                              \
+      if (sc_ == 0) LAUNCH(s, (kern<2, 0>), g, b, __VA_ARGS__);                           \
+      else if (sc_ == 1) LAUNCH(s, (kern<2, 1>), g, b, __VA_ARGS__);                      \
+      else LAUNCH(s, (kern<2, 2>), g, b, __VA_ARGS__);                                    \
+    }                                                                                     \
+  } while (0)
+
+// ---------------------------------------------------------------- boundary conditions
+void bc_vec(wl_sim* s, DevField& a, const float* U, bool saveexit) {
+  BcArgs args;
+  args.l = a.lay; args.a = a.base; args.per = s->per; args.saveexit = saveexit ? 1 : 0;
+  for (int d = 0; d < 3; ++d) args.U.v[d] = U ? U[d] : 0.f;
+  dim3 g, b;
+  plane_launch(a.lay, g, b);
+  g.z = 3 * s->D;
+  DISPATCH_D(s, k_bc_vec, g, b, args);
+}
+void perbc(wl_sim* s, const Lay& l, float* a) {
+  for (int d = 0; d < s->D; ++d) {
+    if (!s->per.p[d]) continue;
+    PerArgs args{l, a, d};
+    dim3 g, b;
+    plane_launch(l, g, b);
+    DISPATCH_D(s, k_perbc, g, b, args);
+  }
+}
+void exitbc(wl_sim* s, DevField& u, DevField& u0, float dt) {
+  ExitArgs args{u.lay, u.base, u0.base, dt};
+  DISPATCH_D(s, k_exitbc, dim3(1), dim3(1024), args);
+}
+
+// ---------------------------------------------------------------- multigrid pieces
+LevArgs lev_args(wl_sim* s, Level& p) {
+  LevArgs a{};
+  a.l = p.lay; a.L = p.L.base; a.x = p.x.base; a.r = p.r.base; a.eps = p.eps.base; a.z = p.z.base;
+  a.omega = 1.f; a.k0 = 0; a.w = s->redw; a.out = s->d_red; a.in = s->d_red; a.want_norms = 0;
+  return a;
+}
+void set_diag(wl_sim* s, Level& p) {
+  DiagArgs a{p.lay, p.L.base, p.Dg.base, p.iD.base};
+  DISPATCH_D(s, k_set_diag, grid_inside(p.lay), blk(s->D), a);
+}
+void increment(wl_sim* s, Level& p, float w, Red* norms) {
+  perbc(s, p.lay, p.eps.base);
+  LevArgs a = lev_args(s, p);
+  a.omega = w; a.want_norms = norms ? 1 : 0; a.out = norms ? norms : s->d_red;
+  DISPATCH_D(s, k_increment, grid_inside(p.lay), blk(s->D), a);
+}
+// Jacobi!(p) with it=1, ω=1 (Poisson.jl:111-114)
+void jacobi(wl_sim* s, Level& p) {
+  LevArgs a = lev_args(s, p);
+  DISPATCH_D(s, k_eps_init, grid_inside(p.lay), blk(s->D), a);
+  increment(s, p, 1.f, nullptr);
+}
+// GaussSeidelRB!(p;it=4,ω) (Poisson.jl:141-148)
+void smooth(wl_sim* s, Level& p, float w, Red* norms) {
+  LevArgs a = lev_args(s, p);
+  DISPATCH_D(s, k_eps_init, grid_inside(p.lay), blk(s->D), a);
+  perbc(s, p.lay, p.eps.base);
+  for (int k0 = 1; k0 <= 4; ++k0) {
+    a.k0 = k0;
+    DISPATCH_D(s, k_gs_half, grid_inside(p.lay), blk(s->D), a);
+  }
+  increment(s, p, w, norms);
+}
+void restrict_r(wl_sim* s, Level& fi, Level& co) {
+  XferArgs a{fi.lay, co.lay, fi.r.base, co.r.base, {co.c[0], co.c[1], co.c[2]}};
+  DISPATCH_D(s, k_restrict, grid_inside(co.lay), blk(s->D), a);
+}
+void prolongate(wl_sim* s, Level& fi, Level& co) {
+  XferArgs a{fi.lay, co.lay, co.x.base, fi.eps.base, {co.c[0], co.c[1], co.c[2]}};
+  DISPATCH_D(s, k_prolongate, grid_inside(fi.lay), blk(s->D), a);
+}
+void restrictL(wl_sim* s, Level& fi, Level& co) {
+  XferLArgs a{fi.lay, co.lay, fi.L.base, co.L.base, {co.c[0], co.c[1], co.c[2]}};
+  DISPATCH_D(s, k_restrictL, grid_inside(co.lay), blk(s->D), a);
+  bc_vec(s, co.L, nullptr, false);
+}
+// Vcycle!(ml;l,ω) (MultiLevelPoisson.jl:88-101)
+void vcycle(wl_sim* s, size_t l, float w) {
+  Level &fine = s->lv[l], &coarse = s->lv[l + 1];
+  jacobi(s, fine);
+  restrict_r(s, fine, coarse);
+  cudaMemsetAsync(coarse.x.alloc, 0, coarse.x.bytes, s->st);
+  if (l + 2 < s->lv.size()) vcycle(s, l + 1, w);
+  smooth(s, coarse, w, nullptr);
+  prolongate(s, fine, coarse);
+  increment(s, fine, w, nullptr);
+}
+
+int fetch_red(wl_sim* s) {
+  WL_CUDA(s, cudaMemcpyAsync(s->h_red, s->d_red, sizeof(Red) * NRED, cudaMemcpyDeviceToHost, s->st));
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  return WL_OK;
+}
+
+struct Trace { int n = 0; int flags = 0; float rinf[34], r1[34], omega[34]; };
+
+// solver!(ml;tol,itmx) (MultiLevelPoisson.jl:108-128).  The loop exit and ω are steered by two
+// scalars per iteration, exactly as in the reference.
+int mlp_solver(wl_sim* s, Trace* tr) {
+  Level& p = s->lv[0];
+  const double tol = s->cfg.tol;
+  const double r1tol = (tol / 10) * (double)p.lay.ninside(), rinftol = tol;
+  const int itmx = s->cfg.itmx;
+  perbc(s, p.lay, p.x.base);
+  {
+    LevArgs a = lev_args(s, p);
+    a.out = s->d_red + 0;
+    DISPATCH_D(s, k_residual, grid_inside(p.lay), blk(s->D), a);
+    a.in = s->d_red + 0; a.out = s->d_red + 1;
+    DISPATCH_D(s, k_shift_norms, grid_inside(p.lay), blk(s->D), a);
+  }
+  if (int e = fetch_red(s)) return e;
+  float r1 = (float)s->h_red[1].sum, rinf = s->h_red[1].maxv, w = 1.f;
+  int np = 0, flags = 0;
+  if (tr) { tr->rinf[0] = rinf; tr->r1[0] = r1; tr->omega[0] = w; }
+  while (np < itmx) {
+    vcycle(s, 0, w);
+    smooth(s, p, w, s->d_red + 1);
+    if (int e = fetch_red(s)) return e;
+    const float rnew = (float)s->h_red[1].sum;
+    rinf = s->h_red[1].maxv; ++np;
+    if (tr && np < 34) { tr->rinf[np] = rinf; tr->r1[np] = rnew; tr->omega[np] = w; }
+    if (rnew >= r1) w = (float)std::fmax(0.2, 0.9 * (double)w);
+    else if (rnew < r1) w = (float)std::fmin(1.0, 1.02 * (double)w);
+    r1 = rnew;
+    if (!std::isfinite(rnew)) flags |= 1;
+    if ((double)r1 < r1tol && (double)rinf < rinftol) break;
+  }
+  if (np >= itmx) flags |= 2;
+  perbc(s, p.lay, p.x.base);
+  if (tr) { tr->n = np; tr->flags = flags; }
+  return WL_OK;
+}
+
+// ---------------------------------------------------------------- momentum pieces
+void mom_rhs(wl_sim* s, DevField& uadv, const float* acc) {
+  MomArgs a{};
+  a.l = s->lay; a.ua = uadv.base; a.u0 = s->u0.base; a.V = s->V.base; a.f = s->f.base;
+  a.per = s->per; a.nu = s->cfg.nu; a.dt = s->dt;
+  for (int d = 0; d < 3; ++d) a.acc.v[d] = acc ? acc[d] : 0.f;
+  DISPATCH_DS(s, k_mom_rhs, grid_all(s->lay), blk(s->D), a);
+}
+void bdim(wl_sim* s, int corrector) {
+  BdimArgs a{s->lay, s->u.base, s->f.base, s->V.base, s->mu0.base, s->mu1.base, corrector};
+  DISPATCH_D(s, k_bdim, grid_inside(s->lay), blk(s->D), a);
+}
+// mom_project!(a,b,w,t) (Flow.jl:223-232)
+int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
+  ProjArgs a{s->lay, s->u.base, s->p.base, s->sigma.base, s->mu0.base, w * s->dt};
+  DISPATCH_D(s, k_div_scale, grid_all(s->lay), blk(s->D), a);
+  if (int e = mlp_solver(s, tr)) return e;
+  DISPATCH_D(s, k_project, grid_inside(s->lay), blk(s->D), a);
+  DISPATCH_D(s, k_unscale, grid_all(s->lay), blk(s->D), a);
+  bc_vec(s, s->u, U, s->cfg.exitBC != 0);
+  return WL_OK;
+}
+int cfl(wl_sim* s, float* out) {
+  CflArgs a{s->lay, s->u.base, s->sigma.base, s->redw, s->d_red + 2};
+  DISPATCH_D(s, k_cfl, grid_all(s->lay), blk(s->D), a);
+  if (int e = fetch_red(s)) return e;
+  const float m = s->h_red[2].maxv;
+  *out = std::fmin(10.f, 1.f / (m + 5.f * s->cfg.nu));
+  return WL_OK;
+}
+void ghost_phi(wl_sim* s) {
+  GhostPhiArgs a{s->lay, s->u.base, s->sigma.base, s->per, s->cfg.nu};
+  dim3 g, b;
+  plane_launch(s->lay, g, b);
+  g.z = s->D;
+  DISPATCH_DS(s, k_ghost_phi, g, b, a);
+}
+
+BodyDev body_at(const wl_body* b, int D, float t) {
+  BodyDev d{};
+  d.kind = b->kind; d.axis = b->axis; d.radius = b->radius; d.minor = b->minor;
+  for (int k = 0; k < 3; ++k) { d.c[k] = 0.f; d.Vb[k] = 0.f; }
+  for (int k = 0; k < D; ++k) {
+    d.c[k] = b->center[k] + b->vel[k] * t + b->acc[k] * t * t + b->amp[k] * std::sin(b->omega * t);
+    d.Vb[k] = b->vel[k] + 2 * b->acc[k] * t + b->amp[k] * b->omega * std::cos(b->omega * t);
+  }
+  return d;
+}
+
+DevField* flow_field(wl_sim* s, int field, int level, Lay* lay) {
+  DevField* f = nullptr;
+  if (field < 10) {
+    switch (field) {
+      case WL_U: f = &s->u; break;
+      case WL_U0: f = &s->u0; break;
+      case WL_F: f = &s->f; break;
+      case WL_P: f = &s->p; break;
+      case WL_SIGMA: f = &s->sigma; break;
+      case WL_V: f = &s->V; break;
+      case WL_MU0: f = &s->mu0; break;
+      case WL_MU1: f = &s->mu1; break;
+      default: return nullptr;
+    }
+  } else {
+    if (level < 0 || level >= (int)s->lv.size()) return nullptr;
+    Level& l = s->lv[level];
+    switch (field) {
+      case WL_X: f = &l.x; break;
+      case WL_R: f = &l.r; break;
+      case WL_EPS: f = &l.eps; break;
+      case WL_Z: f = &l.z; break;
+      case WL_L: f = &l.L; break;
+      case WL_DIAG: f = &l.Dg; break;
+      case WL_IDIAG: f = &l.iD; break;
+      default: return nullptr;
+    }
+  }
+  if (lay) *lay = f->lay;
+  return f;
+}
+
+inline bool divisible(int N) { return N % 2 == 0 && N > 4; }
+
+}  // namespace
+
+#include "wl_abi.cuh"

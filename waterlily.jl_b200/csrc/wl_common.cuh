@@ -1,0 +1,123 @@
+// wl_common.cuh -- device layout and small helpers shared by the sm_100a kernels.
+//
+// Device layout of one scalar field of Julia size (n0,n1,n2) (ghosts included; n2==1 in 2D):
+//   element (i,j,k) lives at  base[i + pitch*j + plane*k],  plane = pitch*n1.
+// `pitch` is a multiple of 32 floats and `base` is chosen so that the FIRST INTERIOR element
+// (i==1) of every row starts a 128-byte line: a warp that owns 32 consecutive interior cells
+// stores exactly one full line.  Vector fields are `ncomp` such scalars `cstride` floats apart.
+// The padding is invisible through the C ABI (upload/download repack).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace wl {
+
+constexpr int LPAD = 31;   // floats in front of i==0 so that i==1 is 128-byte aligned
+
+struct Lay {
+  int n0, n1, n2;    // sizes including ghosts (n2 == 1 for D == 2)
+  int D;
+  int pitch, plane;  // floats
+  long long cstride; // floats between components of a vector field
+  __host__ __device__ int off(int i, int j, int k) const { return i + pitch * j + plane * k; }
+  __host__ __device__ int n(int d) const { return d == 0 ? n0 : d == 1 ? n1 : n2; }
+  __host__ __device__ int stride(int d) const { return d == 0 ? 1 : d == 1 ? pitch : plane; }
+  __host__ __device__ long long ninside() const {
+    long long c = (long long)(n0 - 2) * (n1 - 2);
+    return D == 3 ? c * (n2 - 2) : c;
+  }
+};
+
+inline Lay make_lay(int D, const int* ng) {
+  Lay l;
+  l.D = D;
+  l.n0 = ng[0]; l.n1 = ng[1]; l.n2 = D == 3 ? ng[2] : 1;
+  l.pitch = ((l.n0 + 31) / 32) * 32;
+  if (l.pitch < l.n0 + 0) l.pitch += 32;
+  l.plane = l.pitch * l.n1;
+  long long vol = (long long)l.plane * l.n2;
+  l.cstride = ((vol + 64 + 31) / 32) * 32;   // +LPAD front, slack behind for vector tails
+  return l;
+}
+
+struct Per { int p[3]; };
+struct Vec3 { float v[3]; };
+
+// ---- deterministic block reduction helpers (warp shuffle -> smem -> thread 0)
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_down_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Result slots of the scalar reductions (device memory mirrored into pinned host memory).
+struct Red {
+  double sum;       // Σ r   (residual!)  or Σ|r| (L₁)
+  float  maxv;      // max|r| (L∞) or max σ (CFL)
+  float  pad;
+};
+
+// Two-stage, order-fixed reduction: every block writes one partial; the last block to finish
+// (ticket counter) folds the partials in index order, so the result does not depend on the
+// order blocks ran in (iteration counts must not depend on scheduling).
+struct RedWork {
+  double* psum;          // [maxblocks]
+  float* pmax;           // [maxblocks]
+  unsigned int* ticket;  // zero before and after every use
+};
+
+__device__ __forceinline__ int linear_tid() {
+  return threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
+}
+__device__ __forceinline__ int linear_bid() {
+  return blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+}
+
+// Call from ALL threads of the block (contains __syncthreads).  `out` receives the result.
+__device__ __forceinline__ void block_reduce_finish(double s, float m, const RedWork w, Red* out) {
+  __shared__ double ssum[32];
+  __shared__ float smax[32];
+  __shared__ bool last;
+  const int tid = linear_tid();
+  const int nthr = blockDim.x * blockDim.y * blockDim.z;
+  const int lane = tid & 31, wid = tid >> 5, nw = (nthr + 31) >> 5;
+  s = warp_sum(s); m = warp_max(m);
+  if (lane == 0) { ssum[wid] = s; smax[wid] = m; }
+  __syncthreads();
+  const int nblocks = gridDim.x * gridDim.y * gridDim.z;
+  if (wid == 0) {
+    s = lane < nw ? ssum[lane] : 0.0;
+    m = lane < nw ? smax[lane] : -INFINITY;
+    s = warp_sum(s); m = warp_max(m);
+    if (lane == 0) {
+      const int b = linear_bid();
+      w.psum[b] = s; w.pmax[b] = m;
+      __threadfence();
+      unsigned int t = atomicAdd(w.ticket, 1u);
+      last = (t == (unsigned)nblocks - 1);
+    }
+  }
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  // fixed-order fold: thread t takes partials t, t+nthr, ...; then the same tree as above
+  double a = 0.0; float mm = -INFINITY;
+  for (int i = tid; i < nblocks; i += nthr) { a += __ldcg(&w.psum[i]); mm = fmaxf(mm, __ldcg(&w.pmax[i])); }
+  a = warp_sum(a); mm = warp_max(mm);
+  __syncthreads();
+  if (lane == 0) { ssum[wid] = a; smax[wid] = mm; }
+  __syncthreads();
+  if (wid == 0) {
+    a = lane < nw ? ssum[lane] : 0.0;
+    mm = lane < nw ? smax[lane] : -INFINITY;
+    a = warp_sum(a); mm = warp_max(mm);
+    if (lane == 0) { out->sum = a; out->maxv = mm; *w.ticket = 0u; }
+  }
+}
+
+}  // namespace wl

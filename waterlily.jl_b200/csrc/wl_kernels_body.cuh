@@ -1,0 +1,173 @@
+// wl_kernels_body.cuh -- device-side measure! for parametric bodies and pressure_force.
+// Reference: src/Body.jl:28-60, src/AutoBody.jl:29-37, src/Metrics.jl:116-133.
+#pragma once
+#include "wl_common.cuh"
+
+namespace wl {
+
+struct BodyDev {
+  int kind, axis;
+  float c[3];      // centre(t), evaluated on the host in Float32
+  float Vb[3];     // d centre / dt
+  float radius, minor;
+};
+
+struct Meas { float d; float n[3]; float V[3]; };
+
+// measure(body::AutoBody,x,t;fastd²) AutoBody.jl:29-37 with J = I and the closed-form gradient.
+template <int D>
+__device__ __forceinline__ Meas measure_pt(const BodyDev& b, const float* x, float fastd2) {
+  Meas m;
+  m.d = INFINITY;
+#pragma unroll
+  for (int q = 0; q < 3; ++q) m.n[q] = m.V[q] = 0.f;
+  if (b.kind == 0) return m;
+  float xi[3] = {0.f, 0.f, 0.f}, g[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+  for (int q = 0; q < D; ++q) xi[q] = x[q] - b.c[q];
+  float d;
+  if (b.kind == 1) {
+    float s = 0.f;
+#pragma unroll
+    for (int q = 0; q < D; ++q) s += xi[q] * xi[q];
+    const float rt = sqrtf(s);
+    d = rt - b.radius;
+#pragma unroll
+    for (int q = 0; q < D; ++q) g[q] = xi[q] / rt;
+  } else if (b.kind == 2) {
+    float s = 0.f;
+#pragma unroll
+    for (int q = 0; q < D; ++q) if (q != b.axis) s += xi[q] * xi[q];
+    const float rt = sqrtf(s);
+    d = rt - b.radius;
+#pragma unroll
+    for (int q = 0; q < D; ++q) g[q] = q == b.axis ? 0.f : xi[q] / rt;
+  } else {
+    float s = 0.f, xa = 0.f;
+#pragma unroll
+    for (int q = 0; q < D; ++q) { if (q != b.axis) s += xi[q] * xi[q]; else xa = xi[q]; }
+    const float rho = sqrtf(s), qq = rho - b.radius;
+    const float len = sqrtf(qq * qq + xa * xa);
+    d = len - b.minor;
+#pragma unroll
+    for (int q = 0; q < D; ++q) g[q] = q == b.axis ? xi[q] / len : (qq / len) * (xi[q] / rho);
+  }
+  m.d = d;
+  if (d * d > fastd2) return m;
+  bool nan = false;
+#pragma unroll
+  for (int q = 0; q < D; ++q) nan |= isnan(g[q]);
+  if (nan) return m;
+  float mm = 0.f;
+#pragma unroll
+  for (int q = 0; q < D; ++q) mm += g[q] * g[q];
+  mm = sqrtf(mm);
+  m.d = d / mm;
+#pragma unroll
+  for (int q = 0; q < D; ++q) { m.n[q] = g[q] / mm; m.V[q] = b.Vb[q]; }
+  return m;
+}
+
+// kernels Body.jl:54-60
+__device__ __forceinline__ float kern(float d) { return (1.f + cospif(d)) / 2.f; }
+__device__ __forceinline__ float kern0(float d) { return (1.f + d + sinpif(d) / 3.14159265358979323846f) / 2.f; }
+__device__ __forceinline__ float kern1(float d) {
+  const float pi = 3.14159265358979323846f;
+  return (1.f - d * d) / 4.f - (d * sinpif(d) + (1.f + cospif(d)) / pi) / (2.f * pi);
+}
+__device__ __forceinline__ float mu0f(float d, float e) {
+  const float ad = fabsf(d);
+  const float ulp = nextafterf(ad, INFINITY) - ad;        // eps(d)
+  return d / e < -1.f + sqrtf(ulp) ? 0.f : kern0(fminf(d / e, 1.f));
+}
+__device__ __forceinline__ float mu1f(float d, float e) { return e * kern1(fmaxf(-1.f, fminf(d / e, 1.f))); }
+
+struct MeasArgs {
+  Lay l;
+  BodyDev b;
+  float eps;
+  float* sigma; float* V; float* mu0; float* mu1;
+};
+
+// measure! (Body.jl:28-48) in one pass over ALL cells: the three fills of :29, measure_sdf! :30
+// and the band loop :31-48.  Ghost cells get V=0, μ₀=1, μ₁=0 (σ untouched); BC! follows.
+template <int D>
+__global__ void __launch_bounds__(256) k_measure(const MeasArgs a) {
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z : 0;
+  if (i < 0 || i >= l.n0 || j >= l.n1 || k >= l.n2) return;
+  const int o = l.off(i, j, k);
+  const bool in = i >= 1 && i <= l.n0 - 2 && j >= 1 && j <= l.n1 - 2 && (D == 2 || (k >= 1 && k <= l.n2 - 2));
+  float Vv[3] = {0.f, 0.f, 0.f}, m0[3] = {1.f, 1.f, 1.f}, m1[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (in) {
+    const float d2 = (2.f + a.eps) * (2.f + a.eps);
+    float x[3] = {(float)i - 0.5f, (float)j - 0.5f, (float)k - 0.5f};
+    const float sd = measure_pt<D>(a.b, x, 0.f).d;          // sdf(body,x,t) raw
+    a.sigma[o] = sd;
+    if (sd * sd < d2) {
+#pragma unroll
+      for (int ci = 0; ci < D; ++ci) {
+        float xf[3] = {x[0], x[1], x[2]};
+        xf[ci] -= 0.5f;                                       // loc(i,I) core.jl:177
+        const Meas m = measure_pt<D>(a.b, xf, d2);
+        const float di = fabsf(m.d) <= 0.5f ? m.d : copysignf(m.d, sd);
+        Vv[ci] = m.V[ci];
+        m0[ci] = mu0f(di, a.eps);
+        const float w1 = mu1f(di, a.eps);
+#pragma unroll
+        for (int dj = 0; dj < D; ++dj) m1[ci + D * dj] = w1 * m.n[dj];
+      }
+    } else if (sd < 0.f) {
+#pragma unroll
+      for (int ci = 0; ci < D; ++ci) m0[ci] = 0.f;
+    }
+  }
+#pragma unroll
+  for (int ci = 0; ci < D; ++ci) {
+    a.V[l.cstride * ci + o] = Vv[ci];
+    a.mu0[l.cstride * ci + o] = m0[ci];
+  }
+#pragma unroll
+  for (int q = 0; q < D * D; ++q) a.mu1[l.cstride * q + o] = m1[q];
+}
+
+// pressure_force (Metrics.jl:126-133): df = p·nds over inside (df ≡ flow.f, zero elsewhere).
+struct ForceArgs { Lay l; BodyDev b; const float* p; float* f; };
+template <int D>
+__global__ void __launch_bounds__(256) k_force_df(const ForceArgs a) {
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z : 0;
+  if (i < 0 || i >= l.n0 || j >= l.n1 || k >= l.n2) return;
+  const int o = l.off(i, j, k);
+  const bool in = i >= 1 && i <= l.n0 - 2 && j >= 1 && j <= l.n1 - 2 && (D == 2 || (k >= 1 && k <= l.n2 - 2));
+  float df[3] = {0.f, 0.f, 0.f};
+  if (in) {
+    const float x[3] = {(float)i - 0.5f, (float)j - 0.5f, (float)k - 0.5f};
+    const Meas m = measure_pt<D>(a.b, x, 1.f);
+    const float kq = kern(fmaxf(-1.f, fminf(m.d, 1.f)));
+    const float pv = a.p[o];
+#pragma unroll
+    for (int ci = 0; ci < D; ++ci) df[ci] = pv * (m.n[ci] * kq);
+  }
+#pragma unroll
+  for (int ci = 0; ci < D; ++ci) a.f[l.cstride * ci + o] = df[ci];
+}
+
+// Σ over the whole array of one scalar, in Float64 (sum(To,df,dims=...) Metrics.jl:132)
+struct SumArgs { Lay l; const float* a; RedWork w; Red* out; };
+template <int D>
+__global__ void __launch_bounds__(256) k_sum_all(const SumArgs a) {
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z : 0;
+  double s = 0.0;
+  if (i >= 0 && i < l.n0 && j < l.n1 && k < l.n2) s = (double)a.a[l.off(i, j, k)];
+  block_reduce_finish(s, -INFINITY, a.w, a.out);
+}
+
+}  // namespace wl

@@ -1,0 +1,221 @@
+// wl_kernels_mg.cuh -- pressure-side kernels: operator, residual!, Jacobi!/GaussSeidelRB!/increment!,
+// restrict!/prolongate!, restrictL!/set_diag!.  Reference: src/Poisson.jl, src/MultiLevelPoisson.jl.
+// D and iD are never read on the hot path: they are recomputed from L in the reference's own
+// summation order (`diag`, Poisson.jl:49-55), which is bit-identical and saves 4-8 B/cell.
+#pragma once
+#include "wl_common.cuh"
+
+namespace wl {
+
+struct LevArgs {
+  Lay l;
+  const float* L;
+  float* x;
+  float* r;
+  float* eps;
+  const float* z;
+  float omega;
+  int k0;            // GS colour pass 1..4
+  RedWork w;
+  Red* out;
+  const Red* in;     // residual mean input (k_shift_norms)
+  int want_norms;
+};
+
+#define WL_INTERIOR_IJK(D, l)                                                   \
+  const int i = blockIdx.x * 32 + threadIdx.x + 1;                              \
+  const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;                      \
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;         \
+  const bool inb = !(i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && k > l.n2 - 2));
+
+// `diag(I,L)` Poisson.jl:49-55
+template <int D>
+__device__ __forceinline__ float diagL(const Lay& l, const float* __restrict__ L, int o) {
+  const int st[3] = {1, l.pitch, l.plane};
+  float s = 0.f;
+#pragma unroll
+  for (int d = 0; d < D; ++d) { const float* Ld = L + l.cstride * d; s -= Ld[o] + Ld[o + st[d]]; }
+  return s;
+}
+__device__ __forceinline__ float inv_or_zero(float d) { return d == 0.f ? d : 1.f / d; }   // Poisson.jl:45
+// `mult(I,L,D,x)` Poisson.jl:70-76
+template <int D>
+__device__ __forceinline__ float multA(const Lay& l, const float* __restrict__ L, const float* __restrict__ x, int o) {
+  const int st[3] = {1, l.pitch, l.plane};
+  float s = x[o] * diagL<D>(l, L, o);
+#pragma unroll
+  for (int d = 0; d < D; ++d) {
+    const float* Ld = L + l.cstride * d;
+    s += x[o - st[d]] * Ld[o] + x[o + st[d]] * Ld[o + st[d]];
+  }
+  return s;
+}
+
+// set_diag! (Poisson.jl:43-46): materialises D and iD for the data surface only.
+struct DiagArgs { Lay l; const float* L; float* Dg; float* iD; };
+template <int D>
+__global__ void __launch_bounds__(256) k_set_diag(const DiagArgs a) {
+  const Lay& l = a.l;
+  WL_INTERIOR_IJK(D, l)
+  if (!inb) return;
+  const int o = l.off(i, j, k);
+  const float d = diagL<D>(l, a.L, o);
+  a.Dg[o] = d;
+  a.iD[o] = inv_or_zero(d);
+}
+
+// residual! first loop (Poisson.jl:94) + Σr partials.  perBC!(x) has been applied by the caller.
+template <int D>
+__global__ void __launch_bounds__(256) k_residual(const LevArgs a) {
+  const Lay& l = a.l;
+  WL_INTERIOR_IJK(D, l)
+  double s = 0.0;
+  if (inb) {
+    const int o = l.off(i, j, k);
+    const float d = diagL<D>(l, a.L, o);
+    float r = 0.f;
+    if (d != 0.f) {
+      const int st[3] = {1, l.pitch, l.plane};
+      float ax = a.x[o] * d;
+#pragma unroll
+      for (int q = 0; q < D; ++q) {
+        const float* Lq = a.L + l.cstride * q;
+        ax += a.x[o - st[q]] * Lq[o] + a.x[o + st[q]] * Lq[o + st[q]];
+      }
+      r = a.z[o] - ax;
+    }
+    a.r[o] = r;
+    s = (double)r;
+  }
+  block_reduce_finish(s, -INFINITY, a.w, a.out);
+}
+
+// residual! second loop (Poisson.jl:95-97) fused with the initial L₁/L∞ (MultiLevelPoisson.jl:111):
+// s = Σr/N in Float32; if |s| > 2eps: r -= s inside.  Norms of the resulting r.
+template <int D>
+__global__ void __launch_bounds__(256) k_shift_norms(const LevArgs a) {
+  const Lay& l = a.l;
+  WL_INTERIOR_IJK(D, l)
+  const float s = (float)a.in->sum / (float)l.ninside();
+  const bool shift = fabsf(s) > 2.f * 1.1920929e-07f;
+  double s1 = 0.0; float m = -INFINITY;
+  if (inb) {
+    const int o = l.off(i, j, k);
+    float r = a.r[o];
+    if (shift) { r = r - s; a.r[o] = r; }
+    s1 = (double)fabsf(r); m = fabsf(r);
+  }
+  block_reduce_finish(s1, m, a.w, a.out);
+}
+
+// ϵ = r·iD inside (Jacobi! Poisson.jl:112, GaussSeidelRB! :142)
+template <int D>
+__global__ void __launch_bounds__(256) k_eps_init(const LevArgs a) {
+  const Lay& l = a.l;
+  WL_INTERIOR_IJK(D, l)
+  if (!inb) return;
+  const int o = l.off(i, j, k);
+  a.eps[o] = a.r[o] * inv_or_zero(diagL<D>(l, a.L, o));
+}
+
+// increment! (Poisson.jl:100-104) after the caller's perBC!(ϵ); optional L₁/L∞ of the new r.
+template <int D>
+__global__ void __launch_bounds__(256) k_increment(const LevArgs a) {
+  const Lay& l = a.l;
+  WL_INTERIOR_IJK(D, l)
+  double s1 = 0.0; float m = -INFINITY;
+  if (inb) {
+    const int o = l.off(i, j, k);
+    const float r = a.r[o] - a.omega * multA<D>(l, a.L, a.eps, o);
+    a.r[o] = r;
+    a.x[o] = a.x[o] + a.omega * a.eps[o];
+    s1 = (double)fabsf(r); m = fabsf(r);
+  }
+  if (a.want_norms) block_reduce_finish(s1, m, a.w, a.out);
+}
+
+// One red-black half sweep (gauss_rb Poisson.jl:124-128 over half_rangek :130-132).
+// Sweep k₀ updates the cells whose Julia index sum has parity k₀+1, in the last dimension only up
+// to Julia index 2·(size÷2)−1 (an odd-sized last dimension leaves its last interior cell unswept).
+template <int D>
+__global__ void __launch_bounds__(256) k_gs_half(const LevArgs a) {
+  const Lay& l = a.l;
+  WL_INTERIOR_IJK(D, l)
+  if (!inb) return;
+  const int nl = D == 3 ? l.n2 : l.n1;
+  const int cl = D == 3 ? k : j;
+  if (cl > 2 * (nl / 2) - 2) return;
+  const int jsum = i + j + (D == 3 ? k : 0) + D;          // Julia index sum
+  if (((jsum ^ (a.k0 + 1)) & 1) != 0) return;
+  const int o = l.off(i, j, k);
+  const int st[3] = {1, l.pitch, l.plane};
+  float s = a.r[o];
+  float dg = 0.f;
+#pragma unroll
+  for (int q = 0; q < D; ++q) {
+    const float* Lq = a.L + l.cstride * q;
+    const float lo = Lq[o], hi = Lq[o + st[q]];
+    dg -= lo + hi;
+    s -= a.eps[o - st[q]] * lo + a.eps[o + st[q]] * hi;
+  }
+  a.eps[o] = s * inv_or_zero(dg);
+}
+
+// restrict! (MultiLevelPoisson.jl:13-19,49): coarse r = Σ fine children, first dim fastest.
+struct XferArgs { Lay lf, lc; const float* src; float* dst; int c[3]; };
+template <int D>
+__global__ void __launch_bounds__(256) k_restrict(const XferArgs a) {
+  const Lay& l = a.lc;
+  WL_INTERIOR_IJK(D, l)
+  if (!inb) return;
+  const int cc[3] = {i, j, k};
+  int lo[3], hi[3];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    if (d >= D) { lo[d] = hi[d] = 0; }
+    else if (!a.c[d]) { lo[d] = hi[d] = cc[d]; }
+    else { lo[d] = 2 * cc[d] - 1; hi[d] = 2 * cc[d]; }
+  }
+  float s = 0.f;
+  for (int kk = lo[2]; kk <= hi[2]; ++kk)
+    for (int jj = lo[1]; jj <= hi[1]; ++jj)
+      for (int ii = lo[0]; ii <= hi[0]; ++ii) s += a.src[a.lf.off(ii, jj, kk)];
+  a.dst[l.off(i, j, k)] = s;
+}
+// prolongate! (MultiLevelPoisson.jl:7,50): fine ϵ[I] = coarse x[down(I,c)]
+template <int D>
+__global__ void __launch_bounds__(256) k_prolongate(const XferArgs a) {
+  const Lay& l = a.lf;
+  WL_INTERIOR_IJK(D, l)
+  if (!inb) return;
+  const int ci = a.c[0] ? (i + 1) / 2 : i, cj = a.c[1] ? (j + 1) / 2 : j, ck = (D == 3 && a.c[2]) ? (k + 1) / 2 : k;
+  a.dst[l.off(i, j, k)] = a.src[a.lc.off(ci, cj, ck)];
+}
+// restrictL! interior loop (MultiLevelPoisson.jl:20-26,42-46); BC!(a,0) is applied by the caller.
+struct XferLArgs { Lay lf, lc; const float* Lf; float* Lc; int c[3]; };
+template <int D>
+__global__ void __launch_bounds__(256) k_restrictL(const XferLArgs a) {
+  const Lay& l = a.lc;
+  WL_INTERIOR_IJK(D, l)
+  if (!inb) return;
+  const int cc[3] = {i, j, k};
+#pragma unroll
+  for (int ci = 0; ci < D; ++ci) {
+    int lo[3], hi[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      if (d >= D) { lo[d] = hi[d] = 0; }
+      else if (!a.c[d]) { lo[d] = hi[d] = cc[d]; }
+      else if (d == ci) { lo[d] = hi[d] = 2 * cc[d] - 1; }
+      else { lo[d] = 2 * cc[d] - 1; hi[d] = 2 * cc[d]; }
+    }
+    const float* src = a.Lf + a.lf.cstride * ci;
+    float s = 0.f;
+    for (int kk = lo[2]; kk <= hi[2]; ++kk)
+      for (int jj = lo[1]; jj <= hi[1]; ++jj)
+        for (int ii = lo[0]; ii <= hi[0]; ++ii) s += src[a.lf.off(ii, jj, kk)];
+    a.Lc[l.cstride * ci + l.off(i, j, k)] = a.c[ci] ? s / 2.f : s;
+  }
+}
+
+}  // namespace wl

@@ -1,0 +1,368 @@
+// wl_kernels_mom.cuh -- momentum-side kernels: conv_diff!+accelerate!+BDIM! (RHS and update),
+// BC!, exitBC!, divergence, projection, CFL.  Reference: src/Flow.jl, src/core.jl:192-243.
+#pragma once
+#include "wl_common.cuh"
+
+namespace wl {
+
+// ---------------------------------------------------------------- convective schemes (Flow.jl:4-6,27-36)
+__device__ __forceinline__ float median3(float a, float b, float c) {
+  if (a > b) { if (b >= c) return b; if (a > c) return c; }
+  else       { if (b <= c) return b; if (a < c) return c; }
+  return a;
+}
+template <int S>
+__device__ __forceinline__ float lam(float u, float c, float d) {
+  if (S == 0) return median3((5.f * c + 2.f * d - u) / 6.f, c, median3(10.f * c - 9.f * u, c, d));
+  if (S == 1) return (c + d) / 2.f;
+  return (c <= fminf(u, d) || c >= fmaxf(u, d)) ? c : c + (d - c) * (c - u) / (d - u);
+}
+
+// Φ on the lower j-face of the cell at offset o whose j-coordinate is cj (1..Nj-1):
+// ϕu / ϕuL / ϕuP / ϕuR minus ν∂ (Flow.jl:8-11,47,56-61).  `perj` selects the periodic variant
+// for cj==1; cj==Nj-1 is only evaluated for non-periodic j.
+template <int S>
+__device__ __forceinline__ float face_flux(const float* __restrict__ ui, const float* __restrict__ uj,
+                                           int o, int si, int sj, int cj, int Nj, bool perj, float nu) {
+  const float ua = (uj[o] + uj[o - si]) / 2.f;
+  const float c0 = ui[o], cm = ui[o - sj];
+  const float dif = nu * (c0 - cm);
+  float f;
+  if (cj == 1) {
+    if (ua > 0.f) f = perj ? ua * lam<S>(ui[o + sj * (Nj - 4)], cm, c0) : ua * ((c0 + cm) / 2.f);
+    else f = ua * lam<S>(ui[o + sj], c0, cm);
+  } else if (cj == Nj - 1) {
+    if (ua < 0.f) f = ua * ((c0 + cm) / 2.f);
+    else f = ua * lam<S>(ui[o - 2 * sj], cm, c0);
+  } else {
+    if (ua > 0.f) f = ua * lam<S>(ui[o - 2 * sj], cm, c0);
+    else f = ua * lam<S>(ui[o + sj], c0, cm);
+  }
+  return f - dif;
+}
+
+struct MomArgs {
+  Lay l;
+  const float* ua;   // advecting/advected velocity (u⁰ in the predictor, u in the corrector)
+  const float* u0;   // u⁰
+  const float* V;
+  float* f;
+  Per per;
+  float nu, dt;
+  Vec3 acc;          // accelerate!: space-uniform g+dU/dt
+};
+
+// K-RHS: conv_diff! (Flow.jl:38-62) + accelerate! (:69-73) + first loop of BDIM! (:178):
+//   f[I,i] = u⁰[I,i] + Δt·(r[I,i]+acc_i) − V[I,i]  over ALL indices,
+// with r accumulated exactly in the reference's order (for j: +Φ_low, −Φ_up) and r==0 on cells
+// the reference never writes (any coordinate on the lower ghost).  One thread per cell.
+template <int D, int S>
+__global__ void __launch_bounds__(256) k_mom_rhs(const MomArgs a) {
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x - LPAD;   // lane 31 of block 0 is i==0; i==1 starts a line
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z : 0;
+  if (i < 0 || i >= l.n0 || j >= l.n1 || k >= l.n2) return;
+  const int o = l.off(i, j, k);
+  const int c[3] = {i, j, k};
+  const int N[3] = {l.n0, l.n1, l.n2};
+  const int st[3] = {1, l.pitch, l.plane};
+  bool lowghost = false;
+#pragma unroll
+  for (int d = 0; d < D; ++d) lowghost |= (c[d] == 0);
+#pragma unroll
+  for (int ci = 0; ci < D; ++ci) {
+    const float* ui = a.ua + a.l.cstride * ci;
+    float r = 0.f;
+    if (!lowghost) {
+#pragma unroll
+      for (int dj = 0; dj < D; ++dj) {
+        if (c[dj] > N[dj] - 2) continue;               // upper ghost in j: no j-contribution
+        const float* uj = a.ua + a.l.cstride * dj;
+        const bool pj = a.per.p[dj] != 0;
+        r += face_flux<S>(ui, uj, o, st[ci], st[dj], c[dj], N[dj], pj, a.nu);
+        if (c[dj] == N[dj] - 2 && pj)                  // Φ[CIj(j,I,2)] Flow.jl:62
+          r -= face_flux<S>(ui, uj, o - st[dj] * (N[dj] - 3), st[ci], st[dj], 1, N[dj], true, a.nu);
+        else
+          r -= face_flux<S>(ui, uj, o + st[dj], st[ci], st[dj], c[dj] + 1, N[dj], pj, a.nu);
+      }
+    }
+    r += a.acc.v[ci];
+    const long long oc = a.l.cstride * ci + o;
+    a.f[oc] = a.u0[oc] + a.dt * r - a.V[oc];
+  }
+}
+
+struct BdimArgs {
+  Lay l;
+  float* u;
+  const float* f;
+  const float* V;
+  const float* mu0;
+  const float* mu1;
+  int corrector;     // 0: u = X ; 1: u = (u + X)·½   (scale_u! Flow.jl:209,211-214)
+};
+
+// K-BDIM: second loop of BDIM! (Flow.jl:179) over inside_u, fused with scale_u!.
+template <int D>
+__global__ void __launch_bounds__(256) k_bdim(const BdimArgs a) {
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x + 1;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;
+  if (i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && k > l.n2 - 2)) return;
+  const int o = l.off(i, j, k);
+  const int st[3] = {1, l.pitch, l.plane};
+#pragma unroll
+  for (int ci = 0; ci < D; ++ci) {
+    const long long oc = l.cstride * ci + o;
+    const float* fc = a.f + l.cstride * ci;
+    float s = 0.f;
+#pragma unroll
+    for (int dj = 0; dj < D; ++dj) {
+      const float m = a.mu1[l.cstride * (ci + D * dj) + o];
+      s += m * (fc[o + st[dj]] - fc[o - st[dj]]);       // μddn Flow.jl:20-26
+    }
+    const float X = s / 2.f + a.V[oc] + a.mu0[oc] * fc[o];
+    a.u[oc] = a.corrector ? (a.u[oc] + X) * 0.5f : X;
+  }
+}
+
+// ---------------------------------------------------------------- BC! (core.jl:200-219), fused.
+// The reference fills ghosts with D² sequential passes (component i outer, direction j inner);
+// corner/edge values depend on that order.  Here every written cell resolves its final value in
+// one kernel by walking the passes backwards: the value a pass-j ghost receives is the value its
+// source cell had after passes < j.  The walk always ends either at a Dirichlet constant or at a
+// cell no pass writes, so reading in place is race-free.
+struct BcArgs {
+  Lay l;
+  float* a;
+  Per per;
+  Vec3 U;
+  int saveexit;
+};
+
+template <int D>
+__device__ __forceinline__ float bc_resolve(const BcArgs& a, int ci, int c0, int c1, int c2) {
+  int c[3] = {c0, c1, c2};
+  const int N[3] = {a.l.n0, a.l.n1, a.l.n2};
+#pragma unroll
+  for (int dj = D - 1; dj >= 0; --dj) {
+    const int x = c[dj], n = N[dj];
+    if (a.per.p[dj]) {
+      if (x == 0) c[dj] = n - 2; else if (x == n - 1) c[dj] = 1;
+    } else if (ci == dj) {
+      if (x <= 1 || (x == n - 1 && !(a.saveexit && ci == 0))) return a.U.v[ci];
+    } else {
+      if (x == 0) c[dj] = 1; else if (x == n - 1) c[dj] = n - 2;
+    }
+  }
+  return a.a[a.l.cstride * ci + a.l.off(c[0], c[1], c[2])];
+}
+
+// grid.z enumerates (direction dj, which plane: 0 -> index 0, 1 -> index 1, 2 -> index n-1);
+// threads cover the plane's other two coordinates (fastest remaining dim on threadIdx.x).
+template <int D>
+__global__ void k_bc_vec(const BcArgs a) {
+  const int dj = blockIdx.z / 3, which = blockIdx.z % 3;
+  const Lay& l = a.l;
+  const int N[3] = {l.n0, l.n1, l.n2};
+  const int da = dj == 0 ? 1 : 0;                 // fast in-plane dim
+  const int db = dj == 2 ? 1 : 2;                 // slow in-plane dim (unused in 2D)
+  const int pa = blockIdx.x * blockDim.x + threadIdx.x;
+  const int pb = blockIdx.y * blockDim.y + threadIdx.y;
+  if (pa >= N[da] || (D == 3 ? pb >= N[db] : pb > 0)) return;
+  int c[3] = {0, 0, 0};
+  c[dj] = which == 0 ? 0 : which == 1 ? 1 : N[dj] - 1;
+  c[da] = pa;
+  if (D == 3) c[db] = pb;
+#pragma unroll
+  for (int ci = 0; ci < D; ++ci) {
+    if (which == 1 && (ci != dj || a.per.p[dj])) continue;         // index 1 is only written by Dirichlet
+    if (which == 2 && ci == dj && !a.per.p[dj] && a.saveexit && ci == 0) {
+      // exit plane kept (saveexit): still rewritten by later passes on its edges
+      bool edge = false;
+      for (int d = 0; d < D; ++d) if (d != dj && (c[d] == 0 || c[d] == N[d] - 1)) edge = true;
+      if (!edge) continue;
+    }
+    const float v = bc_resolve<D>(a, ci, c[0], c[1], c[2]);
+    a.a[l.cstride * ci + l.off(c[0], c[1], c[2])] = v;
+  }
+}
+
+// perBC! (core.jl:239-243) for one direction; launched once per periodic direction, in order.
+struct PerArgs { Lay l; float* a; int dj; };
+template <int D>
+__global__ void k_perbc(const PerArgs a) {
+  const Lay& l = a.l;
+  const int N[3] = {l.n0, l.n1, l.n2};
+  const int dj = a.dj;
+  const int da = dj == 0 ? 1 : 0, db = dj == 2 ? 1 : 2;
+  const int pa = blockIdx.x * blockDim.x + threadIdx.x;
+  const int pb = blockIdx.y * blockDim.y + threadIdx.y;
+  if (pa >= N[da] || (D == 3 ? pb >= N[db] : pb > 0)) return;
+  int c[3] = {0, 0, 0};
+  c[da] = pa;
+  if (D == 3) c[db] = pb;
+  const int st = l.stride(dj), n = N[dj];
+  const int o = l.off(c[0], c[1], c[2]);
+  a.a[o] = a.a[o + st * (n - 2)];
+  a.a[o + st * (n - 1)] = a.a[o + st];
+}
+
+// ---------------------------------------------------------------- exitBC! (core.jl:226-233)
+// One block: plane mean, 1-D convection, plane mean, flux correction (sums in double, fixed order).
+struct ExitArgs { Lay l; float* u; const float* u0; float dt; };
+template <int D>
+__global__ void __launch_bounds__(1024) k_exitbc(const ExitArgs a) {
+  __shared__ double sh[32];
+  __shared__ float bcast;
+  const Lay& l = a.l;
+  const int m1 = l.n1 - 2, m2 = D == 3 ? l.n2 - 2 : 1;
+  const int len = m1 * m2;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  auto block_sum = [&](double v) -> double {
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) sh[wid] = v;
+    __syncthreads();
+    double t = 0;
+    if (wid == 0) { t = lane < (blockDim.x >> 5) ? sh[lane] : 0.0; t = warp_sum(t); }
+    return t;   // valid in thread 0
+  };
+  double s = 0;
+  for (int q = tid; q < len; q += blockDim.x) {
+    const int j = 1 + q % m1, k = D == 3 ? 1 + q / m1 : 0;
+    s += (double)a.u[l.off(1, j, k)];
+  }
+  s = block_sum(s);
+  if (tid == 0) bcast = (float)s / (float)len;
+  __syncthreads();
+  const float U = bcast;
+  s = 0;
+  for (int q = tid; q < len; q += blockDim.x) {
+    const int j = 1 + q % m1, k = D == 3 ? 1 + q / m1 : 0;
+    const int o = l.off(l.n0 - 1, j, k);
+    const float v = a.u0[o] - U * a.dt * (a.u0[o] - a.u0[o - 1]);
+    a.u[o] = v;
+    s += (double)v;
+  }
+  s = block_sum(s);
+  __syncthreads();
+  if (tid == 0) bcast = (float)s / (float)len - U;
+  __syncthreads();
+  const float fl = bcast;
+  for (int q = tid; q < len; q += blockDim.x) {
+    const int j = 1 + q % m1, k = D == 3 ? 1 + q / m1 : 0;
+    a.u[l.off(l.n0 - 1, j, k)] -= fl;
+  }
+}
+
+// ---------------------------------------------------------------- projection pieces (Flow.jl:223-232)
+struct ProjArgs { Lay l; float* u; float* x; float* z; const float* L; float dt; };
+
+// z = div(u) inside; x *= dt everywhere (Flow.jl:225)
+template <int D>
+__global__ void __launch_bounds__(256) k_div_scale(const ProjArgs a) {
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z : 0;
+  if (i < 0 || i >= l.n0 || j >= l.n1 || k >= l.n2) return;
+  const int o = l.off(i, j, k);
+  a.x[o] *= a.dt;
+  const bool in = i >= 1 && i <= l.n0 - 2 && j >= 1 && j <= l.n1 - 2 && (D == 2 || (k >= 1 && k <= l.n2 - 2));
+  if (!in) return;
+  const int st[3] = {1, l.pitch, l.plane};
+  float s = 0.f;
+#pragma unroll
+  for (int d = 0; d < D; ++d) { const float* ud = a.u + l.cstride * d; s += ud[o + st[d]] - ud[o]; }
+  a.z[o] = s;
+}
+// u[I,i] -= L[I,i]·∂ᵢx inside (Flow.jl:227-229)
+template <int D>
+__global__ void __launch_bounds__(256) k_project(const ProjArgs a) {
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x + 1;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;
+  if (i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && k > l.n2 - 2)) return;
+  const int o = l.off(i, j, k);
+  const int st[3] = {1, l.pitch, l.plane};
+  const float xc = a.x[o];
+#pragma unroll
+  for (int d = 0; d < D; ++d) {
+    const long long oc = l.cstride * d + o;
+    a.u[oc] -= a.L[oc] * (xc - a.x[o - st[d]]);
+  }
+}
+// x ./= dt everywhere (Flow.jl:230)
+template <int D>
+__global__ void __launch_bounds__(256) k_unscale(const ProjArgs a) {
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z : 0;
+  if (i < 0 || i >= l.n0 || j >= l.n1 || k >= l.n2) return;
+  a.x[l.off(i, j, k)] /= a.dt;
+}
+
+// ---------------------------------------------------------------- CFL (Flow.jl:234-244)
+// σ = flux_out inside; max over the WHOLE σ array (ghosts keep the stale conv-diff Φ values
+// k_ghost_phi wrote, as in the reference).
+struct CflArgs { Lay l; const float* u; float* sigma; RedWork w; Red* out; };
+template <int D>
+__global__ void __launch_bounds__(256) k_cfl(const CflArgs a) {
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z : 0;
+  float m = -INFINITY;
+  if (i >= 0 && i < l.n0 && j < l.n1 && k < l.n2) {
+    const int o = l.off(i, j, k);
+    const bool in = i >= 1 && i <= l.n0 - 2 && j >= 1 && j <= l.n1 - 2 && (D == 2 || (k >= 1 && k <= l.n2 - 2));
+    if (in) {
+      const int st[3] = {1, l.pitch, l.plane};
+      float s = 0.f;
+#pragma unroll
+      for (int d = 0; d < D; ++d) {
+        const float* ud = a.u + l.cstride * d;
+        s += fmaxf(0.f, ud[o + st[d]]) + fmaxf(0.f, -ud[o]);
+      }
+      a.sigma[o] = s;
+      m = s;
+    } else {
+      m = a.sigma[o];
+    }
+  }
+  block_reduce_finish(0.0, m, a.w, a.out);
+}
+
+// Stale Φ left in σ's upper-ghost cells by the corrector's conv_diff! (Flow.jl:47, ranges core.jl:55-57):
+// the last pass (component D, the largest direction j whose range covers the cell) wins.
+struct GhostPhiArgs { Lay l; const float* u; float* sigma; Per per; float nu; };
+template <int D, int S>
+__global__ void k_ghost_phi(const GhostPhiArgs a) {
+  const int dg = blockIdx.z;                       // plane: coordinate dg == N-1
+  const Lay& l = a.l;
+  const int N[3] = {l.n0, l.n1, l.n2};
+  const int da = dg == 0 ? 1 : 0, db = dg == 2 ? 1 : 2;
+  const int pa = blockIdx.x * blockDim.x + threadIdx.x;
+  const int pb = blockIdx.y * blockDim.y + threadIdx.y;
+  if (pa >= N[da] || (D == 3 ? pb >= N[db] : pb > 0)) return;
+  int c[3] = {0, 0, 0};
+  c[dg] = N[dg] - 1; c[da] = pa; if (D == 3) c[db] = pb;
+  for (int d = 0; d < D; ++d) if (c[d] == 0) return;           // lower ghosts are never written
+  const int st[3] = {1, l.pitch, l.plane};
+  const int ci = D - 1;
+  for (int dj = D - 1; dj >= 0; --dj) {
+    const int lo = a.per.p[dj] ? 1 : 2;
+    if (c[dj] < lo || c[dj] > N[dj] - 2) continue;
+    const int o = l.off(c[0], c[1], c[2]);
+    a.sigma[o] = face_flux<S>(a.u + l.cstride * ci, a.u + l.cstride * dj, o, st[ci], st[dj], c[dj], N[dj],
+                              a.per.p[dj] != 0, a.nu);
+    return;
+  }
+}
+
+}  // namespace wl
