@@ -134,6 +134,15 @@ int wl_enable_timing(wl_sim* s, int on);
 /* phases: 0 mom predictor, 1 project(w=1), 2 mom corrector, 3 project(w=.5), 4 cfl; seconds */
 int wl_last_phase_times(const wl_sim* s, double out[8]);
 
+/* ---- measurement hooks (bench.py): per-kernel CUDA-event timing on the launching stream.
+ *      wl_prof_begin(filter): time every kernel whose name contains `filter` ("" = all) until
+ *      wl_prof_end, which writes "<kernel>\t<launches>\t<total_ms>\n" lines into buf.
+ *      wl_event_record / wl_event_elapsed_ms: events on the sim's own stream, slots 0..7.      */
+int wl_prof_begin(wl_sim* s, const char* filter);
+int wl_prof_end(wl_sim* s, char* buf, size_t buflen);
+int wl_event_record(wl_sim* s, int slot);
+int wl_event_elapsed_ms(wl_sim* s, int a, int b, float* ms);
+
 /* ---- test hook: run ONE constituent operation of the step so that kernel-level parity tests can
  *      compare it with the oracle.  op: 0 BC!(u,uBC,exitBC) 1 conv_diff!+BDIM! predictor (u from u⁰)
  *      2 mom_project!(w=arg) 3 residual!(level) 4 Vcycle!(ω=arg) 5 smooth!(level,ω=arg)

@@ -153,7 +153,11 @@ def step_both(sim, ref, nsteps, **kw):
         ref.sim_step(**kw)
 
 
-def check_state(sim, ref, utol=1e-5, ptol=1e-4, U=1.0):
+def check_state(sim, ref, utol=1e-6, ptol=1e-5, U=1.0):
+    """The library is compiled with -fmad=false and evaluates every stencil in the oracle's
+    operation order, so fields normally agree BIT FOR BIT; the tolerances (10x tighter than
+    north_star's 1e-5) only leave room for a last-bit difference in a Float64-accumulated
+    reduction (Σr, Σ|r|) whose summation order differs."""
     assert sim.pois.n == ref.n, (sim.pois.n, ref.n)
     assert np.allclose(sim.flow.Δt, ref.dts, rtol=2e-6), (sim.flow.Δt[-3:], ref.dts[-3:])
     u, p = sim.flow.u, sim.flow.p
@@ -162,6 +166,7 @@ def check_state(sim, ref, utol=1e-5, ptol=1e-4, U=1.0):
     assert eu <= utol * max(U, 1.0), f"max|Δu|={eu:.3e}"
     assert ep <= ptol, f"rel max|Δp|={ep:.3e}"
     assert not np.isnan(u).any()
+    return dict(bit_exact_u=bool(np.array_equal(u, ref.field("u"))), bit_exact_p=bool(np.array_equal(p, ref.field("p"))))
 
 
 def test_config_A_circle_2d(wl):
@@ -173,7 +178,7 @@ def test_config_A_circle_2d(wl):
     close(sim.flow.mu0, ref.field("mu0"), 1e-6, "μ₀")
     close(sim.flow.mu1, ref.field("mu1"), 1e-6, "μ₁")
     step_both(sim, ref, 100, remeasure=False)
-    check_state(sim, ref, utol=2e-5)
+    check_state(sim, ref)
     f_gpu, f_ref = sim.pressure_force(), ref.pressure_force()
     assert np.allclose(f_gpu, f_ref, rtol=1e-4, atol=1e-4 * np.abs(f_ref).max()), (f_gpu, f_ref)
 

@@ -36,7 +36,8 @@ ABI_SYMBOLS = [
     "wl_upload", "wl_nlevels", "wl_finish_ic", "wl_measure_body", "wl_set_body_coeffs",
     "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
     "wl_cfl", "wl_pressure_force", "wl_sync", "wl_launch_count", "wl_enable_timing",
-    "wl_last_phase_times", "wl_debug_op",
+    "wl_last_phase_times", "wl_debug_op", "wl_prof_begin", "wl_prof_end", "wl_event_record",
+    "wl_event_elapsed_ms",
 ]
 
 
@@ -106,6 +107,10 @@ def load_library(path=None):
     lib.wl_enable_timing.argtypes = [P, I]
     lib.wl_last_phase_times.argtypes = [P, C.POINTER(C.c_double * 8)]
     lib.wl_debug_op.argtypes = [P, I, I, F]
+    lib.wl_prof_begin.argtypes = [P, C.c_char_p]
+    lib.wl_prof_end.argtypes = [P, C.c_char_p, C.c_size_t]
+    lib.wl_event_record.argtypes = [P, I]
+    lib.wl_event_elapsed_ms.argtypes = [P, I, I, FP]
     if path == _LIBNAME:
         _lib = lib
     return lib
@@ -363,6 +368,27 @@ class Simulation:
 
     def debug_op(self, op, level=0, arg=0.0):
         self._check(self.lib.wl_debug_op(self.h, int(op), int(level), float(arg)))
+
+    def prof_begin(self, filt=""):
+        self._check(self.lib.wl_prof_begin(self.h, filt.encode()))
+
+    def prof_end(self):
+        """-> {kernel name: (launches, total_ms)} measured with CUDA events on the launching stream."""
+        buf = C.create_string_buffer(1 << 16)
+        self.lib.wl_prof_end(self.h, buf, len(buf))
+        out = {}
+        for line in buf.value.decode().splitlines():
+            name, n, ms = line.split("\t")
+            out[name] = (int(n), float(ms))
+        return out
+
+    def event_record(self, slot):
+        self._check(self.lib.wl_event_record(self.h, slot))
+
+    def event_elapsed_ms(self, a, b):
+        ms = C.c_float()
+        self._check(self.lib.wl_event_elapsed_ms(self.h, a, b, C.byref(ms)))
+        return float(ms.value)
 
     def sync(self):
         self._check(self.lib.wl_sync(self.h))

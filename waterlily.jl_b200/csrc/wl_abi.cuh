@@ -381,6 +381,52 @@ int wl_debug_op(wl_sim* s, int op, int level, float arg) {
   return check_async(s, "wl_debug_op");
 }
 
+int wl_prof_begin(wl_sim* s, const char* filter) {
+  if (!s) return WL_ERR_INVALID;
+  s->prof_on = true;
+  s->prof_filter = filter ? filter : "";
+  return WL_OK;
+}
+// Writes one line per kernel: "<name>\t<launches>\t<total_ms>\n"; returns the number of kernels.
+int wl_prof_end(wl_sim* s, char* buf, size_t buflen) {
+  if (!s) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  cudaStreamSynchronize(s->st);
+  s->prof_on = false;
+  struct Acc { const char* name; long n; double ms; };
+  std::vector<Acc> acc;
+  for (auto& r : s->recs) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r.a, r.b);
+    s->evpool.push_back(r.a); s->evpool.push_back(r.b);
+    size_t i = 0;
+    for (; i < acc.size(); ++i) if (acc[i].name == r.name || !strcmp(acc[i].name, r.name)) break;
+    if (i == acc.size()) acc.push_back({r.name, 0, 0.0});
+    acc[i].n++; acc[i].ms += ms;
+  }
+  s->recs.clear();
+  std::string out;
+  char line[256];
+  for (auto& a : acc) { snprintf(line, sizeof line, "%s\t%ld\t%.6f\n", a.name, a.n, a.ms); out += line; }
+  if (buf && buflen) { strncpy(buf, out.c_str(), buflen - 1); buf[buflen - 1] = 0; }
+  return (int)acc.size();
+}
+// CUDA events on the sim's own stream (torch.cuda.Event only sees torch's stream)
+int wl_event_record(wl_sim* s, int slot) {
+  if (!s || slot < 0 || slot >= 8) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  if (!s->uev[slot]) WL_CUDA(s, cudaEventCreate(&s->uev[slot]));
+  WL_CUDA(s, cudaEventRecord(s->uev[slot], s->st));
+  return WL_OK;
+}
+int wl_event_elapsed_ms(wl_sim* s, int a, int b, float* ms) {
+  if (!s || !ms || a < 0 || b < 0 || a >= 8 || b >= 8 || !s->uev[a] || !s->uev[b]) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  WL_CUDA(s, cudaEventSynchronize(s->uev[b]));
+  WL_CUDA(s, cudaEventElapsedTime(ms, s->uev[a], s->uev[b]));
+  return WL_OK;
+}
+
 int wl_sync(wl_sim* s) {
   if (!s) return WL_ERR_INVALID;
   cudaSetDevice(s->device);

@@ -38,6 +38,8 @@ struct Level {
 
 constexpr int NRED = 8;
 
+struct ProfRec { const char* name; cudaEvent_t a, b; };
+
 }  // namespace
 
 struct wl_sim {
@@ -59,6 +61,12 @@ struct wl_sim {
   cudaEvent_t ev[8] = {};
   double phase_s[8] = {};
   int status = WL_OK;
+  // profiling hooks
+  bool prof_on = false;
+  std::string prof_filter;
+  std::vector<cudaEvent_t> evpool;
+  std::vector<ProfRec> recs;
+  cudaEvent_t uev[8] = {};
 };
 
 namespace {
@@ -100,10 +108,30 @@ void plane_launch(const Lay& l, dim3& g, dim3& b) {
   g = dim3((m + b.x - 1) / b.x, (m2 + b.y - 1) / b.y, 1);
 }
 
-#define LAUNCH(s, kern, g, b, ...)                 \
-  do {                                             \
-    kern<<<g, b, 0, (s)->st>>>(__VA_ARGS__);       \
-    ++(s)->launches;                               \
+// Optional per-kernel CUDA-event timing on the launching stream (wl_prof_begin/wl_prof_end).
+inline bool prof_pre(wl_sim* s, const char* name, cudaEvent_t* a, cudaEvent_t* b) {
+  if (!s->prof_on) return false;
+  if (!s->prof_filter.empty() && !strstr(name, s->prof_filter.c_str())) return false;
+  if (s->evpool.size() < 2) {
+    for (int i = 0; i < 64; ++i) { cudaEvent_t e; cudaEventCreate(&e); s->evpool.push_back(e); }
+  }
+  *a = s->evpool.back(); s->evpool.pop_back();
+  *b = s->evpool.back(); s->evpool.pop_back();
+  cudaEventRecord(*a, s->st);
+  return true;
+}
+inline void prof_post(wl_sim* s, const char* name, cudaEvent_t a, cudaEvent_t b) {
+  cudaEventRecord(b, s->st);
+  s->recs.push_back({name, a, b});
+}
+
+#define LAUNCH(s, kern, g, b, ...)                         \
+  do {                                                     \
+    cudaEvent_t pa_, pb_;                                  \
+    const bool prof_ = prof_pre(s, #kern, &pa_, &pb_);     \
+    kern<<<g, b, 0, (s)->st>>>(__VA_ARGS__);               \
+    if (prof_) prof_post(s, #kern, pa_, pb_);              \
+    ++(s)->launches;                                       \
   } while (0)
 
 #define DISPATCH_D(s, kern, g, b, ...)                                    \

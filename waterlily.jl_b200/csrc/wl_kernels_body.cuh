@@ -69,11 +69,15 @@ __device__ __forceinline__ Meas measure_pt(const BodyDev& b, const float* x, flo
 }
 
 // kernels Body.jl:54-60
-__device__ __forceinline__ float kern(float d) { return (1.f + cospif(d)) / 2.f; }
-__device__ __forceinline__ float kern0(float d) { return (1.f + d + sinpif(d) / 3.14159265358979323846f) / 2.f; }
+// Julia's sinpi/cospi are accurate to the last bit: evaluate in double and round once (the oracle
+// does the same), so μ₀/μ₁ agree bit for bit.  Only band cells reach these, the cost is nil.
+__device__ __forceinline__ float sinpi_r(float d) { return (float)sin(3.14159265358979323846 * (double)d); }
+__device__ __forceinline__ float cospi_r(float d) { return (float)cos(3.14159265358979323846 * (double)d); }
+__device__ __forceinline__ float kern(float d) { return (1.f + cospi_r(d)) / 2.f; }
+__device__ __forceinline__ float kern0(float d) { return (1.f + d + sinpi_r(d) / 3.14159265358979323846f) / 2.f; }
 __device__ __forceinline__ float kern1(float d) {
   const float pi = 3.14159265358979323846f;
-  return (1.f - d * d) / 4.f - (d * sinpif(d) + (1.f + cospif(d)) / pi) / (2.f * pi);
+  return (1.f - d * d) / 4.f - (d * sinpi_r(d) + (1.f + cospi_r(d)) / pi) / (2.f * pi);
 }
 __device__ __forceinline__ float mu0f(float d, float e) {
   const float ad = fabsf(d);
