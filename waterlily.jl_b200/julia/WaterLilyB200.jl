@@ -1,0 +1,182 @@
+# WaterLilyB200.jl -- thin `ccall` shim that plugs libwaterlily_b200.so into WaterLily's own
+# `Simulation` through the documented factory hooks `flow_ctor` / `pois_ctor`
+# (reference src/WaterLily.jl:69-74,93-106).  No KernelAbstractions, no CUDA.jl, no kernels here:
+# every numerical operation is a single call into the C ABI of include/wl_b200.h.
+#
+# STATUS: Julia is not installed in the build image or on the GPU box, so this file has been
+# syntax-reviewed only; the same ABI is exercised by the ctypes mirror in ../__init__.py, whose
+# tests are the executable specification of every call made below.
+#
+#   using WaterLily, WaterLilyB200
+#   sim = B200Simulation((512,256,256), (1,0,0), 64; ν=64/3700, body=B200Sphere((127,127,127),32))
+#   sim_step!(sim, 10.0; remeasure=false)          # WaterLily's own time loop drives the library
+#   pressure_force(sim); Array(sim.flow.u); sim.pois.n; sim.flow.Δt
+module WaterLilyB200
+
+using WaterLily
+import WaterLily: AbstractFlow, AbstractPoisson, AbstractBody, mom_step!, measure!, update!, solver!, CFL,
+                  pressure_force, time
+
+const LIB = get(ENV, "WATERLILY_B200_LIB", joinpath(@__DIR__, "..", "libwaterlily_b200.so"))
+
+# ---- POD mirrors of include/wl_b200.h ------------------------------------------------------------
+struct WLConfig
+    D::Int32; N::NTuple{3,Int32}; perdir::NTuple{3,Int32}; exitBC::Int32; scheme::Int32
+    nu::Float32; dt0::Float32; uBC::NTuple{3,Float32}; maxlevels::Int32; tol::Float32; itmx::Int32
+    device::Int32; flags::Int32
+end
+struct WLBody
+    kind::Int32; axis::Int32; center::NTuple{3,Float32}; radius::Float32; minor::Float32
+    vel::NTuple{3,Float32}; acc::NTuple{3,Float32}; amp::NTuple{3,Float32}; omega::Float32
+end
+struct WLStepInfo
+    dt_next::Float32; n_pred::Int32; n_corr::Int32; flags::Int32; trace_len::NTuple{2,Int32}
+    rinf::NTuple{68,Float32}; r1::NTuple{68,Float32}; omega::NTuple{68,Float32}
+end
+
+const FIELD = (u=0, u⁰=1, f=2, p=3, σ=4, V=5, μ₀=6, μ₁=7, x=10, r=11, ϵ=12, z=13, L=14, D=15, iD=16)
+pad3(t, z) = ntuple(i -> i <= length(t) ? t[i] : z, 3)
+
+mutable struct Handle
+    ptr::Ptr{Cvoid}
+    function Handle(p)
+        h = new(p)
+        finalizer(h -> (h.ptr == C_NULL || ccall((:wl_destroy, LIB), Cvoid, (Ptr{Cvoid},), h.ptr); h.ptr = C_NULL), h)
+    end
+end
+lasterr(h) = unsafe_string(ccall((:wl_last_error, LIB), Cstring, (Ptr{Cvoid},), h))
+check(h::Handle, rc) = rc == 0 ? nothing : error("libwaterlily_b200 ($rc): ", lasterr(h.ptr))
+
+# ---- device array handle: `Array(a)` downloads, `copyto!(a, ::Array)` uploads ---------------------
+struct B200Array{T,N} <: AbstractArray{T,N}
+    h::Handle; field::Int32; level::Int32; dims::NTuple{N,Int}
+end
+Base.size(a::B200Array) = a.dims
+function Base.Array(a::B200Array{T,N}) where {T,N}
+    out = Array{T,N}(undef, a.dims)
+    check(a.h, ccall((:wl_download, LIB), Cint, (Ptr{Cvoid}, Cint, Cint, Ptr{Float32}, Csize_t),
+                     a.h.ptr, a.field, a.level, out, length(out)))
+    out
+end
+function Base.copyto!(a::B200Array{T,N}, src::Array{T,N}) where {T,N}
+    check(a.h, ccall((:wl_upload, LIB), Cint, (Ptr{Cvoid}, Cint, Cint, Ptr{Float32}, Csize_t),
+                     a.h.ptr, a.field, a.level, src, length(src)))
+    a
+end
+Base.getindex(a::B200Array, I...) = Array(a)[I...]        # slow scalar probe, tests only
+Base.maximum(a::B200Array) = maximum(Array(a))
+
+# ---- parametric bodies the device-side measure! understands ---------------------------------------
+struct B200Body <: AbstractBody
+    c::WLBody
+end
+B200Sphere(center, radius; vel=(0,0,0), acc=(0,0,0), amp=(0,0,0), ω=0) =
+    B200Body(WLBody(1, 0, pad3(Float32.(center), 0f0), radius, 0, pad3(Float32.(vel), 0f0), pad3(Float32.(acc), 0f0), pad3(Float32.(amp), 0f0), ω))
+B200Cylinder(center, radius, axis; kw...) = (b = B200Sphere(center, radius; kw...).c;
+    B200Body(WLBody(2, axis - 1, b.center, b.radius, 0, b.vel, b.acc, b.amp, b.omega)))
+B200Torus(center, R, r, axis; kw...) = (b = B200Sphere(center, R; kw...).c;
+    B200Body(WLBody(3, axis - 1, b.center, R, r, b.vel, b.acc, b.amp, b.omega)))
+
+# ---- Flow ------------------------------------------------------------------------------------------
+struct B200Flow{D,T} <: AbstractFlow{D,T}
+    h::Handle
+    u::B200Array{T}; u⁰::B200Array{T}; f::B200Array{T}; p::B200Array{T}; σ::B200Array{T}
+    V::B200Array{T}; μ₀::B200Array{T}; μ₁::B200Array{T}
+    uBC::NTuple{D,T}; Δt::Vector{T}; ν::T; g::Nothing; exitBC::Bool; perdir::NTuple
+end
+const SCHEME = Dict(WaterLily.quick => 0, WaterLily.cds => 1, WaterLily.vanLeer => 2)
+
+"`flow_ctor` for `Simulation` (reference src/Flow.jl:133-147)."
+function B200Flow(N::NTuple{D}, uBC; Δt=0.25, ν=0., g=nothing, u0=nothing, uλ=nothing, perdir=(), exitBC=false,
+                  λ=WaterLily.quick, T=Float32, mem=Array, device=0) where D
+    T == Float32 || error("WL_ERR_UNSUPPORTED: the B200 path is Float32 only")
+    (uBC isa Function || g isa Function) && error("WL_ERR_UNSUPPORTED: Function uBC / g cannot cross the C ABI")
+    haskey(SCHEME, λ) || error("WL_ERR_UNSUPPORTED: λ must be quick, cds or vanLeer")
+    cfg = Ref(WLConfig(D, pad3(Int32.(N), Int32(0)), ntuple(i -> Int32(i in perdir), 3), exitBC, SCHEME[λ], ν, Δt,
+                       pad3(Float32.(uBC), 0f0), 10, 2f-3, 32, device, 0))
+    out = Ref{Ptr{Cvoid}}(C_NULL)
+    rc = ccall((:wl_create, LIB), Cint, (Ref{WLConfig}, Ref{Ptr{Cvoid}}), cfg, out)
+    rc == 0 || error("wl_create ($rc): ", lasterr(C_NULL))
+    h = Handle(out[]); Ng = N .+ 2
+    arr(f, dims) = B200Array{T,length(dims)}(h, Int32(f), Int32(0), dims)
+    flow = B200Flow{D,T}(h, arr(FIELD.u, (Ng..., D)), arr(FIELD.u⁰, (Ng..., D)), arr(FIELD.f, (Ng..., D)),
+                         arr(FIELD.p, Ng), arr(FIELD.σ, Ng), arr(FIELD.V, (Ng..., D)), arr(FIELD.μ₀, (Ng..., D)),
+                         arr(FIELD.μ₁, (Ng..., D, D)), T.(uBC), T[Δt], T(ν), nothing, exitBC, perdir)
+    u0 = isnothing(u0) ? uλ : u0
+    if !isnothing(u0)                                  # apply!(u0,u) on the host, then BC!/exitBC!/u⁰ on the device
+        host = Array{T}(undef, Ng..., D)
+        u0 isa Function ? WaterLily.apply!(u0, host) : WaterLily.apply!((i, x) -> u0[i], host)
+        copyto!(flow.u, host)
+        check(h, ccall((:wl_finish_ic, LIB), Cint, (Ptr{Cvoid}, Ref{NTuple{3,Float32}}), h.ptr, Ref(pad3(Float32.(uBC), 0f0))))
+    end
+    flow
+end
+
+# ---- Poisson -----------------------------------------------------------------------------------------
+struct B200Level{T}
+    x::B200Array{T}; r::B200Array{T}; ϵ::B200Array{T}; z::B200Array{T}; L::B200Array{T}; D::B200Array{T}; iD::B200Array{T}
+end
+struct B200Poisson{T} <: AbstractPoisson{T,B200Array{T},B200Array{T}}
+    h::Handle; x::B200Array{T}; L::B200Array{T}; z::B200Array{T}; levels::Vector{B200Level{T}}; n::Vector{Int16}; perdir::NTuple
+end
+"`pois_ctor` for `Simulation` (reference src/WaterLily.jl:97, src/MultiLevelPoisson.jl:68-76)."
+function B200Poisson(flow::B200Flow{D,T}) where {D,T}
+    h = flow.h
+    rc = ccall((:wl_build_poisson, LIB), Cint, (Ptr{Cvoid},), h.ptr)
+    rc == 0 || (occursin("size=a2", lasterr(h.ptr)) ? throw(AssertionError("MultiLevelPoisson requires size=a2ⁿ, where n>2")) : check(h, rc))
+    nl = ccall((:wl_nlevels, LIB), Cint, (Ptr{Cvoid},), h.ptr)
+    levels = map(0:nl-1) do l
+        dims = Ref(ntuple(_ -> Int32(0), 5)); nd = Ref{Int32}(0)
+        ccall((:wl_field_dims, LIB), Cint, (Ptr{Cvoid}, Cint, Cint, Ref{NTuple{5,Int32}}, Ref{Int32}), h.ptr, FIELD.x, l, dims, nd)
+        ng = Int.(dims[][1:D]); a(f, d) = B200Array{T,length(d)}(h, Int32(f), Int32(l), d)
+        B200Level{T}(a(FIELD.x, ng), a(FIELD.r, ng), a(FIELD.ϵ, ng), a(FIELD.z, ng), a(FIELD.L, (ng..., D)), a(FIELD.D, ng), a(FIELD.iD, ng))
+    end
+    B200Poisson{T}(h, flow.p, flow.μ₀, flow.σ, levels, Int16[], flow.perdir)
+end
+
+# ---- the generic functions WaterLily's time loop calls (src/WaterLily.jl:128-149) --------------------
+function mom_step!(a::B200Flow{D,T}, b::B200Poisson; udf=nothing, kwargs...) where {D,T}
+    isnothing(udf) || error("WL_ERR_UNSUPPORTED: udf hooks cannot cross the C ABI")
+    ccall((:wl_set_dt, LIB), Cint, (Ptr{Cvoid}, Cfloat), a.h.ptr, a.Δt[end])
+    info = Ref{WLStepInfo}()
+    check(a.h, ccall((:wl_mom_step, LIB), Cint, (Ptr{Cvoid}, Ptr{Cfloat}, Ptr{Cfloat}, Ptr{Cfloat}, Ref{WLStepInfo}),
+                     a.h.ptr, C_NULL, C_NULL, C_NULL, info))
+    push!(b.n, info[].n_pred, info[].n_corr)            # MultiLevelPoisson.jl:127
+    push!(a.Δt, info[].dt_next)                         # Flow.jl:166
+end
+measure!(a::B200Flow, ::WaterLily.NoBody; kw...) = nothing
+function measure!(a::B200Flow{D,T}, body::B200Body; t=zero(T), ϵ=1) where {D,T}
+    check(a.h, ccall((:wl_measure_body, LIB), Cint, (Ptr{Cvoid}, Ref{WLBody}, Cdouble, Cdouble), a.h.ptr, Ref(body.c), t, ϵ))
+end
+"Arbitrary `AutoBody` closures: measured by the reference itself on a host `Flow`, then uploaded."
+function measure!(a::B200Flow{D,T}, body::AbstractBody; t=zero(T), ϵ=1) where {D,T}
+    host = WaterLily.Flow(size(a.p) .- 2, a.uBC; T, perdir=a.perdir, exitBC=a.exitBC)
+    fill!(host.V, 0); fill!(host.μ₀, 1); fill!(host.μ₁, 0)
+    WaterLily.measure!(host, body; t, ϵ)               # includes the two BC! calls; the library re-applies them (idempotent)
+    check(a.h, ccall((:wl_set_body_coeffs, LIB), Cint, (Ptr{Cvoid}, Ptr{Float32}, Ptr{Float32}, Ptr{Float32}, Ptr{Float32}),
+                     a.h.ptr, host.μ₀, host.μ₁, host.V, host.σ))
+end
+update!(b::B200Poisson) = check(b.h, ccall((:wl_update_poisson, LIB), Cint, (Ptr{Cvoid},), b.h.ptr))
+function solver!(b::B200Poisson; kw...)
+    n = Ref{Int32}(0)
+    check(b.h, ccall((:wl_solver, LIB), Cint, (Ptr{Cvoid}, Ref{Int32}, Ptr{Int32}, Ptr{Cfloat}, Ptr{Cfloat}, Ptr{Cfloat}),
+                     b.h.ptr, n, C_NULL, C_NULL, C_NULL, C_NULL))
+    push!(b.n, n[])
+end
+function CFL(a::B200Flow; Δt_max=10)
+    dt = Ref{Cfloat}(0)
+    check(a.h, ccall((:wl_cfl, LIB), Cint, (Ptr{Cvoid}, Ref{Cfloat}), a.h.ptr, dt)); min(Δt_max, dt[])
+end
+function pressure_force(a::B200Flow{D}, body::B200Body) where D
+    out = Ref(ntuple(_ -> 0.0, 3))
+    check(a.h, ccall((:wl_pressure_force, LIB), Cint, (Ptr{Cvoid}, Ref{WLBody}, Cdouble, Ref{NTuple{3,Float64}}),
+                     a.h.ptr, Ref(body.c), time(a), out))
+    collect(out[][1:D])
+end
+
+"Drop-in constructor: WaterLily's own `Simulation` with the two factories swapped."
+B200Simulation(dims, uBC, L; device=0, kw...) =
+    WaterLily.Simulation(dims, uBC, L; kw..., flow_ctor=(d, u; k...) -> B200Flow(d, u; device, k...), pois_ctor=B200Poisson)
+
+export B200Simulation, B200Flow, B200Poisson, B200Array, B200Sphere, B200Cylinder, B200Torus
+end # module
