@@ -220,7 +220,8 @@ def main():
         sim.sim_step(remeasure=remeasure)
 
     # ---- timed region: K steps, state resident in HBM, CUDA events on the launching stream
-    dom = "k_mom_rhs"
+    dom = "k_mom3" if D == 3 else "k_mom_rhs"
+    balg_key = "k_mom" if D == 3 else "k_mom_rhs"
     clocks = ClockSampler(local)
     barrier()
     l0 = sim.launch_count()
@@ -251,7 +252,7 @@ def main():
     for name, (n, ms) in prof.items():
         kn += n
         kms += ms
-    balg = B_ALG[dom][D]
+    balg = B_ALG[balg_key][D]
     achieved = (balg * cells) / (kms / max(kn, 1) * 1e-3) / 1e9 if kn else None
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": (achieved / peak) if achieved else None, "traffic": None,

@@ -54,6 +54,7 @@ typedef struct wl_config {
 } wl_config;
 
 #define WL_FLAG_NO_GRAPHS 1   /* disable CUDA-graph replay of the V-cycle (debugging) */
+#define WL_FLAG_NO_FUSED 2    /* 3D: use the un-fused K-RHS + K-BDIM kernels (materialises flow.f) */
 
 /* Parametric AutoBody: primitive sdf composed with map(x,t) = x - centre(t),
  * centre(t) = center + vel*t + acc*t^2 + amp*sin(omega*t)  (src/AutoBody.jl:1-37).

@@ -200,7 +200,7 @@ class Simulation:
 
     def __init__(self, dims, uBC, L=1.0, *, dt=0.25, nu=0.0, U=None, eps=1.0, perdir=(), exitBC=False,
                  scheme="quick", body=None, u0=None, g=None, maxlevels=10, tol=2e-3, itmx=32, device=0,
-                 T=np.float32, lib=None):
+                 T=np.float32, lib=None, flags=0):
         if np.dtype(T) != np.float32:
             raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: the B200 path is Float32 only")
         if callable(uBC) or callable(g):
@@ -222,7 +222,7 @@ class Simulation:
         per = [1 if (d + 1) in perdir else 0 for d in range(3)]
         cfg = WLConfig(self.D, (C.c_int32 * 3)(*(list(self.dims) + [0] * (3 - self.D))), (C.c_int32 * 3)(*per),
                        int(exitBC), SCHEMES[scheme], float(nu), float(dt), _v3f(self.uBC), maxlevels, float(tol),
-                       itmx, device, 0)
+                       itmx, device, int(flags))
         h = C.c_void_p()
         rc = self.lib.wl_create(C.byref(cfg), C.byref(h))
         if rc != WL_OK:

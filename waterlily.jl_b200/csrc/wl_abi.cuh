@@ -106,8 +106,11 @@ int wl_create(const wl_config* cfg, wl_sim** out) {
   if ((e = alloc_field(s, s->u, s->lay, D)) || (e = alloc_field(s, s->u0, s->lay, D)) ||
       (e = alloc_field(s, s->f, s->lay, D)) || (e = alloc_field(s, s->p, s->lay, 1)) ||
       (e = alloc_field(s, s->sigma, s->lay, 1)) || (e = alloc_field(s, s->V, s->lay, D)) ||
-      (e = alloc_field(s, s->mu0, s->lay, D)) || (e = alloc_field(s, s->mu1, s->lay, D * D)))
+      (e = alloc_field(s, s->mu0, s->lay, D)) || (e = alloc_field(s, s->mu1, s->lay, D * D)) ||
+      (D == 3 && (e = alloc_field(s, s->w, s->lay, D))))
     return bail(e);
+  if (cudaMalloc(&s->band_count, sizeof(int)) != cudaSuccess) { s->err = "band counter allocation failed"; return bail(WL_ERR_CUDA); }
+  cudaMemsetAsync(s->band_count, 0, sizeof(int), s->st);
   // reduction scratch: one partial per block of the largest launch
   {
     dim3 g = grid_all(s->lay);
@@ -156,7 +159,9 @@ void wl_destroy(wl_sim* s) {
     free_field(v.r); free_field(v.eps); free_field(v.Dg); free_field(v.iD);
   }
   free_field(s->u); free_field(s->u0); free_field(s->f); free_field(s->p);
-  free_field(s->sigma); free_field(s->V); free_field(s->mu0); free_field(s->mu1);
+  free_field(s->sigma); free_field(s->V); free_field(s->mu0); free_field(s->mu1); free_field(s->w);
+  if (s->band_list) cudaFree(s->band_list);
+  if (s->band_count) cudaFree(s->band_count);
   if (s->redw.psum) cudaFree(s->redw.psum);
   if (s->redw.pmax) cudaFree(s->redw.pmax);
   if (s->redw.ticket) cudaFree(s->redw.ticket);
@@ -203,6 +208,7 @@ static int xfer(wl_sim* s, int field, int level, float* host, size_t count, bool
                                    (size_t)lay.n1 * lay.n2, cudaMemcpyDeviceToHost, s->st));
   }
   WL_CUDA(s, cudaStreamSynchronize(s->st));
+  if (up && field == WL_MU1) s->band_dirty = true;
   return WL_OK;
 }
 int wl_download(wl_sim* s, int field, int level, float* host, size_t count) { return xfer(s, field, level, host, count, false); }
@@ -227,6 +233,7 @@ int wl_measure_body(wl_sim* s, const wl_body* body, double t, double eps) {
   cudaSetDevice(s->device);
   MeasArgs a{s->lay, body_at(body, s->D, (float)t), (float)eps, s->sigma.base, s->V.base, s->mu0.base, s->mu1.base};
   DISPATCH_D(s, k_measure, grid_all(s->lay), blk(s->D), a);
+  s->band_dirty = true;
   bc_vec(s, s->mu0, nullptr, false);
   bc_vec(s, s->V, nullptr, s->cfg.exitBC != 0);
   return check_async(s, "wl_measure_body");
@@ -240,6 +247,7 @@ int wl_set_body_coeffs(wl_sim* s, const float* mu0, const float* mu1, const floa
   if (mu1 && (e = wl_upload(s, WL_MU1, 0, mu1, per * s->D * s->D))) return e;
   if (V && (e = wl_upload(s, WL_V, 0, V, per * s->D))) return e;
   if (sdf && (e = wl_upload(s, WL_SIGMA, 0, sdf, per))) return e;
+  s->band_dirty = true;
   bc_vec(s, s->mu0, nullptr, false);
   bc_vec(s, s->V, nullptr, s->cfg.exitBC != 0);
   return check_async(s, "wl_set_body_coeffs");
@@ -296,12 +304,19 @@ int wl_mom_step(wl_sim* s, const float* uBC_t1, const float* acc0, const float* 
   const float* U = uBC_t1 ? uBC_t1 : s->cfg.uBC;
   const bool ex = s->cfg.exitBC != 0;
   Trace tr[2];
+  const bool fused = s->D == 3 && !(s->cfg.flags & WL_FLAG_NO_FUSED);
+  if (fused && s->band_dirty) { if (int e = band_rebuild(s)) return e; }
   if (s->timing) cudaEventRecord(s->ev[0], s->st);
-  WL_CUDA(s, cudaMemcpyAsync(s->u0.alloc, s->u.alloc, s->u.bytes, cudaMemcpyDeviceToDevice, s->st));   // u⁰ .= u
-  ++s->launches;
-  // predictor
-  mom_rhs(s, s->u0, acc0);
-  bdim(s, 0);
+  if (fused) {
+    // predictor: u⁰ .= u is a buffer rotation; K-MOM writes the new u into the work buffer
+    mom3(s, s->u, s->u, s->w, 0, acc0);
+    DevField old0 = s->u0; s->u0 = s->u; s->u = s->w; s->w = old0;
+  } else {
+    WL_CUDA(s, cudaMemcpyAsync(s->u0.alloc, s->u.alloc, s->u.bytes, cudaMemcpyDeviceToDevice, s->st));   // u⁰ .= u
+    ++s->launches;
+    mom_rhs(s, s->u0, acc0);
+    bdim(s, 0);
+  }
   bc_vec(s, s->u, U, ex);
   if (ex) exitbc(s, s->u, s->u0, s->dt);
   if (s->timing) cudaEventRecord(s->ev[1], s->st);
@@ -309,8 +324,13 @@ int wl_mom_step(wl_sim* s, const float* uBC_t1, const float* acc0, const float* 
   if (s->timing) cudaEventRecord(s->ev[2], s->st);
   // corrector
   ghost_phi(s);
-  mom_rhs(s, s->u, acc1);
-  bdim(s, 1);
+  if (fused) {
+    mom3(s, s->u, s->u0, s->w, 1, acc1);
+    DevField t = s->u; s->u = s->w; s->w = t;
+  } else {
+    mom_rhs(s, s->u, acc1);
+    bdim(s, 1);
+  }
   bc_vec(s, s->u, U, ex);
   if (s->timing) cudaEventRecord(s->ev[3], s->st);
   if (int e = mom_project(s, 0.5f, U, &tr[1])) return e;

@@ -13,7 +13,9 @@
 #include "wl_common.cuh"
 #include "wl_kernels_body.cuh"
 #include "wl_kernels_mg.cuh"
+#include "wl_kernels_mg2.cuh"
 #include "wl_kernels_mom.cuh"
+#include "wl_kernels_mom3.cuh"
 
 using namespace wl;
 
@@ -48,6 +50,11 @@ struct wl_sim {
   Lay lay{};
   Per per{};
   DevField u, u0, f, p, sigma, V, mu0, mu1;
+  DevField w;                 // third rotating velocity buffer of the fused 3D K-MOM path
+  int* band_list = nullptr;   // interior cells with μ₁ ≠ 0 (patched after K-MOM)
+  int* band_count = nullptr;
+  int band_cap = 0;
+  bool band_dirty = false;
   std::vector<Level> lv;
   cudaStream_t st = nullptr;
   RedWork redw{};
@@ -225,16 +232,62 @@ void restrictL(wl_sim* s, Level& fi, Level& co) {
   DISPATCH_D(s, k_restrictL, grid_inside(co.lay), blk(s->D), a);
   bc_vec(s, co.L, nullptr, false);
 }
-// Vcycle!(ml;l,ω) (MultiLevelPoisson.jl:88-101)
-void vcycle(wl_sim* s, size_t l, float w) {
+// Vcycle!(ml;l,ω) (MultiLevelPoisson.jl:88-101), v1 kernels (kept for WL_FLAG_NO_FUSED)
+void vcycle_v1(wl_sim* s, size_t l, float w) {
   Level &fine = s->lv[l], &coarse = s->lv[l + 1];
   jacobi(s, fine);
   restrict_r(s, fine, coarse);
   cudaMemsetAsync(coarse.x.alloc, 0, coarse.x.bytes, s->st);
-  if (l + 2 < s->lv.size()) vcycle(s, l + 1, w);
+  if (l + 2 < s->lv.size()) vcycle_v1(s, l + 1, w);
   smooth(s, coarse, w, nullptr);
   prolongate(s, fine, coarse);
   increment(s, fine, w, nullptr);
+}
+
+// ---- v2: fused kernels (wl_kernels_mg2.cuh)
+LevDev levdev(const Level& p) {
+  LevDev d{};
+  d.l = p.lay; d.L = p.L.base; d.iD = p.iD.base; d.x = p.x.base; d.r = p.r.base; d.eps = p.eps.base;
+  for (int q = 0; q < 3; ++q) d.c[q] = p.c[q];
+  return d;
+}
+// one block of 1024 threads sweeps a level in (cells/1024) dependent round trips to L2 per phase:
+// worthwhile up to ~18^3, beyond that the per-level launches win
+inline bool level_is_small(const Level& p) { return (long long)p.lay.n0 * p.lay.n1 * p.lay.n2 <= 8000; }
+// GaussSeidelRB!(p;it=4,ω): ϵ init + ghost images, 4 half sweeps on stale ghosts, wrap-read increment
+void smooth2(wl_sim* s, Level& p, float w, Red* norms) {
+  SmArgs a{levdev(p), s->per, w, 0, s->redw, norms ? norms : s->d_red, norms ? 1 : 0};
+  DISPATCH_D(s, k_eps_init_g, grid_inside(p.lay), blk(s->D), a);
+  LevArgs g = lev_args(s, p);
+  for (int k0 = 1; k0 <= 4; ++k0) {
+    g.k0 = k0;
+    DISPATCH_D(s, k_gs_half, grid_inside(p.lay), blk(s->D), g);
+  }
+  DISPATCH_D(s, k_increment_w, grid_inside(p.lay), blk(s->D), a);
+}
+// levels first..end in ONE single-block launch: Vcycle!(l=first) (if any coarser level) + smooth!(first)
+void coarse_block(wl_sim* s, size_t first, float w) {
+  CoarseArgs a{};
+  for (size_t l = 0; l < s->lv.size() && l < (size_t)WL_MAXLEV; ++l) a.lv[l] = levdev(s->lv[l]);
+  a.first = (int)first; a.nlev = (int)s->lv.size(); a.per = s->per; a.omega = w;
+  DISPATCH_D(s, k_coarse, dim3(1), dim3(1024), a);
+}
+void vcycle(wl_sim* s, size_t l, float w) {
+  if (s->cfg.flags & WL_FLAG_NO_FUSED) return vcycle_v1(s, l, w);
+  Level &fine = s->lv[l], &coarse = s->lv[l + 1];
+  {
+    DownArgs a{levdev(fine), levdev(coarse), s->per};
+    DISPATCH_D(s, k_down, grid_inside(fine.lay), blk(s->D), a);
+    std::swap(fine.r, fine.eps);                     // K-DOWN staged the new residual in ϵ
+  }
+  if (level_is_small(coarse)) {
+    coarse_block(s, l + 1, w);
+  } else {
+    if (l + 2 < s->lv.size()) vcycle(s, l + 1, w);
+    smooth2(s, coarse, w, nullptr);
+  }
+  UpArgs u{levdev(fine), levdev(coarse), s->per, w, s->redw, s->d_red, 0};
+  DISPATCH_D(s, k_up, grid_inside(fine.lay), blk(s->D), u);
 }
 
 int fetch_red(wl_sim* s) {
@@ -247,16 +300,19 @@ struct Trace { int n = 0; int flags = 0; float rinf[34], r1[34], omega[34]; };
 
 // solver!(ml;tol,itmx) (MultiLevelPoisson.jl:108-128).  The loop exit and ω are steered by two
 // scalars per iteration, exactly as in the reference.
-int mlp_solver(wl_sim* s, Trace* tr) {
+int mlp_solver(wl_sim* s, Trace* tr, bool residual_done = false) {
   Level& p = s->lv[0];
   const double tol = s->cfg.tol;
   const double r1tol = (tol / 10) * (double)p.lay.ninside(), rinftol = tol;
   const int itmx = s->cfg.itmx;
-  perbc(s, p.lay, p.x.base);
+  const bool fused = !(s->cfg.flags & WL_FLAG_NO_FUSED);
   {
     LevArgs a = lev_args(s, p);
-    a.out = s->d_red + 0;
-    DISPATCH_D(s, k_residual, grid_inside(p.lay), blk(s->D), a);
+    if (!residual_done) {                       // K-DIVRES already produced r and Σr in slot 0
+      perbc(s, p.lay, p.x.base);
+      a.out = s->d_red + 0;
+      DISPATCH_D(s, k_residual, grid_inside(p.lay), blk(s->D), a);
+    }
     a.in = s->d_red + 0; a.out = s->d_red + 1;
     DISPATCH_D(s, k_shift_norms, grid_inside(p.lay), blk(s->D), a);
   }
@@ -265,8 +321,16 @@ int mlp_solver(wl_sim* s, Trace* tr) {
   int np = 0, flags = 0;
   if (tr) { tr->rinf[0] = rinf; tr->r1[0] = r1; tr->omega[0] = w; }
   while (np < itmx) {
-    vcycle(s, 0, w);
-    smooth(s, p, w, s->d_red + 1);
+    if (fused && level_is_small(p)) {            // the whole hierarchy fits the single-block kernel
+      coarse_block(s, 0, w);
+      LevArgs a = lev_args(s, p);
+      a.in = s->d_red + 7; a.out = s->d_red + 1; // slot 7 stays zero: no shift, norms only
+      DISPATCH_D(s, k_shift_norms, grid_inside(p.lay), blk(s->D), a);
+    } else {
+      vcycle(s, 0, w);
+      if (fused) smooth2(s, p, w, s->d_red + 1);
+      else smooth(s, p, w, s->d_red + 1);
+    }
     if (int e = fetch_red(s)) return e;
     const float rnew = (float)s->h_red[1].sum;
     rinf = s->h_red[1].maxv; ++np;
@@ -278,7 +342,7 @@ int mlp_solver(wl_sim* s, Trace* tr) {
     if ((double)r1 < r1tol && (double)rinf < rinftol) break;
   }
   if (np >= itmx) flags |= 2;
-  perbc(s, p.lay, p.x.base);
+  if (!residual_done) perbc(s, p.lay, p.x.base);   // fused projection wrap-reads x and stores p's images itself
   if (tr) { tr->n = np; tr->flags = flags; }
   return WL_OK;
 }
@@ -291,12 +355,76 @@ void mom_rhs(wl_sim* s, DevField& uadv, const float* acc) {
   for (int d = 0; d < 3; ++d) a.acc.v[d] = acc ? acc[d] : 0.f;
   DISPATCH_DS(s, k_mom_rhs, grid_all(s->lay), blk(s->D), a);
 }
+// list of band cells for k_mom_patch; rebuilt when μ₁ changed (measure!, uploads)
+int band_rebuild(wl_sim* s) {
+  for (int pass = 0; pass < 2; ++pass) {
+    WL_CUDA(s, cudaMemsetAsync(s->band_count, 0, sizeof(int), s->st));
+    BandArgs a{s->lay, s->mu1.base, s->band_list, s->band_count, s->band_cap};
+    DISPATCH_D(s, k_band_scan, grid_inside(s->lay), blk(s->D), a);
+    int n = 0;
+    WL_CUDA(s, cudaMemcpyAsync(&n, s->band_count, sizeof(int), cudaMemcpyDeviceToHost, s->st));
+    WL_CUDA(s, cudaStreamSynchronize(s->st));
+    if (n <= s->band_cap) break;
+    if (s->band_list) cudaFree(s->band_list);
+    s->band_cap = n + n / 4 + 1024;
+    WL_CUDA(s, cudaMalloc(&s->band_list, sizeof(int) * (size_t)s->band_cap));
+  }
+  s->band_dirty = false;
+  return WL_OK;
+}
+// K-MOM (3D fused): out = new velocity from ua (advecting) and u0
+void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, const float* acc) {
+  Mom3Args a{};
+  a.l = s->lay; a.ua = ua.base; a.u0 = u0.base; a.V = s->V.base; a.mu0 = s->mu0.base; a.un = out.base;
+  a.per = s->per; a.nu = s->cfg.nu; a.dt = s->dt; a.corrector = corrector;
+  for (int d = 0; d < 3; ++d) a.acc.v[d] = acc ? acc[d] : 0.f;
+  const Lay& l = s->lay;
+  // march length: as long as possible (amortises the extra flux plane) while keeping >= 6 waves of
+  // 2 blocks/SM on 148 SMs
+  a.KZ = 64;
+  while (a.KZ > 8 && (long long)((l.n0 - 2 + 30) / 31) * ((l.n1 - 2 + M3_TY - 2) / (M3_TY - 1)) *
+                             ((l.n2 - 2 + a.KZ - 1) / a.KZ) < 148 * 2 * 6)
+    a.KZ >>= 1;
+  dim3 g((l.n0 - 2 + 30) / 31, (l.n1 - 2 + M3_TY - 2) / (M3_TY - 1), (l.n2 - 2 + a.KZ - 1) / a.KZ);
+  dim3 b(32, M3_TY, 1);
+  const int sc = s->cfg.scheme;
+  if (sc == 0) LAUNCH(s, k_mom3<0>, g, b, a);
+  else if (sc == 1) LAUNCH(s, k_mom3<1>, g, b, a);
+  else LAUNCH(s, k_mom3<2>, g, b, a);
+  PatchArgs pa{};
+  pa.m.l = s->lay; pa.m.ua = ua.base; pa.m.u0 = u0.base; pa.m.V = s->V.base; pa.m.f = nullptr;
+  pa.m.per = s->per; pa.m.nu = s->cfg.nu; pa.m.dt = s->dt; pa.m.acc = a.acc;
+  pa.mu0 = s->mu0.base; pa.mu1 = s->mu1.base; pa.un = out.base;
+  pa.list = s->band_list; pa.count = s->band_count; pa.cap = s->band_cap; pa.corrector = corrector;
+  if (s->band_cap > 0) {
+    if (sc == 0) LAUNCH(s, k_mom_patch<0>, dim3(1184), dim3(128), pa);
+    else if (sc == 1) LAUNCH(s, k_mom_patch<1>, dim3(1184), dim3(128), pa);
+    else LAUNCH(s, k_mom_patch<2>, dim3(1184), dim3(128), pa);
+  }
+  if (s->cfg.exitBC) {
+    ExitCopyArgs e{s->lay, ua.base, out.base};
+    LAUNCH(s, k_copy_exit_plane, dim3((l.n1 + 127) / 128, l.n2), dim3(128), e);
+  }
+}
 void bdim(wl_sim* s, int corrector) {
   BdimArgs a{s->lay, s->u.base, s->f.base, s->V.base, s->mu0.base, s->mu1.base, corrector};
   DISPATCH_D(s, k_bdim, grid_inside(s->lay), blk(s->D), a);
 }
 // mom_project!(a,b,w,t) (Flow.jl:223-232)
 int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
+  if (!(s->cfg.flags & WL_FLAG_NO_FUSED)) {
+    Level& p0 = s->lv[0];
+    const float dt = w * s->dt;
+    DivResArgs d{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, p0.r.base, s->per, dt, s->redw, s->d_red + 0};
+    DISPATCH_D(s, k_divres, grid_inside(s->lay), blk(s->D), d);
+    std::swap(s->p, p0.eps); p0.x = s->p;                       // scaled x lives in the former ϵ buffer
+    if (int e = mlp_solver(s, tr, true)) return e;
+    ProjArgs2 q{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, s->per, dt};
+    DISPATCH_D(s, k_proj, grid_inside(s->lay), blk(s->D), q);
+    std::swap(s->p, p0.eps); p0.x = s->p;
+    bc_vec(s, s->u, U, s->cfg.exitBC != 0);
+    return WL_OK;
+  }
   ProjArgs a{s->lay, s->u.base, s->p.base, s->sigma.base, s->mu0.base, w * s->dt};
   DISPATCH_D(s, k_div_scale, grid_all(s->lay), blk(s->D), a);
   if (int e = mlp_solver(s, tr)) return e;

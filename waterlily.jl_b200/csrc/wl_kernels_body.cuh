@@ -69,8 +69,8 @@ __device__ __forceinline__ Meas measure_pt(const BodyDev& b, const float* x, flo
 }
 
 // kernels Body.jl:54-60
-// Julia's sinpi/cospi are accurate to the last bit: evaluate in double and round once (the oracle
-// does the same), so μ₀/μ₁ agree bit for bit.  Only band cells reach these, the cost is nil.
+// Julia's sinpi/cospi are accurate to the last bit: evaluate in double and round once (the CPU
+// checker does the same), so μ₀/μ₁ agree bit for bit.  Only band cells reach these, the cost is nil.
 __device__ __forceinline__ float sinpi_r(float d) { return (float)sin(3.14159265358979323846 * (double)d); }
 __device__ __forceinline__ float cospi_r(float d) { return (float)cos(3.14159265358979323846 * (double)d); }
 __device__ __forceinline__ float kern(float d) { return (1.f + cospi_r(d)) / 2.f; }

@@ -1,0 +1,388 @@
+// wl_kernels_mg2.cuh -- fused pressure-side kernels (v2).
+//
+//  * Periodic directions are handled by WRAP-READS: a kernel that the reference precedes with
+//    perBC!(a) reads a's wrapped interior value instead of a ghost, so the ghost-fill launches
+//    disappear.  Where the reference's ghosts are observable or deliberately stale (ϵ during the
+//    red-black sweeps, the final pressure) the producing thread also stores the periodic images.
+//  * K-DIVRES  = `@inside z=div(u)`, `x.*=dt`, perBC!(x), residual! loop 1, Σr   (Flow.jl:225, Poisson.jl:92-95)
+//  * K-DOWN    = Jacobi! (ϵ=r·iD, perBC!, increment! with ω=1) + restrict! + fill!(coarse.x,0)
+//                (Poisson.jl:100-114, MultiLevelPoisson.jl:92-94); one thread per COARSE cell
+//  * K-UP      = prolongate! + perBC! + increment!(ω)                          (MultiLevelPoisson.jl:99-100)
+//  * K-PROJ    = u -= L·∂x for every component, x./=dt, perBC!(x)              (Flow.jl:227-230, MLP.jl:126)
+//  * k_coarse  = every level below a size threshold in ONE single-block launch (the V-cycle recursion
+//                from that level down and back up, plus its smoother), because those levels are pure
+//                launch latency.
+// All arithmetic keeps the reference's operation order: results are bit-identical to the v1 kernels.
+#pragma once
+#include "wl_kernels_mg.cuh"
+
+namespace wl {
+
+struct LevDev {
+  Lay l;
+  const float* L;
+  const float* iD;
+  float* x;
+  float* r;
+  float* eps;
+  int c[3];          // coarsening mask from the next finer level to this one
+};
+
+// offsets of the lower/upper neighbour in direction d for an INTERIOR cell, wrapped when periodic
+template <int D>
+__device__ __forceinline__ void nbr_off(const Lay& l, const Per& per, int i, int j, int k, int* om, int* op) {
+  const int c[3] = {i, j, k};
+  const int N[3] = {l.n0, l.n1, l.n2};
+  const int st[3] = {1, l.pitch, l.plane};
+#pragma unroll
+  for (int d = 0; d < D; ++d) {
+    om[d] = (per.p[d] && c[d] == 1) ? (N[d] - 3) * st[d] : -st[d];
+    op[d] = (per.p[d] && c[d] == N[d] - 2) ? -(N[d] - 3) * st[d] : st[d];
+  }
+}
+// store v into every periodic image (ghost copy) of interior cell (i,j,k): what the sequential
+// perBC! passes (core.jl:239-243) leave in the ghosts, edges and corners included.
+template <int D>
+__device__ __forceinline__ void store_images(float* a, const Lay& l, const Per& per, int i, int j, int k, float v) {
+  const int c[3] = {i, j, k};
+  const int N[3] = {l.n0, l.n1, l.n2};
+  int img[3];
+  bool any = false;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    img[d] = -1;
+    if (d < D && per.p[d]) {
+      if (c[d] == 1) img[d] = N[d] - 1;
+      else if (c[d] == N[d] - 2) img[d] = 0;
+      if (N[d] == 3 && c[d] == 1) img[d] = -2;      // degenerate single-cell direction: both ghosts
+    }
+    any |= img[d] != -1;
+  }
+  if (!any) return;
+  for (int m = 1; m < 8; ++m) {
+    int q[3];
+    bool ok = true;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      if (m & (1 << d)) { if (img[d] < 0) ok = false; q[d] = img[d]; } else q[d] = c[d];
+    }
+    if (ok) a[l.off(q[0], q[1], q[2])] = v;
+  }
+}
+// `mult` (Poisson.jl:70-76) at an interior cell with wrapped neighbour offsets
+template <int D>
+__device__ __forceinline__ float multA_w(const Lay& l, const float* __restrict__ L, const float* __restrict__ x, int o,
+                                         const int* om, const int* op) {
+  const int st[3] = {1, l.pitch, l.plane};
+  float s = x[o] * diagL<D>(l, L, o);
+#pragma unroll
+  for (int d = 0; d < D; ++d) {
+    const float* Ld = L + l.cstride * d;
+    s += x[o + om[d]] * Ld[o] + x[o + op[d]] * Ld[o + st[d]];
+  }
+  return s;
+}
+
+#define WL_IJK_FROM_BLOCK(D, l)                                                 \
+  const int i = blockIdx.x * 32 + threadIdx.x + 1;                              \
+  const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;                      \
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;         \
+  const bool inb = !(i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && k > l.n2 - 2));
+
+// ---------------------------------------------------------------- K-DIVRES
+// x·dt is written to a second buffer `xs` (the level's idle ϵ array; the host then swaps the two
+// pointers) because neighbours still read the unscaled x.  Non-periodic ghosts of every scalar work
+// array are zero for the whole run, periodic ghosts are rewritten by whoever needs them, so the
+// buffers are interchangeable.
+struct DivResArgs { Lay l; const float* u; const float* x; float* xs; const float* L; float* r; Per per; float dt; RedWork w; Red* out; };
+template <int D>
+__global__ void __launch_bounds__(256) k_divres(const DivResArgs a) {
+  const Lay& l = a.l;
+  WL_IJK_FROM_BLOCK(D, l)
+  double s = 0.0;
+  if (inb) {
+    const int o = l.off(i, j, k);
+    const int st[3] = {1, l.pitch, l.plane};
+    int om[3], op[3];
+    nbr_off<D>(l, a.per, i, j, k, om, op);
+    float z = 0.f;
+#pragma unroll
+    for (int d = 0; d < D; ++d) { const float* ud = a.u + l.cstride * d; z += ud[o + st[d]] - ud[o]; }
+    const float dg = diagL<D>(l, a.L, o);
+    const float xc = a.x[o] * a.dt;
+    float r = 0.f;
+    if (dg != 0.f) {
+      float ax = xc * dg;
+#pragma unroll
+      for (int d = 0; d < D; ++d) {
+        const float* Ld = a.L + l.cstride * d;
+        ax += (a.x[o + om[d]] * a.dt) * Ld[o] + (a.x[o + op[d]] * a.dt) * Ld[o + st[d]];
+      }
+      r = z - ax;
+    }
+    a.r[o] = r;
+    a.xs[o] = xc;
+    s = (double)r;
+  }
+  block_reduce_finish(s, -INFINITY, a.w, a.out);
+}
+
+// ---------------------------------------------------------------- K-DOWN
+struct DownArgs { LevDev f, c; Per per; };
+// One thread per FINE cell (coalesced); the children of a coarse cell sit in one block (block
+// extents are even and blocks start on odd interior indices), so the restriction gathers them from
+// shared memory and adds them in the reference's order (first dimension fastest).
+template <int D>
+__global__ void __launch_bounds__(256) k_down(const DownArgs a) {
+  __shared__ float tile[256];
+  const Lay& lc = a.c.l;
+  const Lay& l = a.f.l;
+  WL_IJK_FROM_BLOCK(D, l)
+  const int tid = threadIdx.x + 32 * (threadIdx.y + blockDim.y * threadIdx.z);
+  float rn = 0.f;
+  if (inb) {
+    const int o = l.off(i, j, k);
+    const int st[3] = {1, l.pitch, l.plane};
+    int om[3], op[3];
+    nbr_off<D>(l, a.per, i, j, k, om, op);
+    const float e0 = a.f.r[o] * a.f.iD[o];                           // ϵ = r·iD  Poisson.jl:112
+    float s = e0 * diagL<D>(l, a.f.L, o);                              // mult(I,L,D,ϵ)
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+      const float* Ld = a.f.L + l.cstride * d;
+      const float em = a.f.r[o + om[d]] * a.f.iD[o + om[d]];
+      const float ep = a.f.r[o + op[d]] * a.f.iD[o + op[d]];
+      s += em * Ld[o] + ep * Ld[o + st[d]];
+    }
+    rn = a.f.r[o] - s;                                                 // increment!, ω = 1  Poisson.jl:102
+    // r is still being read by the neighbours' ϵ: the new residual goes to the idle ϵ array and
+    // the host swaps the two pointers afterwards
+    a.f.eps[o] = rn;
+    a.f.x[o] = a.f.x[o] + e0;                                          // Poisson.jl:103
+  }
+  tile[tid] = rn;
+  __syncthreads();
+  if (!inb) return;
+  const int c[3] = {i, j, k};
+  const int t[3] = {(int)threadIdx.x, (int)threadIdx.y, (int)threadIdx.z};
+  int cc[3], n[3];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const bool co = d < D && a.c.c[d];
+    if (co && (t[d] & 1)) return;                                      // not the first child in this direction
+    cc[d] = co ? (c[d] + 1) / 2 : c[d];
+    n[d] = co ? 2 : 1;
+  }
+  float sum = 0.f;                                                     // restrict  MLP.jl:13-19
+  for (int kk = 0; kk < n[2]; ++kk)
+    for (int jj = 0; jj < n[1]; ++jj)
+      for (int ii = 0; ii < n[0]; ++ii) sum += tile[tid + ii + 32 * (jj + (int)blockDim.y * kk)];
+  const int oc = lc.off(cc[0], cc[1], cc[2]);
+  a.c.r[oc] = sum;
+  a.c.x[oc] = 0.f;                                                     // fill!(coarse.x,0)  MLP.jl:94
+}
+
+// ---------------------------------------------------------------- K-UP
+struct UpArgs { LevDev f, c; Per per; float omega; RedWork w; Red* out; int want_norms; };
+template <int D>
+__global__ void __launch_bounds__(256) k_up(const UpArgs a) {
+  const Lay& l = a.f.l;
+  WL_IJK_FROM_BLOCK(D, l)
+  double s1 = 0.0; float m = -INFINITY;
+  if (inb) {
+    const int o = l.off(i, j, k);
+    const int st[3] = {1, l.pitch, l.plane};
+    const int c[3] = {i, j, k};
+    const int N[3] = {l.n0, l.n1, l.n2};
+    const int cst[3] = {1, a.c.l.pitch, a.c.l.plane};
+    // coarse coordinate of the cell and of its (periodically wrapped) neighbours: down(I,c) MLP.jl:7
+    int cc[3], ccm[3], ccp[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      const bool co = d < D && a.c.c[d];
+      const int xm = (d < D && a.per.p[d] && c[d] == 1) ? N[d] - 2 : c[d] - 1;
+      const int xp = (d < D && a.per.p[d] && c[d] == N[d] - 2) ? 1 : c[d] + 1;
+      cc[d] = co ? (c[d] + 1) / 2 : c[d];
+      ccm[d] = co ? (xm + 1) / 2 : xm;
+      ccp[d] = co ? (xp + 1) / 2 : xp;
+    }
+    const int oc = a.c.l.off(cc[0], cc[1], cc[2]);
+    const float e0 = a.c.x[oc];
+    float s = e0 * diagL<D>(l, a.f.L, o);
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+      const float* Ld = a.f.L + l.cstride * d;
+      s += a.c.x[oc + (ccm[d] - cc[d]) * cst[d]] * Ld[o] + a.c.x[oc + (ccp[d] - cc[d]) * cst[d]] * Ld[o + st[d]];
+    }
+    const float r = a.f.r[o] - a.omega * s;
+    a.f.r[o] = r;
+    a.f.x[o] = a.f.x[o] + a.omega * e0;
+    s1 = (double)fabsf(r); m = fabsf(r);
+  }
+  if (a.want_norms) block_reduce_finish(s1, m, a.w, a.out);
+}
+
+// ---------------------------------------------------------------- smoother pieces
+// ϵ = r·iD inside + perBC!(ϵ) images  (GaussSeidelRB! Poisson.jl:142-143).  The sweeps then read
+// these ghosts as they are (never refreshed between sweeps: the reference's stale-ghost behaviour).
+struct SmArgs { LevDev p; Per per; float omega; int k0; RedWork w; Red* out; int want_norms; };
+template <int D>
+__global__ void __launch_bounds__(256) k_eps_init_g(const SmArgs a) {
+  const Lay& l = a.p.l;
+  WL_IJK_FROM_BLOCK(D, l)
+  if (!inb) return;
+  const int o = l.off(i, j, k);
+  const float e = a.p.r[o] * a.p.iD[o];
+  a.p.eps[o] = e;
+  store_images<D>(a.p.eps, l, a.per, i, j, k, e);
+}
+// increment! (Poisson.jl:100-104) with the perBC!(ϵ) folded into wrap-reads; optional L₁/L∞ of the new r
+template <int D>
+__global__ void __launch_bounds__(256) k_increment_w(const SmArgs a) {
+  const Lay& l = a.p.l;
+  WL_IJK_FROM_BLOCK(D, l)
+  double s1 = 0.0; float m = -INFINITY;
+  if (inb) {
+    const int o = l.off(i, j, k);
+    int om[3], op[3];
+    nbr_off<D>(l, a.per, i, j, k, om, op);
+    const float r = a.p.r[o] - a.omega * multA_w<D>(l, a.p.L, a.p.eps, o, om, op);
+    a.p.r[o] = r;
+    a.p.x[o] = a.p.x[o] + a.omega * a.p.eps[o];
+    s1 = (double)fabsf(r); m = fabsf(r);
+  }
+  if (a.want_norms) block_reduce_finish(s1, m, a.w, a.out);
+}
+
+// ---------------------------------------------------------------- K-PROJ
+// u[I,i] -= L[I,i]·(x[I]-x[I-δᵢ]) for all i (after the solver's final perBC!(x): wrap-read), and the
+// unscaled pressure p = x/dt with its periodic images, written to the spare buffer (host swaps).
+struct ProjArgs2 { Lay l; float* u; const float* x; float* pn; const float* L; Per per; float dt; };
+template <int D>
+__global__ void __launch_bounds__(256) k_proj(const ProjArgs2 a) {
+  const Lay& l = a.l;
+  WL_IJK_FROM_BLOCK(D, l)
+  if (!inb) return;
+  const int o = l.off(i, j, k);
+  int om[3], op[3];
+  nbr_off<D>(l, a.per, i, j, k, om, op);
+  const float xc = a.x[o];
+#pragma unroll
+  for (int d = 0; d < D; ++d) {
+    const long long oc = l.cstride * d + o;
+    a.u[oc] -= a.L[oc] * (xc - a.x[o + om[d]]);
+  }
+  const float p = xc / a.dt;
+  a.pn[o] = p;
+  store_images<D>(a.pn, l, a.per, i, j, k, p);
+}
+
+// ---------------------------------------------------------------- all small levels in one block
+constexpr int WL_MAXLEV = 12;
+struct CoarseArgs {
+  LevDev lv[WL_MAXLEV];
+  int first, nlev;     // levels first..nlev-1 are processed here
+  Per per;
+  float omega;
+};
+template <int D, class F>
+__device__ __forceinline__ void for_inside(const Lay& l, F f) {
+  const int m0 = l.n0 - 2, m1 = l.n1 - 2, m2 = D == 3 ? l.n2 - 2 : 1;
+  const int tot = m0 * m1 * m2;
+  for (int q = threadIdx.x; q < tot; q += blockDim.x) {
+    const int i = 1 + q % m0, t = q / m0, j = 1 + t % m1, k = D == 3 ? 1 + t / m1 : 0;
+    f(i, j, k, l.off(i, j, k));
+  }
+}
+template <int D>
+__device__ void blk_smooth(const LevDev& p, const Per& per, float w) {
+  const Lay& l = p.l;
+  for_inside<D>(l, [&](int i, int j, int k, int o) {
+    const float e = p.r[o] * p.iD[o];
+    p.eps[o] = e;
+    store_images<D>(p.eps, l, per, i, j, k, e);
+  });
+  __syncthreads();
+  const int st[3] = {1, l.pitch, l.plane};
+  const int nl = D == 3 ? l.n2 : l.n1;
+  for (int k0 = 1; k0 <= 4; ++k0) {
+    for_inside<D>(l, [&](int i, int j, int k, int o) {
+      const int cl = D == 3 ? k : j;
+      if (cl > 2 * (nl / 2) - 2) return;
+      const int jsum = i + j + (D == 3 ? k : 0) + D;
+      if (((jsum ^ (k0 + 1)) & 1) != 0) return;
+      float s = p.r[o];
+#pragma unroll
+      for (int q = 0; q < D; ++q) {
+        const float* Lq = p.L + l.cstride * q;
+        s -= p.eps[o - st[q]] * Lq[o] + p.eps[o + st[q]] * Lq[o + st[q]];
+      }
+      p.eps[o] = s * p.iD[o];
+    });
+    __syncthreads();
+  }
+  for_inside<D>(l, [&](int i, int j, int k, int o) {
+    int om[3], op[3];
+    nbr_off<D>(l, per, i, j, k, om, op);
+    p.r[o] = p.r[o] - w * multA_w<D>(l, p.L, p.eps, o, om, op);
+    p.x[o] = p.x[o] + w * p.eps[o];
+  });
+  __syncthreads();
+}
+// Vcycle!(ml;l=first,ω) followed by smooth!(levels[first];ω)   (MultiLevelPoisson.jl:88-101,106)
+template <int D>
+__global__ void __launch_bounds__(1024) k_coarse(const CoarseArgs a) {
+  const int last = a.nlev - 1;
+  for (int lev = a.first; lev < last; ++lev) {            // way down: Jacobi!, restrict!, fill!(x,0)
+    const LevDev& f = a.lv[lev];
+    const LevDev& c = a.lv[lev + 1];
+    const Lay& l = f.l;
+    for_inside<D>(l, [&](int i, int j, int k, int o) { f.eps[o] = f.r[o] * f.iD[o]; });
+    __syncthreads();
+    for_inside<D>(l, [&](int i, int j, int k, int o) {
+      int om[3], op[3];
+      nbr_off<D>(l, a.per, i, j, k, om, op);
+      f.r[o] = f.r[o] - multA_w<D>(l, f.L, f.eps, o, om, op);
+      f.x[o] = f.x[o] + f.eps[o];
+    });
+    __syncthreads();
+    for_inside<D>(c.l, [&](int ci, int cj, int ck, int oc) {
+      const int cc[3] = {ci, cj, ck};
+      int lo[3], hi[3];
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        if (d >= D) { lo[d] = hi[d] = 0; }
+        else if (!c.c[d]) { lo[d] = hi[d] = cc[d]; }
+        else { lo[d] = 2 * cc[d] - 1; hi[d] = 2 * cc[d]; }
+      }
+      float s = 0.f;
+      for (int kk = lo[2]; kk <= hi[2]; ++kk)
+        for (int jj = lo[1]; jj <= hi[1]; ++jj)
+          for (int ii = lo[0]; ii <= hi[0]; ++ii) s += f.r[l.off(ii, jj, kk)];
+      c.r[oc] = s;
+      c.x[oc] = 0.f;
+    });
+    __syncthreads();
+  }
+  for (int lev = last - 1; lev >= a.first; --lev) {       // way up: smooth!(coarse), prolongate!, increment!
+    const LevDev& f = a.lv[lev];
+    const LevDev& c = a.lv[lev + 1];
+    blk_smooth<D>(c, a.per, a.omega);
+    const Lay& l = f.l;
+    for_inside<D>(l, [&](int i, int j, int k, int o) {
+      const int ci = c.c[0] ? (i + 1) / 2 : i, cj = c.c[1] ? (j + 1) / 2 : j, ck = (D == 3 && c.c[2]) ? (k + 1) / 2 : k;
+      f.eps[o] = c.x[c.l.off(ci, cj, ck)];
+    });
+    __syncthreads();
+    for_inside<D>(l, [&](int i, int j, int k, int o) {
+      int om[3], op[3];
+      nbr_off<D>(l, a.per, i, j, k, om, op);
+      f.r[o] = f.r[o] - a.omega * multA_w<D>(l, f.L, f.eps, o, om, op);
+      f.x[o] = f.x[o] + a.omega * f.eps[o];
+    });
+    __syncthreads();
+  }
+  blk_smooth<D>(a.lv[a.first], a.per, a.omega);
+}
+
+}  // namespace wl

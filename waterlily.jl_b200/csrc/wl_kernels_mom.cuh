@@ -56,6 +56,37 @@ struct MomArgs {
 //   f[I,i] = u⁰[I,i] + Δt·(r[I,i]+acc_i) − V[I,i]  over ALL indices,
 // with r accumulated exactly in the reference's order (for j: +Φ_low, −Φ_up) and r==0 on cells
 // the reference never writes (any coordinate on the lower ghost).  One thread per cell.
+// f[I,ci] for ANY cell (ghosts included) straight from global memory, in the reference's order.
+template <int D, int S>
+__device__ __forceinline__ float rhs_f(const MomArgs& a, int ci, int c0, int c1, int c2) {
+  const Lay& l = a.l;
+  const int o = l.off(c0, c1, c2);
+  const int c[3] = {c0, c1, c2};
+  const int N[3] = {l.n0, l.n1, l.n2};
+  const int st[3] = {1, l.pitch, l.plane};
+  bool lowghost = false;
+#pragma unroll
+  for (int d = 0; d < D; ++d) lowghost |= (c[d] == 0);
+  const float* ui = a.ua + l.cstride * ci;
+  float r = 0.f;
+  if (!lowghost) {
+#pragma unroll
+    for (int dj = 0; dj < D; ++dj) {
+      if (c[dj] > N[dj] - 2) continue;               // upper ghost in j: no j-contribution
+      const float* uj = a.ua + l.cstride * dj;
+      const bool pj = a.per.p[dj] != 0;
+      r += face_flux<S>(ui, uj, o, st[ci], st[dj], c[dj], N[dj], pj, a.nu);
+      if (c[dj] == N[dj] - 2 && pj)                  // Φ[CIj(j,I,2)] Flow.jl:62
+        r -= face_flux<S>(ui, uj, o - st[dj] * (N[dj] - 3), st[ci], st[dj], 1, N[dj], true, a.nu);
+      else
+        r -= face_flux<S>(ui, uj, o + st[dj], st[ci], st[dj], c[dj] + 1, N[dj], pj, a.nu);
+    }
+  }
+  r += a.acc.v[ci];
+  const long long oc = l.cstride * ci + o;
+  return a.u0[oc] + a.dt * r - a.V[oc];
+}
+
 template <int D, int S>
 __global__ void __launch_bounds__(256) k_mom_rhs(const MomArgs a) {
   const Lay& l = a.l;
@@ -64,33 +95,8 @@ __global__ void __launch_bounds__(256) k_mom_rhs(const MomArgs a) {
   const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z : 0;
   if (i < 0 || i >= l.n0 || j >= l.n1 || k >= l.n2) return;
   const int o = l.off(i, j, k);
-  const int c[3] = {i, j, k};
-  const int N[3] = {l.n0, l.n1, l.n2};
-  const int st[3] = {1, l.pitch, l.plane};
-  bool lowghost = false;
 #pragma unroll
-  for (int d = 0; d < D; ++d) lowghost |= (c[d] == 0);
-#pragma unroll
-  for (int ci = 0; ci < D; ++ci) {
-    const float* ui = a.ua + a.l.cstride * ci;
-    float r = 0.f;
-    if (!lowghost) {
-#pragma unroll
-      for (int dj = 0; dj < D; ++dj) {
-        if (c[dj] > N[dj] - 2) continue;               // upper ghost in j: no j-contribution
-        const float* uj = a.ua + a.l.cstride * dj;
-        const bool pj = a.per.p[dj] != 0;
-        r += face_flux<S>(ui, uj, o, st[ci], st[dj], c[dj], N[dj], pj, a.nu);
-        if (c[dj] == N[dj] - 2 && pj)                  // Φ[CIj(j,I,2)] Flow.jl:62
-          r -= face_flux<S>(ui, uj, o - st[dj] * (N[dj] - 3), st[ci], st[dj], 1, N[dj], true, a.nu);
-        else
-          r -= face_flux<S>(ui, uj, o + st[dj], st[ci], st[dj], c[dj] + 1, N[dj], pj, a.nu);
-      }
-    }
-    r += a.acc.v[ci];
-    const long long oc = a.l.cstride * ci + o;
-    a.f[oc] = a.u0[oc] + a.dt * r - a.V[oc];
-  }
+  for (int ci = 0; ci < D; ++ci) a.f[l.cstride * ci + o] = rhs_f<D, S>(a, ci, i, j, k);
 }
 
 struct BdimArgs {

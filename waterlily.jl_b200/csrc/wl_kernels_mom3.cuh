@@ -1,0 +1,272 @@
+// wl_kernels_mom3.cuh -- K-MOM: the fused 3D momentum predictor/corrector.
+//
+// One kernel replaces, per phase, `conv_diff!` (1+9·4 launches), `accelerate!`, both loops of
+// `BDIM!` and `scale_u!` (reference src/Flow.jl:38-62,69-73,176-180,211-214).  The flux scratch Φ
+// and the force field f never touch HBM: the kernel reads the advecting velocity (+u⁰, V, μ₀) and
+// writes the new velocity into a third rotating buffer (u⁰ .= u becomes a pointer swap).
+//
+// Decomposition: a block owns a 31×7 column of cells and marches KZ planes up the last
+// dimension.  Every thread evaluates the 9 LOWER-face fluxes Φ[ci][dj] of its cell once; the
+// upper-face fluxes come from the neighbour that owns them:
+//    x: lane+1 by warp shuffle (warps overlap by one cell: 32 faces -> 31 cells),
+//    y: row+1 through a double-buffered shared-memory plane (one __syncthreads per plane),
+//    z: the next plane of the march (the cell is finalised one plane later, from registers).
+// The sum r = Σ_j (+Φ_low −Φ_up) is accumulated in exactly the reference's order, so results are
+// bit-identical to the two-launch scatter of Flow.jl:47-49.  Domain-boundary faces use the
+// ϕuL/ϕuR/ϕuP variants (Flow.jl:9-11,56-62); periodic wrap values come straight from global memory.
+// Blocks that touch no x/y domain boundary run a branch-free FAST body (compile-time face kinds,
+// immediate x offsets, no index clamps); edge blocks run the general body.
+//
+// BDIM: the main kernel assumes μ₁ ≡ 0 (then μddn ≡ 0 exactly) and never reads μ₁ (36 of the 84
+// algorithmic B/cell); the few cells in the body band are recomputed afterwards by k_mom_patch
+// from the exact reference formula, f-neighbours on ghost rows included (Flow.jl:20-26,179).
+#pragma once
+#include "wl_kernels_mom.cuh"
+
+namespace wl {
+
+// x/6 correctly rounded in 3 instructions (Markstein: q0 = x·RN(1/6), r = fma(-6,q0,x) exact,
+// q = fma(r,RN(1/6),q0)); verified bit-identical to IEEE x/6.0f for EVERY float with
+// 1e-30 < |x| < 1e38 (exhaustive 2^32 sweep); outside that range fall back to the IEEE division.
+__device__ __forceinline__ float div6(float x) {
+  const float ax = fabsf(x);
+  if (ax > 1e-30f && ax < 1e38f) {
+    const float y = 1.0f / 6.0f;
+    const float q0 = __fmul_rn(x, y);
+    const float r = __fmaf_rn(-6.0f, q0, x);
+    return __fmaf_rn(r, y, q0);
+  }
+  if (x == 0.f) return x;
+  return x / 6.f;
+}
+// median of three by min/max: same value as Flow.jl:27-36 for all non-NaN inputs, 4 instructions
+__device__ __forceinline__ float med3(float a, float b, float c) { return fmaxf(fminf(a, b), fminf(fmaxf(a, b), c)); }
+template <int S>
+__device__ __forceinline__ float lamf(float u, float c, float d) {
+  if (S == 0) return med3(div6(5.f * c + 2.f * d - u), c, med3(10.f * c - 9.f * u, c, d));
+  if (S == 1) return (c + d) / 2.f;
+  return (c <= fminf(u, d) || c >= fmaxf(u, d)) ? c : c + (d - c) * (c - u) / (d - u);
+}
+// kind: 0 inner (ϕu), 1 lower non-periodic (ϕuL), 2 lower periodic (ϕuP; caller passes the wrapped
+// far-upstream value as um2), 3 upper non-periodic (ϕuR).
+template <int S>
+__device__ __forceinline__ float flux_v(float um2, float um1, float uc, float up1, float ua, float nu, int kind) {
+  const bool pos = ua > 0.f;
+  float v = lamf<S>(pos ? um2 : up1, pos ? um1 : uc, pos ? uc : um1);
+  if ((kind == 1 && pos) || (kind == 3 && ua < 0.f)) v = (uc + um1) / 2.f;
+  return ua * v - nu * (uc - um1);
+}
+
+struct Mom3Args {
+  Lay l;
+  const float* ua;    // advecting velocity: u⁰ (predictor) / projected u (corrector)
+  const float* u0;    // u⁰
+  const float* V;
+  const float* mu0;
+  float* un;          // output velocity buffer (distinct from ua and u0)
+  Per per;
+  float nu, dt;
+  Vec3 acc;
+  int corrector;
+  int KZ;
+};
+
+constexpr int M3_TY = 8;
+
+template <int S, bool FAST>
+__device__ __forceinline__ void mom3_body(const Mom3Args& a, float (*shy)[3][M3_TY][32]) {
+  const Lay& l = a.l;
+  const int lane = threadIdx.x, ty = threadIdx.y;
+  const int N0 = l.n0, N1 = l.n1, N2 = l.n2;
+  const int pitch = l.pitch, plane = l.plane;
+  const int i_raw = 1 + 31 * blockIdx.x + lane, j_raw = 1 + (M3_TY - 1) * blockIdx.y + ty;
+  const int i = FAST ? i_raw : min(i_raw, N0 - 1), j = FAST ? j_raw : min(j_raw, N1 - 1);
+  const int k0 = 1 + a.KZ * blockIdx.z;
+  const int kend = min(k0 + a.KZ, N2 - 1);           // last plane visited: only Φ_z is needed there
+  const bool out_ij = lane < 31 && ty < M3_TY - 1 && (FAST || (i_raw <= N0 - 2 && j_raw <= N1 - 2));
+  const int oij = i + pitch * j;
+  // in-plane neighbour offsets; in the general body they are clamped (clamped values are never
+  // consumed: boundary faces use the one-sided variants)
+  const int dx0 = FAST ? -2 : max(i - 2, 0) - i, dx2 = FAST ? 1 : min(i + 1, N0 - 1) - i;
+  const int dy0 = FAST ? -2 * pitch : (max(j - 2, 0) - j) * pitch, dy1 = -pitch,
+            dy2 = FAST ? pitch : (min(j + 1, N1 - 1) - j) * pitch;
+  const bool p0 = a.per.p[0] != 0, p1 = a.per.p[1] != 0, p2 = a.per.p[2] != 0;
+  const int kx = FAST ? 0 : (i == 1 ? (p0 ? 2 : 1) : (i == N0 - 1 ? (p0 ? 4 : 3) : 0));
+  const int ky = FAST ? 0 : (j == 1 ? (p1 ? 2 : 1) : (j == N1 - 1 ? (p1 ? 4 : 3) : 0));
+  const float* U[3] = {a.ua, a.ua + l.cstride, a.ua + 2 * l.cstride};
+  const float* pc[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) pc[c] = U[c] + (oij + plane * k0);
+  const float nu = a.nu;
+
+  float w[3][4];   // own column: planes k-2, k-1, k, k+1
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    w[c][0] = pc[c][plane * (max(k0 - 2, 0) - k0)];
+    w[c][1] = pc[c][-plane];
+    w[c][2] = pc[c][0];
+    w[c][3] = pc[c][plane * (min(k0 + 1, N2 - 1) - k0)];
+  }
+  float pend[3] = {0.f, 0.f, 0.f};
+
+  for (int k = k0; k <= kend; ++k) {
+    const bool lastp = k == kend;
+    const int kz = k == 1 ? (p2 ? 2 : 1) : (k == N2 - 1 ? (p2 ? 4 : 3) : 0);
+    float nb[3][3][3];   // nb[c][d][m2,m1,p1]
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      nb[c][2][0] = w[c][0]; nb[c][2][1] = w[c][1]; nb[c][2][2] = w[c][3];
+      if (!lastp) {
+        nb[c][0][0] = pc[c][dx0]; nb[c][0][1] = pc[c][-1]; nb[c][0][2] = pc[c][dx2];
+        nb[c][1][0] = pc[c][dy0]; nb[c][1][1] = pc[c][dy1]; nb[c][1][2] = pc[c][dy2];
+      } else {
+#pragma unroll
+        for (int q = 0; q < 3; ++q) { nb[c][0][q] = 0.f; nb[c][1][q] = 0.f; }
+      }
+    }
+    if (lastp) { nb[2][0][1] = pc[2][-1]; nb[2][1][1] = pc[2][dy1]; }   // for ū of the z faces
+    float F[3][3];
+#pragma unroll
+    for (int ci = 0; ci < 3; ++ci) {
+#pragma unroll
+      for (int dj = 0; dj < 3; ++dj) {
+        if (lastp && dj < 2) { F[ci][dj] = 0.f; continue; }
+        const int kind = dj == 0 ? kx : (dj == 1 ? ky : kz);
+        const int sdj = dj == 0 ? 1 : (dj == 1 ? pitch : plane);
+        const int Ndj = dj == 0 ? N0 : (dj == 1 ? N1 : N2);
+        if (kind == 4) {                                     // periodic upper face == Φ of the wrapped cell
+          const int sci = ci == 0 ? 1 : (ci == 1 ? pitch : plane);
+          const int o = oij + plane * k;
+          F[ci][dj] = face_flux<S>(U[ci], U[dj], o - sdj * (Ndj - 2), sci, sdj, 1, Ndj, true, nu);
+        } else {
+          const float ua = (w[dj][2] + nb[dj][ci][1]) / 2.f;  // ϕ(i,CI(I,j),u) Flow.jl:3
+          float um2 = nb[ci][dj][0];
+          if (kind == 2) um2 = pc[ci][sdj * (Ndj - 4)];       // CIj(j,·,N[j]-2) Flow.jl:61
+          F[ci][dj] = flux_v<S>(um2, nb[ci][dj][1], w[ci][2], nb[ci][dj][2], ua, nu, kind);
+        }
+      }
+    }
+    float Fxu[3], Fyu[3];
+    if (!lastp) {
+      const int buf = k & 1;
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci) {
+        Fxu[ci] = __shfl_down_sync(0xffffffffu, F[ci][0], 1);
+        shy[buf][ci][ty][lane] = F[ci][1];
+      }
+      __syncthreads();
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci) Fyu[ci] = shy[buf][ci][min(ty + 1, M3_TY - 1)][lane];
+    }
+    if (k > k0 && out_ij) {                                  // finalise cell (i,j,k-1)
+      const int op = oij + plane * (k - 1);
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci) {
+        float r = pend[ci] - F[ci][2];
+        r += a.acc.v[ci];
+        const long long oc = l.cstride * ci + op;
+        const float Vv = a.V[oc];
+        const float f = a.u0[oc] + a.dt * r - Vv;           // BDIM! loop 1, Flow.jl:178
+        const float X = Vv + a.mu0[oc] * f;                  // loop 2 with μ₁ ≡ 0, Flow.jl:179
+        a.un[oc] = a.corrector ? (w[ci][1] + X) * 0.5f : X;  // scale_u!(½) Flow.jl:209
+      }
+    }
+    if (!lastp) {
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci) {
+        float r = F[ci][0];
+        r -= Fxu[ci]; r += F[ci][1]; r -= Fyu[ci]; r += F[ci][2];
+        pend[ci] = r;
+      }
+      const int dn = plane * (min(k + 2, N2 - 1) - k);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        w[c][0] = w[c][1]; w[c][1] = w[c][2]; w[c][2] = w[c][3];
+        w[c][3] = pc[c][dn];
+        pc[c] += plane;
+      }
+    }
+  }
+}
+
+template <int S>
+__global__ void __launch_bounds__(32 * M3_TY, 2) k_mom3(const Mom3Args a) {
+  __shared__ float shy[2][3][M3_TY][32];
+  const bool inner = blockIdx.x >= 1 && 1 + 31 * (int)blockIdx.x + 31 <= a.l.n0 - 2 &&
+                     blockIdx.y >= 1 && 1 + (M3_TY - 1) * (int)blockIdx.y + (M3_TY - 1) <= a.l.n1 - 2;
+  if (inner) mom3_body<S, true>(a, shy);
+  else mom3_body<S, false>(a, shy);
+}
+
+// ---- band cells (any μ₁ ≠ 0): exact BDIM with μddn, Flow.jl:20-26,176-180.
+// One warp per band cell: lane = 7·ci + nbr evaluates f[I+δ(nbr), ci] (nbr 0 centre, 1/2 ±x, 3/4 ±y,
+// 5/6 ±z) from global memory with the general per-cell routine; the centre lanes then gather.
+struct PatchArgs {
+  MomArgs m;           // ua, u0, V, per, nu, dt, acc (m.f unused)
+  const float* mu0;
+  const float* mu1;
+  float* un;
+  const int* list;
+  const int* count;
+  int cap;
+  int corrector;
+};
+template <int S>
+__global__ void __launch_bounds__(128) k_mom_patch(const PatchArgs a) {
+  const Lay& l = a.m.l;
+  const int n = min(*a.count, a.cap);
+  const int lane = threadIdx.x & 31;
+  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+  const int ci = min(lane / 7, 2), nbr = lane % 7;
+  const int e = nbr == 0 ? 0 : ((nbr & 1) ? 1 : -1), d = nbr == 0 ? 0 : (nbr - 1) >> 1;
+  for (int q = wid; q < n; q += nw) {
+    const int o = a.list[q];
+    const int k = o / l.plane, rem = o - k * l.plane, j = rem / l.pitch, i = rem - j * l.pitch;
+    float fv = 0.f;
+    if (lane < 21) fv = rhs_f<3, S>(a.m, ci, i + (d == 0 ? e : 0), j + (d == 1 ? e : 0), k + (d == 2 ? e : 0));
+    float s = 0.f;
+#pragma unroll
+    for (int dj = 0; dj < 3; ++dj) {
+      const float fp = __shfl_sync(0xffffffffu, fv, ci * 7 + 1 + 2 * dj);
+      const float fm = __shfl_sync(0xffffffffu, fv, ci * 7 + 2 + 2 * dj);
+      if (lane < 21 && nbr == 0) s += a.mu1[l.cstride * (ci + 3 * dj) + o] * (fp - fm);
+    }
+    if (lane < 21 && nbr == 0) {
+      const long long oc = l.cstride * ci + o;
+      const float X = s / 2.f + a.m.V[oc] + a.mu0[oc] * fv;
+      a.un[oc] = a.corrector ? (a.m.ua[oc] + X) * 0.5f : X;
+    }
+  }
+}
+
+// list of interior cells with any μ₁ ≠ 0 (rebuilt whenever the coefficients change)
+struct BandArgs { Lay l; const float* mu1; int* list; int* count; int cap; };
+template <int D>
+__global__ void __launch_bounds__(256) k_band_scan(const BandArgs a) {
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x + 1;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;
+  if (i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && k > l.n2 - 2)) return;
+  const int o = l.off(i, j, k);
+  bool any = false;
+#pragma unroll
+  for (int q = 0; q < D * D; ++q) any |= a.mu1[l.cstride * q + o] != 0.f;
+  if (any) {
+    const int idx = atomicAdd(a.count, 1);
+    if (idx < a.cap) a.list[idx] = o;
+  }
+}
+
+// u[exit plane, comp 1] carried from the previous buffer (the reference updates u in place, so the
+// exit plane keeps its old values until exitBC! rewrites it, core.jl:212,226-233)
+struct ExitCopyArgs { Lay l; const float* src; float* dst; };
+__global__ void k_copy_exit_plane(const ExitCopyArgs a) {
+  const Lay& l = a.l;
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, k = blockIdx.y;
+  if (j >= l.n1 || k >= l.n2) return;
+  const int o = l.off(l.n0 - 1, j, k);
+  a.dst[o] = a.src[o];
+}
+
+}  // namespace wl
