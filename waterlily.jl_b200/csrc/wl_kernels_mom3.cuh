@@ -189,13 +189,167 @@ __device__ __forceinline__ void mom3_body(const Mom3Args& a, float (*shy)[3][M3_
   }
 }
 
+// ---- asynchronous plane staging (cp.async / LDGSTS): the in-plane neighbourhood of the marching
+// plane is served from a 4-slot shared-memory ring filled two planes ahead, so the flux
+// evaluation never waits on a global load (the register-only body above stalls ~6.6 cycles per
+// issue on the long scoreboard with 16 warps/SM resident).
+__device__ __forceinline__ void cp_async4(float* smem, const float* g) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+constexpr int M3_TW = 36;                       // tile row pitch: columns i0-2 .. i0+33
+constexpr int M3_TH = M3_TY + 3;                // tile rows      j0-2 .. j0+TY
+constexpr int M3_TILE = M3_TW * M3_TH;          // floats per component per plane
+constexpr int M3_RING = 4;
+
+struct Mom3Smem {
+  float ring[M3_RING][3][M3_TILE];
+  float shy[2][3][M3_TY][32];
+};
+
+template <int S, bool FAST>
+__device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm) {
+  const Lay& l = a.l;
+  const int lane = threadIdx.x, ty = threadIdx.y, tid = lane + 32 * ty;
+  const int N0 = l.n0, N1 = l.n1, N2 = l.n2;
+  const int pitch = l.pitch, plane = l.plane;
+  const int i0 = 1 + 31 * blockIdx.x, j0 = 1 + (M3_TY - 1) * blockIdx.y;
+  const int i_raw = i0 + lane, j_raw = j0 + ty;
+  const int i = FAST ? i_raw : min(i_raw, N0 - 1), j = FAST ? j_raw : min(j_raw, N1 - 1);
+  const int k0 = 1 + a.KZ * blockIdx.z;
+  const int kend = min(k0 + a.KZ, N2 - 1);
+  const bool out_ij = lane < 31 && ty < M3_TY - 1 && (FAST || (i_raw <= N0 - 2 && j_raw <= N1 - 2));
+  const int oij = i + pitch * j;
+  const bool p0 = a.per.p[0] != 0, p1 = a.per.p[1] != 0, p2 = a.per.p[2] != 0;
+  const int kx = FAST ? 0 : (i == 1 ? (p0 ? 2 : 1) : (i == N0 - 1 ? (p0 ? 4 : 3) : 0));
+  const int ky = FAST ? 0 : (j == 1 ? (p1 ? 2 : 1) : (j == N1 - 1 ? (p1 ? 4 : 3) : 0));
+  const float* U[3] = {a.ua, a.ua + l.cstride, a.ua + 2 * l.cstride};
+  const float nu = a.nu;
+  // staging duty of this thread: tile positions tid and tid+256 (clamped to the array)
+  const int pa = tid, pb = tid + 32 * M3_TY;
+  const bool has_b = pb < M3_TILE;
+  const int ga = min(max(i0 - 2 + pa % M3_TW, 0), N0 - 1) + pitch * min(max(j0 - 2 + pa / M3_TW, 0), N1 - 1);
+  const int gb = has_b ? min(max(i0 - 2 + pb % M3_TW, 0), N0 - 1) + pitch * min(max(j0 - 2 + pb / M3_TW, 0), N1 - 1) : 0;
+  auto stage = [&](int kp) {
+    const int kc = min(kp, N2 - 1);
+    float(*slot)[M3_TILE] = sm.ring[kp & (M3_RING - 1)];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      cp_async4(&slot[c][pa], U[c] + ga + plane * kc);
+      if (has_b) cp_async4(&slot[c][pb], U[c] + gb + plane * kc);
+    }
+  };
+  const int tc = (ty + 2) * M3_TW + lane + 2;     // own position in the tile
+
+  stage(k0); stage(k0 + 1); cp_async_commit();
+  stage(k0 + 2); cp_async_commit();
+  float w[3][4];   // own column: planes k-2, k-1, k, k+1
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    w[c][0] = U[c][oij + plane * max(k0 - 2, 0)];
+    w[c][1] = U[c][oij + plane * (k0 - 1)];
+  }
+  cp_async_wait<1>();
+  __syncthreads();
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    w[c][2] = sm.ring[k0 & (M3_RING - 1)][c][tc];
+    w[c][3] = sm.ring[(k0 + 1) & (M3_RING - 1)][c][tc];
+  }
+  float pend[3] = {0.f, 0.f, 0.f};
+
+  for (int k = k0; k <= kend; ++k) {
+    const bool lastp = k == kend;
+    const int kz = k == 1 ? (p2 ? 2 : 1) : (k == N2 - 1 ? (p2 ? 4 : 3) : 0);
+    if (!lastp) { stage(k + 3); cp_async_commit(); }
+    // operands of the finalisation of cell k-1: issued now, consumed after the fluxes
+    float fu0[3], fV[3], fm0[3];
+    const int opv = oij + plane * (k - 1);
+    if (k > k0 && out_ij) {
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci) {
+        const long long oc = l.cstride * ci + opv;
+        fu0[ci] = a.u0[oc]; fV[ci] = a.V[oc]; fm0[ci] = a.mu0[oc];
+      }
+    }
+    float(*cur)[M3_TILE] = sm.ring[k & (M3_RING - 1)];
+    float nb[3][3][3];   // nb[c][d][m2,m1,p1]
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      nb[c][2][0] = w[c][0]; nb[c][2][1] = w[c][1]; nb[c][2][2] = w[c][3];
+      nb[c][0][0] = cur[c][tc - 2]; nb[c][0][1] = cur[c][tc - 1]; nb[c][0][2] = cur[c][tc + 1];
+      nb[c][1][0] = cur[c][tc - 2 * M3_TW]; nb[c][1][1] = cur[c][tc - M3_TW]; nb[c][1][2] = cur[c][tc + M3_TW];
+    }
+    float F[3][3];
+#pragma unroll
+    for (int ci = 0; ci < 3; ++ci) {
+#pragma unroll
+      for (int dj = 0; dj < 3; ++dj) {
+        if (lastp && dj < 2) { F[ci][dj] = 0.f; continue; }
+        const int kind = dj == 0 ? kx : (dj == 1 ? ky : kz);
+        const int sdj = dj == 0 ? 1 : (dj == 1 ? pitch : plane);
+        const int Ndj = dj == 0 ? N0 : (dj == 1 ? N1 : N2);
+        const int o = oij + plane * k;
+        if (kind == 4) {                                     // periodic upper face == Φ of the wrapped cell
+          const int sci = ci == 0 ? 1 : (ci == 1 ? pitch : plane);
+          F[ci][dj] = face_flux<S>(U[ci], U[dj], o - sdj * (Ndj - 2), sci, sdj, 1, Ndj, true, nu);
+        } else {
+          const float ua = (w[dj][2] + nb[dj][ci][1]) / 2.f;  // ϕ(i,CI(I,j),u) Flow.jl:3
+          float um2 = nb[ci][dj][0];
+          if (kind == 2) um2 = U[ci][o + sdj * (Ndj - 4)];    // CIj(j,·,N[j]-2) Flow.jl:61
+          F[ci][dj] = flux_v<S>(um2, nb[ci][dj][1], w[ci][2], nb[ci][dj][2], ua, nu, kind);
+        }
+      }
+    }
+    float Fxu[3], Fyu[3];
+    if (!lastp) {
+      const int buf = k & 1;
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci) {
+        Fxu[ci] = __shfl_down_sync(0xffffffffu, F[ci][0], 1);
+        sm.shy[buf][ci][ty][lane] = F[ci][1];
+      }
+      cp_async_wait<1>();                                    // plane k+2 has landed (k+3 may be in flight)
+      __syncthreads();
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci) Fyu[ci] = sm.shy[buf][ci][min(ty + 1, M3_TY - 1)][lane];
+    }
+    if (k > k0 && out_ij) {                                  // finalise cell (i,j,k-1)
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci) {
+        float r = pend[ci] - F[ci][2];
+        r += a.acc.v[ci];
+        const float f = fu0[ci] + a.dt * r - fV[ci];         // BDIM! loop 1, Flow.jl:178
+        const float X = fV[ci] + fm0[ci] * f;                // loop 2 with μ₁ ≡ 0, Flow.jl:179
+        a.un[l.cstride * ci + opv] = a.corrector ? (w[ci][1] + X) * 0.5f : X;   // scale_u!(½) Flow.jl:209
+      }
+    }
+    if (!lastp) {
+      float(*nxt)[M3_TILE] = sm.ring[(k + 2) & (M3_RING - 1)];
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci) {
+        float r = F[ci][0];
+        r -= Fxu[ci]; r += F[ci][1]; r -= Fyu[ci]; r += F[ci][2];
+        pend[ci] = r;
+        w[ci][0] = w[ci][1]; w[ci][1] = w[ci][2]; w[ci][2] = w[ci][3];
+        w[ci][3] = nxt[ci][tc];
+      }
+    }
+  }
+  cp_async_wait<0>();
+}
+
 template <int S>
 __global__ void __launch_bounds__(32 * M3_TY, 2) k_mom3(const Mom3Args a) {
-  __shared__ float shy[2][3][M3_TY][32];
+  __shared__ Mom3Smem sm;
   const bool inner = blockIdx.x >= 1 && 1 + 31 * (int)blockIdx.x + 31 <= a.l.n0 - 2 &&
                      blockIdx.y >= 1 && 1 + (M3_TY - 1) * (int)blockIdx.y + (M3_TY - 1) <= a.l.n1 - 2;
-  if (inner) mom3_body<S, true>(a, shy);
-  else mom3_body<S, false>(a, shy);
+  if (inner) mom3_body_async<S, true>(a, sm);
+  else mom3_body_async<S, false>(a, sm);
 }
 
 // ---- band cells (any μ₁ ≠ 0): exact BDIM with μddn, Flow.jl:20-26,176-180.
