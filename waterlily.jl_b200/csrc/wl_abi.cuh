@@ -114,16 +114,17 @@ int wl_create(const wl_config* cfg, wl_sim** out) {
   // reduction scratch: one partial per block of the largest launch
   {
     dim3 g = grid_all(s->lay);
-    size_t nb = (size_t)g.x * g.y * g.z + 64;
+    const size_t ngroups = ((size_t)g.x * g.y * g.z) / RED_GROUP + 8;
+    size_t nb = (size_t)g.x * g.y * g.z + ngroups + 64;     // block partials + group partials
     if (cudaMalloc(&s->redw.psum, nb * sizeof(double)) != cudaSuccess ||
         cudaMalloc(&s->redw.pmax, nb * sizeof(float)) != cudaSuccess ||
-        cudaMalloc(&s->redw.ticket, sizeof(unsigned)) != cudaSuccess ||
+        cudaMalloc(&s->redw.ticket, (ngroups + 1) * sizeof(unsigned)) != cudaSuccess ||
         cudaMalloc(&s->d_red, sizeof(Red) * NRED) != cudaSuccess ||
         cudaHostAlloc(&s->h_red, sizeof(Red) * NRED, cudaHostAllocDefault) != cudaSuccess) {
       s->err = "reduction scratch allocation failed";
       return bail(WL_ERR_CUDA);
     }
-    cudaMemsetAsync(s->redw.ticket, 0, sizeof(unsigned), s->st);
+    cudaMemsetAsync(s->redw.ticket, 0, (ngroups + 1) * sizeof(unsigned), s->st);
     cudaMemsetAsync(s->d_red, 0, sizeof(Red) * NRED, s->st);
   }
   for (int i = 0; i < 8; ++i) cudaEventCreate(&s->ev[i]);
@@ -386,7 +387,7 @@ int wl_debug_op(wl_sim* s, int op, int level, float arg) {
       a.out = s->d_red + 0;
       DISPATCH_D(s, k_residual, grid_inside(p.lay), blk(s->D), a);
       a.in = s->d_red + 0; a.out = s->d_red + 1;
-      DISPATCH_D(s, k_shift_norms, grid_inside(p.lay), blk(s->D), a);
+      DISPATCH_D(s, k_shift_norms, grid_tiles(p.lay, false), blk(s->D), a);
       break;
     }
     case 4: vcycle(s, 0, arg); break;

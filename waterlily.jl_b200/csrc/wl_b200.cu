@@ -98,14 +98,27 @@ int alloc_field(wl_sim* s, DevField& f, const Lay& lay, int ncomp) {
 }
 void free_field(DevField& f) { if (f.alloc) cudaFree(f.alloc); f.alloc = f.base = nullptr; }
 
-dim3 blk(int D) { return D == 3 ? dim3(32, 4, 2) : dim3(32, 8, 1); }
+dim3 blk(int D) {
+  static int bx = 0, by = 4, bz = 2;
+  if (!bx) {   // WL_BLK3="bx,by,bz" overrides the 3D interior tile (experiments); bx*by*bz must be 256, bz even
+    bx = 32;
+    if (const char* e = getenv("WL_BLK3")) { int a, b, c; if (sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a * b * c == 256 && a % 32 == 0 && c % 2 == 0) { bx = a; by = b; bz = c; } }
+  }
+  return D == 3 ? dim3(bx, by, bz) : dim3(32, 8, 1);
+}
 dim3 grid_inside(const Lay& l) {
   dim3 b = blk(l.D);
-  return dim3((l.n0 - 2 + 31) / 32, (l.n1 - 2 + b.y - 1) / b.y, l.D == 3 ? (l.n2 - 2 + b.z - 1) / b.z : 1);
+  return dim3((l.n0 - 2 + b.x - 1) / b.x, (l.n1 - 2 + b.y - 1) / b.y, l.D == 3 ? (l.n2 - 2 + b.z - 1) / b.z : 1);
 }
 dim3 grid_all(const Lay& l) {
   dim3 b = blk(l.D);
   return dim3((l.n0 + LPAD + 31) / 32, (l.n1 + b.y - 1) / b.y, l.D == 3 ? (l.n2 + b.z - 1) / b.z : 1);
+}
+// 1-D persistent grid for the kernels built on for_tiles_inside / for_tiles_all: at most 8 blocks per SM
+dim3 grid_tiles(const Lay& l, bool all) {
+  const dim3 g = all ? grid_all(l) : grid_inside(l);
+  const long long nt = (long long)g.x * g.y * g.z;
+  return dim3((unsigned)(nt < 148 * 8 ? nt : 148 * 8));
 }
 // plane kernels: threads over (fast in-plane dim, slow in-plane dim); sized for the largest plane
 void plane_launch(const Lay& l, dim3& g, dim3& b) {
@@ -263,7 +276,7 @@ void smooth2(wl_sim* s, Level& p, float w, Red* norms) {
     g.k0 = k0;
     DISPATCH_D(s, k_gs_half, grid_inside(p.lay), blk(s->D), g);
   }
-  DISPATCH_D(s, k_increment_w, grid_inside(p.lay), blk(s->D), a);
+  DISPATCH_D(s, k_increment_w, grid_tiles(p.lay, false), blk(s->D), a);
 }
 // levels first..end in ONE single-block launch: Vcycle!(l=first) (if any coarser level) + smooth!(first)
 void coarse_block(wl_sim* s, size_t first, float w) {
@@ -314,7 +327,7 @@ int mlp_solver(wl_sim* s, Trace* tr, bool residual_done = false) {
       DISPATCH_D(s, k_residual, grid_inside(p.lay), blk(s->D), a);
     }
     a.in = s->d_red + 0; a.out = s->d_red + 1;
-    DISPATCH_D(s, k_shift_norms, grid_inside(p.lay), blk(s->D), a);
+    DISPATCH_D(s, k_shift_norms, grid_tiles(p.lay, false), blk(s->D), a);
   }
   if (int e = fetch_red(s)) return e;
   float r1 = (float)s->h_red[1].sum, rinf = s->h_red[1].maxv, w = 1.f;
@@ -325,7 +338,7 @@ int mlp_solver(wl_sim* s, Trace* tr, bool residual_done = false) {
       coarse_block(s, 0, w);
       LevArgs a = lev_args(s, p);
       a.in = s->d_red + 7; a.out = s->d_red + 1; // slot 7 stays zero: no shift, norms only
-      DISPATCH_D(s, k_shift_norms, grid_inside(p.lay), blk(s->D), a);
+      DISPATCH_D(s, k_shift_norms, grid_tiles(p.lay, false), blk(s->D), a);
     } else {
       vcycle(s, 0, w);
       if (fused) smooth2(s, p, w, s->d_red + 1);
@@ -416,7 +429,7 @@ int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
     Level& p0 = s->lv[0];
     const float dt = w * s->dt;
     DivResArgs d{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, p0.r.base, s->per, dt, s->redw, s->d_red + 0};
-    DISPATCH_D(s, k_divres, grid_inside(s->lay), blk(s->D), d);
+    DISPATCH_D(s, k_divres, grid_tiles(s->lay, false), blk(s->D), d);
     std::swap(s->p, p0.eps); p0.x = s->p;                       // scaled x lives in the former ϵ buffer
     if (int e = mlp_solver(s, tr, true)) return e;
     ProjArgs2 q{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, s->per, dt};
@@ -435,7 +448,7 @@ int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
 }
 int cfl(wl_sim* s, float* out) {
   CflArgs a{s->lay, s->u.base, s->sigma.base, s->redw, s->d_red + 2};
-  DISPATCH_D(s, k_cfl, grid_all(s->lay), blk(s->D), a);
+  DISPATCH_D(s, k_cfl, grid_tiles(s->lay, true), blk(s->D), a);
   if (int e = fetch_red(s)) return e;
   const float m = s->h_red[2].maxv;
   *out = std::fmin(10.f, 1.f / (m + 5.f * s->cfg.nu));

@@ -78,36 +78,47 @@ __device__ __forceinline__ int linear_bid() {
   return blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
 }
 
-// Call from ALL threads of the block (contains __syncthreads).  `out` receives the result.
-__device__ __forceinline__ void block_reduce_finish(double s, float m, const RedWork w, Red* out) {
-  __shared__ double ssum[32];
-  __shared__ float smax[32];
-  __shared__ bool last;
+// Persistent tile loop for kernels that end in a reduction: a 1-D grid of at most a few blocks per
+// SM walks the interior tiles, so the fence + ticket round trip of block_reduce_finish is paid once
+// per block instead of once per 256 cells.  f(i,j,k) is called for every interior cell of the tiles
+// this thread owns (tile = blockDim cells, x fastest).
+template <int D, class F>
+__device__ __forceinline__ void for_tiles_inside(const Lay& l, F f) {
+  const int nbx = (l.n0 - 2 + blockDim.x - 1) / blockDim.x, nby = (l.n1 - 2 + blockDim.y - 1) / blockDim.y;
+  const int nbz = D == 3 ? (l.n2 - 2 + blockDim.z - 1) / blockDim.z : 1;
+  const int nt = nbx * nby * nbz;
+  for (int t = blockIdx.x; t < nt; t += gridDim.x) {
+    const int tx = t % nbx, q = t / nbx, ty = q % nby, tz = q / nby;
+    const int i = tx * blockDim.x + threadIdx.x + 1, j = ty * blockDim.y + threadIdx.y + 1;
+    const int k = D == 3 ? tz * blockDim.z + threadIdx.z + 1 : 0;
+    if (i <= l.n0 - 2 && j <= l.n1 - 2 && (D == 2 || k <= l.n2 - 2)) f(i, j, k);
+  }
+}
+// same over ALL cells (ghosts included); i starts LPAD before the row so that interior cells stay aligned
+template <int D, class F>
+__device__ __forceinline__ void for_tiles_all(const Lay& l, F f) {
+  const int nbx = (l.n0 + LPAD + blockDim.x - 1) / blockDim.x, nby = (l.n1 + blockDim.y - 1) / blockDim.y;
+  const int nbz = D == 3 ? (l.n2 + blockDim.z - 1) / blockDim.z : 1;
+  const int nt = nbx * nby * nbz;
+  for (int t = blockIdx.x; t < nt; t += gridDim.x) {
+    const int tx = t % nbx, q = t / nbx, ty = q % nby, tz = q / nby;
+    const int i = tx * blockDim.x + threadIdx.x - LPAD, j = ty * blockDim.y + threadIdx.y;
+    const int k = D == 3 ? tz * blockDim.z + threadIdx.z : 0;
+    if (i >= 0 && i < l.n0 && j < l.n1 && k < l.n2) f(i, j, k);
+  }
+}
+
+constexpr int RED_GROUP = 256;   // blocks per first-level ticket
+
+// fold n partials starting at `base` in a fixed order (thread t takes t, t+nthr, ...; warp tree;
+// then one warp over the warp results).  Result valid in thread 0.  Contains __syncthreads.
+__device__ __forceinline__ void fold_partials(const double* psum, const float* pmax, int base, int n,
+                                              double* ssum, float* smax, double& a, float& mm) {
   const int tid = linear_tid();
   const int nthr = blockDim.x * blockDim.y * blockDim.z;
   const int lane = tid & 31, wid = tid >> 5, nw = (nthr + 31) >> 5;
-  s = warp_sum(s); m = warp_max(m);
-  if (lane == 0) { ssum[wid] = s; smax[wid] = m; }
-  __syncthreads();
-  const int nblocks = gridDim.x * gridDim.y * gridDim.z;
-  if (wid == 0) {
-    s = lane < nw ? ssum[lane] : 0.0;
-    m = lane < nw ? smax[lane] : -INFINITY;
-    s = warp_sum(s); m = warp_max(m);
-    if (lane == 0) {
-      const int b = linear_bid();
-      w.psum[b] = s; w.pmax[b] = m;
-      __threadfence();
-      unsigned int t = atomicAdd(w.ticket, 1u);
-      last = (t == (unsigned)nblocks - 1);
-    }
-  }
-  __syncthreads();
-  if (!last) return;
-  __threadfence();
-  // fixed-order fold: thread t takes partials t, t+nthr, ...; then the same tree as above
-  double a = 0.0; float mm = -INFINITY;
-  for (int i = tid; i < nblocks; i += nthr) { a += __ldcg(&w.psum[i]); mm = fmaxf(mm, __ldcg(&w.pmax[i])); }
+  a = 0.0; mm = -INFINITY;
+  for (int i = tid; i < n; i += nthr) { a += __ldcg(&psum[base + i]); mm = fmaxf(mm, __ldcg(&pmax[base + i])); }
   a = warp_sum(a); mm = warp_max(mm);
   __syncthreads();
   if (lane == 0) { ssum[wid] = a; smax[wid] = mm; }
@@ -116,8 +127,56 @@ __device__ __forceinline__ void block_reduce_finish(double s, float m, const Red
     a = lane < nw ? ssum[lane] : 0.0;
     mm = lane < nw ? smax[lane] : -INFINITY;
     a = warp_sum(a); mm = warp_max(mm);
-    if (lane == 0) { out->sum = a; out->maxv = mm; *w.ticket = 0u; }
   }
+}
+
+// Call from ALL threads of the block (contains __syncthreads).  `out` receives the result.
+// Two ticket levels (groups of RED_GROUP blocks, then the groups): with >10^5 blocks a single ticket
+// serialises that many atomics on one L2 address and the last block would fold 10^5 partials alone.
+// w.psum/w.pmax hold the block partials followed (from index `nblocks`) by the group partials;
+// w.ticket[0] is the top ticket, w.ticket[1+g] the ticket of group g.  All tickets return to zero.
+__device__ __forceinline__ void block_reduce_finish(double s, float m, const RedWork w, Red* out) {
+  __shared__ double ssum[32];
+  __shared__ float smax[32];
+  __shared__ int last;
+  const int tid = linear_tid();
+  const int nthr = blockDim.x * blockDim.y * blockDim.z;
+  const int lane = tid & 31, wid = tid >> 5, nw = (nthr + 31) >> 5;
+  s = warp_sum(s); m = warp_max(m);
+  if (lane == 0) { ssum[wid] = s; smax[wid] = m; }
+  __syncthreads();
+  const int nblocks = gridDim.x * gridDim.y * gridDim.z;
+  const int b = linear_bid();
+  const int g = b / RED_GROUP, ng = (nblocks + RED_GROUP - 1) / RED_GROUP;
+  const int gsize = min(RED_GROUP, nblocks - g * RED_GROUP);
+  if (wid == 0) {
+    s = lane < nw ? ssum[lane] : 0.0;
+    m = lane < nw ? smax[lane] : -INFINITY;
+    s = warp_sum(s); m = warp_max(m);
+    if (lane == 0) {
+      w.psum[b] = s; w.pmax[b] = m;
+      __threadfence();
+      const unsigned int t = atomicAdd(&w.ticket[1 + g], 1u);
+      last = (t == (unsigned)gsize - 1);
+    }
+  }
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  double a; float mm;
+  fold_partials(w.psum, w.pmax, g * RED_GROUP, gsize, ssum, smax, a, mm);
+  if (tid == 0) {
+    w.psum[nblocks + g] = a; w.pmax[nblocks + g] = mm;
+    w.ticket[1 + g] = 0u;
+    __threadfence();
+    const unsigned int t = atomicAdd(&w.ticket[0], 1u);
+    last = (t == (unsigned)ng - 1);
+  }
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  fold_partials(w.psum, w.pmax, nblocks, ng, ssum, smax, a, mm);
+  if (tid == 0) { out->sum = a; out->maxv = mm; w.ticket[0] = 0u; }
 }
 
 }  // namespace wl

@@ -23,7 +23,7 @@ struct LevArgs {
 };
 
 #define WL_INTERIOR_IJK(D, l)                                                   \
-  const int i = blockIdx.x * 32 + threadIdx.x + 1;                              \
+  const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;                              \
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;                      \
   const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;         \
   const bool inb = !(i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && k > l.n2 - 2));
@@ -95,16 +95,15 @@ __global__ void __launch_bounds__(256) k_residual(const LevArgs a) {
 template <int D>
 __global__ void __launch_bounds__(256) k_shift_norms(const LevArgs a) {
   const Lay& l = a.l;
-  WL_INTERIOR_IJK(D, l)
   const float s = (float)a.in->sum / (float)l.ninside();
   const bool shift = fabsf(s) > 2.f * 1.1920929e-07f;
   double s1 = 0.0; float m = -INFINITY;
-  if (inb) {
+  for_tiles_inside<D>(l, [&](int i, int j, int k) {          // 1-D persistent grid
     const int o = l.off(i, j, k);
     float r = a.r[o];
     if (shift) { r = r - s; a.r[o] = r; }
-    s1 = (double)fabsf(r); m = fabsf(r);
-  }
+    s1 += (double)fabsf(r); m = fmaxf(m, fabsf(r));
+  });
   block_reduce_finish(s1, m, a.w, a.out);
 }
 

@@ -84,7 +84,7 @@ __device__ __forceinline__ float multA_w(const Lay& l, const float* __restrict__
 }
 
 #define WL_IJK_FROM_BLOCK(D, l)                                                 \
-  const int i = blockIdx.x * 32 + threadIdx.x + 1;                              \
+  const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;                              \
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;                      \
   const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;         \
   const bool inb = !(i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && k > l.n2 - 2));
@@ -98,9 +98,8 @@ struct DivResArgs { Lay l; const float* u; const float* x; float* xs; const floa
 template <int D>
 __global__ void __launch_bounds__(256) k_divres(const DivResArgs a) {
   const Lay& l = a.l;
-  WL_IJK_FROM_BLOCK(D, l)
   double s = 0.0;
-  if (inb) {
+  for_tiles_inside<D>(l, [&](int i, int j, int k) {
     const int o = l.off(i, j, k);
     const int st[3] = {1, l.pitch, l.plane};
     int om[3], op[3];
@@ -122,8 +121,8 @@ __global__ void __launch_bounds__(256) k_divres(const DivResArgs a) {
     }
     a.r[o] = r;
     a.xs[o] = xc;
-    s = (double)r;
-  }
+    s += (double)r;
+  });
   block_reduce_finish(s, -INFINITY, a.w, a.out);
 }
 
@@ -138,14 +137,15 @@ __global__ void __launch_bounds__(256) k_down(const DownArgs a) {
   const Lay& lc = a.c.l;
   const Lay& l = a.f.l;
   WL_IJK_FROM_BLOCK(D, l)
-  const int tid = threadIdx.x + 32 * (threadIdx.y + blockDim.y * threadIdx.z);
+  const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
   float rn = 0.f;
   if (inb) {
     const int o = l.off(i, j, k);
     const int st[3] = {1, l.pitch, l.plane};
     int om[3], op[3];
     nbr_off<D>(l, a.per, i, j, k, om, op);
-    const float e0 = a.f.r[o] * a.f.iD[o];                           // ϵ = r·iD  Poisson.jl:112
+    const float r0 = a.f.r[o], x0 = a.f.x[o];                        // all reads before the first store
+    const float e0 = r0 * a.f.iD[o];                                  // ϵ = r·iD  Poisson.jl:112
     float s = e0 * diagL<D>(l, a.f.L, o);                              // mult(I,L,D,ϵ)
 #pragma unroll
     for (int d = 0; d < D; ++d) {
@@ -154,11 +154,11 @@ __global__ void __launch_bounds__(256) k_down(const DownArgs a) {
       const float ep = a.f.r[o + op[d]] * a.f.iD[o + op[d]];
       s += em * Ld[o] + ep * Ld[o + st[d]];
     }
-    rn = a.f.r[o] - s;                                                 // increment!, ω = 1  Poisson.jl:102
+    rn = r0 - s;                                                       // increment!, ω = 1  Poisson.jl:102
     // r is still being read by the neighbours' ϵ: the new residual goes to the idle ϵ array and
     // the host swaps the two pointers afterwards
     a.f.eps[o] = rn;
-    a.f.x[o] = a.f.x[o] + e0;                                          // Poisson.jl:103
+    a.f.x[o] = x0 + e0;                                                // Poisson.jl:103
   }
   tile[tid] = rn;
   __syncthreads();
@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(256) k_down(const DownArgs a) {
   float sum = 0.f;                                                     // restrict  MLP.jl:13-19
   for (int kk = 0; kk < n[2]; ++kk)
     for (int jj = 0; jj < n[1]; ++jj)
-      for (int ii = 0; ii < n[0]; ++ii) sum += tile[tid + ii + 32 * (jj + (int)blockDim.y * kk)];
+      for (int ii = 0; ii < n[0]; ++ii) sum += tile[tid + ii + (int)blockDim.x * (jj + (int)blockDim.y * kk)];
   const int oc = lc.off(cc[0], cc[1], cc[2]);
   a.c.r[oc] = sum;
   a.c.x[oc] = 0.f;                                                     // fill!(coarse.x,0)  MLP.jl:94
@@ -208,15 +208,16 @@ __global__ void __launch_bounds__(256) k_up(const UpArgs a) {
     }
     const int oc = a.c.l.off(cc[0], cc[1], cc[2]);
     const float e0 = a.c.x[oc];
+    const float r0 = a.f.r[o], x0 = a.f.x[o];            // all reads before the first store
     float s = e0 * diagL<D>(l, a.f.L, o);
 #pragma unroll
     for (int d = 0; d < D; ++d) {
       const float* Ld = a.f.L + l.cstride * d;
       s += a.c.x[oc + (ccm[d] - cc[d]) * cst[d]] * Ld[o] + a.c.x[oc + (ccp[d] - cc[d]) * cst[d]] * Ld[o + st[d]];
     }
-    const float r = a.f.r[o] - a.omega * s;
+    const float r = r0 - a.omega * s;
     a.f.r[o] = r;
-    a.f.x[o] = a.f.x[o] + a.omega * e0;
+    a.f.x[o] = x0 + a.omega * e0;
     s1 = (double)fabsf(r); m = fabsf(r);
   }
   if (a.want_norms) block_reduce_finish(s1, m, a.w, a.out);
@@ -240,17 +241,19 @@ __global__ void __launch_bounds__(256) k_eps_init_g(const SmArgs a) {
 template <int D>
 __global__ void __launch_bounds__(256) k_increment_w(const SmArgs a) {
   const Lay& l = a.p.l;
-  WL_IJK_FROM_BLOCK(D, l)
   double s1 = 0.0; float m = -INFINITY;
-  if (inb) {
+  // 1-D persistent grid (see for_tiles_inside); every read is issued before the first store so the
+  // thread pays ONE memory round trip (r, x, ϵ may alias as far as the compiler knows)
+  for_tiles_inside<D>(l, [&](int i, int j, int k) {
     const int o = l.off(i, j, k);
     int om[3], op[3];
     nbr_off<D>(l, a.per, i, j, k, om, op);
-    const float r = a.p.r[o] - a.omega * multA_w<D>(l, a.p.L, a.p.eps, o, om, op);
+    const float r0 = a.p.r[o], x0 = a.p.x[o], e0 = a.p.eps[o];
+    const float r = r0 - a.omega * multA_w<D>(l, a.p.L, a.p.eps, o, om, op);
     a.p.r[o] = r;
-    a.p.x[o] = a.p.x[o] + a.omega * a.p.eps[o];
-    s1 = (double)fabsf(r); m = fabsf(r);
-  }
+    a.p.x[o] = x0 + a.omega * e0;
+    s1 += (double)fabsf(r); m = fmaxf(m, fabsf(r));
+  });
   if (a.want_norms) block_reduce_finish(s1, m, a.w, a.out);
 }
 
@@ -267,11 +270,14 @@ __global__ void __launch_bounds__(256) k_proj(const ProjArgs2 a) {
   int om[3], op[3];
   nbr_off<D>(l, a.per, i, j, k, om, op);
   const float xc = a.x[o];
+  float uv[3], Lv[3], xm[3];
 #pragma unroll
-  for (int d = 0; d < D; ++d) {
+  for (int d = 0; d < D; ++d) {                              // all reads first: one memory round trip
     const long long oc = l.cstride * d + o;
-    a.u[oc] -= a.L[oc] * (xc - a.x[o + om[d]]);
+    uv[d] = a.u[oc]; Lv[d] = a.L[oc]; xm[d] = a.x[o + om[d]];
   }
+#pragma unroll
+  for (int d = 0; d < D; ++d) a.u[l.cstride * d + o] = uv[d] - Lv[d] * (xc - xm[d]);
   const float p = xc / a.dt;
   a.pn[o] = p;
   store_images<D>(a.pn, l, a.per, i, j, k, p);

@@ -113,7 +113,7 @@ struct BdimArgs {
 template <int D>
 __global__ void __launch_bounds__(256) k_bdim(const BdimArgs a) {
   const Lay& l = a.l;
-  const int i = blockIdx.x * 32 + threadIdx.x + 1;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
   const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;
   if (i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && k > l.n2 - 2)) return;
@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(256) k_div_scale(const ProjArgs a) {
 template <int D>
 __global__ void __launch_bounds__(256) k_project(const ProjArgs a) {
   const Lay& l = a.l;
-  const int i = blockIdx.x * 32 + threadIdx.x + 1;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
   const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;
   if (i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && k > l.n2 - 2)) return;
@@ -320,11 +320,8 @@ struct CflArgs { Lay l; const float* u; float* sigma; RedWork w; Red* out; };
 template <int D>
 __global__ void __launch_bounds__(256) k_cfl(const CflArgs a) {
   const Lay& l = a.l;
-  const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
-  const int j = blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z : 0;
   float m = -INFINITY;
-  if (i >= 0 && i < l.n0 && j < l.n1 && k < l.n2) {
+  for_tiles_all<D>(l, [&](int i, int j, int k) {               // 1-D persistent grid
     const int o = l.off(i, j, k);
     const bool in = i >= 1 && i <= l.n0 - 2 && j >= 1 && j <= l.n1 - 2 && (D == 2 || (k >= 1 && k <= l.n2 - 2));
     if (in) {
@@ -336,11 +333,11 @@ __global__ void __launch_bounds__(256) k_cfl(const CflArgs a) {
         s += fmaxf(0.f, ud[o + st[d]]) + fmaxf(0.f, -ud[o]);
       }
       a.sigma[o] = s;
-      m = s;
+      m = fmaxf(m, s);
     } else {
-      m = a.sigma[o];
+      m = fmaxf(m, a.sigma[o]);
     }
-  }
+  });
   block_reduce_finish(0.0, m, a.w, a.out);
 }
 

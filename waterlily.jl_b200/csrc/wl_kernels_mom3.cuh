@@ -398,7 +398,7 @@ struct BandArgs { Lay l; const float* mu1; int* list; int* count; int cap; };
 template <int D>
 __global__ void __launch_bounds__(256) k_band_scan(const BandArgs a) {
   const Lay& l = a.l;
-  const int i = blockIdx.x * 32 + threadIdx.x + 1;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
   const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;
   if (i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && k > l.n2 - 2)) return;
