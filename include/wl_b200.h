@@ -88,6 +88,22 @@ typedef struct wl_step_info {
 
 /* ---- lifetime.  wl_create = Flow constructor (src/Flow.jl:133-147) with the default IC.      */
 int wl_create(const wl_config* cfg, wl_sim** out);
+
+/* ---- multi-GPU (the reference has no distributed path, its nearest hook is the
+ *      `mem`/`flow_ctor` injection of src/WaterLily.jl:93-98).  One process per GPU; the grid is
+ *      slab-decomposed along the LAST dimension.  cfg describes the GLOBAL grid; every rank calls
+ *      wl_create_slab with the same cfg and the same NCCL id (made once by wl_nccl_unique_id and
+ *      broadcast by the host) and owns N[D-1]/nranks planes.  All data-surface calls then refer to
+ *      the local slab: size (N1+2, N2+2, N3/nranks+2), whose first/last planes mirror the
+ *      neighbouring slabs.  Every entry point is collective: all ranks call it in the same order.  */
+typedef struct wl_dist {
+  int32_t rank, nranks;
+  char nccl_id[128];
+} wl_dist;
+int wl_nccl_unique_id(char id[128]);
+int wl_create_slab(const wl_config* cfg, const wl_dist* dist, wl_sim** out);
+int wl_slab_info(const wl_sim* s, int32_t* rank, int32_t* nranks, int32_t* k_offset, int32_t* n_local, int32_t* n_global);
+int wl_halo_stats(const wl_sim* s, int64_t* exchanges, int64_t* bytes);
 void wl_destroy(wl_sim* s);
 const char* wl_last_error(const wl_sim* s);   /* s may be NULL: last error of wl_create */
 int wl_version(void);

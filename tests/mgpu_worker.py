@@ -1,0 +1,114 @@
+"""Multi-GPU parity worker (run under torchrun, one rank per GPU; see tests/test_multigpu.py):
+the slab-decomposed run must reproduce the single-GPU run of the same library on the same inputs
+-- identical Poisson iteration counts and Δt history, fields within 1e-6·scale (SURVEY §8e parity
+requirement; reductions fold per-rank partials, so the last bit of a norm may differ).
+
+  torchrun --nproc-per-node 2 tests/mgpu_worker.py [case ...]
+"""
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def tgv(N, nz):
+    k = np.float32(2 * np.pi / N)
+
+    def u0(i, x):
+        if i == 1:
+            return -np.sin(k * x[0]) * np.cos(k * x[1]) * np.cos(k * x[2])
+        if i == 2:
+            return np.cos(k * x[0]) * np.sin(k * x[1]) * np.cos(k * x[2])
+        return 0 * x[0] * x[1] * x[2]
+    return dict(dims=(N, N, nz), uBC=(0.0, 0.0, 0.0), L=float(N),
+                kw=dict(perdir=(1, 2, 3), nu=float(1 / (k * 1600)), U=1.0, u0=u0), body=None, remeasure=False)
+
+
+CASES = {
+    # periodic in every direction: ring exchange, stale-ghost sweeps at the wrap, mean removal
+    "tgv32": lambda: dict(tgv(32, 32), steps=6),
+    "tgv_32x32x64": lambda: dict(tgv(32, 64), steps=4),
+    # body band straddling the slab interface, Dirichlet/Neumann physical boundaries in z
+    "sphere": lambda: dict(dims=(64, 32, 32), uBC=(1.0, 0.0, 0.0), L=8.0, kw=dict(nu=8.0 / 100),
+                           body=dict(kind="sphere", center=(15, 15, 15), radius=4.0), remeasure=False, steps=6),
+    "sphere_exit": lambda: dict(dims=(64, 32, 32), uBC=(1.0, 0.0, 0.0), L=8.0, kw=dict(nu=8.0 / 100, exitBC=True),
+                                body=dict(kind="sphere", center=(15, 15, 17), radius=4.0), remeasure=False, steps=6),
+    # moving body, remeasure every step (measure! + update! across slabs), periodic last dimension
+    "cylinder": lambda: dict(dims=(64, 64, 32), uBC=(0.0, 0.0, 0.0), L=8.0,
+                             kw=dict(nu=8.0 / 100, U=1.0, perdir=(3,)),
+                             body=dict(kind="cylinder", axis=2, center=(32, 32, 0), radius=4.0, amp=(4.0, 0, 0),
+                                       omega=2 * np.pi / 32), remeasure=True, steps=5),
+    "sphere64": lambda: dict(dims=(64, 32, 64), uBC=(1.0, 0.0, 0.0), L=8.0, kw=dict(nu=8.0 / 100, exitBC=True),
+                             body=dict(kind="sphere", center=(15, 15, 31), radius=5.0), remeasure=False, steps=5),
+    # torus ring crossing the interface, vanLeer scheme, semi-coarsening hierarchy (96 = 3·32)
+    "torus": lambda: dict(dims=(48, 32, 32), uBC=(1.0, 0.0, 0.0), L=8.0, kw=dict(nu=0.05, scheme="vanLeer"),
+                          body=dict(kind="torus", axis=0, center=(20, 15, 15), radius=6.0, minor=2.0),
+                          remeasure=False, steps=4),
+}
+
+
+def run_case(wl, name, comm, dev):
+    c = CASES[name]()
+    mk = lambda **extra: wl.Simulation(c["dims"], c["uBC"], c["L"], body=wl.AutoBody(**c["body"]) if c["body"] else None,
+                                       device=dev, **c["kw"], **extra)
+    one = mk()                 # the whole grid on this rank's GPU
+    slab = mk(comm=comm)       # this rank's slab
+    rank, n = comm[0], comm[1]
+    for _ in range(c["steps"]):
+        one.sim_step(remeasure=c["remeasure"])
+        slab.sim_step(remeasure=c["remeasure"])
+    out = dict(case=name, rank=rank, n_one=list(one.pois.n), n_slab=list(slab.pois.n))
+    out["dt_err"] = float(np.abs(np.array(one.flow.Δt) - np.array(slab.flow.Δt)).max())
+    ok = out["n_one"] == out["n_slab"] and out["dt_err"] <= 1e-6
+    for f in ("u", "p", "mu0", "V"):
+        ref = wl.slab_of(getattr(one.flow, f), rank, n)
+        got = getattr(slab.flow, f)
+        scale = max(1.0, float(np.abs(ref).max()))
+        # ghost planes at the physical ends of periodic directions may legitimately hold other images
+        err = float(np.abs(got - ref)[..., 1:-1, :, :].max()) / scale
+        out["err_" + f] = err
+        ok = ok and err <= 1e-6
+    if c["body"]:
+        f1, f2 = one.pressure_force(), slab.pressure_force()
+        out["force_err"] = float(np.abs(f1 - f2).max() / max(1.0, np.abs(f1).max()))
+        ok = ok and out["force_err"] <= 1e-6
+    out["halo"] = slab.halo_stats()
+    out["ok"] = bool(ok)
+    return out
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+    rank, local = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if rank == 0:
+        ge.build()
+    dist.barrier()
+    import waterlily_jl_b200 as wl
+    names = sys.argv[1:] or list(CASES)
+    bad = 0
+    for nm in names:
+        comm = wl.make_slab_comm()
+        res = run_case(wl, nm, comm, local)
+        allres = [None] * dist.get_world_size()
+        dist.all_gather_object(allres, res)
+        if rank == 0:
+            for r in allres:
+                print("MGPU", json.dumps(r), flush=True)
+                bad += 0 if r["ok"] else 1
+    dist.barrier()
+    dist.destroy_process_group()
+    if rank == 0:
+        print("MGPU_RESULT", "FAIL" if bad else "PASS", flush=True)
+    sys.exit(1 if bad else 0)
+
+
+if __name__ == "__main__":
+    main()

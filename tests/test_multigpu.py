@@ -1,0 +1,96 @@
+"""Multi-GPU (slab decomposition) tests.
+
+* `-m gpu` (needs >= 2 devices, skipped otherwise): launches tests/mgpu_worker.py under torchrun
+  with one rank per GPU; every case must reproduce the single-GPU run (identical `pois.n`, Δt,
+  fields within 1e-6).
+* `-m "not gpu"`: the host-side slab logic (partition, scatter/gather, neighbour/halo plan) on
+  world_size-2 gloo process groups, no GPU.
+"""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nproc", [2, 4, 8])
+def test_slab_run_equals_single_gpu(nproc):
+    import torch
+    if torch.cuda.device_count() < nproc:
+        pytest.skip(f"needs {nproc} GPUs")
+    cases = ["tgv32", "sphere", "sphere_exit", "cylinder", "torus"] if nproc == 2 else ["tgv_32x32x64", "sphere64"]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29530 + nproc), os.path.join(ROOT, "tests", "mgpu_worker.py")] + cases
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
+    lines = [l for l in r.stdout.splitlines() if l.startswith("MGPU")]
+    assert r.returncode == 0 and "MGPU_RESULT PASS" in r.stdout, "\n".join(lines[-20:]) + r.stderr[-3000:]
+
+
+# ---------------------------------------------------------------- host logic, CPU only
+def _gloo_worker(rank, world, port, q):
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    import waterlily_jl_b200 as wl
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(7)
+        nz, n2, n1 = 16, 6, 5
+        glob = rng.uniform(-1, 1, (3, nz + 2, n2 + 2, n1 + 2)).astype(np.float32)     # same on every rank (same seed)
+        mine = wl.slab_of(glob, rank, world)
+        k0, n = wl.slab_range(rank, world, nz)
+        ok = mine.shape == (3, n + 2, n2 + 2, n1 + 2) and np.array_equal(mine[:, 1:-1], glob[:, 1 + k0:1 + k0 + n])
+        # the interface ghost planes of a slab are the neighbours' first/last interior planes: emulate the
+        # library's exchange plan (lower, upper sends; upper, lower receives) with gloo send/recv
+        import torch
+        work = mine.copy()
+        work[:, 0] = np.nan
+        work[:, -1] = np.nan
+        lo, hi = (rank - 1) % world, (rank + 1) % world           # periodic ring
+        sends = [(lo, work[:, 1]), (hi, work[:, -2])]
+        recvs = [(hi, -1), (lo, 0)]
+        reqs = [dist.isend(torch.from_numpy(np.ascontiguousarray(a)), dst) for dst, a in sends]
+        for src, where in recvs:
+            t = torch.empty(work[:, where].shape, dtype=torch.float32)
+            dist.recv(t, src)
+            work[:, where] = t.numpy()
+        for r_ in reqs:
+            r_.wait()
+        ring = np.concatenate([glob[:, -2:-1], glob[:, 1:-1], glob[:, 1:2]], axis=1)   # periodic ghosts of the global array
+        ok = ok and np.array_equal(work, ring[:, k0:k0 + n + 2])
+        # gather back
+        parts = [None] * world
+        dist.all_gather_object(parts, mine)
+        ok = ok and np.array_equal(wl.join_slabs(parts), glob)
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_slab_host_logic_gloo_world2():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29600 + os.getpid() % 300
+    ps = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in ps)
+    for p in ps:
+        p.join(timeout=60)
+    assert res == [(0, True), (1, True)], res
+
+
+def test_slab_range_rules():
+    sys.path.insert(0, ROOT)
+    import waterlily_jl_b200 as wl
+    assert wl.slab_range(3, 8, 1024) == (384, 128)
+    assert wl.slab_range(1, 2, 32) == (16, 16)
+    for bad in [(0, 3, 32), (0, 8, 24), (0, 2, 4)]:          # uneven split, odd planes per rank, too thin
+        with pytest.raises(wl.WaterLilyB200Error):
+            wl.slab_range(*bad)

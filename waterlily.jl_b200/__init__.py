@@ -37,7 +37,7 @@ ABI_SYMBOLS = [
     "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
     "wl_cfl", "wl_pressure_force", "wl_sync", "wl_launch_count", "wl_enable_timing",
     "wl_last_phase_times", "wl_debug_op", "wl_prof_begin", "wl_prof_end", "wl_event_record",
-    "wl_event_elapsed_ms",
+    "wl_event_elapsed_ms", "wl_create_slab", "wl_nccl_unique_id", "wl_slab_info", "wl_halo_stats",
 ]
 
 
@@ -46,6 +46,10 @@ class WLConfig(C.Structure):
                 ("scheme", C.c_int32), ("nu", C.c_float), ("dt0", C.c_float), ("uBC", C.c_float * 3),
                 ("maxlevels", C.c_int32), ("tol", C.c_float), ("itmx", C.c_int32), ("device", C.c_int32),
                 ("flags", C.c_int32)]
+
+
+class WLDist(C.Structure):
+    _fields_ = [("rank", C.c_int32), ("nranks", C.c_int32), ("nccl_id", C.c_uint8 * 128)]
 
 
 class WLBody(C.Structure):
@@ -82,6 +86,10 @@ def load_library(path=None):
     P, F, I = C.c_void_p, C.c_float, C.c_int32
     FP = C.POINTER(F)
     lib.wl_create.argtypes = [C.POINTER(WLConfig), C.POINTER(P)]
+    lib.wl_create_slab.argtypes = [C.POINTER(WLConfig), C.POINTER(WLDist), C.POINTER(P)]
+    lib.wl_nccl_unique_id.argtypes = [C.c_char_p]
+    lib.wl_slab_info.argtypes = [P] + [C.POINTER(I)] * 5
+    lib.wl_halo_stats.argtypes = [P, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     lib.wl_destroy.argtypes = [P]
     lib.wl_destroy.restype = None
     lib.wl_last_error.argtypes = [P]
@@ -119,6 +127,49 @@ def load_library(path=None):
 def _v3f(a):
     a = list(a) + [0.0] * (3 - len(a))
     return (C.c_float * 3)(*[float(x) for x in a])
+
+
+def slab_range(rank, nranks, n_last):
+    """Interior planes [k0, k0+n) of the last dimension owned by `rank` (slabs along the
+    slowest index).  The split must be even: every rank gets n_last/nranks planes, an even number."""
+    if n_last % nranks or (n_last // nranks) % 2 or n_last // nranks < 4:
+        raise WaterLilyB200Error("WL_ERR_INVALID: the last dimension must split into an even number (>= 4) "
+                                 "of planes per rank")
+    n = n_last // nranks
+    return rank * n, n
+
+
+def slab_of(a, rank, nranks):
+    """The local slab (one ghost plane per side) of a GLOBAL field array shaped ([D[,D]], n3, n2, n1)."""
+    nz = a.shape[-3] - 2
+    k0, n = slab_range(rank, nranks, nz)
+    return np.ascontiguousarray(a[..., k0:k0 + n + 2, :, :])
+
+
+def join_slabs(parts):
+    """Inverse of slab_of: rank-ordered local slabs -> the global array (interface ghost planes dropped)."""
+    n = len(parts)
+    out = []
+    for r, p in enumerate(parts):
+        lo = 0 if r == 0 else 1
+        hi = p.shape[-3] if r == n - 1 else p.shape[-3] - 1
+        out.append(p[..., lo:hi, :, :])
+    return np.concatenate(out, axis=-3)
+
+
+def make_slab_comm(group=None):
+    """(rank, nranks, nccl_id) for `Simulation(..., comm=...)` from an initialised torch.distributed
+    process group: rank 0 creates the NCCL id inside the library, torch broadcasts the bytes."""
+    import torch.distributed as dist
+    rank, n = dist.get_rank(group), dist.get_world_size(group)
+    box = [None]
+    if rank == 0:
+        buf = C.create_string_buffer(128)
+        if load_library().wl_nccl_unique_id(buf) != WL_OK:
+            raise WaterLilyB200Error("wl_nccl_unique_id failed")
+        box[0] = buf.raw
+    dist.broadcast_object_list(box, src=0, group=group)
+    return rank, n, box[0]
 
 
 class AutoBody:
@@ -200,7 +251,7 @@ class Simulation:
 
     def __init__(self, dims, uBC, L=1.0, *, dt=0.25, nu=0.0, U=None, eps=1.0, perdir=(), exitBC=False,
                  scheme="quick", body=None, u0=None, g=None, maxlevels=10, tol=2e-3, itmx=32, device=0,
-                 T=np.float32, lib=None, flags=0):
+                 T=np.float32, lib=None, flags=0, comm=None):
         if np.dtype(T) != np.float32:
             raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: the B200 path is Float32 only")
         if callable(uBC) or callable(g):
@@ -224,7 +275,15 @@ class Simulation:
                        int(exitBC), SCHEMES[scheme], float(nu), float(dt), _v3f(self.uBC), maxlevels, float(tol),
                        itmx, device, int(flags))
         h = C.c_void_p()
-        rc = self.lib.wl_create(C.byref(cfg), C.byref(h))
+        self.rank, self.nranks, self.k_offset = 0, 1, 0
+        if comm is not None and comm[1] > 1:
+            # one process per GPU, slab along the last dimension: `dims` is the GLOBAL grid
+            self.rank, self.nranks = int(comm[0]), int(comm[1])
+            self.k_offset, _ = slab_range(self.rank, self.nranks, self.dims[-1]) if self.D == 3 else (0, 0)
+            dd = WLDist(self.rank, self.nranks, (C.c_uint8 * 128)(*bytes(comm[2])[:128]))
+            rc = self.lib.wl_create_slab(C.byref(cfg), C.byref(dd), C.byref(h))
+        else:
+            rc = self.lib.wl_create(C.byref(cfg), C.byref(h))
         if rc != WL_OK:
             raise WaterLilyB200Error(f"wl_create failed ({rc}): {self.lib.wl_last_error(None).decode()}")
         self._handle = _Handle(self.lib, h)
@@ -270,9 +329,13 @@ class Simulation:
     def loc(self, i):
         """`loc(i,I)` (src/core.jl:177) for every cell; D arrays broadcastable against a scalar field."""
         n = [d + 2 for d in self.dims]
+        off = [0] * self.D
+        if self.nranks > 1:
+            n[-1] = self.dims[-1] // self.nranks + 2
+            off[-1] = self.k_offset
         out = []
         for d in range(self.D):
-            x = np.arange(n[d], dtype=np.float32) - np.float32(0.5) - (np.float32(0.5) if i == d + 1 else 0)
+            x = (np.arange(n[d]) + off[d]).astype(np.float32) - np.float32(0.5) - (np.float32(0.5) if i == d + 1 else 0)
             shp = [1] * self.D
             shp[self.D - 1 - d] = n[d]
             out.append(x.reshape(shp))
@@ -392,6 +455,22 @@ class Simulation:
 
     def sync(self):
         self._check(self.lib.wl_sync(self.h))
+
+    def halo_stats(self):
+        """(number of halo exchanges, bytes sent) since creation."""
+        n, b = C.c_int64(), C.c_int64()
+        self._check(self.lib.wl_halo_stats(self.h, C.byref(n), C.byref(b)))
+        return int(n.value), int(b.value)
+
+    def gather(self, name, level=0, group=None):
+        """The GLOBAL array of a field on every rank (test/inspection helper; goes through the host)."""
+        a = self.download(name, level)
+        if self.nranks == 1:
+            return a
+        import torch.distributed as dist
+        parts = [None] * self.nranks
+        dist.all_gather_object(parts, a, group=group)
+        return join_slabs(parts)
 
     def launch_count(self):
         return int(self.lib.wl_launch_count(self.h))

@@ -8,7 +8,9 @@ int fail(wl_sim* s, int code, const std::string& msg) {
   return code;
 }
 
-// MultiLevelPoisson(x,L,z;maxlevels,perdir) (MultiLevelPoisson.jl:68-76) + restrictML (:33-41)
+// MultiLevelPoisson(x,L,z;maxlevels,perdir) (MultiLevelPoisson.jl:68-76) + restrictML (:33-41).
+// The hierarchy follows the GLOBAL grid; with several ranks a level stays distributed while every
+// rank keeps an even number (>= dist.min_planes) of planes, coarser levels are replicated.
 int build_levels(wl_sim* s) {
   for (size_t l = 1; l < s->lv.size(); ++l) {
     Level& v = s->lv[l];
@@ -18,26 +20,44 @@ int build_levels(wl_sim* s) {
   s->lv.clear();
   s->lv.reserve(s->cfg.maxlevels + 2);
   s->lv.emplace_back();
+  const int nr = s->dist.n;
+  int gn[3] = {s->lay.n0, s->lay.n1, s->D == 3 ? s->dist.nzg + 2 : 1};   // global sizes incl. ghosts
+  auto gcells = [&](const int* g) {
+    long long c = (long long)(g[0] - 2) * (g[1] - 2);
+    return s->D == 3 ? c * (g[2] - 2) : c;
+  };
   {
     Level& l0 = s->lv.back();
     l0.lay = s->lay; l0.L = s->mu0; l0.x = s->p; l0.z = s->sigma; l0.owns = false;
+    l0.dist = nr > 1; l0.per = s->per; l0.koff = s->per.kz0; l0.ncells = gcells(gn);
     if (int e = alloc_field(s, l0.r, s->lay, 1)) return e;
     if (int e = alloc_field(s, l0.eps, s->lay, 1)) return e;
     if (int e = alloc_field(s, l0.Dg, s->lay, 1)) return e;
     if (int e = alloc_field(s, l0.iD, s->lay, 1)) return e;
-    set_diag(s, l0);
+    if (int e = set_diag_h(s, l0)) return e;
   }
-  auto anydiv = [&](const Level& l) {
-    for (int d = 0; d < s->D; ++d) if (divisible(l.lay.n(d))) return true;
+  auto anydiv = [&]() {
+    for (int d = 0; d < s->D; ++d) if (divisible(gn[d])) return true;
     return false;
   };
-  while (anydiv(s->lv.back()) && (int)s->lv.size() <= s->cfg.maxlevels) {
+  while (anydiv() && (int)s->lv.size() <= s->cfg.maxlevels) {
     const Level& f = s->lv.back();
     Level c;
     int ng[3];
     for (int d = 0; d < 3; ++d) {
-      c.c[d] = d < s->D && divisible(f.lay.n(d));
-      ng[d] = c.c[d] ? 1 + f.lay.n(d) / 2 : f.lay.n(d);
+      c.c[d] = d < s->D && divisible(gn[d]);
+      ng[d] = c.c[d] ? 1 + gn[d] / 2 : gn[d];
+    }
+    for (int d = 0; d < 3; ++d) gn[d] = ng[d];
+    c.ncells = gcells(gn);
+    c.per = s->per_glob;
+    if (f.dist) {
+      const int nzf = f.lay.n2 - 2, nloc = c.c[2] ? nzf / 2 : nzf;
+      if (nloc >= s->dist.min_planes && nloc % 2 == 0) {
+        c.dist = true;
+        ng[2] = nloc + 2;
+        c.per = s->per; c.koff = s->dist.rank * nloc; c.per.kz0 = c.koff;
+      }
     }
     c.lay = make_lay(s->D, ng);
     c.owns = true;
@@ -50,11 +70,10 @@ int build_levels(wl_sim* s) {
     if (int e = alloc_field(s, co.eps, co.lay, 1)) return e;
     if (int e = alloc_field(s, co.Dg, co.lay, 1)) return e;
     if (int e = alloc_field(s, co.iD, co.lay, 1)) return e;
-    restrictL(s, s->lv[s->lv.size() - 2], co);
-    set_diag(s, co);
+    if (int e = restrictL(s, s->lv[s->lv.size() - 2], co)) return e;
+    if (int e = set_diag_h(s, co)) return e;
   }
   if (s->lv.size() <= 2) return fail(s, WL_ERR_INVALID, "MultiLevelPoisson requires size=a2^n, where n>2");
-  // reduction scratch sized for the finest level's largest grid
   return WL_OK;
 }
 
@@ -72,9 +91,17 @@ int wl_version(void) { return 100; }
 
 const char* wl_last_error(const wl_sim* s) { return s ? s->err.c_str() : g_create_error.c_str(); }
 
-int wl_create(const wl_config* cfg, wl_sim** out) {
+static int create_impl(const wl_config* cfg, const wl_dist* dd, wl_sim** out) {
   if (!cfg || !out) return fail(nullptr, WL_ERR_INVALID, "null argument");
   *out = nullptr;
+  const int nranks = dd ? dd->nranks : 1, rank = dd ? dd->rank : 0;
+  if (nranks < 1 || rank < 0 || rank >= nranks || nranks > MAXRANKS) return fail(nullptr, WL_ERR_INVALID, "bad rank / nranks");
+  if (nranks > 1) {
+    if (cfg->D != 3) return fail(nullptr, WL_ERR_UNSUPPORTED, "slab decomposition needs a 3D grid");
+    if (cfg->flags & WL_FLAG_NO_FUSED) return fail(nullptr, WL_ERR_UNSUPPORTED, "slab decomposition runs the fused kernels only");
+    if (cfg->N[2] % nranks != 0 || (cfg->N[2] / nranks) % 2 != 0 || cfg->N[2] / nranks < 4)
+      return fail(nullptr, WL_ERR_INVALID, "the last dimension must split into an even number (>= 4) of planes per rank");
+  }
   if (cfg->D != 2 && cfg->D != 3) return fail(nullptr, WL_ERR_INVALID, "D must be 2 or 3");
   for (int d = 0; d < cfg->D; ++d)
     if (cfg->N[d] < 2) return fail(nullptr, WL_ERR_INVALID, "each dimension needs at least 2 cells");
@@ -100,7 +127,32 @@ int wl_create(const wl_config* cfg, wl_sim** out) {
   if (cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking) != cudaSuccess) { s->err = "stream create failed"; return bail(WL_ERR_CUDA); }
   int ng[3];
   for (int d = 0; d < 3; ++d) { ng[d] = cfg->N[d] + 2; s->per.p[d] = d < cfg->D ? (cfg->perdir[d] != 0) : 0; }
-  s->lay = make_lay(cfg->D, ng);
+  s->per.zlo = s->per.zhi = s->per.kz0 = 0;
+  s->per_glob = s->per;
+  s->dist.rank = rank; s->dist.n = nranks; s->dist.nzg = cfg->N[2]; s->dist.nzl = cfg->N[2];
+  if (const char* e = getenv("WL_DIST_MIN_PLANES")) s->dist.min_planes = std::max(2, atoi(e));
+  if (nranks > 1) {
+    Dist& d = s->dist;
+    const bool pz = s->per.p[2] != 0;
+    d.nzl = cfg->N[2] / nranks;
+    d.lo = rank > 0 ? rank - 1 : (pz ? nranks - 1 : -1);
+    d.hi = rank < nranks - 1 ? rank + 1 : (pz ? 0 : -1);
+    d.lo_wrap = rank == 0 && pz; d.hi_wrap = rank == nranks - 1 && pz;
+    s->per.p[2] = 0; s->per.zlo = d.lo >= 0; s->per.zhi = d.hi >= 0; s->per.kz0 = rank * d.nzl;
+    ng[2] = d.nzl + 2;
+    { const std::string why = nccl_load(); if (!why.empty()) { s->err = why; return bail(WL_ERR_CUDA); } }
+    ncclUniqueId id;
+    static_assert(sizeof(id) <= sizeof(dd->nccl_id), "wl_dist.nccl_id too small");
+    memcpy(&id, dd->nccl_id, sizeof(id));
+    ncclResult_t r = ncclCommInitRank(&d.comm, nranks, id, rank);
+    if (r != ncclSuccess) { s->err = std::string("ncclCommInitRank: ") + ncclGetErrorString(r); return bail(WL_ERR_CUDA); }
+    if (cudaMalloc(&s->d_redg, sizeof(Red) * NRED * nranks) != cudaSuccess ||
+        cudaHostAlloc(&s->h_redg, sizeof(Red) * NRED * nranks, cudaHostAllocDefault) != cudaSuccess) {
+      s->err = "reduction gather buffers allocation failed";
+      return bail(WL_ERR_CUDA);
+    }
+  }
+  s->lay = make_lay(cfg->D, ng, nranks > 1 ? 2 : 0);
   const int D = s->D;
   int e = 0;
   if ((e = alloc_field(s, s->u, s->lay, D)) || (e = alloc_field(s, s->u0, s->lay, D)) ||
@@ -142,6 +194,7 @@ int wl_create(const wl_config* cfg, wl_sim** out) {
   *out = s;
   if ((e = wl_finish_ic(s, cfg->uBC))) { *out = nullptr; return bail(e); }
   bc_vec(s, s->mu0, nullptr, false);
+  if ((e = halo(s, s->mu0, 1))) { *out = nullptr; return bail(e); }
   if (cudaStreamSynchronize(s->st) != cudaSuccess || cudaGetLastError() != cudaSuccess) {
     s->err = "device initialisation failed";
     *out = nullptr;
@@ -150,10 +203,46 @@ int wl_create(const wl_config* cfg, wl_sim** out) {
   return WL_OK;
 }
 
+int wl_create(const wl_config* cfg, wl_sim** out) { return create_impl(cfg, nullptr, out); }
+
+// Slab decomposition: cfg describes the GLOBAL grid; every rank calls this with the
+// same cfg and NCCL id and receives the sim of its slab of N[2]/nranks planes.
+int wl_create_slab(const wl_config* cfg, const wl_dist* dist, wl_sim** out) {
+  if (!dist) return fail(nullptr, WL_ERR_INVALID, "null argument");
+  return create_impl(cfg, dist, out);
+}
+int wl_nccl_unique_id(char id[128]) {
+  if (!id) return WL_ERR_INVALID;
+  { const std::string why = nccl_load(); if (!why.empty()) return fail(nullptr, WL_ERR_CUDA, why); }
+  ncclUniqueId u;
+  if (ncclGetUniqueId(&u) != ncclSuccess) return fail(nullptr, WL_ERR_CUDA, "ncclGetUniqueId failed");
+  memset(id, 0, 128);
+  memcpy(id, &u, sizeof(u));
+  return WL_OK;
+}
+int wl_slab_info(const wl_sim* s, int32_t* rank, int32_t* nranks, int32_t* k_offset, int32_t* n_local, int32_t* n_global) {
+  if (!s) return WL_ERR_INVALID;
+  if (rank) *rank = s->dist.rank;
+  if (nranks) *nranks = s->dist.n;
+  if (k_offset) *k_offset = s->per.kz0;
+  if (n_local) *n_local = s->dist.nzl;
+  if (n_global) *n_global = s->dist.nzg;
+  return WL_OK;
+}
+int wl_halo_stats(const wl_sim* s, int64_t* exchanges, int64_t* bytes) {
+  if (!s) return WL_ERR_INVALID;
+  if (exchanges) *exchanges = s->halo_msgs;
+  if (bytes) *bytes = s->halo_bytes;
+  return WL_OK;
+}
+
 void wl_destroy(wl_sim* s) {
   if (!s) return;
   cudaSetDevice(s->device);
   if (s->st) cudaStreamSynchronize(s->st);
+  if (s->dist.comm) ncclCommDestroy(s->dist.comm);
+  if (s->d_redg) cudaFree(s->d_redg);
+  if (s->h_redg) cudaFreeHost(s->h_redg);
   for (size_t l = 0; l < s->lv.size(); ++l) {
     Level& v = s->lv[l];
     if (v.owns) { free_field(v.L); free_field(v.x); free_field(v.z); }
@@ -208,6 +297,10 @@ static int xfer(wl_sim* s, int field, int level, float* host, size_t count, bool
       WL_CUDA(s, cudaMemcpy2DAsync(h, lay.n0 * sizeof(float), dev, lay.pitch * sizeof(float), lay.n0 * sizeof(float),
                                    (size_t)lay.n1 * lay.n2, cudaMemcpyDeviceToHost, s->st));
   }
+  if (up && s->dist.n > 1 && (field < 10 || s->lv[level].dist)) {
+    // the caller's slab carries one ghost plane; deeper halo planes come from the neighbours
+    if (int e = halo(s, *f, (field == WL_U || field == WL_U0) ? 3 : 1)) return e;
+  }
   WL_CUDA(s, cudaStreamSynchronize(s->st));
   if (up && field == WL_MU1) s->band_dirty = true;
   return WL_OK;
@@ -221,7 +314,8 @@ int wl_finish_ic(wl_sim* s, const float uBC[3]) {
   if (!s) return WL_ERR_INVALID;
   cudaSetDevice(s->device);
   bc_vec(s, s->u, uBC ? uBC : s->cfg.uBC, s->cfg.exitBC != 0);
-  exitbc(s, s->u, s->u, 0.f);                        // runs even when exitBC=false (Flow.jl:141)
+  if (int e = exitbc(s, s->u, s->u, 0.f)) return e;  // runs even when exitBC=false (Flow.jl:141)
+  if (int e = halo(s, s->u, 3)) return e;
   WL_CUDA(s, cudaMemcpyAsync(s->u0.alloc, s->u.alloc, s->u.bytes, cudaMemcpyDeviceToDevice, s->st));
   WL_CUDA(s, cudaStreamSynchronize(s->st));
   return check_async(s, "wl_finish_ic");
@@ -232,11 +326,13 @@ int wl_measure_body(wl_sim* s, const wl_body* body, double t, double eps) {
   if (body->kind == 0) return WL_OK;                 // NoBody: measure! is a no-op (Body.jl:83)
   if (body->kind < 0 || body->kind > 3) return fail(s, WL_ERR_UNSUPPORTED, "unknown body kind");
   cudaSetDevice(s->device);
-  MeasArgs a{s->lay, body_at(body, s->D, (float)t), (float)eps, s->sigma.base, s->V.base, s->mu0.base, s->mu1.base};
+  MeasArgs a{s->lay, body_at(body, s->D, (float)t), (float)eps, s->per.kz0, s->sigma.base, s->V.base, s->mu0.base, s->mu1.base};
   DISPATCH_D(s, k_measure, grid_all(s->lay), blk(s->D), a);
   s->band_dirty = true;
   bc_vec(s, s->mu0, nullptr, false);
   bc_vec(s, s->V, nullptr, s->cfg.exitBC != 0);
+  if (int e = halo(s, s->mu0, 1)) return e;
+  if (int e = halo(s, s->V, 1)) return e;
   return check_async(s, "wl_measure_body");
 }
 
@@ -251,6 +347,8 @@ int wl_set_body_coeffs(wl_sim* s, const float* mu0, const float* mu1, const floa
   s->band_dirty = true;
   bc_vec(s, s->mu0, nullptr, false);
   bc_vec(s, s->V, nullptr, s->cfg.exitBC != 0);
+  if (int e = halo(s, s->mu0, 1)) return e;
+  if (int e = halo(s, s->V, 1)) return e;
   return check_async(s, "wl_set_body_coeffs");
 }
 
@@ -266,8 +364,11 @@ int wl_build_poisson(wl_sim* s) {
 int wl_update_poisson(wl_sim* s) {
   if (!s || s->lv.empty()) return WL_ERR_INVALID;
   cudaSetDevice(s->device);
-  set_diag(s, s->lv[0]);
-  for (size_t l = 1; l < s->lv.size(); ++l) { restrictL(s, s->lv[l - 1], s->lv[l]); set_diag(s, s->lv[l]); }
+  if (int e = set_diag_h(s, s->lv[0])) return e;
+  for (size_t l = 1; l < s->lv.size(); ++l) {
+    if (int e = restrictL(s, s->lv[l - 1], s->lv[l])) return e;
+    if (int e = set_diag_h(s, s->lv[l])) return e;
+  }
   return check_async(s, "wl_update_poisson");
 }
 
@@ -319,9 +420,11 @@ int wl_mom_step(wl_sim* s, const float* uBC_t1, const float* acc0, const float* 
     bdim(s, 0);
   }
   bc_vec(s, s->u, U, ex);
-  if (ex) exitbc(s, s->u, s->u0, s->dt);
+  if (ex) { if (int e = exitbc(s, s->u, s->u0, s->dt)) return e; }
+  if (int e = halo(s, s->u, 1)) return e;              // K-DIVRES reads u one plane up
   if (s->timing) cudaEventRecord(s->ev[1], s->st);
   if (int e = mom_project(s, 1.f, U, &tr[0])) return e;
+  if (int e = halo(s, s->u, 3)) return e;              // K-MOM: QUICK reaches 2 planes, the band's f-neighbours 3
   if (s->timing) cudaEventRecord(s->ev[2], s->st);
   // corrector
   ghost_phi(s);
@@ -333,8 +436,10 @@ int wl_mom_step(wl_sim* s, const float* uBC_t1, const float* acc0, const float* 
     bdim(s, 1);
   }
   bc_vec(s, s->u, U, ex);
+  if (int e = halo(s, s->u, 1)) return e;
   if (s->timing) cudaEventRecord(s->ev[3], s->st);
   if (int e = mom_project(s, 0.5f, U, &tr[1])) return e;
+  if (int e = halo(s, s->u, 3)) return e;
   if (s->timing) cudaEventRecord(s->ev[4], s->st);
   float dtn = 0.f;
   if (int e = cfl(s, &dtn)) return e;
@@ -360,7 +465,7 @@ int wl_mom_step(wl_sim* s, const float* uBC_t1, const float* acc0, const float* 
 int wl_pressure_force(wl_sim* s, const wl_body* body, double t, double out[3]) {
   if (!s || !body || !out) return WL_ERR_INVALID;
   cudaSetDevice(s->device);
-  ForceArgs a{s->lay, body_at(body, s->D, (float)t), s->p.base, s->f.base};
+  ForceArgs a{s->lay, body_at(body, s->D, (float)t), s->p.base, s->f.base, s->per.kz0};
   DISPATCH_D(s, k_force_df, grid_all(s->lay), blk(s->D), a);
   for (int c = 0; c < s->D; ++c) {
     SumArgs sa{s->lay, s->f.base + s->lay.cstride * c, s->redw, s->d_red + 3 + c};
@@ -382,11 +487,13 @@ int wl_debug_op(wl_sim* s, int op, int level, float arg) {
     case 2: { Trace tr; if (int e = mom_project(s, arg, s->cfg.uBC, &tr)) return e; break; }
     case 3: {
       Level& p = s->lv[level];
-      perbc(s, p.lay, p.x.base);
+      perbc(s, p.lay, p.x.base, &p.per);
+      if (p.dist) { if (int e = halo(s, p.x, 1)) return e; }
       LevArgs a = lev_args(s, p);
       a.out = s->d_red + 0;
       DISPATCH_D(s, k_residual, grid_inside(p.lay), blk(s->D), a);
-      a.in = s->d_red + 0; a.out = s->d_red + 1;
+      if (int e = gather_red(s)) return e;
+      a.in = red_in(s, 0); a.out = s->d_red + 1;
       DISPATCH_D(s, k_shift_norms, grid_tiles(p.lay, false), blk(s->D), a);
       break;
     }

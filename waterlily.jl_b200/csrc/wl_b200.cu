@@ -11,6 +11,7 @@
 
 #include "../../include/wl_b200.h"
 #include "wl_common.cuh"
+#include "wl_nccl.cuh"
 #include "wl_kernels_body.cuh"
 #include "wl_kernels_mg.cuh"
 #include "wl_kernels_mg2.cuh"
@@ -36,9 +37,26 @@ struct Level {
   DevField L, x, z, r, eps, Dg, iD;
   bool owns = false;
   int c[3] = {0, 0, 0};
+  // multi-GPU: a level is either DISTRIBUTED (each rank holds its slab; `per` marks the interfaces
+  // and koff is the global plane offset) or REPLICATED (every rank holds and solves the whole level)
+  bool dist = false;
+  int koff = 0;
+  Per per{};
+  long long ncells = 0;      // interior cells of the global level
 };
 
-constexpr int NRED = 8;
+constexpr int NRED = 12;     // slots: 0 Σr, 1 norms, 2 CFL, 3-5 force, 7 zero, 8-9 exitBC!
+constexpr int MAXRANKS = 64;
+
+// Slab decomposition along the last dimension, one process per GPU.
+struct Dist {
+  int rank = 0, n = 1;
+  ncclComm_t comm = nullptr;
+  int lo = -1, hi = -1;                    // neighbour ranks, -1 at a physical (non-periodic) boundary
+  bool lo_wrap = false, hi_wrap = false;   // neighbour reached through the periodic wrap
+  int nzg = 0, nzl = 0;                    // global / local interior planes
+  int min_planes = 4;                      // levels with fewer local planes are replicated
+};
 
 struct ProfRec { const char* name; cudaEvent_t a, b; };
 
@@ -48,7 +66,12 @@ struct wl_sim {
   wl_config cfg{};
   int D = 3;
   Lay lay{};
-  Per per{};
+  Per per{};                  // what the kernels of the (local) fine grid see
+  Per per_glob{};             // true periodicity of the global grid (replicated levels)
+  Dist dist{};
+  Red* d_redg = nullptr;      // all-gathered reduction slots [rank][NRED]
+  Red* h_redg = nullptr;
+  int64_t halo_msgs = 0, halo_bytes = 0;
   DevField u, u0, f, p, sigma, V, mu0, mu1;
   DevField w;                 // third rotating velocity buffer of the fused 3D K-MOM path
   int* band_list = nullptr;   // interior cells with μ₁ ≠ 0 (patched after K-MOM)
@@ -93,7 +116,7 @@ int alloc_field(wl_sim* s, DevField& f, const Lay& lay, int ncomp) {
   f.bytes = (size_t)lay.cstride * ncomp * sizeof(float) + 256;
   WL_CUDA(s, cudaMalloc(&f.alloc, f.bytes));
   WL_CUDA(s, cudaMemsetAsync(f.alloc, 0, f.bytes, s->st));
-  f.base = f.alloc + LPAD;
+  f.base = f.alloc + LPAD + (size_t)lay.zpad * lay.plane;
   return WL_OK;
 }
 void free_field(DevField& f) { if (f.alloc) cudaFree(f.alloc); f.alloc = f.base = nullptr; }
@@ -174,35 +197,98 @@ inline void prof_post(wl_sim* s, const char* name, cudaEvent_t a, cudaEvent_t b)
     }                                                                                     \
   } while (0)
 
+#define WL_NCCL(s, call)                                                                   \
+  do {                                                                                     \
+    ncclResult_t r_ = (call);                                                              \
+    if (r_ != ncclSuccess) {                                                               \
+      (s)->err = std::string(#call) + ": " + ncclGetErrorString(r_);                       \
+      (s)->status = WL_ERR_CUDA;                                                           \
+      return WL_ERR_CUDA;                                                                  \
+    }                                                                                      \
+  } while (0)
+
+// ---------------------------------------------------------------- slab halos and global scalars
+// Exchange `depth` planes per side of every component of `f` with the slab neighbours, on the
+// sim's stream: interior planes [1,1+depth) go to the lower neighbour's [n2-1,n2-1+depth) and
+// [n2-1-depth,n2-1) to the upper neighbour's [1-depth,1).  Whole planes travel (x/y ghosts
+// included), which is what the sequential BC!/perBC! passes of the reference produce for the last
+// direction (core.jl:207-217,239-243).  wrap=false skips the pair that closes a periodic ring (the
+// reference's red-black sweeps never refresh that ghost, Poisson.jl:141-148).
+int halo(wl_sim* s, const DevField& f, int depth, bool wrap = true) {
+  const Dist& d = s->dist;
+  if (d.n == 1) return WL_OK;
+  const Lay& l = f.lay;
+  const size_t cnt = (size_t)l.plane * depth;
+  const bool use_lo = d.lo >= 0 && (wrap || !d.lo_wrap), use_hi = d.hi >= 0 && (wrap || !d.hi_wrap);
+  if (!use_lo && !use_hi) return WL_OK;
+  WL_NCCL(s, ncclGroupStart());
+  for (int c = 0; c < f.ncomp; ++c) {
+    float* b = f.base + l.cstride * c;
+    // sends in (lower, upper) order, receives in (upper, lower) order: with two ranks on a periodic
+    // ring both neighbours are the same peer and messages match in posting order
+    if (use_lo) WL_NCCL(s, ncclSend(b + (size_t)l.plane * 1, cnt, ncclFloat, d.lo, d.comm, s->st));
+    if (use_hi) WL_NCCL(s, ncclSend(b + (size_t)l.plane * (l.n2 - 1 - depth), cnt, ncclFloat, d.hi, d.comm, s->st));
+    if (use_hi) WL_NCCL(s, ncclRecv(b + (size_t)l.plane * (l.n2 - 1), cnt, ncclFloat, d.hi, d.comm, s->st));
+    if (use_lo) WL_NCCL(s, ncclRecv(b + (ptrdiff_t)l.plane * (1 - depth), cnt, ncclFloat, d.lo, d.comm, s->st));
+  }
+  WL_NCCL(s, ncclGroupEnd());
+  s->halo_msgs += 1;
+  s->halo_bytes += (int64_t)cnt * 4 * f.ncomp * ((use_lo ? 1 : 0) + (use_hi ? 1 : 0));
+  return WL_OK;
+}
+// The reduction slots of all ranks, gathered so that every consumer folds them in rank order
+// (results do not depend on the collective's algorithm).  Single GPU: the slots themselves.
+RedIn red_in(wl_sim* s, int slot) {
+  if (s->dist.n == 1) return RedIn{s->d_red + slot, 1, NRED};
+  return RedIn{s->d_redg + slot, s->dist.n, NRED};
+}
+int gather_red(wl_sim* s) {
+  if (s->dist.n == 1) return WL_OK;
+  WL_NCCL(s, ncclAllGather(s->d_red, s->d_redg, sizeof(Red) * NRED, ncclChar, s->dist.comm, s->st));
+  return WL_OK;
+}
+
 // ---------------------------------------------------------------- boundary conditions
-void bc_vec(wl_sim* s, DevField& a, const float* U, bool saveexit) {
+void bc_vec(wl_sim* s, DevField& a, const float* U, bool saveexit, const Per* per = nullptr) {
   BcArgs args;
-  args.l = a.lay; args.a = a.base; args.per = s->per; args.saveexit = saveexit ? 1 : 0;
+  args.l = a.lay; args.a = a.base; args.per = per ? *per : s->per; args.saveexit = saveexit ? 1 : 0;
   for (int d = 0; d < 3; ++d) args.U.v[d] = U ? U[d] : 0.f;
   dim3 g, b;
   plane_launch(a.lay, g, b);
   g.z = 3 * s->D;
   DISPATCH_D(s, k_bc_vec, g, b, args);
 }
-void perbc(wl_sim* s, const Lay& l, float* a) {
+void perbc(wl_sim* s, const Lay& l, float* a, const Per* per = nullptr) {
+  const Per& pp = per ? *per : s->per;
   for (int d = 0; d < s->D; ++d) {
-    if (!s->per.p[d]) continue;
+    if (!pp.p[d]) continue;
     PerArgs args{l, a, d};
     dim3 g, b;
     plane_launch(l, g, b);
     DISPATCH_D(s, k_perbc, g, b, args);
   }
 }
-void exitbc(wl_sim* s, DevField& u, DevField& u0, float dt) {
-  ExitArgs args{u.lay, u.base, u0.base, dt};
-  DISPATCH_D(s, k_exitbc, dim3(1), dim3(1024), args);
+int exitbc(wl_sim* s, DevField& u, DevField& u0, float dt) {
+  if (s->dist.n == 1) {
+    ExitArgs args{u.lay, u.base, u0.base, dt};
+    DISPATCH_D(s, k_exitbc, dim3(1), dim3(1024), args);
+    return WL_OK;
+  }
+  const long long len = (long long)(u.lay.n1 - 2) * s->dist.nzg;
+  for (int stage = 0; stage < 3; ++stage) {
+    ExitDistArgs a{u.lay, u.base, u0.base, dt, stage, len, red_in(s, 8), red_in(s, 9), s->d_red + 8 + (stage == 1)};
+    LAUNCH(s, k_exitbc_dist, dim3(1), dim3(1024), a);
+    if (stage < 2) { if (int e = gather_red(s)) return e; }
+  }
+  return WL_OK;
 }
 
 // ---------------------------------------------------------------- multigrid pieces
 LevArgs lev_args(wl_sim* s, Level& p) {
   LevArgs a{};
   a.l = p.lay; a.L = p.L.base; a.x = p.x.base; a.r = p.r.base; a.eps = p.eps.base; a.z = p.z.base;
-  a.omega = 1.f; a.k0 = 0; a.w = s->redw; a.out = s->d_red; a.in = s->d_red; a.want_norms = 0;
+  a.omega = 1.f; a.k0 = 0; a.w = s->redw; a.out = s->d_red; a.in = red_in(s, 0); a.want_norms = 0;
+  a.ncells = p.ncells;
   return a;
 }
 void set_diag(wl_sim* s, Level& p) {
@@ -210,7 +296,7 @@ void set_diag(wl_sim* s, Level& p) {
   DISPATCH_D(s, k_set_diag, grid_inside(p.lay), blk(s->D), a);
 }
 void increment(wl_sim* s, Level& p, float w, Red* norms) {
-  perbc(s, p.lay, p.eps.base);
+  perbc(s, p.lay, p.eps.base, &p.per);
   LevArgs a = lev_args(s, p);
   a.omega = w; a.want_norms = norms ? 1 : 0; a.out = norms ? norms : s->d_red;
   DISPATCH_D(s, k_increment, grid_inside(p.lay), blk(s->D), a);
@@ -225,7 +311,7 @@ void jacobi(wl_sim* s, Level& p) {
 void smooth(wl_sim* s, Level& p, float w, Red* norms) {
   LevArgs a = lev_args(s, p);
   DISPATCH_D(s, k_eps_init, grid_inside(p.lay), blk(s->D), a);
-  perbc(s, p.lay, p.eps.base);
+  perbc(s, p.lay, p.eps.base, &p.per);
   for (int k0 = 1; k0 <= 4; ++k0) {
     a.k0 = k0;
     DISPATCH_D(s, k_gs_half, grid_inside(p.lay), blk(s->D), a);
@@ -240,10 +326,38 @@ void prolongate(wl_sim* s, Level& fi, Level& co) {
   XferArgs a{fi.lay, co.lay, co.x.base, fi.eps.base, {co.c[0], co.c[1], co.c[2]}};
   DISPATCH_D(s, k_prolongate, grid_inside(fi.lay), blk(s->D), a);
 }
-void restrictL(wl_sim* s, Level& fi, Level& co) {
-  XferLArgs a{fi.lay, co.lay, fi.L.base, co.L.base, {co.c[0], co.c[1], co.c[2]}};
-  DISPATCH_D(s, k_restrictL, grid_inside(co.lay), blk(s->D), a);
-  bc_vec(s, co.L, nullptr, false);
+// restrictL! (MultiLevelPoisson.jl:42-47).  Distributed fine level over a replicated coarse one: every
+// rank fills its plane range of the coarse array, the ranges are all-gathered in place, then BC!.
+int restrictL(wl_sim* s, Level& fi, Level& co) {
+  const bool gather = fi.dist && !co.dist;
+  const int nzc = co.c[2] ? s->dist.nzl >> 0 : 0;   // (unused; the local coarse extent follows from fi.lay)
+  (void)nzc;
+  Lay lc = co.lay;
+  float* Lc = co.L.base;
+  int nloc = 0;
+  if (gather) {                                     // local view of the replicated coarse array
+    nloc = co.c[2] ? (fi.lay.n2 - 2) / 2 : fi.lay.n2 - 2;
+    lc.n2 = nloc + 2;
+    Lc += (size_t)co.lay.plane * (s->dist.rank * nloc);
+  }
+  XferLArgs a{fi.lay, lc, fi.L.base, Lc, {co.c[0], co.c[1], co.c[2]}};
+  DISPATCH_D(s, k_restrictL, grid_inside(lc), blk(s->D), a);
+  if (gather) {
+    const size_t cnt = (size_t)co.lay.plane * nloc;
+    for (int c = 0; c < s->D; ++c) {
+      float* b = co.L.base + co.lay.cstride * c + co.lay.plane;
+      WL_NCCL(s, ncclAllGather(b + cnt * s->dist.rank, b, cnt, ncclFloat, s->dist.comm, s->st));
+    }
+  }
+  bc_vec(s, co.L, nullptr, false, &co.per);
+  if (co.dist) return halo(s, co.L, 1);
+  return WL_OK;
+}
+// set_diag! + the halo of iD that the fused kernels read at neighbour cells
+int set_diag_h(wl_sim* s, Level& p) {
+  set_diag(s, p);
+  if (p.dist) return halo(s, p.iD, 1);
+  return WL_OK;
 }
 // Vcycle!(ml;l,ω) (MultiLevelPoisson.jl:88-101), v1 kernels (kept for WL_FLAG_NO_FUSED)
 void vcycle_v1(wl_sim* s, size_t l, float w) {
@@ -264,48 +378,96 @@ LevDev levdev(const Level& p) {
   for (int q = 0; q < 3; ++q) d.c[q] = p.c[q];
   return d;
 }
+// the rank's window into a REPLICATED coarse level as seen from the DISTRIBUTED level above it:
+// local plane k of the window is global plane k + koff of the coarse array
+LevDev levdev_window(wl_sim* s, const Level& fine, const Level& co) {
+  LevDev d = levdev(co);
+  if (fine.dist && !co.dist) {
+    const int nloc = co.c[2] ? (fine.lay.n2 - 2) / 2 : fine.lay.n2 - 2;
+    const size_t sh = (size_t)co.lay.plane * (s->dist.rank * nloc);
+    d.l.n2 = nloc + 2;
+    d.x += sh; d.r += sh; d.eps += sh;
+  }
+  return d;
+}
 // one block of 1024 threads sweeps a level in (cells/1024) dependent round trips to L2 per phase:
 // worthwhile up to ~18^3, beyond that the per-level launches win
-inline bool level_is_small(const Level& p) { return (long long)p.lay.n0 * p.lay.n1 * p.lay.n2 <= 8000; }
-// GaussSeidelRB!(p;it=4,ω): ϵ init + ghost images, 4 half sweeps on stale ghosts, wrap-read increment
-void smooth2(wl_sim* s, Level& p, float w, Red* norms) {
-  SmArgs a{levdev(p), s->per, w, 0, s->redw, norms ? norms : s->d_red, norms ? 1 : 0};
+inline bool level_is_small(const Level& p) { return !p.dist && (long long)p.lay.n0 * p.lay.n1 * p.lay.n2 <= 8000; }
+// GaussSeidelRB!(p;it=4,ω): ϵ init + ghost images, 4 half sweeps on stale ghosts, wrap-read increment.
+// Distributed levels: the ϵ ghost planes at slab interfaces are refreshed after every half sweep (a
+// colour only reads the other colour, so this reproduces the single-domain sweep exactly); the
+// planes across a periodic wrap are sent once after the init and once before the increment, which
+// is when the reference's perBC!(ϵ) runs.
+int smooth2(wl_sim* s, Level& p, float w, Red* norms) {
+  SmArgs a{levdev(p), p.per, w, 0, s->redw, norms ? norms : s->d_red, norms ? 1 : 0};
   DISPATCH_D(s, k_eps_init_g, grid_inside(p.lay), blk(s->D), a);
+  if (p.dist) { if (int e = halo(s, p.eps, 1, true)) return e; }
   LevArgs g = lev_args(s, p);
   for (int k0 = 1; k0 <= 4; ++k0) {
     g.k0 = k0;
     DISPATCH_D(s, k_gs_half, grid_inside(p.lay), blk(s->D), g);
+    if (p.dist) { if (int e = halo(s, p.eps, 1, k0 == 4)) return e; }
   }
   DISPATCH_D(s, k_increment_w, grid_tiles(p.lay, false), blk(s->D), a);
+  return WL_OK;
 }
 // levels first..end in ONE single-block launch: Vcycle!(l=first) (if any coarser level) + smooth!(first)
 void coarse_block(wl_sim* s, size_t first, float w) {
   CoarseArgs a{};
   for (size_t l = 0; l < s->lv.size() && l < (size_t)WL_MAXLEV; ++l) a.lv[l] = levdev(s->lv[l]);
-  a.first = (int)first; a.nlev = (int)s->lv.size(); a.per = s->per; a.omega = w;
+  a.first = (int)first; a.nlev = (int)s->lv.size(); a.per = s->per_glob; a.omega = w;
   DISPATCH_D(s, k_coarse, dim3(1), dim3(1024), a);
 }
-void vcycle(wl_sim* s, size_t l, float w) {
-  if (s->cfg.flags & WL_FLAG_NO_FUSED) return vcycle_v1(s, l, w);
+int vcycle(wl_sim* s, size_t l, float w) {
+  if (s->cfg.flags & WL_FLAG_NO_FUSED) { vcycle_v1(s, l, w); return WL_OK; }
   Level &fine = s->lv[l], &coarse = s->lv[l + 1];
+  const bool gather = fine.dist && !coarse.dist;
   {
-    DownArgs a{levdev(fine), levdev(coarse), s->per};
+    if (fine.dist) { if (int e = halo(s, fine.r, 1)) return e; }       // K-DOWN reads ϵ = r·iD at the neighbours
+    DownArgs a{levdev(fine), levdev_window(s, fine, coarse), fine.per};
     DISPATCH_D(s, k_down, grid_inside(fine.lay), blk(s->D), a);
     std::swap(fine.r, fine.eps);                     // K-DOWN staged the new residual in ϵ
+    if (gather) {                                    // assemble the replicated coarse residual
+      const int nloc = a.c.l.n2 - 2;
+      const size_t cnt = (size_t)coarse.lay.plane * nloc;
+      float* b = coarse.r.base + coarse.lay.plane;
+      WL_NCCL(s, ncclAllGather(b + cnt * s->dist.rank, b, cnt, ncclFloat, s->dist.comm, s->st));
+      WL_CUDA(s, cudaMemsetAsync(coarse.x.alloc, 0, coarse.x.bytes, s->st));   // fill!(coarse.x,0) on every rank's copy
+    }
   }
   if (level_is_small(coarse)) {
     coarse_block(s, l + 1, w);
   } else {
-    if (l + 2 < s->lv.size()) vcycle(s, l + 1, w);
-    smooth2(s, coarse, w, nullptr);
+    if (l + 2 < s->lv.size()) { if (int e = vcycle(s, l + 1, w)) return e; }
+    if (int e = smooth2(s, coarse, w, nullptr)) return e;
   }
-  UpArgs u{levdev(fine), levdev(coarse), s->per, w, s->redw, s->d_red, 0};
+  if (coarse.dist) { if (int e = halo(s, coarse.x, 1)) return e; }     // K-UP prolongates the neighbours' coarse cells too
+  else if (gather && s->per_glob.p[2]) {                               // rank windows read the wrap planes as ghosts
+    PerArgs pa{coarse.lay, coarse.x.base, 2};
+    dim3 g, b;
+    plane_launch(coarse.lay, g, b);
+    DISPATCH_D(s, k_perbc, g, b, pa);
+  }
+  UpArgs u{levdev(fine), levdev_window(s, fine, coarse), fine.per, w, s->redw, s->d_red, 0};
   DISPATCH_D(s, k_up, grid_inside(fine.lay), blk(s->D), u);
+  return WL_OK;
 }
 
+// reduction slots -> pinned host memory (all ranks' slots folded in rank order)
 int fetch_red(wl_sim* s) {
-  WL_CUDA(s, cudaMemcpyAsync(s->h_red, s->d_red, sizeof(Red) * NRED, cudaMemcpyDeviceToHost, s->st));
+  if (s->dist.n == 1) {
+    WL_CUDA(s, cudaMemcpyAsync(s->h_red, s->d_red, sizeof(Red) * NRED, cudaMemcpyDeviceToHost, s->st));
+    WL_CUDA(s, cudaStreamSynchronize(s->st));
+    return WL_OK;
+  }
+  if (int e = gather_red(s)) return e;
+  WL_CUDA(s, cudaMemcpyAsync(s->h_redg, s->d_redg, sizeof(Red) * NRED * s->dist.n, cudaMemcpyDeviceToHost, s->st));
   WL_CUDA(s, cudaStreamSynchronize(s->st));
+  for (int q = 0; q < NRED; ++q) {
+    double sum = 0.0; float m = -INFINITY;
+    for (int r = 0; r < s->dist.n; ++r) { sum += s->h_redg[r * NRED + q].sum; m = std::fmax(m, s->h_redg[r * NRED + q].maxv); }
+    s->h_red[q].sum = sum; s->h_red[q].maxv = m;
+  }
   return WL_OK;
 }
 
@@ -316,17 +478,19 @@ struct Trace { int n = 0; int flags = 0; float rinf[34], r1[34], omega[34]; };
 int mlp_solver(wl_sim* s, Trace* tr, bool residual_done = false) {
   Level& p = s->lv[0];
   const double tol = s->cfg.tol;
-  const double r1tol = (tol / 10) * (double)p.lay.ninside(), rinftol = tol;
+  const double r1tol = (tol / 10) * (double)p.ncells, rinftol = tol;
   const int itmx = s->cfg.itmx;
   const bool fused = !(s->cfg.flags & WL_FLAG_NO_FUSED);
   {
     LevArgs a = lev_args(s, p);
     if (!residual_done) {                       // K-DIVRES already produced r and Σr in slot 0
-      perbc(s, p.lay, p.x.base);
+      perbc(s, p.lay, p.x.base, &p.per);
+      if (p.dist) { if (int e = halo(s, p.x, 1)) return e; }
       a.out = s->d_red + 0;
       DISPATCH_D(s, k_residual, grid_inside(p.lay), blk(s->D), a);
     }
-    a.in = s->d_red + 0; a.out = s->d_red + 1;
+    if (int e = gather_red(s)) return e;
+    a.in = red_in(s, 0); a.out = s->d_red + 1;
     DISPATCH_D(s, k_shift_norms, grid_tiles(p.lay, false), blk(s->D), a);
   }
   if (int e = fetch_red(s)) return e;
@@ -337,11 +501,11 @@ int mlp_solver(wl_sim* s, Trace* tr, bool residual_done = false) {
     if (fused && level_is_small(p)) {            // the whole hierarchy fits the single-block kernel
       coarse_block(s, 0, w);
       LevArgs a = lev_args(s, p);
-      a.in = s->d_red + 7; a.out = s->d_red + 1; // slot 7 stays zero: no shift, norms only
+      a.in = red_in(s, 7); a.out = s->d_red + 1; // slot 7 stays zero: no shift, norms only
       DISPATCH_D(s, k_shift_norms, grid_tiles(p.lay, false), blk(s->D), a);
     } else {
-      vcycle(s, 0, w);
-      if (fused) smooth2(s, p, w, s->d_red + 1);
+      if (int e = vcycle(s, 0, w)) return e;
+      if (fused) { if (int e = smooth2(s, p, w, s->d_red + 1)) return e; }
       else smooth(s, p, w, s->d_red + 1);
     }
     if (int e = fetch_red(s)) return e;
@@ -355,7 +519,10 @@ int mlp_solver(wl_sim* s, Trace* tr, bool residual_done = false) {
     if ((double)r1 < r1tol && (double)rinf < rinftol) break;
   }
   if (np >= itmx) flags |= 2;
-  if (!residual_done) perbc(s, p.lay, p.x.base);   // fused projection wrap-reads x and stores p's images itself
+  if (!residual_done) {                             // fused projection wrap-reads x and stores p's images itself
+    perbc(s, p.lay, p.x.base, &p.per);
+    if (p.dist) { if (int e = halo(s, p.x, 1)) return e; }
+  }
   if (tr) { tr->n = np; tr->flags = flags; }
   return WL_OK;
 }
@@ -432,9 +599,11 @@ int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
     DISPATCH_D(s, k_divres, grid_tiles(s->lay, false), blk(s->D), d);
     std::swap(s->p, p0.eps); p0.x = s->p;                       // scaled x lives in the former ϵ buffer
     if (int e = mlp_solver(s, tr, true)) return e;
+    if (int e = halo(s, p0.x, 1)) return e;                     // the solver's final perBC!(x) across slabs
     ProjArgs2 q{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, s->per, dt};
     DISPATCH_D(s, k_proj, grid_inside(s->lay), blk(s->D), q);
     std::swap(s->p, p0.eps); p0.x = s->p;
+    if (int e = halo(s, s->p, 1)) return e;                     // p's ghost planes (next K-DIVRES, data surface)
     bc_vec(s, s->u, U, s->cfg.exitBC != 0);
     return WL_OK;
   }
@@ -447,7 +616,7 @@ int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
   return WL_OK;
 }
 int cfl(wl_sim* s, float* out) {
-  CflArgs a{s->lay, s->u.base, s->sigma.base, s->redw, s->d_red + 2};
+  CflArgs a{s->lay, s->u.base, s->sigma.base, s->redw, s->d_red + 2, s->per.zlo, s->per.zhi};
   DISPATCH_D(s, k_cfl, grid_tiles(s->lay, true), blk(s->D), a);
   if (int e = fetch_red(s)) return e;
   const float m = s->h_red[2].maxv;

@@ -19,6 +19,7 @@ struct Lay {
   int D;
   int pitch, plane;  // floats
   long long cstride; // floats between components of a vector field
+  int zpad;          // planes allocated beyond each z ghost plane (host bookkeeping)
   __host__ __device__ int off(int i, int j, int k) const { return i + pitch * j + plane * k; }
   __host__ __device__ int n(int d) const { return d == 0 ? n0 : d == 1 ? n1 : n2; }
   __host__ __device__ int stride(int d) const { return d == 0 ? 1 : d == 1 ? pitch : plane; }
@@ -28,19 +29,25 @@ struct Lay {
   }
 };
 
-inline Lay make_lay(int D, const int* ng) {
+// zpad: extra planes allocated below k==0 and above k==n2-1 (slab decomposition: the velocity
+// needs 3 halo planes per side, the first of which is the ordinary ghost plane)
+inline Lay make_lay(int D, const int* ng, int zpad = 0) {
   Lay l;
-  l.D = D;
+  l.D = D; l.zpad = zpad;
   l.n0 = ng[0]; l.n1 = ng[1]; l.n2 = D == 3 ? ng[2] : 1;
   l.pitch = ((l.n0 + 31) / 32) * 32;
   if (l.pitch < l.n0 + 0) l.pitch += 32;
   l.plane = l.pitch * l.n1;
-  long long vol = (long long)l.plane * l.n2;
+  long long vol = (long long)l.plane * (l.n2 + 2 * zpad);
   l.cstride = ((vol + 64 + 31) / 32) * 32;   // +LPAD front, slack behind for vector tails
   return l;
 }
 
-struct Per { int p[3]; };
+// p[d]: direction d is periodic AND handled inside the kernel (wrap-reads / image stores).
+// zlo/zhi: the lower/upper end of the last dimension is an INTERFACE to a neighbouring slab
+// (multi-GPU): its ghost planes hold the neighbour's cells (filled by halo exchange), so no
+// boundary variant applies there and p[2] is 0.  kz0: global index of local plane k==0.
+struct Per { int p[3]; int zlo, zhi; int kz0; };
 struct Vec3 { float v[3]; };
 
 // ---- deterministic block reduction helpers (warp shuffle -> smem -> thread 0)
@@ -61,6 +68,14 @@ struct Red {
   float  maxv;      // max|r| (L∞) or max σ (CFL)
   float  pad;
 };
+// A reduction result as its consumers see it: one Red per rank, `stride` Reds apart, folded in rank
+// order (multi-GPU: the slots of all ranks are all-gathered; single GPU: n == 1).
+struct RedIn { const Red* p; int n, stride; };
+__host__ __device__ inline double redin_sum(const RedIn& r) {
+  double s = 0.0;
+  for (int q = 0; q < r.n; ++q) s += r.p[(size_t)q * r.stride].sum;
+  return s;
+}
 
 // Two-stage, order-fixed reduction: every block writes one partial; the last block to finish
 // (ticket counter) folds the partials in index order, so the result does not depend on the

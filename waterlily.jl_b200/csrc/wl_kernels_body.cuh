@@ -90,6 +90,7 @@ struct MeasArgs {
   Lay l;
   BodyDev b;
   float eps;
+  int kz0;           // global index of local plane 0 (slab decomposition)
   float* sigma; float* V; float* mu0; float* mu1;
 };
 
@@ -107,7 +108,7 @@ __global__ void __launch_bounds__(256) k_measure(const MeasArgs a) {
   float Vv[3] = {0.f, 0.f, 0.f}, m0[3] = {1.f, 1.f, 1.f}, m1[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (in) {
     const float d2 = (2.f + a.eps) * (2.f + a.eps);
-    float x[3] = {(float)i - 0.5f, (float)j - 0.5f, (float)k - 0.5f};
+    float x[3] = {(float)i - 0.5f, (float)j - 0.5f, (float)(k + a.kz0) - 0.5f};
     const float sd = measure_pt<D>(a.b, x, 0.f).d;          // sdf(body,x,t) raw
     a.sigma[o] = sd;
     if (sd * sd < d2) {
@@ -138,7 +139,7 @@ __global__ void __launch_bounds__(256) k_measure(const MeasArgs a) {
 }
 
 // pressure_force (Metrics.jl:126-133): df = p·nds over inside (df ≡ flow.f, zero elsewhere).
-struct ForceArgs { Lay l; BodyDev b; const float* p; float* f; };
+struct ForceArgs { Lay l; BodyDev b; const float* p; float* f; int kz0; };
 template <int D>
 __global__ void __launch_bounds__(256) k_force_df(const ForceArgs a) {
   const Lay& l = a.l;
@@ -150,7 +151,7 @@ __global__ void __launch_bounds__(256) k_force_df(const ForceArgs a) {
   const bool in = i >= 1 && i <= l.n0 - 2 && j >= 1 && j <= l.n1 - 2 && (D == 2 || (k >= 1 && k <= l.n2 - 2));
   float df[3] = {0.f, 0.f, 0.f};
   if (in) {
-    const float x[3] = {(float)i - 0.5f, (float)j - 0.5f, (float)k - 0.5f};
+    const float x[3] = {(float)i - 0.5f, (float)j - 0.5f, (float)(k + a.kz0) - 0.5f};
     const Meas m = measure_pt<D>(a.b, x, 1.f);
     const float kq = kern(fmaxf(-1.f, fminf(m.d, 1.f)));
     const float pv = a.p[o];

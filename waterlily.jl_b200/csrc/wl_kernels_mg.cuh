@@ -18,7 +18,8 @@ struct LevArgs {
   int k0;            // GS colour pass 1..4
   RedWork w;
   Red* out;
-  const Red* in;     // residual mean input (k_shift_norms)
+  RedIn in;          // residual sum input (k_shift_norms)
+  long long ncells;  // interior cells of the GLOBAL level (mean of the residual)
   int want_norms;
 };
 
@@ -95,7 +96,7 @@ __global__ void __launch_bounds__(256) k_residual(const LevArgs a) {
 template <int D>
 __global__ void __launch_bounds__(256) k_shift_norms(const LevArgs a) {
   const Lay& l = a.l;
-  const float s = (float)a.in->sum / (float)l.ninside();
+  const float s = (float)redin_sum(a.in) / (float)a.ncells;
   const bool shift = fabsf(s) > 2.f * 1.1920929e-07f;
   double s1 = 0.0; float m = -INFINITY;
   for_tiles_inside<D>(l, [&](int i, int j, int k) {          // 1-D persistent grid

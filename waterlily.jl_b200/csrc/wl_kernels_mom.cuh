@@ -41,6 +41,12 @@ __device__ __forceinline__ float face_flux(const float* __restrict__ ui, const f
   return f - dif;
 }
 
+// Slab interfaces (multi-GPU): a z-face next to an interface is an ordinary inner face whose
+// stencil reaches into the halo planes, so the boundary variants must not be selected there.
+__device__ __forceinline__ void zface_eff(const Per& per, int dj, int& cj, int& Nj) {
+  if (dj == 2 && ((per.zlo && cj <= 1) || (per.zhi && cj >= Nj - 1))) { cj = 2; Nj = 1 << 28; }
+}
+
 struct MomArgs {
   Lay l;
   const float* ua;   // advecting/advected velocity (u⁰ in the predictor, u in the corrector)
@@ -66,20 +72,23 @@ __device__ __forceinline__ float rhs_f(const MomArgs& a, int ci, int c0, int c1,
   const int st[3] = {1, l.pitch, l.plane};
   bool lowghost = false;
 #pragma unroll
-  for (int d = 0; d < D; ++d) lowghost |= (c[d] == 0);
+  for (int d = 0; d < D; ++d) lowghost |= (c[d] == 0) && !(d == 2 && a.per.zlo);
   const float* ui = a.ua + l.cstride * ci;
   float r = 0.f;
   if (!lowghost) {
 #pragma unroll
     for (int dj = 0; dj < D; ++dj) {
-      if (c[dj] > N[dj] - 2) continue;               // upper ghost in j: no j-contribution
+      if (c[dj] > N[dj] - 2 && !(dj == 2 && a.per.zhi)) continue;   // upper ghost in j: no j-contribution
       const float* uj = a.ua + l.cstride * dj;
       const bool pj = a.per.p[dj] != 0;
-      r += face_flux<S>(ui, uj, o, st[ci], st[dj], c[dj], N[dj], pj, a.nu);
+      int cl = c[dj], Nl = N[dj], cu = c[dj] + 1, Nu = N[dj];
+      zface_eff(a.per, dj, cl, Nl);
+      zface_eff(a.per, dj, cu, Nu);
+      r += face_flux<S>(ui, uj, o, st[ci], st[dj], cl, Nl, pj, a.nu);
       if (c[dj] == N[dj] - 2 && pj)                  // Φ[CIj(j,I,2)] Flow.jl:62
         r -= face_flux<S>(ui, uj, o - st[dj] * (N[dj] - 3), st[ci], st[dj], 1, N[dj], true, a.nu);
       else
-        r -= face_flux<S>(ui, uj, o + st[dj], st[ci], st[dj], c[dj] + 1, N[dj], pj, a.nu);
+        r -= face_flux<S>(ui, uj, o + st[dj], st[ci], st[dj], cu, Nu, pj, a.nu);
     }
   }
   r += a.acc.v[ci];
@@ -155,12 +164,13 @@ __device__ __forceinline__ float bc_resolve(const BcArgs& a, int ci, int c0, int
 #pragma unroll
   for (int dj = D - 1; dj >= 0; --dj) {
     const int x = c[dj], n = N[dj];
+    const bool lo_if = dj == 2 && a.per.zlo, hi_if = dj == 2 && a.per.zhi;   // slab interface: no pass writes there
     if (a.per.p[dj]) {
       if (x == 0) c[dj] = n - 2; else if (x == n - 1) c[dj] = 1;
     } else if (ci == dj) {
-      if (x <= 1 || (x == n - 1 && !(a.saveexit && ci == 0))) return a.U.v[ci];
+      if ((x <= 1 && !lo_if) || (x == n - 1 && !hi_if && !(a.saveexit && ci == 0))) return a.U.v[ci];
     } else {
-      if (x == 0) c[dj] = 1; else if (x == n - 1) c[dj] = n - 2;
+      if (x == 0 && !lo_if) c[dj] = 1; else if (x == n - 1 && !hi_if) c[dj] = n - 2;
     }
   }
   return a.a[a.l.cstride * ci + a.l.off(c[0], c[1], c[2])];
@@ -173,6 +183,7 @@ __global__ void k_bc_vec(const BcArgs a) {
   const int dj = blockIdx.z / 3, which = blockIdx.z % 3;
   const Lay& l = a.l;
   const int N[3] = {l.n0, l.n1, l.n2};
+  if (dj == 2 && (which == 2 ? a.per.zhi : a.per.zlo)) return;   // slab interface: filled by the halo exchange
   const int da = dj == 0 ? 1 : 0;                 // fast in-plane dim
   const int db = dj == 2 ? 1 : 2;                 // slow in-plane dim (unused in 2D)
   const int pa = blockIdx.x * blockDim.x + threadIdx.x;
@@ -264,6 +275,44 @@ __global__ void __launch_bounds__(1024) k_exitbc(const ExitArgs a) {
   }
 }
 
+// exitBC! across slabs: every rank owns a z-range of both x-planes, so the two plane means become
+// all-gathered partial sums (folded in rank order) and the kernel splits in three.
+// stage 0: Σ u[2,J] -> out;  stage 1: convect the exit plane with U from in0, Σ -> out;
+// stage 2: subtract the flux defect (in0: inflow sums, in1: exit sums).  `len` = cells of the GLOBAL plane.
+struct ExitDistArgs { Lay l; float* u; const float* u0; float dt; int stage; long long len; RedIn in0, in1; Red* out; };
+__global__ void __launch_bounds__(1024) k_exitbc_dist(const ExitDistArgs a) {
+  __shared__ double sh[32];
+  const Lay& l = a.l;
+  const int m1 = l.n1 - 2, m2 = l.n2 - 2;
+  const int len = m1 * m2;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const float U = a.stage > 0 ? (float)redin_sum(a.in0) / (float)a.len : 0.f;
+  const float fl = a.stage == 2 ? (float)redin_sum(a.in1) / (float)a.len - U : 0.f;
+  double s = 0;
+  for (int q = tid; q < len; q += blockDim.x) {
+    const int j = 1 + q % m1, k = 1 + q / m1;
+    if (a.stage == 0) {
+      s += (double)a.u[l.off(1, j, k)];
+    } else if (a.stage == 1) {
+      const int o = l.off(l.n0 - 1, j, k);
+      const float v = a.u0[o] - U * a.dt * (a.u0[o] - a.u0[o - 1]);
+      a.u[o] = v;
+      s += (double)v;
+    } else {
+      a.u[l.off(l.n0 - 1, j, k)] -= fl;
+    }
+  }
+  if (a.stage == 2) return;
+  s = warp_sum(s);
+  if (lane == 0) sh[wid] = s;
+  __syncthreads();
+  if (wid == 0) {
+    double t = lane < (blockDim.x >> 5) ? sh[lane] : 0.0;
+    t = warp_sum(t);
+    if (lane == 0) { a.out->sum = t; a.out->maxv = -INFINITY; }
+  }
+}
+
 // ---------------------------------------------------------------- projection pieces (Flow.jl:223-232)
 struct ProjArgs { Lay l; float* u; float* x; float* z; const float* L; float dt; };
 
@@ -316,7 +365,7 @@ __global__ void __launch_bounds__(256) k_unscale(const ProjArgs a) {
 // ---------------------------------------------------------------- CFL (Flow.jl:234-244)
 // σ = flux_out inside; max over the WHOLE σ array (ghosts keep the stale conv-diff Φ values
 // k_ghost_phi wrote, as in the reference).
-struct CflArgs { Lay l; const float* u; float* sigma; RedWork w; Red* out; };
+struct CflArgs { Lay l; const float* u; float* sigma; RedWork w; Red* out; int zlo, zhi; };
 template <int D>
 __global__ void __launch_bounds__(256) k_cfl(const CflArgs a) {
   const Lay& l = a.l;
@@ -334,7 +383,7 @@ __global__ void __launch_bounds__(256) k_cfl(const CflArgs a) {
       }
       a.sigma[o] = s;
       m = fmaxf(m, s);
-    } else {
+    } else if (!(D == 3 && ((a.zlo && k == 0) || (a.zhi && k == l.n2 - 1)))) {   // interface planes belong to the neighbour
       m = fmaxf(m, a.sigma[o]);
     }
   });
@@ -355,14 +404,18 @@ __global__ void k_ghost_phi(const GhostPhiArgs a) {
   if (pa >= N[da] || (D == 3 ? pb >= N[db] : pb > 0)) return;
   int c[3] = {0, 0, 0};
   c[dg] = N[dg] - 1; c[da] = pa; if (D == 3) c[db] = pb;
-  for (int d = 0; d < D; ++d) if (c[d] == 0) return;           // lower ghosts are never written
+  if (D == 3 && dg == 2 && a.per.zhi) return;                  // not a ghost plane of the global grid
+  for (int d = 0; d < D; ++d) if (c[d] == 0) return;           // lower ghosts are never written (interface planes: the neighbour's)
+  if (D == 3 && a.per.zhi && c[2] == N[2] - 1) return;
   const int st[3] = {1, l.pitch, l.plane};
   const int ci = D - 1;
   for (int dj = D - 1; dj >= 0; --dj) {
-    const int lo = a.per.p[dj] ? 1 : 2;
+    const int lo = (a.per.p[dj] || (dj == 2 && a.per.zlo)) ? 1 : 2;
     if (c[dj] < lo || c[dj] > N[dj] - 2) continue;
     const int o = l.off(c[0], c[1], c[2]);
-    a.sigma[o] = face_flux<S>(a.u + l.cstride * ci, a.u + l.cstride * dj, o, st[ci], st[dj], c[dj], N[dj],
+    int cj = c[dj], Nj = N[dj];
+    zface_eff(a.per, dj, cj, Nj);
+    a.sigma[o] = face_flux<S>(a.u + l.cstride * ci, a.u + l.cstride * dj, o, st[ci], st[dj], cj, Nj,
                               a.per.p[dj] != 0, a.nu);
     return;
   }

@@ -91,6 +91,7 @@ __device__ __forceinline__ void mom3_body(const Mom3Args& a, float (*shy)[3][M3_
   const int dy0 = FAST ? -2 * pitch : (max(j - 2, 0) - j) * pitch, dy1 = -pitch,
             dy2 = FAST ? pitch : (min(j + 1, N1 - 1) - j) * pitch;
   const bool p0 = a.per.p[0] != 0, p1 = a.per.p[1] != 0, p2 = a.per.p[2] != 0;
+  const int klo = a.per.zlo ? -1 : 0, khi = a.per.zhi ? N2 : N2 - 1;   // readable plane range (slab halos)
   const int kx = FAST ? 0 : (i == 1 ? (p0 ? 2 : 1) : (i == N0 - 1 ? (p0 ? 4 : 3) : 0));
   const int ky = FAST ? 0 : (j == 1 ? (p1 ? 2 : 1) : (j == N1 - 1 ? (p1 ? 4 : 3) : 0));
   const float* U[3] = {a.ua, a.ua + l.cstride, a.ua + 2 * l.cstride};
@@ -102,16 +103,16 @@ __device__ __forceinline__ void mom3_body(const Mom3Args& a, float (*shy)[3][M3_
   float w[3][4];   // own column: planes k-2, k-1, k, k+1
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    w[c][0] = pc[c][plane * (max(k0 - 2, 0) - k0)];
+    w[c][0] = pc[c][plane * (max(k0 - 2, klo) - k0)];
     w[c][1] = pc[c][-plane];
     w[c][2] = pc[c][0];
-    w[c][3] = pc[c][plane * (min(k0 + 1, N2 - 1) - k0)];
+    w[c][3] = pc[c][plane * (min(k0 + 1, khi) - k0)];
   }
   float pend[3] = {0.f, 0.f, 0.f};
 
   for (int k = k0; k <= kend; ++k) {
     const bool lastp = k == kend;
-    const int kz = k == 1 ? (p2 ? 2 : 1) : (k == N2 - 1 ? (p2 ? 4 : 3) : 0);
+    const int kz = k == 1 ? (a.per.zlo ? 0 : (p2 ? 2 : 1)) : (k == N2 - 1 ? (a.per.zhi ? 0 : (p2 ? 4 : 3)) : 0);
     float nb[3][3][3];   // nb[c][d][m2,m1,p1]
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
@@ -178,7 +179,7 @@ __device__ __forceinline__ void mom3_body(const Mom3Args& a, float (*shy)[3][M3_
         r -= Fxu[ci]; r += F[ci][1]; r -= Fyu[ci]; r += F[ci][2];
         pend[ci] = r;
       }
-      const int dn = plane * (min(k + 2, N2 - 1) - k);
+      const int dn = plane * (min(k + 2, khi) - k);
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
         w[c][0] = w[c][1]; w[c][1] = w[c][2]; w[c][2] = w[c][3];
@@ -225,6 +226,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   const bool out_ij = lane < 31 && ty < M3_TY - 1 && (FAST || (i_raw <= N0 - 2 && j_raw <= N1 - 2));
   const int oij = i + pitch * j;
   const bool p0 = a.per.p[0] != 0, p1 = a.per.p[1] != 0, p2 = a.per.p[2] != 0;
+  const int klo = a.per.zlo ? -1 : 0, khi = a.per.zhi ? N2 : N2 - 1;   // readable plane range (slab halos)
   const int kx = FAST ? 0 : (i == 1 ? (p0 ? 2 : 1) : (i == N0 - 1 ? (p0 ? 4 : 3) : 0));
   const int ky = FAST ? 0 : (j == 1 ? (p1 ? 2 : 1) : (j == N1 - 1 ? (p1 ? 4 : 3) : 0));
   const float* U[3] = {a.ua, a.ua + l.cstride, a.ua + 2 * l.cstride};
@@ -235,7 +237,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   const int ga = min(max(i0 - 2 + pa % M3_TW, 0), N0 - 1) + pitch * min(max(j0 - 2 + pa / M3_TW, 0), N1 - 1);
   const int gb = has_b ? min(max(i0 - 2 + pb % M3_TW, 0), N0 - 1) + pitch * min(max(j0 - 2 + pb / M3_TW, 0), N1 - 1) : 0;
   auto stage = [&](int kp) {
-    const int kc = min(kp, N2 - 1);
+    const int kc = min(kp, khi);
     float(*slot)[M3_TILE] = sm.ring[kp & (M3_RING - 1)];
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
@@ -250,7 +252,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   float w[3][4];   // own column: planes k-2, k-1, k, k+1
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    w[c][0] = U[c][oij + plane * max(k0 - 2, 0)];
+    w[c][0] = U[c][oij + plane * max(k0 - 2, klo)];
     w[c][1] = U[c][oij + plane * (k0 - 1)];
   }
   cp_async_wait<1>();
@@ -264,7 +266,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
 
   for (int k = k0; k <= kend; ++k) {
     const bool lastp = k == kend;
-    const int kz = k == 1 ? (p2 ? 2 : 1) : (k == N2 - 1 ? (p2 ? 4 : 3) : 0);
+    const int kz = k == 1 ? (a.per.zlo ? 0 : (p2 ? 2 : 1)) : (k == N2 - 1 ? (a.per.zhi ? 0 : (p2 ? 4 : 3)) : 0);
     if (!lastp) { stage(k + 3); cp_async_commit(); }
     // operands of the finalisation of cell k-1: issued now, consumed after the fluxes
     float fu0[3], fV[3], fm0[3];
