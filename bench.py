@@ -44,25 +44,29 @@ def tgv3d(i, x, k):
     return 0 * x[0] * x[1] * x[2]
 
 
-def workload(name, size=None):
-    """-> (description, dims, uBC, L, kwargs, body dict or None, remeasure)   (SURVEY §8d)."""
+def workload(name, size=None, zmul=1):
+    """-> (description, dims, uBC, L, kwargs, body dict or None, remeasure)   (SURVEY §8d).
+    zmul stretches the last dimension (weak scaling: every GPU keeps the single-GPU slab)."""
     if name == "tgv":
         N = size or 128
         k = np.float32(2 * np.pi / N)
         kw = dict(perdir=(1, 2, 3), nu=float(1 / (k * 1600)), U=1.0, u0=lambda i, x: tgv3d(i, x, k))
-        return f"3D Taylor-Green vortex {N}^3 Float32 periodic Re=1600", (N, N, N), (0.0, 0.0, 0.0), float(N), kw, None, False
+        nz = N * zmul
+        return (f"3D Taylor-Green vortex {N}^3 Float32 periodic Re=1600" if zmul == 1 else
+                f"3D Taylor-Green vortex {N}x{N}x{nz} Float32 periodic Re=1600"), (N, N, nz), (0.0, 0.0, 0.0), float(N), kw, None, False
     if name == "sphere":
         m = size or 256
         R = m / 8
-        body = dict(kind="sphere", center=(m / 2 - 1,) * 3, radius=R)
+        body = dict(kind="sphere", center=(m / 2 - 1, m / 2 - 1, m * zmul / 2 - 1), radius=R)
         kw = dict(nu=2 * R / 3700)
-        return f"3D static sphere Re=3700 grid {2*m}x{m}x{m} BDIM", (2 * m, m, m), (1.0, 0.0, 0.0), 2 * R, kw, body, False
+        return f"3D static sphere Re=3700 grid {2*m}x{m}x{m*zmul} BDIM", (2 * m, m, m * zmul), (1.0, 0.0, 0.0), 2 * R, kw, body, False
     if name == "cylinder":
         m = size or 256
         R = m / 8
         body = dict(kind="cylinder", axis=2, center=(m, m, 0), radius=R, amp=(R, 0, 0), omega=2 * np.pi / (8 * R))
         kw = dict(nu=2 * R / 1000, U=1.0, perdir=(3,))
-        return f"3D moving cylinder remeasure grid {2*m}x{2*m}x{m}", (2 * m, 2 * m, m), (0.0, 0.0, 0.0), 2 * R, kw, body, True
+        return (f"3D moving cylinder remeasure grid {2*m}x{2*m}x{m*zmul}", (2 * m, 2 * m, m * zmul), (0.0, 0.0, 0.0), 2 * R,
+                kw, body, True)
     if name == "circle":
         n, m = 96, 64
         R = m / 8
@@ -185,6 +189,8 @@ def main():
     ap.add_argument("--workload", default="tgv")
     ap.add_argument("--size", type=int, default=None)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="N>1: weak = every GPU keeps the single-GPU grid (last dimension x N), strong = the same grid split N ways")
     ap.add_argument("--breakdown", default=None, help="write a per-kernel CUDA-event breakdown (3 extra steps) here")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -205,10 +211,12 @@ def main():
         dist.barrier()
     import waterlily_jl_b200 as wl
 
-    desc, dims, uBC, L, kw, body, remeasure = workload(args.workload, args.size)
+    # N>1: ONE simulation, slab-decomposed along the last dimension, one rank per GPU
+    desc, dims, uBC, L, kw, body, remeasure = workload(args.workload, args.size, world if args.scaling == "weak" else 1)
     D = len(dims)
-    cells = int(np.prod(dims))
-    sim = wl.Simulation(dims, uBC, L, body=wl.AutoBody(**body) if body else None, device=local, **kw)
+    cells = int(np.prod(dims))                       # whole job
+    comm = wl.make_slab_comm() if world > 1 else None
+    sim = wl.Simulation(dims, uBC, L, body=wl.AutoBody(**body) if body else None, device=local, comm=comm, **kw)
 
     def barrier():
         sim.sync()
@@ -244,7 +252,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         t_max = float(t.item())
     ms_per_step = t_max / args.steps
-    value = t_max * 1e6 / args.steps / (cells * world)     # ns per cell per step, whole job
+    value = t_max * 1e6 / args.steps / cells               # ns per cell per step, whole job
 
     # ---- roofline of the dominant kernel (live CUDA events inside the timed region)
     peak, peak_src = measured_peak()
@@ -253,7 +261,7 @@ def main():
         kn += n
         kms += ms
     balg = B_ALG[balg_key][D]
-    achieved = (balg * cells) / (kms / max(kn, 1) * 1e-3) / 1e9 if kn else None
+    achieved = (balg * cells / world) / (kms / max(kn, 1) * 1e-3) / 1e9 if kn else None     # per GPU (rank 0's kernel)
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": (achieved / peak) if achieved else None, "traffic": None,
                 "alg_bytes_per_cell": balg, "launches": kn, "avg_ms": kms / max(kn, 1), "peak_source": peak_src,
@@ -280,8 +288,8 @@ def main():
         t = torch.tensor([e2e_wall], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_wall = float(t.item())
-    e2e = {"value": e2e_wall / e2e_steps / (cells * world) * 1e9, "unit": "ns/cell/step",
-           "h2d_bytes_per_step": int(hu.nbytes + hp.nbytes), "d2h_bytes_per_step": int(hu.nbytes + hp.nbytes),
+    e2e = {"value": e2e_wall / e2e_steps / cells * 1e9, "unit": "ns/cell/step",
+           "h2d_bytes_per_step": int(hu.nbytes + hp.nbytes) * world, "d2h_bytes_per_step": int(hu.nbytes + hp.nbytes) * world,
            "steps": e2e_steps, "what": "upload u,p from pinned host + sim_step + download u,p"}
 
     # ---- optional per-kernel breakdown (outside the timed region)
@@ -300,6 +308,8 @@ def main():
             for name, (n, ms) in sorted(allp.items(), key=lambda kv: -kv[1][1]):
                 f.write(f"{name}\t{n}\t{ms:.4f}\t{ms / n * 1e3:.2f}\t{ms / ksum:.3f}\n")
 
+    halo = sim.halo_stats()
+    nsteps_total = len(sim.pois.n) // 2
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu_size = {"tgv": min(args.size or 128, 128), "sphere": 64, "cylinder": 64, "circle": None}[args.workload]
@@ -313,11 +323,14 @@ def main():
         line = {
             "metric": "ns_per_cell_per_step", "value": value, "unit": "ns/cell/step", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": False,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": desc, "cells_per_gpu": cells, "remeasure": remeasure,
-                       "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (slab decomposition: see DESIGN.md)",
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc, "cells": cells, "cells_per_gpu": cells // world, "remeasure": remeasure,
+                       "parallelism": "single GPU" if world == 1 else
+                       f"{world} slabs along the last dimension, NCCL halo exchange ({halo[0] // max(1, nsteps_total)} exchanges, "
+                       f"{halo[1] / max(1, nsteps_total) / 1e6:.1f} MB sent per rank per step), coarse levels replicated",
                        "poisson_iters_per_step": float(np.mean(n_iters)) * 2,
-                       "l2": "working set (%.0f MB) exceeds L2, no flush" % (30 * 4 * cells / 1e6) if cells > 1.5e6 else "fits L2"},
+                       "l2": "working set (%.0f MB per GPU) exceeds L2, no flush" % (30 * 4 * cells / world / 1e6)
+                             if cells / world > 1.5e6 else "fits L2"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
             "wall_ms_per_step": wall / args.steps * 1e3,
         }

@@ -53,7 +53,9 @@ int build_levels(wl_sim* s) {
     c.per = s->per_glob;
     if (f.dist) {
       const int nzf = f.lay.n2 - 2, nloc = c.c[2] ? nzf / 2 : nzf;
-      if (nloc >= s->dist.min_planes && nloc % 2 == 0) {
+      // small levels are launch/latency bound: solving them redundantly on every rank is cheaper than
+      // ~8 halo exchanges per level per V-cycle
+      if (nloc >= s->dist.min_planes && nloc % 2 == 0 && c.ncells > s->dist.min_cells) {
         c.dist = true;
         ng[2] = nloc + 2;
         c.per = s->per; c.koff = s->dist.rank * nloc; c.per.kz0 = c.koff;
@@ -131,6 +133,7 @@ static int create_impl(const wl_config* cfg, const wl_dist* dd, wl_sim** out) {
   s->per_glob = s->per;
   s->dist.rank = rank; s->dist.n = nranks; s->dist.nzg = cfg->N[2]; s->dist.nzl = cfg->N[2];
   if (const char* e = getenv("WL_DIST_MIN_PLANES")) s->dist.min_planes = std::max(2, atoi(e));
+  if (const char* e = getenv("WL_DIST_MIN_CELLS")) s->dist.min_cells = atoll(e);
   if (nranks > 1) {
     Dist& d = s->dist;
     const bool pz = s->per.p[2] != 0;

@@ -56,6 +56,7 @@ struct Dist {
   bool lo_wrap = false, hi_wrap = false;   // neighbour reached through the periodic wrap
   int nzg = 0, nzl = 0;                    // global / local interior planes
   int min_planes = 4;                      // levels with fewer local planes are replicated
+  long long min_cells = 1 << 20;           // ... and so are levels with at most this many cells in total
 };
 
 struct ProfRec { const char* name; cudaEvent_t a, b; };
