@@ -17,6 +17,7 @@
 #include "wl_kernels_mg2.cuh"
 #include "wl_kernels_mom.cuh"
 #include "wl_kernels_mom3.cuh"
+#include "wl_kernels_smooth.cuh"
 
 using namespace wl;
 
@@ -399,7 +400,50 @@ inline bool level_is_small(const Level& p) { return !p.dist && (long long)p.lay.
 // colour only reads the other colour, so this reproduces the single-domain sweep exactly); the
 // planes across a periodic wrap are sent once after the init and once before the increment, which
 // is when the reference's perBC!(ϵ) runs.
+// K-SMOOTH applies when no reference quirk outside its model is in play: 3D, even last dimension
+// (half_rangek sweeps every plane), even interior extent in periodic directions (colours continue
+// across the seam), and extents that the 5-cell halo cannot wrap twice.
+bool smooth_fusable(wl_sim* s, const Level& p) {
+  // opt-in (WL_FLAG_FUSED_SMOOTH or WL_FUSED_SMOOTH=1): bit-identical to the per-sweep kernels but, at
+  // ~620 issued instructions per thread and plane, not yet faster than them
+  static int env = -1;
+  if (env < 0) env = getenv("WL_FUSED_SMOOTH") ? 1 : 0;
+  if (!(env || (s->cfg.flags & WL_FLAG_FUSED_SMOOTH)) || s->D != 3 || p.dist) return false;
+  const Lay& l = p.lay;
+  if (l.n2 % 2 != 0 || l.n0 - 2 < 8 || l.n1 - 2 < 8 || l.n2 - 2 < 8) return false;
+  for (int d = 0; d < 3; ++d) if (p.per.p[d] && (l.n(d) - 2) % 2 != 0) return false;
+  return true;
+}
+int smooth_fused(wl_sim* s, Level& p, float w, Red* norms) {
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(k_smooth_fused<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SfSmem));
+    attr = true;
+  }
+  const Lay& l = p.lay;
+  SmoothFArgs a{};
+  a.p = levdev(p); a.rn = p.eps.base; a.per = p.per; a.omega = w;
+  a.w = s->redw; a.out = norms ? norms : s->d_red; a.want_norms = norms ? 1 : 0;
+  a.zh = 0; a.seam_zlo = a.seam_zhi = 0;
+  const int gx = (l.n0 - 2 + SF_TX - 1) / SF_TX, gy = (l.n1 - 2 + SF_TY - 1) / SF_TY;
+  int KZ = l.n2 - 2;
+  while (KZ > SF_MAXKZ) KZ = (KZ + 1) / 2;
+  // every z-chunk recomputes 10 warm-up planes: chunks of >= 32 planes, and only as many as fill the GPU once
+  while (KZ > 32 && (long long)gx * gy * ((l.n2 - 2 + KZ - 1) / KZ) < 148 * 2) KZ = (KZ + 1) / 2;
+  a.KZ = KZ;
+  dim3 g(gx, gy, (l.n2 - 2 + KZ - 1) / KZ);
+  {
+    cudaEvent_t pa_, pb_;
+    const bool prof_ = prof_pre(s, "k_smooth_fused<3>", &pa_, &pb_);
+    k_smooth_fused<3><<<g, SF_NT, sizeof(SfSmem), s->st>>>(a);
+    if (prof_) prof_post(s, "k_smooth_fused<3>", pa_, pb_);
+    ++s->launches;
+  }
+  std::swap(p.r, p.eps);                           // the new residual was staged in the idle ϵ array
+  return WL_OK;
+}
 int smooth2(wl_sim* s, Level& p, float w, Red* norms) {
+  if (smooth_fusable(s, p)) return smooth_fused(s, p, w, norms);
   SmArgs a{levdev(p), p.per, w, 0, s->redw, norms ? norms : s->d_red, norms ? 1 : 0};
   DISPATCH_D(s, k_eps_init_g, grid_inside(p.lay), blk(s->D), a);
   if (p.dist) { if (int e = halo(s, p.eps, 1, true)) return e; }
