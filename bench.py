@@ -293,7 +293,12 @@ def main():
            "steps": e2e_steps, "what": "upload u,p from pinned host + sim_step + download u,p"}
 
     # ---- optional per-kernel breakdown (outside the timed region)
-    if args.breakdown and rank == 0:
+    phases = None
+    if args.breakdown:                      # every rank steps (collective); rank 0 writes
+        sim.enable_timing(True)
+        sim.sim_step(remeasure=remeasure)
+        phases = [round(t * 1e3, 4) for t in sim.phase_times()[:5]]
+        sim.enable_timing(False)
         sim.prof_begin("")
         sim.event_record(2)
         for _ in range(3):
@@ -301,7 +306,9 @@ def main():
         sim.event_record(3)
         allp = sim.prof_end()
         tot = sim.event_elapsed_ms(2, 3)
-        with open(args.breakdown, "w") as f:
+        with open(args.breakdown if rank == 0 else os.devnull, "w") as f:
+            f.write(f"# phases of one step [ms]: predictor {phases[0]}, project {phases[1]}, corrector {phases[2]}, "
+                    f"project {phases[3]}, CFL {phases[4]}\n")
             f.write(f"# {desc}; 3 steps, {tot:.3f} ms total with per-launch events (events add overhead)\n")
             f.write("kernel\tlaunches\ttotal_ms\tavg_us\tshare_of_kernel_time\n")
             ksum = sum(ms for _, ms in allp.values())
@@ -326,7 +333,7 @@ def main():
             "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": desc, "cells": cells, "cells_per_gpu": cells // world, "remeasure": remeasure,
                        "parallelism": "single GPU" if world == 1 else
-                       f"{world} slabs along the last dimension, NCCL halo exchange ({halo[0] // max(1, nsteps_total)} exchanges, "
+                       f"{world} slabs along the last dimension, halo exchange by {sim.halo_transport()} ({halo[0] // max(1, nsteps_total)} exchanges, "
                        f"{halo[1] / max(1, nsteps_total) / 1e6:.1f} MB sent per rank per step), coarse levels replicated",
                        "poisson_iters_per_step": float(np.mean(n_iters)) * 2,
                        "l2": "working set (%.0f MB per GPU) exceeds L2, no flush" % (30 * 4 * cells / world / 1e6)

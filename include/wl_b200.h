@@ -105,6 +105,8 @@ int wl_nccl_unique_id(char id[128]);
 int wl_create_slab(const wl_config* cfg, const wl_dist* dist, wl_sim** out);
 int wl_slab_info(const wl_sim* s, int32_t* rank, int32_t* nranks, int32_t* k_offset, int32_t* n_local, int32_t* n_global);
 int wl_halo_stats(const wl_sim* s, int64_t* exchanges, int64_t* bytes);
+/* 0 single GPU, 1 NCCL send/recv, 2 direct peer stores over NVLink (CUDA IPC; WL_NO_P2P=1 disables) */
+int wl_halo_transport(const wl_sim* s);
 void wl_destroy(wl_sim* s);
 const char* wl_last_error(const wl_sim* s);   /* s may be NULL: last error of wl_create */
 int wl_version(void);

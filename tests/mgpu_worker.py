@@ -76,7 +76,9 @@ def run_case(wl, name, comm, dev):
         f1, f2 = one.pressure_force(), slab.pressure_force()
         out["force_err"] = float(np.abs(f1 - f2).max() / max(1.0, np.abs(f1).max()))
         ok = ok and out["force_err"] <= 1e-6
+    slab.sync()
     out["halo"] = slab.halo_stats()
+    out["transport"] = slab.halo_transport()
     out["ok"] = bool(ok)
     return out
 

@@ -37,7 +37,7 @@ ABI_SYMBOLS = [
     "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
     "wl_cfl", "wl_pressure_force", "wl_sync", "wl_launch_count", "wl_enable_timing",
     "wl_last_phase_times", "wl_debug_op", "wl_prof_begin", "wl_prof_end", "wl_event_record",
-    "wl_event_elapsed_ms", "wl_create_slab", "wl_nccl_unique_id", "wl_slab_info", "wl_halo_stats",
+    "wl_event_elapsed_ms", "wl_create_slab", "wl_nccl_unique_id", "wl_slab_info", "wl_halo_stats", "wl_halo_transport",
 ]
 
 
@@ -90,6 +90,7 @@ def load_library(path=None):
     lib.wl_nccl_unique_id.argtypes = [C.c_char_p]
     lib.wl_slab_info.argtypes = [P] + [C.POINTER(I)] * 5
     lib.wl_halo_stats.argtypes = [P, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    lib.wl_halo_transport.argtypes = [P]
     lib.wl_destroy.argtypes = [P]
     lib.wl_destroy.restype = None
     lib.wl_last_error.argtypes = [P]
@@ -455,6 +456,9 @@ class Simulation:
 
     def sync(self):
         self._check(self.lib.wl_sync(self.h))
+
+    def halo_transport(self):
+        return {0: "none", 1: "nccl", 2: "p2p"}.get(self.lib.wl_halo_transport(self.h), "?")
 
     def halo_stats(self):
         """(number of halo exchanges, bytes sent) since creation."""

@@ -20,6 +20,10 @@ int build_levels(wl_sim* s) {
   s->lv.clear();
   s->lv.reserve(s->cfg.maxlevels + 2);
   s->lv.emplace_back();
+  if (s->arena) {                               // level arrays are carved after the flow fields; a rebuild starts over
+    if (!s->arena_mark) s->arena_mark = s->arena_used;
+    s->arena_used = s->arena_mark;
+  }
   const int nr = s->dist.n;
   int gn[3] = {s->lay.n0, s->lay.n1, s->D == 3 ? s->dist.nzg + 2 : 1};   // global sizes incl. ghosts
   auto gcells = [&](const int* g) {
@@ -76,6 +80,78 @@ int build_levels(wl_sim* s) {
     if (int e = set_diag_h(s, co)) return e;
   }
   if (s->lv.size() <= 2) return fail(s, WL_ERR_INVALID, "MultiLevelPoisson requires size=a2^n, where n>2");
+  return WL_OK;
+}
+
+// Bytes the fields of a slab-decomposed sim need (same walk as create_impl + build_levels), so that
+// they can all be carved from ONE peer-mapped allocation.
+size_t plan_arena_bytes(wl_sim* s) {
+  auto fld = [](const Lay& l, int ncomp) { return (((size_t)l.cstride * ncomp * sizeof(float) + 256) + 255) & ~(size_t)255; };
+  const int D = s->D;
+  size_t tot = 4096;                                                    // flags
+  tot += fld(s->lay, D) * 6 + fld(s->lay, 1) * 2 + fld(s->lay, D * D);   // u,u0,f,V,mu0,w ; p,sigma ; mu1
+  tot += fld(s->lay, 1) * 4;                                            // level 0: r, eps, D, iD
+  int gn[3] = {s->lay.n0, s->lay.n1, s->dist.nzg + 2};
+  bool fdist = true;
+  int nzf = s->lay.n2 - 2;
+  int nlev = 1;
+  auto anydiv = [&]() { for (int d = 0; d < D; ++d) if (divisible(gn[d])) return true; return false; };
+  while (anydiv() && nlev <= s->cfg.maxlevels) {
+    int ng[3], c[3];
+    for (int d = 0; d < 3; ++d) { c[d] = d < D && divisible(gn[d]); ng[d] = c[d] ? 1 + gn[d] / 2 : gn[d]; }
+    for (int d = 0; d < 3; ++d) gn[d] = ng[d];
+    const long long cells = (long long)(gn[0] - 2) * (gn[1] - 2) * (gn[2] - 2);
+    bool cdist = false;
+    if (fdist) {
+      const int nloc = c[2] ? nzf / 2 : nzf;
+      if (nloc >= s->dist.min_planes && nloc % 2 == 0 && cells > s->dist.min_cells) { cdist = true; ng[2] = nloc + 2; nzf = nloc; }
+    }
+    fdist = cdist;
+    const Lay l = make_lay(D, ng);
+    tot += fld(l, D) + fld(l, 1) * 6;
+    ++nlev;
+  }
+  return tot + tot / 64 + (1 << 20);
+}
+
+// Allocate the arena, exchange its IPC handle with the slab neighbours and map theirs.
+int setup_p2p(wl_sim* s) {
+  if (getenv("WL_NO_P2P")) return WL_OK;
+  Dist& d = s->dist;
+  const size_t cap = plan_arena_bytes(s);
+  if (cudaMalloc(&s->arena, cap) != cudaSuccess) { cudaGetLastError(); s->arena = nullptr; return WL_OK; }   // fall back to NCCL halos
+  s->arena_cap = cap; s->arena_used = 4096;
+  cudaMemsetAsync(s->arena, 0, 4096, s->st);
+  cudaIpcMemHandle_t mine;
+  if (cudaIpcGetMemHandle(&mine, s->arena) != cudaSuccess) { cudaGetLastError(); return WL_OK; }
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  char* dbuf = nullptr;
+  WL_CUDA(s, cudaMalloc(&dbuf, 64 * (size_t)d.n));
+  WL_CUDA(s, cudaMemcpyAsync(dbuf + 64 * d.rank, &mine, 64, cudaMemcpyHostToDevice, s->st));
+  WL_NCCL(s, ncclAllGather(dbuf + 64 * d.rank, dbuf, 64, ncclChar, d.comm, s->st));
+  std::vector<cudaIpcMemHandle_t> all(d.n);
+  WL_CUDA(s, cudaMemcpyAsync(all.data(), dbuf, 64 * (size_t)d.n, cudaMemcpyDeviceToHost, s->st));
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  cudaFree(dbuf);
+  bool ok = true;
+  if (d.lo >= 0) ok = ok && cudaIpcOpenMemHandle((void**)&s->peer_lo, all[d.lo], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+  if (d.hi >= 0) {
+    if (d.hi == d.lo) s->peer_hi = s->peer_lo;
+    else ok = ok && cudaIpcOpenMemHandle((void**)&s->peer_hi, all[d.hi], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+  }
+  if (!ok) cudaGetLastError();
+  // every rank must agree on the transport (the flag protocol needs both ends): gather the verdicts
+  int* dv = nullptr;
+  WL_CUDA(s, cudaMalloc(&dv, sizeof(int) * (size_t)d.n));
+  const int v = ok ? 1 : 0;
+  WL_CUDA(s, cudaMemcpyAsync(dv + d.rank, &v, sizeof(int), cudaMemcpyHostToDevice, s->st));
+  WL_NCCL(s, ncclAllGather(dv + d.rank, dv, sizeof(int), ncclChar, d.comm, s->st));
+  std::vector<int> vs(d.n);
+  WL_CUDA(s, cudaMemcpyAsync(vs.data(), dv, sizeof(int) * (size_t)d.n, cudaMemcpyDeviceToHost, s->st));
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  cudaFree(dv);
+  s->p2p = true;
+  for (int q = 0; q < d.n; ++q) s->p2p = s->p2p && vs[q] == 1;
   return WL_OK;
 }
 
@@ -157,6 +233,7 @@ static int create_impl(const wl_config* cfg, const wl_dist* dd, wl_sim** out) {
   }
   s->lay = make_lay(cfg->D, ng, nranks > 1 ? 2 : 0);
   const int D = s->D;
+  if (nranks > 1) { if (int e2 = setup_p2p(s)) return bail(e2); }
   int e = 0;
   if ((e = alloc_field(s, s->u, s->lay, D)) || (e = alloc_field(s, s->u0, s->lay, D)) ||
       (e = alloc_field(s, s->f, s->lay, D)) || (e = alloc_field(s, s->p, s->lay, 1)) ||
@@ -232,6 +309,7 @@ int wl_slab_info(const wl_sim* s, int32_t* rank, int32_t* nranks, int32_t* k_off
   if (n_global) *n_global = s->dist.nzg;
   return WL_OK;
 }
+int wl_halo_transport(const wl_sim* s) { return s ? (s->dist.n > 1 ? (s->p2p ? 2 : 1) : 0) : -1; }
 int wl_halo_stats(const wl_sim* s, int64_t* exchanges, int64_t* bytes) {
   if (!s) return WL_ERR_INVALID;
   if (exchanges) *exchanges = s->halo_msgs;
@@ -243,6 +321,14 @@ void wl_destroy(wl_sim* s) {
   if (!s) return;
   cudaSetDevice(s->device);
   if (s->st) cudaStreamSynchronize(s->st);
+  if (s->arena) {
+    // no neighbour may still be storing into this arena: meet once before unmapping / freeing
+    if (s->dist.comm && s->d_redg) { ncclAllGather(s->d_red, s->d_redg, sizeof(Red) * NRED, ncclChar, s->dist.comm, s->st); cudaStreamSynchronize(s->st); }
+    if (s->peer_lo) cudaIpcCloseMemHandle(s->peer_lo);
+    if (s->peer_hi && s->peer_hi != s->peer_lo) cudaIpcCloseMemHandle(s->peer_hi);
+    cudaFree(s->arena);
+    s->arena = nullptr;
+  }
   if (s->dist.comm) ncclCommDestroy(s->dist.comm);
   if (s->d_redg) cudaFree(s->d_redg);
   if (s->h_redg) cudaFreeHost(s->h_redg);
@@ -562,6 +648,11 @@ int wl_sync(wl_sim* s) {
   if (!s) return WL_ERR_INVALID;
   cudaSetDevice(s->device);
   WL_CUDA(s, cudaStreamSynchronize(s->st));
+  if (s->p2p) {                                   // a halo kernel that gave up waiting for its neighbour
+    unsigned int err = 0;
+    WL_CUDA(s, cudaMemcpy(&err, s->arena + 5 * sizeof(unsigned int), sizeof(err), cudaMemcpyDeviceToHost));
+    if (err) return fail(s, WL_ERR_CUDA, "halo exchange timed out waiting for a neighbouring rank");
+  }
   return WL_OK;
 }
 int64_t wl_launch_count(const wl_sim* s) { return s ? s->launches : 0; }

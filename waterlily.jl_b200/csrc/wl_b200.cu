@@ -12,6 +12,7 @@
 #include "../../include/wl_b200.h"
 #include "wl_common.cuh"
 #include "wl_nccl.cuh"
+#include "wl_kernels_halo.cuh"
 #include "wl_kernels_body.cuh"
 #include "wl_kernels_mg.cuh"
 #include "wl_kernels_mg2.cuh"
@@ -31,6 +32,7 @@ struct DevField {
   Lay lay{};
   int ncomp = 0;
   size_t bytes = 0;
+  bool in_arena = false;   // carved from the sim's peer-mapped arena (slab decomposition): not freed one by one
 };
 
 struct Level {
@@ -71,6 +73,14 @@ struct wl_sim {
   Per per{};                  // what the kernels of the (local) fine grid see
   Per per_glob{};             // true periodicity of the global grid (replicated levels)
   Dist dist{};
+  // peer-mapped arena (slab decomposition): every rank carves the same fields at the same offsets, so
+  // a neighbour's copy of any field is peer_base + (ptr - arena).  Halo planes are then stored
+  // straight into the neighbour's ghost planes over NVLink (k_halo_p2p) instead of NCCL send/recv.
+  char* arena = nullptr;
+  size_t arena_cap = 0, arena_used = 0, arena_mark = 0;
+  char* peer_lo = nullptr; char* peer_hi = nullptr;   // neighbours' arenas mapped with cudaIpcOpenMemHandle
+  bool p2p = false;
+  unsigned int seq_lo = 0, seq_hi = 0;                // exchanges done on the lower / upper link
   Red* d_redg = nullptr;      // all-gathered reduction slots [rank][NRED]
   Red* h_redg = nullptr;
   int64_t halo_msgs = 0, halo_bytes = 0;
@@ -116,12 +126,24 @@ namespace {
 int alloc_field(wl_sim* s, DevField& f, const Lay& lay, int ncomp) {
   f.lay = lay; f.ncomp = ncomp;
   f.bytes = (size_t)lay.cstride * ncomp * sizeof(float) + 256;
-  WL_CUDA(s, cudaMalloc(&f.alloc, f.bytes));
+  if (s->arena) {
+    const size_t need = (f.bytes + 255) & ~(size_t)255;
+    if (s->arena_used + need > s->arena_cap) {
+      s->err = "peer arena exhausted (layout plan and allocation disagree)";
+      s->status = WL_ERR_CUDA;
+      return WL_ERR_CUDA;
+    }
+    f.alloc = reinterpret_cast<float*>(s->arena + s->arena_used);
+    s->arena_used += need;
+    f.in_arena = true;
+  } else {
+    WL_CUDA(s, cudaMalloc(&f.alloc, f.bytes));
+  }
   WL_CUDA(s, cudaMemsetAsync(f.alloc, 0, f.bytes, s->st));
   f.base = f.alloc + LPAD + (size_t)lay.zpad * lay.plane;
   return WL_OK;
 }
-void free_field(DevField& f) { if (f.alloc) cudaFree(f.alloc); f.alloc = f.base = nullptr; }
+void free_field(DevField& f) { if (f.alloc && !f.in_arena) cudaFree(f.alloc); f.alloc = f.base = nullptr; f.in_arena = false; }
 
 dim3 blk(int D) {
   static int bx = 0, by = 4, bz = 2;
@@ -223,6 +245,29 @@ int halo(wl_sim* s, const DevField& f, int depth, bool wrap = true) {
   const size_t cnt = (size_t)l.plane * depth;
   const bool use_lo = d.lo >= 0 && (wrap || !d.lo_wrap), use_hi = d.hi >= 0 && (wrap || !d.hi_wrap);
   if (!use_lo && !use_hi) return WL_OK;
+  s->halo_msgs += 1;
+  s->halo_bytes += (int64_t)cnt * 4 * f.ncomp * ((use_lo ? 1 : 0) + (use_hi ? 1 : 0));
+  if (s->p2p && f.in_arena && 2 * f.ncomp <= HALO_MAXSEG) {
+    // direct stores into the neighbours' ghost planes (wl_kernels_halo.cuh)
+    HaloP2PArgs a{};
+    auto peer = [&](char* pb, const float* mine) { return reinterpret_cast<float*>(pb + (reinterpret_cast<const char*>(mine) - s->arena)); };
+    for (int c = 0; c < f.ncomp; ++c) {
+      float* b = f.base + l.cstride * c;
+      if (use_lo) a.seg[a.nseg++] = HaloSeg{b + (size_t)l.plane * 1, peer(s->peer_lo, b + (size_t)l.plane * (l.n2 - 1))};
+      if (use_hi) a.seg[a.nseg++] = HaloSeg{b + (size_t)l.plane * (l.n2 - 1 - depth), peer(s->peer_hi, b + (ptrdiff_t)l.plane * (1 - depth))};
+    }
+    a.cnt = (long long)cnt;
+    a.my = reinterpret_cast<unsigned int*>(s->arena);
+    a.nb_lo = reinterpret_cast<unsigned int*>(s->peer_lo);
+    a.nb_hi = reinterpret_cast<unsigned int*>(s->peer_hi);
+    a.use_lo = use_lo; a.use_hi = use_hi;
+    if (use_lo) a.seq_lo = ++s->seq_lo;
+    if (use_hi) a.seq_hi = ++s->seq_hi;
+    long long nb = ((long long)cnt * a.nseg + 2047) / 2048;
+    nb = nb < 1 ? 1 : (nb > 296 ? 296 : nb);
+    LAUNCH(s, k_halo_p2p, dim3((unsigned)nb), dim3(256), a);
+    return WL_OK;
+  }
   WL_NCCL(s, ncclGroupStart());
   for (int c = 0; c < f.ncomp; ++c) {
     float* b = f.base + l.cstride * c;
@@ -234,8 +279,6 @@ int halo(wl_sim* s, const DevField& f, int depth, bool wrap = true) {
     if (use_lo) WL_NCCL(s, ncclRecv(b + (ptrdiff_t)l.plane * (1 - depth), cnt, ncclFloat, d.lo, d.comm, s->st));
   }
   WL_NCCL(s, ncclGroupEnd());
-  s->halo_msgs += 1;
-  s->halo_bytes += (int64_t)cnt * 4 * f.ncomp * ((use_lo ? 1 : 0) + (use_hi ? 1 : 0));
   return WL_OK;
 }
 // The reduction slots of all ranks, gathered so that every consumer folds them in rank order

@@ -1,0 +1,87 @@
+// wl_kernels_halo.cuh -- halo exchange between neighbouring slabs as direct stores into the
+// neighbour's memory (NVLink peer access through CUDA IPC), one kernel per exchange.
+//
+// Every rank carves its fields from an arena with the same layout, so the ghost plane that must
+// receive my boundary plane lives at the same offset in the neighbour's arena.  Per link (lower /
+// upper neighbour) two monotonically increasing flags live in the RECEIVER's arena:
+//    ready: "my ghost planes may be overwritten for exchange n"  (set when the rank's stream reaches
+//           exchange n, i.e. after every kernel that read the ghosts of exchange n-1)
+//    done : "exchange n has landed in your ghost planes"
+// The kernel announces ready, waits for the neighbours' ready, copies, fences, and its last block
+// raises the neighbours' done flags and waits for its own: when the kernel retires, the rank's ghost
+// planes are current.  ~2 NVLink round trips instead of an NCCL send/recv group (~18 µs measured).
+// All spins give up after 10 s and raise an error flag instead of hanging the GPU.
+#pragma once
+#include "wl_common.cuh"
+
+namespace wl {
+
+constexpr int HALO_MAXSEG = 8;
+struct HaloSeg { const float* src; float* dst; };
+struct HaloP2PArgs {
+  HaloSeg seg[HALO_MAXSEG];
+  int nseg;
+  long long cnt;                       // floats per segment
+  unsigned int* my;                    // local flags: [0] ready from lower, [1] ready from upper, [2] done from lower,
+                                       // [3] done from upper, [4] block ticket, [5] error
+  unsigned int* nb_lo;                 // lower neighbour's flag block (I am ITS upper neighbour: slots 1 and 3)
+  unsigned int* nb_hi;                 // upper neighbour's flag block (slots 0 and 2)
+  unsigned int seq_lo, seq_hi;
+  int use_lo, use_hi;
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long wl_now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// spin until *p has reached seq (wrap-safe); false on timeout
+__device__ __forceinline__ bool wait_flag(const unsigned int* p, unsigned int seq, unsigned int* err) {
+  const unsigned long long t0 = wl_now_ns();
+  while ((int)(ld_acquire_sys(p) - seq) < 0) {
+    if (wl_now_ns() - t0 > 10000000000ull) { atomicExch(err, 1u); return false; }
+    __nanosleep(20);
+  }
+  return true;
+}
+
+__global__ void __launch_bounds__(256) k_halo_p2p(const HaloP2PArgs a) {
+  __shared__ int last;
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    if (blockIdx.x == 0) {
+      if (a.use_lo) st_release_sys(a.nb_lo + 1, a.seq_lo);
+      if (a.use_hi) st_release_sys(a.nb_hi + 0, a.seq_hi);
+    }
+    if (a.use_lo) wait_flag(a.my + 0, a.seq_lo, a.my + 5);
+    if (a.use_hi) wait_flag(a.my + 1, a.seq_hi, a.my + 5);
+  }
+  __syncthreads();
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (int sgi = 0; sgi < a.nseg; ++sgi) {
+    const float* __restrict__ src = a.seg[sgi].src;
+    float* __restrict__ dst = a.seg[sgi].dst;
+    for (long long e = (long long)blockIdx.x * blockDim.x + tid; e < a.cnt; e += stride) dst[e] = src[e];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (tid == 0) last = atomicAdd(a.my + 4, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!last || tid != 0) return;
+  a.my[4] = 0u;
+  __threadfence_system();
+  if (a.use_lo) st_release_sys(a.nb_lo + 3, a.seq_lo);
+  if (a.use_hi) st_release_sys(a.nb_hi + 2, a.seq_hi);
+  if (a.use_lo) wait_flag(a.my + 2, a.seq_lo, a.my + 5);
+  if (a.use_hi) wait_flag(a.my + 3, a.seq_hi, a.my + 5);
+}
+
+}  // namespace wl
