@@ -44,15 +44,15 @@ def tgv3d(i, x, k):
     return 0 * x[0] * x[1] * x[2]
 
 
-def workload(name, size=None, zmul=1):
+def workload(name, size=None, zmul=1, nz=None):
     """-> (description, dims, uBC, L, kwargs, body dict or None, remeasure)   (SURVEY §8d).
     zmul stretches the last dimension (weak scaling: every GPU keeps the single-GPU slab)."""
     if name == "tgv":
         N = size or 128
         k = np.float32(2 * np.pi / N)
         kw = dict(perdir=(1, 2, 3), nu=float(1 / (k * 1600)), U=1.0, u0=lambda i, x: tgv3d(i, x, k))
-        nz = N * zmul
-        return (f"3D Taylor-Green vortex {N}^3 Float32 periodic Re=1600" if zmul == 1 else
+        nz = (nz or N) * zmul
+        return (f"3D Taylor-Green vortex {N}^3 Float32 periodic Re=1600" if nz == N else
                 f"3D Taylor-Green vortex {N}x{N}x{nz} Float32 periodic Re=1600"), (N, N, nz), (0.0, 0.0, 0.0), float(N), kw, None, False
     if name == "sphere":
         m = size or 256
@@ -188,6 +188,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default="tgv")
     ap.add_argument("--size", type=int, default=None)
+    ap.add_argument("--nz", type=int, default=None, help="tgv: planes per GPU in the last dimension (default: size)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N>1: weak = every GPU keeps the single-GPU grid (last dimension x N), strong = the same grid split N ways")
@@ -212,7 +213,7 @@ def main():
     import waterlily_jl_b200 as wl
 
     # N>1: ONE simulation, slab-decomposed along the last dimension, one rank per GPU
-    desc, dims, uBC, L, kw, body, remeasure = workload(args.workload, args.size, world if args.scaling == "weak" else 1)
+    desc, dims, uBC, L, kw, body, remeasure = workload(args.workload, args.size, world if args.scaling == "weak" else 1, args.nz)
     D = len(dims)
     cells = int(np.prod(dims))                       # whole job
     comm = wl.make_slab_comm() if world > 1 else None

@@ -491,9 +491,11 @@ int smooth2(wl_sim* s, Level& p, float w, Red* norms) {
   DISPATCH_D(s, k_eps_init_g, grid_inside(p.lay), blk(s->D), a);
   if (p.dist) { if (int e = halo(s, p.eps, 1, true)) return e; }
   LevArgs g = lev_args(s, p);
+  dim3 gg = grid_inside(p.lay);
+  gg.x = (p.lay.n0 - 2 + 2 * blk(s->D).x - 1) / (2 * blk(s->D).x);   // colour-compacted: a thread per x-pair
   for (int k0 = 1; k0 <= 4; ++k0) {
     g.k0 = k0;
-    DISPATCH_D(s, k_gs_half, grid_inside(p.lay), blk(s->D), g);
+    DISPATCH_D(s, k_gs_half_c, gg, blk(s->D), g);
     if (p.dist) { if (int e = halo(s, p.eps, 1, k0 == 4)) return e; }
   }
   DISPATCH_D(s, k_increment_w, grid_tiles(p.lay, false), blk(s->D), a);

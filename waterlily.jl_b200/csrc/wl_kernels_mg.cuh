@@ -161,6 +161,39 @@ __global__ void __launch_bounds__(256) k_gs_half(const LevArgs a) {
   a.eps[o] = s * inv_or_zero(dg);
 }
 
+// The same half sweep with the threads COMPACTED onto the colour being updated: thread tx owns the
+// x-pair (2tx+1, 2tx+2) of its row and updates the member of the sweep's colour, so every lane of a
+// warp does work (the one-thread-per-cell version idles half of them and is issue-bound).
+// gridDim.x = ceil((n0-2)/64).  Same arithmetic, same order: bit-identical.
+template <int D>
+__global__ void __launch_bounds__(256) k_gs_half_c(const LevArgs a) {
+  const Lay& l = a.l;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;
+  const int i = 1 + 2 * (blockIdx.x * blockDim.x + threadIdx.x) + ((j + k + D + a.k0) & 1);
+  if (i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && k > l.n2 - 2)) return;
+  const int nl = D == 3 ? l.n2 : l.n1;
+  const int cl = D == 3 ? k : j;
+  if (cl > 2 * (nl / 2) - 2) return;
+  const int o = l.off(i, j, k);
+  const int st[3] = {1, l.pitch, l.plane};
+  float lo[3], hi[3], em[3], ep[3];
+  const float r0 = a.r[o];
+#pragma unroll
+  for (int q = 0; q < D; ++q) {                      // every load before the first use: one memory round trip
+    const float* Lq = a.L + l.cstride * q;
+    lo[q] = Lq[o]; hi[q] = Lq[o + st[q]];
+    em[q] = a.eps[o - st[q]]; ep[q] = a.eps[o + st[q]];
+  }
+  float s = r0, dg = 0.f;
+#pragma unroll
+  for (int q = 0; q < D; ++q) {
+    dg -= lo[q] + hi[q];
+    s -= em[q] * lo[q] + ep[q] * hi[q];
+  }
+  a.eps[o] = s * inv_or_zero(dg);
+}
+
 // restrict! (MultiLevelPoisson.jl:13-19,49): coarse r = Σ fine children, first dim fastest.
 struct XferArgs { Lay lf, lc; const float* src; float* dst; int c[3]; };
 template <int D>
