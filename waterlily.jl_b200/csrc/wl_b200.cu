@@ -147,9 +147,9 @@ void free_field(DevField& f) { if (f.alloc && !f.in_arena) cudaFree(f.alloc); f.
 
 dim3 blk(int D) {
   static int bx = 0, by = 4, bz = 2;
-  if (!bx) {   // WL_BLK3="bx,by,bz" overrides the 3D interior tile (experiments); bx*by*bz must be 256, bz even
+  if (!bx) {   // WL_BLK3="bx,by,bz" overrides the 3D interior tile (experiments); bx*by*bz must be 256, by and bz even (K-DOWN keeps the children of a coarse cell in one block)
     bx = 32;
-    if (const char* e = getenv("WL_BLK3")) { int a, b, c; if (sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a * b * c == 256 && a % 32 == 0 && c % 2 == 0) { bx = a; by = b; bz = c; } }
+    if (const char* e = getenv("WL_BLK3")) { int a, b, c; if (sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a * b * c == 256 && a % 32 == 0 && b % 2 == 0 && c % 2 == 0) { bx = a; by = b; bz = c; } }
   }
   return D == 3 ? dim3(bx, by, bz) : dim3(32, 8, 1);
 }

@@ -28,16 +28,46 @@ struct LevDev {
   int c[3];          // coarsening mask from the next finer level to this one
 };
 
-// offsets of the lower/upper neighbour in direction d for an INTERIOR cell, wrapped when periodic
-template <int D>
+// offsets of the lower/upper neighbour in direction d for an INTERIOR cell, wrapped when periodic.
+// EDGE=false: the caller knows that no cell of its tile sits next to a periodic seam, so the
+// offsets are the plain strides (no compares/selects: these kernels are issue-bound, not HBM-bound).
+template <int D, bool EDGE = true>
 __device__ __forceinline__ void nbr_off(const Lay& l, const Per& per, int i, int j, int k, int* om, int* op) {
   const int c[3] = {i, j, k};
   const int N[3] = {l.n0, l.n1, l.n2};
   const int st[3] = {1, l.pitch, l.plane};
 #pragma unroll
   for (int d = 0; d < D; ++d) {
-    om[d] = (per.p[d] && c[d] == 1) ? (N[d] - 3) * st[d] : -st[d];
-    op[d] = (per.p[d] && c[d] == N[d] - 2) ? -(N[d] - 3) * st[d] : st[d];
+    om[d] = (EDGE && per.p[d] && c[d] == 1) ? (N[d] - 3) * st[d] : -st[d];
+    op[d] = (EDGE && per.p[d] && c[d] == N[d] - 2) ? -(N[d] - 3) * st[d] : st[d];
+  }
+}
+// does the tile of blockDim cells whose first interior cell is (i0,j0,k0) touch a periodic seam?
+template <int D>
+__device__ __forceinline__ bool tile_on_seam(const Lay& l, const Per& per, int i0, int j0, int k0) {
+  bool e = false;
+  if (per.p[0]) e |= i0 == 1 || i0 + (int)blockDim.x > l.n0 - 2;
+  if (per.p[1]) e |= j0 == 1 || j0 + (int)blockDim.y > l.n1 - 2;
+  if (D == 3 && per.p[2]) e |= k0 == 1 || k0 + (int)blockDim.z > l.n2 - 2;
+  return e;
+}
+// for_tiles_inside with the seam decision made once per tile: f(i,j,k,EdgeYes/EdgeNo)
+template <int D, class F>
+__device__ __forceinline__ void for_tiles_seam(const Lay& l, const Per& per, F f);
+struct EdgeYes { static constexpr bool value = true; };
+struct EdgeNo { static constexpr bool value = false; };
+template <int D, class F>
+__device__ __forceinline__ void for_tiles_seam(const Lay& l, const Per& per, F f) {
+  const int nbx = (l.n0 - 2 + blockDim.x - 1) / blockDim.x, nby = (l.n1 - 2 + blockDim.y - 1) / blockDim.y;
+  const int nbz = D == 3 ? (l.n2 - 2 + blockDim.z - 1) / blockDim.z : 1;
+  const int nt = nbx * nby * nbz;
+  for (int t = blockIdx.x; t < nt; t += gridDim.x) {
+    const int tx = t % nbx, q = t / nbx, ty = q % nby, tz = q / nby;
+    const int i0 = tx * blockDim.x + 1, j0 = ty * blockDim.y + 1, k0 = D == 3 ? tz * blockDim.z + 1 : 0;
+    const int i = i0 + threadIdx.x, j = j0 + threadIdx.y, k = D == 3 ? k0 + threadIdx.z : 0;
+    const bool in = i <= l.n0 - 2 && j <= l.n1 - 2 && (D == 2 || k <= l.n2 - 2);
+    if (tile_on_seam<D>(l, per, i0, j0, k0)) { if (in) f(i, j, k, EdgeYes{}); }
+    else if (in) f(i, j, k, EdgeNo{});
   }
 }
 // store v into every periodic image (ghost copy) of interior cell (i,j,k): what the sequential
@@ -99,24 +129,31 @@ template <int D>
 __global__ void __launch_bounds__(256) k_divres(const DivResArgs a) {
   const Lay& l = a.l;
   double s = 0.0;
-  for_tiles_inside<D>(l, [&](int i, int j, int k) {
+  for_tiles_seam<D>(l, a.per, [&](int i, int j, int k, auto edge) {
+    constexpr bool EDGE = decltype(edge)::value;
     const int o = l.off(i, j, k);
     const int st[3] = {1, l.pitch, l.plane};
     int om[3], op[3];
-    nbr_off<D>(l, a.per, i, j, k, om, op);
-    float z = 0.f;
+    nbr_off<D, EDGE>(l, a.per, i, j, k, om, op);
+    float u0[3], u1[3], L0[3], L1[3], xm[3], xp[3];
+    const float x0 = __ldg(a.x + o);
 #pragma unroll
-    for (int d = 0; d < D; ++d) { const float* ud = a.u + l.cstride * d; z += ud[o + st[d]] - ud[o]; }
-    const float dg = diagL<D>(l, a.L, o);
-    const float xc = a.x[o] * a.dt;
+    for (int d = 0; d < D; ++d) {                    // every load before the first use
+      const float* ud = a.u + l.cstride * d;
+      const float* Ld = a.L + l.cstride * d;
+      u0[d] = __ldg(ud + o); u1[d] = __ldg(ud + o + st[d]);
+      L0[d] = __ldg(Ld + o); L1[d] = __ldg(Ld + o + st[d]);
+      xm[d] = __ldg(a.x + o + om[d]); xp[d] = __ldg(a.x + o + op[d]);
+    }
+    float z = 0.f, dg = 0.f;
+#pragma unroll
+    for (int d = 0; d < D; ++d) { z += u1[d] - u0[d]; dg -= L0[d] + L1[d]; }
+    const float xc = x0 * a.dt;
     float r = 0.f;
     if (dg != 0.f) {
       float ax = xc * dg;
 #pragma unroll
-      for (int d = 0; d < D; ++d) {
-        const float* Ld = a.L + l.cstride * d;
-        ax += (a.x[o + om[d]] * a.dt) * Ld[o] + (a.x[o + op[d]] * a.dt) * Ld[o + st[d]];
-      }
+      for (int d = 0; d < D; ++d) ax += (xm[d] * a.dt) * L0[d] + (xp[d] * a.dt) * L1[d];
       r = z - ax;
     }
     a.r[o] = r;
@@ -139,26 +176,38 @@ __global__ void __launch_bounds__(256) k_down(const DownArgs a) {
   WL_IJK_FROM_BLOCK(D, l)
   const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
   float rn = 0.f;
-  if (inb) {
+  auto body = [&](auto edge) {
+    constexpr bool EDGE = decltype(edge)::value;
     const int o = l.off(i, j, k);
     const int st[3] = {1, l.pitch, l.plane};
     int om[3], op[3];
-    nbr_off<D>(l, a.per, i, j, k, om, op);
-    const float r0 = a.f.r[o], x0 = a.f.x[o];                        // all reads before the first store
-    const float e0 = r0 * a.f.iD[o];                                  // ϵ = r·iD  Poisson.jl:112
-    float s = e0 * diagL<D>(l, a.f.L, o);                              // mult(I,L,D,ϵ)
+    nbr_off<D, EDGE>(l, a.per, i, j, k, om, op);
+    float L0[3], L1[3], rm[3], rp[3], dm[3], dp[3];
+    const float r0 = a.f.r[o], x0 = a.f.x[o], d0 = __ldg(a.f.iD + o);   // all reads before the first store
 #pragma unroll
     for (int d = 0; d < D; ++d) {
       const float* Ld = a.f.L + l.cstride * d;
-      const float em = a.f.r[o + om[d]] * a.f.iD[o + om[d]];
-      const float ep = a.f.r[o + op[d]] * a.f.iD[o + op[d]];
-      s += em * Ld[o] + ep * Ld[o + st[d]];
+      L0[d] = __ldg(Ld + o); L1[d] = __ldg(Ld + o + st[d]);
+      rm[d] = a.f.r[o + om[d]]; dm[d] = __ldg(a.f.iD + o + om[d]);
+      rp[d] = a.f.r[o + op[d]]; dp[d] = __ldg(a.f.iD + o + op[d]);
     }
+    const float e0 = r0 * d0;                                          // ϵ = r·iD  Poisson.jl:112
+    float dg = 0.f;
+#pragma unroll
+    for (int d = 0; d < D; ++d) dg -= L0[d] + L1[d];
+    float s = e0 * dg;                                                 // mult(I,L,D,ϵ)
+#pragma unroll
+    for (int d = 0; d < D; ++d) s += (rm[d] * dm[d]) * L0[d] + (rp[d] * dp[d]) * L1[d];
     rn = r0 - s;                                                       // increment!, ω = 1  Poisson.jl:102
     // r is still being read by the neighbours' ϵ: the new residual goes to the idle ϵ array and
     // the host swaps the two pointers afterwards
     a.f.eps[o] = rn;
     a.f.x[o] = x0 + e0;                                                // Poisson.jl:103
+  };
+  if (inb) {
+    if (tile_on_seam<D>(l, a.per, (int)(blockIdx.x * blockDim.x) + 1, (int)(blockIdx.y * blockDim.y) + 1,
+                        D == 3 ? (int)(blockIdx.z * blockDim.z) + 1 : 0)) body(EdgeYes{});
+    else body(EdgeNo{});
   }
   tile[tid] = rn;
   __syncthreads();
@@ -189,36 +238,57 @@ __global__ void __launch_bounds__(256) k_up(const UpArgs a) {
   const Lay& l = a.f.l;
   WL_IJK_FROM_BLOCK(D, l)
   double s1 = 0.0; float m = -INFINITY;
-  if (inb) {
+  auto body = [&](auto edge) {
+    constexpr bool EDGE = decltype(edge)::value;
     const int o = l.off(i, j, k);
     const int st[3] = {1, l.pitch, l.plane};
     const int c[3] = {i, j, k};
     const int N[3] = {l.n0, l.n1, l.n2};
     const int cst[3] = {1, a.c.l.pitch, a.c.l.plane};
-    // coarse coordinate of the cell and of its (periodically wrapped) neighbours: down(I,c) MLP.jl:7
-    int cc[3], ccm[3], ccp[3];
+    // coarse cell of this cell and of its (periodically wrapped) neighbours: down(I,c) MLP.jl:7.
+    // Away from a seam the lower neighbour of an odd index and the upper neighbour of an even index
+    // share the cell's own parent.
+    int oc = 0, dm[3], dp[3];
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
-      const bool co = d < D && a.c.c[d];
-      const int xm = (d < D && a.per.p[d] && c[d] == 1) ? N[d] - 2 : c[d] - 1;
-      const int xp = (d < D && a.per.p[d] && c[d] == N[d] - 2) ? 1 : c[d] + 1;
-      cc[d] = co ? (c[d] + 1) / 2 : c[d];
-      ccm[d] = co ? (xm + 1) / 2 : xm;
-      ccp[d] = co ? (xp + 1) / 2 : xp;
+      if (d >= D) { dm[d] = dp[d] = 0; continue; }
+      const bool co = a.c.c[d] != 0;
+      const int cc = co ? (c[d] + 1) >> 1 : c[d];
+      oc += cc * cst[d];
+      if (EDGE) {
+        const int xm = (a.per.p[d] && c[d] == 1) ? N[d] - 2 : c[d] - 1;
+        const int xp = (a.per.p[d] && c[d] == N[d] - 2) ? 1 : c[d] + 1;
+        dm[d] = ((co ? (xm + 1) >> 1 : xm) - cc) * cst[d];
+        dp[d] = ((co ? (xp + 1) >> 1 : xp) - cc) * cst[d];
+      } else {
+        dm[d] = co ? -(c[d] & 1) * cst[d] : -cst[d];
+        dp[d] = co ? ((c[d] & 1) ^ 1) * cst[d] : cst[d];
+      }
     }
-    const int oc = a.c.l.off(cc[0], cc[1], cc[2]);
-    const float e0 = a.c.x[oc];
+    float L0[3], L1[3], em[3], ep[3];
+    const float e0 = __ldg(a.c.x + oc);
     const float r0 = a.f.r[o], x0 = a.f.x[o];            // all reads before the first store
-    float s = e0 * diagL<D>(l, a.f.L, o);
 #pragma unroll
     for (int d = 0; d < D; ++d) {
       const float* Ld = a.f.L + l.cstride * d;
-      s += a.c.x[oc + (ccm[d] - cc[d]) * cst[d]] * Ld[o] + a.c.x[oc + (ccp[d] - cc[d]) * cst[d]] * Ld[o + st[d]];
+      L0[d] = __ldg(Ld + o); L1[d] = __ldg(Ld + o + st[d]);
+      em[d] = __ldg(a.c.x + oc + dm[d]); ep[d] = __ldg(a.c.x + oc + dp[d]);
     }
+    float dg = 0.f;
+#pragma unroll
+    for (int d = 0; d < D; ++d) dg -= L0[d] + L1[d];
+    float s = e0 * dg;
+#pragma unroll
+    for (int d = 0; d < D; ++d) s += em[d] * L0[d] + ep[d] * L1[d];
     const float r = r0 - a.omega * s;
     a.f.r[o] = r;
     a.f.x[o] = x0 + a.omega * e0;
     s1 = (double)fabsf(r); m = fabsf(r);
+  };
+  if (inb) {
+    if (tile_on_seam<D>(l, a.per, (int)(blockIdx.x * blockDim.x) + 1, (int)(blockIdx.y * blockDim.y) + 1,
+                        D == 3 ? (int)(blockIdx.z * blockDim.z) + 1 : 0)) body(EdgeYes{});
+    else body(EdgeNo{});
   }
   if (a.want_norms) block_reduce_finish(s1, m, a.w, a.out);
 }
@@ -233,9 +303,11 @@ __global__ void __launch_bounds__(256) k_eps_init_g(const SmArgs a) {
   WL_IJK_FROM_BLOCK(D, l)
   if (!inb) return;
   const int o = l.off(i, j, k);
-  const float e = a.p.r[o] * a.p.iD[o];
+  const float e = a.p.r[o] * __ldg(a.p.iD + o);
   a.p.eps[o] = e;
-  store_images<D>(a.p.eps, l, a.per, i, j, k, e);
+  if (tile_on_seam<D>(l, a.per, (int)(blockIdx.x * blockDim.x) + 1, (int)(blockIdx.y * blockDim.y) + 1,
+                      D == 3 ? (int)(blockIdx.z * blockDim.z) + 1 : 0))
+    store_images<D>(a.p.eps, l, a.per, i, j, k, e);
 }
 // increment! (Poisson.jl:100-104) with the perBC!(ϵ) folded into wrap-reads; optional L₁/L∞ of the new r
 template <int D>
@@ -244,12 +316,27 @@ __global__ void __launch_bounds__(256) k_increment_w(const SmArgs a) {
   double s1 = 0.0; float m = -INFINITY;
   // 1-D persistent grid (see for_tiles_inside); every read is issued before the first store so the
   // thread pays ONE memory round trip (r, x, ϵ may alias as far as the compiler knows)
-  for_tiles_inside<D>(l, [&](int i, int j, int k) {
+  for_tiles_seam<D>(l, a.per, [&](int i, int j, int k, auto edge) {
+    constexpr bool EDGE = decltype(edge)::value;
     const int o = l.off(i, j, k);
+    const int st[3] = {1, l.pitch, l.plane};
     int om[3], op[3];
-    nbr_off<D>(l, a.per, i, j, k, om, op);
+    nbr_off<D, EDGE>(l, a.per, i, j, k, om, op);
+    float L0[3], L1[3], em[3], ep[3];
     const float r0 = a.p.r[o], x0 = a.p.x[o], e0 = a.p.eps[o];
-    const float r = r0 - a.omega * multA_w<D>(l, a.p.L, a.p.eps, o, om, op);
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+      const float* Ld = a.p.L + l.cstride * d;
+      L0[d] = __ldg(Ld + o); L1[d] = __ldg(Ld + o + st[d]);
+      em[d] = a.p.eps[o + om[d]]; ep[d] = a.p.eps[o + op[d]];
+    }
+    float dg = 0.f;
+#pragma unroll
+    for (int d = 0; d < D; ++d) dg -= L0[d] + L1[d];
+    float s = e0 * dg;                                       // mult(I,L,D,ϵ)  Poisson.jl:70-76
+#pragma unroll
+    for (int d = 0; d < D; ++d) s += em[d] * L0[d] + ep[d] * L1[d];
+    const float r = r0 - a.omega * s;
     a.p.r[o] = r;
     a.p.x[o] = x0 + a.omega * e0;
     s1 += (double)fabsf(r); m = fmaxf(m, fabsf(r));
@@ -267,20 +354,23 @@ __global__ void __launch_bounds__(256) k_proj(const ProjArgs2 a) {
   WL_IJK_FROM_BLOCK(D, l)
   if (!inb) return;
   const int o = l.off(i, j, k);
+  const bool edge = tile_on_seam<D>(l, a.per, (int)(blockIdx.x * blockDim.x) + 1, (int)(blockIdx.y * blockDim.y) + 1,
+                                    D == 3 ? (int)(blockIdx.z * blockDim.z) + 1 : 0);
   int om[3], op[3];
-  nbr_off<D>(l, a.per, i, j, k, om, op);
-  const float xc = a.x[o];
+  if (edge) nbr_off<D, true>(l, a.per, i, j, k, om, op);
+  else nbr_off<D, false>(l, a.per, i, j, k, om, op);
+  const float xc = __ldg(a.x + o);
   float uv[3], Lv[3], xm[3];
 #pragma unroll
   for (int d = 0; d < D; ++d) {                              // all reads first: one memory round trip
     const long long oc = l.cstride * d + o;
-    uv[d] = a.u[oc]; Lv[d] = a.L[oc]; xm[d] = a.x[o + om[d]];
+    uv[d] = a.u[oc]; Lv[d] = __ldg(a.L + oc); xm[d] = __ldg(a.x + o + om[d]);
   }
 #pragma unroll
   for (int d = 0; d < D; ++d) a.u[l.cstride * d + o] = uv[d] - Lv[d] * (xc - xm[d]);
   const float p = xc / a.dt;
   a.pn[o] = p;
-  store_images<D>(a.pn, l, a.per, i, j, k, p);
+  if (edge) store_images<D>(a.pn, l, a.per, i, j, k, p);
 }
 
 // ---------------------------------------------------------------- all small levels in one block

@@ -370,23 +370,48 @@ template <int D>
 __global__ void __launch_bounds__(256) k_cfl(const CflArgs a) {
   const Lay& l = a.l;
   float m = -INFINITY;
-  for_tiles_all<D>(l, [&](int i, int j, int k) {               // 1-D persistent grid
-    const int o = l.off(i, j, k);
-    const bool in = i >= 1 && i <= l.n0 - 2 && j >= 1 && j <= l.n1 - 2 && (D == 2 || (k >= 1 && k <= l.n2 - 2));
-    if (in) {
-      const int st[3] = {1, l.pitch, l.plane};
-      float s = 0.f;
+  // 1-D persistent grid over ALL cells, four tiles per trip with their loads issued together (see
+  // k_shift_norms): the loop is otherwise latency-bound
+  const int nbx = (l.n0 + LPAD + blockDim.x - 1) / blockDim.x, nby = (l.n1 + blockDim.y - 1) / blockDim.y;
+  const int nbz = D == 3 ? (l.n2 + blockDim.z - 1) / blockDim.z : 1;
+  const int nt = nbx * nby * nbz;
+  const int st[3] = {1, l.pitch, l.plane};
+  for (int t0 = blockIdx.x; t0 < nt; t0 += 4 * gridDim.x) {
+    int o[4]; int cls[4];          // 0 skip, 1 interior, 2 ghost that takes part in the max
+    float lo[4][3], hi[4][3], sg[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int t = t0 + u * gridDim.x;
+      const int tx = t % nbx, q = t / nbx, ty = q % nby, tz = q / nby;
+      const int i = tx * blockDim.x + threadIdx.x - LPAD, j = ty * blockDim.y + threadIdx.y;
+      const int k = D == 3 ? tz * blockDim.z + threadIdx.z : 0;
+      const bool have = t < nt && i >= 0 && i < l.n0 && j < l.n1 && k < l.n2;
+      const bool in = i >= 1 && i <= l.n0 - 2 && j >= 1 && j <= l.n1 - 2 && (D == 2 || (k >= 1 && k <= l.n2 - 2));
+      // slab interfaces: the planes beyond them belong to the neighbour
+      const bool mine = !(D == 3 && ((a.zlo && k == 0) || (a.zhi && k == l.n2 - 1)));
+      cls[u] = !have ? 0 : (in ? 1 : (mine ? 2 : 0));
+      o[u] = have ? l.off(i, j, k) : l.off(1, 1, D == 3 ? 1 : 0);
+      const int oi = cls[u] == 1 ? o[u] : l.off(1, 1, D == 3 ? 1 : 0);
 #pragma unroll
       for (int d = 0; d < D; ++d) {
         const float* ud = a.u + l.cstride * d;
-        s += fmaxf(0.f, ud[o + st[d]]) + fmaxf(0.f, -ud[o]);
+        lo[u][d] = ud[oi]; hi[u][d] = ud[oi + st[d]];
       }
-      a.sigma[o] = s;
-      m = fmaxf(m, s);
-    } else if (!(D == 3 && ((a.zlo && k == 0) || (a.zhi && k == l.n2 - 1)))) {   // interface planes belong to the neighbour
-      m = fmaxf(m, a.sigma[o]);
+      sg[u] = cls[u] == 2 ? a.sigma[o[u]] : 0.f;
     }
-  });
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (cls[u] == 1) {
+        float s = 0.f;
+#pragma unroll
+        for (int d = 0; d < D; ++d) s += fmaxf(0.f, hi[u][d]) + fmaxf(0.f, -lo[u][d]);
+        a.sigma[o[u]] = s;
+        m = fmaxf(m, s);
+      } else if (cls[u] == 2) {
+        m = fmaxf(m, sg[u]);
+      }
+    }
+  }
   block_reduce_finish(0.0, m, a.w, a.out);
 }
 
