@@ -485,10 +485,10 @@ int smooth_fused(wl_sim* s, Level& p, float w, Red* norms) {
   std::swap(p.r, p.eps);                           // the new residual was staged in the idle ϵ array
   return WL_OK;
 }
-int smooth2(wl_sim* s, Level& p, float w, Red* norms) {
+int smooth2(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready = false) {
   if (smooth_fusable(s, p)) return smooth_fused(s, p, w, norms);
   SmArgs a{levdev(p), p.per, w, 0, s->redw, norms ? norms : s->d_red, norms ? 1 : 0};
-  DISPATCH_D(s, k_eps_init_g, grid_inside(p.lay), blk(s->D), a);
+  if (!eps_ready) DISPATCH_D(s, k_eps_init_g, grid_inside(p.lay), blk(s->D), a);   // else K-UP left ϵ = r·iD behind
   if (p.dist) { if (int e = halo(s, p.eps, 1, true)) return e; }
   LevArgs g = lev_args(s, p);
   dim3 gg = grid_inside(p.lay);
@@ -508,14 +508,24 @@ void coarse_block(wl_sim* s, size_t first, float w) {
   a.first = (int)first; a.nlev = (int)s->lv.size(); a.per = s->per_glob; a.omega = w;
   DISPATCH_D(s, k_coarse, dim3(1), dim3(1024), a);
 }
-int vcycle(wl_sim* s, size_t l, float w) {
+// first: the top level's residual still needs its mean removed; K-DOWN does it on the fly and leaves the
+// norms of the shifted residual in slot 10
+int vcycle(wl_sim* s, size_t l, float w, bool first = false) {
   if (s->cfg.flags & WL_FLAG_NO_FUSED) { vcycle_v1(s, l, w); return WL_OK; }
   Level &fine = s->lv[l], &coarse = s->lv[l + 1];
   const bool gather = fine.dist && !coarse.dist;
   {
     if (fine.dist) { if (int e = halo(s, fine.r, 1)) return e; }       // K-DOWN reads ϵ = r·iD at the neighbours
-    DownArgs a{levdev(fine), levdev_window(s, fine, coarse), fine.per};
-    DISPATCH_D(s, k_down, grid_inside(fine.lay), blk(s->D), a);
+    DownArgs a{levdev(fine), levdev_window(s, fine, coarse), fine.per, first ? 1 : 0, red_in(s, 0), fine.ncells, s->redw, s->d_red + 10};
+    {
+      const dim3 g3 = grid_inside(fine.lay);
+      const long long nt = (long long)g3.x * g3.y * g3.z;
+      DISPATCH_D(s, k_down, dim3((unsigned)nt), blk(s->D), a);
+      if (first) {
+        FoldArgs fa{s->redw, (int)nt, s->d_red + 10};
+        LAUNCH(s, k_fold_partials, dim3(1), dim3(1024), fa);
+      }
+    }
     std::swap(fine.r, fine.eps);                     // K-DOWN staged the new residual in ϵ
     if (gather) {                                    // assemble the replicated coarse residual
       const int nloc = a.c.l.n2 - 2;
@@ -528,8 +538,9 @@ int vcycle(wl_sim* s, size_t l, float w) {
   if (level_is_small(coarse)) {
     coarse_block(s, l + 1, w);
   } else {
-    if (l + 2 < s->lv.size()) { if (int e = vcycle(s, l + 1, w)) return e; }
-    if (int e = smooth2(s, coarse, w, nullptr)) return e;
+    const bool deeper = l + 2 < s->lv.size();
+    if (deeper) { if (int e = vcycle(s, l + 1, w)) return e; }
+    if (int e = smooth2(s, coarse, w, nullptr, deeper)) return e;
   }
   if (coarse.dist) { if (int e = halo(s, coarse.x, 1)) return e; }     // K-UP prolongates the neighbours' coarse cells too
   else if (gather && s->per_glob.p[2]) {                               // rank windows read the wrap planes as ghosts
@@ -538,7 +549,7 @@ int vcycle(wl_sim* s, size_t l, float w) {
     plane_launch(coarse.lay, g, b);
     DISPATCH_D(s, k_perbc, g, b, pa);
   }
-  UpArgs u{levdev(fine), levdev_window(s, fine, coarse), fine.per, w, s->redw, s->d_red, 0};
+  UpArgs u{levdev(fine), levdev_window(s, fine, coarse), fine.per, w, s->redw, s->d_red, 0, smooth_fusable(s, fine) ? 0 : 1};
   DISPATCH_D(s, k_up, grid_inside(fine.lay), blk(s->D), u);
   return WL_OK;
 }
@@ -567,6 +578,7 @@ struct Trace { int n = 0; int flags = 0; float rinf[34], r1[34], omega[34]; };
 // scalars per iteration, exactly as in the reference.
 int mlp_solver(wl_sim* s, Trace* tr, bool residual_done = false) {
   Level& p = s->lv[0];
+  bool lazy = false;
   const double tol = s->cfg.tol;
   const double r1tol = (tol / 10) * (double)p.ncells, rinftol = tol;
   const int itmx = s->cfg.itmx;
@@ -581,12 +593,17 @@ int mlp_solver(wl_sim* s, Trace* tr, bool residual_done = false) {
     }
     if (int e = gather_red(s)) return e;
     a.in = red_in(s, 0); a.out = s->d_red + 1;
-    DISPATCH_D(s, k_shift_norms, grid_tiles(p.lay, false), blk(s->D), a);
+    // fused solve on a multi-kernel hierarchy: the first K-DOWN removes the mean and takes the norms
+    lazy = fused && residual_done && !level_is_small(p);
+    if (!lazy) DISPATCH_D(s, k_shift_norms, grid_tiles(p.lay, false), blk(s->D), a);
   }
-  if (int e = fetch_red(s)) return e;
-  float r1 = (float)s->h_red[1].sum, rinf = s->h_red[1].maxv, w = 1.f;
+  float r1 = 0.f, rinf = 0.f, w = 1.f;
   int np = 0, flags = 0;
-  if (tr) { tr->rinf[0] = rinf; tr->r1[0] = r1; tr->omega[0] = w; }
+  if (!lazy) {
+    if (int e = fetch_red(s)) return e;
+    r1 = (float)s->h_red[1].sum; rinf = s->h_red[1].maxv;
+    if (tr) { tr->rinf[0] = rinf; tr->r1[0] = r1; tr->omega[0] = w; }
+  }
   while (np < itmx) {
     if (fused && level_is_small(p)) {            // the whole hierarchy fits the single-block kernel
       coarse_block(s, 0, w);
@@ -594,11 +611,15 @@ int mlp_solver(wl_sim* s, Trace* tr, bool residual_done = false) {
       a.in = red_in(s, 7); a.out = s->d_red + 1; // slot 7 stays zero: no shift, norms only
       DISPATCH_D(s, k_shift_norms, grid_tiles(p.lay, false), blk(s->D), a);
     } else {
-      if (int e = vcycle(s, 0, w)) return e;
-      if (fused) { if (int e = smooth2(s, p, w, s->d_red + 1)) return e; }
+      if (int e = vcycle(s, 0, w, lazy && np == 0)) return e;
+      if (fused) { if (int e = smooth2(s, p, w, s->d_red + 1, true)) return e; }
       else smooth(s, p, w, s->d_red + 1);
     }
     if (int e = fetch_red(s)) return e;
+    if (lazy && np == 0) {                        // the initial norms arrive with the first iteration's
+      r1 = (float)s->h_red[10].sum; rinf = s->h_red[10].maxv;
+      if (tr) { tr->rinf[0] = rinf; tr->r1[0] = r1; tr->omega[0] = w; }
+    }
     const float rnew = (float)s->h_red[1].sum;
     rinf = s->h_red[1].maxv; ++np;
     if (tr && np < 34) { tr->rinf[np] = rinf; tr->r1[np] = rnew; tr->omega[np] = w; }

@@ -145,6 +145,33 @@ __device__ __forceinline__ void fold_partials(const double* psum, const float* p
   }
 }
 
+// Reduction in two launches for kernels with ~10^5 blocks: every block leaves one partial
+// (block_reduce_partial, no fence, no atomic), k_fold_partials folds them in index order.
+__device__ __forceinline__ void block_reduce_partial(double s, float m, const RedWork w) {
+  __shared__ double ssum[32];
+  __shared__ float smax[32];
+  const int tid = linear_tid();
+  const int nthr = blockDim.x * blockDim.y * blockDim.z;
+  const int lane = tid & 31, wid = tid >> 5, nw = (nthr + 31) >> 5;
+  s = warp_sum(s); m = warp_max(m);
+  if (lane == 0) { ssum[wid] = s; smax[wid] = m; }
+  __syncthreads();
+  if (wid == 0) {
+    s = lane < nw ? ssum[lane] : 0.0;
+    m = lane < nw ? smax[lane] : -INFINITY;
+    s = warp_sum(s); m = warp_max(m);
+    if (lane == 0) { const int b = linear_bid(); w.psum[b] = s; w.pmax[b] = m; }
+  }
+}
+struct FoldArgs { RedWork w; int n; Red* out; };
+__global__ void __launch_bounds__(1024) k_fold_partials(const FoldArgs a) {
+  __shared__ double ssum[32];
+  __shared__ float smax[32];
+  double s; float m;
+  fold_partials(a.w.psum, a.w.pmax, 0, a.n, ssum, smax, s, m);
+  if (threadIdx.x == 0) { a.out->sum = s; a.out->maxv = m; }
+}
+
 // Call from ALL threads of the block (contains __syncthreads).  `out` receives the result.
 // Two ticket levels (groups of RED_GROUP blocks, then the groups): with >10^5 blocks a single ticket
 // serialises that many atomics on one L2 address and the last block would fold 10^5 partials alone.

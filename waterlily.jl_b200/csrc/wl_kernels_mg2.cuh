@@ -164,7 +164,11 @@ __global__ void __launch_bounds__(256) k_divres(const DivResArgs a) {
 }
 
 // ---------------------------------------------------------------- K-DOWN
-struct DownArgs { LevDev f, c; Per per; };
+// first != 0 (level 1 of the first V-cycle of a solve): the residual still lacks the mean removal of
+// residual! (Poisson.jl:95-97).  The mean Σr/N arrives in `in`; the kernel subtracts it on the fly
+// from every r it reads and reports L₁/L∞ of the shifted residual (MultiLevelPoisson.jl:111) in
+// `out`, which saves the separate pass over r and one host round trip per solve.
+struct DownArgs { LevDev f, c; Per per; int first; RedIn in; long long ncells; RedWork w; Red* out; };
 // One thread per FINE cell (coalesced); the children of a coarse cell sit in one block (block
 // extents are even and blocks start on odd interior indices), so the restriction gathers them from
 // shared memory and adds them in the reference's order (first dimension fastest).
@@ -173,8 +177,24 @@ __global__ void __launch_bounds__(256) k_down(const DownArgs a) {
   __shared__ float tile[256];
   const Lay& lc = a.c.l;
   const Lay& l = a.f.l;
-  WL_IJK_FROM_BLOCK(D, l)
   const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
+  double s1 = 0.0; float mx = -INFINITY;
+  float sh = 0.f;                                                      // residual mean to remove (first cycle only)
+  if (a.first) {
+    const float mean = (float)redin_sum(a.in) / (float)a.ncells;
+    if (fabsf(mean) > 2.f * 1.1920929e-07f) sh = mean;
+  }
+  const bool shift = sh != 0.f;
+  // 1-D grid over the tiles of blockDim cells: one tile per block, or (first cycle, where the block
+  // ends in a grid-wide reduction) a persistent loop of a few blocks per SM
+  const int nbx = (l.n0 - 2 + blockDim.x - 1) / blockDim.x, nby = (l.n1 - 2 + blockDim.y - 1) / blockDim.y;
+  const int nbz = D == 3 ? (l.n2 - 2 + blockDim.z - 1) / blockDim.z : 1;
+  const int nt = nbx * nby * nbz;
+  for (int tq = blockIdx.x; tq < nt; tq += gridDim.x) {
+  const int tbx = tq % nbx, tqq = tq / nbx, tby = tqq % nby, tbz = tqq / nby;
+  const int i0 = tbx * blockDim.x + 1, j0 = tby * blockDim.y + 1, k0 = D == 3 ? tbz * blockDim.z + 1 : 0;
+  const int i = i0 + threadIdx.x, j = j0 + threadIdx.y, k = D == 3 ? k0 + threadIdx.z : 0;
+  const bool inb = !(i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && k > l.n2 - 2));
   float rn = 0.f;
   auto body = [&](auto edge) {
     constexpr bool EDGE = decltype(edge)::value;
@@ -183,7 +203,8 @@ __global__ void __launch_bounds__(256) k_down(const DownArgs a) {
     int om[3], op[3];
     nbr_off<D, EDGE>(l, a.per, i, j, k, om, op);
     float L0[3], L1[3], rm[3], rp[3], dm[3], dp[3];
-    const float r0 = a.f.r[o], x0 = a.f.x[o], d0 = __ldg(a.f.iD + o);   // all reads before the first store
+    float r0 = a.f.r[o];
+    const float x0 = a.f.x[o], d0 = __ldg(a.f.iD + o);                 // all reads before the first store
 #pragma unroll
     for (int d = 0; d < D; ++d) {
       const float* Ld = a.f.L + l.cstride * d;
@@ -191,6 +212,14 @@ __global__ void __launch_bounds__(256) k_down(const DownArgs a) {
       rm[d] = a.f.r[o + om[d]]; dm[d] = __ldg(a.f.iD + o + om[d]);
       rp[d] = a.f.r[o + op[d]]; dp[d] = __ldg(a.f.iD + o + op[d]);
     }
+    if (shift) {
+      // ghost neighbours of non-periodic directions are not shifted by the reference, but their iD is
+      // 0 and so is the face coefficient: the product contributes a (signed) zero either way
+      r0 = r0 - sh;
+#pragma unroll
+      for (int d = 0; d < D; ++d) { rm[d] = rm[d] - sh; rp[d] = rp[d] - sh; }
+    }
+    if (a.first) { s1 += (double)fabsf(r0); mx = fmaxf(mx, fabsf(r0)); }
     const float e0 = r0 * d0;                                          // ϵ = r·iD  Poisson.jl:112
     float dg = 0.f;
 #pragma unroll
@@ -205,34 +234,40 @@ __global__ void __launch_bounds__(256) k_down(const DownArgs a) {
     a.f.x[o] = x0 + e0;                                                // Poisson.jl:103
   };
   if (inb) {
-    if (tile_on_seam<D>(l, a.per, (int)(blockIdx.x * blockDim.x) + 1, (int)(blockIdx.y * blockDim.y) + 1,
-                        D == 3 ? (int)(blockIdx.z * blockDim.z) + 1 : 0)) body(EdgeYes{});
+    if (tile_on_seam<D>(l, a.per, i0, j0, k0)) body(EdgeYes{});
     else body(EdgeNo{});
   }
   tile[tid] = rn;
   __syncthreads();
-  if (!inb) return;
   const int c[3] = {i, j, k};
   const int t[3] = {(int)threadIdx.x, (int)threadIdx.y, (int)threadIdx.z};
   int cc[3], n[3];
+  bool parent = inb;                                                   // first child of its coarse cell
 #pragma unroll
   for (int d = 0; d < 3; ++d) {
     const bool co = d < D && a.c.c[d];
-    if (co && (t[d] & 1)) return;                                      // not the first child in this direction
+    if (co && (t[d] & 1)) parent = false;
     cc[d] = co ? (c[d] + 1) / 2 : c[d];
     n[d] = co ? 2 : 1;
   }
-  float sum = 0.f;                                                     // restrict  MLP.jl:13-19
-  for (int kk = 0; kk < n[2]; ++kk)
-    for (int jj = 0; jj < n[1]; ++jj)
-      for (int ii = 0; ii < n[0]; ++ii) sum += tile[tid + ii + (int)blockDim.x * (jj + (int)blockDim.y * kk)];
-  const int oc = lc.off(cc[0], cc[1], cc[2]);
-  a.c.r[oc] = sum;
-  a.c.x[oc] = 0.f;                                                     // fill!(coarse.x,0)  MLP.jl:94
+  if (parent) {
+    float sum = 0.f;                                                   // restrict  MLP.jl:13-19
+    for (int kk = 0; kk < n[2]; ++kk)
+      for (int jj = 0; jj < n[1]; ++jj)
+        for (int ii = 0; ii < n[0]; ++ii) sum += tile[tid + ii + (int)blockDim.x * (jj + (int)blockDim.y * kk)];
+    const int oc = lc.off(cc[0], cc[1], cc[2]);
+    a.c.r[oc] = sum;
+    a.c.x[oc] = 0.f;                                                   // fill!(coarse.x,0)  MLP.jl:94
+  }
+  __syncthreads();                                                     // the tile buffer is reused by the next trip
+  }
+  if (a.first) block_reduce_partial(s1, mx, a.w);                      // folded by k_fold_partials
 }
 
 // ---------------------------------------------------------------- K-UP
-struct UpArgs { LevDev f, c; Per per; float omega; RedWork w; Red* out; int want_norms; };
+// write_eps: the smoother of this level always follows (MultiLevelPoisson.jl:97-100,115), so K-UP also
+// leaves its first statement ϵ = r·iD (+ periodic images, Poisson.jl:142-143) behind
+struct UpArgs { LevDev f, c; Per per; float omega; RedWork w; Red* out; int want_norms; int write_eps; };
 template <int D>
 __global__ void __launch_bounds__(256) k_up(const UpArgs a) {
   const Lay& l = a.f.l;
@@ -268,6 +303,7 @@ __global__ void __launch_bounds__(256) k_up(const UpArgs a) {
     float L0[3], L1[3], em[3], ep[3];
     const float e0 = __ldg(a.c.x + oc);
     const float r0 = a.f.r[o], x0 = a.f.x[o];            // all reads before the first store
+    const float d0 = a.write_eps ? __ldg(a.f.iD + o) : 0.f;
 #pragma unroll
     for (int d = 0; d < D; ++d) {
       const float* Ld = a.f.L + l.cstride * d;
@@ -283,6 +319,11 @@ __global__ void __launch_bounds__(256) k_up(const UpArgs a) {
     const float r = r0 - a.omega * s;
     a.f.r[o] = r;
     a.f.x[o] = x0 + a.omega * e0;
+    if (a.write_eps) {
+      const float e = r * d0;
+      a.f.eps[o] = e;
+      if (EDGE) store_images<D>(a.f.eps, l, a.per, i, j, k, e);
+    }
     s1 = (double)fabsf(r); m = fabsf(r);
   };
   if (inb) {
