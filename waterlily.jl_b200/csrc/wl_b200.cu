@@ -19,6 +19,7 @@
 #include "wl_kernels_mom.cuh"
 #include "wl_kernels_mom3.cuh"
 #include "wl_kernels_smooth.cuh"
+#include "wl_kernels_mg4.cuh"
 
 using namespace wl;
 
@@ -443,6 +444,20 @@ inline bool level_is_small(const Level& p) { return !p.dist && (long long)p.lay.
 // colour only reads the other colour, so this reproduces the single-domain sweep exactly); the
 // planes across a periodic wrap are sent once after the init and once before the increment, which
 // is when the reference's perBC!(ϵ) runs.
+// x-vectorised pressure kernels (wl_kernels_mg4.cuh): fixed 32x4x2 blocks of quads
+bool use_vec4(const Lay& l) {
+  static int off = -1;
+  if (off < 0) off = getenv("WL_NO_VEC4") ? 1 : 0;
+  return !off && vec4_ok(l);
+}
+dim3 grid_quads(const Lay& l, int cells_per_thread = 4) {
+  return dim3((l.n0 - 2 + 32 * cells_per_thread - 1) / (32 * cells_per_thread), (l.n1 - 2 + 3) / 4, (l.n2 - 2 + 1) / 2);
+}
+void fold_partials_to(wl_sim* s, const dim3& g, Red* out) {
+  FoldArgs fa{s->redw, (int)(g.x * g.y * g.z), out};
+  LAUNCH(s, k_fold_partials, dim3(1), dim3(1024), fa);
+}
+
 // K-SMOOTH applies when no reference quirk outside its model is in play: 3D, even last dimension
 // (half_rangek sweeps every plane), even interior extent in periodic directions (colours continue
 // across the seam), and extents that the 5-cell halo cannot wrap twice.
@@ -493,12 +508,23 @@ int smooth2(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready = false) {
   LevArgs g = lev_args(s, p);
   dim3 gg = grid_inside(p.lay);
   gg.x = (p.lay.n0 - 2 + 2 * blk(s->D).x - 1) / (2 * blk(s->D).x);   // colour-compacted: a thread per x-pair
+  const bool v4 = use_vec4(p.lay);
+  // k_gs8 (8 cells per thread) measured no faster than the colour-compacted scalar sweep: opt-in only
+  static const bool gs8 = getenv("WL_GS8") != nullptr;
+  const bool v8 = gs8 && v4 && (p.lay.n0 - 2) % 8 == 0;
   for (int k0 = 1; k0 <= 4; ++k0) {
     g.k0 = k0;
-    DISPATCH_D(s, k_gs_half_c, gg, blk(s->D), g);
+    if (v8) LAUNCH(s, k_gs8, grid_quads(p.lay, 8), dim3(32, 4, 2), g);
+    else DISPATCH_D(s, k_gs_half_c, gg, blk(s->D), g);
     if (p.dist) { if (int e = halo(s, p.eps, 1, k0 == 4)) return e; }
   }
-  DISPATCH_D(s, k_increment_w, grid_tiles(p.lay, false), blk(s->D), a);
+  if (v4) {
+    const dim3 gq = grid_quads(p.lay);
+    LAUNCH(s, k_incr4, gq, dim3(32, 4, 2), a);
+    if (norms) fold_partials_to(s, gq, norms);
+  } else {
+    DISPATCH_D(s, k_increment_w, grid_tiles(p.lay, false), blk(s->D), a);
+  }
   return WL_OK;
 }
 // levels first..end in ONE single-block launch: Vcycle!(l=first) (if any coarser level) + smooth!(first)
@@ -520,10 +546,13 @@ int vcycle(wl_sim* s, size_t l, float w, bool first = false) {
     {
       const dim3 g3 = grid_inside(fine.lay);
       const long long nt = (long long)g3.x * g3.y * g3.z;
-      DISPATCH_D(s, k_down, dim3((unsigned)nt), blk(s->D), a);
-      if (first) {
-        FoldArgs fa{s->redw, (int)nt, s->d_red + 10};
-        LAUNCH(s, k_fold_partials, dim3(1), dim3(1024), fa);
+      if (use_vec4(fine.lay) && coarse.c[0] && coarse.c[1] && coarse.c[2]) {
+        const dim3 gq = grid_quads(fine.lay);
+        LAUNCH(s, k_down4, gq, dim3(32, 4, 2), a);
+        if (first) fold_partials_to(s, gq, s->d_red + 10);
+      } else {
+        DISPATCH_D(s, k_down, dim3((unsigned)nt), blk(s->D), a);
+        if (first) fold_partials_to(s, dim3((unsigned)nt), s->d_red + 10);
       }
     }
     std::swap(fine.r, fine.eps);                     // K-DOWN staged the new residual in ϵ
@@ -550,7 +579,8 @@ int vcycle(wl_sim* s, size_t l, float w, bool first = false) {
     DISPATCH_D(s, k_perbc, g, b, pa);
   }
   UpArgs u{levdev(fine), levdev_window(s, fine, coarse), fine.per, w, s->redw, s->d_red, 0, smooth_fusable(s, fine) ? 0 : 1};
-  DISPATCH_D(s, k_up, grid_inside(fine.lay), blk(s->D), u);
+  if (use_vec4(fine.lay)) LAUNCH(s, k_up4, grid_quads(fine.lay), dim3(32, 4, 2), u);
+  else DISPATCH_D(s, k_up, grid_inside(fine.lay), blk(s->D), u);
   return WL_OK;
 }
 
@@ -707,12 +737,19 @@ int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
     Level& p0 = s->lv[0];
     const float dt = w * s->dt;
     DivResArgs d{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, p0.r.base, s->per, dt, s->redw, s->d_red + 0};
-    DISPATCH_D(s, k_divres, grid_tiles(s->lay, false), blk(s->D), d);
+    if (use_vec4(s->lay)) {
+      const dim3 gq = grid_quads(s->lay);
+      LAUNCH(s, k_divres4, gq, dim3(32, 4, 2), d);
+      fold_partials_to(s, gq, s->d_red + 0);
+    } else {
+      DISPATCH_D(s, k_divres, grid_tiles(s->lay, false), blk(s->D), d);
+    }
     std::swap(s->p, p0.eps); p0.x = s->p;                       // scaled x lives in the former ϵ buffer
     if (int e = mlp_solver(s, tr, true)) return e;
     if (int e = halo(s, p0.x, 1)) return e;                     // the solver's final perBC!(x) across slabs
     ProjArgs2 q{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, s->per, dt};
-    DISPATCH_D(s, k_proj, grid_inside(s->lay), blk(s->D), q);
+    if (use_vec4(s->lay)) LAUNCH(s, k_proj4, grid_quads(s->lay), dim3(32, 4, 2), q);
+    else DISPATCH_D(s, k_proj, grid_inside(s->lay), blk(s->D), q);
     std::swap(s->p, p0.eps); p0.x = s->p;
     if (int e = halo(s, s->p, 1)) return e;                     // p's ghost planes (next K-DIVRES, data surface)
     bc_vec(s, s->u, U, s->cfg.exitBC != 0);

@@ -1,0 +1,355 @@
+// wl_kernels_mg4.cuh -- x-vectorised pressure kernels: one thread owns FOUR consecutive cells of a row.
+//
+// ncu on the one-cell-per-thread kernels (profiles/r1_v9_ncu_full_sphere512.tsv) shows them issue-bound,
+// not HBM-bound: 120-400 instructions per cell, most of them 64-bit address arithmetic around scalar
+// loads (K-UP: 80 % issue-active at 52 % DRAM).  With four cells per thread the rows above/below and
+// the planes in front/behind arrive as one 128-bit load each, the index arithmetic is paid once per
+// four cells, and the kernels move towards the HBM roofline.  The arithmetic per cell and its order
+// are those of the scalar kernels (wl_kernels_mg2.cuh), so results stay bit-identical.
+//
+// Layout facts used: interior cell i==1 of every row is 128-byte aligned, pitch/plane/cstride are
+// multiples of 32 floats, so a thread whose first cell is i = 1+4m loads aligned float4s.  The
+// kernels require (n0-2) % 4 == 0; other levels use the scalar kernels.
+#pragma once
+#include "wl_kernels_mg2.cuh"
+
+namespace wl {
+
+struct F4 { float v[4]; };
+__device__ __forceinline__ F4 ld4g(const float* p) {           // read-only data
+  const float4 t = __ldg(reinterpret_cast<const float4*>(p));
+  return F4{{t.x, t.y, t.z, t.w}};
+}
+__device__ __forceinline__ F4 ld4(const float* p) {            // data other threads of this kernel may write elsewhere
+  const float4 t = *reinterpret_cast<const float4*>(p);
+  return F4{{t.x, t.y, t.z, t.w}};
+}
+__device__ __forceinline__ void st4(float* p, const F4& a) {
+  *reinterpret_cast<float4*>(p) = make_float4(a.v[0], a.v[1], a.v[2], a.v[3]);
+}
+inline bool vec4_ok(const Lay& l) { return l.D == 3 && (l.n0 - 2) % 4 == 0 && l.n0 - 2 >= 8; }
+
+// thread -> first cell of its quad; blockDim = (32,4,2) covers 128 x 4 x 2 cells
+#define WL_QUAD_FROM_BLOCK(l)                                                   \
+  const int i = 1 + 4 * (blockIdx.x * blockDim.x + threadIdx.x);                \
+  const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;                      \
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + 1;                      \
+  const bool inb = !(i > l.n0 - 2 || j > l.n1 - 2 || k > l.n2 - 2);
+
+// y/z neighbour offsets of the quad's row (wrapped across periodic seams) and the x offsets of the
+// cell left of the quad / right of it
+__device__ __forceinline__ void quad_nbr(const Lay& l, const Per& per, int i, int j, int k, int& oxm, int& oxp,
+                                         int& oym, int& oyp, int& ozm, int& ozp) {
+  oxm = (per.p[0] && i == 1) ? l.n0 - 3 : -1;                            // relative to the quad's first cell
+  oxp = (per.p[0] && i + 3 == l.n0 - 2) ? 3 - (l.n0 - 3) : 4;
+  oym = (per.p[1] && j == 1) ? (l.n1 - 3) * l.pitch : -l.pitch;
+  oyp = (per.p[1] && j == l.n1 - 2) ? -(l.n1 - 3) * l.pitch : l.pitch;
+  ozm = (per.p[2] && k == 1) ? (l.n2 - 3) * l.plane : -l.plane;
+  ozp = (per.p[2] && k == l.n2 - 2) ? -(l.n2 - 3) * l.plane : l.plane;
+}
+
+// ---------------------------------------------------------------- increment! (Poisson.jl:100-104), 4 cells per thread
+// perBC!(ϵ) folded into wrap-reads as in k_increment_w; L₁/L∞ partials per block (k_fold_partials folds them)
+__global__ void __launch_bounds__(256) k_incr4(const SmArgs a) {
+  const Lay& l = a.p.l;
+  WL_QUAD_FROM_BLOCK(l)
+  double s1 = 0.0; float m = -INFINITY;
+  if (inb) {
+    const int o = l.off(i, j, k);
+    int oxm, oxp, oym, oyp, ozm, ozp;
+    quad_nbr(l, a.per, i, j, k, oxm, oxp, oym, oyp, ozm, ozp);
+    const float* Lx = a.p.L; const float* Ly = a.p.L + l.cstride; const float* Lz = a.p.L + 2 * l.cstride;
+    const F4 lx = ld4g(Lx + o); const float lx4 = __ldg(Lx + o + 4);
+    const F4 ly0 = ld4g(Ly + o), ly1 = ld4g(Ly + o + l.pitch), lz0 = ld4g(Lz + o), lz1 = ld4g(Lz + o + l.plane);
+    const F4 e = ld4(a.p.eps + o), eym = ld4(a.p.eps + o + oym), eyp = ld4(a.p.eps + o + oyp),
+             ezm = ld4(a.p.eps + o + ozm), ezp = ld4(a.p.eps + o + ozp);
+    const float exm = a.p.eps[o + oxm], exp_ = a.p.eps[o + oxp];
+    const F4 r0 = ld4(a.p.r + o), x0 = ld4(a.p.x + o);
+    F4 rn, xn;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float lxl = lx.v[q], lxu = q < 3 ? lx.v[q < 3 ? q + 1 : 3] : lx4;
+      const float el = q == 0 ? exm : e.v[q > 0 ? q - 1 : 0], er = q == 3 ? exp_ : e.v[q < 3 ? q + 1 : 3];
+      float dg = 0.f;                                              // diag(I,L)  Poisson.jl:49-55
+      dg -= lxl + lxu; dg -= ly0.v[q] + ly1.v[q]; dg -= lz0.v[q] + lz1.v[q];
+      float s = e.v[q] * dg;                                       // mult(I,L,D,ϵ)  Poisson.jl:70-76
+      s += el * lxl + er * lxu;
+      s += eym.v[q] * ly0.v[q] + eyp.v[q] * ly1.v[q];
+      s += ezm.v[q] * lz0.v[q] + ezp.v[q] * lz1.v[q];
+      const float r = r0.v[q] - a.omega * s;
+      rn.v[q] = r;
+      xn.v[q] = x0.v[q] + a.omega * e.v[q];
+      s1 += (double)fabsf(r); m = fmaxf(m, fabsf(r));
+    }
+    st4(a.p.r + o, rn);
+    st4(a.p.x + o, xn);
+  }
+  if (a.want_norms) block_reduce_partial(s1, m, a.w);
+}
+
+// ---------------------------------------------------------------- red-black half sweep, 8 cells per thread (4 updated)
+// gauss_rb (Poisson.jl:124-128) over half_rangek (:130-132).  The thread rewrites its two quads whole:
+// the cells of the other colour get back the value that was read (nobody writes them in this sweep).
+__global__ void __launch_bounds__(256) k_gs8(const LevArgs a) {
+  const Lay& l = a.l;
+  const int i = 1 + 8 * (blockIdx.x * blockDim.x + threadIdx.x);
+  const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z + 1;
+  if (i > l.n0 - 2 || j > l.n1 - 2 || k > l.n2 - 2) return;
+  if (k > 2 * (l.n2 / 2) - 2) return;
+  const int b = (j + k + 3 + a.k0) & 1;                            // updated cells: q = b, b+2, b+4, b+6
+  const int o = l.off(i, j, k);
+  const float* Lx = a.L; const float* Ly = a.L + l.cstride; const float* Lz = a.L + 2 * l.cstride;
+  const int pitch = l.pitch, plane = l.plane;
+  float lx[9], ly0[8], ly1[8], lz0[8], lz1[8], e[10], eym[8], eyp[8], ezm[8], ezp[8], r[8];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int oh = o + 4 * h;
+    const F4 t0 = ld4g(Lx + oh), t1 = ld4g(Ly + oh), t2 = ld4g(Ly + oh + pitch), t3 = ld4g(Lz + oh), t4 = ld4g(Lz + oh + plane);
+    const F4 t5 = ld4(a.eps + oh), t6 = ld4(a.eps + oh - pitch), t7 = ld4(a.eps + oh + pitch),
+             t8 = ld4(a.eps + oh - plane), t9 = ld4(a.eps + oh + plane), ta = ld4(a.r + oh);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      lx[4 * h + q] = t0.v[q]; ly0[4 * h + q] = t1.v[q]; ly1[4 * h + q] = t2.v[q]; lz0[4 * h + q] = t3.v[q]; lz1[4 * h + q] = t4.v[q];
+      e[1 + 4 * h + q] = t5.v[q]; eym[4 * h + q] = t6.v[q]; eyp[4 * h + q] = t7.v[q]; ezm[4 * h + q] = t8.v[q]; ezp[4 * h + q] = t9.v[q];
+      r[4 * h + q] = ta.v[q];
+    }
+  }
+  lx[8] = __ldg(Lx + o + 8);
+  e[0] = a.eps[o - 1]; e[9] = a.eps[o + 8];                        // ghosts as they are (stale under periodic BCs)
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+#pragma unroll
+    for (int bb = 0; bb < 2; ++bb) {
+      if (bb != b) continue;
+      const int q = 2 * p + bb;
+      float s = r[q], dg = 0.f;
+      dg -= lx[q] + lx[q + 1];   s -= e[q] * lx[q] + e[q + 2] * lx[q + 1];
+      dg -= ly0[q] + ly1[q];     s -= eym[q] * ly0[q] + eyp[q] * ly1[q];
+      dg -= lz0[q] + lz1[q];     s -= ezm[q] * lz0[q] + ezp[q] * lz1[q];
+      e[1 + q] = s * inv_or_zero(dg);
+    }
+  }
+  st4(a.eps + o, F4{{e[1], e[2], e[3], e[4]}});
+  st4(a.eps + o + 4, F4{{e[5], e[6], e[7], e[8]}});
+}
+
+// ---------------------------------------------------------------- K-DIVRES, 4 cells per thread (see k_divres)
+__global__ void __launch_bounds__(256) k_divres4(const DivResArgs a) {
+  const Lay& l = a.l;
+  WL_QUAD_FROM_BLOCK(l)
+  double s = 0.0;
+  if (inb) {
+    const int o = l.off(i, j, k);
+    int oxm, oxp, oym, oyp, ozm, ozp;
+    quad_nbr(l, a.per, i, j, k, oxm, oxp, oym, oyp, ozm, ozp);
+    const float* ux = a.u; const float* uy = a.u + l.cstride; const float* uz = a.u + 2 * l.cstride;
+    const float* Lx = a.L; const float* Ly = a.L + l.cstride; const float* Lz = a.L + 2 * l.cstride;
+    const F4 u0 = ld4g(ux + o); const float u04 = __ldg(ux + o + 4);
+    const F4 v0 = ld4g(uy + o), v1 = ld4g(uy + o + l.pitch), w0 = ld4g(uz + o), w1 = ld4g(uz + o + l.plane);
+    const F4 lx = ld4g(Lx + o); const float lx4 = __ldg(Lx + o + 4);
+    const F4 ly0 = ld4g(Ly + o), ly1 = ld4g(Ly + o + l.pitch), lz0 = ld4g(Lz + o), lz1 = ld4g(Lz + o + l.plane);
+    const F4 x = ld4g(a.x + o), xym = ld4g(a.x + o + oym), xyp = ld4g(a.x + o + oyp),
+             xzm = ld4g(a.x + o + ozm), xzp = ld4g(a.x + o + ozp);
+    const float xxm = __ldg(a.x + o + oxm), xxp = __ldg(a.x + o + oxp);
+    F4 rr, xs;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float uxu = q < 3 ? u0.v[q < 3 ? q + 1 : 3] : u04;
+      const float lxl = lx.v[q], lxu = q < 3 ? lx.v[q < 3 ? q + 1 : 3] : lx4;
+      const float xl = q == 0 ? xxm : x.v[q > 0 ? q - 1 : 0], xr = q == 3 ? xxp : x.v[q < 3 ? q + 1 : 3];
+      float z = 0.f, dg = 0.f;
+      z += uxu - u0.v[q]; z += v1.v[q] - v0.v[q]; z += w1.v[q] - w0.v[q];
+      dg -= lxl + lxu; dg -= ly0.v[q] + ly1.v[q]; dg -= lz0.v[q] + lz1.v[q];
+      const float xc = x.v[q] * a.dt;
+      float r = 0.f;
+      if (dg != 0.f) {
+        float ax = xc * dg;
+        ax += (xl * a.dt) * lxl + (xr * a.dt) * lxu;
+        ax += (xym.v[q] * a.dt) * ly0.v[q] + (xyp.v[q] * a.dt) * ly1.v[q];
+        ax += (xzm.v[q] * a.dt) * lz0.v[q] + (xzp.v[q] * a.dt) * lz1.v[q];
+        r = z - ax;
+      }
+      rr.v[q] = r; xs.v[q] = xc;
+      s += (double)r;
+    }
+    st4(a.r + o, rr);
+    st4(a.xs + o, xs);
+  }
+  block_reduce_partial(s, -INFINITY, a.w);
+}
+
+// ---------------------------------------------------------------- K-PROJ, 4 cells per thread (see k_proj)
+__global__ void __launch_bounds__(256) k_proj4(const ProjArgs2 a) {
+  const Lay& l = a.l;
+  WL_QUAD_FROM_BLOCK(l)
+  if (!inb) return;
+  const int o = l.off(i, j, k);
+  int oxm, oxp, oym, oyp, ozm, ozp;
+  quad_nbr(l, a.per, i, j, k, oxm, oxp, oym, oyp, ozm, ozp);
+  const F4 x = ld4g(a.x + o), xym = ld4g(a.x + o + oym), xzm = ld4g(a.x + o + ozm);
+  const float xxm = __ldg(a.x + o + oxm);
+  float* ux = a.u; float* uy = a.u + l.cstride; float* uz = a.u + 2 * l.cstride;
+  const F4 u0 = ld4(ux + o), v0 = ld4(uy + o), w0 = ld4(uz + o);
+  const F4 lx = ld4g(a.L + o), ly = ld4g(a.L + l.cstride + o), lz = ld4g(a.L + 2 * l.cstride + o);
+  F4 un, vn, wn, pn;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float xl = q == 0 ? xxm : x.v[q > 0 ? q - 1 : 0];
+    un.v[q] = u0.v[q] - lx.v[q] * (x.v[q] - xl);
+    vn.v[q] = v0.v[q] - ly.v[q] * (x.v[q] - xym.v[q]);
+    wn.v[q] = w0.v[q] - lz.v[q] * (x.v[q] - xzm.v[q]);
+    pn.v[q] = x.v[q] / a.dt;
+  }
+  st4(ux + o, un); st4(uy + o, vn); st4(uz + o, wn);
+  st4(a.pn + o, pn);
+  const bool seam = (a.per.p[0] && (i == 1 || i + 3 == l.n0 - 2)) || (a.per.p[1] && (j == 1 || j == l.n1 - 2)) ||
+                    (a.per.p[2] && (k == 1 || k == l.n2 - 2));
+  if (seam) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) store_images<3>(a.pn, l, a.per, i + q, j, k, pn.v[q]);
+  }
+}
+
+// ---------------------------------------------------------------- K-UP, 4 cells per thread (see k_up)
+// prolongate! + perBC! + increment!(ω) (+ ϵ = r·iD for the smoother that follows).  Any coarsening mask.
+__global__ void __launch_bounds__(256) k_up4(const UpArgs a) {
+  const Lay& l = a.f.l;
+  const Lay& lc = a.c.l;
+  WL_QUAD_FROM_BLOCK(l)
+  if (!inb) return;
+  const int o = l.off(i, j, k);
+  const bool cx = a.c.c[0] != 0, cy = a.c.c[1] != 0, cz = a.c.c[2] != 0;
+  // coarse coordinates of the row and of its (periodically wrapped) neighbours: down(I,c) MLP.jl:7
+  const int jm = (a.per.p[1] && j == 1) ? l.n1 - 2 : j - 1, jp = (a.per.p[1] && j == l.n1 - 2) ? 1 : j + 1;
+  const int km = (a.per.p[2] && k == 1) ? l.n2 - 2 : k - 1, kp = (a.per.p[2] && k == l.n2 - 2) ? 1 : k + 1;
+  const int im = (a.per.p[0] && i == 1) ? l.n0 - 2 : i - 1, ip = (a.per.p[0] && i + 3 == l.n0 - 2) ? 1 : i + 4;
+  auto dn = [](bool co, int c) { return co ? (c + 1) >> 1 : c; };
+  const int cj = dn(cy, j), ck = dn(cz, k);
+  const int c0 = dn(cx, i);
+  auto row = [&](int jj, int kk) {                              // coarse values under the quad's four cells
+    const float* p = a.c.x + lc.pitch * jj + lc.plane * kk;
+    if (cx) { const float v0 = __ldg(p + c0), v1 = __ldg(p + c0 + 1); return F4{{v0, v0, v1, v1}}; }
+    return ld4g(p + i);
+  };
+  const F4 e = row(cj, ck), eym = row(dn(cy, jm), ck), eyp = row(dn(cy, jp), ck), ezm = row(cj, dn(cz, km)), ezp = row(cj, dn(cz, kp));
+  const float* pc = a.c.x + lc.pitch * cj + lc.plane * ck;
+  const float exm = __ldg(pc + dn(cx, im)), exp_ = __ldg(pc + dn(cx, ip));
+  const float* Lx = a.f.L; const float* Ly = a.f.L + l.cstride; const float* Lz = a.f.L + 2 * l.cstride;
+  const F4 lx = ld4g(Lx + o); const float lx4 = __ldg(Lx + o + 4);
+  const F4 ly0 = ld4g(Ly + o), ly1 = ld4g(Ly + o + l.pitch), lz0 = ld4g(Lz + o), lz1 = ld4g(Lz + o + l.plane);
+  const F4 r0 = ld4(a.f.r + o), x0 = ld4(a.f.x + o);
+  F4 d0{{0.f, 0.f, 0.f, 0.f}};
+  if (a.write_eps) d0 = ld4g(a.f.iD + o);
+  F4 rn, xn, en;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float lxl = lx.v[q], lxu = q < 3 ? lx.v[q < 3 ? q + 1 : 3] : lx4;
+    const float el = q == 0 ? exm : e.v[q > 0 ? q - 1 : 0], er = q == 3 ? exp_ : e.v[q < 3 ? q + 1 : 3];
+    float dg = 0.f;
+    dg -= lxl + lxu; dg -= ly0.v[q] + ly1.v[q]; dg -= lz0.v[q] + lz1.v[q];
+    float s = e.v[q] * dg;
+    s += el * lxl + er * lxu;
+    s += eym.v[q] * ly0.v[q] + eyp.v[q] * ly1.v[q];
+    s += ezm.v[q] * lz0.v[q] + ezp.v[q] * lz1.v[q];
+    const float r = r0.v[q] - a.omega * s;
+    rn.v[q] = r;
+    xn.v[q] = x0.v[q] + a.omega * e.v[q];
+    en.v[q] = r * d0.v[q];
+  }
+  st4(a.f.r + o, rn);
+  st4(a.f.x + o, xn);
+  if (a.write_eps) {
+    st4(a.f.eps + o, en);
+    const bool seam = (a.per.p[0] && (i == 1 || i + 3 == l.n0 - 2)) || (a.per.p[1] && (j == 1 || j == l.n1 - 2)) ||
+                      (a.per.p[2] && (k == 1 || k == l.n2 - 2));
+    if (seam) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) store_images<3>(a.f.eps, l, a.per, i + q, j, k, en.v[q]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- K-DOWN, 4 cells per thread (see k_down)
+// Jacobi! (ϵ=r·iD, perBC!, increment! with ω=1) + restrict! + fill!(coarse.x,0), for levels coarsened
+// in every direction.  blockDim (32,4,2): the block's 128x4x2 cells are the children of 64x2x1 coarse cells.
+__global__ void __launch_bounds__(256) k_down4(const DownArgs a) {
+  __shared__ float tile[2][4][128];
+  const Lay& l = a.f.l;
+  const Lay& lc = a.c.l;
+  WL_QUAD_FROM_BLOCK(l)
+  double s1 = 0.0; float mx = -INFINITY;
+  float sh = 0.f;                                                      // residual mean to remove (first cycle only)
+  if (a.first) {
+    const float mean = (float)redin_sum(a.in) / (float)a.ncells;
+    if (fabsf(mean) > 2.f * 1.1920929e-07f) sh = mean;
+  }
+  F4 rn{{0.f, 0.f, 0.f, 0.f}};
+  if (inb) {
+    const int o = l.off(i, j, k);
+    int oxm, oxp, oym, oyp, ozm, ozp;
+    quad_nbr(l, a.per, i, j, k, oxm, oxp, oym, oyp, ozm, ozp);
+    const float* Lx = a.f.L; const float* Ly = a.f.L + l.cstride; const float* Lz = a.f.L + 2 * l.cstride;
+    const F4 lx = ld4g(Lx + o); const float lx4 = __ldg(Lx + o + 4);
+    const F4 ly0 = ld4g(Ly + o), ly1 = ld4g(Ly + o + l.pitch), lz0 = ld4g(Lz + o), lz1 = ld4g(Lz + o + l.plane);
+    F4 r = ld4g(a.f.r + o), rym = ld4g(a.f.r + o + oym), ryp = ld4g(a.f.r + o + oyp), rzm = ld4g(a.f.r + o + ozm),
+       rzp = ld4g(a.f.r + o + ozp);
+    float rxm = __ldg(a.f.r + o + oxm), rxp = __ldg(a.f.r + o + oxp);
+    const F4 d = ld4g(a.f.iD + o), dym = ld4g(a.f.iD + o + oym), dyp = ld4g(a.f.iD + o + oyp), dzm = ld4g(a.f.iD + o + ozm),
+             dzp = ld4g(a.f.iD + o + ozp);
+    const float dxm = __ldg(a.f.iD + o + oxm), dxp = __ldg(a.f.iD + o + oxp);
+    const F4 x0 = ld4(a.f.x + o);
+    if (sh != 0.f) {
+      // ghost neighbours of non-periodic directions are not shifted by the reference, but their iD and
+      // the face coefficient towards them are 0: they contribute a (signed) zero either way
+      rxm = rxm - sh; rxp = rxp - sh;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        r.v[q] = r.v[q] - sh; rym.v[q] = rym.v[q] - sh; ryp.v[q] = ryp.v[q] - sh; rzm.v[q] = rzm.v[q] - sh; rzp.v[q] = rzp.v[q] - sh;
+      }
+    }
+    F4 xn;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float lxl = lx.v[q], lxu = q < 3 ? lx.v[q < 3 ? q + 1 : 3] : lx4;
+      const float el = q == 0 ? rxm * dxm : r.v[q > 0 ? q - 1 : 0] * d.v[q > 0 ? q - 1 : 0];
+      const float er = q == 3 ? rxp * dxp : r.v[q < 3 ? q + 1 : 3] * d.v[q < 3 ? q + 1 : 3];
+      const float e0 = r.v[q] * d.v[q];                                // ϵ = r·iD  Poisson.jl:112
+      float dg = 0.f;
+      dg -= lxl + lxu; dg -= ly0.v[q] + ly1.v[q]; dg -= lz0.v[q] + lz1.v[q];
+      float s = e0 * dg;                                               // mult(I,L,D,ϵ)
+      s += el * lxl + er * lxu;
+      s += (rym.v[q] * dym.v[q]) * ly0.v[q] + (ryp.v[q] * dyp.v[q]) * ly1.v[q];
+      s += (rzm.v[q] * dzm.v[q]) * lz0.v[q] + (rzp.v[q] * dzp.v[q]) * lz1.v[q];
+      rn.v[q] = r.v[q] - s;                                            // increment!, ω = 1  Poisson.jl:102
+      xn.v[q] = x0.v[q] + e0;                                          // Poisson.jl:103
+      if (a.first) { s1 += (double)fabsf(r.v[q]); mx = fmaxf(mx, fabsf(r.v[q])); }
+    }
+    st4(a.f.eps + o, rn);          // neighbours still read r: the new residual is staged in ϵ (host swaps the pointers)
+    st4(a.f.x + o, xn);
+  }
+  {
+    float* t = &tile[threadIdx.z][threadIdx.y][4 * threadIdx.x];
+    t[0] = rn.v[0]; t[1] = rn.v[1]; t[2] = rn.v[2]; t[3] = rn.v[3];
+  }
+  __syncthreads();
+  if (inb && !(threadIdx.y & 1) && !(threadIdx.z & 1)) {             // first child in y and z: two coarse cells
+    const int cj = (j + 1) >> 1, ck = (k + 1) >> 1, c0 = (i + 1) >> 1;
+    const int oc = lc.off(c0, cj, ck);
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+      float sum = 0.f;                                                 // restrict  MLP.jl:13-19, first dimension fastest
+#pragma unroll
+      for (int kk = 0; kk < 2; ++kk)
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+          for (int ii = 0; ii < 2; ++ii) sum += tile[threadIdx.z + kk][threadIdx.y + jj][4 * threadIdx.x + 2 * p + ii];
+      a.c.r[oc + p] = sum;
+      a.c.x[oc + p] = 0.f;                                             // fill!(coarse.x,0)  MLP.jl:94
+    }
+  }
+  if (a.first) block_reduce_partial(s1, mx, a.w);
+}
+
+}  // namespace wl
