@@ -317,6 +317,7 @@ def main():
                 f.write(f"{name}\t{n}\t{ms:.4f}\t{ms / n * 1e3:.2f}\t{ms / ksum:.3f}\n")
 
     halo = sim.halo_stats()
+    halo_us = sim.halo_timing() if world > 1 else None
     nsteps_total = len(sim.pois.n) // 2
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -339,7 +340,7 @@ def main():
                        "poisson_iters_per_step": float(np.mean(n_iters)) * 2,
                        "l2": "working set (%.0f MB per GPU) exceeds L2, no flush" % (30 * 4 * cells / world / 1e6)
                              if cells / world > 1.5e6 else "fits L2"},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
+            "halo_us_per_exchange": halo_us, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
             "wall_ms_per_step": wall / args.steps * 1e3,
         }
         print(json.dumps(line), flush=True)

@@ -107,6 +107,9 @@ int wl_slab_info(const wl_sim* s, int32_t* rank, int32_t* nranks, int32_t* k_off
 int wl_halo_stats(const wl_sim* s, int64_t* exchanges, int64_t* bytes);
 /* 0 single GPU, 1 NCCL send/recv, 2 direct peer stores over NVLink (CUDA IPC; WL_NO_P2P=1 disables) */
 int wl_halo_transport(const wl_sim* s);
+/* peer-store halos: accumulated ns [waiting for the neighbours' ready, copy + fence, waiting for their done]
+ * and the number of exchanges, as seen by this rank's halo kernels */
+int wl_halo_timing(wl_sim* s, double out[4]);
 void wl_destroy(wl_sim* s);
 const char* wl_last_error(const wl_sim* s);   /* s may be NULL: last error of wl_create */
 int wl_version(void);

@@ -37,7 +37,7 @@ ABI_SYMBOLS = [
     "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
     "wl_cfl", "wl_pressure_force", "wl_sync", "wl_launch_count", "wl_enable_timing",
     "wl_last_phase_times", "wl_debug_op", "wl_prof_begin", "wl_prof_end", "wl_event_record",
-    "wl_event_elapsed_ms", "wl_create_slab", "wl_nccl_unique_id", "wl_slab_info", "wl_halo_stats", "wl_halo_transport",
+    "wl_event_elapsed_ms", "wl_create_slab", "wl_nccl_unique_id", "wl_slab_info", "wl_halo_stats", "wl_halo_transport", "wl_halo_timing",
 ]
 
 
@@ -91,6 +91,7 @@ def load_library(path=None):
     lib.wl_slab_info.argtypes = [P] + [C.POINTER(I)] * 5
     lib.wl_halo_stats.argtypes = [P, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     lib.wl_halo_transport.argtypes = [P]
+    lib.wl_halo_timing.argtypes = [P, C.POINTER(C.c_double * 4)]
     lib.wl_destroy.argtypes = [P]
     lib.wl_destroy.restype = None
     lib.wl_last_error.argtypes = [P]
@@ -459,6 +460,13 @@ class Simulation:
 
     def halo_transport(self):
         return {0: "none", 1: "nccl", 2: "p2p"}.get(self.lib.wl_halo_transport(self.h), "?")
+
+    def halo_timing(self):
+        """peer-store halos: mean µs per exchange spent [waiting for ready, copying, waiting for done], count."""
+        out = (C.c_double * 4)()
+        self._check(self.lib.wl_halo_timing(self.h, C.byref(out)))
+        n = max(out[3], 1.0)
+        return [out[0] / n / 1e3, out[1] / n / 1e3, out[2] / n / 1e3, int(out[3])]
 
     def halo_stats(self):
         """(number of halo exchanges, bytes sent) since creation."""

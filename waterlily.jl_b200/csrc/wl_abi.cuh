@@ -310,6 +310,17 @@ int wl_slab_info(const wl_sim* s, int32_t* rank, int32_t* nranks, int32_t* k_off
   return WL_OK;
 }
 int wl_halo_transport(const wl_sim* s) { return s ? (s->dist.n > 1 ? (s->p2p ? 2 : 1) : 0) : -1; }
+int wl_halo_timing(wl_sim* s, double out[4]) {
+  if (!s || !out) return WL_ERR_INVALID;
+  for (int q = 0; q < 4; ++q) out[q] = 0.0;
+  if (!s->p2p) return WL_OK;
+  cudaSetDevice(s->device);
+  unsigned long long st[4];
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  WL_CUDA(s, cudaMemcpy(st, s->arena + 16 * sizeof(unsigned int), sizeof(st), cudaMemcpyDeviceToHost));
+  for (int q = 0; q < 4; ++q) out[q] = (double)st[q];
+  return WL_OK;
+}
 int wl_halo_stats(const wl_sim* s, int64_t* exchanges, int64_t* bytes) {
   if (!s) return WL_ERR_INVALID;
   if (exchanges) *exchanges = s->halo_msgs;

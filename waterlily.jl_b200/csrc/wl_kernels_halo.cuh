@@ -53,9 +53,13 @@ __device__ __forceinline__ bool wait_flag(const unsigned int* p, unsigned int se
   return true;
 }
 
+// a.my + 16 (as unsigned long long[4]): accumulated ns spent waiting for ready / copying+fencing / waiting for
+// done, and the number of exchanges (read by wl_halo_stats; block 0 / the last block only)
 __global__ void __launch_bounds__(256) k_halo_p2p(const HaloP2PArgs a) {
   __shared__ int last;
   const int tid = threadIdx.x;
+  unsigned long long* stat = reinterpret_cast<unsigned long long*>(a.my + 16);
+  const unsigned long long t_start = wl_now_ns();
   if (tid == 0) {
     if (blockIdx.x == 0) {
       if (a.use_lo) st_release_sys(a.nb_lo + 1, a.seq_lo);
@@ -65,14 +69,31 @@ __global__ void __launch_bounds__(256) k_halo_p2p(const HaloP2PArgs a) {
     if (a.use_hi) wait_flag(a.my + 1, a.seq_hi, a.my + 5);
   }
   __syncthreads();
+  const unsigned long long t_ready = wl_now_ns();
+  if (tid == 0 && blockIdx.x == 0) atomicAdd(stat + 0, t_ready - t_start);
   const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long gt = (long long)blockIdx.x * blockDim.x + tid;
   for (int sgi = 0; sgi < a.nseg; ++sgi) {
     const float* __restrict__ src = a.seg[sgi].src;
     float* __restrict__ dst = a.seg[sgi].dst;
-    for (long long e = (long long)blockIdx.x * blockDim.x + tid; e < a.cnt; e += stride) dst[e] = src[e];
+    // planes start 124 bytes past a 128-byte boundary (wl_common.cuh): one scalar, then aligned 16-byte
+    // stores (source and destination share the layout, hence the alignment), then the tail
+    const long long head = (4 - (((uintptr_t)src >> 2) & 3)) & 3;
+    const long long nv = (a.cnt - head) / 4, tail0 = head + 4 * nv;
+    if (((uintptr_t)src & 3) == 0 && ((((uintptr_t)src >> 2) & 3) == (((uintptr_t)dst >> 2) & 3))) {
+      if (gt < head) dst[gt] = src[gt];
+      const float4* s4 = reinterpret_cast<const float4*>(src + head);
+      float4* d4 = reinterpret_cast<float4*>(dst + head);
+      for (long long e = gt; e < nv; e += stride) d4[e] = s4[e];
+      if (gt < a.cnt - tail0) dst[tail0 + gt] = src[tail0 + gt];
+    } else {
+      for (long long e = gt; e < a.cnt; e += stride) dst[e] = src[e];
+    }
   }
-  __threadfence_system();
+  // one system-scope fence per block: the barrier orders the block's stores before thread 0's fence,
+  // and the fence is cumulative (per-thread membar.sys cost ~10 µs per exchange)
   __syncthreads();
+  if (tid == 0) __threadfence_system();
   if (tid == 0) last = atomicAdd(a.my + 4, 1u) == gridDim.x - 1;
   __syncthreads();
   if (!last || tid != 0) return;
@@ -80,8 +101,13 @@ __global__ void __launch_bounds__(256) k_halo_p2p(const HaloP2PArgs a) {
   __threadfence_system();
   if (a.use_lo) st_release_sys(a.nb_lo + 3, a.seq_lo);
   if (a.use_hi) st_release_sys(a.nb_hi + 2, a.seq_hi);
+  const unsigned long long t_copied = wl_now_ns();
   if (a.use_lo) wait_flag(a.my + 2, a.seq_lo, a.my + 5);
   if (a.use_hi) wait_flag(a.my + 3, a.seq_hi, a.my + 5);
+  const unsigned long long t_done = wl_now_ns();
+  atomicAdd(stat + 1, t_copied - t_ready);
+  atomicAdd(stat + 2, t_done - t_copied);
+  atomicAdd(stat + 3, 1ull);
 }
 
 }  // namespace wl
