@@ -342,6 +342,7 @@ void wl_destroy(wl_sim* s) {
   }
   if (s->dist.comm) ncclCommDestroy(s->dist.comm);
   if (s->d_redg) cudaFree(s->d_redg);
+  if (s->stage) cudaFree(s->stage);
   if (s->h_redg) cudaFreeHost(s->h_redg);
   for (size_t l = 0; l < s->lv.size(); ++l) {
     Level& v = s->lv[l];
@@ -387,15 +388,34 @@ static int xfer(wl_sim* s, int field, int level, float* host, size_t count, bool
   const size_t per = (size_t)lay.n0 * lay.n1 * lay.n2;
   if (count != per * f->ncomp) return fail(s, WL_ERR_INVALID, "host buffer has the wrong number of elements");
   WL_CUDA(s, cudaStreamSynchronize(s->st));
-  for (int c = 0; c < f->ncomp; ++c) {
-    float* dev = f->base + lay.cstride * c;
-    float* h = host + per * c;
-    if (up)
-      WL_CUDA(s, cudaMemcpy2DAsync(dev, lay.pitch * sizeof(float), h, lay.n0 * sizeof(float), lay.n0 * sizeof(float),
-                                   (size_t)lay.n1 * lay.n2, cudaMemcpyHostToDevice, s->st));
-    else
-      WL_CUDA(s, cudaMemcpy2DAsync(h, lay.n0 * sizeof(float), dev, lay.pitch * sizeof(float), lay.n0 * sizeof(float),
-                                   (size_t)lay.n1 * lay.n2, cudaMemcpyDeviceToHost, s->st));
+  const size_t bytes = count * sizeof(float);
+  if (s->stage_bytes < bytes) {
+    if (s->stage) cudaFree(s->stage);
+    s->stage = nullptr; s->stage_bytes = 0;
+    if (cudaMalloc(&s->stage, bytes) == cudaSuccess) s->stage_bytes = bytes; else cudaGetLastError();
+  }
+  if (s->stage) {
+    // one contiguous DMA + a repack kernel (pinned host memory runs at the PCIe rate)
+    PackArgs pa{lay, f->base, s->stage, f->ncomp, up ? 1 : 0};
+    const unsigned nb = (unsigned)std::min<size_t>((count + 1023) / 1024, 148 * 16);
+    if (up) {
+      WL_CUDA(s, cudaMemcpyAsync(s->stage, host, bytes, cudaMemcpyHostToDevice, s->st));
+      LAUNCH(s, k_repack, dim3(nb), dim3(256), pa);
+    } else {
+      LAUNCH(s, k_repack, dim3(nb), dim3(256), pa);
+      WL_CUDA(s, cudaMemcpyAsync(host, s->stage, bytes, cudaMemcpyDeviceToHost, s->st));
+    }
+  } else {
+    for (int c = 0; c < f->ncomp; ++c) {
+      float* dev = f->base + lay.cstride * c;
+      float* h = host + per * c;
+      if (up)
+        WL_CUDA(s, cudaMemcpy2DAsync(dev, lay.pitch * sizeof(float), h, lay.n0 * sizeof(float), lay.n0 * sizeof(float),
+                                     (size_t)lay.n1 * lay.n2, cudaMemcpyHostToDevice, s->st));
+      else
+        WL_CUDA(s, cudaMemcpy2DAsync(h, lay.n0 * sizeof(float), dev, lay.pitch * sizeof(float), lay.n0 * sizeof(float),
+                                     (size_t)lay.n1 * lay.n2, cudaMemcpyDeviceToHost, s->st));
+    }
   }
   if (up && s->dist.n > 1 && (field < 10 || s->lv[level].dist)) {
     // the caller's slab carries one ghost plane; deeper halo planes come from the neighbours

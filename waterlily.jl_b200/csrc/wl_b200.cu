@@ -82,6 +82,8 @@ struct wl_sim {
   char* peer_lo = nullptr; char* peer_hi = nullptr;   // neighbours' arenas mapped with cudaIpcOpenMemHandle
   bool p2p = false;
   unsigned int seq_lo = 0, seq_hi = 0;                // exchanges done on the lower / upper link
+  float* stage = nullptr;     // packed device buffer for upload/download (grown on demand)
+  size_t stage_bytes = 0;
   Red* d_redg = nullptr;      // all-gathered reduction slots [rank][NRED]
   Red* h_redg = nullptr;
   int64_t halo_msgs = 0, halo_bytes = 0;

@@ -175,4 +175,23 @@ __global__ void __launch_bounds__(256) k_sum_all(const SumArgs a) {
   block_reduce_finish(s, -INFINITY, a.w, a.out);
 }
 
+// ---------------------------------------------------------------- host <-> device repacking
+// The C ABI moves fields in the reference's dense layout (n0,n1,n2[,comp]); one contiguous DMA to or
+// from a packed device buffer plus this kernel replaces a strided cudaMemcpy2D per component (whose
+// 520-byte rows ran at a fraction of the PCIe rate).
+struct PackArgs { Lay l; float* field; float* packed; int ncomp; int to_field; };
+__global__ void __launch_bounds__(256) k_repack(const PackArgs a) {
+  const Lay& l = a.l;
+  const long long per = (long long)l.n0 * l.n1 * l.n2, tot = per * a.ncomp;
+  for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < tot; q += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(q / per);
+    long long r = q - c * per;
+    const int k = (int)(r / ((long long)l.n0 * l.n1));
+    r -= (long long)k * l.n0 * l.n1;
+    const int j = (int)(r / l.n0), i = (int)(r - (long long)j * l.n0);
+    float* f = a.field + l.cstride * c + l.off(i, j, k);
+    if (a.to_field) *f = a.packed[q]; else a.packed[q] = *f;
+  }
+}
+
 }  // namespace wl
