@@ -86,16 +86,36 @@ struct B200Flow{D,T} <: AbstractFlow{D,T}
 end
 const SCHEME = Dict(WaterLily.quick => 0, WaterLily.cds => 1, WaterLily.vanLeer => 2)
 
-"`flow_ctor` for `Simulation` (reference src/Flow.jl:133-147)."
+# ---- multi-GPU: one Julia process per GPU (e.g. MPI.jl or Distributed), slabs along the last dimension.
+# `comm = (rank, nranks, id)`; rank 0 obtains `id = nccl_unique_id()` and ships the 128 bytes to the
+# other ranks with whatever transport the host program uses (MPI.Bcast!, a file, a socket).
+struct WLDist; rank::Int32; nranks::Int32; id::NTuple{128,UInt8}; end
+function nccl_unique_id()
+    id = Ref(ntuple(_ -> 0x00, 128))
+    ccall((:wl_nccl_unique_id, LIB), Cint, (Ref{NTuple{128,UInt8}},), id) == 0 || error("wl_nccl_unique_id: ", lasterr(C_NULL))
+    id[]
+end
+
+"`flow_ctor` for `Simulation` (reference src/Flow.jl:133-147).  With `comm`, `N` is the GLOBAL grid and the
+returned flow holds this rank's slab: arrays have `N[end]÷nranks+2` planes and `loc` is offset by the slab origin."
 function B200Flow(N::NTuple{D}, uBC; Δt=0.25, ν=0., g=nothing, u0=nothing, uλ=nothing, perdir=(), exitBC=false,
-                  λ=WaterLily.quick, T=Float32, mem=Array, device=0) where D
+                  λ=WaterLily.quick, T=Float32, mem=Array, device=0, comm=nothing) where D
     T == Float32 || error("WL_ERR_UNSUPPORTED: the B200 path is Float32 only")
     (uBC isa Function || g isa Function) && error("WL_ERR_UNSUPPORTED: Function uBC / g cannot cross the C ABI")
     haskey(SCHEME, λ) || error("WL_ERR_UNSUPPORTED: λ must be quick, cds or vanLeer")
     cfg = Ref(WLConfig(D, pad3(Int32.(N), Int32(0)), ntuple(i -> Int32(i in perdir), 3), exitBC, SCHEME[λ], ν, Δt,
                        pad3(Float32.(uBC), 0f0), 10, 2f-3, 32, device, 0))
     out = Ref{Ptr{Cvoid}}(C_NULL)
-    rc = ccall((:wl_create, LIB), Cint, (Ref{WLConfig}, Ref{Ptr{Cvoid}}), cfg, out)
+    koff = 0
+    if isnothing(comm) || comm[2] == 1
+        rc = ccall((:wl_create, LIB), Cint, (Ref{WLConfig}, Ref{Ptr{Cvoid}}), cfg, out)
+    else
+        rank, nranks, id = comm
+        rc = ccall((:wl_create_slab, LIB), Cint, (Ref{WLConfig}, Ref{WLDist}, Ref{Ptr{Cvoid}}),
+                   cfg, Ref(WLDist(rank, nranks, id)), out)
+        koff = rank * (N[end] ÷ nranks)
+        N = (N[1:end-1]..., N[end] ÷ nranks)           # everything below is the local slab
+    end
     rc == 0 || error("wl_create ($rc): ", lasterr(C_NULL))
     h = Handle(out[]); Ng = N .+ 2
     arr(f, dims) = B200Array{T,length(dims)}(h, Int32(f), Int32(0), dims)
@@ -105,7 +125,8 @@ function B200Flow(N::NTuple{D}, uBC; Δt=0.25, ν=0., g=nothing, u0=nothing, uλ
     u0 = isnothing(u0) ? uλ : u0
     if !isnothing(u0)                                  # apply!(u0,u) on the host, then BC!/exitBC!/u⁰ on the device
         host = Array{T}(undef, Ng..., D)
-        u0 isa Function ? WaterLily.apply!(u0, host) : WaterLily.apply!((i, x) -> u0[i], host)
+        shift(x) = x .+ ntuple(d -> d == D ? T(koff) : zero(T), D)        # slab origin in the global grid
+        u0 isa Function ? WaterLily.apply!((i, x) -> u0(i, shift(x)), host) : WaterLily.apply!((i, x) -> u0[i], host)
         copyto!(flow.u, host)
         check(h, ccall((:wl_finish_ic, LIB), Cint, (Ptr{Cvoid}, Ref{NTuple{3,Float32}}), h.ptr, Ref(pad3(Float32.(uBC), 0f0))))
     end
