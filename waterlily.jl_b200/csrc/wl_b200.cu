@@ -534,6 +534,23 @@ void coarse_block(wl_sim* s, size_t first, float w) {
   CoarseArgs a{};
   for (size_t l = 0; l < s->lv.size() && l < (size_t)WL_MAXLEV; ++l) a.lv[l] = levdev(s->lv[l]);
   a.first = (int)first; a.nlev = (int)s->lv.size(); a.per = s->per_glob; a.omega = w;
+  const size_t smem = coarse_smem_bytes(a, s->D);
+  static const bool nosm = getenv("WL_NO_COARSE_SMEM") != nullptr;
+  if (!nosm && smem <= 200 * 1024) {                 // every array of the small levels fits in shared memory
+    static bool attr = false;
+    if (!attr) {
+      cudaFuncSetAttribute(k_coarse_sm<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      cudaFuncSetAttribute(k_coarse_sm<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      attr = true;
+    }
+    cudaEvent_t pa_, pb_;
+    const bool prof_ = prof_pre(s, "k_coarse_sm", &pa_, &pb_);
+    if (s->D == 3) k_coarse_sm<3><<<1, 1024, smem, s->st>>>(a);
+    else k_coarse_sm<2><<<1, 1024, smem, s->st>>>(a);
+    if (prof_) prof_post(s, "k_coarse_sm", pa_, pb_);
+    ++s->launches;
+    return;
+  }
   DISPATCH_D(s, k_coarse, dim3(1), dim3(1024), a);
 }
 // first: the top level's residual still needs its mean removed; K-DOWN does it on the fly and leaves the
