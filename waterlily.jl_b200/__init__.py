@@ -77,7 +77,7 @@ def load_library(path=None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    path = path or _LIBNAME
+    path = path or os.environ.get("WL_B200_LIB") or _LIBNAME   # WL_B200_LIB: an alternative build of the same ABI
     if not os.path.exists(path):
         raise WaterLilyB200Error(
             f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "

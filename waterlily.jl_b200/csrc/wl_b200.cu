@@ -534,9 +534,14 @@ void coarse_block(wl_sim* s, size_t first, float w) {
   CoarseArgs a{};
   for (size_t l = 0; l < s->lv.size() && l < (size_t)WL_MAXLEV; ++l) a.lv[l] = levdev(s->lv[l]);
   a.first = (int)first; a.nlev = (int)s->lv.size(); a.per = s->per_glob; a.omega = w;
-  const size_t smem = coarse_smem_bytes(a, s->D);
-  static const bool nosm = getenv("WL_NO_COARSE_SMEM") != nullptr;
-  if (!nosm && smem <= 200 * 1024) {                 // every array of the small levels fits in shared memory
+  // stage as many of the smallest levels in shared memory as fit the budget (WL_COARSE_SMEM_KB, default 200)
+  static const int budget_kb = getenv("WL_COARSE_SMEM_KB") ? atoi(getenv("WL_COARSE_SMEM_KB")) : 200;
+  const size_t budget = (size_t)std::min(std::max(budget_kb, 0), 200) * 1024;
+  int from = a.nlev;
+  while (from > a.first && coarse_smem_bytes(a, s->D, from - 1) <= budget) --from;
+  a.stage_from = from;
+  const size_t smem = coarse_smem_bytes(a, s->D, from);
+  if (from < a.nlev) {
     static bool attr = false;
     if (!attr) {
       cudaFuncSetAttribute(k_coarse_sm<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
@@ -719,6 +724,10 @@ void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, c
   a.per = s->per; a.nu = s->cfg.nu; a.dt = s->dt; a.corrector = corrector;
   for (int d = 0; d < 3; ++d) a.acc.v[d] = acc ? acc[d] : 0.f;
   const Lay& l = s->lay;
+  for (int c = 0; c < 3; ++c) {
+    const long long oc = l.cstride * c;
+    a.uac[c] = a.ua + oc; a.u0c[c] = a.u0 + oc; a.Vc[c] = a.V + oc; a.m0c[c] = a.mu0 + oc; a.unc[c] = a.un + oc;
+  }
   // march length: as long as possible (amortises the extra flux plane) while keeping >= 6 waves of
   // 2 blocks/SM on 148 SMs
   a.KZ = 64;

@@ -419,6 +419,7 @@ constexpr int WL_MAXLEV = 12;
 struct CoarseArgs {
   LevDev lv[WL_MAXLEV];
   int first, nlev;     // levels first..nlev-1 are processed here
+  int stage_from;      // k_coarse_sm: levels stage_from..nlev-1 live in shared memory
   Per per;
   float omega;
 };
@@ -426,13 +427,16 @@ template <int D, class F>
 __device__ __forceinline__ void for_inside(const Lay& l, F f) {
   const int m0 = l.n0 - 2, m1 = l.n1 - 2, m2 = D == 3 ? l.n2 - 2 : 1;
   const int tot = m0 * m1 * m2;
+  // q < 2^21: (q+0.5)*(1/m) truncates to q/m exactly, and costs 3 instructions instead of ~40
+  const float im0 = 1.0f / (float)m0, im1 = 1.0f / (float)m1;
   for (int q = threadIdx.x; q < tot; q += blockDim.x) {
-    const int i = 1 + q % m0, t = q / m0, j = 1 + t % m1, k = D == 3 ? 1 + t / m1 : 0;
+    const int t = (int)(((float)q + 0.5f) * im0), i = 1 + q - t * m0;
+    const int tk = D == 3 ? (int)(((float)t + 0.5f) * im1) : 0, j = 1 + t - tk * m1, k = D == 3 ? 1 + tk : 0;
     f(i, j, k, l.off(i, j, k));
   }
 }
 template <int D>
-__device__ void blk_smooth(const LevDev& p, const Per& per, float w) {
+__device__ __forceinline__ void blk_smooth(const LevDev& p, const Per& per, float w) {
   const Lay& l = p.l;
   for_inside<D>(l, [&](int i, int j, int k, int o) {
     const float e = p.r[o] * p.iD[o];
@@ -471,8 +475,8 @@ template <int D>
 __device__ __forceinline__ void coarse_body(const LevDev* lv, int first, int nlev, const Per& per, float omega) {
   const int last = nlev - 1;
   for (int lev = first; lev < last; ++lev) {              // way down: Jacobi!, restrict!, fill!(x,0)
-    const LevDev& f = lv[lev];
-    const LevDev& c = lv[lev + 1];
+    const LevDev f = lv[lev];
+    const LevDev c = lv[lev + 1];
     const Lay& l = f.l;
     for_inside<D>(l, [&](int i, int j, int k, int o) { f.eps[o] = f.r[o] * f.iD[o]; });
     __syncthreads();
@@ -502,8 +506,8 @@ __device__ __forceinline__ void coarse_body(const LevDev* lv, int first, int nle
     __syncthreads();
   }
   for (int lev = last - 1; lev >= first; --lev) {         // way up: smooth!(coarse), prolongate!, increment!
-    const LevDev& f = lv[lev];
-    const LevDev& c = lv[lev + 1];
+    const LevDev f = lv[lev];
+    const LevDev c = lv[lev + 1];
     blk_smooth<D>(c, per, omega);
     const Lay& l = f.l;
     for_inside<D>(l, [&](int i, int j, int k, int o) {
@@ -519,7 +523,7 @@ __device__ __forceinline__ void coarse_body(const LevDev* lv, int first, int nle
     });
     __syncthreads();
   }
-  blk_smooth<D>(lv[first], per, omega);
+  { const LevDev f = lv[first]; blk_smooth<D>(f, per, omega); }
 }
 template <int D>
 __global__ void __launch_bounds__(1024) k_coarse(const CoarseArgs a) {
@@ -530,9 +534,9 @@ __global__ void __launch_bounds__(1024) k_coarse(const CoarseArgs a) {
 // ~40 phases of the recursion are separated by __syncthreads only, instead of a round trip to L2 each
 // (57 -> ~12 µs for the 18³..4³ tail of a 128³ grid).  L, iD, r, x are copied in (ghosts included), x, r, ϵ
 // are copied back, so the data surface sees exactly what the global-memory version leaves.
-inline size_t coarse_smem_bytes(const CoarseArgs& a, int D) {
+inline size_t coarse_smem_bytes(const CoarseArgs& a, int D, int from) {
   size_t cells = 0;
-  for (int l = a.first; l < a.nlev; ++l) cells += (size_t)a.lv[l].l.n0 * a.lv[l].l.n1 * a.lv[l].l.n2;
+  for (int l = from; l < a.nlev; ++l) cells += (size_t)a.lv[l].l.n0 * a.lv[l].l.n1 * a.lv[l].l.n2;
   return cells * (D + 4) * sizeof(float);
 }
 template <int D>
@@ -541,7 +545,8 @@ __global__ void __launch_bounds__(1024) k_coarse_sm(const CoarseArgs a) {
   __shared__ LevDev slv[WL_MAXLEV];
   if (threadIdx.x == 0) {
     float* p = csm;
-    for (int l = a.first; l < a.nlev; ++l) {
+    for (int l = a.first; l < a.stage_from; ++l) slv[l] = a.lv[l];
+    for (int l = a.stage_from; l < a.nlev; ++l) {
       LevDev d = a.lv[l];
       const int n = d.l.n0 * d.l.n1 * d.l.n2;
       d.l.pitch = d.l.n0; d.l.plane = d.l.n0 * d.l.n1; d.l.cstride = n;
@@ -554,12 +559,13 @@ __global__ void __launch_bounds__(1024) k_coarse_sm(const CoarseArgs a) {
     }
   }
   __syncthreads();
-  for (int l = a.first; l < a.nlev; ++l) {
-    const LevDev& g = a.lv[l];
-    const LevDev& s = slv[l];
+  for (int l = a.stage_from; l < a.nlev; ++l) {
+    const LevDev g = a.lv[l];
+    const LevDev s = slv[l];
     const int n0 = g.l.n0, n01 = g.l.n0 * g.l.n1, n = n01 * g.l.n2;
+    const float in01 = 1.0f / (float)n01, in0 = 1.0f / (float)n0;
     for (int q = threadIdx.x; q < n; q += blockDim.x) {
-      const int k = q / n01, r = q - k * n01, j = r / n0, i = r - j * n0;
+      const int k = (int)(((float)q + 0.5f) * in01), r = q - k * n01, j = (int)(((float)r + 0.5f) * in0), i = r - j * n0;
       const int o = g.l.off(i, j, k);
 #pragma unroll
       for (int d = 0; d < D; ++d) const_cast<float*>(s.L)[n * d + q] = g.L[g.l.cstride * d + o];
@@ -569,12 +575,13 @@ __global__ void __launch_bounds__(1024) k_coarse_sm(const CoarseArgs a) {
   }
   __syncthreads();
   coarse_body<D>(slv, a.first, a.nlev, a.per, a.omega);
-  for (int l = a.first; l < a.nlev; ++l) {
-    const LevDev& g = a.lv[l];
-    const LevDev& s = slv[l];
+  for (int l = a.stage_from; l < a.nlev; ++l) {
+    const LevDev g = a.lv[l];
+    const LevDev s = slv[l];
     const int n0 = g.l.n0, n01 = g.l.n0 * g.l.n1, n = n01 * g.l.n2;
+    const float in01 = 1.0f / (float)n01, in0 = 1.0f / (float)n0;
     for (int q = threadIdx.x; q < n; q += blockDim.x) {
-      const int k = q / n01, r = q - k * n01, j = r / n0, i = r - j * n0;
+      const int k = (int)(((float)q + 0.5f) * in01), r = q - k * n01, j = (int)(((float)r + 0.5f) * in0), i = r - j * n0;
       const int o = g.l.off(i, j, k);
       g.x[o] = s.x[q]; g.r[o] = s.r[q]; g.eps[o] = s.eps[q];
     }

@@ -21,6 +21,8 @@
 // algorithmic B/cell); the few cells in the body band are recomputed afterwards by k_mom_patch
 // from the exact reference formula, f-neighbours on ghost rows included (Flow.jl:20-26,179).
 #pragma once
+#include <type_traits>
+
 #include "wl_kernels_mom.cuh"
 
 namespace wl {
@@ -57,6 +59,32 @@ __device__ __forceinline__ float flux_v(float um2, float um1, float uc, float up
   return ua * v - nu * (uc - um1);
 }
 
+// Branch-free x/6 for the marching kernel: the Markstein quotient of div6 for every x (exact zeros
+// pass through with their sign), while the smallest non-zero and the largest |x| seen are recorded in
+// amin/amax.  The caller re-evaluates the plane's fluxes with div6 when any |x| fell outside
+// (1e-30, 1e38), so the nine face fluxes of a cell form one straight-line block that the scheduler can
+// interleave.  Exact zeros must stay on this path: early in a run whole regions hold u_y = u_z = 0.
+__device__ __forceinline__ float div6_track(float x, float& amin, float& amax) {
+  const float ax = fabsf(x);
+  const bool z = x == 0.f;
+  amax = fmaxf(amax, ax);
+  amin = fminf(amin, z ? 1.f : ax);
+  const float y = 1.0f / 6.0f;
+  const float q0 = __fmul_rn(x, y);
+  const float r = __fmaf_rn(-6.0f, q0, x);
+  return z ? x : __fmaf_rn(r, y, q0);
+}
+template <int S, bool EXACT>
+__device__ __forceinline__ float flux_q(float um2, float um1, float uc, float up1, float ua, float nu, int kind,
+                                        float& amin, float& amax) {
+  if (S != 0 || EXACT) return flux_v<S>(um2, um1, uc, up1, ua, nu, kind);
+  const bool pos = ua > 0.f;
+  const float u = pos ? um2 : up1, c = pos ? um1 : uc, d = pos ? uc : um1;
+  float v = med3(div6_track(5.f * c + 2.f * d - u, amin, amax), c, med3(10.f * c - 9.f * u, c, d));
+  if ((kind == 1 && pos) || (kind == 3 && ua < 0.f)) v = (uc + um1) / 2.f;
+  return ua * v - nu * (uc - um1);
+}
+
 struct Mom3Args {
   Lay l;
   const float* ua;    // advecting velocity: u⁰ (predictor) / projected u (corrector)
@@ -64,6 +92,8 @@ struct Mom3Args {
   const float* V;
   const float* mu0;
   float* un;          // output velocity buffer (distinct from ua and u0)
+  // the same arrays per component (base + cstride·c), so every address is constant-bank base + offset
+  const float* uac[3]; const float* u0c[3]; const float* Vc[3]; const float* m0c[3]; float* unc[3];
   Per per;
   float nu, dt;
   Vec3 acc;
@@ -73,127 +103,10 @@ struct Mom3Args {
 
 constexpr int M3_TY = 8;
 
-template <int S, bool FAST>
-__device__ __forceinline__ void mom3_body(const Mom3Args& a, float (*shy)[3][M3_TY][32]) {
-  const Lay& l = a.l;
-  const int lane = threadIdx.x, ty = threadIdx.y;
-  const int N0 = l.n0, N1 = l.n1, N2 = l.n2;
-  const int pitch = l.pitch, plane = l.plane;
-  const int i_raw = 1 + 31 * blockIdx.x + lane, j_raw = 1 + (M3_TY - 1) * blockIdx.y + ty;
-  const int i = FAST ? i_raw : min(i_raw, N0 - 1), j = FAST ? j_raw : min(j_raw, N1 - 1);
-  const int k0 = 1 + a.KZ * blockIdx.z;
-  const int kend = min(k0 + a.KZ, N2 - 1);           // last plane visited: only Φ_z is needed there
-  const bool out_ij = lane < 31 && ty < M3_TY - 1 && (FAST || (i_raw <= N0 - 2 && j_raw <= N1 - 2));
-  const int oij = i + pitch * j;
-  // in-plane neighbour offsets; in the general body they are clamped (clamped values are never
-  // consumed: boundary faces use the one-sided variants)
-  const int dx0 = FAST ? -2 : max(i - 2, 0) - i, dx2 = FAST ? 1 : min(i + 1, N0 - 1) - i;
-  const int dy0 = FAST ? -2 * pitch : (max(j - 2, 0) - j) * pitch, dy1 = -pitch,
-            dy2 = FAST ? pitch : (min(j + 1, N1 - 1) - j) * pitch;
-  const bool p0 = a.per.p[0] != 0, p1 = a.per.p[1] != 0, p2 = a.per.p[2] != 0;
-  const int klo = a.per.zlo ? -1 : 0, khi = a.per.zhi ? N2 : N2 - 1;   // readable plane range (slab halos)
-  const int kx = FAST ? 0 : (i == 1 ? (p0 ? 2 : 1) : (i == N0 - 1 ? (p0 ? 4 : 3) : 0));
-  const int ky = FAST ? 0 : (j == 1 ? (p1 ? 2 : 1) : (j == N1 - 1 ? (p1 ? 4 : 3) : 0));
-  const float* U[3] = {a.ua, a.ua + l.cstride, a.ua + 2 * l.cstride};
-  const float* pc[3];
-#pragma unroll
-  for (int c = 0; c < 3; ++c) pc[c] = U[c] + (oij + plane * k0);
-  const float nu = a.nu;
-
-  float w[3][4];   // own column: planes k-2, k-1, k, k+1
-#pragma unroll
-  for (int c = 0; c < 3; ++c) {
-    w[c][0] = pc[c][plane * (max(k0 - 2, klo) - k0)];
-    w[c][1] = pc[c][-plane];
-    w[c][2] = pc[c][0];
-    w[c][3] = pc[c][plane * (min(k0 + 1, khi) - k0)];
-  }
-  float pend[3] = {0.f, 0.f, 0.f};
-
-  for (int k = k0; k <= kend; ++k) {
-    const bool lastp = k == kend;
-    const int kz = k == 1 ? (a.per.zlo ? 0 : (p2 ? 2 : 1)) : (k == N2 - 1 ? (a.per.zhi ? 0 : (p2 ? 4 : 3)) : 0);
-    float nb[3][3][3];   // nb[c][d][m2,m1,p1]
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      nb[c][2][0] = w[c][0]; nb[c][2][1] = w[c][1]; nb[c][2][2] = w[c][3];
-      if (!lastp) {
-        nb[c][0][0] = pc[c][dx0]; nb[c][0][1] = pc[c][-1]; nb[c][0][2] = pc[c][dx2];
-        nb[c][1][0] = pc[c][dy0]; nb[c][1][1] = pc[c][dy1]; nb[c][1][2] = pc[c][dy2];
-      } else {
-#pragma unroll
-        for (int q = 0; q < 3; ++q) { nb[c][0][q] = 0.f; nb[c][1][q] = 0.f; }
-      }
-    }
-    if (lastp) { nb[2][0][1] = pc[2][-1]; nb[2][1][1] = pc[2][dy1]; }   // for ū of the z faces
-    float F[3][3];
-#pragma unroll
-    for (int ci = 0; ci < 3; ++ci) {
-#pragma unroll
-      for (int dj = 0; dj < 3; ++dj) {
-        if (lastp && dj < 2) { F[ci][dj] = 0.f; continue; }
-        const int kind = dj == 0 ? kx : (dj == 1 ? ky : kz);
-        const int sdj = dj == 0 ? 1 : (dj == 1 ? pitch : plane);
-        const int Ndj = dj == 0 ? N0 : (dj == 1 ? N1 : N2);
-        if (kind == 4) {                                     // periodic upper face == Φ of the wrapped cell
-          const int sci = ci == 0 ? 1 : (ci == 1 ? pitch : plane);
-          const int o = oij + plane * k;
-          F[ci][dj] = face_flux<S>(U[ci], U[dj], o - sdj * (Ndj - 2), sci, sdj, 1, Ndj, true, nu);
-        } else {
-          const float ua = (w[dj][2] + nb[dj][ci][1]) / 2.f;  // ϕ(i,CI(I,j),u) Flow.jl:3
-          float um2 = nb[ci][dj][0];
-          if (kind == 2) um2 = pc[ci][sdj * (Ndj - 4)];       // CIj(j,·,N[j]-2) Flow.jl:61
-          F[ci][dj] = flux_v<S>(um2, nb[ci][dj][1], w[ci][2], nb[ci][dj][2], ua, nu, kind);
-        }
-      }
-    }
-    float Fxu[3], Fyu[3];
-    if (!lastp) {
-      const int buf = k & 1;
-#pragma unroll
-      for (int ci = 0; ci < 3; ++ci) {
-        Fxu[ci] = __shfl_down_sync(0xffffffffu, F[ci][0], 1);
-        shy[buf][ci][ty][lane] = F[ci][1];
-      }
-      __syncthreads();
-#pragma unroll
-      for (int ci = 0; ci < 3; ++ci) Fyu[ci] = shy[buf][ci][min(ty + 1, M3_TY - 1)][lane];
-    }
-    if (k > k0 && out_ij) {                                  // finalise cell (i,j,k-1)
-      const int op = oij + plane * (k - 1);
-#pragma unroll
-      for (int ci = 0; ci < 3; ++ci) {
-        float r = pend[ci] - F[ci][2];
-        r += a.acc.v[ci];
-        const long long oc = l.cstride * ci + op;
-        const float Vv = a.V[oc];
-        const float f = a.u0[oc] + a.dt * r - Vv;           // BDIM! loop 1, Flow.jl:178
-        const float X = Vv + a.mu0[oc] * f;                  // loop 2 with μ₁ ≡ 0, Flow.jl:179
-        a.un[oc] = a.corrector ? (w[ci][1] + X) * 0.5f : X;  // scale_u!(½) Flow.jl:209
-      }
-    }
-    if (!lastp) {
-#pragma unroll
-      for (int ci = 0; ci < 3; ++ci) {
-        float r = F[ci][0];
-        r -= Fxu[ci]; r += F[ci][1]; r -= Fyu[ci]; r += F[ci][2];
-        pend[ci] = r;
-      }
-      const int dn = plane * (min(k + 2, khi) - k);
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        w[c][0] = w[c][1]; w[c][1] = w[c][2]; w[c][2] = w[c][3];
-        w[c][3] = pc[c][dn];
-        pc[c] += plane;
-      }
-    }
-  }
-}
-
 // ---- asynchronous plane staging (cp.async / LDGSTS): the in-plane neighbourhood of the marching
 // plane is served from a 4-slot shared-memory ring filled two planes ahead, so the flux
-// evaluation never waits on a global load (the register-only body above stalls ~6.6 cycles per
-// issue on the long scoreboard with 16 warps/SM resident).
+// evaluation never waits on a global load (a register-only body stalls ~6.6 cycles per issue on the
+// long scoreboard with 16 warps/SM resident).
 __device__ __forceinline__ void cp_async4(float* smem, const float* g) {
   const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(g) : "memory");
@@ -229,7 +142,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   const int klo = a.per.zlo ? -1 : 0, khi = a.per.zhi ? N2 : N2 - 1;   // readable plane range (slab halos)
   const int kx = FAST ? 0 : (i == 1 ? (p0 ? 2 : 1) : (i == N0 - 1 ? (p0 ? 4 : 3) : 0));
   const int ky = FAST ? 0 : (j == 1 ? (p1 ? 2 : 1) : (j == N1 - 1 ? (p1 ? 4 : 3) : 0));
-  const float* U[3] = {a.ua, a.ua + l.cstride, a.ua + 2 * l.cstride};
+  const float* const* U = a.uac;
   const float nu = a.nu;
   // staging duty of this thread: tile positions tid and tid+256 (clamped to the array)
   const int pa = tid, pb = tid + 32 * M3_TY;
@@ -264,18 +177,24 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   }
   float pend[3] = {0.f, 0.f, 0.f};
 
-  for (int k = k0; k <= kend; ++k) {
-    const bool lastp = k == kend;
-    const int kz = k == 1 ? (a.per.zlo ? 0 : (p2 ? 2 : 1)) : (k == N2 - 1 ? (a.per.zhi ? 0 : (p2 ? 4 : 3)) : 0);
+  // one plane of the march.  ZIN: an inner plane (ordinary z faces, not the last visited plane) -- with
+  // FAST that body has no data-dependent branch at all.
+  // TOP: the last row of the block only supplies the upper y faces of the row below, so of its nine
+  // fluxes only the three y-face ones are evaluated (the row is one whole warp: no divergence).
+  auto plane_step = [&](auto zin_tag, auto top_tag, const int k) {
+    constexpr bool ZIN = decltype(zin_tag)::value;
+    constexpr bool TOP = decltype(top_tag)::value;
+    const bool lastp = ZIN ? false : k == kend;
+    const int kz = ZIN ? 0 : (k == 1 ? (a.per.zlo ? 0 : (p2 ? 2 : 1)) : (k == N2 - 1 ? (a.per.zhi ? 0 : (p2 ? 4 : 3)) : 0));
     if (!lastp) { stage(k + 3); cp_async_commit(); }
     // operands of the finalisation of cell k-1: issued now, consumed after the fluxes
     float fu0[3], fV[3], fm0[3];
     const int opv = oij + plane * (k - 1);
-    if (k > k0 && out_ij) {
+    const bool fin = !TOP && k > k0 && out_ij;
+    if (fin) {
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) {
-        const long long oc = l.cstride * ci + opv;
-        fu0[ci] = a.u0[oc]; fV[ci] = a.V[oc]; fm0[ci] = a.mu0[oc];
+        fu0[ci] = a.u0c[ci][opv]; fV[ci] = a.Vc[ci][opv]; fm0[ci] = a.m0c[ci][opv];
       }
     }
     float(*cur)[M3_TILE] = sm.ring[k & (M3_RING - 1)];
@@ -287,26 +206,32 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
       nb[c][1][0] = cur[c][tc - 2 * M3_TW]; nb[c][1][1] = cur[c][tc - M3_TW]; nb[c][1][2] = cur[c][tc + M3_TW];
     }
     float F[3][3];
+    auto fluxes = [&](auto exact_tag) -> bool {
+      constexpr bool EX = decltype(exact_tag)::value;
+      float amin = 1.f, amax = 1.f;
 #pragma unroll
-    for (int ci = 0; ci < 3; ++ci) {
+      for (int ci = 0; ci < 3; ++ci) {
 #pragma unroll
-      for (int dj = 0; dj < 3; ++dj) {
-        if (lastp && dj < 2) { F[ci][dj] = 0.f; continue; }
-        const int kind = dj == 0 ? kx : (dj == 1 ? ky : kz);
-        const int sdj = dj == 0 ? 1 : (dj == 1 ? pitch : plane);
-        const int Ndj = dj == 0 ? N0 : (dj == 1 ? N1 : N2);
-        const int o = oij + plane * k;
-        if (kind == 4) {                                     // periodic upper face == Φ of the wrapped cell
-          const int sci = ci == 0 ? 1 : (ci == 1 ? pitch : plane);
-          F[ci][dj] = face_flux<S>(U[ci], U[dj], o - sdj * (Ndj - 2), sci, sdj, 1, Ndj, true, nu);
-        } else {
-          const float ua = (w[dj][2] + nb[dj][ci][1]) / 2.f;  // ϕ(i,CI(I,j),u) Flow.jl:3
-          float um2 = nb[ci][dj][0];
-          if (kind == 2) um2 = U[ci][o + sdj * (Ndj - 4)];    // CIj(j,·,N[j]-2) Flow.jl:61
-          F[ci][dj] = flux_v<S>(um2, nb[ci][dj][1], w[ci][2], nb[ci][dj][2], ua, nu, kind);
+        for (int dj = 0; dj < 3; ++dj) {
+          if ((lastp && dj < 2) || (TOP && dj != 1)) { F[ci][dj] = 0.f; continue; }
+          const int kind = dj == 0 ? kx : (dj == 1 ? ky : kz);
+          const int sdj = dj == 0 ? 1 : (dj == 1 ? pitch : plane);
+          const int Ndj = dj == 0 ? N0 : (dj == 1 ? N1 : N2);
+          const int o = oij + plane * k;
+          if (kind == 4) {                                     // periodic upper face == Φ of the wrapped cell
+            const int sci = ci == 0 ? 1 : (ci == 1 ? pitch : plane);
+            F[ci][dj] = face_flux<S>(U[ci], U[dj], o - sdj * (Ndj - 2), sci, sdj, 1, Ndj, true, nu);
+          } else {
+            const float ua = (w[dj][2] + nb[dj][ci][1]) / 2.f;  // ϕ(i,CI(I,j),u) Flow.jl:3
+            float um2 = nb[ci][dj][0];
+            if (kind == 2) um2 = U[ci][o + sdj * (Ndj - 4)];    // CIj(j,·,N[j]-2) Flow.jl:61
+            F[ci][dj] = flux_q<S, EX>(um2, nb[ci][dj][1], w[ci][2], nb[ci][dj][2], ua, nu, kind, amin, amax);
+          }
         }
       }
-    }
+      return !(amin > 1e-30f && amax < 1e38f);
+    };
+    if (fluxes(std::false_type{})) fluxes(std::true_type{});
     float Fxu[3], Fyu[3];
     if (!lastp) {
       const int buf = k & 1;
@@ -320,14 +245,14 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) Fyu[ci] = sm.shy[buf][ci][min(ty + 1, M3_TY - 1)][lane];
     }
-    if (k > k0 && out_ij) {                                  // finalise cell (i,j,k-1)
+    if (fin) {                                               // finalise cell (i,j,k-1)
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) {
         float r = pend[ci] - F[ci][2];
         r += a.acc.v[ci];
         const float f = fu0[ci] + a.dt * r - fV[ci];         // BDIM! loop 1, Flow.jl:178
         const float X = fV[ci] + fm0[ci] * f;                // loop 2 with μ₁ ≡ 0, Flow.jl:179
-        a.un[l.cstride * ci + opv] = a.corrector ? (w[ci][1] + X) * 0.5f : X;   // scale_u!(½) Flow.jl:209
+        a.unc[ci][opv] = a.corrector ? (w[ci][1] + X) * 0.5f : X;   // scale_u!(½) Flow.jl:209
       }
     }
     if (!lastp) {
@@ -341,7 +266,16 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
         w[ci][3] = nxt[ci][tc];
       }
     }
-  }
+  };
+  auto march = [&](auto top_tag) {
+    for (int k = k0; k <= kend; ++k) {
+      if (k > 1 && k < kend) plane_step(std::true_type{}, top_tag, k);
+      else plane_step(std::false_type{}, top_tag, k);
+    }
+  };
+  // (evaluating only the y faces in the block's last row was tried: one light warp per block does not
+  //  shorten the plane, whose time is set by the SMSPs that host four full warps)
+  march(std::false_type{});
   cp_async_wait<0>();
 }
 
