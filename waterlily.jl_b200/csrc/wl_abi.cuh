@@ -88,7 +88,7 @@ int build_levels(wl_sim* s) {
 size_t plan_arena_bytes(wl_sim* s) {
   auto fld = [](const Lay& l, int ncomp) { return (((size_t)l.cstride * ncomp * sizeof(float) + 256) + 255) & ~(size_t)255; };
   const int D = s->D;
-  size_t tot = 4096;                                                    // flags
+  size_t tot = ARENA_HDR;                                               // flags, gather tables
   tot += fld(s->lay, D) * 6 + fld(s->lay, 1) * 2 + fld(s->lay, D * D);   // u,u0,f,V,mu0,w ; p,sigma ; mu1
   tot += fld(s->lay, 1) * 4;                                            // level 0: r, eps, D, iD
   int gn[3] = {s->lay.n0, s->lay.n1, s->dist.nzg + 2};
@@ -120,8 +120,8 @@ int setup_p2p(wl_sim* s) {
   Dist& d = s->dist;
   const size_t cap = plan_arena_bytes(s);
   if (cudaMalloc(&s->arena, cap) != cudaSuccess) { cudaGetLastError(); s->arena = nullptr; return WL_OK; }   // fall back to NCCL halos
-  s->arena_cap = cap; s->arena_used = 4096;
-  cudaMemsetAsync(s->arena, 0, 4096, s->st);
+  s->arena_cap = cap; s->arena_used = ARENA_HDR;
+  cudaMemsetAsync(s->arena, 0, ARENA_HDR, s->st);
   cudaIpcMemHandle_t mine;
   if (cudaIpcGetMemHandle(&mine, s->arena) != cudaSuccess) { cudaGetLastError(); return WL_OK; }
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
@@ -134,10 +134,23 @@ int setup_p2p(wl_sim* s) {
   WL_CUDA(s, cudaStreamSynchronize(s->st));
   cudaFree(dbuf);
   bool ok = true;
-  if (d.lo >= 0) ok = ok && cudaIpcOpenMemHandle((void**)&s->peer_lo, all[d.lo], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
-  if (d.hi >= 0) {
-    if (d.hi == d.lo) s->peer_hi = s->peer_lo;
-    else ok = ok && cudaIpcOpenMemHandle((void**)&s->peer_hi, all[d.hi], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+  const bool all_peers = d.n <= P2P_MAXRANKS && !getenv("WL_NO_P2P_GATHER");   // one NVSwitch box: map everyone
+  if (all_peers) {
+    for (int r = 0; r < d.n && ok; ++r) {
+      if (r == d.rank) { s->peer_all[r] = s->arena; continue; }
+      ok = cudaIpcOpenMemHandle((void**)&s->peer_all[r], all[r], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+      if (!ok) s->peer_all[r] = nullptr;
+    }
+    if (ok) {
+      if (d.lo >= 0) s->peer_lo = s->peer_all[d.lo];
+      if (d.hi >= 0) s->peer_hi = s->peer_all[d.hi];
+    }
+  } else {
+    if (d.lo >= 0) ok = ok && cudaIpcOpenMemHandle((void**)&s->peer_lo, all[d.lo], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+    if (d.hi >= 0) {
+      if (d.hi == d.lo) s->peer_hi = s->peer_lo;
+      else ok = ok && cudaIpcOpenMemHandle((void**)&s->peer_hi, all[d.hi], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+    }
   }
   if (!ok) cudaGetLastError();
   // every rank must agree on the transport (the flag protocol needs both ends): gather the verdicts
@@ -152,6 +165,7 @@ int setup_p2p(wl_sim* s) {
   cudaFree(dv);
   s->p2p = true;
   for (int q = 0; q < d.n; ++q) s->p2p = s->p2p && vs[q] == 1;
+  s->p2p_gather = s->p2p && all_peers;
   return WL_OK;
 }
 
@@ -335,8 +349,13 @@ void wl_destroy(wl_sim* s) {
   if (s->arena) {
     // no neighbour may still be storing into this arena: meet once before unmapping / freeing
     if (s->dist.comm && s->d_redg) { ncclAllGather(s->d_red, s->d_redg, sizeof(Red) * NRED, ncclChar, s->dist.comm, s->st); cudaStreamSynchronize(s->st); }
-    if (s->peer_lo) cudaIpcCloseMemHandle(s->peer_lo);
-    if (s->peer_hi && s->peer_hi != s->peer_lo) cudaIpcCloseMemHandle(s->peer_hi);
+    bool mapped_all = false;
+    for (int r = 0; r < P2P_MAXRANKS; ++r)
+      if (s->peer_all[r]) { mapped_all = true; if (s->peer_all[r] != s->arena) cudaIpcCloseMemHandle(s->peer_all[r]); }
+    if (!mapped_all) {
+      if (s->peer_lo) cudaIpcCloseMemHandle(s->peer_lo);
+      if (s->peer_hi && s->peer_hi != s->peer_lo) cudaIpcCloseMemHandle(s->peer_hi);
+    }
     cudaFree(s->arena);
     s->arena = nullptr;
   }

@@ -6,6 +6,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -49,7 +50,6 @@ struct Level {
   long long ncells = 0;      // interior cells of the global level
 };
 
-constexpr int NRED = 12;     // slots: 0 Σr, 1 norms, 2 CFL, 3-5 force, 7 zero, 8-9 exitBC!
 constexpr int MAXRANKS = 64;
 
 // Slab decomposition along the last dimension, one process per GPU.
@@ -80,6 +80,9 @@ struct wl_sim {
   char* arena = nullptr;
   size_t arena_cap = 0, arena_used = 0, arena_mark = 0;
   char* peer_lo = nullptr; char* peer_hi = nullptr;   // neighbours' arenas mapped with cudaIpcOpenMemHandle
+  char* peer_all[P2P_MAXRANKS] = {};                  // every rank's arena (own included) when nranks <= P2P_MAXRANKS
+  bool p2p_gather = false;                            // reduction slots travel by k_gather_p2p instead of NCCL
+  unsigned int gseq = 0;
   bool p2p = false;
   unsigned int seq_lo = 0, seq_hi = 0;                // exchanges done on the lower / upper link
   float* stage = nullptr;     // packed device buffer for upload/download (grown on demand)
@@ -234,6 +237,14 @@ inline void prof_post(wl_sim* s, const char* name, cudaEvent_t a, cudaEvent_t b)
     }                                                                                      \
   } while (0)
 
+static bool getenv_flag(const char* name) {
+  static std::map<std::string, bool> cache;
+  auto it = cache.find(name);
+  if (it != cache.end()) return it->second;
+  const bool v = getenv(name) != nullptr;
+  cache[name] = v;
+  return v;
+}
 // ---------------------------------------------------------------- slab halos and global scalars
 // Exchange `depth` planes per side of every component of `f` with the slab neighbours, on the
 // sim's stream: interior planes [1,1+depth) go to the lower neighbour's [n2-1,n2-1+depth) and
@@ -241,7 +252,12 @@ inline void prof_post(wl_sim* s, const char* name, cudaEvent_t a, cudaEvent_t b)
 // included), which is what the sequential BC!/perBC! passes of the reference produce for the last
 // direction (core.jl:207-217,239-243).  wrap=false skips the pair that closes a periodic ring (the
 // reference's red-black sweeps never refresh that ghost, Poisson.jl:141-148).
-int halo(wl_sim* s, const DevField& f, int depth, bool wrap = true) {
+// idle=true: no kernel since the previous exchange of `f` with the same neighbours can observe a change in
+// the ghost planes this exchange rewrites, so the "ready" handshake is skipped.  Used between red-black
+// half-sweeps: the sweep that ran since the last exchange read only ghost cells of the OTHER colour, whose
+// values this exchange rewrites unchanged, and the neighbour cannot be further behind than that sweep
+// (it left the previous exchange only after receiving this rank's planes).
+int halo(wl_sim* s, const DevField& f, int depth, bool wrap = true, bool idle = false) {
   const Dist& d = s->dist;
   if (d.n == 1) return WL_OK;
   const Lay& l = f.lay;
@@ -264,6 +280,9 @@ int halo(wl_sim* s, const DevField& f, int depth, bool wrap = true) {
     a.nb_lo = reinterpret_cast<unsigned int*>(s->peer_lo);
     a.nb_hi = reinterpret_cast<unsigned int*>(s->peer_hi);
     a.use_lo = use_lo; a.use_hi = use_hi;
+    // (a link that closes a periodic ring sat out the exchanges between the sweeps: it keeps its handshake)
+    const bool skip = idle && !getenv_flag("WL_HALO_ALWAYS_READY");
+    a.skip_lo = skip && !d.lo_wrap; a.skip_hi = skip && !d.hi_wrap;
     if (use_lo) a.seq_lo = ++s->seq_lo;
     if (use_hi) a.seq_hi = ++s->seq_hi;
     long long nb = ((long long)cnt * a.nseg + 2047) / 2048;
@@ -286,12 +305,23 @@ int halo(wl_sim* s, const DevField& f, int depth, bool wrap = true) {
 }
 // The reduction slots of all ranks, gathered so that every consumer folds them in rank order
 // (results do not depend on the collective's algorithm).  Single GPU: the slots themselves.
+Red* gather_table(wl_sim* s) {      // the table the LAST gather filled (consumers are enqueued after it)
+  if (!s->p2p_gather) return s->d_redg;
+  return reinterpret_cast<Red*>(s->arena + GATHER_TABLE_BYTE) + (size_t)(s->gseq & 1) * P2P_MAXRANKS * NRED;
+}
 RedIn red_in(wl_sim* s, int slot) {
   if (s->dist.n == 1) return RedIn{s->d_red + slot, 1, NRED};
-  return RedIn{s->d_redg + slot, s->dist.n, NRED};
+  return RedIn{gather_table(s) + slot, s->dist.n, NRED};
 }
 int gather_red(wl_sim* s) {
   if (s->dist.n == 1) return WL_OK;
+  if (s->p2p_gather) {
+    GatherArgs a{};
+    a.mine = s->d_red; a.n = s->dist.n; a.rank = s->dist.rank; a.seq = ++s->gseq;
+    for (int r = 0; r < s->dist.n; ++r) a.peer[r] = s->peer_all[r];
+    LAUNCH(s, k_gather_p2p, dim3(1), dim3(128), a);
+    return WL_OK;
+  }
   WL_NCCL(s, ncclAllGather(s->d_red, s->d_redg, sizeof(Red) * NRED, ncclChar, s->dist.comm, s->st));
   return WL_OK;
 }
@@ -518,7 +548,7 @@ int smooth2(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready = false) {
     g.k0 = k0;
     if (v8) LAUNCH(s, k_gs8, grid_quads(p.lay, 8), dim3(32, 4, 2), g);
     else DISPATCH_D(s, k_gs_half_c, gg, blk(s->D), g);
-    if (p.dist) { if (int e = halo(s, p.eps, 1, k0 == 4)) return e; }
+    if (p.dist) { if (int e = halo(s, p.eps, 1, k0 == 4, true)) return e; }
   }
   if (v4) {
     const dim3 gq = grid_quads(p.lay);
@@ -534,8 +564,10 @@ void coarse_block(wl_sim* s, size_t first, float w) {
   CoarseArgs a{};
   for (size_t l = 0; l < s->lv.size() && l < (size_t)WL_MAXLEV; ++l) a.lv[l] = levdev(s->lv[l]);
   a.first = (int)first; a.nlev = (int)s->lv.size(); a.per = s->per_glob; a.omega = w;
-  // stage as many of the smallest levels in shared memory as fit the budget (WL_COARSE_SMEM_KB, default 200)
-  static const int budget_kb = getenv("WL_COARSE_SMEM_KB") ? atoi(getenv("WL_COARSE_SMEM_KB")) : 200;
+  // optionally stage the smallest levels in shared memory (WL_COARSE_SMEM_KB > 0).  Measured slower than
+  // leaving them in L2 (52 -> 58..75 µs on the 18³..4³ tail of a 128³ grid): the recursion is bound by
+  // the dependent-issue latency of a few warps per phase, not by memory, so the staging copies only add.
+  static const int budget_kb = getenv("WL_COARSE_SMEM_KB") ? atoi(getenv("WL_COARSE_SMEM_KB")) : 0;
   const size_t budget = (size_t)std::min(std::max(budget_kb, 0), 200) * 1024;
   int from = a.nlev;
   while (from > a.first && coarse_smem_bytes(a, s->D, from - 1) <= budget) --from;
@@ -616,7 +648,7 @@ int fetch_red(wl_sim* s) {
     return WL_OK;
   }
   if (int e = gather_red(s)) return e;
-  WL_CUDA(s, cudaMemcpyAsync(s->h_redg, s->d_redg, sizeof(Red) * NRED * s->dist.n, cudaMemcpyDeviceToHost, s->st));
+  WL_CUDA(s, cudaMemcpyAsync(s->h_redg, gather_table(s), sizeof(Red) * NRED * s->dist.n, cudaMemcpyDeviceToHost, s->st));
   WL_CUDA(s, cudaStreamSynchronize(s->st));
   for (int q = 0; q < NRED; ++q) {
     double sum = 0.0; float m = -INFINITY;
@@ -778,8 +810,7 @@ int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
     ProjArgs2 q{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, s->per, dt};
     if (use_vec4(s->lay)) LAUNCH(s, k_proj4, grid_quads(s->lay), dim3(32, 4, 2), q);
     else DISPATCH_D(s, k_proj, grid_inside(s->lay), blk(s->D), q);
-    std::swap(s->p, p0.eps); p0.x = s->p;
-    if (int e = halo(s, s->p, 1)) return e;                     // p's ghost planes (next K-DIVRES, data surface)
+    std::swap(s->p, p0.eps); p0.x = s->p;                       // (K-PROJ also wrote p's interface ghost planes)
     bc_vec(s, s->u, U, s->cfg.exitBC != 0);
     return WL_OK;
   }

@@ -63,6 +63,7 @@ __device__ __forceinline__ float warp_max(float v) {
 }
 
 // Result slots of the scalar reductions (device memory mirrored into pinned host memory).
+constexpr int NRED = 12;     // reduction slots per sim: 0 Σr, 1 norms, 2 CFL, 3-5 force, 7 zero, 8-9 exitBC!, 10 first-cycle norms
 struct Red {
   double sum;       // Σ r   (residual!)  or Σ|r| (L₁)
   float  maxv;      // max|r| (L∞) or max σ (CFL)

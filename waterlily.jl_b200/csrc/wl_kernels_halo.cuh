@@ -28,10 +28,14 @@ struct HaloP2PArgs {
   unsigned int* nb_hi;                 // upper neighbour's flag block (slots 0 and 2)
   unsigned int seq_lo, seq_hi;
   int use_lo, use_hi;
+  int skip_lo, skip_hi;                // per link: the caller proved the ghost planes idle (see halo() in wl_b200.cu)
 };
 
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
   unsigned int v;
@@ -60,15 +64,18 @@ __global__ void __launch_bounds__(256) k_halo_p2p(const HaloP2PArgs a) {
   const int tid = threadIdx.x;
   unsigned long long* stat = reinterpret_cast<unsigned long long*>(a.my + 16);
   const unsigned long long t_start = wl_now_ns();
-  if (tid == 0) {
-    if (blockIdx.x == 0) {
-      if (a.use_lo) st_release_sys(a.nb_lo + 1, a.seq_lo);
-      if (a.use_hi) st_release_sys(a.nb_hi + 0, a.seq_hi);
+  const bool rdy_lo = a.use_lo && !a.skip_lo, rdy_hi = a.use_hi && !a.skip_hi;
+  if (rdy_lo || rdy_hi) {
+    if (tid == 0) {
+      if (blockIdx.x == 0) {
+        if (rdy_lo) st_release_sys(a.nb_lo + 1, a.seq_lo);
+        if (rdy_hi) st_release_sys(a.nb_hi + 0, a.seq_hi);
+      }
+      if (rdy_lo) wait_flag(a.my + 0, a.seq_lo, a.my + 5);
+      if (rdy_hi) wait_flag(a.my + 1, a.seq_hi, a.my + 5);
     }
-    if (a.use_lo) wait_flag(a.my + 0, a.seq_lo, a.my + 5);
-    if (a.use_hi) wait_flag(a.my + 1, a.seq_hi, a.my + 5);
+    __syncthreads();
   }
-  __syncthreads();
   const unsigned long long t_ready = wl_now_ns();
   if (tid == 0 && blockIdx.x == 0) atomicAdd(stat + 0, t_ready - t_start);
   const long long stride = (long long)gridDim.x * blockDim.x;
@@ -98,9 +105,11 @@ __global__ void __launch_bounds__(256) k_halo_p2p(const HaloP2PArgs a) {
   __syncthreads();
   if (!last || tid != 0) return;
   a.my[4] = 0u;
+  // every block fenced (system scope) before taking its ticket; this fence pairs with those (acquire side)
+  // and orders the flag stores after the whole exchange (release side): one fence, two relaxed stores
   __threadfence_system();
-  if (a.use_lo) st_release_sys(a.nb_lo + 3, a.seq_lo);
-  if (a.use_hi) st_release_sys(a.nb_hi + 2, a.seq_hi);
+  if (a.use_lo) st_relaxed_sys(a.nb_lo + 3, a.seq_lo);
+  if (a.use_hi) st_relaxed_sys(a.nb_hi + 2, a.seq_hi);
   const unsigned long long t_copied = wl_now_ns();
   if (a.use_lo) wait_flag(a.my + 2, a.seq_lo, a.my + 5);
   if (a.use_hi) wait_flag(a.my + 3, a.seq_hi, a.my + 5);
@@ -108,6 +117,39 @@ __global__ void __launch_bounds__(256) k_halo_p2p(const HaloP2PArgs a) {
   atomicAdd(stat + 1, t_copied - t_ready);
   atomicAdd(stat + 2, t_done - t_copied);
   atomicAdd(stat + 3, 1ull);
+}
+
+// ---------------------------------------------------------------- reduction slots of all ranks, by peer stores
+// Every rank stores its NRED reduction slots into each peer's gather table (arena header), raises a
+// per-source flag there, and waits until all sources have raised its own: one small kernel (~2 NVLink
+// latencies) in place of an NCCL all-gather.  Two tables alternate by sequence parity: a peer can be
+// at most one gather ahead (it needs my flag to finish the current one), so the table it writes next
+// is never the one my kernels are still reading.
+constexpr int P2P_MAXRANKS = 8;
+constexpr int GATHER_FLAG_WORD = 64;          // unsigned[P2P_MAXRANKS] in the arena header
+constexpr int GATHER_TABLE_BYTE = 4096;       // Red[2][P2P_MAXRANKS][NRED]
+constexpr int ARENA_HDR = 8192;
+struct GatherArgs {
+  const Red* mine;
+  char* peer[P2P_MAXRANKS];                   // arenas of all ranks (own included)
+  int n, rank;
+  unsigned int seq;
+};
+__global__ void __launch_bounds__(128) k_gather_p2p(const GatherArgs a) {
+  const int tid = threadIdx.x;
+  const int par = a.seq & 1;
+  for (int e = tid; e < a.n * NRED; e += blockDim.x) {
+    const int r = e / NRED, q = e - r * NRED;
+    Red* dst = reinterpret_cast<Red*>(a.peer[r] + GATHER_TABLE_BYTE) + (par * P2P_MAXRANKS + a.rank) * NRED + q;
+    *dst = a.mine[q];
+  }
+  __syncthreads();
+  if (tid < a.n) {
+    unsigned int* my = reinterpret_cast<unsigned int*>(a.peer[a.rank]);
+    __threadfence_system();
+    st_release_sys(reinterpret_cast<unsigned int*>(a.peer[tid]) + GATHER_FLAG_WORD + a.rank, a.seq);
+    wait_flag(my + GATHER_FLAG_WORD + tid, a.seq, my + 5);
+  }
 }
 
 }  // namespace wl

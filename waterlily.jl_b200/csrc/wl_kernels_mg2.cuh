@@ -412,6 +412,10 @@ __global__ void __launch_bounds__(256) k_proj(const ProjArgs2 a) {
   const float p = xc / a.dt;
   a.pn[o] = p;
   if (edge) store_images<D>(a.pn, l, a.per, i, j, k, p);
+  if (D == 3) {                                              // slab interfaces: see k_proj4
+    if (a.per.zlo && k == 1) a.pn[o - l.plane] = xm[2] / a.dt;
+    if (a.per.zhi && k == l.n2 - 2) a.pn[o + l.plane] = __ldg(a.x + o + l.plane) / a.dt;
+  }
 }
 
 // ---------------------------------------------------------------- all small levels in one block

@@ -209,6 +209,21 @@ __global__ void __launch_bounds__(256) k_proj4(const ProjArgs2 a) {
 #pragma unroll
     for (int q = 0; q < 4; ++q) store_images<3>(a.pn, l, a.per, i + q, j, k, pn.v[q]);
   }
+  // slab interfaces: the neighbour's p on the ghost plane is x/Δt of the exchanged x ghost -- the same
+  // operation on the same operands, so it is written here instead of being exchanged
+  if (a.per.zlo && k == 1) {
+    F4 g;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) g.v[q] = xzm.v[q] / a.dt;
+    st4(a.pn + o - l.plane, g);
+  }
+  if (a.per.zhi && k == l.n2 - 2) {
+    const F4 xzp = ld4g(a.x + o + l.plane);
+    F4 g;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) g.v[q] = xzp.v[q] / a.dt;
+    st4(a.pn + o + l.plane, g);
+  }
 }
 
 // ---------------------------------------------------------------- K-UP, 4 cells per thread (see k_up)
