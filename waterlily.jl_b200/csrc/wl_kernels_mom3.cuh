@@ -140,17 +140,25 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   const int oij = i + pitch * j;
   const bool p0 = a.per.p[0] != 0, p1 = a.per.p[1] != 0, p2 = a.per.p[2] != 0;
   const int klo = a.per.zlo ? -1 : 0, khi = a.per.zhi ? N2 : N2 - 1;   // readable plane range (slab halos)
-  const int kx = FAST ? 0 : (i == 1 ? (p0 ? 2 : 1) : (i == N0 - 1 ? (p0 ? 4 : 3) : 0));
-  const int ky = FAST ? 0 : (j == 1 ? (p1 ? 2 : 1) : (j == N1 - 1 ? (p1 ? 4 : 3) : 0));
+  // Periodic directions have no special faces here: the ghost layer holds exact images (BC! ran on the
+  // advecting field), and the one value QUICK needs beyond it -- CIj(j,·,N[j]-2) of ϕuP, Flow.jl:10,61 -- is
+  // fetched from its wrapped position when the tile / the column is staged.  The face on the upper ghost
+  // is then the same expression on the same values as Φ of the wrapped cell (Flow.jl:57-59).
+  const int kx = (FAST || p0) ? 0 : (i == 1 ? 1 : (i == N0 - 1 ? 3 : 0));
+  const int ky = (FAST || p1) ? 0 : (j == 1 ? 1 : (j == N1 - 1 ? 3 : 0));
   const float* const* U = a.uac;
   const float nu = a.nu;
-  // staging duty of this thread: tile positions tid and tid+256 (clamped to the array)
+  auto fold = [](int g, int N, bool per) {        // array index of tile coordinate g
+    if (per) g = g < 0 ? g + (N - 2) : (g > N - 1 ? g - (N - 2) : g);
+    return min(max(g, 0), N - 1);
+  };
+  // staging duty of this thread: tile positions tid and tid+256
   const int pa = tid, pb = tid + 32 * M3_TY;
   const bool has_b = pb < M3_TILE;
-  const int ga = min(max(i0 - 2 + pa % M3_TW, 0), N0 - 1) + pitch * min(max(j0 - 2 + pa / M3_TW, 0), N1 - 1);
-  const int gb = has_b ? min(max(i0 - 2 + pb % M3_TW, 0), N0 - 1) + pitch * min(max(j0 - 2 + pb / M3_TW, 0), N1 - 1) : 0;
+  const int ga = fold(i0 - 2 + pa % M3_TW, N0, p0) + pitch * fold(j0 - 2 + pa / M3_TW, N1, p1);
+  const int gb = has_b ? fold(i0 - 2 + pb % M3_TW, N0, p0) + pitch * fold(j0 - 2 + pb / M3_TW, N1, p1) : 0;
   auto stage = [&](int kp) {
-    const int kc = min(kp, khi);
+    const int kc = p2 ? (kp > N2 - 1 ? min(kp - (N2 - 2), N2 - 1) : kp) : min(kp, khi);
     float(*slot)[M3_TILE] = sm.ring[kp & (M3_RING - 1)];
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
@@ -165,7 +173,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   float w[3][4];   // own column: planes k-2, k-1, k, k+1
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    w[c][0] = U[c][oij + plane * max(k0 - 2, klo)];
+    w[c][0] = U[c][oij + plane * ((p2 && k0 == 1) ? N2 - 3 : max(k0 - 2, klo))];
     w[c][1] = U[c][oij + plane * (k0 - 1)];
   }
   cp_async_wait<1>();
@@ -185,7 +193,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
     constexpr bool ZIN = decltype(zin_tag)::value;
     constexpr bool TOP = decltype(top_tag)::value;
     const bool lastp = ZIN ? false : k == kend;
-    const int kz = ZIN ? 0 : (k == 1 ? (a.per.zlo ? 0 : (p2 ? 2 : 1)) : (k == N2 - 1 ? (a.per.zhi ? 0 : (p2 ? 4 : 3)) : 0));
+    const int kz = (ZIN || p2) ? 0 : (k == 1 ? (a.per.zlo ? 0 : 1) : (k == N2 - 1 ? (a.per.zhi ? 0 : 3) : 0));
     if (!lastp) { stage(k + 3); cp_async_commit(); }
     // operands of the finalisation of cell k-1: issued now, consumed after the fluxes
     float fu0[3], fV[3], fm0[3];
@@ -215,18 +223,8 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
         for (int dj = 0; dj < 3; ++dj) {
           if ((lastp && dj < 2) || (TOP && dj != 1)) { F[ci][dj] = 0.f; continue; }
           const int kind = dj == 0 ? kx : (dj == 1 ? ky : kz);
-          const int sdj = dj == 0 ? 1 : (dj == 1 ? pitch : plane);
-          const int Ndj = dj == 0 ? N0 : (dj == 1 ? N1 : N2);
-          const int o = oij + plane * k;
-          if (kind == 4) {                                     // periodic upper face == Φ of the wrapped cell
-            const int sci = ci == 0 ? 1 : (ci == 1 ? pitch : plane);
-            F[ci][dj] = face_flux<S>(U[ci], U[dj], o - sdj * (Ndj - 2), sci, sdj, 1, Ndj, true, nu);
-          } else {
-            const float ua = (w[dj][2] + nb[dj][ci][1]) / 2.f;  // ϕ(i,CI(I,j),u) Flow.jl:3
-            float um2 = nb[ci][dj][0];
-            if (kind == 2) um2 = U[ci][o + sdj * (Ndj - 4)];    // CIj(j,·,N[j]-2) Flow.jl:61
-            F[ci][dj] = flux_q<S, EX>(um2, nb[ci][dj][1], w[ci][2], nb[ci][dj][2], ua, nu, kind, amin, amax);
-          }
+          const float ua = (w[dj][2] + nb[dj][ci][1]) / 2.f;    // ϕ(i,CI(I,j),u) Flow.jl:3
+          F[ci][dj] = flux_q<S, EX>(nb[ci][dj][0], nb[ci][dj][1], w[ci][2], nb[ci][dj][2], ua, nu, kind, amin, amax);
         }
       }
       return !(amin > 1e-30f && amax < 1e38f);
@@ -269,7 +267,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   };
   auto march = [&](auto top_tag) {
     for (int k = k0; k <= kend; ++k) {
-      if (k > 1 && k < kend) plane_step(std::true_type{}, top_tag, k);
+      if ((k > 1 || p2 || a.per.zlo) && k < kend) plane_step(std::true_type{}, top_tag, k);
       else plane_step(std::false_type{}, top_tag, k);
     }
   };
@@ -282,8 +280,11 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
 template <int S>
 __global__ void __launch_bounds__(32 * M3_TY, 2) k_mom3(const Mom3Args a) {
   __shared__ Mom3Smem sm;
-  const bool inner = blockIdx.x >= 1 && 1 + 31 * (int)blockIdx.x + 31 <= a.l.n0 - 2 &&
-                     blockIdx.y >= 1 && 1 + (M3_TY - 1) * (int)blockIdx.y + (M3_TY - 1) <= a.l.n1 - 2;
+  // FAST: every thread of the block sits on an ordinary cell with ordinary faces (in a periodic direction
+  // that is every block whose last lane / row still lies inside the array)
+  const int px = a.per.p[0] ? 1 : 0, py = a.per.p[1] ? 1 : 0;
+  const bool inner = (int)blockIdx.x >= 1 - px && 1 + 31 * (int)blockIdx.x + 31 <= a.l.n0 - 2 + px &&
+                     (int)blockIdx.y >= 1 - py && 1 + (M3_TY - 1) * (int)blockIdx.y + (M3_TY - 1) <= a.l.n1 - 2 + py;
   if (inner) mom3_body_async<S, true>(a, sm);
   else mom3_body_async<S, false>(a, sm);
 }
