@@ -565,8 +565,9 @@ void coarse_block(wl_sim* s, size_t first, float w) {
   for (size_t l = 0; l < s->lv.size() && l < (size_t)WL_MAXLEV; ++l) a.lv[l] = levdev(s->lv[l]);
   a.first = (int)first; a.nlev = (int)s->lv.size(); a.per = s->per_glob; a.omega = w;
   // optionally stage the smallest levels in shared memory (WL_COARSE_SMEM_KB > 0).  Measured slower than
-  // leaving them in L2 (52 -> 58..75 µs on the 18³..4³ tail of a 128³ grid): the recursion is bound by
-  // the dependent-issue latency of a few warps per phase, not by memory, so the staging copies only add.
+  // leaving them in L2 (52 -> 75 µs on the 18³..4³ tail of a 128³ grid: the recursion itself drops to 35 µs,
+  // but launch + descriptor setup cost 7 µs and the generic staging copies 33 µs; the recursion is bound by
+  // the instruction issue of one SM on the largest staged level and by ~40 dependent phases, not by memory).
   static const int budget_kb = getenv("WL_COARSE_SMEM_KB") ? atoi(getenv("WL_COARSE_SMEM_KB")) : 0;
   const size_t budget = (size_t)std::min(std::max(budget_kb, 0), 200) * 1024;
   int from = a.nlev;
@@ -760,12 +761,22 @@ void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, c
     const long long oc = l.cstride * c;
     a.uac[c] = a.ua + oc; a.u0c[c] = a.u0 + oc; a.Vc[c] = a.V + oc; a.m0c[c] = a.mu0 + oc; a.unc[c] = a.un + oc;
   }
-  // march length: as long as possible (amortises the extra flux plane) while keeping >= 6 waves of
-  // 2 blocks/SM on 148 SMs
-  a.KZ = 64;
-  while (a.KZ > 8 && (long long)((l.n0 - 2 + 30) / 31) * ((l.n1 - 2 + M3_TY - 2) / (M3_TY - 1)) *
-                             ((l.n2 - 2 + a.KZ - 1) / a.KZ) < 148 * 2 * 6)
-    a.KZ >>= 1;
+  // march length: the chunk count that minimises waves x (planes per chunk + ~4 planes of pipeline fill and
+  // the extra flux plane), a wave being 2 blocks on each of the 148 SMs (measured on 128³ and 512x256²:
+  // a grid just under a whole number of waves beats a finer split by up to 8%)
+  {
+    const long long bxy = (long long)((l.n0 - 2 + 30) / 31) * ((l.n1 - 2 + M3_TY - 2) / (M3_TY - 1));
+    const int nz = l.n2 - 2;
+    long long best = -1;
+    a.KZ = nz;
+    for (int n = 1; n <= (nz + 3) / 4; ++n) {
+      const int kz = (nz + n - 1) / n;
+      const long long chunks = (nz + kz - 1) / kz;
+      const long long cost = ((bxy * chunks + 295) / 296) * (kz + 4);
+      if (best < 0 || cost < best) { best = cost; a.KZ = kz; }
+    }
+  }
+  { static const int kz_env = getenv("WL_M3_KZ") ? atoi(getenv("WL_M3_KZ")) : 0; if (kz_env >= 2) a.KZ = kz_env; }
   dim3 g((l.n0 - 2 + 30) / 31, (l.n1 - 2 + M3_TY - 2) / (M3_TY - 1), (l.n2 - 2 + a.KZ - 1) / a.KZ);
   dim3 b(32, M3_TY, 1);
   const int sc = s->cfg.scheme;
