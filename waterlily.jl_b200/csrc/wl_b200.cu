@@ -8,6 +8,7 @@
 #include <cstring>
 #include <map>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/wl_b200.h"
@@ -181,6 +182,20 @@ void plane_launch(const Lay& l, dim3& g, dim3& b) {
   g = dim3((m + b.x - 1) / b.x, (m2 + b.y - 1) / b.y, 1);
 }
 
+// Every kernel goes through here: a launch that may overlap its scheduling with the tail of the
+// previous kernel of the stream (see pdl_entry in wl_common.cuh).  WL_NO_PDL=1 restores plain launches.
+template <class... KArgs, class... Args>
+inline void launch_pdl(cudaStream_t st, dim3 g, dim3 b, void (*kern)(KArgs...), Args&&... args) {
+  static const bool off = getenv("WL_NO_PDL") != nullptr;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = g; cfg.blockDim = b; cfg.dynamicSmemBytes = 0; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = off ? 0 : 1;
+  cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+
 // Optional per-kernel CUDA-event timing on the launching stream (wl_prof_begin/wl_prof_end).
 inline bool prof_pre(wl_sim* s, const char* name, cudaEvent_t* a, cudaEvent_t* b) {
   if (!s->prof_on) return false;
@@ -202,7 +217,7 @@ inline void prof_post(wl_sim* s, const char* name, cudaEvent_t a, cudaEvent_t b)
   do {                                                     \
     cudaEvent_t pa_, pb_;                                  \
     const bool prof_ = prof_pre(s, #kern, &pa_, &pb_);     \
-    kern<<<g, b, 0, (s)->st>>>(__VA_ARGS__);               \
+    launch_pdl((s)->st, g, b, kern, __VA_ARGS__);          \
     if (prof_) prof_post(s, #kern, pa_, pb_);              \
     ++(s)->launches;                                       \
   } while (0)

@@ -12,6 +12,17 @@
 
 namespace wl {
 
+// Programmatic dependent launch (sm_90+): first statement of every kernel.  launch_dependents lets the
+// NEXT kernel of the stream be scheduled while this one still runs (its blocks become resident and
+// park in their own wait); wait returns once the PREVIOUS kernel has completed and its writes are
+// visible.  Nothing a kernel does precedes its wait, so ordering is exactly that of a plain stream;
+// what overlaps is launch latency and block scheduling (~1 µs per kernel boundary, ~60 boundaries per
+// step).  Without the launch attribute (host side, LAUNCH in wl_b200.cu) both are no-ops.
+__device__ __forceinline__ void pdl_entry() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 constexpr int LPAD = 31;   // floats in front of i==0 so that i==1 is 128-byte aligned
 
 struct Lay {
@@ -166,6 +177,7 @@ __device__ __forceinline__ void block_reduce_partial(double s, float m, const Re
 }
 struct FoldArgs { RedWork w; int n; Red* out; };
 __global__ void __launch_bounds__(1024) k_fold_partials(const FoldArgs a) {
+  pdl_entry();
   __shared__ double ssum[32];
   __shared__ float smax[32];
   double s; float m;

@@ -98,6 +98,7 @@ struct MeasArgs {
 // and the band loop :31-48.  Ghost cells get V=0, μ₀=1, μ₁=0 (σ untouched); BC! follows.
 template <int D>
 __global__ void __launch_bounds__(256) k_measure(const MeasArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
@@ -142,6 +143,7 @@ __global__ void __launch_bounds__(256) k_measure(const MeasArgs a) {
 struct ForceArgs { Lay l; BodyDev b; const float* p; float* f; int kz0; };
 template <int D>
 __global__ void __launch_bounds__(256) k_force_df(const ForceArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
@@ -166,6 +168,7 @@ __global__ void __launch_bounds__(256) k_force_df(const ForceArgs a) {
 struct SumArgs { Lay l; const float* a; RedWork w; Red* out; };
 template <int D>
 __global__ void __launch_bounds__(256) k_sum_all(const SumArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
@@ -181,6 +184,7 @@ __global__ void __launch_bounds__(256) k_sum_all(const SumArgs a) {
 // 520-byte rows ran at a fraction of the PCIe rate).
 struct PackArgs { Lay l; float* field; float* packed; int ncomp; int to_field; };
 __global__ void __launch_bounds__(256) k_repack(const PackArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const long long per = (long long)l.n0 * l.n1 * l.n2, tot = per * a.ncomp;
   for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < tot; q += (long long)gridDim.x * blockDim.x) {

@@ -60,6 +60,7 @@ __device__ __forceinline__ bool wait_flag(const unsigned int* p, unsigned int se
 // a.my + 16 (as unsigned long long[4]): accumulated ns spent waiting for ready / copying+fencing / waiting for
 // done, and the number of exchanges (read by wl_halo_stats; block 0 / the last block only)
 __global__ void __launch_bounds__(256) k_halo_p2p(const HaloP2PArgs a) {
+  pdl_entry();
   __shared__ int last;
   const int tid = threadIdx.x;
   unsigned long long* stat = reinterpret_cast<unsigned long long*>(a.my + 16);
@@ -136,6 +137,7 @@ struct GatherArgs {
   unsigned int seq;
 };
 __global__ void __launch_bounds__(128) k_gather_p2p(const GatherArgs a) {
+  pdl_entry();
   const int tid = threadIdx.x;
   const int par = a.seq & 1;
   for (int e = tid; e < a.n * NRED; e += blockDim.x) {

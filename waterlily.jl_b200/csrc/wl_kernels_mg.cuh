@@ -56,6 +56,7 @@ __device__ __forceinline__ float multA(const Lay& l, const float* __restrict__ L
 struct DiagArgs { Lay l; const float* L; float* Dg; float* iD; };
 template <int D>
 __global__ void __launch_bounds__(256) k_set_diag(const DiagArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   WL_INTERIOR_IJK(D, l)
   if (!inb) return;
@@ -68,6 +69,7 @@ __global__ void __launch_bounds__(256) k_set_diag(const DiagArgs a) {
 // residual! first loop (Poisson.jl:94) + Σr partials.  perBC!(x) has been applied by the caller.
 template <int D>
 __global__ void __launch_bounds__(256) k_residual(const LevArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   WL_INTERIOR_IJK(D, l)
   double s = 0.0;
@@ -95,6 +97,7 @@ __global__ void __launch_bounds__(256) k_residual(const LevArgs a) {
 // s = Σr/N in Float32; if |s| > 2eps: r -= s inside.  Norms of the resulting r.
 template <int D>
 __global__ void __launch_bounds__(256) k_shift_norms(const LevArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const float s = (float)redin_sum(a.in) / (float)a.ncells;
   const bool shift = fabsf(s) > 2.f * 1.1920929e-07f;
@@ -130,6 +133,7 @@ __global__ void __launch_bounds__(256) k_shift_norms(const LevArgs a) {
 // ϵ = r·iD inside (Jacobi! Poisson.jl:112, GaussSeidelRB! :142)
 template <int D>
 __global__ void __launch_bounds__(256) k_eps_init(const LevArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   WL_INTERIOR_IJK(D, l)
   if (!inb) return;
@@ -140,6 +144,7 @@ __global__ void __launch_bounds__(256) k_eps_init(const LevArgs a) {
 // increment! (Poisson.jl:100-104) after the caller's perBC!(ϵ); optional L₁/L∞ of the new r.
 template <int D>
 __global__ void __launch_bounds__(256) k_increment(const LevArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   WL_INTERIOR_IJK(D, l)
   double s1 = 0.0; float m = -INFINITY;
@@ -158,6 +163,7 @@ __global__ void __launch_bounds__(256) k_increment(const LevArgs a) {
 // to Julia index 2·(size÷2)−1 (an odd-sized last dimension leaves its last interior cell unswept).
 template <int D>
 __global__ void __launch_bounds__(256) k_gs_half(const LevArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   WL_INTERIOR_IJK(D, l)
   if (!inb) return;
@@ -186,6 +192,7 @@ __global__ void __launch_bounds__(256) k_gs_half(const LevArgs a) {
 // gridDim.x = ceil((n0-2)/64).  Same arithmetic, same order: bit-identical.
 template <int D>
 __global__ void __launch_bounds__(256) k_gs_half_c(const LevArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
   const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;
@@ -217,6 +224,7 @@ __global__ void __launch_bounds__(256) k_gs_half_c(const LevArgs a) {
 struct XferArgs { Lay lf, lc; const float* src; float* dst; int c[3]; };
 template <int D>
 __global__ void __launch_bounds__(256) k_restrict(const XferArgs a) {
+  pdl_entry();
   const Lay& l = a.lc;
   WL_INTERIOR_IJK(D, l)
   if (!inb) return;
@@ -237,6 +245,7 @@ __global__ void __launch_bounds__(256) k_restrict(const XferArgs a) {
 // prolongate! (MultiLevelPoisson.jl:7,50): fine ϵ[I] = coarse x[down(I,c)]
 template <int D>
 __global__ void __launch_bounds__(256) k_prolongate(const XferArgs a) {
+  pdl_entry();
   const Lay& l = a.lf;
   WL_INTERIOR_IJK(D, l)
   if (!inb) return;
@@ -247,6 +256,7 @@ __global__ void __launch_bounds__(256) k_prolongate(const XferArgs a) {
 struct XferLArgs { Lay lf, lc; const float* Lf; float* Lc; int c[3]; };
 template <int D>
 __global__ void __launch_bounds__(256) k_restrictL(const XferLArgs a) {
+  pdl_entry();
   const Lay& l = a.lc;
   WL_INTERIOR_IJK(D, l)
   if (!inb) return;

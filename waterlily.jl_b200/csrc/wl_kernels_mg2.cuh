@@ -127,6 +127,7 @@ __device__ __forceinline__ float multA_w(const Lay& l, const float* __restrict__
 struct DivResArgs { Lay l; const float* u; const float* x; float* xs; const float* L; float* r; Per per; float dt; RedWork w; Red* out; };
 template <int D>
 __global__ void __launch_bounds__(256) k_divres(const DivResArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   double s = 0.0;
   for_tiles_seam<D>(l, a.per, [&](int i, int j, int k, auto edge) {
@@ -174,6 +175,7 @@ struct DownArgs { LevDev f, c; Per per; int first; RedIn in; long long ncells; R
 // shared memory and adds them in the reference's order (first dimension fastest).
 template <int D>
 __global__ void __launch_bounds__(256) k_down(const DownArgs a) {
+  pdl_entry();
   __shared__ float tile[256];
   const Lay& lc = a.c.l;
   const Lay& l = a.f.l;
@@ -270,6 +272,7 @@ __global__ void __launch_bounds__(256) k_down(const DownArgs a) {
 struct UpArgs { LevDev f, c; Per per; float omega; RedWork w; Red* out; int want_norms; int write_eps; };
 template <int D>
 __global__ void __launch_bounds__(256) k_up(const UpArgs a) {
+  pdl_entry();
   const Lay& l = a.f.l;
   WL_IJK_FROM_BLOCK(D, l)
   double s1 = 0.0; float m = -INFINITY;
@@ -340,6 +343,7 @@ __global__ void __launch_bounds__(256) k_up(const UpArgs a) {
 struct SmArgs { LevDev p; Per per; float omega; int k0; RedWork w; Red* out; int want_norms; };
 template <int D>
 __global__ void __launch_bounds__(256) k_eps_init_g(const SmArgs a) {
+  pdl_entry();
   const Lay& l = a.p.l;
   WL_IJK_FROM_BLOCK(D, l)
   if (!inb) return;
@@ -353,6 +357,7 @@ __global__ void __launch_bounds__(256) k_eps_init_g(const SmArgs a) {
 // increment! (Poisson.jl:100-104) with the perBC!(ϵ) folded into wrap-reads; optional L₁/L∞ of the new r
 template <int D>
 __global__ void __launch_bounds__(256) k_increment_w(const SmArgs a) {
+  pdl_entry();
   const Lay& l = a.p.l;
   double s1 = 0.0; float m = -INFINITY;
   // 1-D persistent grid (see for_tiles_inside); every read is issued before the first store so the
@@ -391,6 +396,7 @@ __global__ void __launch_bounds__(256) k_increment_w(const SmArgs a) {
 struct ProjArgs2 { Lay l; float* u; const float* x; float* pn; const float* L; Per per; float dt; };
 template <int D>
 __global__ void __launch_bounds__(256) k_proj(const ProjArgs2 a) {
+  pdl_entry();
   const Lay& l = a.l;
   WL_IJK_FROM_BLOCK(D, l)
   if (!inb) return;
@@ -531,6 +537,7 @@ __device__ __forceinline__ void coarse_body(const LevDev* lv, int first, int nle
 }
 template <int D>
 __global__ void __launch_bounds__(1024) k_coarse(const CoarseArgs a) {
+  pdl_entry();
   coarse_body<D>(a.lv, a.first, a.nlev, a.per, a.omega);
 }
 
@@ -545,6 +552,7 @@ inline size_t coarse_smem_bytes(const CoarseArgs& a, int D, int from) {
 }
 template <int D>
 __global__ void __launch_bounds__(1024) k_coarse_sm(const CoarseArgs a) {
+  pdl_entry();
   extern __shared__ __align__(16) float csm[];
   __shared__ LevDev slv[WL_MAXLEV];
   if (threadIdx.x == 0) {

@@ -51,6 +51,7 @@ __device__ __forceinline__ void quad_nbr(const Lay& l, const Per& per, int i, in
 // ---------------------------------------------------------------- increment! (Poisson.jl:100-104), 4 cells per thread
 // perBC!(ϵ) folded into wrap-reads as in k_increment_w; L₁/L∞ partials per block (k_fold_partials folds them)
 __global__ void __launch_bounds__(256) k_incr4(const SmArgs a) {
+  pdl_entry();
   const Lay& l = a.p.l;
   WL_QUAD_FROM_BLOCK(l)
   double s1 = 0.0; float m = -INFINITY;
@@ -91,6 +92,7 @@ __global__ void __launch_bounds__(256) k_incr4(const SmArgs a) {
 // gauss_rb (Poisson.jl:124-128) over half_rangek (:130-132).  The thread rewrites its two quads whole:
 // the cells of the other colour get back the value that was read (nobody writes them in this sweep).
 __global__ void __launch_bounds__(256) k_gs8(const LevArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const int i = 1 + 8 * (blockIdx.x * blockDim.x + threadIdx.x);
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
@@ -136,6 +138,7 @@ __global__ void __launch_bounds__(256) k_gs8(const LevArgs a) {
 
 // ---------------------------------------------------------------- K-DIVRES, 4 cells per thread (see k_divres)
 __global__ void __launch_bounds__(256) k_divres4(const DivResArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   WL_QUAD_FROM_BLOCK(l)
   double s = 0.0;
@@ -181,6 +184,7 @@ __global__ void __launch_bounds__(256) k_divres4(const DivResArgs a) {
 
 // ---------------------------------------------------------------- K-PROJ, 4 cells per thread (see k_proj)
 __global__ void __launch_bounds__(256) k_proj4(const ProjArgs2 a) {
+  pdl_entry();
   const Lay& l = a.l;
   WL_QUAD_FROM_BLOCK(l)
   if (!inb) return;
@@ -229,6 +233,7 @@ __global__ void __launch_bounds__(256) k_proj4(const ProjArgs2 a) {
 // ---------------------------------------------------------------- K-UP, 4 cells per thread (see k_up)
 // prolongate! + perBC! + increment!(ω) (+ ϵ = r·iD for the smoother that follows).  Any coarsening mask.
 __global__ void __launch_bounds__(256) k_up4(const UpArgs a) {
+  pdl_entry();
   const Lay& l = a.f.l;
   const Lay& lc = a.c.l;
   WL_QUAD_FROM_BLOCK(l)
@@ -289,6 +294,7 @@ __global__ void __launch_bounds__(256) k_up4(const UpArgs a) {
 // Jacobi! (ϵ=r·iD, perBC!, increment! with ω=1) + restrict! + fill!(coarse.x,0), for levels coarsened
 // in every direction.  blockDim (32,4,2): the block's 128x4x2 cells are the children of 64x2x1 coarse cells.
 __global__ void __launch_bounds__(256) k_down4(const DownArgs a) {
+  pdl_entry();
   __shared__ float tile[2][4][128];
   const Lay& l = a.f.l;
   const Lay& lc = a.c.l;

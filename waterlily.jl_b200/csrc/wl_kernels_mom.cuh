@@ -98,6 +98,7 @@ __device__ __forceinline__ float rhs_f(const MomArgs& a, int ci, int c0, int c1,
 
 template <int D, int S>
 __global__ void __launch_bounds__(256) k_mom_rhs(const MomArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const int i = blockIdx.x * 32 + threadIdx.x - LPAD;   // lane 31 of block 0 is i==0; i==1 starts a line
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
@@ -121,6 +122,7 @@ struct BdimArgs {
 // K-BDIM: second loop of BDIM! (Flow.jl:179) over inside_u, fused with scale_u!.
 template <int D>
 __global__ void __launch_bounds__(256) k_bdim(const BdimArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
@@ -180,6 +182,7 @@ __device__ __forceinline__ float bc_resolve(const BcArgs& a, int ci, int c0, int
 // threads cover the plane's other two coordinates (fastest remaining dim on threadIdx.x).
 template <int D>
 __global__ void k_bc_vec(const BcArgs a) {
+  pdl_entry();
   const int dj = blockIdx.z / 3, which = blockIdx.z % 3;
   const Lay& l = a.l;
   const int N[3] = {l.n0, l.n1, l.n2};
@@ -211,6 +214,7 @@ __global__ void k_bc_vec(const BcArgs a) {
 struct PerArgs { Lay l; float* a; int dj; };
 template <int D>
 __global__ void k_perbc(const PerArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const int N[3] = {l.n0, l.n1, l.n2};
   const int dj = a.dj;
@@ -232,6 +236,7 @@ __global__ void k_perbc(const PerArgs a) {
 struct ExitArgs { Lay l; float* u; const float* u0; float dt; };
 template <int D>
 __global__ void __launch_bounds__(1024) k_exitbc(const ExitArgs a) {
+  pdl_entry();
   __shared__ double sh[32];
   __shared__ float bcast;
   const Lay& l = a.l;
@@ -281,6 +286,7 @@ __global__ void __launch_bounds__(1024) k_exitbc(const ExitArgs a) {
 // stage 2: subtract the flux defect (in0: inflow sums, in1: exit sums).  `len` = cells of the GLOBAL plane.
 struct ExitDistArgs { Lay l; float* u; const float* u0; float dt; int stage; long long len; RedIn in0, in1; Red* out; };
 __global__ void __launch_bounds__(1024) k_exitbc_dist(const ExitDistArgs a) {
+  pdl_entry();
   __shared__ double sh[32];
   const Lay& l = a.l;
   const int m1 = l.n1 - 2, m2 = l.n2 - 2;
@@ -319,6 +325,7 @@ struct ProjArgs { Lay l; float* u; float* x; float* z; const float* L; float dt;
 // z = div(u) inside; x *= dt everywhere (Flow.jl:225)
 template <int D>
 __global__ void __launch_bounds__(256) k_div_scale(const ProjArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
@@ -337,6 +344,7 @@ __global__ void __launch_bounds__(256) k_div_scale(const ProjArgs a) {
 // u[I,i] -= L[I,i]·∂ᵢx inside (Flow.jl:227-229)
 template <int D>
 __global__ void __launch_bounds__(256) k_project(const ProjArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
@@ -354,6 +362,7 @@ __global__ void __launch_bounds__(256) k_project(const ProjArgs a) {
 // x ./= dt everywhere (Flow.jl:230)
 template <int D>
 __global__ void __launch_bounds__(256) k_unscale(const ProjArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
   const int j = blockIdx.y * blockDim.y + threadIdx.y;
@@ -368,6 +377,7 @@ __global__ void __launch_bounds__(256) k_unscale(const ProjArgs a) {
 struct CflArgs { Lay l; const float* u; float* sigma; RedWork w; Red* out; int zlo, zhi; };
 template <int D>
 __global__ void __launch_bounds__(256) k_cfl(const CflArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   float m = -INFINITY;
   // 1-D persistent grid over ALL cells, four tiles per trip with their loads issued together (see
@@ -420,6 +430,7 @@ __global__ void __launch_bounds__(256) k_cfl(const CflArgs a) {
 struct GhostPhiArgs { Lay l; const float* u; float* sigma; Per per; float nu; };
 template <int D, int S>
 __global__ void k_ghost_phi(const GhostPhiArgs a) {
+  pdl_entry();
   const int dg = blockIdx.z;                       // plane: coordinate dg == N-1
   const Lay& l = a.l;
   const int N[3] = {l.n0, l.n1, l.n2};

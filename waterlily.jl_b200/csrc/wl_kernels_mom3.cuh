@@ -279,6 +279,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
 
 template <int S>
 __global__ void __launch_bounds__(32 * M3_TY, 2) k_mom3(const Mom3Args a) {
+  pdl_entry();
   __shared__ Mom3Smem sm;
   // FAST: every thread of the block sits on an ordinary cell with ordinary faces (in a periodic direction
   // that is every block whose last lane / row still lies inside the array)
@@ -304,6 +305,7 @@ struct PatchArgs {
 };
 template <int S>
 __global__ void __launch_bounds__(128) k_mom_patch(const PatchArgs a) {
+  pdl_entry();
   const Lay& l = a.m.l;
   const int n = min(*a.count, a.cap);
   const int lane = threadIdx.x & 31;
@@ -334,6 +336,7 @@ __global__ void __launch_bounds__(128) k_mom_patch(const PatchArgs a) {
 struct BandArgs { Lay l; const float* mu1; int* list; int* count; int cap; };
 template <int D>
 __global__ void __launch_bounds__(256) k_band_scan(const BandArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
@@ -353,6 +356,7 @@ __global__ void __launch_bounds__(256) k_band_scan(const BandArgs a) {
 // exit plane keeps its old values until exitBC! rewrites it, core.jl:212,226-233)
 struct ExitCopyArgs { Lay l; const float* src; float* dst; };
 __global__ void k_copy_exit_plane(const ExitCopyArgs a) {
+  pdl_entry();
   const Lay& l = a.l;
   const int j = blockIdx.x * blockDim.x + threadIdx.x, k = blockIdx.y;
   if (j >= l.n1 || k >= l.n2) return;

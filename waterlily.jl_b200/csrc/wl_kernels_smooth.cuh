@@ -143,6 +143,7 @@ __device__ __forceinline__ void sf_sweep(const SmoothFArgs& a, SfSmem& sm, const
 
 template <int D>
 __global__ void __launch_bounds__(SF_NT, 2) k_smooth_fused(const SmoothFArgs a) {
+  pdl_entry();
   extern __shared__ __align__(16) unsigned char sf_raw[];
   SfSmem& sm = *reinterpret_cast<SfSmem*>(sf_raw);
   const Lay& l = a.p.l;
