@@ -483,9 +483,13 @@ LevDev levdev_window(wl_sim* s, const Level& fine, const Level& co) {
   }
   return d;
 }
-// one block of 1024 threads sweeps a level in (cells/1024) dependent round trips to L2 per phase:
-// worthwhile up to ~18^3, beyond that the per-level launches win
-inline bool level_is_small(const Level& p) { return !p.dist && (long long)p.lay.n0 * p.lay.n1 * p.lay.n2 <= 8000; }
+// one block of 1024 threads sweeps a level in (cells/1024) dependent round trips to L2 per phase (~1 µs
+// per phase whatever the size): with dependent launches costing ~2.5 µs per kernel it pays up to ~10³
+// (measured on TGV 128³: limit 8000 -> 0.311, 2000 -> 0.298, 300 -> 0.303 ns/cell/step)
+inline bool level_is_small(const Level& p) {
+  static const long long lim = getenv("WL_SMALL_CELLS") ? atoll(getenv("WL_SMALL_CELLS")) : 2000;
+  return !p.dist && (long long)p.lay.n0 * p.lay.n1 * p.lay.n2 <= lim;
+}
 // GaussSeidelRB!(p;it=4,ω): ϵ init + ghost images, 4 half sweeps on stale ghosts, wrap-read increment.
 // Distributed levels: the ϵ ghost planes at slab interfaces are refreshed after every half sweep (a
 // colour only reads the other colour, so this reproduces the single-domain sweep exactly); the
