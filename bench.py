@@ -116,6 +116,14 @@ class ClockSampler:
         return out
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from `ncu --set full`
+# captures of these exact workloads on one GPU (summaries under profiles/): (bytes per launch, source)
+NCU_TRAFFIC = {
+    ("tgv", (128, 128, 128)): (83.80e6 + 11.83e6, "profiles/r1_v12_ncu_full_kmom3_tgv128.tsv (most of the 128^3 working set stays in the 126 MB L2)"),
+    ("sphere", (512, 256, 256)): (1276.7e6 + 392.1e6, "profiles/r1_v12_ncu_full_kmom3_sphere512.tsv"),
+}
+
+
 def measured_peak():
     try:
         pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -264,7 +272,9 @@ def main():
     balg = B_ALG[balg_key][D]
     achieved = (balg * cells / world) / (kms / max(kn, 1) * 1e-3) / 1e9 if kn else None     # per GPU (rank 0's kernel)
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": (achieved / peak) if achieved else None, "traffic": None,
+                "frac": (achieved / peak) if achieved else None,
+                "traffic": NCU_TRAFFIC.get((args.workload, tuple(dims)), (None, None))[0] if world == 1 else None,
+                "traffic_source": NCU_TRAFFIC.get((args.workload, tuple(dims)), (None, None))[1] if world == 1 else None,
                 "alg_bytes_per_cell": balg, "launches": kn, "avg_ms": kms / max(kn, 1), "peak_source": peak_src,
                 "share_of_step": kms / dev_ms}
 

@@ -84,6 +84,7 @@ struct wl_sim {
   char* peer_all[P2P_MAXRANKS] = {};                  // every rank's arena (own included) when nranks <= P2P_MAXRANKS
   bool p2p_gather = false;                            // reduction slots travel by k_gather_p2p instead of NCCL
   unsigned int gseq = 0;
+  unsigned int cnt_lo = 0, cnt_hi = 0;                // halo arrival-counter totals per link
   bool p2p = false;
   unsigned int seq_lo = 0, seq_hi = 0;                // exchanges done on the lower / upper link
   float* stage = nullptr;     // packed device buffer for upload/download (grown on demand)
@@ -302,6 +303,10 @@ int halo(wl_sim* s, const DevField& f, int depth, bool wrap = true, bool idle = 
     if (use_hi) a.seq_hi = ++s->seq_hi;
     long long nb = ((long long)cnt * a.nseg + 2047) / 2048;
     nb = nb < 1 ? 1 : (nb > 296 ? 296 : nb);
+    // both ends of a link run this exchange with the same segment count and size, hence the same grid
+    a.counters = getenv_flag("WL_HALO_COUNTERS") ? 1 : 0;
+    if (use_lo) a.cnt_lo = (s->cnt_lo += (unsigned)nb);
+    if (use_hi) a.cnt_hi = (s->cnt_hi += (unsigned)nb);
     LAUNCH(s, k_halo_p2p, dim3((unsigned)nb), dim3(256), a);
     return WL_OK;
   }
