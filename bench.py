@@ -76,12 +76,31 @@ def workload(name, size=None, zmul=1, nz=None):
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md): NVML polled every
+    millisecond from a thread (the default timed region lasts ~15 ms, too short for `nvidia-smi -lms`), with
+    the nvidia-smi loop as the fallback when NVML cannot be loaded."""
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, device):
+        self.samples, self.mask, self.max_mhz, self.power = [], 0, None, 0.0
+        self.stop_flag = False
+        self.thread = self.p = self.f = None
+        try:
+            import pynvml
+            import threading
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(int(device))
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self._poll()
+            self.thread = threading.Thread(target=self._run, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.thread = None
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(device), f"--query-gpu={self.Q}",
@@ -90,8 +109,37 @@ class ClockSampler:
         except Exception:
             self.p = None
 
+    def _poll(self):
+        nv = self.nv
+        self.samples.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+        try:
+            get = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            self.mask |= int(get(self.h))
+            self.power = max(self.power, nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+        except Exception:
+            pass
+
+    def _run(self):
+        while not self.stop_flag:
+            try:
+                self._poll()
+            except Exception:
+                break
+            time.sleep(0.001)
+
     def stop(self):
         out = dict(sm_mhz=None, sm_max_mhz=None, reasons=[])
+        if self.thread is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=2)
+            try:
+                self._poll()
+            except Exception:
+                pass
+            sm = sorted(self.samples)
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=self.max_mhz, power_w_max=self.power, samples=len(sm),
+                       reasons=[nm for bit, nm in self.REASONS if self.mask & bit], source="nvml, 1 ms polling")
+            return out
         if self.p is None:
             return out
         self.p.terminate()
@@ -113,6 +161,7 @@ class ClockSampler:
             if any("Active" == r[5 + i].strip() for r in rows):
                 out["reasons"].append(nm)
         out["samples"] = len(rows)
+        out["source"] = "nvidia-smi -lms 100"
         return out
 
 

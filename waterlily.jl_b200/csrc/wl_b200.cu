@@ -85,6 +85,7 @@ struct wl_sim {
   bool p2p_gather = false;                            // reduction slots travel by k_gather_p2p instead of NCCL
   unsigned int gseq = 0;
   unsigned int cnt_lo = 0, cnt_hi = 0;                // halo arrival-counter totals per link
+  unsigned int gs_seq_lo = 0, gs_seq_hi = 0;          // fused half-sweep pushes per link (k_gs_half_cx)
   bool p2p = false;
   unsigned int seq_lo = 0, seq_hi = 0;                // exchanges done on the lower / upper link
   float* stage = nullptr;     // packed device buffer for upload/download (grown on demand)
@@ -273,12 +274,14 @@ static bool getenv_flag(const char* name) {
 // half-sweeps: the sweep that ran since the last exchange read only ghost cells of the OTHER colour, whose
 // values this exchange rewrites unchanged, and the neighbour cannot be further behind than that sweep
 // (it left the previous exchange only after receiving this rank's planes).
-int halo(wl_sim* s, const DevField& f, int depth, bool wrap = true, bool idle = false) {
+// only_wrap: just the links that close a periodic ring (the others were served by fused kernels).
+int halo(wl_sim* s, const DevField& f, int depth, bool wrap = true, bool idle = false, bool only_wrap = false) {
   const Dist& d = s->dist;
   if (d.n == 1) return WL_OK;
   const Lay& l = f.lay;
   const size_t cnt = (size_t)l.plane * depth;
-  const bool use_lo = d.lo >= 0 && (wrap || !d.lo_wrap), use_hi = d.hi >= 0 && (wrap || !d.hi_wrap);
+  const bool use_lo = d.lo >= 0 && (wrap || !d.lo_wrap) && (!only_wrap || d.lo_wrap),
+             use_hi = d.hi >= 0 && (wrap || !d.hi_wrap) && (!only_wrap || d.hi_wrap);
   if (!use_lo && !use_hi) return WL_OK;
   s->halo_msgs += 1;
   s->halo_bytes += (int64_t)cnt * 4 * f.ncomp * ((use_lo ? 1 : 0) + (use_hi ? 1 : 0));
@@ -568,11 +571,39 @@ int smooth2(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready = false) {
   // k_gs8 (8 cells per thread) measured no faster than the colour-compacted scalar sweep: opt-in only
   static const bool gs8 = getenv("WL_GS8") != nullptr;
   const bool v8 = gs8 && v4 && (p.lay.n0 - 2) % 8 == 0;
+  // slab interfaces: exchange fused into the sweeps (k_gs_half_cx) when the planes can be pushed to peers
+  const Dist& d = s->dist;
+  const bool link_lo = d.lo >= 0 && !d.lo_wrap, link_hi = d.hi >= 0 && !d.hi_wrap;
+  const bool fuse = p.dist && s->p2p && p.eps.in_arena && s->D == 3 && v4 && !v8 && blk(3).z == 2 &&
+                    (link_lo || link_hi) && !getenv_flag("WL_NO_GS_FUSE");
+  GsLink x{};
+  if (fuse) {
+    auto peer = [&](char* pb, float* mine) { return reinterpret_cast<float*>(pb + (reinterpret_cast<char*>(mine) - s->arena)); };
+    if (link_lo) x.peer_lo = peer(s->peer_lo, p.eps.base);
+    if (link_hi) x.peer_hi = peer(s->peer_hi, p.eps.base);
+    x.my = reinterpret_cast<unsigned int*>(s->arena);
+    x.nb_lo = reinterpret_cast<unsigned int*>(s->peer_lo);
+    x.nb_hi = reinterpret_cast<unsigned int*>(s->peer_hi);
+  }
   for (int k0 = 1; k0 <= 4; ++k0) {
     g.k0 = k0;
+    if (fuse) {
+      x.wait_lo = link_lo && k0 > 1; x.wait_hi = link_hi && k0 > 1;
+      x.wait_seq_lo = s->gs_seq_lo; x.wait_seq_hi = s->gs_seq_hi;
+      x.push_lo = link_lo; x.push_hi = link_hi;
+      if (link_lo) x.push_seq_lo = ++s->gs_seq_lo;
+      if (link_hi) x.push_seq_hi = ++s->gs_seq_hi;
+      LAUNCH(s, k_gs_half_cx<3>, gg, blk(3), g, x);
+      if (k0 == 4 && (d.lo_wrap || d.hi_wrap)) { if (int e = halo(s, p.eps, 1, true, false, true)) return e; }
+      continue;
+    }
     if (v8) LAUNCH(s, k_gs8, grid_quads(p.lay, 8), dim3(32, 4, 2), g);
     else DISPATCH_D(s, k_gs_half_c, gg, blk(s->D), g);
     if (p.dist) { if (int e = halo(s, p.eps, 1, k0 == 4, true)) return e; }
+  }
+  if (fuse) {
+    a.wflag = x.my; a.wait_lo = link_lo; a.wait_hi = link_hi;
+    a.wait_seq_lo = s->gs_seq_lo; a.wait_seq_hi = s->gs_seq_hi;
   }
   if (v4) {
     const dim3 gq = grid_quads(p.lay);

@@ -220,6 +220,77 @@ __global__ void __launch_bounds__(256) k_gs_half_c(const LevArgs a) {
   a.eps[o] = s * inv_or_zero(dg);
 }
 
+// The half sweep with the slab-interface exchange FUSED in (multi-GPU, peer-mapped arenas; host side in
+// smooth2).  Blocks of the two boundary slabs run first.  Producer: a thread that updates a cell of plane 1
+// (plane n2-2) also stores it into the lower (upper) neighbour's ghost plane over NVLink; the last block of
+// each boundary slab raises that neighbour's arrival flag.  Consumer: the boundary-slab blocks of the NEXT
+// sweep (or of the increment) wait for their arrival flag before they read the ghost plane; everything
+// else of that kernel overlaps the transfer.  No separate exchange kernel, no ready handshake: having seen
+// arrival(s-1) from a neighbour proves that its boundary blocks finished sweep s-1, the only readers of the
+// ghost cells sweep s overwrites.
+struct GsLink {
+  float* peer_lo; float* peer_hi;                    // the neighbours' copies of ϵ (same arena offset)
+  unsigned int* my; unsigned int* nb_lo; unsigned int* nb_hi;   // arena headers: [8],[9] tickets, [10] arrival
+                                                     // from the lower neighbour, [11] from the upper
+  unsigned int push_seq_lo, push_seq_hi, wait_seq_lo, wait_seq_hi;
+  int push_lo, push_hi, wait_lo, wait_hi;
+};
+template <int D>
+__global__ void __launch_bounds__(256) k_gs_half_cx(const LevArgs a, const GsLink x) {
+  pdl_entry();
+  const Lay& l = a.l;
+  const int gz = gridDim.z;
+  const int zb = blockIdx.z == 0 ? 0 : (blockIdx.z == 1 ? gz - 1 : (int)blockIdx.z - 1);   // boundary slabs first
+  const bool lo_blk = zb == 0, hi_blk = zb == gz - 1;
+  const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
+  if ((lo_blk && x.wait_lo) || (hi_blk && x.wait_hi)) {
+    if (tid == 0) {
+      if (lo_blk && x.wait_lo) wait_flag(x.my + 10, x.wait_seq_lo, x.my + 5);
+      if (hi_blk && x.wait_hi) wait_flag(x.my + 11, x.wait_seq_hi, x.my + 5);
+    }
+    __syncthreads();
+  }
+  const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  const int k = zb * blockDim.z + threadIdx.z + 1;
+  const int i = 1 + 2 * (blockIdx.x * blockDim.x + threadIdx.x) + ((j + k + D + a.k0) & 1);
+  if (i <= l.n0 - 2 && j <= l.n1 - 2 && k <= l.n2 - 2 && k <= 2 * (l.n2 / 2) - 2) {
+    const int o = l.off(i, j, k);
+    const int st[3] = {1, l.pitch, l.plane};
+    float lo[3], hi[3], em[3], ep[3];
+    const float r0 = a.r[o];
+#pragma unroll
+    for (int q = 0; q < D; ++q) {
+      const float* Lq = a.L + l.cstride * q;
+      lo[q] = Lq[o]; hi[q] = Lq[o + st[q]];
+      em[q] = a.eps[o - st[q]]; ep[q] = a.eps[o + st[q]];
+    }
+    float s = r0, dg = 0.f;
+#pragma unroll
+    for (int q = 0; q < D; ++q) {
+      dg -= lo[q] + hi[q];
+      s -= em[q] * lo[q] + ep[q] * hi[q];
+    }
+    const float v = s * inv_or_zero(dg);
+    a.eps[o] = v;
+    if (x.push_lo && k == 1) x.peer_lo[o + l.plane * (l.n2 - 2)] = v;
+    if (x.push_hi && k == l.n2 - 2) x.peer_hi[o - l.plane * (l.n2 - 2)] = v;
+  }
+  const bool sig_lo = lo_blk && x.push_lo, sig_hi = hi_blk && x.push_hi;
+  if (sig_lo || sig_hi) {
+    __syncthreads();
+    if (tid == 0) {
+      __threadfence_system();
+      const unsigned int nside = gridDim.x * gridDim.y;
+      if (sig_lo && atomicAdd(x.my + 8, 1u) == nside - 1) {
+        x.my[8] = 0u; __threadfence_system(); st_relaxed_sys(x.nb_lo + 11, x.push_seq_lo);
+      }
+      if (sig_hi && atomicAdd(x.my + 9, 1u) == nside - 1) {
+        x.my[9] = 0u; __threadfence_system(); st_relaxed_sys(x.nb_hi + 10, x.push_seq_hi);
+      }
+    }
+  }
+}
+
 // restrict! (MultiLevelPoisson.jl:13-19,49): coarse r = Σ fine children, first dim fastest.
 struct XferArgs { Lay lf, lc; const float* src; float* dst; int c[3]; };
 template <int D>

@@ -340,7 +340,11 @@ __global__ void __launch_bounds__(256) k_up(const UpArgs a) {
 // ---------------------------------------------------------------- smoother pieces
 // ϵ = r·iD inside + perBC!(ϵ) images  (GaussSeidelRB! Poisson.jl:142-143).  The sweeps then read
 // these ghosts as they are (never refreshed between sweeps: the reference's stale-ghost behaviour).
-struct SmArgs { LevDev p; Per per; float omega; int k0; RedWork w; Red* out; int want_norms; };
+struct SmArgs {
+  LevDev p; Per per; float omega; int k0; RedWork w; Red* out; int want_norms;
+  // k_incr4 after fused half sweeps (k_gs_half_cx): arrival flags the boundary slabs wait for
+  unsigned int* wflag; unsigned int wait_seq_lo, wait_seq_hi; int wait_lo, wait_hi;
+};
 template <int D>
 __global__ void __launch_bounds__(256) k_eps_init_g(const SmArgs a) {
   pdl_entry();

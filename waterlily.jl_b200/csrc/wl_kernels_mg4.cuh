@@ -53,6 +53,16 @@ __device__ __forceinline__ void quad_nbr(const Lay& l, const Per& per, int i, in
 __global__ void __launch_bounds__(256) k_incr4(const SmArgs a) {
   pdl_entry();
   const Lay& l = a.p.l;
+  if (a.wait_lo | a.wait_hi) {                         // ϵ ghost planes pushed by the neighbours' last half sweep
+    const bool wlo = a.wait_lo && blockIdx.z == 0, whi = a.wait_hi && blockIdx.z == gridDim.z - 1;
+    if (wlo || whi) {
+      if (threadIdx.x + threadIdx.y + threadIdx.z == 0) {
+        if (wlo) wait_flag(a.wflag + 10, a.wait_seq_lo, a.wflag + 5);
+        if (whi) wait_flag(a.wflag + 11, a.wait_seq_hi, a.wflag + 5);
+      }
+      __syncthreads();
+    }
+  }
   WL_QUAD_FROM_BLOCK(l)
   double s1 = 0.0; float m = -INFINITY;
   if (inb) {
