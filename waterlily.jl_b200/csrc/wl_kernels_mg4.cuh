@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(256) k_incr4(const SmArgs a) {
     st4(a.p.r + o, rn);
     st4(a.p.x + o, xn);
   }
-  if (a.want_norms) block_reduce_partial(s1, m, a.w);
+  if (a.want_norms) { if (a.w.finish) block_reduce_finish(s1, m, a.w, a.out); else block_reduce_partial(s1, m, a.w); }
 }
 
 // ---------------------------------------------------------------- red-black half sweep, 8 cells per thread (4 updated)
@@ -189,7 +189,8 @@ __global__ void __launch_bounds__(256) k_divres4(const DivResArgs a) {
     st4(a.r + o, rr);
     st4(a.xs + o, xs);
   }
-  block_reduce_partial(s, -INFINITY, a.w);
+  if (a.w.finish) block_reduce_finish(s, -INFINITY, a.w, a.out);
+  else block_reduce_partial(s, -INFINITY, a.w);
 }
 
 // ---------------------------------------------------------------- K-PROJ, 4 cells per thread (see k_proj)
@@ -380,7 +381,7 @@ __global__ void __launch_bounds__(256) k_down4(const DownArgs a) {
       a.c.x[oc + p] = 0.f;                                             // fill!(coarse.x,0)  MLP.jl:94
     }
   }
-  if (a.first) block_reduce_partial(s1, mx, a.w);
+  if (a.first) { if (a.w.finish) block_reduce_finish(s1, mx, a.w, a.out); else block_reduce_partial(s1, mx, a.w); }
 }
 
 }  // namespace wl
