@@ -134,6 +134,12 @@ int wl_build_poisson(wl_sim* s);
 int wl_update_poisson(wl_sim* s);
 int wl_solver(wl_sim* s, int32_t* n_iter, int32_t* trace_len, float* rinf, float* r1, float* omega);
 
+/* ---- stand-alone single-level solver: `solver!(p::Poisson;tol,itmx)` with the Jacobi-preconditioned
+ *      `pcg!(p;it=6)` smoother (src/Poisson.jl:166-186,212-223) on level 1 (x = p, z = σ, L = μ₀), for
+ *      users who pass `pois_ctor = flow->Poisson(flow.p,flow.μ₀,flow.σ)`.  tol comes from the config.
+ *      Single GPU (WL_ERR_UNSUPPORTED on a slab-decomposed sim).                                 */
+int wl_poisson_solver(wl_sim* s, int32_t itmx, int32_t* n_iter);
+
 /* ---- time step: mom_step! (src/Flow.jl:156-167).  uBC_t1 = boundary velocity at t₁ (NULL: cfg.uBC);
  *      acc0/acc1 = space-uniform g+dU/dt at t₀/t₁ for accelerate! (src/Flow.jl:69-73), may be NULL.
  *      Uses and replaces the stored Δt (wl_get_dt / wl_set_dt).                                */
@@ -169,7 +175,8 @@ int wl_event_elapsed_ms(wl_sim* s, int a, int b, float* ms);
 /* ---- test hook: run ONE constituent operation of the step so that kernel-level parity tests can
  *      compare it with the oracle.  op: 0 BC!(u,uBC,exitBC) 1 conv_diff!+BDIM! predictor (u from u⁰)
  *      2 mom_project!(w=arg) 3 residual!(level) 4 Vcycle!(ω=arg) 5 smooth!(level,ω=arg)
- *      6 Jacobi!(level) 7 exitBC!(u,u⁰,Δt) 8 conv_diff!+BDIM!+scale corrector 9 u⁰ .= u          */
+ *      6 Jacobi!(level) 7 exitBC!(u,u⁰,Δt) 8 conv_diff!+BDIM!+scale corrector 9 u⁰ .= u
+ *      10 pcg!(levels[1];it=arg)                                                                 */
 int wl_debug_op(wl_sim* s, int op, int level, float arg);
 
 #ifdef __cplusplus

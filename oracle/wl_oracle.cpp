@@ -920,6 +920,7 @@ void wlo_op_smooth(void* h, int l, real w) { GaussSeidelRB(((Sim*)h)->ml.lv[l], 
 void wlo_op_increment(void* h, int l, real w) { increment(((Sim*)h)->ml.lv[l], w); }
 void wlo_op_restrict(void* h, int l) { Sim* s = (Sim*)h; restrict_r(s->ml.lv[l + 1], s->ml.lv[l]); }
 void wlo_op_prolongate(void* h, int l) { Sim* s = (Sim*)h; prolongate(s->ml.lv[l], s->ml.lv[l + 1]); }
+void wlo_op_pcg(void* h, int l, int it) { pcg(((Sim*)h)->ml.lv[l], it); }
 void wlo_op_vcycle(void* h, real w) { Vcycle(((Sim*)h)->ml, 0, w); }
 real wlo_op_L1(void* h, int l) { return L1(((Sim*)h)->ml.lv[l]); }
 real wlo_op_Linf(void* h, int l) { return Linf(((Sim*)h)->ml.lv[l]); }

@@ -106,6 +106,7 @@ def load(dtype=np.float32, fast_path=None):
     lib.wlo_op_smooth.argtypes = [C.c_void_p, C.c_int, R]
     lib.wlo_op_increment.argtypes = [C.c_void_p, C.c_int, R]
     lib.wlo_op_vcycle.argtypes = [C.c_void_p, R]
+    lib.wlo_op_pcg.argtypes = [C.c_void_p, C.c_int, C.c_int]
     lib.wlo_op_L1.restype = R
     lib.wlo_op_L1.argtypes = [C.c_void_p, C.c_int]
     lib.wlo_op_Linf.restype = R

@@ -132,6 +132,54 @@ def test_solver_manufactured(wl, N, n_max):
         assert np.abs(sim.pois.levels[0].r).max() < 2e-3
 
 
+@pytest.mark.parametrize("N,n_max,err_max", [((66, 66), 340, 5e-6), ((18, 18, 18), 40, 1e-6), ((34, 18, 10), 200, 1e-5)])
+def test_poisson_pcg_manufactured(wl, N, n_max, err_max):
+    """`Poisson_setup(Poisson, N)` (test/test_poisson.jl:1-12,20-26): the stand-alone single-level
+    `solver!` with `pcg!` (src/Poisson.jl:166-186,212-223) on the GPU against the oracle's restatement:
+    same iteration count, x within 1e-5 of the oracle's, and the reference's own error bounds."""
+    D = len(N)
+    dims = tuple(n - 2 for n in N)
+    sim, ref = pair(wl, dims, (0.0,) * D)
+    soln = np.zeros(ref.field("p").shape, np.float32)
+    soln[...] = (np.arange(N[0], dtype=np.float32) - 1).reshape((1,) * (D - 1) + (N[0],))
+    ref.lib.wlo_mult(ref.h, soln.ctypes.data)
+    sim.upload("sigma", ref.field("sigma"))
+    n_ref = ref.lib.wlo_poisson_solver(ref.h, 1000)
+    n = sim.poisson_solver(1000)
+    # CG amplifies last-bit differences of the dot products (block order vs row order): the count may move by
+    # an iteration over a few hundred, and x agrees to the solver's own tolerance rather than to rounding
+    assert abs(n - n_ref) <= 1 + n_ref // 50 and n < n_max, (n, n_ref)
+    x = sim.flow.p
+    close(x, ref.field("p"), 1e-4, "x")
+    x = x - x[(1,) * D]
+    inner = tuple(slice(1, -1) for _ in N)
+    err = np.sum((x - soln)[inner].astype(np.float64) ** 2) / np.sum(soln[inner].astype(np.float64) ** 2)
+    assert err < err_max
+    assert np.abs(sim.pois.levels[0].r).max() < 2e-3
+
+
+@pytest.mark.parametrize("dims,perdir,body", [
+    ((32, 16), (), dict(kind="sphere", center=(10, 8), radius=4.0)),
+    ((16, 16, 8), (3,), dict(kind="sphere", center=(8, 8, 4), radius=3.0)),
+    ((16, 8, 8), (1, 2, 3), None)])
+def test_pcg_single_call(wl, dims, perdir, body):
+    """One `pcg!(p;it=6)` (src/Poisson.jl:166-186) from the same random r and x on a variable-coefficient
+    operator: x, r and the search direction agree with the oracle to kernel-level tolerance."""
+    sim, ref = pair(wl, dims, (0.0,) * len(dims), body=body, perdir=perdir)
+    rng = np.random.default_rng(11)
+    inner = tuple(slice(1, -1) for _ in dims)
+    for nm, lev in (("r", 0), ("p", None)):
+        a = ref.field(nm, 0) if lev is not None else ref.field(nm)
+        a[...] = 0
+        a[inner] = rng.uniform(-1, 1, a[inner].shape).astype(np.float32)
+        sim.upload(nm, a) if lev is None else sim.upload(nm, a, 0)
+    ref.lib.wlo_op_pcg(ref.h, 0, 6)
+    sim.debug_op(10, 0, 6)
+    close(sim.flow.p, ref.field("p"), 2e-5, "x")
+    close(sim.pois.levels[0].r, ref.field("r", 0), 2e-5, "r")
+    close(sim.download("eps", 0)[inner], ref.field("eps", 0)[inner], 2e-5, "eps")
+
+
 def test_level_data_surface(wl):
     """pois.levels[l].D / .L after update! (test/test_poisson.jl:54-60) through download/upload."""
     sim, ref = pair(wl, (8, 8), (0.0, 0.0))

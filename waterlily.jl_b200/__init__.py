@@ -34,7 +34,7 @@ KINDS = dict(none=0, sphere=1, circle=1, cylinder=2, torus=3)
 ABI_SYMBOLS = [
     "wl_create", "wl_destroy", "wl_last_error", "wl_version", "wl_field_dims", "wl_download",
     "wl_upload", "wl_nlevels", "wl_finish_ic", "wl_measure_body", "wl_set_body_coeffs",
-    "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
+    "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_poisson_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
     "wl_cfl", "wl_pressure_force", "wl_sync", "wl_launch_count", "wl_enable_timing",
     "wl_last_phase_times", "wl_debug_op", "wl_prof_begin", "wl_prof_end", "wl_event_record",
     "wl_event_elapsed_ms", "wl_create_slab", "wl_nccl_unique_id", "wl_slab_info", "wl_halo_stats", "wl_halo_transport", "wl_halo_timing",
@@ -106,6 +106,7 @@ def load_library(path=None):
     lib.wl_build_poisson.argtypes = [P]
     lib.wl_update_poisson.argtypes = [P]
     lib.wl_solver.argtypes = [P, C.POINTER(I), C.POINTER(I), FP, FP, FP]
+    lib.wl_poisson_solver.argtypes = [P, I, C.POINTER(I)]
     lib.wl_mom_step.argtypes = [P, FP, FP, FP, C.POINTER(WLStepInfo)]
     lib.wl_get_dt.argtypes = [P, FP]
     lib.wl_set_dt.argtypes = [P, F]
@@ -413,6 +414,12 @@ class Simulation:
         self._check(self.lib.wl_solver(self.h, C.byref(n), C.byref(tl), a, b, c))
         k = tl.value
         return dict(n=n.value, rinf=list(a[:k]), r1=list(b[:k]), omega=list(c[:k]))
+
+    def poisson_solver(self, itmx=1000):
+        """Stand-alone single-level `solver!(p::Poisson;itmx)` with `pcg!` (src/Poisson.jl:166-186,212-223)."""
+        n = C.c_int32()
+        self._check(self.lib.wl_poisson_solver(self.h, int(itmx), C.byref(n)))
+        return n.value
 
     def trace(self, which):
         i = self.last_info

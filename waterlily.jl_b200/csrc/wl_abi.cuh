@@ -527,6 +527,17 @@ int wl_solver(wl_sim* s, int32_t* n_iter, int32_t* trace_len, float* rinf, float
   return check_async(s, "wl_solver");
 }
 
+int wl_poisson_solver(wl_sim* s, int32_t itmx, int32_t* n_iter) {
+  if (!s || s->lv.empty() || itmx < 0) return WL_ERR_INVALID;
+  if (s->dist.n > 1) return fail(s, WL_ERR_UNSUPPORTED, "the stand-alone Poisson/pcg! solver is single-GPU");
+  cudaSetDevice(s->device);
+  int n = 0;
+  if (int e = poisson_solver(s, itmx, &n)) return e;
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  if (n_iter) *n_iter = n;
+  return check_async(s, "wl_poisson_solver");
+}
+
 int wl_get_dt(const wl_sim* s, float* dt) { if (!s || !dt) return WL_ERR_INVALID; *dt = s->dt; return WL_OK; }
 int wl_set_dt(wl_sim* s, float dt) { if (!s) return WL_ERR_INVALID; s->dt = dt; return WL_OK; }
 
@@ -642,6 +653,7 @@ int wl_debug_op(wl_sim* s, int op, int level, float arg) {
     case 7: exitbc(s, s->u, s->u0, s->dt); break;
     case 8: ghost_phi(s); mom_rhs(s, s->u, nullptr); bdim(s, 1); break;
     case 9: cudaMemcpyAsync(s->u0.alloc, s->u.alloc, s->u.bytes, cudaMemcpyDeviceToDevice, s->st); break;
+    case 10: if (s->lv.empty() || s->dist.n > 1) return WL_ERR_INVALID; if (int e = pcg(s, s->lv[0], (int)arg)) return e; break;
     default: return fail(s, WL_ERR_INVALID, "unknown debug op");
   }
   WL_CUDA(s, cudaStreamSynchronize(s->st));

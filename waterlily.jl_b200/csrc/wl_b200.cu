@@ -22,6 +22,7 @@
 #include "wl_kernels_mom3.cuh"
 #include "wl_kernels_smooth.cuh"
 #include "wl_kernels_mg4.cuh"
+#include "wl_kernels_pcg.cuh"
 
 using namespace wl;
 
@@ -790,6 +791,62 @@ int mlp_solver(wl_sim* s, Trace* tr, bool residual_done = false) {
   return WL_OK;
 }
 
+// pcg!(p;it=6) (Poisson.jl:166-186): host control flow of the reference, one read-back per dot product
+int pcg(wl_sim* s, Level& p, int it = 6) {
+  const float epsT = 1.1920929e-07f;
+  PcgArgs a{p.lay, p.L.base, p.iD.base, p.x.base, p.r.base, p.eps.base, p.z.base, 0.f, 0, s->redw, s->d_red + 11};
+  const dim3 g = grid_inside(p.lay), b = blk(s->D);
+  DISPATCH_D(s, k_pcg_init, g, b, a);
+  if (int e = fetch_red(s)) return e;
+  float rho = (float)s->h_red[11].sum;
+  if (std::fabs(rho) < 10 * epsT) return WL_OK;
+  for (int i = 1; i <= it; ++i) {
+    perbc(s, p.lay, p.eps.base, &p.per);
+    DISPATCH_D(s, k_pcg_mult, g, b, a);
+    if (int e = fetch_red(s)) return e;
+    const float alpha = rho / (float)s->h_red[11].sum;
+    if (std::fabs(alpha) < 1e-2 || std::fabs(alpha) > 1e2) return WL_OK;   // also leaves on NaN-free garbage only
+    a.coef = alpha; a.more = i == it ? 0 : 1;
+    DISPATCH_D(s, k_pcg_update, g, b, a);
+    if (i == it) return WL_OK;
+    if (int e = fetch_red(s)) return e;
+    const float rho2 = (float)s->h_red[11].sum;
+    if (std::fabs(rho2) < 10 * epsT) return WL_OK;
+    a.coef = rho2 / rho;
+    DISPATCH_D(s, k_pcg_dir, g, b, a);
+    rho = rho2;
+  }
+  return WL_OK;
+}
+
+// stand-alone solver!(p::Poisson;tol,itmx) (Poisson.jl:212-223) on level 1: residual!, then pcg! until
+// Σ|r| < (tol/10)·N and max|r| < tol; single GPU only
+int poisson_solver(wl_sim* s, int itmx, int* n_out) {
+  Level& p = s->lv[0];
+  const double tol = s->cfg.tol;
+  const double r1tol = (tol / 10) * (double)p.ncells, rinftol = tol;
+  LevArgs a = lev_args(s, p);
+  perbc(s, p.lay, p.x.base, &p.per);
+  a.out = s->d_red + 0;
+  DISPATCH_D(s, k_residual, grid_inside(p.lay), blk(s->D), a);
+  a.in = red_in(s, 0); a.out = s->d_red + 1;
+  DISPATCH_D(s, k_shift_norms, grid_tiles(p.lay, false), blk(s->D), a);
+  int np = 0;
+  while (np < itmx) {
+    if (int e = pcg(s, p)) return e;
+    a.in = red_in(s, 7); a.out = s->d_red + 1;                      // slot 7 stays zero: norms only
+    DISPATCH_D(s, k_shift_norms, grid_tiles(p.lay, false), blk(s->D), a);
+    if (int e = fetch_red(s)) return e;
+    ++np;
+    const float r1 = (float)s->h_red[1].sum, rinf = s->h_red[1].maxv;
+    if (!std::isfinite(r1)) break;
+    if ((double)r1 < r1tol && (double)rinf < rinftol) break;
+  }
+  perbc(s, p.lay, p.x.base, &p.per);
+  if (n_out) *n_out = np;
+  return WL_OK;
+}
+
 // ---------------------------------------------------------------- momentum pieces
 void mom_rhs(wl_sim* s, DevField& uadv, const float* acc) {
   MomArgs a{};
@@ -901,7 +958,15 @@ int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
 }
 int cfl(wl_sim* s, float* out) {
   CflArgs a{s->lay, s->u.base, s->sigma.base, s->redw, s->d_red + 2, s->per.zlo, s->per.zhi};
-  DISPATCH_D(s, k_cfl, grid_tiles(s->lay, true), blk(s->D), a);
+  static const bool scalar_cfl = getenv("WL_SCALAR_CFL") != nullptr;
+  if (use_vec4(s->lay) && !scalar_cfl) {                          // all rows and planes, ghosts included
+    const dim3 g((s->lay.n0 - 2 + 127) / 128, (s->lay.n1 + 3) / 4, (s->lay.n2 + 1) / 2);
+    a.w.finish = finish_in_kernel(g) ? 1 : 0;
+    LAUNCH(s, k_cfl4, g, dim3(32, 4, 2), a);
+    if (!a.w.finish) fold_partials_to(s, g, s->d_red + 2);
+  } else {
+    DISPATCH_D(s, k_cfl, grid_tiles(s->lay, true), blk(s->D), a);
+  }
   if (int e = fetch_red(s)) return e;
   const float m = s->h_red[2].maxv;
   *out = std::fmin(10.f, 1.f / (m + 5.f * s->cfg.nu));

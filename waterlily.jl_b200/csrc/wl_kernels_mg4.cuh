@@ -146,6 +146,52 @@ __global__ void __launch_bounds__(256) k_gs8(const LevArgs a) {
   st4(a.eps + o + 4, F4{{e[5], e[6], e[7], e[8]}});
 }
 
+// ---------------------------------------------------------------- CFL (Flow.jl:234-244), 4 cells per thread
+// Same cells, same per-cell expression and the same "whole-array maximum" as k_cfl: rows and planes
+// 0..N-1 are all visited, a thread on a ghost row takes the maximum of the σ already stored there (zeros
+// below, the corrector's stale Φ above -- k_ghost_phi), a thread on an interior row computes its quad and
+// the first / last thread of the row also folds in the row's two x ghosts.  The maximum does not depend
+// on the order, so Δt is bit-identical to the scalar kernel's.
+__global__ void __launch_bounds__(256) k_cfl4(const CflArgs a) {
+  pdl_entry();
+  const Lay& l = a.l;
+  const int i = 1 + 4 * (blockIdx.x * blockDim.x + threadIdx.x);
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = blockIdx.z * blockDim.z + threadIdx.z;
+  float m = -INFINITY;
+  // slab interfaces: the planes beyond them belong to the neighbour
+  const bool mine = !((a.zlo && k == 0) || (a.zhi && k == l.n2 - 1));
+  if (i <= l.n0 - 2 && j < l.n1 && k < l.n2 && mine) {
+    const int o = l.off(i, j, k);
+    const bool in = j >= 1 && j <= l.n1 - 2 && k >= 1 && k <= l.n2 - 2;
+    const float g0 = i == 1 ? a.sigma[o - 1] : -INFINITY, g1 = i + 3 == l.n0 - 2 ? a.sigma[o + 4] : -INFINITY;
+    m = fmaxf(g0, g1);
+    if (in) {
+      const float* ux = a.u; const float* uy = a.u + l.cstride; const float* uz = a.u + 2 * l.cstride;
+      const F4 u0 = ld4g(ux + o); const float u04 = __ldg(ux + o + 4);
+      const F4 v0 = ld4g(uy + o), v1 = ld4g(uy + o + l.pitch), w0 = ld4g(uz + o), w1 = ld4g(uz + o + l.plane);
+      F4 sg;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float uxu = q < 3 ? u0.v[q < 3 ? q + 1 : 3] : u04;
+        float s = 0.f;                                             // flux_out, Flow.jl:238-244
+        s += fmaxf(0.f, uxu) + fmaxf(0.f, -u0.v[q]);
+        s += fmaxf(0.f, v1.v[q]) + fmaxf(0.f, -v0.v[q]);
+        s += fmaxf(0.f, w1.v[q]) + fmaxf(0.f, -w0.v[q]);
+        sg.v[q] = s;
+        m = fmaxf(m, s);
+      }
+      st4(a.sigma + o, sg);
+    } else {
+      const F4 sg = ld4(a.sigma + o);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) m = fmaxf(m, sg.v[q]);
+    }
+  }
+  if (a.w.finish) block_reduce_finish(0.0, m, a.w, a.out);
+  else block_reduce_partial(0.0, m, a.w);
+}
+
 // ---------------------------------------------------------------- K-DIVRES, 4 cells per thread (see k_divres)
 __global__ void __launch_bounds__(256) k_divres4(const DivResArgs a) {
   pdl_entry();
