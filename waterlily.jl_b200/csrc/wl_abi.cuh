@@ -442,6 +442,7 @@ static int xfer(wl_sim* s, int field, int level, float* host, size_t count, bool
   }
   WL_CUDA(s, cudaStreamSynchronize(s->st));
   if (up && field == WL_MU1) s->band_dirty = true;
+  if (up && (field == WL_MU1 || field == WL_MU0 || field == WL_V)) s->free_flow = false;
   return WL_OK;
 }
 int wl_download(wl_sim* s, int field, int level, float* host, size_t count) { return xfer(s, field, level, host, count, false); }
@@ -467,7 +468,7 @@ int wl_measure_body(wl_sim* s, const wl_body* body, double t, double eps) {
   cudaSetDevice(s->device);
   MeasArgs a{s->lay, body_at(body, s->D, (float)t), (float)eps, s->per.kz0, s->sigma.base, s->V.base, s->mu0.base, s->mu1.base};
   DISPATCH_D(s, k_measure, grid_all(s->lay), blk(s->D), a);
-  s->band_dirty = true;
+  s->band_dirty = true; s->free_flow = false;
   bc_vec(s, s->mu0, nullptr, false);
   bc_vec(s, s->V, nullptr, s->cfg.exitBC != 0);
   if (int e = halo(s, s->mu0, 1)) return e;

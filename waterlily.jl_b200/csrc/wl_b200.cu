@@ -100,6 +100,7 @@ struct wl_sim {
   int* band_count = nullptr;
   int band_cap = 0;
   bool band_dirty = false;
+  bool free_flow = true;      // V ≡ 0, μ₀ ≡ 1, μ₁ ≡ 0 as the constructor left them (no measure!, no upload of them)
   std::vector<Level> lv;
   cudaStream_t st = nullptr;
   RedWork redw{};
@@ -902,9 +903,18 @@ void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, c
   dim3 g((l.n0 - 2 + 30) / 31, (l.n1 - 2 + M3_TY - 2) / (M3_TY - 1), (l.n2 - 2 + a.KZ - 1) / a.KZ);
   dim3 b(32, M3_TY, 1);
   const int sc = s->cfg.scheme;
-  if (sc == 0) LAUNCH(s, k_mom3<0>, g, b, a);
-  else if (sc == 1) LAUNCH(s, k_mom3<1>, g, b, a);
-  else LAUNCH(s, k_mom3<2>, g, b, a);
+  // body-free, fully periodic flow: V ≡ 0 and μ₀ ≡ 1 everywhere, the kernel need not read them
+  static const bool nb_off = getenv("WL_NO_NOBODY") != nullptr;
+  const bool nb = !nb_off && s->free_flow && s->per_glob.p[0] && s->per_glob.p[1] && s->per_glob.p[2];
+  if (nb) {
+    if (sc == 0) LAUNCH(s, (k_mom3<0, true>), g, b, a);
+    else if (sc == 1) LAUNCH(s, (k_mom3<1, true>), g, b, a);
+    else LAUNCH(s, (k_mom3<2, true>), g, b, a);
+  } else {
+    if (sc == 0) LAUNCH(s, (k_mom3<0, false>), g, b, a);
+    else if (sc == 1) LAUNCH(s, (k_mom3<1, false>), g, b, a);
+    else LAUNCH(s, (k_mom3<2, false>), g, b, a);
+  }
   PatchArgs pa{};
   pa.m.l = s->lay; pa.m.ua = ua.base; pa.m.u0 = u0.base; pa.m.V = s->V.base; pa.m.f = nullptr;
   pa.m.per = s->per; pa.m.nu = s->cfg.nu; pa.m.dt = s->dt; pa.m.acc = a.acc;

@@ -59,24 +59,28 @@ __device__ __forceinline__ float flux_v(float um2, float um1, float uc, float up
   return ua * v - nu * (uc - um1);
 }
 
-// Branch-free x/6 for the marching kernel: the Markstein quotient of div6 for every x (exact zeros
-// pass through with their sign), while the smallest non-zero and the largest |x| seen are recorded in
-// amin/amax.  The caller re-evaluates the plane's fluxes with div6 when any |x| fell outside
-// (1e-30, 1e38), so the nine face fluxes of a cell form one straight-line block that the scheduler can
-// interleave.  Exact zeros must stay on this path: early in a run whole regions hold u_y = u_z = 0.
-__device__ __forceinline__ float div6_track(float x, float& amin, float& amax) {
-  const float ax = fabsf(x);
-  const bool z = x == 0.f;
-  amax = fmaxf(amax, ax);
-  amin = fminf(amin, z ? 1.f : ax);
+// Branch-free x/6 for the marching kernel: the Markstein quotient of div6 for every x, while the range of
+// |x| seen is recorded: with b = bits(x)<<1 (sign dropped), bmax = largest b, bmin = smallest b-1 as unsigned, so
+// an exact zero wraps to 0xffffffff and never counts as "too small" (early in a run whole regions hold
+// u_y = u_z = 0).  One integer add-min and one integer max per face, no predicate.  The caller re-evaluates
+// the plane's fluxes with div6 when any non-zero |x| fell outside (1e-30, 1e38), so the nine face fluxes of
+// a cell form one straight-line block that the scheduler can interleave.  For x = ±0 the quotient is +0
+// where IEEE gives ±0: the sign of a zero flux cannot reach a non-zero value (no division by a velocity).
+__device__ __forceinline__ float div6_track(float x, unsigned& bmin, unsigned& bmax) {
+  const unsigned b = __float_as_uint(x) << 1;      // |x| without the sign bit, order-preserving
+  bmax = max(bmax, b);
+  bmin = min(bmin, b - 1u);
   const float y = 1.0f / 6.0f;
   const float q0 = __fmul_rn(x, y);
   const float r = __fmaf_rn(-6.0f, q0, x);
-  return z ? x : __fmaf_rn(r, y, q0);
+  return __fmaf_rn(r, y, q0);
 }
+// bit patterns of the bounds of div6's verified range
+constexpr unsigned DIV6_LO = 0x0DA24260u << 1;   // 1e-30f
+constexpr unsigned DIV6_HI = 0x7E967699u << 1;   // 1e38f
 template <int S, bool EXACT>
 __device__ __forceinline__ float flux_q(float um2, float um1, float uc, float up1, float ua, float nu, int kind,
-                                        float& amin, float& amax) {
+                                        unsigned& amin, unsigned& amax) {
   if (S != 0 || EXACT) return flux_v<S>(um2, um1, uc, up1, ua, nu, kind);
   const bool pos = ua > 0.f;
   const float u = pos ? um2 : up1, c = pos ? um1 : uc, d = pos ? uc : um1;
@@ -125,7 +129,10 @@ struct Mom3Smem {
   float shy[2][3][M3_TY][32];
 };
 
-template <int S, bool FAST>
+// NB ("no body"): the host knows V ≡ 0 and μ₀ ≡ 1 on every cell (no body was ever measured or uploaded
+// and every direction is periodic, so BC!(μ₀,0) left no zero faces): then f - V = f and V + μ₀·f = f
+// exactly, and the kernel skips those two fields (24 of its 84 B/cell and their address arithmetic).
+template <int S, bool FAST, bool NB>
 __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm) {
   const Lay& l = a.l;
   const int lane = threadIdx.x, ty = threadIdx.y, tid = lane + 32 * ty;
@@ -202,7 +209,8 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
     if (fin) {
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) {
-        fu0[ci] = a.u0c[ci][opv]; fV[ci] = a.Vc[ci][opv]; fm0[ci] = a.m0c[ci][opv];
+        fu0[ci] = a.u0c[ci][opv];
+        if (!NB) { fV[ci] = a.Vc[ci][opv]; fm0[ci] = a.m0c[ci][opv]; }
       }
     }
     float(*cur)[M3_TILE] = sm.ring[k & (M3_RING - 1)];
@@ -216,7 +224,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
     float F[3][3];
     auto fluxes = [&](auto exact_tag) -> bool {
       constexpr bool EX = decltype(exact_tag)::value;
-      float amin = 1.f, amax = 1.f;
+      unsigned amin = 0xffffffffu, amax = 0u;
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) {
 #pragma unroll
@@ -227,7 +235,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
           F[ci][dj] = flux_q<S, EX>(nb[ci][dj][0], nb[ci][dj][1], w[ci][2], nb[ci][dj][2], ua, nu, kind, amin, amax);
         }
       }
-      return !(amin > 1e-30f && amax < 1e38f);
+      return !(amin >= DIV6_LO && amax < DIV6_HI);       // bits-1 >= LO  <=>  |x| > 1e-30 (or x == 0)
     };
     if (fluxes(std::false_type{})) fluxes(std::true_type{});
     float Fxu[3], Fyu[3];
@@ -248,8 +256,13 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
       for (int ci = 0; ci < 3; ++ci) {
         float r = pend[ci] - F[ci][2];
         r += a.acc.v[ci];
-        const float f = fu0[ci] + a.dt * r - fV[ci];         // BDIM! loop 1, Flow.jl:178
-        const float X = fV[ci] + fm0[ci] * f;                // loop 2 with μ₁ ≡ 0, Flow.jl:179
+        float X;
+        if (NB) {
+          X = fu0[ci] + a.dt * r;                            // f - 0, then 0 + 1·f
+        } else {
+          const float f = fu0[ci] + a.dt * r - fV[ci];       // BDIM! loop 1, Flow.jl:178
+          X = fV[ci] + fm0[ci] * f;                          // loop 2 with μ₁ ≡ 0, Flow.jl:179
+        }
         a.unc[ci][opv] = a.corrector ? (w[ci][1] + X) * 0.5f : X;   // scale_u!(½) Flow.jl:209
       }
     }
@@ -277,7 +290,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   cp_async_wait<0>();
 }
 
-template <int S>
+template <int S, bool NB>
 __global__ void __launch_bounds__(32 * M3_TY, 2) k_mom3(const Mom3Args a) {
   pdl_entry();
   __shared__ Mom3Smem sm;
@@ -286,8 +299,8 @@ __global__ void __launch_bounds__(32 * M3_TY, 2) k_mom3(const Mom3Args a) {
   const int px = a.per.p[0] ? 1 : 0, py = a.per.p[1] ? 1 : 0;
   const bool inner = (int)blockIdx.x >= 1 - px && 1 + 31 * (int)blockIdx.x + 31 <= a.l.n0 - 2 + px &&
                      (int)blockIdx.y >= 1 - py && 1 + (M3_TY - 1) * (int)blockIdx.y + (M3_TY - 1) <= a.l.n1 - 2 + py;
-  if (inner) mom3_body_async<S, true>(a, sm);
-  else mom3_body_async<S, false>(a, sm);
+  if (inner) mom3_body_async<S, true, NB>(a, sm);
+  else mom3_body_async<S, false, NB>(a, sm);
 }
 
 // ---- band cells (any μ₁ ≠ 0): exact BDIM with μddn, Flow.jl:20-26,176-180.
