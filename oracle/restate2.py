@@ -1,0 +1,205 @@
+"""Second, independent restatement of the momentum-side loops in plain Python (TEST INFRASTRUCTURE).
+
+SURVEY §8c names the residual risk of the oracle: the C++ restatement (oracle/wl_oracle.cpp) could
+deviate from the Julia semantics.  This file restates the same `@loop`s a second time, written
+directly from the Julia source with Julia's own 1-based CartesianIndex arithmetic (no shared code, no
+shared index conventions with the C++ file), one Python loop per cell, Float32 scalars.  It is only
+usable on tiny grids; tests/test_oracle_restatement2.py compares it with the C++ oracle bit for bit.
+
+Arrays are numpy views in Julia order: a[i-1, j-1(, k-1)(, c-1)] == Julia a[i,j(,k)(,c)]
+(`OracleSim.field(name).T`).  Only tests/ may import this module.
+"""
+import itertools
+
+import numpy as np
+
+f32 = np.float32
+
+
+class J:
+    """1-based view of a numpy array: J(a)[I] with I a tuple of Julia indices."""
+
+    def __init__(self, a):
+        self.a = a
+
+    def __getitem__(self, I):
+        return self.a[tuple(x - 1 for x in I)]
+
+    def __setitem__(self, I, v):
+        self.a[tuple(x - 1 for x in I)] = v
+
+
+def CR(*ranges):      # CartesianIndices((lo:hi, ...)), first index fastest like Julia
+    for I in itertools.product(*[range(lo, hi + 1) for lo, hi in reversed(ranges)]):
+        yield tuple(reversed(I))
+
+
+def d_(j, n):          # δ(j, Val{n}) core.jl:39
+    return tuple(1 if k == j else 0 for k in range(1, n + 1))
+
+
+def plus(I, K, s=1):
+    return tuple(a + s * b for a, b in zip(I, K))
+
+
+def CIj(j, I, k):      # core.jl:31
+    return tuple(k if i == j else I[i - 1] for i in range(1, len(I) + 1))
+
+
+def inside_u(N, j):    # core.jl:55-57
+    return CR(*[(3, N[i - 1] - 1) if i == j else (2, N[i - 1]) for i in range(1, len(N) + 1)])
+
+
+def slice_(N, i, j, low=1):   # core.jl:188-190
+    return CR(*[(i, i) if k == j else (low, N[k - 1]) for k in range(1, len(N) + 1)])
+
+
+def median(a, b, c):   # Flow.jl:27-36
+    if a > b:
+        if b >= c:
+            return b
+        if a > c:
+            return c
+    else:
+        if b <= c:
+            return b
+        if a < c:
+            return c
+    return a
+
+
+def quick(u, c, d):    # Flow.jl:4
+    return median((f32(5) * c + f32(2) * d - u) / f32(6), c, median(f32(10) * c - f32(9) * u, c, d))
+
+
+def vanLeer(u, c, d):  # Flow.jl:5
+    return c if (c <= min(u, d) or c >= max(u, d)) else c + (d - c) * (c - u) / (d - u)
+
+
+def cds(u, c, d):      # Flow.jl:6
+    return (c + d) / f32(2)
+
+
+SCHEME = dict(quick=quick, vanLeer=vanLeer, cds=cds)
+
+
+def conv_diff(r, u, Phi, lam, nu, perdir):
+    """`conv_diff!(r,u,Φ,λ;ν,perdir)` Flow.jl:38-62.  r,u: (N...,n); Φ: (N...)."""
+    r[...] = 0
+    N, n = u.shape[:-1], u.shape[-1]
+    R, U, F = J(r), J(u), J(Phi)
+    nu = f32(nu)
+
+    def phi(a, I, f):                                   # ϕ(a,I,f) Flow.jl:3 ; I carries the component
+        return (f[I] + f[plus(I, d_(a, n + 1), -1)]) / f32(2)
+
+    def dd(a, I, f):                                    # ∂(a,I::CI{d},f::Array{T,d}) Flow.jl:1
+        return f[I] - f[plus(I, d_(a, n + 1), -1)]
+
+    def phiu(a, I, f, ua):                              # ϕu Flow.jl:8
+        e = d_(a, n + 1)
+        if ua > 0:
+            return ua * lam(f[plus(I, e, -2)], f[plus(I, e, -1)], f[I])
+        return ua * lam(f[plus(I, e)], f[I], f[plus(I, e, -1)])
+
+    def phiuP(a, Ip, I, f, ua):                         # ϕuP Flow.jl:9
+        e = d_(a, n + 1)
+        if ua > 0:
+            return ua * lam(f[Ip], f[plus(I, e, -1)], f[I])
+        return ua * lam(f[plus(I, e)], f[I], f[plus(I, e, -1)])
+
+    def phiuL(a, I, f, ua):                             # ϕuL Flow.jl:10
+        e = d_(a, n + 1)
+        if ua > 0:
+            return ua * phi(a, I, f)
+        return ua * lam(f[plus(I, e)], f[I], f[plus(I, e, -1)])
+
+    def phiuR(a, I, f, ua):                             # ϕuR Flow.jl:11
+        e = d_(a, n + 1)
+        if ua < 0:
+            return ua * phi(a, I, f)
+        return ua * lam(f[plus(I, e, -2)], f[plus(I, e, -1)], f[I])
+
+    for i in range(1, n + 1):
+        for j in range(1, n + 1):
+            ej = d_(j, n)
+            if j in perdir:                              # lowerBoundary! Val{true} Flow.jl:60-61
+                for I in slice_(N, 2, j, 2):
+                    Ii = I + (i,)
+                    F[I] = phiuP(j, CIj(j, Ii, N[j - 1] - 2), Ii, U, phi(i, I + (j,), U)) - nu * dd(j, Ii, U)
+                    R[Ii] = R[Ii] + F[I]
+            else:                                        # lowerBoundary! Val{false} Flow.jl:56
+                for I in slice_(N, 2, j, 2):
+                    Ii = I + (i,)
+                    R[Ii] = R[Ii] + (phiuL(j, Ii, U, phi(i, I + (j,), U)) - nu * dd(j, Ii, U))
+            for I in inside_u(N, j):                     # Flow.jl:46-48
+                Ii = I + (i,)
+                F[I] = phiu(j, Ii, U, phi(i, I + (j,), U)) - nu * dd(j, Ii, U)
+                R[Ii] = R[Ii] + F[I]
+            for I in inside_u(N, j):                     # Flow.jl:49
+                Im = plus(I, ej, -1) + (i,)
+                R[Im] = R[Im] - F[I]
+            if j in perdir:                              # upperBoundary! Val{true} Flow.jl:62
+                for I in slice_(N, N[j - 1], j, 2):
+                    Im = plus(I, ej, -1) + (i,)
+                    R[Im] = R[Im] - F[CIj(j, I, 2)]
+            else:                                        # upperBoundary! Val{false} Flow.jl:57
+                for I in slice_(N, N[j - 1], j, 2):
+                    Ii = I + (i,)
+                    Im = plus(I, ej, -1) + (i,)
+                    R[Im] = R[Im] + (-phiuR(j, Ii, U, phi(i, I + (j,), U)) + nu * dd(j, Ii, U))
+
+
+def BDIM(u, u0, f, V, mu0, mu1, dt):
+    """`BDIM!(a)` Flow.jl:176-180 with `μddn` :20-26.  mu1: (N...,n,n)."""
+    N, n = u.shape[:-1], u.shape[-1]
+    dt = f32(dt)
+    f[...] = u0 + dt * f - V                              # all indices
+    Uu, Ff, Vv, M0, M1 = J(u), J(f), J(V), J(mu0), J(mu1)
+    for Ii in CR(*[(2, k - 1) for k in N], (1, n)):        # inside_u(size(p)) core.jl:58
+        I, i = Ii[:-1], Ii[-1]
+        s = f32(0)
+        for j in range(1, n + 1):
+            e = d_(j, n)
+            s = s + M1[I + (i, j)] * (Ff[plus(I, e) + (i,)] - Ff[plus(I, e, -1) + (i,)])
+        Uu[Ii] = Uu[Ii] + (s / f32(2) + Vv[Ii] + M0[Ii] * Ff[Ii])
+
+
+def BC(a, A, saveexit, perdir):
+    """`BC!(a,A,saveexit,perdir)` with a constant tuple A, core.jl:200-219."""
+    N, n = a.shape[:-1], a.shape[-1]
+    Aa = J(a)
+    for i in range(1, n + 1):
+        for j in range(1, n + 1):
+            e = d_(j, n)
+            if j in perdir:
+                for I in slice_(N, 1, j):
+                    Aa[I + (i,)] = Aa[CIj(j, I, N[j - 1] - 1) + (i,)]
+                for I in slice_(N, N[j - 1], j):
+                    Aa[I + (i,)] = Aa[CIj(j, I, 2) + (i,)]
+            elif i == j:
+                for s in (1, 2):
+                    for I in slice_(N, s, j):
+                        Aa[I + (i,)] = f32(A[i - 1])
+                if (not saveexit) or i > 1:
+                    for I in slice_(N, N[j - 1], j):
+                        Aa[I + (i,)] = f32(A[i - 1])
+            else:
+                # `uBC + a[I±δ] - uBC` with a constant tuple: the reference's own test compares the result
+                # with == against the neighbour (test/test_core.jl:24-27), i.e. the copy is exact
+                for I in slice_(N, 1, j):
+                    Aa[I + (i,)] = Aa[plus(I, e) + (i,)]
+                for I in slice_(N, N[j - 1], j):
+                    Aa[I + (i,)] = Aa[plus(I, e, -1) + (i,)]
+
+
+def CFL(u, sigma, nu):
+    """`CFL(a)` Flow.jl:234-244: σ = flux_out inside, then the maximum over the WHOLE σ."""
+    N, n = u.shape[:-1], u.shape[-1]
+    Uu, S = J(u), J(sigma)
+    for I in CR(*[(2, k - 1) for k in N]):
+        s = f32(0)
+        for i in range(1, n + 1):
+            s = s + (max(f32(0), Uu[plus(I, d_(i, n)) + (i,)]) + max(f32(0), -Uu[I + (i,)]))
+        S[I] = s
+    return min(f32(10), f32(1) / (sigma.max() + f32(5) * f32(nu)))

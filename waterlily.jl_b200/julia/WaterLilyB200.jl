@@ -184,6 +184,23 @@ function solver!(b::B200Poisson; kw...)
                      b.h.ptr, n, C_NULL, C_NULL, C_NULL, C_NULL))
     push!(b.n, n[])
 end
+"""
+Single-level counterpart of `Poisson(x,L,z)` (reference src/Poisson.jl:22-39): the same device fields, but
+`solver!` runs the Jacobi-preconditioned `pcg!` loop of src/Poisson.jl:166-186,212-223 (`wl_poisson_solver`).
+Stand-alone solves only (`Poisson_setup`-style use, test/test_poisson.jl:1-26); `mom_step!` always projects
+with the multigrid solver.
+"""
+struct B200PCGPoisson{T} <: AbstractPoisson{T,B200Array{T},B200Array{T}}
+    ml::B200Poisson{T}
+end
+B200PCGPoisson(flow::B200Flow) = B200PCGPoisson(B200Poisson(flow))
+Base.getproperty(p::B200PCGPoisson, s::Symbol) = s === :ml ? getfield(p, :ml) : getproperty(getfield(p, :ml), s)
+update!(p::B200PCGPoisson) = update!(p.ml)
+function solver!(p::B200PCGPoisson; itmx=1e3, kw...)
+    n = Ref{Int32}(0)
+    check(p.h, ccall((:wl_poisson_solver, LIB), Cint, (Ptr{Cvoid}, Int32, Ref{Int32}), p.h.ptr, Int32(min(itmx, typemax(Int32))), n))
+    push!(p.n, n[])
+end
 function CFL(a::B200Flow; Δt_max=10)
     dt = Ref{Cfloat}(0)
     check(a.h, ccall((:wl_cfl, LIB), Cint, (Ptr{Cvoid}, Ref{Cfloat}), a.h.ptr, dt)); min(Δt_max, dt[])
