@@ -203,3 +203,148 @@ def CFL(u, sigma, nu):
             s = s + (max(f32(0), Uu[plus(I, d_(i, n)) + (i,)]) + max(f32(0), -Uu[I + (i,)]))
         S[I] = s
     return min(f32(10), f32(1) / (sigma.max() + f32(5) * f32(nu)))
+
+
+# ---------------------------------------------------------------------------------------------------
+# Pressure side: Poisson.jl:43-148, MultiLevelPoisson.jl:1-50,88-101 (one level = dict of Julia-order arrays)
+
+def inside(a):         # core.jl:47
+    return CR(*[(2, k - 1) for k in a.shape])
+
+
+def perBC(a, perdir):  # core.jl:239-243
+    N = a.shape
+    A = J(a)
+    for j in perdir:
+        for I in slice_(N, 1, j):
+            A[I] = A[CIj(j, I, N[j - 1] - 1)]
+        for I in slice_(N, N[j - 1], j):
+            A[I] = A[CIj(j, I, 2)]
+
+
+def diag(I, L):        # Poisson.jl:49-55
+    d = len(I)
+    s = f32(0)
+    for i in range(1, d + 1):
+        s = s - (L[I + (i,)] + L[plus(I, d_(i, d)) + (i,)])
+    return s
+
+
+def set_diag(p):       # Poisson.jl:43-46
+    D, iD, L = J(p["D"]), J(p["iD"]), J(p["L"])
+    for I in inside(p["D"]):
+        D[I] = diag(I, L)
+    for I in inside(p["D"]):
+        iD[I] = D[I] if D[I] == 0 else f32(1) / D[I]
+
+
+def mult(I, L, D, x):  # Poisson.jl:70-76
+    d = len(I)
+    s = x[I] * D[I]
+    for i in range(1, d + 1):
+        e = d_(i, d)
+        s = s + (x[plus(I, e, -1)] * L[I + (i,)] + x[plus(I, e)] * L[plus(I, e) + (i,)])
+    return s
+
+
+def residual(p):       # Poisson.jl:92-98
+    perBC(p["x"], p["perdir"])
+    r, iD, z, L, D, x = (J(p[k]) for k in ("r", "iD", "z", "L", "D", "x"))
+    for I in inside(p["r"]):
+        r[I] = f32(0) if iD[I] == 0 else z[I] - mult(I, L, D, x)
+    n_in = int(np.prod([k - 2 for k in p["r"].shape]))
+    s = f32(p["r"].sum(dtype=np.float64)) / f32(n_in)
+    if abs(s) <= 2 * np.finfo(np.float32).eps:
+        return
+    for I in inside(p["r"]):
+        r[I] = r[I] - s
+
+
+def increment(p, w=1):  # Poisson.jl:100-104
+    w = f32(w)
+    perBC(p["eps"], p["perdir"])
+    r, x, e, L, D = (J(p[k]) for k in ("r", "x", "eps", "L", "D"))
+    for I in inside(p["x"]):
+        r[I] = r[I] - w * mult(I, L, D, e)
+        x[I] = x[I] + w * e[I]
+
+
+def jacobi(p):         # Poisson.jl:111-114 (it=1, ω=1)
+    e, r, iD = J(p["eps"]), J(p["r"]), J(p["iD"])
+    for I in inside(p["eps"]):
+        e[I] = r[I] * iD[I]
+    increment(p, 1)
+
+
+def gauss_seidel_rb(p, it=4, w=1):   # Poisson.jl:116-148
+    e, r, iD, L = J(p["eps"]), J(p["r"]), J(p["iD"]), J(p["L"])
+    for I in inside(p["eps"]):
+        e[I] = r[I] * iD[I]
+    perBC(p["eps"], p["perdir"])
+    sh = p["eps"].shape
+    d = len(sh)
+    half = [(2, sh[i] // 2) if i == d - 1 else (2, sh[i] - 1) for i in range(d)]   # half_rangek :130-132
+    for k0 in range(1, it + 1):
+        for Iv in CR(*half):
+            k = 2 * Iv[-1] - 1 - (sum(Iv[:-1]) + k0) % 2
+            I = Iv[:-1] + (k,)
+            s = r[I]                                                               # gauss :116-122
+            for i in range(1, d + 1):
+                ei = d_(i, d)
+                s = s - (e[plus(I, ei, -1)] * L[I + (i,)] + e[plus(I, ei)] * L[plus(I, ei) + (i,)])
+            e[I] = s * iD[I]
+    increment(p, w)
+
+
+def coarsen_mask(fine, coarse):     # MultiLevelPoisson.jl:29
+    return tuple(coarse.shape[j] < fine.shape[j] for j in range(fine.ndim))
+
+
+def up(I, c):          # MultiLevelPoisson.jl:6
+    return CR(*[(2 * I[j] - 2, 2 * I[j] - 1) if c[j] else (I[j], I[j]) for j in range(len(I))])
+
+
+def down(I, c):        # MultiLevelPoisson.jl:7
+    return tuple((I[j] + 2) // 2 if c[j] else I[j] for j in range(len(I)))
+
+
+def restrict(a, b, c):  # restrict!(a,b,c) MultiLevelPoisson.jl:13-19,49
+    A, B = J(a), J(b)
+    for I in inside(a):
+        s = f32(0)
+        for K in up(I, c):
+            s = s + B[K]
+        A[I] = s
+
+
+def prolongate(a, b, c):  # MultiLevelPoisson.jl:50
+    A, B = J(a), J(b)
+    for I in inside(a):
+        A[I] = B[down(I, c)]
+
+
+def restrictL(a, b, c, perdir):   # MultiLevelPoisson.jl:9-11,20-26,42-48
+    Na, n = a.shape[:-1], a.shape[-1]
+    A, B = J(a), J(b)
+    for i in range(1, n + 1):
+        for I in CR(*[(2, k - 1) for k in Na]):
+            rng = [((2 * I[j] - 2, 2 * I[j] - 2) if c[i - 1] else (I[j], I[j])) if j == i - 1 else
+                   ((2 * I[j] - 2, 2 * I[j] - 1) if c[j] else (I[j], I[j])) for j in range(n)]
+            s = f32(0)
+            for K in CR(*rng):
+                s = s + B[K + (i,)]
+            A[I + (i,)] = s / f32(2) if c[i - 1] else s
+    BC(a, (0.0,) * n, False, perdir)
+
+
+def vcycle(levels, l=1, w=1):     # Vcycle!(ml;l,ω) MultiLevelPoisson.jl:88-101
+    fine, coarse = levels[l - 1], levels[l]
+    c = coarsen_mask(fine["x"], coarse["x"])
+    jacobi(fine)
+    restrict(coarse["r"], fine["r"], c)
+    coarse["x"][...] = 0
+    if l + 1 < len(levels):
+        vcycle(levels, l + 1, w)
+    gauss_seidel_rb(coarse, 4, w)
+    prolongate(fine["eps"], coarse["x"], c)
+    increment(fine, w)

@@ -80,3 +80,61 @@ def test_cfl_two_restatements(dims):
     sig[(-1,) * len(dims)] = 0.0
     s2[(-1,) * len(dims)] = 0.0
     assert np.float32(sim.cfl()) == r2.CFL(u.T, s2.T, 0.03)
+
+
+# ------------------------------------------------------------------------------------------ pressure side
+def _levels(sim):
+    """Copies of every level's arrays in Julia order (what restate2 works on)."""
+    per = tuple(d + 1 for d in range(sim.D) if sim.cfg.perdir[d])
+    return [dict({k: sim.field(k, l).copy().T for k in ("x", "r", "eps", "z", "L", "D", "iD")}, perdir=per)
+            for l in range(sim.nlevels)]
+
+
+def _same(sim, lev, names, l):
+    for k in names:
+        assert np.array_equal(sim.field(k, l), lev[l][k].T), (k, l)
+
+
+MG_CASES = [((12, 8), (), dict(kind="sphere", center=(5, 4), radius=2.5)),
+            ((8, 12), (1,), None),
+            ((8, 8, 4), (3,), dict(kind="sphere", center=(4, 4, 2), radius=2.0)),
+            ((8, 4, 6), (1, 2, 3), None)]
+
+
+@pytest.mark.parametrize("dims,perdir,body", MG_CASES)
+def test_poisson_ops_two_restatements(dims, perdir, body):
+    """Level construction (restrictL!, set_diag!) and every operator of the V-cycle, one at a time and as a
+    whole `Vcycle!`, on a variable-coefficient hierarchy incl. semi-coarsened and odd-sized levels."""
+    b = wo.make_body(**body) if body else None
+    sim = wo.OracleSim(dims, (0.0,) * len(dims), perdir=perdir, body=b)
+    rng = np.random.default_rng(21)
+    inner = tuple(slice(1, -1) for _ in dims)
+    for nm in ("x", "z"):
+        a = sim.field(nm, 0)
+        a[...] = 0
+        a[inner] = rng.standard_normal(a[inner].shape).astype(np.float32)
+    lev = _levels(sim)
+    # hierarchy: coarse L from the fine L, D and iD on every level
+    for l in range(1, sim.nlevels):
+        c = r2.coarsen_mask(lev[l - 1]["x"], lev[l]["x"])
+        a = np.zeros_like(lev[l]["L"])
+        r2.restrictL(a, lev[l - 1]["L"], c, lev[l]["perdir"])
+        assert np.array_equal(a, lev[l]["L"]), l
+    for l in range(sim.nlevels):
+        p = dict(lev[l], D=np.zeros_like(lev[l]["D"]), iD=np.zeros_like(lev[l]["iD"]))
+        r2.set_diag(p)
+        assert np.array_equal(p["D"], lev[l]["D"]) and np.array_equal(p["iD"], lev[l]["iD"]), l
+    # single operators on level 1
+    sim.lib.wlo_op_residual(sim.h, 0); r2.residual(lev[0]); _same(sim, lev, ("r", "x"), 0)
+    sim.lib.wlo_op_jacobi(sim.h, 0); r2.jacobi(lev[0]); _same(sim, lev, ("r", "x", "eps"), 0)
+    sim.lib.wlo_op_smooth(sim.h, 0, 0.9); r2.gauss_seidel_rb(lev[0], 4, 0.9); _same(sim, lev, ("r", "x", "eps"), 0)
+    c = r2.coarsen_mask(lev[0]["x"], lev[1]["x"])
+    sim.lib.wlo_op_restrict(sim.h, 0); r2.restrict(lev[1]["r"], lev[0]["r"], c); _same(sim, lev, ("r",), 1)
+    a = sim.field("x", 1)
+    a[inner] = rng.standard_normal(a[inner].shape).astype(np.float32)
+    lev[1]["x"][...] = a.T
+    sim.lib.wlo_op_prolongate(sim.h, 0); r2.prolongate(lev[0]["eps"], lev[1]["x"], c); _same(sim, lev, ("eps",), 0)
+    # one whole V-cycle
+    sim.lib.wlo_op_vcycle(sim.h, 0.95); r2.vcycle(lev, 1, 0.95)
+    for l in range(sim.nlevels):
+        _same(sim, lev, ("x", "r", "eps"), l)
