@@ -884,11 +884,14 @@ void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, c
     const long long oc = l.cstride * c;
     a.uac[c] = a.ua + oc; a.u0c[c] = a.u0 + oc; a.Vc[c] = a.V + oc; a.m0c[c] = a.mu0 + oc; a.unc[c] = a.un + oc;
   }
+  // 32-column tiles (the block's last row supplies lane 31's upper x faces): opt-in while it is being measured
+  static const bool w32 = getenv("WL_M3_W32") != nullptr && atoi(getenv("WL_M3_W32")) != 0;
+  const int bw = w32 ? 32 : 31;
   // march length: the chunk count that minimises waves x (planes per chunk + ~4 planes of pipeline fill and
   // the extra flux plane), a wave being 2 blocks on each of the 148 SMs (measured on 128³ and 512x256²:
   // a grid just under a whole number of waves beats a finer split by up to 8%)
   {
-    const long long bxy = (long long)((l.n0 - 2 + 30) / 31) * ((l.n1 - 2 + M3_TY - 2) / (M3_TY - 1));
+    const long long bxy = (long long)((l.n0 - 2 + bw - 1) / bw) * ((l.n1 - 2 + M3_TY - 2) / (M3_TY - 1));
     const int nz = l.n2 - 2;
     long long best = -1;
     a.KZ = nz;
@@ -900,21 +903,21 @@ void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, c
     }
   }
   { static const int kz_env = getenv("WL_M3_KZ") ? atoi(getenv("WL_M3_KZ")) : 0; if (kz_env >= 2) a.KZ = kz_env; }
-  dim3 g((l.n0 - 2 + 30) / 31, (l.n1 - 2 + M3_TY - 2) / (M3_TY - 1), (l.n2 - 2 + a.KZ - 1) / a.KZ);
+  dim3 g((l.n0 - 2 + bw - 1) / bw, (l.n1 - 2 + M3_TY - 2) / (M3_TY - 1), (l.n2 - 2 + a.KZ - 1) / a.KZ);
   dim3 b(32, M3_TY, 1);
   const int sc = s->cfg.scheme;
   // body-free, fully periodic flow: V ≡ 0 and μ₀ ≡ 1 everywhere, the kernel need not read them
   static const bool nb_off = getenv("WL_NO_NOBODY") != nullptr;
   const bool nb = !nb_off && s->free_flow && s->per_glob.p[0] && s->per_glob.p[1] && s->per_glob.p[2];
-  if (nb) {
-    if (sc == 0) LAUNCH(s, (k_mom3<0, true>), g, b, a);
-    else if (sc == 1) LAUNCH(s, (k_mom3<1, true>), g, b, a);
-    else LAUNCH(s, (k_mom3<2, true>), g, b, a);
-  } else {
-    if (sc == 0) LAUNCH(s, (k_mom3<0, false>), g, b, a);
-    else if (sc == 1) LAUNCH(s, (k_mom3<1, false>), g, b, a);
-    else LAUNCH(s, (k_mom3<2, false>), g, b, a);
-  }
+#define WL_MOM3_LAUNCH(NB, W)                                        \
+  do {                                                               \
+    if (sc == 0) LAUNCH(s, (k_mom3<0, NB, W>), g, b, a);             \
+    else if (sc == 1) LAUNCH(s, (k_mom3<1, NB, W>), g, b, a);        \
+    else LAUNCH(s, (k_mom3<2, NB, W>), g, b, a);                     \
+  } while (0)
+  if (nb) { if (w32) WL_MOM3_LAUNCH(true, true); else WL_MOM3_LAUNCH(true, false); }
+  else { if (w32) WL_MOM3_LAUNCH(false, true); else WL_MOM3_LAUNCH(false, false); }
+#undef WL_MOM3_LAUNCH
   PatchArgs pa{};
   pa.m.l = s->lay; pa.m.ua = ua.base; pa.m.u0 = u0.base; pa.m.V = s->V.base; pa.m.f = nullptr;
   pa.m.per = s->per; pa.m.nu = s->cfg.nu; pa.m.dt = s->dt; pa.m.acc = a.acc;

@@ -13,6 +13,16 @@
 #pragma once
 #include "wl_kernels_mg2.cuh"
 
+// resident blocks per SM the register allocation is held to: K-UP and K-PROJ fit 64 registers without
+// spilling (50 % occupancy instead of 37.5 %; ncu shows them latency-bound: 60 % DRAM at 32 % warps active),
+// K-DOWN and K-DIVRES would spill 40-80 bytes and keep the 3-block allocation
+#ifndef WL_MG4_MINB_A
+#define WL_MG4_MINB_A 4
+#endif
+#ifndef WL_MG4_MINB_B
+#define WL_MG4_MINB_B 3
+#endif
+
 namespace wl {
 
 struct F4 { float v[4]; };
@@ -193,7 +203,7 @@ __global__ void __launch_bounds__(256) k_cfl4(const CflArgs a) {
 }
 
 // ---------------------------------------------------------------- K-DIVRES, 4 cells per thread (see k_divres)
-__global__ void __launch_bounds__(256) k_divres4(const DivResArgs a) {
+__global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_divres4(const DivResArgs a) {
   pdl_entry();
   const Lay& l = a.l;
   WL_QUAD_FROM_BLOCK(l)
@@ -240,7 +250,7 @@ __global__ void __launch_bounds__(256) k_divres4(const DivResArgs a) {
 }
 
 // ---------------------------------------------------------------- K-PROJ, 4 cells per thread (see k_proj)
-__global__ void __launch_bounds__(256) k_proj4(const ProjArgs2 a) {
+__global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_proj4(const ProjArgs2 a) {
   pdl_entry();
   const Lay& l = a.l;
   WL_QUAD_FROM_BLOCK(l)
@@ -289,7 +299,7 @@ __global__ void __launch_bounds__(256) k_proj4(const ProjArgs2 a) {
 
 // ---------------------------------------------------------------- K-UP, 4 cells per thread (see k_up)
 // prolongate! + perBC! + increment!(ω) (+ ϵ = r·iD for the smoother that follows).  Any coarsening mask.
-__global__ void __launch_bounds__(256) k_up4(const UpArgs a) {
+__global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_up4(const UpArgs a) {
   pdl_entry();
   const Lay& l = a.f.l;
   const Lay& lc = a.c.l;
@@ -350,7 +360,7 @@ __global__ void __launch_bounds__(256) k_up4(const UpArgs a) {
 // ---------------------------------------------------------------- K-DOWN, 4 cells per thread (see k_down)
 // Jacobi! (ϵ=r·iD, perBC!, increment! with ω=1) + restrict! + fill!(coarse.x,0), for levels coarsened
 // in every direction.  blockDim (32,4,2): the block's 128x4x2 cells are the children of 64x2x1 coarse cells.
-__global__ void __launch_bounds__(256) k_down4(const DownArgs a) {
+__global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_down4(const DownArgs a) {
   pdl_entry();
   __shared__ float tile[2][4][128];
   const Lay& l = a.f.l;

@@ -127,23 +127,30 @@ constexpr int M3_RING = 4;
 struct Mom3Smem {
   float ring[M3_RING][3][M3_TILE];
   float shy[2][3][M3_TY][32];
+  float shx[2][3][M3_TY];          // W32: x-face fluxes of the column right of the block, per row
 };
 
 // NB ("no body"): the host knows V ≡ 0 and μ₀ ≡ 1 on every cell (no body was ever measured or uploaded
 // and every direction is periodic, so BC!(μ₀,0) left no zero faces): then f - V = f and V + μ₀·f = f
 // exactly, and the kernel skips those two fields (24 of its 84 B/cell and their address arithmetic).
-template <int S, bool FAST, bool NB>
+// W32: the block owns 32 columns instead of 31.  Lane 31 has no lane+1 to take its upper x face from; the
+// block's last row (a whole warp that only supplies y faces, six of its nine fluxes are unused) evaluates
+// those 3x7 faces at column i0+32 -- the same expression on the same staged values as lane 0 of the next
+// block -- and hands them over through shared memory.  Power-of-two grids then tile exactly (128 = 4x32
+// instead of 5x31 columns) and every lane of the seven output rows produces a cell.
+template <int S, bool FAST, bool NB, bool W32>
 __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm) {
   const Lay& l = a.l;
   const int lane = threadIdx.x, ty = threadIdx.y, tid = lane + 32 * ty;
   const int N0 = l.n0, N1 = l.n1, N2 = l.n2;
   const int pitch = l.pitch, plane = l.plane;
-  const int i0 = 1 + 31 * blockIdx.x, j0 = 1 + (M3_TY - 1) * blockIdx.y;
+  constexpr int BW = W32 ? 32 : 31;
+  const int i0 = 1 + BW * blockIdx.x, j0 = 1 + (M3_TY - 1) * blockIdx.y;
   const int i_raw = i0 + lane, j_raw = j0 + ty;
   const int i = FAST ? i_raw : min(i_raw, N0 - 1), j = FAST ? j_raw : min(j_raw, N1 - 1);
   const int k0 = 1 + a.KZ * blockIdx.z;
   const int kend = min(k0 + a.KZ, N2 - 1);
-  const bool out_ij = lane < 31 && ty < M3_TY - 1 && (FAST || (i_raw <= N0 - 2 && j_raw <= N1 - 2));
+  const bool out_ij = lane < BW && ty < M3_TY - 1 && (FAST || (i_raw <= N0 - 2 && j_raw <= N1 - 2));
   const int oij = i + pitch * j;
   const bool p0 = a.per.p[0] != 0, p1 = a.per.p[1] != 0, p2 = a.per.p[2] != 0;
   const int klo = a.per.zlo ? -1 : 0, khi = a.per.zhi ? N2 : N2 - 1;   // readable plane range (slab halos)
@@ -174,6 +181,13 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
     }
   };
   const int tc = (ty + 2) * M3_TW + lane + 2;     // own position in the tile
+  // W32: lane = 7·c + r of the last row evaluates the x face of component c at column i0+32, row j0+r
+  const bool xact = W32 && ty == M3_TY - 1 && lane < 3 * (M3_TY - 1);
+  const int xr = lane % (M3_TY - 1), xc = min(lane / (M3_TY - 1), 2);
+  const int pX = (xr + 2) * M3_TW + 34;           // tile position of (i0+32, j0+xr)
+  const int pA = xc == 0 ? pX - 1 : pX - M3_TW;   // the other operand of the advecting mean (xc == 2: previous plane)
+  const int kxX = (FAST || p0) ? 0 : (i0 + 32 == N0 - 1 ? 3 : 0);
+  float xprev = 0.f;                              // u_x(i0+32, j0+xr) one plane below
 
   stage(k0); stage(k0 + 1); cp_async_commit();
   stage(k0 + 2); cp_async_commit();
@@ -183,6 +197,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
     w[c][0] = U[c][oij + plane * ((p2 && k0 == 1) ? N2 - 3 : max(k0 - 2, klo))];
     w[c][1] = U[c][oij + plane * (k0 - 1)];
   }
+  if (xact) xprev = U[0][fold(i0 + 32, N0, p0) + pitch * fold(j0 + xr, N1, p1) + plane * (k0 - 1)];
   cp_async_wait<1>();
   __syncthreads();
 #pragma unroll
@@ -241,6 +256,16 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
     float Fxu[3], Fyu[3];
     if (!lastp) {
       const int buf = k & 1;
+      if (W32 && ty == M3_TY - 1) {                          // one warp: the faces right of the block
+        if (xact) {
+          const float* cx = cur[xc];
+          const float ux0 = cur[0][pX];
+          const float ux1 = xc == 2 ? xprev : cur[0][pA];
+          const float uaX = (ux0 + ux1) / 2.f;
+          sm.shx[buf][xc][xr] = flux_v<S>(cx[pX - 2], cx[pX - 1], cx[pX], cx[pX + 1], uaX, nu, kxX);
+          xprev = ux0;
+        }
+      }
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) {
         Fxu[ci] = __shfl_down_sync(0xffffffffu, F[ci][0], 1);
@@ -250,6 +275,10 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
       __syncthreads();
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) Fyu[ci] = sm.shy[buf][ci][min(ty + 1, M3_TY - 1)][lane];
+      if (W32 && lane == 31) {
+#pragma unroll
+        for (int ci = 0; ci < 3; ++ci) Fxu[ci] = sm.shx[buf][ci][min(ty, M3_TY - 2)];
+      }
     }
     if (fin) {                                               // finalise cell (i,j,k-1)
 #pragma unroll
@@ -290,17 +319,21 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   cp_async_wait<0>();
 }
 
-template <int S, bool NB>
+template <int S, bool NB, bool W32>
 __global__ void __launch_bounds__(32 * M3_TY, 2) k_mom3(const Mom3Args a) {
   pdl_entry();
   __shared__ Mom3Smem sm;
   // FAST: every thread of the block sits on an ordinary cell with ordinary faces (in a periodic direction
   // that is every block whose last lane / row still lies inside the array)
   const int px = a.per.p[0] ? 1 : 0, py = a.per.p[1] ? 1 : 0;
-  const bool inner = (int)blockIdx.x >= 1 - px && 1 + 31 * (int)blockIdx.x + 31 <= a.l.n0 - 2 + px &&
+  // (W32: lane 31 is an output cell, so it must be a real cell, and the face at column i0+32 an ordinary one)
+  const bool inner_x = W32 ? ((int)blockIdx.x >= 1 - px && 1 + 32 * (int)blockIdx.x + 31 <= a.l.n0 - 2 &&
+                              1 + 32 * (int)blockIdx.x + 32 <= a.l.n0 - 2 + px)
+                           : ((int)blockIdx.x >= 1 - px && 1 + 31 * (int)blockIdx.x + 31 <= a.l.n0 - 2 + px);
+  const bool inner = inner_x &&
                      (int)blockIdx.y >= 1 - py && 1 + (M3_TY - 1) * (int)blockIdx.y + (M3_TY - 1) <= a.l.n1 - 2 + py;
-  if (inner) mom3_body_async<S, true, NB>(a, sm);
-  else mom3_body_async<S, false, NB>(a, sm);
+  if (inner) mom3_body_async<S, true, NB, W32>(a, sm);
+  else mom3_body_async<S, false, NB, W32>(a, sm);
 }
 
 // ---- band cells (any μ₁ ≠ 0): exact BDIM with μddn, Flow.jl:20-26,176-180.
