@@ -231,6 +231,28 @@ def test_config_A_circle_2d(wl):
     assert np.allclose(f_gpu, f_ref, rtol=1e-4, atol=1e-4 * np.abs(f_ref).max()), (f_gpu, f_ref)
 
 
+def _golden_cases():
+    import os, sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import make_golden as mg
+    return mg
+
+
+@pytest.mark.parametrize("name", ["A_circle_96x64", "B_tgv_16", "C_sphere_32x16x16_exit", "D_cylinder_32x32x8"])
+def test_cuda_matches_golden_fixtures(wl, name):
+    """The CUDA path through the C ABI against the committed golden vectors (tests/golden/*.npz): u, p,
+    the Δt history, the Poisson iteration log and pressure_force, at north_star's tolerance or tighter."""
+    from test_golden import compare
+    mg = _golden_cases()
+    kw, nsteps, remeasure = mg.cases()[name]
+    dims, uBC, L, body, rest = mg.build(wl, lambda **b: wl.AutoBody(**b), kw)
+    sim = wl.Simulation(dims, uBC, L, body=body, **rest)
+    for _ in range(nsteps):
+        sim.sim_step(remeasure=remeasure)
+    force = sim.pressure_force() if body is not None else np.zeros(len(dims))
+    compare(name, sim.flow.u, sim.flow.p, sim.flow.Δt, sim.pois.n, force)
+
+
 def tgv3d(i, x, k):
     if i == 1:
         return -np.sin(k * x[0]) * np.cos(k * x[1]) * np.cos(k * x[2])

@@ -884,8 +884,9 @@ void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, c
     const long long oc = l.cstride * c;
     a.uac[c] = a.ua + oc; a.u0c[c] = a.u0 + oc; a.Vc[c] = a.V + oc; a.m0c[c] = a.mu0 + oc; a.unc[c] = a.un + oc;
   }
-  // 32-column tiles (the block's last row supplies lane 31's upper x faces): opt-in while it is being measured
-  static const bool w32 = getenv("WL_M3_W32") != nullptr && atoi(getenv("WL_M3_W32")) != 0;
+  // 32-column tiles (the block's last row supplies lane 31's upper x faces); WL_M3_W32=0 selects the 31-column
+  // tiling.  Measured (profiles/r1_v14_kmom_march_sweep.tsv): TGV 128³ 67.3 -> 58.7 us, sphere 512x256² 810 -> 795 us.
+  static const bool w32 = !(getenv("WL_M3_W32") != nullptr && atoi(getenv("WL_M3_W32")) == 0);
   const int bw = w32 ? 32 : 31;
   // march length: the chunk count that minimises waves x (planes per chunk + ~4 planes of pipeline fill and
   // the extra flux plane), a wave being 2 blocks on each of the 148 SMs (measured on 128³ and 512x256²:
@@ -895,7 +896,9 @@ void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, c
     const int nz = l.n2 - 2;
     long long best = -1;
     a.KZ = nz;
-    for (int n = 1; n <= (nz + 3) / 4; ++n) {
+    // chunks longer than 64 planes lose more to the ragged finish of the last blocks than they save in
+    // pipeline fill (sphere 512x256², 32-column tiles, planes per chunk -> us: 256 848, 128 821, 64 795, 43 786)
+    for (int n = (nz + 63) / 64; n <= (nz + 3) / 4; ++n) {
       const int kz = (nz + n - 1) / n;
       const long long chunks = (nz + kz - 1) / kz;
       const long long cost = ((bxy * chunks + 295) / 296) * (kz + 4);

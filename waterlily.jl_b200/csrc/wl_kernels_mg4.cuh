@@ -13,9 +13,10 @@
 #pragma once
 #include "wl_kernels_mg2.cuh"
 
-// resident blocks per SM the register allocation is held to: K-UP and K-PROJ fit 64 registers without
-// spilling (50 % occupancy instead of 37.5 %; ncu shows them latency-bound: 60 % DRAM at 32 % warps active),
-// K-DOWN and K-DIVRES would spill 40-80 bytes and keep the 3-block allocation
+// resident blocks per SM the register allocation is held to.  K-UP fits 64 registers without spilling (50 %
+// occupancy instead of 37.5 %; ncu showed it latency-bound, 60 % DRAM at 32 % warps active): 54.7 -> 51.2 us
+// per launch averaged over the levels of config C.  K-PROJ is already DRAM-bound (no gain), K-DOWN and
+// K-DIVRES would spill 40-80 bytes (measured 40 % and 4 % slower): they keep the 3-block allocation
 #ifndef WL_MG4_MINB_A
 #define WL_MG4_MINB_A 4
 #endif
@@ -250,7 +251,7 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_divres4(const DivResArgs
 }
 
 // ---------------------------------------------------------------- K-PROJ, 4 cells per thread (see k_proj)
-__global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_proj4(const ProjArgs2 a) {
+__global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_proj4(const ProjArgs2 a) {
   pdl_entry();
   const Lay& l = a.l;
   WL_QUAD_FROM_BLOCK(l)
