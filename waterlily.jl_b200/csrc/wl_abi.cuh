@@ -371,6 +371,9 @@ void wl_destroy(wl_sim* s) {
   free_field(s->u); free_field(s->u0); free_field(s->f); free_field(s->p);
   free_field(s->sigma); free_field(s->V); free_field(s->mu0); free_field(s->mu1); free_field(s->w);
   if (s->band_list) cudaFree(s->band_list);
+  if (s->band_list2) cudaFree(s->band_list2);
+  if (s->band_mark) cudaFree(s->band_mark);
+  if (s->band_count2) cudaFree(s->band_count2);
   if (s->band_count) cudaFree(s->band_count);
   if (s->redw.psum) cudaFree(s->redw.psum);
   if (s->redw.pmax) cudaFree(s->redw.pmax);

@@ -99,6 +99,10 @@ struct wl_sim {
   int* band_list = nullptr;   // interior cells with μ₁ ≠ 0 (patched after K-MOM)
   int* band_count = nullptr;
   int band_cap = 0;
+  int* band_mark = nullptr;   // per cell: epoch of the last list2 build that took it (de-duplication)
+  int* band_list2 = nullptr;  // band cells and their face neighbours: the cells whose f the patch needs
+  int* band_count2 = nullptr;
+  int band_cap2 = 0, band_epoch = 0;
   bool band_dirty = false;
   bool free_flow = true;      // V ≡ 0, μ₀ ≡ 1, μ₁ ≡ 0 as the constructor left them (no measure!, no upload of them)
   std::vector<Level> lv;
@@ -870,6 +874,23 @@ int band_rebuild(wl_sim* s) {
     s->band_cap = n + n / 4 + 1024;
     WL_CUDA(s, cudaMalloc(&s->band_list, sizeof(int) * (size_t)s->band_cap));
   }
+  // the cells whose f the two-pass patch needs: the band and its face neighbours, each once
+  if (s->band_cap > 0) {
+    if (!s->band_mark) {
+      WL_CUDA(s, cudaMalloc(&s->band_mark, sizeof(int) * (size_t)s->lay.cstride));
+      WL_CUDA(s, cudaMemsetAsync(s->band_mark, 0, sizeof(int) * (size_t)s->lay.cstride, s->st));
+      WL_CUDA(s, cudaMalloc(&s->band_count2, sizeof(int)));
+    }
+    if (s->band_cap2 < 7 * s->band_cap) {
+      if (s->band_list2) cudaFree(s->band_list2);
+      s->band_cap2 = 7 * s->band_cap;
+      WL_CUDA(s, cudaMalloc(&s->band_list2, sizeof(int) * (size_t)s->band_cap2));
+    }
+    WL_CUDA(s, cudaMemsetAsync(s->band_count2, 0, sizeof(int), s->st));
+    Band2Args b{s->lay, s->band_list, s->band_count, s->band_cap, s->band_mark, ++s->band_epoch,
+                s->band_list2, s->band_count2, s->band_cap2};
+    LAUNCH(s, k_band_nbrs, dim3(592), dim3(256), b);
+  }
   s->band_dirty = false;
   return WL_OK;
 }
@@ -926,10 +947,17 @@ void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, c
   pa.m.per = s->per; pa.m.nu = s->cfg.nu; pa.m.dt = s->dt; pa.m.acc = a.acc;
   pa.mu0 = s->mu0.base; pa.mu1 = s->mu1.base; pa.un = out.base;
   pa.list = s->band_list; pa.count = s->band_count; pa.cap = s->band_cap; pa.corrector = corrector;
-  if (s->band_cap > 0) {
+  static const bool patch1 = getenv("WL_PATCH_1PASS") != nullptr;      // the one-warp-per-cell kernel
+  if (s->band_cap > 0 && (patch1 || !s->band_list2)) {
     if (sc == 0) LAUNCH(s, k_mom_patch<0>, dim3(1184), dim3(128), pa);
     else if (sc == 1) LAUNCH(s, k_mom_patch<1>, dim3(1184), dim3(128), pa);
     else LAUNCH(s, k_mom_patch<2>, dim3(1184), dim3(128), pa);
+  } else if (s->band_cap > 0) {
+    pa.m.f = s->f.base;
+    if (sc == 0) LAUNCH(s, k_patch_f<0>, dim3(1184), dim3(128), pa, s->band_list2, s->band_count2, s->band_cap2);
+    else if (sc == 1) LAUNCH(s, k_patch_f<1>, dim3(1184), dim3(128), pa, s->band_list2, s->band_count2, s->band_cap2);
+    else LAUNCH(s, k_patch_f<2>, dim3(1184), dim3(128), pa, s->band_list2, s->band_count2, s->band_cap2);
+    LAUNCH(s, k_patch_apply, dim3(1184), dim3(128), pa);
   }
   if (s->cfg.exitBC) {
     ExitCopyArgs e{s->lay, ua.base, out.base};

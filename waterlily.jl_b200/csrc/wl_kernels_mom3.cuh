@@ -381,6 +381,54 @@ __global__ void __launch_bounds__(128) k_mom_patch(const PatchArgs a) {
   }
 }
 
+// ---- band patch in two passes (default).  The one-warp-per-cell kernel above evaluates every f value up to
+// seven times (a band cell and its six neighbours are mostly band cells themselves): 141 us per call on the
+// sphere of config C, 521 us on the cylinder of config D.  Here the cells whose f is needed -- the band and its
+// face neighbours, de-duplicated once per measure! into `list2` -- get f[I,ci] exactly once (K-PATCH-F, one thread
+// per cell and component, written to the otherwise idle flow.f), then one thread per band cell and component
+// applies μddn (K-PATCH-APPLY).  Same rhs_f, same summation order: bit-identical to k_mom_patch.
+struct Band2Args { Lay l; const int* list; const int* count; int cap; int* mark; int epoch; int* list2; int* count2; int cap2; };
+__global__ void __launch_bounds__(256) k_band_nbrs(const Band2Args a) {
+  pdl_entry();
+  const int n = min(*a.count, a.cap);
+  const int st[3] = {1, a.l.pitch, a.l.plane};
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < 7 * n; t += gridDim.x * blockDim.x) {
+    const int q = t / 7, m = t - 7 * q;
+    const int o = a.list[q] + (m == 0 ? 0 : ((m & 1) ? st[(m - 1) >> 1] : -st[(m - 1) >> 1]));
+    if (atomicExch(&a.mark[o], a.epoch) != a.epoch) {
+      const int idx = atomicAdd(a.count2, 1);
+      if (idx < a.cap2) a.list2[idx] = o;
+    }
+  }
+}
+template <int S>
+__global__ void __launch_bounds__(128) k_patch_f(const PatchArgs a, const int* list2, const int* count2, int cap2) {
+  pdl_entry();
+  const Lay& l = a.m.l;
+  const int n = min(*count2, cap2);
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < 3 * n; t += gridDim.x * blockDim.x) {
+    const int ci = t / n, o = list2[t - ci * n];
+    const int k = o / l.plane, rem = o - k * l.plane, j = rem / l.pitch, i = rem - j * l.pitch;
+    a.m.f[l.cstride * ci + o] = rhs_f<3, S>(a.m, ci, i, j, k);
+  }
+}
+__global__ void __launch_bounds__(128) k_patch_apply(const PatchArgs a) {
+  pdl_entry();
+  const Lay& l = a.m.l;
+  const int n = min(*a.count, a.cap);
+  const int st[3] = {1, l.pitch, l.plane};
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < 3 * n; t += gridDim.x * blockDim.x) {
+    const int ci = t / n, o = a.list[t - ci * n];
+    const float* fc = a.m.f + l.cstride * ci;
+    float s = 0.f;
+#pragma unroll
+    for (int dj = 0; dj < 3; ++dj) s += a.mu1[l.cstride * (ci + 3 * dj) + o] * (fc[o + st[dj]] - fc[o - st[dj]]);
+    const long long oc = l.cstride * ci + o;
+    const float X = s / 2.f + a.m.V[oc] + a.mu0[oc] * fc[o];
+    a.un[oc] = a.corrector ? (a.m.ua[oc] + X) * 0.5f : X;
+  }
+}
+
 // list of interior cells with any μ₁ ≠ 0 (rebuilt whenever the coefficients change)
 struct BandArgs { Lay l; const float* mu1; int* list; int* count; int cap; };
 template <int D>
