@@ -168,8 +168,9 @@ class ClockSampler:
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from `ncu --set full`
 # captures of these exact workloads on one GPU (summaries under profiles/): (bytes per launch, source)
 NCU_TRAFFIC = {
-    ("tgv", (128, 128, 128)): (83.80e6 + 11.83e6, "profiles/r1_v12_ncu_full_kmom3_tgv128.tsv (most of the 128^3 working set stays in the 126 MB L2)"),
-    ("sphere", (512, 256, 256)): (1276.7e6 + 392.1e6, "profiles/r1_v12_ncu_full_kmom3_sphere512.tsv"),
+    # mean of the two captured launches (predictor, corrector)
+    ("tgv", (128, 128, 128)): ((32.50e6 + 0.21e6 + 58.01e6 + 4.11e6) / 2, "profiles/r1_v15_ncu_full_kmom3_tgv128.tsv (most of the 128^3 working set stays in the 126 MB L2)"),
+    ("sphere", (512, 256, 256)): ((1273.3e6 + 387.2e6 + 1678.3e6 + 389.9e6) / 2, "profiles/r1_v15_ncu_full_kmom3_sphere512.tsv"),
 }
 
 
