@@ -348,3 +348,90 @@ def vcycle(levels, l=1, w=1):     # Vcycle!(ml;l,ω) MultiLevelPoisson.jl:88-101
     gauss_seidel_rb(coarse, 4, w)
     prolongate(fine["eps"], coarse["x"], c)
     increment(fine, w)
+
+
+# ---------------------------------------------------------------------------------------------------
+# The whole step: exitBC! (core.jl:226-233), solver! (MultiLevelPoisson.jl:108-128), mom_project!
+# (Flow.jl:223-232), mom_step! (Flow.jl:156-167).  `fl` = dict of Julia-order arrays u,u0,f,p,sigma,V,mu0,mu1
+# plus scalars; levels[0] aliases x≡p, L≡mu0, z≡sigma like the reference (WaterLily.jl:97).
+
+def exitBC(u, u0, dt):
+    N, n = u.shape[:-1], u.shape[-1]
+    dt = f32(dt)
+    Nm = tuple(k - 1 for k in N)
+    exitR = list(slice_(Nm, N[0], 1, 2))
+    inR = list(slice_(Nm, 2, 1, 2))
+    Uu, U0 = J(u), J(u0)
+    U = f32(sum(np.float64(Uu[I + (1,)]) for I in inR)) / f32(len(exitR))
+    for I in exitR:
+        Uu[I + (1,)] = U0[I + (1,)] - U * dt * (U0[I + (1,)] - U0[plus(I, d_(1, n), -1) + (1,)])
+    flux = f32(sum(np.float64(Uu[I + (1,)]) for I in exitR)) / f32(len(exitR)) - U
+    for I in exitR:
+        Uu[I + (1,)] = Uu[I + (1,)] - flux
+
+
+def solver(levels, n_log, tol=2e-3, itmx=32):
+    p = levels[0]
+    n_in = int(np.prod([k - 2 for k in p["r"].shape]))
+    r1tol, rinftol = (float(tol) / 10) * n_in, tol
+    residual(p)
+    L1 = lambda: f32(np.abs(p["r"]).sum(dtype=np.float64))
+    Linf = lambda: f32(np.abs(p["r"]).max())
+    r1, rinf, w = L1(), Linf(), f32(1)
+    npn = 0
+    while npn < itmx:
+        vcycle(levels, 1, w)
+        gauss_seidel_rb(p, 4, w)
+        rnew, rinf = L1(), Linf()
+        npn += 1
+        if rnew >= r1:
+            w = f32(max(0.2, 0.9 * float(w)))
+        elif rnew < r1:
+            w = f32(min(1.0, 1.02 * float(w)))
+        r1 = rnew
+        if float(r1) < r1tol and float(rinf) < rinftol:
+            break
+    perBC(p["x"], p["perdir"])
+    n_log.append(npn)
+
+
+def mom_project(fl, levels, w, n_log):
+    u, x, z, L = fl["u"], levels[0]["x"], levels[0]["z"], levels[0]["L"]
+    n = u.shape[-1]
+    dt = f32(w) * f32(fl["dt"][-1])
+    Uu, X, Z, Ll = J(u), J(x), J(z), J(L)
+    for I in inside(z):                                   # div(I,u) Flow.jl:13-19
+        s = f32(0)
+        for i in range(1, n + 1):
+            s = s + (Uu[plus(I, d_(i, n)) + (i,)] - Uu[I + (i,)])
+        Z[I] = s
+    x *= dt
+    solver(levels, n_log)
+    for i in range(1, n + 1):
+        for I in inside(x):
+            Uu[I + (i,)] = Uu[I + (i,)] - Ll[I + (i,)] * (X[I] - X[plus(I, d_(i, n), -1)])
+    x /= dt
+    BC(u, fl["uBC"], fl["exitBC"], fl["perdir"])
+
+
+def mom_step(fl, levels, n_log):
+    u, u0, f = fl["u"], fl["u0"], fl["f"]
+    lam = SCHEME[fl["scheme"]]
+    u0[...] = u
+    n = u.shape[-1]
+    u[tuple(slice(1, -1) for _ in range(n)) + (slice(None),)] = 0        # scale_u!(a,0) over inside_u(size(p))
+    # predictor
+    conv_diff(f, u0, fl["sigma"], lam, fl["nu"], fl["perdir"])
+    BDIM(u, u0, f, fl["V"], fl["mu0"], fl["mu1"], fl["dt"][-1])
+    BC(u, fl["uBC"], fl["exitBC"], fl["perdir"])
+    if fl["exitBC"]:
+        exitBC(u, u0, fl["dt"][-1])
+    mom_project(fl, levels, 1, n_log)
+    # corrector
+    conv_diff(f, u, fl["sigma"], lam, fl["nu"], fl["perdir"])
+    BDIM(u, u0, f, fl["V"], fl["mu0"], fl["mu1"], fl["dt"][-1])
+    inner = tuple(slice(1, -1) for _ in range(n)) + (slice(None),)
+    u[inner] = u[inner] * f32(0.5)
+    BC(u, fl["uBC"], fl["exitBC"], fl["perdir"])
+    mom_project(fl, levels, 0.5, n_log)
+    fl["dt"].append(CFL(u, fl["sigma"], fl["nu"]))

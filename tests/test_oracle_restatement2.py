@@ -138,3 +138,35 @@ def test_poisson_ops_two_restatements(dims, perdir, body):
     sim.lib.wlo_op_vcycle(sim.h, 0.95); r2.vcycle(lev, 1, 0.95)
     for l in range(sim.nlevels):
         _same(sim, lev, ("x", "r", "eps"), l)
+
+
+# ------------------------------------------------------------------------------------------ whole steps
+STEP_CASES = [((16, 12), (), True, "quick", dict(kind="sphere", center=(6, 6), radius=2.5)),
+              ((16, 12), (2,), False, "vanLeer", dict(kind="sphere", center=(6, 6), radius=2.5)),
+              ((12, 8, 4), (3,), True, "quick", dict(kind="sphere", center=(5, 4, 2), radius=2.0)),
+              ((8, 8, 8), (1, 2, 3), False, "cds", None)]
+
+
+@pytest.mark.parametrize("dims,perdir,exitBC,scheme,body", STEP_CASES)
+def test_mom_step_two_restatements(dims, perdir, exitBC, scheme, body):
+    """Three whole `mom_step!`s (Flow.jl:156-167: predictor, exitBC!, mom_project! with the multigrid
+    `solver!` loop and its ω adaptation, corrector, CFL) by both restatements from the same constructed state:
+    identical u, p, Δt history and iteration log."""
+    D = len(dims)
+    U = (1.0,) + (0.0,) * (D - 1)
+    b = wo.make_body(**body) if body else None
+    k = np.float32(2 * np.pi / dims[0])
+    u0 = lambda i, x: (0.2 * np.sin(k * x[0]) * np.cos(k * x[1]) + (1.0 if i == 1 else 0.0)) * np.ones(np.broadcast(*x).shape, np.float32)
+    sim = wo.OracleSim(dims, U, 4.0, nu=0.05, perdir=perdir, exitBC=exitBC, scheme=scheme, body=b, u0=u0)
+    fl = {nm: sim.field(nm).copy().T for nm in ("u", "u0", "f", "p", "sigma", "V", "mu0", "mu1")}
+    fl.update(dt=[np.float32(sim.dts[-1])], uBC=U, exitBC=exitBC, perdir=perdir, scheme=scheme, nu=0.05)
+    lev = _levels(sim)
+    lev[0].update(x=fl["p"], L=fl["mu0"], z=fl["sigma"])          # the aliases of WaterLily.jl:97
+    n_log = []
+    for _ in range(3):
+        sim.sim_step(remeasure=False)
+        r2.mom_step(fl, lev, n_log)
+    assert n_log == list(sim.n), (n_log, sim.n)
+    assert [float(x) for x in fl["dt"]] == [float(x) for x in sim.dts]
+    assert np.array_equal(sim.field("u"), fl["u"].T)
+    assert np.array_equal(sim.field("p"), fl["p"].T)
