@@ -444,7 +444,7 @@ static int xfer(wl_sim* s, int field, int level, float* host, size_t count, bool
     if (int e = halo(s, *f, (field == WL_U || field == WL_U0) ? 3 : 1)) return e;
   }
   WL_CUDA(s, cudaStreamSynchronize(s->st));
-  if (up && field == WL_MU1) s->band_dirty = true;
+  if (up && field == WL_MU1) { s->band_dirty = true; s->band_from_measure = false; }
   if (up && (field == WL_MU1 || field == WL_MU0 || field == WL_V)) s->free_flow = false;
   return WL_OK;
 }
@@ -469,7 +469,13 @@ int wl_measure_body(wl_sim* s, const wl_body* body, double t, double eps) {
   if (body->kind == 0) return WL_OK;                 // NoBody: measure! is a no-op (Body.jl:83)
   if (body->kind < 0 || body->kind > 3) return fail(s, WL_ERR_UNSUPPORTED, "unknown body kind");
   cudaSetDevice(s->device);
-  MeasArgs a{s->lay, body_at(body, s->D, (float)t), (float)eps, s->per.kz0, s->sigma.base, s->V.base, s->mu0.base, s->mu1.base};
+  MeasArgs a{s->lay, body_at(body, s->D, (float)t), (float)eps, s->per.kz0, s->sigma.base, s->V.base, s->mu0.base, s->mu1.base,
+             nullptr, nullptr, 0};
+  if (s->D == 3 && s->band_count) {                 // K-MOM's band list comes out of the same pass (no k_band_scan)
+    WL_CUDA(s, cudaMemsetAsync(s->band_count, 0, sizeof(int), s->st));
+    a.band_list = s->band_list; a.band_count = s->band_count; a.band_cap = s->band_cap;
+    s->band_from_measure = true;
+  }
   DISPATCH_D(s, k_measure, grid_all(s->lay), blk(s->D), a);
   s->band_dirty = true; s->free_flow = false;
   bc_vec(s, s->mu0, nullptr, false);

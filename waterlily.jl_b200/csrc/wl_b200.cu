@@ -104,6 +104,7 @@ struct wl_sim {
   int* band_count2 = nullptr;
   int band_cap2 = 0, band_epoch = 0;
   bool band_dirty = false;
+  bool band_from_measure = false;   // k_measure appended the band cells itself: only the count has to be checked
   bool free_flow = true;      // V ≡ 0, μ₀ ≡ 1, μ₁ ≡ 0 as the constructor left them (no measure!, no upload of them)
   std::vector<Level> lv;
   cudaStream_t st = nullptr;
@@ -192,6 +193,17 @@ void plane_launch(const Lay& l, dim3& g, dim3& b) {
 
 // Every kernel goes through here: a launch that may overlap its scheduling with the tail of the
 // previous kernel of the stream (see pdl_entry in wl_common.cuh).  WL_NO_PDL=1 restores plain launches.
+template <class... KArgs, class... Args>
+inline void launch_pdl_smem(cudaStream_t st, dim3 g, dim3 b, size_t smem, void (*kern)(KArgs...), Args&&... args) {
+  static const bool off = getenv("WL_NO_PDL") != nullptr;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = g; cfg.blockDim = b; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = off ? 0 : 1;
+  cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
 template <class... KArgs, class... Args>
 inline void launch_pdl(cudaStream_t st, dim3 g, dim3 b, void (*kern)(KArgs...), Args&&... args) {
   static const bool off = getenv("WL_NO_PDL") != nullptr;
@@ -653,8 +665,8 @@ void coarse_block(wl_sim* s, size_t first, float w) {
     }
     cudaEvent_t pa_, pb_;
     const bool prof_ = prof_pre(s, "k_coarse_sm", &pa_, &pb_);
-    if (s->D == 3) k_coarse_sm<3><<<1, 1024, smem, s->st>>>(a);
-    else k_coarse_sm<2><<<1, 1024, smem, s->st>>>(a);
+    if (s->D == 3) launch_pdl_smem(s->st, dim3(1), dim3(1024), smem, k_coarse_sm<3>, a);
+    else launch_pdl_smem(s->st, dim3(1), dim3(1024), smem, k_coarse_sm<2>, a);
     if (prof_) prof_post(s, "k_coarse_sm", pa_, pb_);
     ++s->launches;
     return;
@@ -862,7 +874,20 @@ void mom_rhs(wl_sim* s, DevField& uadv, const float* acc) {
 }
 // list of band cells for k_mom_patch; rebuilt when μ₁ changed (measure!, uploads)
 int band_rebuild(wl_sim* s) {
-  for (int pass = 0; pass < 2; ++pass) {
+  bool have = false;
+  if (s->band_from_measure) {                       // list written by k_measure: valid unless it overflowed
+    int n = 0;
+    WL_CUDA(s, cudaMemcpyAsync(&n, s->band_count, sizeof(int), cudaMemcpyDeviceToHost, s->st));
+    WL_CUDA(s, cudaStreamSynchronize(s->st));
+    have = n <= s->band_cap;
+    if (!have) {
+      if (s->band_list) cudaFree(s->band_list);
+      s->band_cap = n + n / 4 + 1024;
+      WL_CUDA(s, cudaMalloc(&s->band_list, sizeof(int) * (size_t)s->band_cap));
+    }
+    s->band_from_measure = false;
+  }
+  for (int pass = 0; pass < 2 && !have; ++pass) {
     WL_CUDA(s, cudaMemsetAsync(s->band_count, 0, sizeof(int), s->st));
     BandArgs a{s->lay, s->mu1.base, s->band_list, s->band_count, s->band_cap};
     DISPATCH_D(s, k_band_scan, grid_inside(s->lay), blk(s->D), a);

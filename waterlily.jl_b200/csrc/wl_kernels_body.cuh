@@ -92,6 +92,7 @@ struct MeasArgs {
   float eps;
   int kz0;           // global index of local plane 0 (slab decomposition)
   float* sigma; float* V; float* mu0; float* mu1;
+  int* band_list; int* band_count; int band_cap;   // interior cells with any μ₁ ≠ 0, appended here (K-MOM's band patch)
 };
 
 // measure! (Body.jl:28-48) in one pass over ALL cells: the three fills of :29, measure_sdf! :30
@@ -137,6 +138,15 @@ __global__ void __launch_bounds__(256) k_measure(const MeasArgs a) {
   }
 #pragma unroll
   for (int q = 0; q < D * D; ++q) a.mu1[l.cstride * q + o] = m1[q];
+  if (a.band_count && in) {                                   // same predicate as k_band_scan, on the values just written
+    bool any = false;
+#pragma unroll
+    for (int q = 0; q < D * D; ++q) any |= m1[q] != 0.f;
+    if (any) {
+      const int idx = atomicAdd(a.band_count, 1);
+      if (idx < a.band_cap) a.band_list[idx] = o;
+    }
+  }
 }
 
 // pressure_force (Metrics.jl:126-133): df = p·nds over inside (df ≡ flow.f, zero elsewhere).
