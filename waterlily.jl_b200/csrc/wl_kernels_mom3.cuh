@@ -128,6 +128,9 @@ struct Mom3Smem {
   float ring[M3_RING][3][M3_TILE];
   float shy[2][3][M3_TY][32];
   float shx[2][3][M3_TY];          // W32: x-face fluxes of the column right of the block, per row
+#ifndef WL_M3_FIN_LDG
+  float fin[2][9][32 * M3_TY];     // u⁰, V, μ₀ of the thread's own cell, staged two planes ahead (slot = plane & 1)
+#endif
 };
 
 // NB ("no body"): the host knows V ≡ 0 and μ₀ ≡ 1 on every cell (no body was ever measured or uploaded
@@ -181,6 +184,26 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
     }
   };
   const int tc = (ty + 2) * M3_TW + lane + 2;     // own position in the tile
+#ifndef WL_M3_FIN_LDG
+  // Operands of the finalisation (u⁰, V, μ₀ of the own cell): ncu showed 9 % of the kernel's stall samples on
+  // the first use of these loads although they were issued a whole plane of flux arithmetic earlier.  They now
+  // travel by cp.async too, two planes ahead and without holding registers; each thread reads back what it
+  // staged itself, so its own wait_group is the only synchronisation.
+  const bool fin_thread = out_ij && ty < M3_TY - 1;
+  auto stage_fin = [&](int kp) {
+    if (!fin_thread) return;
+    const int o = oij + plane * kp;
+    float* dst = &sm.fin[kp & 1][0][tid];
+#pragma unroll
+    for (int ci = 0; ci < 3; ++ci) {
+      cp_async4(dst + ci * (32 * M3_TY), a.u0c[ci] + o);
+      if (!NB) {
+        cp_async4(dst + (3 + ci) * (32 * M3_TY), a.Vc[ci] + o);
+        cp_async4(dst + (6 + ci) * (32 * M3_TY), a.m0c[ci] + o);
+      }
+    }
+  };
+#endif
   // W32: lane = 7·c + r of the last row evaluates the x face of component c at column i0+32, row j0+r
   const bool xact = W32 && ty == M3_TY - 1 && lane < 3 * (M3_TY - 1);
   const int xr = lane % (M3_TY - 1), xc = min(lane / (M3_TY - 1), 2);
@@ -189,7 +212,11 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   const int kxX = (FAST || p0) ? 0 : (i0 + 32 == N0 - 1 ? 3 : 0);
   float xprev = 0.f;                              // u_x(i0+32, j0+xr) one plane below
 
-  stage(k0); stage(k0 + 1); cp_async_commit();
+  stage(k0); stage(k0 + 1);
+#ifndef WL_M3_FIN_LDG
+  if (k0 <= kend - 1) stage_fin(k0);
+#endif
+  cp_async_commit();
   stage(k0 + 2); cp_async_commit();
   float w[3][4];   // own column: planes k-2, k-1, k, k+1
 #pragma unroll
@@ -221,6 +248,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
     float fu0[3], fV[3], fm0[3];
     const int opv = oij + plane * (k - 1);
     const bool fin = !TOP && k > k0 && out_ij;
+#ifdef WL_M3_FIN_LDG
     if (fin) {
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) {
@@ -228,6 +256,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
         if (!NB) { fV[ci] = a.Vc[ci][opv]; fm0[ci] = a.m0c[ci][opv]; }
       }
     }
+#endif
     float(*cur)[M3_TILE] = sm.ring[k & (M3_RING - 1)];
     float nb[3][3][3];   // nb[c][d][m2,m1,p1]
 #pragma unroll
@@ -280,6 +309,18 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
         for (int ci = 0; ci < 3; ++ci) Fxu[ci] = sm.shx[buf][ci][min(ty, M3_TY - 2)];
       }
     }
+#ifndef WL_M3_FIN_LDG
+    if (lastp) cp_async_wait<0>();                           // no wait_group above on the last plane
+    if (fin) {
+      const float* src = &sm.fin[(k - 1) & 1][0][tid];
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci) {
+        fu0[ci] = src[ci * (32 * M3_TY)];
+        if (!NB) { fV[ci] = src[(3 + ci) * (32 * M3_TY)]; fm0[ci] = src[(6 + ci) * (32 * M3_TY)]; }
+      }
+    }
+    if (!TOP && k + 1 <= kend - 1) stage_fin(k + 1);        // joins the group committed at the top of the next plane
+#endif
     if (fin) {                                               // finalise cell (i,j,k-1)
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) {
