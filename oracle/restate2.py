@@ -435,3 +435,103 @@ def mom_step(fl, levels, n_log):
     BC(u, fl["uBC"], fl["exitBC"], fl["perdir"])
     mom_project(fl, levels, 0.5, n_log)
     fl["dt"].append(CFL(u, fl["sigma"], fl["nu"]))
+
+
+# ---------------------------------------------------------------------------------------------------
+# Body side: measure! (Body.jl:28-51), kernels (:54-60), measure(::AutoBody) (AutoBody.jl:29-37) for a
+# sphere/circle `sdf(ξ)=|ξ|-R` under the translation map `ξ = x - (c + v t)`, pressure_force (Metrics.jl:116-133).
+# The gradient of the sdf is written in closed form (the reference differentiates it with ForwardDiff).
+
+def sinpi(d):
+    return f32(np.sin(np.pi * np.float64(d)))
+
+
+def cospi(d):
+    return f32(np.cos(np.pi * np.float64(d)))
+
+
+PI32 = f32(np.pi)
+
+
+def kern(d):
+    return (f32(1) + cospi(d)) / f32(2)
+
+
+def kern0(d):
+    return (f32(1) + d + sinpi(d) / PI32) / f32(2)
+
+
+def kern1(d):
+    return (f32(1) - d * d) / f32(4) - (d * sinpi(d) + (f32(1) + cospi(d)) / PI32) / (f32(2) * PI32)
+
+
+def mu0(d, e):
+    d, e = f32(d), f32(e)
+    return f32(0) if d / e < f32(-1) + np.sqrt(np.spacing(abs(d))) else kern0(min(d / e, f32(1)))
+
+
+def mu1(d, e):
+    d, e = f32(d), f32(e)
+    return e * kern1(max(f32(-1), min(d / e, f32(1))))
+
+
+def measure_sphere(center, R, vel, x, t, fastd2):
+    n = len(x)
+    t = f32(t)
+    xi = [f32(x[k]) - (f32(center[k]) + f32(vel[k]) * t) for k in range(n)]
+    s = f32(0)
+    for k in range(n):
+        s = s + xi[k] * xi[k]
+    rt = np.sqrt(s)
+    d = rt - f32(R)
+    zero = [f32(0)] * n
+    if d * d > fastd2:
+        return d, zero, zero
+    g = [xi[k] / rt for k in range(n)]
+    if any(np.isnan(v) for v in g):
+        return d, zero, zero
+    m = f32(0)
+    for k in range(n):
+        m = m + g[k] * g[k]
+    m = np.sqrt(m)
+    return d / m, [v / m for v in g], [f32(v) for v in vel]
+
+
+def measure_flow(fl, center, R, vel, t, eps, exitBC, perdir):
+    """`measure!(a,body;t,ϵ)`: fills V, μ₀, μ₁, σ (Julia-order arrays in `fl`), then the two BC! calls."""
+    V, m0, m1, sg = fl["V"], fl["mu0"], fl["mu1"], fl["sigma"]
+    n = V.shape[-1]
+    V[...] = 0; m0[...] = 1; m1[...] = 0
+    eps = f32(eps)
+    d2 = (f32(2) + eps) * (f32(2) + eps)
+    Vv, M0, M1, S = J(V), J(m0), J(m1), J(sg)
+    loc = lambda i, I: [f32(I[k] - 1.5) - (f32(0.5) if k + 1 == i else f32(0)) for k in range(n)]   # core.jl:177
+    for I in inside(sg):
+        S[I] = measure_sphere(center, R, vel, loc(0, I), t, f32(0))[0]          # measure_sdf!: the raw sdf
+    for I in inside(sg):
+        if S[I] * S[I] < d2:
+            for i in range(1, n + 1):
+                di, ni, Vi = measure_sphere(center, R, vel, loc(i, I), t, d2)
+                di = di if abs(di) <= 0.5 else np.copysign(di, S[I])
+                Vv[I + (i,)] = Vi[i - 1]
+                M0[I + (i,)] = mu0(di, eps)
+                for j in range(1, n + 1):
+                    M1[I + (i, j)] = mu1(di, eps) * ni[j - 1]
+        elif S[I] < 0:
+            for i in range(1, n + 1):
+                M0[I + (i,)] = 0
+    BC(m0, (0.0,) * n, False, perdir)
+    BC(V, (0.0,) * n, exitBC, perdir)
+
+
+def pressure_force(p, center, R, vel, t):
+    n = p.ndim
+    P = J(p)
+    out = np.zeros(n, np.float64)
+    for I in inside(p):
+        x = [f32(I[k] - 1.5) for k in range(n)]
+        d, nn, _ = measure_sphere(center, R, vel, x, t, f32(1))
+        kq = kern(max(f32(-1), min(d, f32(1))))
+        for c in range(n):
+            out[c] += np.float64(P[I] * (nn[c] * kq))
+    return out
