@@ -150,6 +150,9 @@ int wl_cfl(wl_sim* s, float* dt);                       /* CFL(a) src/Flow.jl:23
 
 /* ---- pressure_force(sim) (src/Metrics.jl:116-133); clobbers flow.f like the reference        */
 int wl_pressure_force(wl_sim* s, const wl_body* body, double t, double out[3]);
+/* ---- viscous_force(sim) (src/Metrics.jl:140-152): -2ν Σ S(I,u)·nds; clobbers flow.f like the reference.
+ *      total_force(sim) (:159) is the sum of the two, formed by the caller.                     */
+int wl_viscous_force(wl_sim* s, const wl_body* body, double t, double out[3]);
 
 /* ---- asynchronous stepping for host-overlap: enqueue `nsteps` mom_steps without reading
  *      results back between them is not possible (Δt and the solver loop are host-steered in

@@ -535,3 +535,31 @@ def pressure_force(p, center, R, vel, t):
         for c in range(n):
             out[c] += np.float64(P[I] * (nn[c] * kq))
     return out
+
+
+def viscous_force(u, nu, center, R, vel, t):
+    """`viscous_force(u,ν,df,body,t)` Metrics.jl:140-152 with `∂(i,j,I,u)` :42-45 and `S(I,u)` :134."""
+    N, n = u.shape[:-1], u.shape[-1]
+    Uu = J(u)
+
+    def dudx(i, j, I):
+        ei, ej = d_(i, n), d_(j, n)
+        if i == j:
+            return Uu[plus(I, ei) + (i,)] - Uu[I + (i,)]
+        return (Uu[plus(I, ej) + (i,)] + Uu[plus(plus(I, ej), ei) + (i,)]
+                - Uu[plus(I, ej, -1) + (i,)] - Uu[plus(plus(I, ej, -1), ei) + (i,)]) / f32(4)
+
+    m2nu = f32(-2) * f32(nu)
+    out = np.zeros(n, np.float64)
+    for I in CR(*[(2, k - 1) for k in N]):
+        x = [f32(I[k] - 1.5) for k in range(n)]
+        d, nn, _ = measure_sphere(center, R, vel, x, t, f32(1))
+        kq = kern(max(f32(-1), min(d, f32(1))))
+        nds = [nn[c] * kq for c in range(n)]
+        for a in range(1, n + 1):
+            acc = f32(0)
+            for c in range(1, n + 1):
+                S = (dudx(a, c, I) + dudx(c, a, I)) / f32(2)
+                acc = acc + (m2nu * S) * nds[c - 1]
+            out[a - 1] += np.float64(acc)
+    return out

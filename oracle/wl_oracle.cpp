@@ -725,6 +725,40 @@ void pressure_force(Sim& s, const wlo_body& b, real t, double* out) {
   }
 }
 
+// `∂(i,j,I,u)` Metrics.jl:42-45: ∂uᵢ/∂xⱼ at the centre of cell I
+inline real dudx(const Grid& g, const real* u, int i, int j, long I) {
+  const real* ui = u + g.cells * i;
+  if (i == j) return ui[I + g.s[i]] - ui[I];
+  return (ui[I + g.s[j]] + ui[I + g.s[j] + g.s[i]] - ui[I - g.s[j]] - ui[I - g.s[j] + g.s[i]]) / 4;
+}
+// `viscous_force(u,ν,df,body,t)` Metrics.jl:140-152: df[I,:] = -2ν·S(I,u)·nds over inside_u(u) (clobbers f)
+void viscous_force(Sim& s, const wlo_body& b, real t, double* out) {
+  const Grid& g = s.g; const int D = g.D;
+  std::fill(s.f.begin(), s.f.end(), (real)0);
+  const real m2nu = -2 * (real)s.cfg.nu;
+  const real* u = s.u.data();
+  loop(g, inside(g), [&](long I, int i, int j, int k) {
+    real x[3] = {(real)i - (real)0.5, (real)j - (real)0.5, (real)k - (real)0.5};
+    Meas m = measure(b, D, x, t, (real)1);
+    real kq = kern(std::max((real)-1, std::min(m.d, (real)1)));
+    real nds[3];
+    for (int c = 0; c < D; ++c) nds[c] = m.n[c] * kq;
+    for (int a = 0; a < D; ++a) {
+      real acc = 0;
+      for (int c = 0; c < D; ++c) {
+        real S = (dudx(g, u, a, c, I) + dudx(g, u, c, a, I)) / 2;          // S(I,u) Metrics.jl:134
+        acc += (m2nu * S) * nds[c];
+      }
+      s.f[g.cells * a + I] = acc;
+    }
+  });
+  for (int c = 0; c < 3; ++c) out[c] = 0;
+  for (int c = 0; c < D; ++c) {
+    const real* fc = s.f.data() + g.cells * c;
+    out[c] = sum_box(g, whole(g), [&](long I) { return fc[I]; });
+  }
+}
+
 // `accelerate!(r,t,g,U)` Flow.jl:69-73 restricted to space-uniform g(i,t)+dU(i,t)/dt
 void accelerate(const Grid& g, real* r, const real* acc) {
   if (!acc) return;
@@ -898,6 +932,7 @@ int wlo_poisson_solver(void* h, int itmx) {   // stand-alone single-level pcg so
 void wlo_mult(void* h, real* x) { mult_into_z(((Sim*)h)->ml.lv[0], x); }   // z = A x  (mult!)
 real wlo_cfl(void* h) { return CFL(*(Sim*)h); }
 void wlo_pressure_force(void* h, const wlo_body* b, double t, double* out) { pressure_force(*(Sim*)h, *b, (real)t, out); }
+void wlo_viscous_force(void* h, const wlo_body* b, double t, double* out) { viscous_force(*(Sim*)h, *b, (real)t, out); }
 
 // ---- single operations, for kernel-level parity tests
 void wlo_op_conv_diff(void* h, int use_u0) {

@@ -97,6 +97,7 @@ def load(dtype=np.float32, fast_path=None):
     lib.wlo_cfl.restype = R
     lib.wlo_cfl.argtypes = [C.c_void_p]
     lib.wlo_pressure_force.argtypes = [C.c_void_p, C.POINTER(Body), C.c_double, C.POINTER(C.c_double)]
+    lib.wlo_viscous_force.argtypes = [C.c_void_p, C.POINTER(Body), C.c_double, C.POINTER(C.c_double)]
     lib.wlo_op_conv_diff.argtypes = [C.c_void_p, C.c_int]
     lib.wlo_op_bdim.argtypes = [C.c_void_p]
     lib.wlo_op_scale_u.argtypes = [C.c_void_p, R]
@@ -259,6 +260,12 @@ class OracleSim:
         out = (C.c_double * 3)()
         t = self.time() if t is None else t
         self.lib.wlo_pressure_force(self.h, C.byref(self.body), float(t), out)
+        return np.array(out[: self.D])
+
+    def viscous_force(self, t=None):
+        out = (C.c_double * 3)()
+        t = self.time() if t is None else t
+        self.lib.wlo_viscous_force(self.h, C.byref(self.body), float(t), out)
         return np.array(out[: self.D])
 
     def cfl(self):

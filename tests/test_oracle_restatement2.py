@@ -198,3 +198,12 @@ def test_measure_and_force_two_restatements(dims, center, R, vel, t, exitBC, per
     f_ref = sim.pressure_force(t)
     f_py = r2.pressure_force(p.T, center, R, vel, t)
     assert np.allclose(f_ref, f_py, rtol=1e-6, atol=1e-6)
+    u = sim.field("u")
+    u[...] = np.random.default_rng(9).standard_normal(u.shape).astype(np.float32)
+    sim.cfg.nu = 0.07
+    # viscous_force (Metrics.jl:140-152): strain-rate tensor from the staggered differences
+    sim2 = wo.OracleSim(dims, (1.0,) + (0.0,) * (D - 1), perdir=perdir, exitBC=exitBC, body=b, nu=0.07, build_poisson=False)
+    sim2.field("u")[...] = u
+    v_ref = sim2.viscous_force(t)
+    v_py = r2.viscous_force(u.T, 0.07, center, R, vel, t)
+    assert np.abs(v_ref).max() > 1e-3 and np.allclose(v_ref, v_py, rtol=1e-6, atol=1e-6), (v_ref, v_py)

@@ -231,6 +231,22 @@ def test_config_A_circle_2d(wl):
     assert np.allclose(f_gpu, f_ref, rtol=1e-4, atol=1e-4 * np.abs(f_ref).max()), (f_gpu, f_ref)
 
 
+@pytest.mark.parametrize("dims,perdir,body", [
+    ((32, 24), (), dict(kind="circle", center=(12, 11), radius=4.0)),
+    ((32, 16, 16), (3,), dict(kind="sphere", center=(12, 8, 8), radius=4.0)),
+    ((24, 16, 16), (), dict(kind="cylinder", axis=2, center=(10, 8, 0), radius=3.0))])
+def test_viscous_and_total_force(wl, dims, perdir, body):
+    """viscous_force / total_force (src/Metrics.jl:140-159) after a few steps: CUDA vs oracle."""
+    D = len(dims)
+    sim, ref = pair(wl, dims, (1.0,) + (0.0,) * (D - 1), 8.0, body=body, nu=0.05, perdir=perdir)
+    step_both(sim, ref, 3, remeasure=False)
+    v_gpu, v_ref = sim.viscous_force(), ref.viscous_force()
+    assert np.abs(v_ref).max() > 1e-4
+    assert np.allclose(v_gpu, v_ref, rtol=1e-5, atol=1e-5 * np.abs(v_ref).max()), (v_gpu, v_ref)
+    t_gpu = sim.total_force()
+    assert np.allclose(t_gpu, ref.pressure_force() + v_ref, rtol=1e-4, atol=1e-4 * np.abs(t_gpu).max())
+
+
 def _golden_cases():
     import os, sys
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))

@@ -35,7 +35,7 @@ ABI_SYMBOLS = [
     "wl_create", "wl_destroy", "wl_last_error", "wl_version", "wl_field_dims", "wl_download",
     "wl_upload", "wl_nlevels", "wl_finish_ic", "wl_measure_body", "wl_set_body_coeffs",
     "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_poisson_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
-    "wl_cfl", "wl_pressure_force", "wl_sync", "wl_launch_count", "wl_enable_timing",
+    "wl_cfl", "wl_pressure_force", "wl_viscous_force", "wl_sync", "wl_launch_count", "wl_enable_timing",
     "wl_last_phase_times", "wl_debug_op", "wl_prof_begin", "wl_prof_end", "wl_event_record",
     "wl_event_elapsed_ms", "wl_create_slab", "wl_nccl_unique_id", "wl_slab_info", "wl_halo_stats", "wl_halo_transport", "wl_halo_timing",
 ]
@@ -112,6 +112,7 @@ def load_library(path=None):
     lib.wl_set_dt.argtypes = [P, F]
     lib.wl_cfl.argtypes = [P, FP]
     lib.wl_pressure_force.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3)]
+    lib.wl_viscous_force.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3)]
     lib.wl_sync.argtypes = [P]
     lib.wl_launch_count.argtypes = [P]
     lib.wl_launch_count.restype = C.c_int64
@@ -438,6 +439,17 @@ class Simulation:
         self._check(self.lib.wl_pressure_force(self.h, C.byref(self.body.c), float(t), C.byref(out)))
         return np.array(out[: self.D])
 
+    def viscous_force(self, t=None):
+        """`viscous_force(sim)` (src/Metrics.jl:140-152)."""
+        out = (C.c_double * 3)()
+        t = self.time() if t is None else t
+        self._check(self.lib.wl_viscous_force(self.h, C.byref(self.body.c), float(t), C.byref(out)))
+        return np.array(out[: self.D])
+
+    def total_force(self, t=None):
+        """`total_force(sim)` (src/Metrics.jl:159)."""
+        return self.pressure_force(t) + self.viscous_force(t)
+
     def debug_op(self, op, level=0, arg=0.0):
         self._check(self.lib.wl_debug_op(self.h, int(op), int(level), float(arg)))
 
@@ -517,3 +529,11 @@ def measure(sim, t=None):
 
 def pressure_force(sim):
     return sim.pressure_force()
+
+
+def viscous_force(sim):
+    return sim.viscous_force()
+
+
+def total_force(sim):
+    return sim.total_force()

@@ -636,6 +636,21 @@ int wl_pressure_force(wl_sim* s, const wl_body* body, double t, double out[3]) {
   return check_async(s, "wl_pressure_force");
 }
 
+int wl_viscous_force(wl_sim* s, const wl_body* body, double t, double out[3]) {
+  if (!s || !body || !out) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  if (int e = halo(s, s->u, 1)) return e;               // the strain rate reads u across slab interfaces
+  ViscArgs a{s->lay, body_at(body, s->D, (float)t), s->u.base, s->f.base, s->cfg.nu, s->per.kz0};
+  DISPATCH_D(s, k_visc_df, grid_all(s->lay), blk(s->D), a);
+  for (int c = 0; c < s->D; ++c) {
+    SumArgs sa{s->lay, s->f.base + s->lay.cstride * c, s->redw, s->d_red + 3 + c};
+    DISPATCH_D(s, k_sum_all, grid_all(s->lay), blk(s->D), sa);
+  }
+  if (int e = fetch_red(s)) return e;
+  for (int c = 0; c < 3; ++c) out[c] = c < s->D ? s->h_red[3 + c].sum : 0.0;
+  return check_async(s, "wl_viscous_force");
+}
+
 int wl_debug_op(wl_sim* s, int op, int level, float arg) {
   if (!s) return WL_ERR_INVALID;
   cudaSetDevice(s->device);

@@ -174,6 +174,47 @@ __global__ void __launch_bounds__(256) k_force_df(const ForceArgs a) {
   for (int ci = 0; ci < D; ++ci) a.f[l.cstride * ci + o] = df[ci];
 }
 
+// viscous_force (Metrics.jl:140-152): df = -2ν·S(I,u)·nds over inside_u(u), S the rate-of-strain tensor
+// (:134) from the staggered differences ∂(i,j,I,u) (:42-45); summed per component by k_sum_all.
+struct ViscArgs { Lay l; BodyDev b; const float* u; float* f; float nu; int kz0; };
+template <int D>
+__global__ void __launch_bounds__(256) k_visc_df(const ViscArgs a) {
+  pdl_entry();
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z : 0;
+  if (i < 0 || i >= l.n0 || j >= l.n1 || k >= l.n2) return;
+  const int o = l.off(i, j, k);
+  const bool in = i >= 1 && i <= l.n0 - 2 && j >= 1 && j <= l.n1 - 2 && (D == 2 || (k >= 1 && k <= l.n2 - 2));
+  float df[3] = {0.f, 0.f, 0.f};
+  if (in) {
+    const float x[3] = {(float)i - 0.5f, (float)j - 0.5f, (float)(k + a.kz0) - 0.5f};
+    const Meas m = measure_pt<D>(a.b, x, 1.f);
+    const float kq = kern(fmaxf(-1.f, fminf(m.d, 1.f)));
+    const int st[3] = {1, l.pitch, l.plane};
+    float g[3][3];                                           // g[c][d] = ∂u_c/∂x_d
+#pragma unroll
+    for (int c = 0; c < D; ++c) {
+      const float* uc = a.u + l.cstride * c;
+#pragma unroll
+      for (int d = 0; d < D; ++d)
+        g[c][d] = c == d ? uc[o + st[c]] - uc[o]
+                         : (uc[o + st[d]] + uc[o + st[d] + st[c]] - uc[o - st[d]] - uc[o - st[d] + st[c]]) / 4.f;
+    }
+    const float m2nu = -2.f * a.nu;
+#pragma unroll
+    for (int c = 0; c < D; ++c) {
+      float acc = 0.f;
+#pragma unroll
+      for (int d = 0; d < D; ++d) acc += (m2nu * ((g[c][d] + g[d][c]) / 2.f)) * (m.n[d] * kq);
+      df[c] = acc;
+    }
+  }
+#pragma unroll
+  for (int ci = 0; ci < D; ++ci) a.f[l.cstride * ci + o] = df[ci];
+}
+
 // Σ over the whole array of one scalar, in Float64 (sum(To,df,dims=...) Metrics.jl:132)
 struct SumArgs { Lay l; const float* a; RedWork w; Red* out; };
 template <int D>

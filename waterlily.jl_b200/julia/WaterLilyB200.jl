@@ -15,7 +15,7 @@ module WaterLilyB200
 
 using WaterLily
 import WaterLily: AbstractFlow, AbstractPoisson, AbstractBody, mom_step!, measure!, update!, solver!, CFL,
-                  pressure_force, time
+                  pressure_force, viscous_force, total_force, time
 
 const LIB = get(ENV, "WATERLILY_B200_LIB", joinpath(@__DIR__, "..", "libwaterlily_b200.so"))
 
@@ -211,6 +211,14 @@ function pressure_force(a::B200Flow{D}, body::B200Body) where D
                      a.h.ptr, Ref(body.c), time(a), out))
     collect(out[][1:D])
 end
+
+function viscous_force(a::B200Flow{D}, body::B200Body) where D
+    out = Ref(ntuple(_ -> 0.0, 3))
+    check(a.h, ccall((:wl_viscous_force, LIB), Cint, (Ptr{Cvoid}, Ref{WLBody}, Cdouble, Ref{NTuple{3,Float64}}),
+                     a.h.ptr, Ref(body.c), time(a), out))
+    collect(out[][1:D])
+end
+total_force(a::B200Flow, body::B200Body) = pressure_force(a, body) .+ viscous_force(a, body)
 
 "Drop-in constructor: WaterLily's own `Simulation` with the two factories swapped."
 B200Simulation(dims, uBC, L; device=0, kw...) =
