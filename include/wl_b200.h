@@ -153,6 +153,10 @@ int wl_pressure_force(wl_sim* s, const wl_body* body, double t, double out[3]);
 /* ---- viscous_force(sim) (src/Metrics.jl:140-152): -2ν Σ S(I,u)·nds; clobbers flow.f like the reference.
  *      total_force(sim) (:159) is the sum of the two, formed by the caller.                     */
 int wl_viscous_force(wl_sim* s, const wl_body* body, double t, double out[3]);
+/* ---- pressure_moment(x₀,sim) (viscous = 0) / viscous_moment(x₀,sim) (viscous = 1) (src/Metrics.jl:168-192);
+ *      x₀ is converted to Float32 (the reference promotes to the type of x₀).  In 2D both components of
+ *      `out` hold the scalar moment, as the reference's broadcast leaves them.                   */
+int wl_force_moment(wl_sim* s, const wl_body* body, double t, const double x0[3], int viscous, double out[3]);
 
 /* ---- asynchronous stepping for host-overlap: enqueue `nsteps` mom_steps without reading
  *      results back between them is not possible (Δt and the solver loop are host-steered in

@@ -563,3 +563,43 @@ def viscous_force(u, nu, center, R, vel, t):
                 acc = acc + (m2nu * S) * nds[c - 1]
             out[a - 1] += np.float64(acc)
     return out
+
+
+def force_moment(p, u, nu, x0, center, R, vel, t, viscous):
+    """`pressure_moment` / `viscous_moment` (Metrics.jl:168-192), x₀ in Float32."""
+    N, n = u.shape[:-1], u.shape[-1]
+    Uu, P = J(u), J(p)
+
+    def dudx(i, j, I):
+        ei, ej = d_(i, n), d_(j, n)
+        if i == j:
+            return Uu[plus(I, ei) + (i,)] - Uu[I + (i,)]
+        return (Uu[plus(I, ej) + (i,)] + Uu[plus(plus(I, ej), ei) + (i,)]
+                - Uu[plus(I, ej, -1) + (i,)] - Uu[plus(plus(I, ej, -1), ei) + (i,)]) / f32(4)
+
+    def cross(a, b):
+        if n == 3:
+            return [a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0]]
+        c = a[0] * b[1] - a[1] * b[0]
+        return [c, c]
+
+    out = np.zeros(n, np.float64)
+    for I in CR(*[(2, k - 1) for k in N]):
+        x = [f32(I[k] - 1.5) for k in range(n)]
+        d, nn, _ = measure_sphere(center, R, vel, x, t, f32(1))
+        kq = kern(max(f32(-1), min(d, f32(1))))
+        v = [nn[c] * kq for c in range(n)]
+        r = [x[c] - f32(x0[c]) for c in range(n)]
+        if viscous:
+            w = []
+            for a in range(1, n + 1):
+                acc = f32(0)
+                for c in range(1, n + 1):
+                    acc = acc + ((dudx(a, c, I) + dudx(c, a, I)) / f32(2)) * v[c - 1]
+                w.append(acc)
+            df = [f32(-2) * f32(nu) * q for q in cross(r, w)]
+        else:
+            df = [P[I] * q for q in cross(r, v)]
+        for c in range(n):
+            out[c] += np.float64(df[c])
+    return out

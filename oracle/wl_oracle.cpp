@@ -759,6 +759,45 @@ void viscous_force(Sim& s, const wlo_body& b, real t, double* out) {
   }
 }
 
+// `pressure_moment(x₀,p,df,body,t)` / `viscous_moment(x₀,u,ν,df,body,t)` Metrics.jl:168-192 with x₀ in T.
+// 3D: cross(a,b); 2D: the scalar a₁b₂-a₂b₁ broadcast to both components of df (StaticArrays).
+void force_moment(Sim& s, const wlo_body& b, real t, const real* x0, int viscous, double* out) {
+  const Grid& g = s.g; const int D = g.D;
+  std::fill(s.f.begin(), s.f.end(), (real)0);
+  const real m2nu = -2 * (real)s.cfg.nu;
+  const real* u = s.u.data();
+  loop(g, inside(g), [&](long I, int i, int j, int k) {
+    real x[3] = {(real)i - (real)0.5, (real)j - (real)0.5, (real)k - (real)0.5};
+    Meas m = measure(b, D, x, t, (real)1);
+    real kq = kern(std::max((real)-1, std::min(m.d, (real)1)));
+    real v[3] = {0, 0, 0}, r[3] = {0, 0, 0};
+    for (int c = 0; c < D; ++c) { v[c] = m.n[c] * kq; r[c] = x[c] - x0[c]; }
+    if (viscous) {                                                   // S(I,u)*nds
+      real w[3] = {0, 0, 0};
+      for (int a = 0; a < D; ++a) {
+        real acc = 0;
+        for (int c = 0; c < D; ++c) acc += ((dudx(g, u, a, c, I) + dudx(g, u, c, a, I)) / 2) * v[c];
+        w[a] = acc;
+      }
+      for (int c = 0; c < D; ++c) v[c] = w[c];
+    }
+    const real sc = viscous ? m2nu : s.p[I];
+    if (D == 3) {
+      s.f[I] = sc * (r[1] * v[2] - r[2] * v[1]);
+      s.f[g.cells + I] = sc * (r[2] * v[0] - r[0] * v[2]);
+      s.f[2 * g.cells + I] = sc * (r[0] * v[1] - r[1] * v[0]);
+    } else {
+      const real cz = sc * (r[0] * v[1] - r[1] * v[0]);
+      s.f[I] = cz; s.f[g.cells + I] = cz;
+    }
+  });
+  for (int c = 0; c < 3; ++c) out[c] = 0;
+  for (int c = 0; c < D; ++c) {
+    const real* fc = s.f.data() + g.cells * c;
+    out[c] = sum_box(g, whole(g), [&](long I) { return fc[I]; });
+  }
+}
+
 // `accelerate!(r,t,g,U)` Flow.jl:69-73 restricted to space-uniform g(i,t)+dU(i,t)/dt
 void accelerate(const Grid& g, real* r, const real* acc) {
   if (!acc) return;
@@ -933,6 +972,10 @@ void wlo_mult(void* h, real* x) { mult_into_z(((Sim*)h)->ml.lv[0], x); }   // z 
 real wlo_cfl(void* h) { return CFL(*(Sim*)h); }
 void wlo_pressure_force(void* h, const wlo_body* b, double t, double* out) { pressure_force(*(Sim*)h, *b, (real)t, out); }
 void wlo_viscous_force(void* h, const wlo_body* b, double t, double* out) { viscous_force(*(Sim*)h, *b, (real)t, out); }
+void wlo_force_moment(void* h, const wlo_body* b, double t, const double* x0, int viscous, double* out) {
+  real x[3] = {(real)x0[0], (real)x0[1], (real)x0[2]};
+  force_moment(*(Sim*)h, *b, (real)t, x, viscous, out);
+}
 
 // ---- single operations, for kernel-level parity tests
 void wlo_op_conv_diff(void* h, int use_u0) {

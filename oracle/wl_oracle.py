@@ -98,6 +98,7 @@ def load(dtype=np.float32, fast_path=None):
     lib.wlo_cfl.argtypes = [C.c_void_p]
     lib.wlo_pressure_force.argtypes = [C.c_void_p, C.POINTER(Body), C.c_double, C.POINTER(C.c_double)]
     lib.wlo_viscous_force.argtypes = [C.c_void_p, C.POINTER(Body), C.c_double, C.POINTER(C.c_double)]
+    lib.wlo_force_moment.argtypes = [C.c_void_p, C.POINTER(Body), C.c_double, C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_double)]
     lib.wlo_op_conv_diff.argtypes = [C.c_void_p, C.c_int]
     lib.wlo_op_bdim.argtypes = [C.c_void_p]
     lib.wlo_op_scale_u.argtypes = [C.c_void_p, R]
@@ -266,6 +267,14 @@ class OracleSim:
         out = (C.c_double * 3)()
         t = self.time() if t is None else t
         self.lib.wlo_viscous_force(self.h, C.byref(self.body), float(t), out)
+        return np.array(out[: self.D])
+
+    def moment(self, x0, viscous=False, t=None):
+        """`pressure_moment(x₀,sim)` / `viscous_moment(x₀,sim)` (Metrics.jl:168-192)."""
+        out = (C.c_double * 3)()
+        t = self.time() if t is None else t
+        xx = (C.c_double * 3)(*(list(x0) + [0.0] * (3 - len(x0))))
+        self.lib.wlo_force_moment(self.h, C.byref(self.body), float(t), xx, int(viscous), out)
         return np.array(out[: self.D])
 
     def cfl(self):

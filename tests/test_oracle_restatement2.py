@@ -207,3 +207,10 @@ def test_measure_and_force_two_restatements(dims, center, R, vel, t, exitBC, per
     v_ref = sim2.viscous_force(t)
     v_py = r2.viscous_force(u.T, 0.07, center, R, vel, t)
     assert np.abs(v_ref).max() > 1e-3 and np.allclose(v_ref, v_py, rtol=1e-6, atol=1e-6), (v_ref, v_py)
+    # pressure_moment / viscous_moment (Metrics.jl:168-192) about an off-centre point
+    x0 = tuple(c + 0.75 for c in center)
+    sim2.field("p")[...] = p
+    for visc in (False, True):
+        m_ref = sim2.moment(x0, visc, t)
+        m_py = r2.force_moment(p.T, u.T, 0.07, x0, center, R, vel, t, visc)
+        assert np.abs(m_ref).max() > 1e-3 and np.allclose(m_ref, m_py, rtol=1e-6, atol=1e-5), (visc, m_ref, m_py)

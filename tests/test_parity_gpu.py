@@ -245,6 +245,12 @@ def test_viscous_and_total_force(wl, dims, perdir, body):
     assert np.allclose(v_gpu, v_ref, rtol=1e-5, atol=1e-5 * np.abs(v_ref).max()), (v_gpu, v_ref)
     t_gpu = sim.total_force()
     assert np.allclose(t_gpu, ref.pressure_force() + v_ref, rtol=1e-4, atol=1e-4 * np.abs(t_gpu).max())
+    # pressure_moment / viscous_moment (src/Metrics.jl:168-192) about an off-centre point
+    x0 = tuple(float(c) + 0.75 for c in body["center"][:D])
+    for visc in (False, True):
+        m_gpu, m_ref = sim.moment(x0, visc), ref.moment(x0, visc)
+        assert np.abs(m_ref).max() > 1e-5
+        assert np.allclose(m_gpu, m_ref, rtol=1e-4, atol=1e-4 * np.abs(m_ref).max()), (visc, m_gpu, m_ref)
 
 
 def _golden_cases():

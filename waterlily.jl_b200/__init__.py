@@ -35,7 +35,7 @@ ABI_SYMBOLS = [
     "wl_create", "wl_destroy", "wl_last_error", "wl_version", "wl_field_dims", "wl_download",
     "wl_upload", "wl_nlevels", "wl_finish_ic", "wl_measure_body", "wl_set_body_coeffs",
     "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_poisson_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
-    "wl_cfl", "wl_pressure_force", "wl_viscous_force", "wl_sync", "wl_launch_count", "wl_enable_timing",
+    "wl_cfl", "wl_pressure_force", "wl_viscous_force", "wl_force_moment", "wl_sync", "wl_launch_count", "wl_enable_timing",
     "wl_last_phase_times", "wl_debug_op", "wl_prof_begin", "wl_prof_end", "wl_event_record",
     "wl_event_elapsed_ms", "wl_create_slab", "wl_nccl_unique_id", "wl_slab_info", "wl_halo_stats", "wl_halo_transport", "wl_halo_timing",
 ]
@@ -113,6 +113,7 @@ def load_library(path=None):
     lib.wl_cfl.argtypes = [P, FP]
     lib.wl_pressure_force.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3)]
     lib.wl_viscous_force.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3)]
+    lib.wl_force_moment.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3), I, C.POINTER(C.c_double * 3)]
     lib.wl_sync.argtypes = [P]
     lib.wl_launch_count.argtypes = [P]
     lib.wl_launch_count.restype = C.c_int64
@@ -445,6 +446,18 @@ class Simulation:
         t = self.time() if t is None else t
         self._check(self.lib.wl_viscous_force(self.h, C.byref(self.body.c), float(t), C.byref(out)))
         return np.array(out[: self.D])
+
+    def moment(self, x0, viscous=False, t=None):
+        """`pressure_moment(x₀,sim)` / `viscous_moment(x₀,sim)` (src/Metrics.jl:168-192)."""
+        out = (C.c_double * 3)()
+        t = self.time() if t is None else t
+        xx = (C.c_double * 3)(*(list(x0) + [0.0] * (3 - len(x0))))
+        self._check(self.lib.wl_force_moment(self.h, C.byref(self.body.c), float(t), C.byref(xx), int(viscous), C.byref(out)))
+        return np.array(out[: self.D])
+
+    def total_moment(self, x0, t=None):
+        """`total_moment(x₀,sim)` (src/Metrics.jl:199)."""
+        return self.moment(x0, False, t) + self.moment(x0, True, t)
 
     def total_force(self, t=None):
         """`total_force(sim)` (src/Metrics.jl:159)."""

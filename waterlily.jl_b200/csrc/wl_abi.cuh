@@ -651,6 +651,22 @@ int wl_viscous_force(wl_sim* s, const wl_body* body, double t, double out[3]) {
   return check_async(s, "wl_viscous_force");
 }
 
+int wl_force_moment(wl_sim* s, const wl_body* body, double t, const double x0[3], int viscous, double out[3]) {
+  if (!s || !body || !out || !x0) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  if (viscous) { if (int e = halo(s, s->u, 1)) return e; }
+  MomentArgs a{s->lay, body_at(body, s->D, (float)t), s->p.base, s->u.base, s->f.base, s->cfg.nu, s->per.kz0, viscous ? 1 : 0,
+               {(float)x0[0], (float)x0[1], (float)x0[2]}};
+  DISPATCH_D(s, k_moment_df, grid_all(s->lay), blk(s->D), a);
+  for (int c = 0; c < s->D; ++c) {
+    SumArgs sa{s->lay, s->f.base + s->lay.cstride * c, s->redw, s->d_red + 3 + c};
+    DISPATCH_D(s, k_sum_all, grid_all(s->lay), blk(s->D), sa);
+  }
+  if (int e = fetch_red(s)) return e;
+  for (int c = 0; c < 3; ++c) out[c] = c < s->D ? s->h_red[3 + c].sum : 0.0;
+  return check_async(s, "wl_force_moment");
+}
+
 int wl_debug_op(wl_sim* s, int op, int level, float arg) {
   if (!s) return WL_ERR_INVALID;
   cudaSetDevice(s->device);

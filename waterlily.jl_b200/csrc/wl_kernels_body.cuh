@@ -215,6 +215,62 @@ __global__ void __launch_bounds__(256) k_visc_df(const ViscArgs a) {
   for (int ci = 0; ci < D; ++ci) a.f[l.cstride * ci + o] = df[ci];
 }
 
+// pressure_moment / viscous_moment (Metrics.jl:168-192): df = p·cross(x-x₀, nds) or -2ν·cross(x-x₀, S·nds);
+// in 2D the cross product is the scalar a₁b₂-a₂b₁, stored in both components like the reference's broadcast.
+struct MomentArgs { Lay l; BodyDev b; const float* p; const float* u; float* f; float nu; int kz0; int viscous; float x0[3]; };
+template <int D>
+__global__ void __launch_bounds__(256) k_moment_df(const MomentArgs a) {
+  pdl_entry();
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z : 0;
+  if (i < 0 || i >= l.n0 || j >= l.n1 || k >= l.n2) return;
+  const int o = l.off(i, j, k);
+  const bool in = i >= 1 && i <= l.n0 - 2 && j >= 1 && j <= l.n1 - 2 && (D == 2 || (k >= 1 && k <= l.n2 - 2));
+  float df[3] = {0.f, 0.f, 0.f};
+  if (in) {
+    const float x[3] = {(float)i - 0.5f, (float)j - 0.5f, (float)(k + a.kz0) - 0.5f};
+    const Meas m = measure_pt<D>(a.b, x, 1.f);
+    const float kq = kern(fmaxf(-1.f, fminf(m.d, 1.f)));
+    float v[3] = {0.f, 0.f, 0.f}, r[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+    for (int c = 0; c < D; ++c) { v[c] = m.n[c] * kq; r[c] = x[c] - a.x0[c]; }
+    if (a.viscous) {
+      const int st[3] = {1, l.pitch, l.plane};
+      float g[3][3];
+#pragma unroll
+      for (int c = 0; c < D; ++c) {
+        const float* uc = a.u + l.cstride * c;
+#pragma unroll
+        for (int d = 0; d < D; ++d)
+          g[c][d] = c == d ? uc[o + st[c]] - uc[o]
+                           : (uc[o + st[d]] + uc[o + st[d] + st[c]] - uc[o - st[d]] - uc[o - st[d] + st[c]]) / 4.f;
+      }
+      float w[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+      for (int c = 0; c < D; ++c) {
+        float acc = 0.f;
+#pragma unroll
+        for (int d = 0; d < D; ++d) acc += ((g[c][d] + g[d][c]) / 2.f) * v[d];
+        w[c] = acc;
+      }
+#pragma unroll
+      for (int c = 0; c < D; ++c) v[c] = w[c];
+    }
+    const float sc = a.viscous ? -2.f * a.nu : a.p[o];
+    if (D == 3) {
+      df[0] = sc * (r[1] * v[2] - r[2] * v[1]);
+      df[1] = sc * (r[2] * v[0] - r[0] * v[2]);
+      df[2] = sc * (r[0] * v[1] - r[1] * v[0]);
+    } else {
+      df[0] = df[1] = sc * (r[0] * v[1] - r[1] * v[0]);
+    }
+  }
+#pragma unroll
+  for (int ci = 0; ci < D; ++ci) a.f[l.cstride * ci + o] = df[ci];
+}
+
 // Σ over the whole array of one scalar, in Float64 (sum(To,df,dims=...) Metrics.jl:132)
 struct SumArgs { Lay l; const float* a; RedWork w; Red* out; };
 template <int D>

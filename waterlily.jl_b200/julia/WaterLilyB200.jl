@@ -15,7 +15,7 @@ module WaterLilyB200
 
 using WaterLily
 import WaterLily: AbstractFlow, AbstractPoisson, AbstractBody, mom_step!, measure!, update!, solver!, CFL,
-                  pressure_force, viscous_force, total_force, time
+                  pressure_force, viscous_force, total_force, pressure_moment, viscous_moment, total_moment, time
 
 const LIB = get(ENV, "WATERLILY_B200_LIB", joinpath(@__DIR__, "..", "libwaterlily_b200.so"))
 
@@ -219,6 +219,15 @@ function viscous_force(a::B200Flow{D}, body::B200Body) where D
     collect(out[][1:D])
 end
 total_force(a::B200Flow, body::B200Body) = pressure_force(a, body) .+ viscous_force(a, body)
+function force_moment(x₀, a::B200Flow{D}, body::B200Body, viscous::Bool) where D
+    out = Ref(ntuple(_ -> 0.0, 3)); x = Ref(ntuple(i -> i <= D ? Float64(x₀[i]) : 0.0, 3))
+    check(a.h, ccall((:wl_force_moment, LIB), Cint, (Ptr{Cvoid}, Ref{WLBody}, Cdouble, Ref{NTuple{3,Float64}}, Cint, Ref{NTuple{3,Float64}}),
+                     a.h.ptr, Ref(body.c), time(a), x, viscous, out))
+    collect(out[][1:D])
+end
+pressure_moment(x₀, a::B200Flow, body::B200Body) = force_moment(x₀, a, body, false)
+viscous_moment(x₀, a::B200Flow, body::B200Body) = force_moment(x₀, a, body, true)
+total_moment(x₀, a::B200Flow, body::B200Body) = pressure_moment(x₀, a, body) .+ viscous_moment(x₀, a, body)
 
 "Drop-in constructor: WaterLily's own `Simulation` with the two factories swapped."
 B200Simulation(dims, uBC, L; device=0, kw...) =
