@@ -74,7 +74,8 @@ typedef struct wl_body {
 /* Fields a caller can read or write (sim.flow.* and sim.pois.levels[l].*). */
 enum wl_field {
   WL_U = 0, WL_U0 = 1, WL_F = 2, WL_P = 3, WL_SIGMA = 4, WL_V = 5, WL_MU0 = 6, WL_MU1 = 7,
-  WL_X = 10, WL_R = 11, WL_EPS = 12, WL_Z = 13, WL_L = 14, WL_DIAG = 15, WL_IDIAG = 16
+  WL_X = 10, WL_R = 11, WL_EPS = 12, WL_Z = 13, WL_L = 14, WL_DIAG = 15, WL_IDIAG = 16,
+  WL_MEAN_P = 20, WL_MEAN_U = 21, WL_MEAN_UU = 22   /* MeanFlow.P/.U/.UU, after wl_meanflow_init */
 };
 
 /* Per-step results: replaces `push!(a.Δt,CFL(a))` (src/Flow.jl:166), the two `push!(ml.n,nᵖ)`
@@ -157,6 +158,15 @@ int wl_viscous_force(wl_sim* s, const wl_body* body, double t, double out[3]);
  *      x₀ is converted to Float32 (the reference promotes to the type of x₀).  In 2D both components of
  *      `out` hold the scalar moment, as the reference's broadcast leaves them.                   */
 int wl_force_moment(wl_sim* s, const wl_body* body, double t, const double x0[3], int viscous, double out[3]);
+
+/* ---- running statistics: MeanFlow (src/Metrics.jl:205-263).  wl_meanflow_init = the constructor / reset!
+ *      (P, U and, with uu_stats, UU allocated and zeroed); wl_meanflow_update = the three loops of update!
+ *      with ε = dt/(dt + time(meanflow) + eps(T)) formed by the caller, who owns the time vector `t` like
+ *      the reference; wl_meanflow_copy_to_flow = copy!(flow, meanflow).  P/U/UU are read and written
+ *      through wl_download / wl_upload (WL_MEAN_P, WL_MEAN_U, WL_MEAN_UU).                          */
+int wl_meanflow_init(wl_sim* s, int uu_stats);
+int wl_meanflow_update(wl_sim* s, float eps);
+int wl_meanflow_copy_to_flow(wl_sim* s);
 
 /* ---- asynchronous stepping for host-overlap: enqueue `nsteps` mom_steps without reading
  *      results back between them is not possible (Δt and the solver loop are host-steered in

@@ -603,3 +603,16 @@ def force_moment(p, u, nu, x0, center, R, vel, t, viscous):
         for c in range(n):
             out[c] += np.float64(df[c])
     return out
+
+
+def mean_update(P, U, UU, p, u, eps):
+    """`update!(meanflow,flow)` Metrics.jl:239-249 on Julia-order arrays (UU may be None)."""
+    eps = f32(eps)
+    om = f32(1) - eps
+    P[...] = eps * p + om * P
+    U[...] = eps * u + om * U
+    if UU is not None:
+        n = u.shape[-1]
+        for i in range(n):
+            for j in range(n):
+                UU[..., i, j] = eps * (u[..., i] * u[..., j]) + om * UU[..., i, j]

@@ -972,6 +972,20 @@ void wlo_mult(void* h, real* x) { mult_into_z(((Sim*)h)->ml.lv[0], x); }   // z 
 real wlo_cfl(void* h) { return CFL(*(Sim*)h); }
 void wlo_pressure_force(void* h, const wlo_body* b, double t, double* out) { pressure_force(*(Sim*)h, *b, (real)t, out); }
 void wlo_viscous_force(void* h, const wlo_body* b, double t, double* out) { viscous_force(*(Sim*)h, *b, (real)t, out); }
+// `update!(meanflow,flow)` Metrics.jl:239-249: the three running-average loops over ALL indices, ε from the caller
+void wlo_meanflow_update(void* h, real* P, real* U, real* UU, real eps) {
+  Sim* s = (Sim*)h; const Grid& g = s->g; const int D = g.D;
+  const real om = 1 - eps;
+  for (long I = 0; I < g.cells; ++I) P[I] = eps * s->p[I] + om * P[I];
+  for (long I = 0; I < g.cells * D; ++I) U[I] = eps * s->u[I] + om * U[I];
+  if (UU)
+    for (int i = 0; i < D; ++i)
+      for (int j = 0; j < D; ++j)
+        for (long I = 0; I < g.cells; ++I) {
+          real& q = UU[I + g.cells * (i + (long)D * j)];
+          q = eps * (s->u[g.cells * i + I] * s->u[g.cells * j + I]) + om * q;
+        }
+}
 void wlo_force_moment(void* h, const wlo_body* b, double t, const double* x0, int viscous, double* out) {
   real x[3] = {(real)x0[0], (real)x0[1], (real)x0[2]};
   force_moment(*(Sim*)h, *b, (real)t, x, viscous, out);

@@ -98,6 +98,7 @@ def load(dtype=np.float32, fast_path=None):
     lib.wlo_cfl.argtypes = [C.c_void_p]
     lib.wlo_pressure_force.argtypes = [C.c_void_p, C.POINTER(Body), C.c_double, C.POINTER(C.c_double)]
     lib.wlo_viscous_force.argtypes = [C.c_void_p, C.POINTER(Body), C.c_double, C.POINTER(C.c_double)]
+    lib.wlo_meanflow_update.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, R]
     lib.wlo_force_moment.argtypes = [C.c_void_p, C.POINTER(Body), C.c_double, C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_double)]
     lib.wlo_op_conv_diff.argtypes = [C.c_void_p, C.c_int]
     lib.wlo_op_bdim.argtypes = [C.c_void_p]
@@ -279,3 +280,31 @@ class OracleSim:
 
     def cfl(self):
         return float(self.lib.wlo_cfl(self.h))
+
+
+class MeanFlow:
+    """`MeanFlow(flow; t_init, uu_stats)` + `update!`/`reset!`/`uu`/`copy!` (src/Metrics.jl:205-263) on an OracleSim."""
+
+    def __init__(self, sim, t_init=None, uu_stats=False):
+        self.sim = sim
+        T = sim.dtype
+        self.P = np.zeros_like(sim.field("p"))
+        self.U = np.zeros_like(sim.field("u"))
+        self.UU = np.zeros((sim.D, sim.D) + self.P.shape, T) if uu_stats else None
+        self.t = [T(sim.time() if t_init is None else t_init)]
+
+    def time(self):
+        return self.t[-1] - self.t[0]
+
+    def update(self):
+        T = self.sim.dtype
+        dt = T(self.sim.time()) - self.t[-1]
+        eps = dt / (dt + self.time() + np.finfo(T).eps)
+        if len(self.t) == 1:
+            eps = T(1)
+        uu = self.UU.ctypes.data if self.UU is not None else None
+        self.sim.lib.wlo_meanflow_update(self.sim.h, self.P.ctypes.data, self.U.ctypes.data, uu, float(eps))
+        self.t.append(self.t[-1] + dt)
+
+    def uu(self):
+        return self.UU - self.U[None, :] * self.U[:, None]

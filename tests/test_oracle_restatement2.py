@@ -214,3 +214,20 @@ def test_measure_and_force_two_restatements(dims, center, R, vel, t, exitBC, per
         m_ref = sim2.moment(x0, visc, t)
         m_py = r2.force_moment(p.T, u.T, 0.07, x0, center, R, vel, t, visc)
         assert np.abs(m_ref).max() > 1e-3 and np.allclose(m_ref, m_py, rtol=1e-6, atol=1e-5), (visc, m_ref, m_py)
+
+
+def test_meanflow_two_restatements():
+    """MeanFlow update! (Metrics.jl:239-249): ε schedule and the three running averages, incl. the u⊗u tensor."""
+    sim = wo.OracleSim((16, 12), (1.0, 0.0), 4.0, nu=0.05, body=wo.make_body(kind="sphere", center=(6, 6), radius=2.5))
+    mf = wo.MeanFlow(sim, uu_stats=True)
+    P, U, UU = (np.zeros_like(a).T for a in (mf.P, mf.U, mf.UU))
+    t = [np.float32(sim.time())]
+    for n in range(4):
+        sim.sim_step(remeasure=False)
+        mf.update()
+        dt = np.float32(sim.time()) - t[-1]
+        eps = np.float32(1) if len(t) == 1 else dt / (dt + (t[-1] - t[0]) + np.finfo(np.float32).eps)
+        r2.mean_update(P, U, UU, sim.field("p").T, sim.field("u").T, eps)
+        t.append(t[-1] + dt)
+    assert np.array_equal(mf.P, P.T) and np.array_equal(mf.U, U.T) and np.array_equal(mf.UU, UU.T)
+    assert np.abs(mf.uu()).max() > 0 and [float(x) for x in mf.t] == [float(x) for x in t]

@@ -253,6 +253,29 @@ def test_viscous_and_total_force(wl, dims, perdir, body):
         assert np.allclose(m_gpu, m_ref, rtol=1e-4, atol=1e-4 * np.abs(m_ref).max()), (visc, m_gpu, m_ref)
 
 
+@pytest.mark.parametrize("dims,perdir", [((32, 24), ()), ((24, 16, 16), (3,))])
+def test_meanflow(wl, dims, perdir):
+    """MeanFlow (src/Metrics.jl:205-263): running averages of p, u and u⊗u over ALL indices, the ε schedule,
+    uu(), reset! and copy!(flow, meanflow): CUDA vs oracle."""
+    D = len(dims)
+    body = dict(kind="sphere", center=tuple(d / 2.5 for d in dims), radius=3.0)
+    sim, ref = pair(wl, dims, (1.0,) + (0.0,) * (D - 1), 6.0, body=body, nu=0.05, perdir=perdir)
+    mg, mr = wl.MeanFlow(sim, uu_stats=True), wo.MeanFlow(ref, uu_stats=True)
+    for _ in range(4):
+        step_both(sim, ref, 1, remeasure=False)
+        mg.update()
+        mr.update()
+    assert np.allclose(np.array(mg.t, np.float64), np.array(mr.t, np.float64), rtol=1e-6, atol=0)
+    close(mg.P, mr.P, 1e-5, "P")
+    close(mg.U, mr.U, 1e-5, "U")
+    close(mg.UU, mr.UU, 1e-5, "UU")
+    close(mg.uu(), mr.uu(), 2e-5, "uu")
+    mg.copy_to_flow()
+    assert np.array_equal(sim.flow.u, mg.U) and np.array_equal(sim.flow.p, mg.P)
+    mg.reset()
+    assert float(np.abs(mg.U).max()) == 0.0 and len(mg.t) == 1
+
+
 def _golden_cases():
     import os, sys
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))

@@ -26,7 +26,7 @@ _LIBNAME = os.path.join(_HERE, "libwaterlily_b200.so")
 
 WL_OK, WL_ERR_INVALID, WL_ERR_UNSUPPORTED, WL_ERR_CUDA, WL_ERR_NO_DEVICE = range(5)
 FIELDS = dict(u=0, u0=1, f=2, p=3, sigma=4, V=5, mu0=6, mu1=7,
-              x=10, r=11, eps=12, z=13, L=14, D=15, iD=16)
+              x=10, r=11, eps=12, z=13, L=14, D=15, iD=16, mean_P=20, mean_U=21, mean_UU=22)
 SCHEMES = dict(quick=0, cds=1, vanLeer=2)
 KINDS = dict(none=0, sphere=1, circle=1, cylinder=2, torus=3)
 
@@ -35,7 +35,7 @@ ABI_SYMBOLS = [
     "wl_create", "wl_destroy", "wl_last_error", "wl_version", "wl_field_dims", "wl_download",
     "wl_upload", "wl_nlevels", "wl_finish_ic", "wl_measure_body", "wl_set_body_coeffs",
     "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_poisson_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
-    "wl_cfl", "wl_pressure_force", "wl_viscous_force", "wl_force_moment", "wl_sync", "wl_launch_count", "wl_enable_timing",
+    "wl_cfl", "wl_pressure_force", "wl_viscous_force", "wl_force_moment", "wl_meanflow_init", "wl_meanflow_update", "wl_meanflow_copy_to_flow", "wl_sync", "wl_launch_count", "wl_enable_timing",
     "wl_last_phase_times", "wl_debug_op", "wl_prof_begin", "wl_prof_end", "wl_event_record",
     "wl_event_elapsed_ms", "wl_create_slab", "wl_nccl_unique_id", "wl_slab_info", "wl_halo_stats", "wl_halo_transport", "wl_halo_timing",
 ]
@@ -114,6 +114,9 @@ def load_library(path=None):
     lib.wl_pressure_force.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3)]
     lib.wl_viscous_force.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3)]
     lib.wl_force_moment.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3), I, C.POINTER(C.c_double * 3)]
+    lib.wl_meanflow_init.argtypes = [P, I]
+    lib.wl_meanflow_update.argtypes = [P, F]
+    lib.wl_meanflow_copy_to_flow.argtypes = [P]
     lib.wl_sync.argtypes = [P]
     lib.wl_launch_count.argtypes = [P]
     lib.wl_launch_count.restype = C.c_int64
@@ -538,6 +541,42 @@ def sim_time(sim):
 
 def measure(sim, t=None):
     return sim.measure(t)
+
+
+class MeanFlow:
+    """`MeanFlow(flow; t_init, uu_stats)` (src/Metrics.jl:205-227) with `update!` (:239-249), `reset!` (:231-236),
+    `uu` (:251-259) and `copy!(flow, meanflow)` (:260-263).  P/U/UU live on the device; `t` is a host list."""
+
+    def __init__(self, sim, t_init=None, uu_stats=False):
+        self.sim, self.uu_stats = sim, bool(uu_stats)
+        sim._check(sim.lib.wl_meanflow_init(sim.h, int(self.uu_stats)))
+        self.t = [np.float32(sim.time() if t_init is None else t_init)]
+
+    P = property(lambda self: self.sim.download("mean_P"))
+    U = property(lambda self: self.sim.download("mean_U"))
+    UU = property(lambda self: self.sim.download("mean_UU") if self.uu_stats else None)
+
+    def time(self):
+        return self.t[-1] - self.t[0]
+
+    def reset(self, t_init=0.0):
+        self.sim._check(self.sim.lib.wl_meanflow_init(self.sim.h, int(self.uu_stats)))
+        self.t = [np.float32(t_init)]
+
+    def update(self):
+        dt = np.float32(self.sim.time()) - self.t[-1]
+        eps = dt / (dt + self.time() + np.finfo(np.float32).eps)
+        if len(self.t) == 1:
+            eps = np.float32(1)          # the first update takes the instantaneous field
+        self.sim._check(self.sim.lib.wl_meanflow_update(self.sim.h, float(eps)))
+        self.t.append(self.t[-1] + dt)
+
+    def uu(self):
+        U = self.U
+        return self.UU - U[None, :] * U[:, None]
+
+    def copy_to_flow(self):
+        self.sim._check(self.sim.lib.wl_meanflow_copy_to_flow(self.sim.h))
 
 
 def pressure_force(sim):

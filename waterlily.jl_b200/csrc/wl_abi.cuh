@@ -370,6 +370,7 @@ void wl_destroy(wl_sim* s) {
   }
   free_field(s->u); free_field(s->u0); free_field(s->f); free_field(s->p);
   free_field(s->sigma); free_field(s->V); free_field(s->mu0); free_field(s->mu1); free_field(s->w);
+  free_field(s->mf_P); free_field(s->mf_U); free_field(s->mf_UU);
   if (s->band_list) cudaFree(s->band_list);
   if (s->band_list2) cudaFree(s->band_list2);
   if (s->band_mark) cudaFree(s->band_mark);
@@ -395,7 +396,7 @@ int wl_field_dims(const wl_sim* s, int field, int level, int32_t dims[5], int32_
   int n = 0;
   dims[n++] = lay.n0; dims[n++] = lay.n1;
   if (s->D == 3) dims[n++] = lay.n2;
-  if (f->ncomp == s->D * s->D && field == WL_MU1) { dims[n++] = s->D; dims[n++] = s->D; }
+  if (f->ncomp == s->D * s->D && (field == WL_MU1 || field == WL_MEAN_UU)) { dims[n++] = s->D; dims[n++] = s->D; }
   else if (f->ncomp > 1) dims[n++] = f->ncomp;
   *ndims = n;
   return WL_OK;
@@ -439,7 +440,7 @@ static int xfer(wl_sim* s, int field, int level, float* host, size_t count, bool
                                      (size_t)lay.n1 * lay.n2, cudaMemcpyDeviceToHost, s->st));
     }
   }
-  if (up && s->dist.n > 1 && (field < 10 || s->lv[level].dist)) {
+  if (up && s->dist.n > 1 && field < WL_MEAN_P && (field < 10 || s->lv[level].dist)) {
     // the caller's slab carries one ghost plane; deeper halo planes come from the neighbours
     if (int e = halo(s, *f, (field == WL_U || field == WL_U0) ? 3 : 1)) return e;
   }
@@ -665,6 +666,36 @@ int wl_force_moment(wl_sim* s, const wl_body* body, double t, const double x0[3]
   if (int e = fetch_red(s)) return e;
   for (int c = 0; c < 3; ++c) out[c] = c < s->D ? s->h_red[3 + c].sum : 0.0;
   return check_async(s, "wl_force_moment");
+}
+
+int wl_meanflow_init(wl_sim* s, int uu_stats) {
+  if (!s) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  char* arena = s->arena; s->arena = nullptr;       // private to the rank: plain allocations, never peer-mapped
+  int e = WL_OK;
+  free_field(s->mf_P); free_field(s->mf_U); free_field(s->mf_UU);
+  if (!(e = alloc_field(s, s->mf_P, s->lay, 1)) && !(e = alloc_field(s, s->mf_U, s->lay, s->D)) && uu_stats)
+    e = alloc_field(s, s->mf_UU, s->lay, s->D * s->D);
+  s->arena = arena;
+  if (e) return e;
+  return check_async(s, "wl_meanflow_init");
+}
+int wl_meanflow_update(wl_sim* s, float eps) {
+  if (!s) return WL_ERR_INVALID;
+  if (!s->mf_P.alloc) return fail(s, WL_ERR_INVALID, "wl_meanflow_init has not been called");
+  cudaSetDevice(s->device);
+  MeanArgs a{s->lay, s->p.base, s->u.base, s->mf_P.base, s->mf_U.base, s->mf_UU.alloc ? s->mf_UU.base : nullptr, eps};
+  DISPATCH_D(s, k_mean_update, grid_all(s->lay), blk(s->D), a);
+  return check_async(s, "wl_meanflow_update");
+}
+int wl_meanflow_copy_to_flow(wl_sim* s) {
+  if (!s) return WL_ERR_INVALID;
+  if (!s->mf_P.alloc) return fail(s, WL_ERR_INVALID, "wl_meanflow_init has not been called");
+  cudaSetDevice(s->device);
+  WL_CUDA(s, cudaMemcpyAsync(s->u.alloc, s->mf_U.alloc, s->u.bytes, cudaMemcpyDeviceToDevice, s->st));   // a.u .= b.U
+  WL_CUDA(s, cudaMemcpyAsync(s->p.alloc, s->mf_P.alloc, s->p.bytes, cudaMemcpyDeviceToDevice, s->st));   // a.p .= b.P
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  return check_async(s, "wl_meanflow_copy_to_flow");
 }
 
 int wl_debug_op(wl_sim* s, int op, int level, float arg) {

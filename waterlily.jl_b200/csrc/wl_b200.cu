@@ -99,6 +99,7 @@ struct wl_sim {
   int* band_list = nullptr;   // interior cells with μ₁ ≠ 0 (patched after K-MOM)
   int* band_count = nullptr;
   int band_cap = 0;
+  DevField mf_P, mf_U, mf_UU;  // MeanFlow (Metrics.jl:205-263): allocated by wl_meanflow_init
   int* band_mark = nullptr;   // per cell: epoch of the last list2 build that took it (de-duplication)
   int* band_list2 = nullptr;  // band cells and their face neighbours: the cells whose f the patch needs
   int* band_count2 = nullptr;
@@ -1074,6 +1075,9 @@ DevField* flow_field(wl_sim* s, int field, int level, Lay* lay) {
       case WL_MU1: f = &s->mu1; break;
       default: return nullptr;
     }
+  } else if (field >= WL_MEAN_P && field <= WL_MEAN_UU) {
+    f = field == WL_MEAN_P ? &s->mf_P : (field == WL_MEAN_U ? &s->mf_U : &s->mf_UU);
+    if (!f->alloc) return nullptr;
   } else {
     if (level < 0 || level >= (int)s->lv.size()) return nullptr;
     Level& l = s->lv[level];

@@ -271,6 +271,37 @@ __global__ void __launch_bounds__(256) k_moment_df(const MomentArgs a) {
   for (int ci = 0; ci < D; ++ci) a.f[l.cstride * ci + o] = df[ci];
 }
 
+// update!(meanflow,flow) (Metrics.jl:239-249): P, U and (optionally) the u⊗u tensor as running averages over
+// ALL indices, ghosts included; ε = dt/(dt + T_avg + eps(T)) is formed by the caller, who owns the time vector.
+struct MeanArgs { Lay l; const float* p; const float* u; float* P; float* U; float* UU; float eps; };
+template <int D>
+__global__ void __launch_bounds__(256) k_mean_update(const MeanArgs a) {
+  pdl_entry();
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z : 0;
+  if (i < 0 || i >= l.n0 || j >= l.n1 || k >= l.n2) return;
+  const int o = l.off(i, j, k);
+  const float e = a.eps, om = 1.f - a.eps;
+  a.P[o] = e * a.p[o] + om * a.P[o];
+  float uc[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+  for (int c = 0; c < D; ++c) {
+    uc[c] = a.u[l.cstride * c + o];
+    a.U[l.cstride * c + o] = e * uc[c] + om * a.U[l.cstride * c + o];
+  }
+  if (a.UU) {
+#pragma unroll
+    for (int c = 0; c < D; ++c)
+#pragma unroll
+      for (int d = 0; d < D; ++d) {
+        float* q = a.UU + l.cstride * (c + D * d) + o;
+        *q = e * (uc[c] * uc[d]) + om * *q;
+      }
+  }
+}
+
 // Σ over the whole array of one scalar, in Float64 (sum(To,df,dims=...) Metrics.jl:132)
 struct SumArgs { Lay l; const float* a; RedWork w; Red* out; };
 template <int D>

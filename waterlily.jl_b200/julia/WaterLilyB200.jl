@@ -229,6 +229,28 @@ pressure_moment(x₀, a::B200Flow, body::B200Body) = force_moment(x₀, a, body,
 viscous_moment(x₀, a::B200Flow, body::B200Body) = force_moment(x₀, a, body, true)
 total_moment(x₀, a::B200Flow, body::B200Body) = pressure_moment(x₀, a, body) .+ viscous_moment(x₀, a, body)
 
+# ---- MeanFlow (src/Metrics.jl:205-263): device-resident running averages --------------------------------
+struct B200MeanFlow{T}
+    h::Handle; P::B200Array{T}; U::B200Array{T}; UU::Union{Nothing,B200Array{T}}; t::Vector{T}; uu_stats::Bool
+end
+function B200MeanFlow(flow::B200Flow{D,T}; t_init=time(flow), uu_stats=false) where {D,T}
+    check(flow.h, ccall((:wl_meanflow_init, LIB), Cint, (Ptr{Cvoid}, Cint), flow.h.ptr, uu_stats))
+    ng = size(flow.p); a(f, d) = B200Array{T,length(d)}(flow.h, Int32(f), Int32(0), d)
+    B200MeanFlow{T}(flow.h, a(20, ng), a(21, (ng..., D)), uu_stats ? a(22, (ng..., D, D)) : nothing, T[t_init], uu_stats)
+end
+time(m::B200MeanFlow) = m.t[end] - m.t[1]
+function update!(m::B200MeanFlow{T}, flow::B200Flow) where T
+    dt = time(flow) - m.t[end]
+    ε = length(m.t) == 1 ? one(T) : dt / (dt + time(m) + eps(T))
+    check(m.h, ccall((:wl_meanflow_update, LIB), Cint, (Ptr{Cvoid}, Cfloat), m.h.ptr, ε))
+    push!(m.t, m.t[end] + dt)
+end
+function reset!(m::B200MeanFlow{T}; t_init=0.0) where T
+    check(m.h, ccall((:wl_meanflow_init, LIB), Cint, (Ptr{Cvoid}, Cint), m.h.ptr, m.uu_stats))
+    empty!(m.t); push!(m.t, T(t_init))
+end
+copy!(flow::B200Flow, m::B200MeanFlow) = check(m.h, ccall((:wl_meanflow_copy_to_flow, LIB), Cint, (Ptr{Cvoid},), m.h.ptr))
+
 "Drop-in constructor: WaterLily's own `Simulation` with the two factories swapped."
 B200Simulation(dims, uBC, L; device=0, kw...) =
     WaterLily.Simulation(dims, uBC, L; kw..., flow_ctor=(d, u; k...) -> B200Flow(d, u; device, k...), pois_ctor=B200Poisson)
