@@ -498,7 +498,14 @@ def measure_sphere(center, R, vel, x, t, fastd2):
 
 
 def measure_flow(fl, center, R, vel, t, eps, exitBC, perdir):
-    """`measure!(a,body;t,ϵ)`: fills V, μ₀, μ₁, σ (Julia-order arrays in `fl`), then the two BC! calls."""
+    """`measure!(a,body;t,ϵ)` for the translating sphere."""
+    measure_flow_fn(fl, lambda x, fd2: measure_sphere(center, R, vel, x, t, fd2),
+                    lambda x, fd2: measure_sphere(center, R, vel, x, t, f32(0))[0], eps, exitBC, perdir)
+
+
+def measure_flow_fn(fl, meas, sdf, eps, exitBC, perdir):
+    """`measure!(a,body;t,ϵ)`: fills V, μ₀, μ₁, σ (Julia-order arrays in `fl`), then the two BC! calls.
+    `meas(x,fastd²)` is `measure(body,x,t;fastd²)`, `sdf(x,fastd²)` is `sdf(body,x,t;fastd²)` of measure_sdf!."""
     V, m0, m1, sg = fl["V"], fl["mu0"], fl["mu1"], fl["sigma"]
     n = V.shape[-1]
     V[...] = 0; m0[...] = 1; m1[...] = 0
@@ -507,11 +514,11 @@ def measure_flow(fl, center, R, vel, t, eps, exitBC, perdir):
     Vv, M0, M1, S = J(V), J(m0), J(m1), J(sg)
     loc = lambda i, I: [f32(I[k] - 1.5) - (f32(0.5) if k + 1 == i else f32(0)) for k in range(n)]   # core.jl:177
     for I in inside(sg):
-        S[I] = measure_sphere(center, R, vel, loc(0, I), t, f32(0))[0]          # measure_sdf!: the raw sdf
+        S[I] = sdf(loc(0, I), d2)                                                # measure_sdf!(a.σ,body,t;fastd²=d²)
     for I in inside(sg):
         if S[I] * S[I] < d2:
             for i in range(1, n + 1):
-                di, ni, Vi = measure_sphere(center, R, vel, loc(i, I), t, d2)
+                di, ni, Vi = meas(loc(i, I), d2)
                 di = di if abs(di) <= 0.5 else np.copysign(di, S[I])
                 Vv[I + (i,)] = Vi[i - 1]
                 M0[I + (i,)] = mu0(di, eps)
@@ -522,6 +529,122 @@ def measure_flow(fl, center, R, vel, t, eps, exitBC, perdir):
                 M0[I + (i,)] = 0
     BC(m0, (0.0,) * n, False, perdir)
     BC(V, (0.0,) * n, exitBC, perdir)
+
+
+# ---- RigidMap.jl + SetBody (Body.jl:91-107), written from the Julia source with 1-based matrices ----------
+def rotation(theta, n):
+    """`rotation(θ)` RigidMap.jl:45-49 as a dict {(i,j): R̂[i,j]} (1-based)."""
+    c, s_ = (lambda a: f32(np.cos(np.float64(a)))), (lambda a: f32(np.sin(np.float64(a))))
+    if n == 2:
+        th = f32(theta)
+        return {(1, 1): c(th), (1, 2): s_(th), (2, 1): -s_(th), (2, 2): c(th)}
+    t1, t2, t3 = (f32(v) for v in theta)
+    return {(1, 1): c(t3) * c(t2), (1, 2): c(t3) * s_(t2) * s_(t1) + s_(t3) * c(t1), (1, 3): -c(t3) * s_(t2) * c(t1) + s_(t3) * s_(t1),
+            (2, 1): -s_(t3) * c(t2), (2, 2): -s_(t3) * s_(t2) * s_(t1) + c(t3) * c(t1), (2, 3): s_(t3) * s_(t2) * c(t1) + c(t3) * s_(t1),
+            (3, 1): s_(t2), (3, 2): -c(t2) * s_(t1), (3, 3): c(t2) * c(t1)}
+
+
+def cross(w, b):
+    if len(b) == 2:                                   # ×(a::Number,b) = a*SA[-b[2],b[1]]
+        return [f32(w) * -b[1], f32(w) * b[0]]
+    return [f32(w[1]) * b[2] - f32(w[2]) * b[1], f32(w[2]) * b[0] - f32(w[0]) * b[2], f32(w[0]) * b[1] - f32(w[1]) * b[0]]
+
+
+def lib_sdf(kind, radius, minor, axis, xi):
+    """The library sdfs and their body-frame gradients (what ForwardDiff returns away from kinks)."""
+    n = len(xi)
+    if kind == "capsule":
+        y = list(xi)
+        y[axis] = xi[axis] - max(-f32(minor), min(xi[axis], f32(minor)))
+        s = f32(0)
+        for v in y:
+            s = s + v * v
+        ln = np.sqrt(s)
+        return ln - f32(radius), [v / ln for v in y]
+    if kind in ("sphere", "circle", "cylinder"):
+        s = f32(0)
+        for k in range(n):
+            if kind != "cylinder" or k != axis:
+                s = s + xi[k] * xi[k]
+        rt = np.sqrt(s)
+        return rt - f32(radius), [f32(0) if (kind == "cylinder" and k == axis) else xi[k] / rt for k in range(n)]
+    s = f32(0)                                            # torus
+    for k in range(n):
+        if k != axis:
+            s = s + xi[k] * xi[k]
+    rho = np.sqrt(s); q = rho - f32(radius)
+    ln = np.sqrt(q * q + xi[axis] * xi[axis])
+    return ln - f32(minor), [xi[k] / ln if k == axis else (q / ln) * (xi[k] / rho) for k in range(n)]
+
+
+def measure_rigid(leaf, x, fastd2):
+    """`measure(AutoBody(sdf,RigidMap),x,t;fastd²)` AutoBody.jl:29-37 with RigidMap.jl:38-41."""
+    n = len(x)
+    with np.errstate(all="ignore"):
+        R = rotation(leaf["theta"], n)
+        x0, xp = [f32(v) for v in leaf["x0"]], [f32(v) for v in leaf.get("xp") or (0,) * n]
+        r = [f32(x[k]) - x0[k] - xp[k] for k in range(n)]
+        xi = []
+        for i in range(1, n + 1):                         # m.R̂*(x-m.x₀-m.xₚ)+m.xₚ
+            a = R[i, 1] * r[0]
+            for j in range(2, n + 1):
+                a = a + R[i, j] * r[j - 1]
+            xi.append(a + xp[i - 1])
+        d, g = lib_sdf(leaf["kind"], leaf.get("radius", 0), leaf.get("minor", 0), leaf.get("axis", 2), xi)
+        zero = [f32(0)] * n
+        if d * d > fastd2 or any(np.isnan(v) for v in g):
+            return d, zero, zero
+        nn = []
+        for j in range(1, n + 1):                         # n = J'n
+            a = R[1, j] * g[0]
+            for i in range(2, n + 1):
+                a = a + R[i, j] * g[i - 1]
+            nn.append(a)
+        m = f32(0)
+        for v in nn:
+            m = m + v * v
+        m = np.sqrt(m)
+        Vc = [f32(v) for v in leaf.get("V") or (0,) * n]
+        w = leaf.get("omega", 0.0)
+        if n == 3 and np.isscalar(w):
+            w = (0.0, 0.0, w)
+        cr = cross(w, r)                                   # -J\∂ₜmap = V + ω×(x-x₀-xₚ) in exact arithmetic
+        return d / m, [v / m for v in nn], [Vc[k] + cr[k] for k in range(n)]
+
+
+def _isless(a, b):
+    return (not np.isnan(a)) and (np.isnan(b) or (np.signbit(a) and not np.signbit(b) and a == b) or a < b)
+
+
+def _tuple_less(A, B):
+    """`isless` on (d, n::SVector, V::SVector) tuples: lexicographic."""
+    fa, fb = [A[0]] + list(A[1]) + list(A[2]), [B[0]] + list(B[1]) + list(B[2])
+    for a, b in zip(fa, fb):
+        if _isless(a, b):
+            return True
+        if _isless(b, a):
+            return False
+    return False
+
+
+def measure_set(body, x, fastd2):
+    """`measure(body::SetBody,...)` Body.jl:104-107 on a nested tuple: ("leaf", {...}) | ("min"|"max", a, b) | ("neg", a)."""
+    if body[0] == "leaf":
+        return measure_rigid(body[1], x, fastd2)
+    if body[0] == "neg":
+        d, nn, V = measure_set(body[1], x, fastd2)
+        return -d, [-v for v in nn], V
+    a, b = measure_set(body[1], x, fastd2), measure_set(body[2], x, fastd2)
+    if body[0] == "min":
+        return b if _tuple_less(b, a) else a
+    return b if _tuple_less(a, b) else a
+
+
+def sdf_set(body, x, fastd2):
+    """`sdf(body,x,t;fastd²)`: AutoBody.jl:19 (raw) for a lone AutoBody, Body.jl:66 (`measure(...)[1]`) for a SetBody."""
+    if body[0] == "leaf":
+        return measure_rigid(body[1], x, f32(0))[0]
+    return measure_set(body, x, fastd2)[0]
 
 
 def pressure_force(p, center, R, vel, t):

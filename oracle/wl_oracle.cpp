@@ -589,6 +589,13 @@ struct wlo_body {
   float vel[3], acc[3], amp[3];
   float omega;
 };
+// One entry of a postfix CSG program over `AutoBody(sdf, RigidMap(x₀,θ;xₚ,V,ω))` leaves (Body.jl:91-107, RigidMap.jl:28-50).
+struct wlo_node {
+  int op;            // 0 leaf (push), 1 ∪/+ = min, 2 ∩ = max, 3 unary − (complement)
+  int kind, axis;    // leaf: 0 NoBody, 1 sphere/circle, 2 cylinder, 3 torus, 4 capsule (segment ±minor along `axis`, radius)
+  float radius, minor;
+  float x0[3], theta[3], xp[3], V[3], omega[3];   // 2D: θ and ω are theta[2], omega[2]
+};
 struct wlo_config {
   int D;
   int N[3];          // interior cells per direction
@@ -647,6 +654,113 @@ Meas measure(const wlo_body& b, int D, const real* x, real t, real fastd2) {
 inline real sdf_raw(const wlo_body& b, int D, const real* x, real t) {
   return measure(b, D, x, t, (real)0).d;                       // sdf(body,x,t) AutoBody.jl:19
 }
+inline bool is_nobody(const wlo_body& b) { return b.kind == 0; }
+inline real sdf_fill(const wlo_body& b, int D, const real* x, real t, real) { return sdf_raw(b, D, x, t); }
+
+// ---- SetBody programs over RigidMap leaves ------------------------------------------------------------
+struct Prog { int n; const wlo_node* nd; };
+
+// rotation(θ) RigidMap.jl:45-49 (2D = the z rotation), row-major
+void rotation(const wlo_node& b, int D, real R[3][3]) {
+  const real t1 = D == 3 ? (real)b.theta[0] : 0, t2 = D == 3 ? (real)b.theta[1] : 0, t3 = (real)b.theta[2];
+  const real c1 = std::cos(t1), s1 = std::sin(t1), c2 = std::cos(t2), s2 = std::sin(t2), c3 = std::cos(t3), s3 = std::sin(t3);
+  if (D == 2) { R[0][0] = c3; R[0][1] = s3; R[1][0] = -s3; R[1][1] = c3; R[0][2] = R[1][2] = R[2][0] = R[2][1] = 0; R[2][2] = 1; return; }
+  R[0][0] = c3 * c2;  R[0][1] = c3 * s2 * s1 + s3 * c1;   R[0][2] = -c3 * s2 * c1 + s3 * s1;
+  R[1][0] = -s3 * c2; R[1][1] = -s3 * s2 * s1 + c3 * c1;  R[1][2] = s3 * s2 * c1 + c3 * s1;
+  R[2][0] = s2;       R[2][1] = -c2 * s1;                 R[2][2] = c2 * c1;
+}
+
+// measure(body::AutoBody,x,t;fastd²) AutoBody.jl:29-37 for a library sdf under a RigidMap:
+// ξ = R̂(x−x₀−xₚ)+xₚ (RigidMap.jl:38), J = R̂ (:40), n = J'∇sdf(ξ), V = −J\∂ₜmap = V + ω×(x−x₀−xₚ) (:41; the
+// reference's LU solve of R̂·V' = R̂·(V+ω×r) differs from this at rounding level only).
+Meas measure_leaf(const wlo_node& b, int D, const real* x, real fastd2) {
+  Meas m; m.d = std::numeric_limits<real>::infinity();
+  for (int k = 0; k < 3; ++k) m.n[k] = m.V[k] = 0;
+  if (b.kind == 0) return m;
+  real R[3][3]; rotation(b, D, R);
+  real r[3] = {0, 0, 0}, xi[3] = {0, 0, 0}, g[3] = {0, 0, 0};
+  for (int k = 0; k < D; ++k) r[k] = x[k] - (real)b.x0[k] - (real)b.xp[k];
+  for (int k = 0; k < D; ++k) {
+    real a = R[k][0] * r[0];
+    for (int q = 1; q < D; ++q) a += R[k][q] * r[q];
+    xi[k] = a + (real)b.xp[k];
+  }
+  real d;
+  if (b.kind == 1) {
+    real s = 0; for (int k = 0; k < D; ++k) s += xi[k] * xi[k];
+    real rt = std::sqrt(s); d = rt - (real)b.radius;
+    for (int k = 0; k < D; ++k) g[k] = xi[k] / rt;
+  } else if (b.kind == 2) {
+    real s = 0; for (int k = 0; k < D; ++k) if (k != b.axis) s += xi[k] * xi[k];
+    real rt = std::sqrt(s); d = rt - (real)b.radius;
+    for (int k = 0; k < D; ++k) g[k] = k == b.axis ? (real)0 : xi[k] / rt;
+  } else if (b.kind == 3) {
+    real s = 0; for (int k = 0; k < D; ++k) if (k != b.axis) s += xi[k] * xi[k];
+    real rho = std::sqrt(s), q = rho - (real)b.radius;
+    real len = std::sqrt(q * q + xi[b.axis] * xi[b.axis]); d = len - (real)b.minor;
+    for (int k = 0; k < D; ++k) g[k] = k == b.axis ? xi[k] / len : (q / len) * (xi[k] / rho);
+  } else {                                                     // capsule: √Σ(ξ − clamp(ξ_axis,±h)ê)² − r
+    real y[3] = {xi[0], xi[1], xi[2]};
+    const real h = (real)b.minor;
+    y[b.axis] = xi[b.axis] - std::max(-h, std::min(xi[b.axis], h));
+    real s = 0; for (int k = 0; k < D; ++k) s += y[k] * y[k];
+    real len = std::sqrt(s); d = len - (real)b.radius;
+    for (int k = 0; k < D; ++k) g[k] = y[k] / len;
+  }
+  m.d = d;
+  if (d * d > fastd2) return m;                                // AutoBody.jl:31
+  for (int k = 0; k < D; ++k) if (std::isnan(g[k])) return m;  // AutoBody.jl:33
+  real n[3] = {0, 0, 0};
+  for (int k = 0; k < D; ++k) {                                // n = J'n AutoBody.jl:35
+    real a = R[0][k] * g[0];
+    for (int q = 1; q < D; ++q) a += R[q][k] * g[q];
+    n[k] = a;
+  }
+  real mm = 0; for (int k = 0; k < D; ++k) mm += n[k] * n[k];
+  mm = std::sqrt(mm);
+  m.d = d / mm;
+  for (int k = 0; k < D; ++k) m.n[k] = n[k] / mm;
+  const float* w = b.omega;
+  real cr[3];
+  if (D == 2) { cr[0] = (real)w[2] * -r[1]; cr[1] = (real)w[2] * r[0]; cr[2] = 0; }          // ×(a::Number,b) RigidMap.jl:44
+  else { cr[0] = (real)w[1] * r[2] - (real)w[2] * r[1]; cr[1] = (real)w[2] * r[0] - (real)w[0] * r[2]; cr[2] = (real)w[0] * r[1] - (real)w[1] * r[0]; }
+  for (int k = 0; k < D; ++k) m.V[k] = (real)b.V[k] + cr[k];
+  return m;
+}
+
+// isless on floats / tuples / vectors (Base): NaN is greatest, −0.0 < 0.0, lexicographic
+inline bool fless(real a, real b) { return !std::isnan(a) && (std::isnan(b) || (std::signbit(a) && !std::signbit(b) && a == b) || a < b); }
+inline bool fequal(real a, real b) { return (std::isnan(a) && std::isnan(b)) || (a == b && std::signbit(a) == std::signbit(b)); }
+bool meas_less(const Meas& a, const Meas& b, int D) {
+  if (fless(a.d, b.d)) return true;
+  if (!fequal(a.d, b.d)) return false;
+  for (int k = 0; k < D; ++k) { if (fless(a.n[k], b.n[k])) return true; if (fless(b.n[k], a.n[k])) return false; }
+  for (int k = 0; k < D; ++k) { if (fless(a.V[k], b.V[k])) return true; if (fless(b.V[k], a.V[k])) return false; }
+  return false;
+}
+
+// measure(body::SetBody,x,t;fastd²) Body.jl:104-107: min / max of the (d,n,V) tuples, (−d,−n,V) for the complement
+Meas measure(const Prog& p, int D, const real* x, real, real fastd2) {
+  Meas st[8]; int sp = 0;
+  for (int i = 0; i < p.n; ++i) {
+    const wlo_node& b = p.nd[i];
+    if (b.op == 0) st[sp++] = measure_leaf(b, D, x, fastd2);
+    else if (b.op == 3) { Meas& a = st[sp - 1]; a.d = -a.d; for (int k = 0; k < D; ++k) a.n[k] = -a.n[k]; }
+    else {
+      const Meas bb = st[--sp]; Meas& a = st[sp - 1];
+      if (b.op == 1) { if (meas_less(bb, a, D)) a = bb; }      // min(x,y) = isless(y,x) ? y : x
+      else           { if (meas_less(a, bb, D)) a = bb; }      // max(x,y) = isless(x,y) ? y : x
+    }
+  }
+  return st[0];
+}
+inline bool is_nobody(const Prog& p) { return p.n == 0 || (p.n == 1 && p.nd[0].kind == 0); }
+// measure_sdf!(σ,body,t;fastd²) Body.jl:74: a lone AutoBody gives the raw sdf (AutoBody.jl:19), a SetBody goes
+// through measure(...)[1] (Body.jl:66), i.e. the gradient-normalised distance inside the band.
+inline real sdf_fill(const Prog& p, int D, const real* x, real t, real fastd2) {
+  if (p.n == 1) return measure_leaf(p.nd[0], D, x, (real)0).d;
+  return measure(p, D, x, t, fastd2).d;
+}
 
 const real PI_R = (real)3.14159265358979323846;
 // kernels Body.jl:54-60
@@ -676,8 +790,9 @@ struct Sim {
 };
 
 // `measure!(a,body;t,ϵ)` Body.jl:28-51
-void measure_flow(Sim& s, const wlo_body& b, real t, real eps) {
-  if (b.kind == 0) return;                                     // Body.jl:83
+template <class B>
+void measure_flow(Sim& s, const B& b, real t, real eps) {
+  if (is_nobody(b)) return;                                    // Body.jl:83
   const Grid& g = s.g; const int D = g.D;
   std::fill(s.V.begin(), s.V.end(), (real)0);
   std::fill(s.mu0.begin(), s.mu0.end(), (real)1);
@@ -686,7 +801,7 @@ void measure_flow(Sim& s, const wlo_body& b, real t, real eps) {
   real* sg = s.sigma.data();
   loop(g, inside(g), [&](long I, int i, int j, int k) {       // measure_sdf! Body.jl:74
     real x[3] = {(real)i - (real)0.5, (real)j - (real)0.5, (real)k - (real)0.5};
-    sg[I] = sdf_raw(b, D, x, t);
+    sg[I] = sdf_fill(b, D, x, t, d2);
   });
   loop(g, inside(g), [&](long I, int i, int j, int k) {
     if (sg[I] * sg[I] < d2) {
@@ -709,7 +824,8 @@ void measure_flow(Sim& s, const wlo_body& b, real t, real eps) {
 }
 
 // `pressure_force(p,df,body,t)` Metrics.jl:116-133 (clobbers f, returns Float64 sums)
-void pressure_force(Sim& s, const wlo_body& b, real t, double* out) {
+template <class B>
+void pressure_force(Sim& s, const B& b, real t, double* out) {
   const Grid& g = s.g; const int D = g.D;
   std::fill(s.f.begin(), s.f.end(), (real)0);
   loop(g, inside(g), [&](long I, int i, int j, int k) {
@@ -732,7 +848,8 @@ inline real dudx(const Grid& g, const real* u, int i, int j, long I) {
   return (ui[I + g.s[j]] + ui[I + g.s[j] + g.s[i]] - ui[I - g.s[j]] - ui[I - g.s[j] + g.s[i]]) / 4;
 }
 // `viscous_force(u,ν,df,body,t)` Metrics.jl:140-152: df[I,:] = -2ν·S(I,u)·nds over inside_u(u) (clobbers f)
-void viscous_force(Sim& s, const wlo_body& b, real t, double* out) {
+template <class B>
+void viscous_force(Sim& s, const B& b, real t, double* out) {
   const Grid& g = s.g; const int D = g.D;
   std::fill(s.f.begin(), s.f.end(), (real)0);
   const real m2nu = -2 * (real)s.cfg.nu;
@@ -761,7 +878,8 @@ void viscous_force(Sim& s, const wlo_body& b, real t, double* out) {
 
 // `pressure_moment(x₀,p,df,body,t)` / `viscous_moment(x₀,u,ν,df,body,t)` Metrics.jl:168-192 with x₀ in T.
 // 3D: cross(a,b); 2D: the scalar a₁b₂-a₂b₁ broadcast to both components of df (StaticArrays).
-void force_moment(Sim& s, const wlo_body& b, real t, const real* x0, int viscous, double* out) {
+template <class B>
+void force_moment(Sim& s, const B& b, real t, const real* x0, int viscous, double* out) {
   const Grid& g = s.g; const int D = g.D;
   std::fill(s.f.begin(), s.f.end(), (real)0);
   const real m2nu = -2 * (real)s.cfg.nu;
@@ -985,6 +1103,20 @@ void wlo_meanflow_update(void* h, real* P, real* U, real* UU, real eps) {
           real& q = UU[I + g.cells * (i + (long)D * j)];
           q = eps * (s->u[g.cells * i + I] * s->u[g.cells * j + I]) + om * q;
         }
+}
+void wlo_measure_csg(void* h, const wlo_node* nd, int n, double eps) {
+  Sim* s = (Sim*)h; s->eps = (real)eps;
+  measure_flow(*s, Prog{n, nd}, (real)0, (real)eps);
+}
+void wlo_pressure_force_csg(void* h, const wlo_node* nd, int n, double* out) { pressure_force(*(Sim*)h, Prog{n, nd}, (real)0, out); }
+void wlo_viscous_force_csg(void* h, const wlo_node* nd, int n, double* out) { viscous_force(*(Sim*)h, Prog{n, nd}, (real)0, out); }
+void wlo_force_moment_csg(void* h, const wlo_node* nd, int n, const double* x0, int viscous, double* out) {
+  real x[3] = {(real)x0[0], (real)x0[1], (real)x0[2]};
+  force_moment(*(Sim*)h, Prog{n, nd}, (real)0, x, viscous, out);
+}
+void wlo_measure_point_csg(const wlo_node* nd, int n, int D, const real* x, real fastd2, real* d, real* nn, real* V) {
+  Meas m = measure(Prog{n, nd}, D, x, (real)0, fastd2);
+  *d = m.d; for (int k = 0; k < 3; ++k) { nn[k] = m.n[k]; V[k] = m.V[k]; }
 }
 void wlo_force_moment(void* h, const wlo_body* b, double t, const double* x0, int viscous, double* out) {
   real x[3] = {(real)x0[0], (real)x0[1], (real)x0[2]};

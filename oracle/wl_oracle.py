@@ -41,6 +41,72 @@ def make_body(kind="none", center=(0, 0, 0), radius=0.0, minor=0.0, axis=2, vel=
                 v3(amp), float(omega))
 
 
+class Node(C.Structure):
+    """One entry of a postfix SetBody program over `AutoBody(sdf, RigidMap(x₀,θ;xₚ,V,ω))` leaves
+    (src/Body.jl:91-107, src/RigidMap.jl:28-50); layout of `wlo_node`."""
+    _fields_ = [("op", C.c_int), ("kind", C.c_int), ("axis", C.c_int), ("radius", C.c_float), ("minor", C.c_float),
+                ("x0", C.c_float * 3), ("theta", C.c_float * 3), ("xp", C.c_float * 3), ("V", C.c_float * 3),
+                ("omega", C.c_float * 3)]
+
+
+LEAF_KINDS = dict(KINDS, capsule=4)
+
+
+class CsgBody:
+    """`AutoBody(sdf, RigidMap(...))` leaves combined with `+ ∪ ∩ −` (lazy `SetBody`, Body.jl:91-101) as a postfix list."""
+
+    def __init__(self, prog):
+        self.prog = [dict(p) for p in prog]
+
+    @classmethod
+    def leaf(cls, kind, x0, theta=0.0, *, xp=None, V=None, omega=0.0, radius=0.0, minor=0.0, axis=2):
+        return cls([dict(op=0, kind=LEAF_KINDS[kind], axis=axis, radius=radius, minor=minor, x0=x0, theta=theta,
+                         xp=xp, V=V, omega=omega)])
+
+    kind = property(lambda self: 1)                      # "not NoBody" for sim_step's remeasure test
+    __add__ = __or__ = lambda a, b: CsgBody(a.prog + b.prog + [dict(op=1)])
+    __and__ = lambda a, b: CsgBody(a.prog + b.prog + [dict(op=2)])
+    __neg__ = lambda a: CsgBody(a.prog + [dict(op=3)])
+    __sub__ = lambda a, b: a & (-b)
+
+    def setmap(self, **kw):
+        """`setmap(body; x₀, θ, xₚ, V, ω)` (RigidMap.jl:54-56): every leaf gets the new map fields."""
+        names = {"x0": "x0", "x₀": "x0", "theta": "theta", "θ": "theta", "xp": "xp", "xₚ": "xp", "V": "V", "omega": "omega", "ω": "omega"}
+        out = CsgBody(self.prog)
+        for p in out.prog:
+            if p["op"] == 0:
+                for k, v in kw.items():
+                    p[names[k]] = v
+        return out
+
+    def nodes(self):
+        def v3(a, rot=False):
+            if a is None:
+                a = ()
+            if np.isscalar(a):
+                a = (0.0, 0.0, a) if rot else (a,)       # 2D: θ and ω are rotations about z
+            a = [float(x) for x in a]
+            return (C.c_float * 3)(*(a + [0.0] * (3 - len(a))))
+        arr = (Node * len(self.prog))()
+        for q, p in zip(arr, self.prog):
+            q.op = p["op"]
+            if p["op"] == 0:
+                q.kind, q.axis, q.radius, q.minor = p["kind"], p["axis"], p["radius"], p["minor"]
+                q.x0, q.theta, q.xp, q.V, q.omega = v3(p["x0"]), v3(p["theta"], True), v3(p["xp"]), v3(p["V"]), v3(p["omega"], True)
+        return arr, len(self.prog)
+
+
+def measure_point_csg(body, x, fastd2=np.inf, dtype=np.float32):
+    """`measure(body,x,t;fastd²)` for a CsgBody at one point -> (d, n, V)."""
+    lib = load(dtype)
+    D = len(x)
+    xx = (lib.real * 3)(*(list(map(float, x)) + [0.0] * (3 - D)))
+    d, n, V = lib.real(), (lib.real * 3)(), (lib.real * 3)()
+    arr, k = body.nodes()
+    lib.wlo_measure_point_csg(arr, k, D, xx, float(fastd2), C.byref(d), n, V)
+    return d.value, np.array(n[:D]), np.array(V[:D])
+
+
 class Config(C.Structure):
     _fields_ = [("D", C.c_int), ("N", C.c_int * 3), ("perdir", C.c_int * 3), ("exitBC", C.c_int),
                 ("scheme", C.c_int), ("nu", C.c_float), ("dt0", C.c_float), ("uBC", C.c_float * 3),
@@ -125,6 +191,12 @@ def load(dtype=np.float32, fast_path=None):
     lib.wlo_mu1.restype = R
     lib.wlo_mu1.argtypes = [R, R]
     lib.wlo_measure_point.argtypes = [C.POINTER(Body), C.c_int, RP, R, R, RP, RP, RP]
+    NP, DP = C.POINTER(Node), C.POINTER(C.c_double)
+    lib.wlo_measure_csg.argtypes = [C.c_void_p, NP, C.c_int, C.c_double]
+    lib.wlo_pressure_force_csg.argtypes = [C.c_void_p, NP, C.c_int, DP]
+    lib.wlo_viscous_force_csg.argtypes = [C.c_void_p, NP, C.c_int, DP]
+    lib.wlo_force_moment_csg.argtypes = [C.c_void_p, NP, C.c_int, DP, C.c_int, DP]
+    lib.wlo_measure_point_csg.argtypes = [NP, C.c_int, C.c_int, RP, R, RP, RP, RP]
     _LIBS[key] = lib
     return lib
 
@@ -158,7 +230,7 @@ class OracleSim:
         self.n = []
         if u0 is not None:
             self.apply_ic(u0)
-        self.lib.wlo_measure(self.h, C.byref(self.body), 0.0, float(eps))
+        self._measure(0.0)
         self.nlevels = 0
         if build_poisson:
             self.nlevels = self.lib.wlo_build_poisson(self.h)
@@ -218,8 +290,15 @@ class OracleSim:
         """`measure!(sim,t=sum(Δt))` (WaterLily.jl:146-149)."""
         if t is None:
             t = float(np.sum(np.asarray(self.dts, dtype=self.dtype), dtype=self.dtype))
-        self.lib.wlo_measure(self.h, C.byref(self.body), float(t), float(self.eps))
+        self._measure(t)
         self.lib.wlo_update_poisson(self.h)
+
+    def _measure(self, t):
+        if isinstance(self.body, CsgBody):
+            arr, n = self.body.nodes()
+            self.lib.wlo_measure_csg(self.h, arr, n, float(self.eps))
+        else:
+            self.lib.wlo_measure(self.h, C.byref(self.body), float(t), float(self.eps))
 
     def mom_step(self, U1=None, acc0=None, acc1=None):
         def arr(v):
@@ -261,12 +340,20 @@ class OracleSim:
     def pressure_force(self, t=None):
         out = (C.c_double * 3)()
         t = self.time() if t is None else t
+        if isinstance(self.body, CsgBody):
+            arr, n = self.body.nodes()
+            self.lib.wlo_pressure_force_csg(self.h, arr, n, out)
+            return np.array(out[: self.D])
         self.lib.wlo_pressure_force(self.h, C.byref(self.body), float(t), out)
         return np.array(out[: self.D])
 
     def viscous_force(self, t=None):
         out = (C.c_double * 3)()
         t = self.time() if t is None else t
+        if isinstance(self.body, CsgBody):
+            arr, n = self.body.nodes()
+            self.lib.wlo_viscous_force_csg(self.h, arr, n, out)
+            return np.array(out[: self.D])
         self.lib.wlo_viscous_force(self.h, C.byref(self.body), float(t), out)
         return np.array(out[: self.D])
 
@@ -275,6 +362,10 @@ class OracleSim:
         out = (C.c_double * 3)()
         t = self.time() if t is None else t
         xx = (C.c_double * 3)(*(list(x0) + [0.0] * (3 - len(x0))))
+        if isinstance(self.body, CsgBody):
+            arr, n = self.body.nodes()
+            self.lib.wlo_force_moment_csg(self.h, arr, n, xx, int(viscous), out)
+            return np.array(out[: self.D])
         self.lib.wlo_force_moment(self.h, C.byref(self.body), float(t), xx, int(viscous), out)
         return np.array(out[: self.D])
 
