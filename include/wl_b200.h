@@ -71,6 +71,19 @@ typedef struct wl_body {
   float omega;
 } wl_body;
 
+/* One entry of a postfix `SetBody` program (src/Body.jl:91-107) whose leaves are library sdfs under a
+ * `RigidMap(x0, theta; xp, V, omega)` (src/RigidMap.jl:28-50).  `a + b`, `a ∪ b` -> a b {op 1}; `a ∩ b` -> a b {op 2};
+ * `-a` -> a {op 3}; `a - b` -> a b {op 3} {op 2}.  At most WL_CSG_MAX entries.  In 2D theta[2] / omega[2] are the
+ * scalar angle / angular velocity.  `setmap(body; ...)` (RigidMap.jl:54-56) = rewrite the fields and measure again. */
+#define WL_CSG_MAX 8
+typedef struct wl_body_node {
+  int32_t op;           /* 0 leaf, 1 union (min), 2 intersection (max), 3 complement                             */
+  int32_t kind;         /* leaf: 0 NoBody, 1 sphere/circle, 2 cylinder, 3 torus, 4 capsule (segment +-minor on `axis`) */
+  int32_t axis;
+  float radius, minor;
+  float x0[3], theta[3], xp[3], V[3], omega[3];
+} wl_body_node;
+
 /* Fields a caller can read or write (sim.flow.* and sim.pois.levels[l].*). */
 enum wl_field {
   WL_U = 0, WL_U0 = 1, WL_F = 2, WL_P = 3, WL_SIGMA = 4, WL_V = 5, WL_MU0 = 6, WL_MU1 = 7,
@@ -158,6 +171,14 @@ int wl_viscous_force(wl_sim* s, const wl_body* body, double t, double out[3]);
  *      x₀ is converted to Float32 (the reference promotes to the type of x₀).  In 2D both components of
  *      `out` hold the scalar moment, as the reference's broadcast leaves them.                   */
 int wl_force_moment(wl_sim* s, const wl_body* body, double t, const double x0[3], int viscous, double out[3]);
+
+/* The same four calls for a `SetBody` / `RigidMap` body given as a postfix program of `n` nodes:
+ * `measure!(flow, body; ϵ)` (src/Body.jl:28-51 with :104-107 and src/AutoBody.jl:29-37 per leaf), `pressure_force`,
+ * `viscous_force` and the moments (src/Metrics.jl:116-192).  The maps carry no time: the caller rewrites the nodes. */
+int wl_measure_csg(wl_sim* s, const wl_body_node* nodes, int32_t n, double eps);
+int wl_pressure_force_csg(wl_sim* s, const wl_body_node* nodes, int32_t n, double out[3]);
+int wl_viscous_force_csg(wl_sim* s, const wl_body_node* nodes, int32_t n, double out[3]);
+int wl_force_moment_csg(wl_sim* s, const wl_body_node* nodes, int32_t n, const double x0[3], int viscous, double out[3]);
 
 /* ---- running statistics: MeanFlow (src/Metrics.jl:205-263).  wl_meanflow_init = the constructor / reset!
  *      (P, U and, with uu_stats, UU allocated and zeroed); wl_meanflow_update = the three loops of update!

@@ -276,6 +276,63 @@ def test_meanflow(wl, dims, perdir):
     assert float(np.abs(mg.U).max()) == 0.0 and len(mg.t) == 1
 
 
+CSG_CASES = [
+    ((32, 24), lambda L: L("circle", (12.3, 11.7), 0.0, radius=4.2, V=(0.25, 0.0), omega=0.1), False, ()),
+    ((32, 24), lambda L: L("capsule", (13.5, 12.2), 0.6, radius=1.6, minor=5.0, axis=0, xp=(0.5, 0.0), omega=-0.05)
+                         + L("circle", (20.0, 8.0), 0.0, radius=3.0), True, (2,)),
+    ((32, 24), lambda L: L("circle", (14.0, 12.0), 0.3, radius=7.0) - L("circle", (14.0, 12.0), 0.3, radius=3.5), False, ()),
+    ((24, 16, 16), lambda L: L("torus", (10.0, 8.0, 8.0), (0.3, -0.2, 0.5), radius=4.0, minor=1.6, axis=2, V=(0.1, 0, 0),
+                               omega=(0.0, 0.02, -0.05)) & -L("sphere", (13.0, 8.0, 8.0), (0, 0, 0), radius=2.5), False, (3,)),
+    ((24, 16, 16), lambda L: L("cylinder", (10.0, 8.0, 8.0), (0.0, 0.4, 0.0), radius=3.0, axis=2)
+                             & L("capsule", (10.0, 8.0, 8.0), (0, 0, 0), radius=5.0, minor=2.0, axis=1), True, ()),
+]
+
+
+@pytest.mark.parametrize("dims,mk,exitBC,perdir", CSG_CASES)
+def test_csg_rigid_bodies(wl, dims, mk, exitBC, perdir):
+    """SetBody programs over RigidMap leaves (src/Body.jl:91-107, src/RigidMap.jl:28-50): device measure!, remeasured
+    stepping with `setmap` between steps (the loop of RigidMap.jl:17-26), forces and moments: CUDA vs oracle."""
+    D = len(dims)
+    kw = dict(nu=0.05, perdir=perdir, exitBC=exitBC)
+    U = (1.0,) + (0.0,) * (D - 1)
+    sim = wl.Simulation(dims, U, 8.0, body=mk(wl.RigidBody), **kw)
+    ref = wo.OracleSim(dims, U, 8.0, body=mk(wo.CsgBody.leaf), **kw)
+    inner = tuple(slice(1, -1) for _ in dims)
+    close(sim.flow.sigma[inner], ref.field("sigma")[inner], 2e-6, "σ")
+    assert int((np.abs(ref.field("mu1")) > 0).sum()) > 50
+    for nm in ("V", "mu0", "mu1"):
+        close(sim.download(nm), ref.field(nm), 2e-6, nm)
+    for n in range(3):
+        shift = tuple(0.05 * (n + 1) for _ in range(D))
+        for s_ in (sim, ref):                                     # setmap(body; x₀, θ) then sim_step!(remeasure=true)
+            b0 = s_.body.prog[0]
+            th = b0["theta"]
+            th = th + 0.02 if np.isscalar(th) else tuple(t + 0.02 for t in th)
+            s_.body = s_.body.setmap(theta=th, x0=tuple(c + d for c, d in zip(b0["x0"], shift)))
+        step_both(sim, ref, 1, remeasure=True)
+    check_state(sim, ref, utol=2e-5, ptol=1e-4)
+    for nm in ("V", "mu0", "mu1"):
+        close(sim.download(nm), ref.field(nm), 2e-6, nm + " after setmap")
+    f_gpu, f_ref = sim.pressure_force(), ref.pressure_force()
+    assert np.allclose(f_gpu, f_ref, rtol=1e-4, atol=1e-4 * np.abs(f_ref).max()), (f_gpu, f_ref)
+    v_gpu, v_ref = sim.viscous_force(), ref.viscous_force()
+    assert np.allclose(v_gpu, v_ref, rtol=1e-4, atol=1e-4 * np.abs(v_ref).max()), (v_gpu, v_ref)
+    x0 = tuple(d / 3.0 for d in dims)
+    for visc in (False, True):
+        m_gpu, m_ref = sim.moment(x0, visc), ref.moment(x0, visc)
+        assert np.allclose(m_gpu, m_ref, rtol=1e-4, atol=1e-4 * np.abs(m_ref).max()), (visc, m_gpu, m_ref)
+
+
+def test_csg_program_validation(wl):
+    """Malformed programs are rejected on the host with WL_ERR_INVALID, never launched."""
+    good = wl.RigidBody("circle", (8, 8), 0.0, radius=3)
+    sim = wl.Simulation((16, 16), (1.0, 0.0), 4.0, body=good)
+    for bad in ([dict(op=1)], good.prog + good.prog, good.prog + [dict(op=7)], good.prog * 5 + [dict(op=1)] * 4):
+        sim.body = wl.RigidBody(prog=bad)
+        with pytest.raises(wl.WaterLilyB200Error):
+            sim.measure()
+
+
 def _golden_cases():
     import os, sys
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))

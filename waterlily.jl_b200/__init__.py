@@ -35,7 +35,8 @@ ABI_SYMBOLS = [
     "wl_create", "wl_destroy", "wl_last_error", "wl_version", "wl_field_dims", "wl_download",
     "wl_upload", "wl_nlevels", "wl_finish_ic", "wl_measure_body", "wl_set_body_coeffs",
     "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_poisson_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
-    "wl_cfl", "wl_pressure_force", "wl_viscous_force", "wl_force_moment", "wl_meanflow_init", "wl_meanflow_update", "wl_meanflow_copy_to_flow", "wl_sync", "wl_launch_count", "wl_enable_timing",
+    "wl_cfl", "wl_pressure_force", "wl_viscous_force", "wl_force_moment", "wl_measure_csg", "wl_pressure_force_csg",
+    "wl_viscous_force_csg", "wl_force_moment_csg", "wl_meanflow_init", "wl_meanflow_update", "wl_meanflow_copy_to_flow", "wl_sync", "wl_launch_count", "wl_enable_timing",
     "wl_last_phase_times", "wl_debug_op", "wl_prof_begin", "wl_prof_end", "wl_event_record",
     "wl_event_elapsed_ms", "wl_create_slab", "wl_nccl_unique_id", "wl_slab_info", "wl_halo_stats", "wl_halo_transport", "wl_halo_timing",
 ]
@@ -56,6 +57,13 @@ class WLBody(C.Structure):
     _fields_ = [("kind", C.c_int32), ("axis", C.c_int32), ("center", C.c_float * 3), ("radius", C.c_float),
                 ("minor", C.c_float), ("vel", C.c_float * 3), ("acc", C.c_float * 3), ("amp", C.c_float * 3),
                 ("omega", C.c_float)]
+
+
+class WLNode(C.Structure):
+    """`wl_body_node` (include/wl_b200.h)."""
+    _fields_ = [("op", C.c_int32), ("kind", C.c_int32), ("axis", C.c_int32), ("radius", C.c_float), ("minor", C.c_float),
+                ("x0", C.c_float * 3), ("theta", C.c_float * 3), ("xp", C.c_float * 3), ("V", C.c_float * 3),
+                ("omega", C.c_float * 3)]
 
 
 class WLStepInfo(C.Structure):
@@ -114,6 +122,11 @@ def load_library(path=None):
     lib.wl_pressure_force.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3)]
     lib.wl_viscous_force.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3)]
     lib.wl_force_moment.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3), I, C.POINTER(C.c_double * 3)]
+    D3 = C.POINTER(C.c_double * 3)
+    lib.wl_measure_csg.argtypes = [P, C.POINTER(WLNode), I, C.c_double]
+    lib.wl_pressure_force_csg.argtypes = [P, C.POINTER(WLNode), I, D3]
+    lib.wl_viscous_force_csg.argtypes = [P, C.POINTER(WLNode), I, D3]
+    lib.wl_force_moment_csg.argtypes = [P, C.POINTER(WLNode), I, D3, I, D3]
     lib.wl_meanflow_init.argtypes = [P, I]
     lib.wl_meanflow_update.argtypes = [P, F]
     lib.wl_meanflow_copy_to_flow.argtypes = [P]
@@ -193,6 +206,61 @@ class AutoBody:
     @property
     def kind(self):
         return self.c.kind
+
+
+LEAF_KINDS = dict(none=0, sphere=1, circle=1, cylinder=2, torus=3, capsule=4)
+
+
+class RigidBody:
+    """`AutoBody(sdf, RigidMap(x₀, θ; xₚ, V, ω))` (src/RigidMap.jl:28-50) for a library sdf, and the lazy `SetBody`
+    algebra `+ | & -` over such leaves (src/Body.jl:91-101), held as the postfix program `wl_measure_csg` takes.
+    `setmap(...)` (RigidMap.jl:54-56) returns a copy with every leaf's map fields replaced."""
+
+    def __init__(self, kind=None, x0=None, theta=0.0, *, xp=None, V=None, omega=0.0, radius=0.0, minor=0.0, axis=2, prog=None):
+        if prog is not None:
+            self.prog = [dict(p) for p in prog]
+        else:
+            self.prog = [dict(op=0, kind=LEAF_KINDS[kind], axis=int(axis), radius=float(radius), minor=float(minor),
+                              x0=x0, theta=theta, xp=xp, V=V, omega=omega)]
+
+    kind = property(lambda self: 0 if (len(self.prog) == 1 and self.prog[0].get("kind", 1) == 0) else 1)
+
+    def __add__(self, other):
+        return RigidBody(prog=self.prog + other.prog + [dict(op=1)])
+    __or__ = __add__
+
+    def __and__(self, other):
+        return RigidBody(prog=self.prog + other.prog + [dict(op=2)])
+
+    def __neg__(self):
+        return RigidBody(prog=self.prog + [dict(op=3)])
+
+    def __sub__(self, other):
+        return self & (-other)
+
+    def setmap(self, **kw):
+        names = {"x0": "x0", "x₀": "x0", "theta": "theta", "θ": "theta", "xp": "xp", "xₚ": "xp", "V": "V", "omega": "omega", "ω": "omega"}
+        out = RigidBody(prog=self.prog)
+        for p in out.prog:
+            if p["op"] == 0:
+                for k, v in kw.items():
+                    p[names[k]] = v
+        return out
+
+    def nodes(self):
+        def v3(a, rot=False):
+            if a is None:
+                a = ()
+            if np.isscalar(a):
+                a = (0.0, 0.0, a) if rot else (a,)       # 2D: θ and ω are rotations about z
+            return _v3f([float(x) for x in a])
+        arr = (WLNode * len(self.prog))()
+        for q, p in zip(arr, self.prog):
+            q.op = p["op"]
+            if p["op"] == 0:
+                q.kind, q.axis, q.radius, q.minor = p["kind"], p["axis"], p["radius"], p["minor"]
+                q.x0, q.theta, q.xp, q.V, q.omega = v3(p["x0"]), v3(p["theta"], True), v3(p["xp"]), v3(p["V"]), v3(p["omega"], True)
+        return arr, len(self.prog)
 
 
 def NoBody():
@@ -301,7 +369,7 @@ class Simulation:
         self.last_info = None
         if u0 is not None:
             self.apply_ic(u0)
-        self._check(self.lib.wl_measure_body(self.h, C.byref(self.body.c), 0.0, float(eps)))   # measure!(flow,body;ϵ)
+        self._measure(0.0)                                                                      # measure!(flow,body;ϵ)
         self._check(self.lib.wl_build_poisson(self.h))                                        # pois_ctor(flow)
         self.nlevels = self.lib.wl_nlevels(self.h)
         self.flow = B200Flow(self)
@@ -370,8 +438,15 @@ class Simulation:
         """`measure!(sim,t=sum(Δt))` = measure!(flow,body) + update!(pois) (src/WaterLily.jl:146-149)."""
         if t is None:
             t = float(np.sum(np.asarray(self._dts, np.float32), dtype=np.float32))
-        self._check(self.lib.wl_measure_body(self.h, C.byref(self.body.c), float(t), float(self.eps)))
+        self._measure(t)
         self._check(self.lib.wl_update_poisson(self.h))
+
+    def _measure(self, t):
+        if isinstance(self.body, RigidBody):
+            arr, n = self.body.nodes()
+            self._check(self.lib.wl_measure_csg(self.h, arr, n, float(self.eps)))
+        else:
+            self._check(self.lib.wl_measure_body(self.h, C.byref(self.body.c), float(t), float(self.eps)))
 
     def set_body_coeffs(self, mu0=None, mu1=None, V=None, sdf=None):
         """Upload host-measured BDIM coefficients (arbitrary AutoBody closures), then update!(pois)."""
@@ -440,14 +515,22 @@ class Simulation:
         """`pressure_force(sim)` (src/Metrics.jl:116-133)."""
         out = (C.c_double * 3)()
         t = self.time() if t is None else t
-        self._check(self.lib.wl_pressure_force(self.h, C.byref(self.body.c), float(t), C.byref(out)))
+        if isinstance(self.body, RigidBody):
+            arr, n = self.body.nodes()
+            self._check(self.lib.wl_pressure_force_csg(self.h, arr, n, C.byref(out)))
+        else:
+            self._check(self.lib.wl_pressure_force(self.h, C.byref(self.body.c), float(t), C.byref(out)))
         return np.array(out[: self.D])
 
     def viscous_force(self, t=None):
         """`viscous_force(sim)` (src/Metrics.jl:140-152)."""
         out = (C.c_double * 3)()
         t = self.time() if t is None else t
-        self._check(self.lib.wl_viscous_force(self.h, C.byref(self.body.c), float(t), C.byref(out)))
+        if isinstance(self.body, RigidBody):
+            arr, n = self.body.nodes()
+            self._check(self.lib.wl_viscous_force_csg(self.h, arr, n, C.byref(out)))
+        else:
+            self._check(self.lib.wl_viscous_force(self.h, C.byref(self.body.c), float(t), C.byref(out)))
         return np.array(out[: self.D])
 
     def moment(self, x0, viscous=False, t=None):
@@ -455,7 +538,11 @@ class Simulation:
         out = (C.c_double * 3)()
         t = self.time() if t is None else t
         xx = (C.c_double * 3)(*(list(x0) + [0.0] * (3 - len(x0))))
-        self._check(self.lib.wl_force_moment(self.h, C.byref(self.body.c), float(t), C.byref(xx), int(viscous), C.byref(out)))
+        if isinstance(self.body, RigidBody):
+            arr, n = self.body.nodes()
+            self._check(self.lib.wl_force_moment_csg(self.h, arr, n, C.byref(xx), int(viscous), C.byref(out)))
+        else:
+            self._check(self.lib.wl_force_moment(self.h, C.byref(self.body.c), float(t), C.byref(xx), int(viscous), C.byref(out)))
         return np.array(out[: self.D])
 
     def total_moment(self, x0, t=None):

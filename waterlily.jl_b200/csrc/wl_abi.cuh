@@ -465,25 +465,40 @@ int wl_finish_ic(wl_sim* s, const float uBC[3]) {
   return check_async(s, "wl_finish_ic");
 }
 
-int wl_measure_body(wl_sim* s, const wl_body* body, double t, double eps) {
-  if (!s || !body) return WL_ERR_INVALID;
-  if (body->kind == 0) return WL_OK;                 // NoBody: measure! is a no-op (Body.jl:83)
-  if (body->kind < 0 || body->kind > 3) return fail(s, WL_ERR_UNSUPPORTED, "unknown body kind");
+extern "C++" {
+template <class B>
+static int measure_impl(wl_sim* s, const B& body, double eps, const char* what) {
   cudaSetDevice(s->device);
-  MeasArgs a{s->lay, body_at(body, s->D, (float)t), (float)eps, s->per.kz0, s->sigma.base, s->V.base, s->mu0.base, s->mu1.base,
-             nullptr, nullptr, 0};
+  MeasArgsT<B> a{s->lay, body, (float)eps, s->per.kz0, s->sigma.base, s->V.base, s->mu0.base, s->mu1.base,
+                 nullptr, nullptr, 0};
   if (s->D == 3 && s->band_count) {                 // K-MOM's band list comes out of the same pass (no k_band_scan)
     WL_CUDA(s, cudaMemsetAsync(s->band_count, 0, sizeof(int), s->st));
     a.band_list = s->band_list; a.band_count = s->band_count; a.band_cap = s->band_cap;
     s->band_from_measure = true;
   }
-  DISPATCH_D(s, k_measure, grid_all(s->lay), blk(s->D), a);
+  DISPATCH_DB(s, k_measure, B, grid_all(s->lay), blk(s->D), a);
   s->band_dirty = true; s->free_flow = false;
   bc_vec(s, s->mu0, nullptr, false);
   bc_vec(s, s->V, nullptr, s->cfg.exitBC != 0);
   if (int e = halo(s, s->mu0, 1)) return e;
   if (int e = halo(s, s->V, 1)) return e;
-  return check_async(s, "wl_measure_body");
+  return check_async(s, what);
+}
+}  // extern "C++"
+
+int wl_measure_body(wl_sim* s, const wl_body* body, double t, double eps) {
+  if (!s || !body) return WL_ERR_INVALID;
+  if (body->kind == 0) return WL_OK;                 // NoBody: measure! is a no-op (Body.jl:83)
+  if (body->kind < 0 || body->kind > 3) return fail(s, WL_ERR_UNSUPPORTED, "unknown body kind");
+  return measure_impl(s, body_at(body, s->D, (float)t), eps, "wl_measure_body");
+}
+
+int wl_measure_csg(wl_sim* s, const wl_body_node* nodes, int32_t n, double eps) {
+  if (!s) return WL_ERR_INVALID;
+  BodyProg p;
+  if (const char* m = prog_from(nodes, n, s->D, &p)) return fail(s, WL_ERR_INVALID, m);
+  if (p.n == 1 && p.nd[0].kind == 0) return WL_OK;   // NoBody
+  return measure_impl(s, p, eps, "wl_measure_csg");
 }
 
 int wl_set_body_coeffs(wl_sim* s, const float* mu0, const float* mu1, const float* V, const float* sdf) {
@@ -623,49 +638,71 @@ int wl_mom_step(wl_sim* s, const float* uBC_t1, const float* acc0, const float* 
   return check_async(s, "wl_mom_step");
 }
 
-int wl_pressure_force(wl_sim* s, const wl_body* body, double t, double out[3]) {
-  if (!s || !body || !out) return WL_ERR_INVALID;
-  cudaSetDevice(s->device);
-  ForceArgs a{s->lay, body_at(body, s->D, (float)t), s->p.base, s->f.base, s->per.kz0};
-  DISPATCH_D(s, k_force_df, grid_all(s->lay), blk(s->D), a);
+extern "C++" {
+static int sum_df(wl_sim* s, double out[3], const char* what) {
   for (int c = 0; c < s->D; ++c) {
     SumArgs sa{s->lay, s->f.base + s->lay.cstride * c, s->redw, s->d_red + 3 + c};
     DISPATCH_D(s, k_sum_all, grid_all(s->lay), blk(s->D), sa);
   }
   if (int e = fetch_red(s)) return e;
   for (int c = 0; c < 3; ++c) out[c] = c < s->D ? s->h_red[3 + c].sum : 0.0;
-  return check_async(s, "wl_pressure_force");
+  return check_async(s, what);
 }
-
-int wl_viscous_force(wl_sim* s, const wl_body* body, double t, double out[3]) {
-  if (!s || !body || !out) return WL_ERR_INVALID;
+template <class B>
+static int pressure_force_impl(wl_sim* s, const B& body, double out[3], const char* what) {
+  cudaSetDevice(s->device);
+  ForceArgsT<B> a{s->lay, body, s->p.base, s->f.base, s->per.kz0};
+  DISPATCH_DB(s, k_force_df, B, grid_all(s->lay), blk(s->D), a);
+  return sum_df(s, out, what);
+}
+template <class B>
+static int viscous_force_impl(wl_sim* s, const B& body, double out[3], const char* what) {
   cudaSetDevice(s->device);
   if (int e = halo(s, s->u, 1)) return e;               // the strain rate reads u across slab interfaces
-  ViscArgs a{s->lay, body_at(body, s->D, (float)t), s->u.base, s->f.base, s->cfg.nu, s->per.kz0};
-  DISPATCH_D(s, k_visc_df, grid_all(s->lay), blk(s->D), a);
-  for (int c = 0; c < s->D; ++c) {
-    SumArgs sa{s->lay, s->f.base + s->lay.cstride * c, s->redw, s->d_red + 3 + c};
-    DISPATCH_D(s, k_sum_all, grid_all(s->lay), blk(s->D), sa);
-  }
-  if (int e = fetch_red(s)) return e;
-  for (int c = 0; c < 3; ++c) out[c] = c < s->D ? s->h_red[3 + c].sum : 0.0;
-  return check_async(s, "wl_viscous_force");
+  ViscArgsT<B> a{s->lay, body, s->u.base, s->f.base, s->cfg.nu, s->per.kz0};
+  DISPATCH_DB(s, k_visc_df, B, grid_all(s->lay), blk(s->D), a);
+  return sum_df(s, out, what);
 }
-
-int wl_force_moment(wl_sim* s, const wl_body* body, double t, const double x0[3], int viscous, double out[3]) {
-  if (!s || !body || !out || !x0) return WL_ERR_INVALID;
+template <class B>
+static int force_moment_impl(wl_sim* s, const B& body, const double x0[3], int viscous, double out[3], const char* what) {
   cudaSetDevice(s->device);
   if (viscous) { if (int e = halo(s, s->u, 1)) return e; }
-  MomentArgs a{s->lay, body_at(body, s->D, (float)t), s->p.base, s->u.base, s->f.base, s->cfg.nu, s->per.kz0, viscous ? 1 : 0,
-               {(float)x0[0], (float)x0[1], (float)x0[2]}};
-  DISPATCH_D(s, k_moment_df, grid_all(s->lay), blk(s->D), a);
-  for (int c = 0; c < s->D; ++c) {
-    SumArgs sa{s->lay, s->f.base + s->lay.cstride * c, s->redw, s->d_red + 3 + c};
-    DISPATCH_D(s, k_sum_all, grid_all(s->lay), blk(s->D), sa);
-  }
-  if (int e = fetch_red(s)) return e;
-  for (int c = 0; c < 3; ++c) out[c] = c < s->D ? s->h_red[3 + c].sum : 0.0;
-  return check_async(s, "wl_force_moment");
+  MomentArgsT<B> a{s->lay, body, s->p.base, s->u.base, s->f.base, s->cfg.nu, s->per.kz0, viscous ? 1 : 0,
+                   {(float)x0[0], (float)x0[1], (float)x0[2]}};
+  DISPATCH_DB(s, k_moment_df, B, grid_all(s->lay), blk(s->D), a);
+  return sum_df(s, out, what);
+}
+}  // extern "C++"
+
+int wl_pressure_force(wl_sim* s, const wl_body* body, double t, double out[3]) {
+  if (!s || !body || !out) return WL_ERR_INVALID;
+  return pressure_force_impl(s, body_at(body, s->D, (float)t), out, "wl_pressure_force");
+}
+int wl_viscous_force(wl_sim* s, const wl_body* body, double t, double out[3]) {
+  if (!s || !body || !out) return WL_ERR_INVALID;
+  return viscous_force_impl(s, body_at(body, s->D, (float)t), out, "wl_viscous_force");
+}
+int wl_force_moment(wl_sim* s, const wl_body* body, double t, const double x0[3], int viscous, double out[3]) {
+  if (!s || !body || !out || !x0) return WL_ERR_INVALID;
+  return force_moment_impl(s, body_at(body, s->D, (float)t), x0, viscous, out, "wl_force_moment");
+}
+int wl_pressure_force_csg(wl_sim* s, const wl_body_node* nodes, int32_t n, double out[3]) {
+  if (!s || !out) return WL_ERR_INVALID;
+  BodyProg p;
+  if (const char* m = prog_from(nodes, n, s->D, &p)) return fail(s, WL_ERR_INVALID, m);
+  return pressure_force_impl(s, p, out, "wl_pressure_force_csg");
+}
+int wl_viscous_force_csg(wl_sim* s, const wl_body_node* nodes, int32_t n, double out[3]) {
+  if (!s || !out) return WL_ERR_INVALID;
+  BodyProg p;
+  if (const char* m = prog_from(nodes, n, s->D, &p)) return fail(s, WL_ERR_INVALID, m);
+  return viscous_force_impl(s, p, out, "wl_viscous_force_csg");
+}
+int wl_force_moment_csg(wl_sim* s, const wl_body_node* nodes, int32_t n, const double x0[3], int viscous, double out[3]) {
+  if (!s || !out || !x0) return WL_ERR_INVALID;
+  BodyProg p;
+  if (const char* m = prog_from(nodes, n, s->D, &p)) return fail(s, WL_ERR_INVALID, m);
+  return force_moment_impl(s, p, x0, viscous, out, "wl_force_moment_csg");
 }
 
 int wl_meanflow_init(wl_sim* s, int uu_stats) {

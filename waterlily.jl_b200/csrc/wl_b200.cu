@@ -249,6 +249,12 @@ inline void prof_post(wl_sim* s, const char* name, cudaEvent_t a, cudaEvent_t b)
     else LAUNCH(s, kern<2>, g, b, __VA_ARGS__);                           \
   } while (0)
 
+#define DISPATCH_DB(s, kern, B, g, b, ...)                                \
+  do {                                                                    \
+    if ((s)->D == 3) LAUNCH(s, (kern<3, B>), g, b, __VA_ARGS__);          \
+    else LAUNCH(s, (kern<2, B>), g, b, __VA_ARGS__);                      \
+  } while (0)
+
 #define DISPATCH_DS(s, kern, g, b, ...)                                                   \
   do {                                                                                    \
     const int sc_ = (s)->cfg.scheme;                                                      \
@@ -1059,6 +1065,42 @@ BodyDev body_at(const wl_body* b, int D, float t) {
     d.Vb[k] = b->vel[k] + 2 * b->acc[k] * t + b->amp[k] * b->omega * std::cos(b->omega * t);
   }
   return d;
+}
+
+// wl_body_node[] -> BodyProg: rotation(θ) (RigidMap.jl:45-49) in Float32 on the host, stack discipline checked here
+// so the device loop can trust it.  Returns nullptr or a message.
+const char* prog_from(const wl_body_node* nd, int n, int D, BodyProg* out) {
+  if (!nd || n < 1 || n > CSG_MAX) return "a body program needs 1..WL_CSG_MAX nodes";
+  int sp = 0;
+  out->n = n;
+  for (int i = 0; i < n; ++i) {
+    const wl_body_node& b = nd[i];
+    NodeDev& q = out->nd[i];
+    q = NodeDev{};
+    q.op = b.op;
+    if (b.op == 0) {
+      if (b.kind < 0 || b.kind > 4) return "unknown leaf kind";
+      if (b.kind >= 2 && (b.axis < 0 || b.axis >= D)) return "leaf axis out of range";
+      ++sp;
+      q.kind = b.kind; q.axis = b.axis; q.radius = b.radius; q.minor = b.minor;
+      const float t1 = D == 3 ? b.theta[0] : 0.f, t2 = D == 3 ? b.theta[1] : 0.f, t3 = b.theta[2];
+      const float c1 = std::cos(t1), s1 = std::sin(t1), c2 = std::cos(t2), s2 = std::sin(t2), c3 = std::cos(t3), s3 = std::sin(t3);
+      float* R = q.R;
+      if (D == 2) { R[0] = c3; R[1] = s3; R[3] = -s3; R[4] = c3; R[8] = 1.f; }
+      else {
+        R[0] = c3 * c2;  R[1] = c3 * s2 * s1 + s3 * c1;   R[2] = -c3 * s2 * c1 + s3 * s1;
+        R[3] = -s3 * c2; R[4] = -s3 * s2 * s1 + c3 * c1;  R[5] = s3 * s2 * c1 + c3 * s1;
+        R[6] = s2;       R[7] = -c2 * s1;                 R[8] = c2 * c1;
+      }
+      for (int k = 0; k < 3; ++k) { q.x0[k] = b.x0[k]; q.xp[k] = b.xp[k]; q.V[k] = b.V[k]; q.w[k] = b.omega[k]; }
+    } else if (b.op == 3) {
+      if (sp < 1) return "complement of an empty stack";
+    } else if (b.op == 1 || b.op == 2) {
+      if (sp < 2) return "set operation needs two operands";
+      --sp;
+    } else return "unknown node op";
+  }
+  return sp == 1 ? nullptr : "body program leaves more than one body on the stack";
 }
 
 DevField* flow_field(wl_sim* s, int field, int level, Lay* lay) {

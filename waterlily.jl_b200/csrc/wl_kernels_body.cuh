@@ -68,6 +68,147 @@ __device__ __forceinline__ Meas measure_pt(const BodyDev& b, const float* x, flo
   return m;
 }
 
+template <int D>
+__device__ __forceinline__ float sdf_fill(const BodyDev& b, const float* x, float) { return measure_pt<D>(b, x, 0.f).d; }
+
+// ---- SetBody programs over RigidMap leaves (Body.jl:91-107, RigidMap.jl:28-50) ------------------------------
+constexpr int CSG_MAX = 8;
+struct NodeDev {
+  int op, kind, axis;          // op: 0 leaf, 1 min (∪,+), 2 max (∩), 3 complement
+  float radius, minor;
+  float x0[3], xp[3], R[9], V[3], w[3];   // R̂ = rotation(θ), row-major, formed on the host (RigidMap.jl:45-49)
+};
+struct BodyProg { int n; NodeDev nd[CSG_MAX]; };
+
+// measure(AutoBody(sdf,RigidMap),x,t;fastd²): ξ = R̂(x−x₀−xₚ)+xₚ, n = R̂ᵀ∇sdf(ξ) normalised, V = V + ω×(x−x₀−xₚ)
+template <int D>
+__device__ __forceinline__ Meas measure_leaf(const NodeDev& b, const float* x, float fastd2) {
+  Meas m;
+  m.d = INFINITY;
+#pragma unroll
+  for (int q = 0; q < 3; ++q) m.n[q] = m.V[q] = 0.f;
+  if (b.kind == 0) return m;
+  float r[3] = {0.f, 0.f, 0.f}, xi[3] = {0.f, 0.f, 0.f}, g[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+  for (int q = 0; q < D; ++q) r[q] = x[q] - b.x0[q] - b.xp[q];
+#pragma unroll
+  for (int k = 0; k < D; ++k) {
+    float a = b.R[3 * k] * r[0];
+#pragma unroll
+    for (int q = 1; q < D; ++q) a += b.R[3 * k + q] * r[q];
+    xi[k] = a + b.xp[k];
+  }
+  float d;
+  if (b.kind == 1) {
+    float s = 0.f;
+#pragma unroll
+    for (int q = 0; q < D; ++q) s += xi[q] * xi[q];
+    const float rt = sqrtf(s);
+    d = rt - b.radius;
+#pragma unroll
+    for (int q = 0; q < D; ++q) g[q] = xi[q] / rt;
+  } else if (b.kind == 2) {
+    float s = 0.f;
+#pragma unroll
+    for (int q = 0; q < D; ++q) if (q != b.axis) s += xi[q] * xi[q];
+    const float rt = sqrtf(s);
+    d = rt - b.radius;
+#pragma unroll
+    for (int q = 0; q < D; ++q) g[q] = q == b.axis ? 0.f : xi[q] / rt;
+  } else if (b.kind == 3) {
+    float s = 0.f, xa = 0.f;
+#pragma unroll
+    for (int q = 0; q < D; ++q) { if (q != b.axis) s += xi[q] * xi[q]; else xa = xi[q]; }
+    const float rho = sqrtf(s), qq = rho - b.radius;
+    const float len = sqrtf(qq * qq + xa * xa);
+    d = len - b.minor;
+#pragma unroll
+    for (int q = 0; q < D; ++q) g[q] = q == b.axis ? xi[q] / len : (qq / len) * (xi[q] / rho);
+  } else {                                                   // capsule
+    float y[3] = {xi[0], xi[1], xi[2]};
+    const float h = b.minor;
+#pragma unroll
+    for (int q = 0; q < D; ++q) if (q == b.axis) y[q] = xi[q] - fmaxf(-h, fminf(xi[q], h));
+    float s = 0.f;
+#pragma unroll
+    for (int q = 0; q < D; ++q) s += y[q] * y[q];
+    const float len = sqrtf(s);
+    d = len - b.radius;
+#pragma unroll
+    for (int q = 0; q < D; ++q) g[q] = y[q] / len;
+  }
+  m.d = d;
+  if (d * d > fastd2) return m;
+  bool nan = false;
+#pragma unroll
+  for (int q = 0; q < D; ++q) nan |= isnan(g[q]);
+  if (nan) return m;
+  float nn[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+  for (int k = 0; k < D; ++k) {
+    float a = b.R[k] * g[0];
+#pragma unroll
+    for (int q = 1; q < D; ++q) a += b.R[3 * q + k] * g[q];
+    nn[k] = a;
+  }
+  float mm = 0.f;
+#pragma unroll
+  for (int q = 0; q < D; ++q) mm += nn[q] * nn[q];
+  mm = sqrtf(mm);
+  m.d = d / mm;
+  float cr[3];
+  if (D == 2) { cr[0] = b.w[2] * -r[1]; cr[1] = b.w[2] * r[0]; cr[2] = 0.f; }
+  else { cr[0] = b.w[1] * r[2] - b.w[2] * r[1]; cr[1] = b.w[2] * r[0] - b.w[0] * r[2]; cr[2] = b.w[0] * r[1] - b.w[1] * r[0]; }
+#pragma unroll
+  for (int q = 0; q < D; ++q) { m.n[q] = nn[q] / mm; m.V[q] = b.V[q] + cr[q]; }
+  return m;
+}
+
+// Base.isless on floats and on (d, n, V) tuples: NaN greatest, −0.0 < 0.0, lexicographic
+__device__ __forceinline__ bool fless(float a, float b) {
+  return !isnan(a) && (isnan(b) || (signbit(a) && !signbit(b) && a == b) || a < b);
+}
+__device__ __forceinline__ bool fequal(float a, float b) { return (isnan(a) && isnan(b)) || (a == b && signbit(a) == signbit(b)); }
+template <int D>
+__device__ __forceinline__ bool meas_less(const Meas& a, const Meas& b) {
+  if (fless(a.d, b.d)) return true;
+  if (!fequal(a.d, b.d)) return false;
+#pragma unroll
+  for (int k = 0; k < D; ++k) { if (fless(a.n[k], b.n[k])) return true; if (fless(b.n[k], a.n[k])) return false; }
+#pragma unroll
+  for (int k = 0; k < D; ++k) { if (fless(a.V[k], b.V[k])) return true; if (fless(b.V[k], a.V[k])) return false; }
+  return false;
+}
+
+// measure(body::SetBody,x,t;fastd²) Body.jl:104-107 over the postfix program (validated on the host)
+template <int D>
+__device__ __forceinline__ Meas measure_pt(const BodyProg& p, const float* x, float fastd2) {
+  Meas st[CSG_MAX];
+  int sp = 0;
+  for (int i = 0; i < p.n; ++i) {
+    const NodeDev& b = p.nd[i];
+    if (b.op == 0) st[sp++] = measure_leaf<D>(b, x, fastd2);
+    else if (b.op == 3) {
+      Meas& a = st[sp - 1];
+      a.d = -a.d;
+#pragma unroll
+      for (int k = 0; k < D; ++k) a.n[k] = -a.n[k];
+    } else {
+      const Meas bb = st[--sp];
+      Meas& a = st[sp - 1];
+      if (b.op == 1) { if (meas_less<D>(bb, a)) a = bb; }
+      else           { if (meas_less<D>(a, bb)) a = bb; }
+    }
+  }
+  return st[0];
+}
+// measure_sdf!(σ,body,t;fastd²): raw sdf for a lone AutoBody (AutoBody.jl:19), measure(...)[1] for a SetBody (Body.jl:66)
+template <int D>
+__device__ __forceinline__ float sdf_fill(const BodyProg& p, const float* x, float fastd2) {
+  if (p.n == 1) return measure_leaf<D>(p.nd[0], x, 0.f).d;
+  return measure_pt<D>(p, x, fastd2).d;
+}
+
 // kernels Body.jl:54-60
 // Julia's sinpi/cospi are accurate to the last bit: evaluate in double and round once (the CPU
 // checker does the same), so μ₀/μ₁ agree bit for bit.  Only band cells reach these, the cost is nil.
@@ -86,9 +227,10 @@ __device__ __forceinline__ float mu0f(float d, float e) {
 }
 __device__ __forceinline__ float mu1f(float d, float e) { return e * kern1(fmaxf(-1.f, fminf(d / e, 1.f))); }
 
-struct MeasArgs {
+template <class B>
+struct MeasArgsT {
   Lay l;
-  BodyDev b;
+  B b;
   float eps;
   int kz0;           // global index of local plane 0 (slab decomposition)
   float* sigma; float* V; float* mu0; float* mu1;
@@ -97,8 +239,9 @@ struct MeasArgs {
 
 // measure! (Body.jl:28-48) in one pass over ALL cells: the three fills of :29, measure_sdf! :30
 // and the band loop :31-48.  Ghost cells get V=0, μ₀=1, μ₁=0 (σ untouched); BC! follows.
-template <int D>
-__global__ void __launch_bounds__(256) k_measure(const MeasArgs a) {
+using MeasArgs = MeasArgsT<BodyDev>;
+template <int D, class B>
+__global__ void __launch_bounds__(256) k_measure(const MeasArgsT<B> a) {
   pdl_entry();
   const Lay& l = a.l;
   const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
@@ -111,7 +254,7 @@ __global__ void __launch_bounds__(256) k_measure(const MeasArgs a) {
   if (in) {
     const float d2 = (2.f + a.eps) * (2.f + a.eps);
     float x[3] = {(float)i - 0.5f, (float)j - 0.5f, (float)(k + a.kz0) - 0.5f};
-    const float sd = measure_pt<D>(a.b, x, 0.f).d;          // sdf(body,x,t) raw
+    const float sd = sdf_fill<D>(a.b, x, d2);               // measure_sdf!(a.σ,body,t;fastd²=d²)
     a.sigma[o] = sd;
     if (sd * sd < d2) {
 #pragma unroll
@@ -150,9 +293,10 @@ __global__ void __launch_bounds__(256) k_measure(const MeasArgs a) {
 }
 
 // pressure_force (Metrics.jl:126-133): df = p·nds over inside (df ≡ flow.f, zero elsewhere).
-struct ForceArgs { Lay l; BodyDev b; const float* p; float* f; int kz0; };
-template <int D>
-__global__ void __launch_bounds__(256) k_force_df(const ForceArgs a) {
+template <class B> struct ForceArgsT { Lay l; B b; const float* p; float* f; int kz0; };
+using ForceArgs = ForceArgsT<BodyDev>;
+template <int D, class B>
+__global__ void __launch_bounds__(256) k_force_df(const ForceArgsT<B> a) {
   pdl_entry();
   const Lay& l = a.l;
   const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
@@ -176,9 +320,10 @@ __global__ void __launch_bounds__(256) k_force_df(const ForceArgs a) {
 
 // viscous_force (Metrics.jl:140-152): df = -2ν·S(I,u)·nds over inside_u(u), S the rate-of-strain tensor
 // (:134) from the staggered differences ∂(i,j,I,u) (:42-45); summed per component by k_sum_all.
-struct ViscArgs { Lay l; BodyDev b; const float* u; float* f; float nu; int kz0; };
-template <int D>
-__global__ void __launch_bounds__(256) k_visc_df(const ViscArgs a) {
+template <class B> struct ViscArgsT { Lay l; B b; const float* u; float* f; float nu; int kz0; };
+using ViscArgs = ViscArgsT<BodyDev>;
+template <int D, class B>
+__global__ void __launch_bounds__(256) k_visc_df(const ViscArgsT<B> a) {
   pdl_entry();
   const Lay& l = a.l;
   const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
@@ -217,9 +362,10 @@ __global__ void __launch_bounds__(256) k_visc_df(const ViscArgs a) {
 
 // pressure_moment / viscous_moment (Metrics.jl:168-192): df = p·cross(x-x₀, nds) or -2ν·cross(x-x₀, S·nds);
 // in 2D the cross product is the scalar a₁b₂-a₂b₁, stored in both components like the reference's broadcast.
-struct MomentArgs { Lay l; BodyDev b; const float* p; const float* u; float* f; float nu; int kz0; int viscous; float x0[3]; };
-template <int D>
-__global__ void __launch_bounds__(256) k_moment_df(const MomentArgs a) {
+template <class B> struct MomentArgsT { Lay l; B b; const float* p; const float* u; float* f; float nu; int kz0; int viscous; float x0[3]; };
+using MomentArgs = MomentArgsT<BodyDev>;
+template <int D, class B>
+__global__ void __launch_bounds__(256) k_moment_df(const MomentArgsT<B> a) {
   pdl_entry();
   const Lay& l = a.l;
   const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
