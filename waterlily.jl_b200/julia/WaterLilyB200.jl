@@ -29,6 +29,10 @@ struct WLBody
     kind::Int32; axis::Int32; center::NTuple{3,Float32}; radius::Float32; minor::Float32
     vel::NTuple{3,Float32}; acc::NTuple{3,Float32}; amp::NTuple{3,Float32}; omega::Float32
 end
+struct WLNode                                   # wl_body_node (include/wl_b200.h)
+    op::Int32; kind::Int32; axis::Int32; radius::Float32; minor::Float32
+    x0::NTuple{3,Float32}; theta::NTuple{3,Float32}; xp::NTuple{3,Float32}; V::NTuple{3,Float32}; omega::NTuple{3,Float32}
+end
 struct WLStepInfo
     dt_next::Float32; n_pred::Int32; n_corr::Int32; flags::Int32; trace_len::NTuple{2,Int32}
     rinf::NTuple{68,Float32}; r1::NTuple{68,Float32}; omega::NTuple{68,Float32}
@@ -76,6 +80,32 @@ B200Cylinder(center, radius, axis; kw...) = (b = B200Sphere(center, radius; kw..
     B200Body(WLBody(2, axis - 1, b.center, b.radius, 0, b.vel, b.acc, b.amp, b.omega)))
 B200Torus(center, R, r, axis; kw...) = (b = B200Sphere(center, R; kw...).c;
     B200Body(WLBody(3, axis - 1, b.center, R, r, b.vel, b.acc, b.amp, b.omega)))
+
+# ---- library sdfs under a `RigidMap`, combined with WaterLily's own lazy `SetBody` algebra (+ ∪ ∩ -) -----------
+# `body.map` is a real `WaterLily.RigidMap`, so `setmap(body; θ, x₀, ...)` (src/RigidMap.jl:54-56) works unchanged,
+# on single leaves and through `SetBody` trees alike.
+struct B200Rigid{M<:WaterLily.RigidMap} <: AbstractBody
+    kind::Int32; axis::Int32; radius::Float32; minor::Float32
+    map::M
+end
+B200Rigid(kind::Symbol, map::WaterLily.RigidMap; radius=0, minor=0, axis=3) =
+    B200Rigid(Int32((sphere=1, circle=1, cylinder=2, torus=3, capsule=4)[kind]), Int32(axis - 1), Float32(radius), Float32(minor), map)
+rot3(θ::Number) = (0f0, 0f0, Float32(θ)); rot3(θ) = pad3(Float32.(θ), 0f0)       # 2D: θ and ω turn about z
+node(b::B200Rigid) = (m = b.map; WLNode(0, b.kind, b.axis, b.radius, b.minor, pad3(Float32.(m.x₀), 0f0), rot3(m.θ),
+                                        pad3(Float32.(m.xₚ), 0f0), pad3(Float32.(m.V), 0f0), rot3(m.ω)))
+const OPNODE = Dict(1 => WLNode(1, 0, 0, 0, 0, ntuple(_ -> ntuple(_ -> 0f0, 3), 5)...),
+                    2 => WLNode(2, 0, 0, 0, 0, ntuple(_ -> ntuple(_ -> 0f0, 3), 5)...),
+                    3 => WLNode(3, 0, 0, 0, 0, ntuple(_ -> ntuple(_ -> 0f0, 3), 5)...))
+"Postfix program of a body, or `nothing` when a leaf is not a library primitive (then the host path measures it)."
+nodes(b::B200Rigid) = WLNode[node(b)]
+nodes(::AbstractBody) = nothing
+nodes(b::WaterLily.SetBody{typeof(-)}) = (a = nodes(b.a); a === nothing ? nothing : [a; OPNODE[3]])
+function nodes(b::WaterLily.SetBody)
+    op = b.op === min ? 1 : b.op === max ? 2 : 0
+    a, c = nodes(b.a), nodes(b.b)
+    (op == 0 || a === nothing || c === nothing || length(a) + length(c) + 1 > 8) ? nothing : [a; c; OPNODE[op]]
+end
+const CsgBody = Union{B200Rigid,WaterLily.SetBody}
 
 # ---- Flow ------------------------------------------------------------------------------------------
 struct B200Flow{D,T} <: AbstractFlow{D,T}
@@ -169,8 +199,14 @@ measure!(a::B200Flow, ::WaterLily.NoBody; kw...) = nothing
 function measure!(a::B200Flow{D,T}, body::B200Body; t=zero(T), ϵ=1) where {D,T}
     check(a.h, ccall((:wl_measure_body, LIB), Cint, (Ptr{Cvoid}, Ref{WLBody}, Cdouble, Cdouble), a.h.ptr, Ref(body.c), t, ϵ))
 end
-"Arbitrary `AutoBody` closures: measured by the reference itself on a host `Flow`, then uploaded."
+"Arbitrary `AutoBody` closures: measured by the reference itself on a host `Flow`, then uploaded.
+`SetBody` trees of `B200Rigid` leaves go to the device instead (`wl_measure_csg`)."
 function measure!(a::B200Flow{D,T}, body::AbstractBody; t=zero(T), ϵ=1) where {D,T}
+    nd = nodes(body)
+    if nd !== nothing
+        check(a.h, ccall((:wl_measure_csg, LIB), Cint, (Ptr{Cvoid}, Ptr{WLNode}, Cint, Cdouble), a.h.ptr, nd, length(nd), ϵ))
+        return
+    end
     host = WaterLily.Flow(size(a.p) .- 2, a.uBC; T, perdir=a.perdir, exitBC=a.exitBC)
     fill!(host.V, 0); fill!(host.μ₀, 1); fill!(host.μ₁, 0)
     WaterLily.measure!(host, body; t, ϵ)               # includes the two BC! calls; the library re-applies them (idempotent)
@@ -228,6 +264,24 @@ end
 pressure_moment(x₀, a::B200Flow, body::B200Body) = force_moment(x₀, a, body, false)
 viscous_moment(x₀, a::B200Flow, body::B200Body) = force_moment(x₀, a, body, true)
 total_moment(x₀, a::B200Flow, body::B200Body) = pressure_moment(x₀, a, body) .+ viscous_moment(x₀, a, body)
+
+function csg_call(sym, a::B200Flow{D}, body, extra...) where D
+    nd = nodes(body); nd === nothing && error("force metrics on the device need library primitives (B200Rigid leaves)")
+    out = Ref(ntuple(_ -> 0.0, 3))
+    sym === :wl_force_moment_csg ?
+        check(a.h, ccall((:wl_force_moment_csg, LIB), Cint, (Ptr{Cvoid}, Ptr{WLNode}, Cint, Ref{NTuple{3,Float64}}, Cint, Ref{NTuple{3,Float64}}),
+                         a.h.ptr, nd, length(nd), Ref(ntuple(i -> i <= D ? Float64(extra[1][i]) : 0.0, 3)), extra[2], out)) :
+    sym === :wl_viscous_force_csg ?
+        check(a.h, ccall((:wl_viscous_force_csg, LIB), Cint, (Ptr{Cvoid}, Ptr{WLNode}, Cint, Ref{NTuple{3,Float64}}), a.h.ptr, nd, length(nd), out)) :
+        check(a.h, ccall((:wl_pressure_force_csg, LIB), Cint, (Ptr{Cvoid}, Ptr{WLNode}, Cint, Ref{NTuple{3,Float64}}), a.h.ptr, nd, length(nd), out))
+    collect(out[][1:D])
+end
+pressure_force(a::B200Flow, body::CsgBody) = csg_call(:wl_pressure_force_csg, a, body)
+viscous_force(a::B200Flow, body::CsgBody) = csg_call(:wl_viscous_force_csg, a, body)
+total_force(a::B200Flow, body::CsgBody) = pressure_force(a, body) .+ viscous_force(a, body)
+pressure_moment(x₀, a::B200Flow, body::CsgBody) = csg_call(:wl_force_moment_csg, a, body, x₀, 0)
+viscous_moment(x₀, a::B200Flow, body::CsgBody) = csg_call(:wl_force_moment_csg, a, body, x₀, 1)
+total_moment(x₀, a::B200Flow, body::CsgBody) = pressure_moment(x₀, a, body) .+ viscous_moment(x₀, a, body)
 
 # ---- MeanFlow (src/Metrics.jl:205-263): device-resident running averages --------------------------------
 struct B200MeanFlow{T}
