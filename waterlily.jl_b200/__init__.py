@@ -434,6 +434,11 @@ class Simulation:
     def sim_time(self):
         return self.time() * self.U / self.L
 
+    def set_dts(self, dts):
+        """`empty!(flow.Δt); push!(flow.Δt, dts...)` (the `load!` methods): the host vector and the device-side Δt[end]."""
+        self._dts[:] = [np.float32(x) for x in dts]            # in place: `sim.flow.Δt` aliases this list
+        self._check(self.lib.wl_set_dt(self.h, float(self._dts[-1])))
+
     def measure(self, t=None):
         """`measure!(sim,t=sum(Δt))` = measure!(flow,body) + update!(pois) (src/WaterLily.jl:146-149)."""
         if t is None:
