@@ -193,6 +193,54 @@ def BC(a, A, saveexit, perdir):
                     Aa[I + (i,)] = Aa[plus(I, e, -1) + (i,)]
 
 
+def loc_(i, I, T=f32):
+    """`loc(i,I,T)` core.jl:177 for a 1-based CartesianIndex tuple."""
+    return [T(I[k] - 1.5) - (T(0.5) if k + 1 == i else T(0)) for k in range(len(I))]
+
+
+def BC_fn(a, uBC, saveexit, perdir, t, T=f32):
+    """`BC!(a,uBC::Function,saveexit,perdir,t)` core.jl:201-219.  The tangential sum is written as
+    a[I±δ] + (uBC(I) − uBC(I±δ)): an exact copy when uBC does not vary along j (see `BC`)."""
+    N, n = a.shape[:-1], a.shape[-1]
+    Aa = J(a)
+    ub = lambda i, I: T(uBC(i, loc_(i, I, T), T(t)))
+    for i in range(1, n + 1):
+        for j in range(1, n + 1):
+            e = d_(j, n)
+            if j in perdir:
+                for I in slice_(N, 1, j):
+                    Aa[I + (i,)] = Aa[CIj(j, I, N[j - 1] - 1) + (i,)]
+                for I in slice_(N, N[j - 1], j):
+                    Aa[I + (i,)] = Aa[CIj(j, I, 2) + (i,)]
+            elif i == j:
+                for s in (1, 2):
+                    for I in slice_(N, s, j):
+                        Aa[I + (i,)] = ub(i, I)
+                if (not saveexit) or i > 1:
+                    for I in slice_(N, N[j - 1], j):
+                        Aa[I + (i,)] = ub(i, I)
+            else:
+                for I in slice_(N, 1, j):
+                    Aa[I + (i,)] = Aa[plus(I, e) + (i,)] + (ub(i, I) - ub(i, plus(I, e)))
+                for I in slice_(N, N[j - 1], j):
+                    Aa[I + (i,)] = Aa[plus(I, e, -1) + (i,)] + (ub(i, I) - ub(i, plus(I, e, -1)))
+
+
+def accelerate_fn(r, t, g, dUdt, T=f32):
+    """`accelerate!(r,t,g,U)` Flow.jl:69-73 over CartesianIndices(r); `dUdt` is ∂ₜU in closed form."""
+    N, n = r.shape[:-1], r.shape[-1]
+    R = J(r)
+    for i in range(1, n + 1):
+        for I in CR(*[(1, m) for m in N]):
+            x = loc_(i, I, T)
+            if g is not None and dUdt is not None:
+                R[I + (i,)] += T(g(i, x, T(t))) + T(dUdt(i, x, T(t)))
+            elif g is not None:
+                R[I + (i,)] += T(g(i, x, T(t)))
+            elif dUdt is not None:
+                R[I + (i,)] += T(dUdt(i, x, T(t)))
+
+
 def CFL(u, sigma, nu):
     """`CFL(a)` Flow.jl:234-244: σ = flux_out inside, then the maximum over the WHOLE σ."""
     N, n = u.shape[:-1], u.shape[-1]

@@ -153,6 +153,48 @@ void BC(const Grid& g, real* a, const real* U, bool saveexit, const int* per) {
   }
 }
 
+// `BC!(a,uBC::Function,saveexit,perdir,t)` core.jl:201-219: Dirichlet uBC(i,loc(i,I),t) on the normal component,
+// `uBC(I) + a[I±δ] − uBC(I±δ)` on the tangential ones.  `i` is passed 1-based, like the reference's closures.
+// The reference evaluates that sum under @fastmath (core.jl:139,150), which lets LLVM fold it to a plain copy when
+// uBC does not vary along j (its own test demands `==` there, test_core.jl:24-27); the association used here,
+// a[I±δ] + (uBC(I) − uBC(I±δ)), has that property exactly and is one of the orders @fastmath permits otherwise.
+typedef real (*wlo_fn)(int i, const real* x, real t);
+inline real at_loc(wlo_fn f, int i, int a, int b, int c, real t) {      // f(i, loc(i,I), t), 0-based (a,b,c)
+  real x[3] = {(real)a - (real)0.5, (real)b - (real)0.5, (real)c - (real)0.5};
+  x[i] -= (real)0.5;
+  return f(i + 1, x, t);
+}
+void BC_fn(const Grid& g, real* a, wlo_fn ub, bool saveexit, const int* per, real t) {
+  const int D = g.D;
+  for (int i = 0; i < D; ++i) {
+    real* ai = a + g.cells * i;
+    for (int j = 0; j < D; ++j) {
+      const long sj = g.s[j];
+      const int N = g.n[j];
+      const int dj[3] = {j == 0, j == 1, j == 2};
+      if (per[j]) {
+        loop(g, slice(g, 0, j), [&](long I, int, int, int) { ai[I] = ai[I + sj * (N - 2)]; });
+        loop(g, slice(g, N - 1, j), [&](long I, int, int, int) { ai[I] = ai[I - sj * (N - 2)]; });
+      } else if (i == j) {
+        for (int s = 0; s < 2; ++s)
+          loop(g, slice(g, s, j), [&](long I, int x, int y, int z) { ai[I] = at_loc(ub, i, x, y, z, t); });
+        if (!saveexit || i > 0)
+          loop(g, slice(g, N - 1, j), [&](long I, int x, int y, int z) { ai[I] = at_loc(ub, i, x, y, z, t); });
+      } else {
+        loop(g, slice(g, 0, j), [&](long I, int x, int y, int z) {
+          ai[I] = ai[I + sj] + (at_loc(ub, i, x, y, z, t) - at_loc(ub, i, x + dj[0], y + dj[1], z + dj[2], t)); });
+        loop(g, slice(g, N - 1, j), [&](long I, int x, int y, int z) {
+          ai[I] = ai[I - sj] + (at_loc(ub, i, x, y, z, t) - at_loc(ub, i, x - dj[0], y - dj[1], z - dj[2], t)); });
+      }
+    }
+  }
+}
+// either form of flow.uBC at time t
+struct BCSpec { const real* U; wlo_fn fn; real t; };
+inline void BC(const Grid& g, real* a, const BCSpec& b, bool saveexit, const int* per) {
+  if (b.fn) BC_fn(g, a, b.fn, saveexit, per, b.t); else BC(g, a, b.U, saveexit, per);
+}
+
 // `exitBC!(u,u⁰,Δt)` core.jl:226-233
 void exitBC(const Grid& g, real* u, const real* u0, real dt) {
   Box ex;   // slice(N.-1, N[1], 1, 2): dim 1 at the upper ghost, others interior
@@ -927,8 +969,22 @@ void accelerate(const Grid& g, real* r, const real* acc) {
   }
 }
 
+// `accelerate!(r,t,g::Function,U::Function)` Flow.jl:69-73: r[Ii] += g(i,loc(Ii),t) + ∂ₜU(i,loc(Ii),t) over ALL of r;
+// the caller supplies ∂ₜU in closed form (the reference differentiates U with ForwardDiff).
+void accelerate_fn(const Grid& g, real* r, real t, wlo_fn gf, wlo_fn dUdt) {
+  if (!gf && !dUdt) return;
+  for (int i = 0; i < g.D; ++i) {
+    real* ri = r + g.cells * i;
+    loop(g, whole(g), [&](long I, int x, int y, int z) {
+      real a = gf ? at_loc(gf, i, x, y, z, t) : (real)0;
+      if (gf && dUdt) a = a + at_loc(dUdt, i, x, y, z, t); else if (dUdt) a = at_loc(dUdt, i, x, y, z, t);
+      ri[I] += a;
+    });
+  }
+}
+
 // `mom_project!(a,b,w,t)` Flow.jl:223-232
-void mom_project(Sim& s, real w, const real* U, Trace* tr) {
+void mom_project(Sim& s, real w, const BCSpec& U, Trace* tr) {
   const Grid& g = s.g; const int D = g.D;
   real dt = w * s.dts.back();
   real *x = s.p.data(), *z = s.sigma.data(), *u = s.u.data(); const real* L = s.mu0.data();
@@ -956,25 +1012,31 @@ real CFL(Sim& s) {
 
 // `mom_step!(a,b)` Flow.jl:156-167 with mom_predict! :190-196 and mom_correct! :205-210.
 // U1 = uBC at t₁ (space-uniform); acc0/acc1 = g+dU/dt at t₀/t₁ (may be null).
-void mom_step(Sim& s, const real* U1, const real* acc0, const real* acc1) {
+void mom_step(Sim& s, const real* U1, const real* acc0, const real* acc1, wlo_fn ub = nullptr, wlo_fn gf = nullptr,
+              wlo_fn dUdt = nullptr) {
   const Grid& g = s.g;
   const real nu = s.cfg.nu; const int sch = s.cfg.scheme; const bool ex = s.cfg.exitBC != 0;
   s.u0 = s.u; scale_u(g, s.u.data(), 0);
   const real dt = s.dts.back();
+  real t1 = 0; for (real d : s.dts) t1 += d;              // t₁ = sum(a.Δt); t₀ = t₁ − a.Δt[end]  Flow.jl:157
+  const real t0 = t1 - dt;
+  const BCSpec bc{U1, ub, t1};
   // predictor
   conv_diff(g, s.f.data(), s.u0.data(), s.sigma.data(), sch, nu, s.per);
   accelerate(g, s.f.data(), acc0);
+  accelerate_fn(g, s.f.data(), t0, gf, dUdt);
   BDIM(g, s.u.data(), s.u0.data(), s.f.data(), s.V.data(), s.mu0.data(), s.mu1.data(), dt);
-  BC(g, s.u.data(), U1, ex, s.per);
+  BC(g, s.u.data(), bc, ex, s.per);
   if (ex) exitBC(g, s.u.data(), s.u0.data(), dt);
-  mom_project(s, 1, U1, &s.last_trace[0]);
+  mom_project(s, 1, bc, &s.last_trace[0]);
   // corrector
   conv_diff(g, s.f.data(), s.u.data(), s.sigma.data(), sch, nu, s.per);
   accelerate(g, s.f.data(), acc1);
+  accelerate_fn(g, s.f.data(), t1, gf, dUdt);
   BDIM(g, s.u.data(), s.u0.data(), s.f.data(), s.V.data(), s.mu0.data(), s.mu1.data(), dt);
   scale_u(g, s.u.data(), (real)0.5);
-  BC(g, s.u.data(), U1, ex, s.per);
-  mom_project(s, (real)0.5, U1, &s.last_trace[1]);
+  BC(g, s.u.data(), bc, ex, s.per);
+  mom_project(s, (real)0.5, bc, &s.last_trace[1]);
   s.dts.push_back(CFL(s));
 }
 
@@ -1073,6 +1135,36 @@ real wlo_mom_step(void* h, const real* U1, const real* acc0, const real* acc1, i
   if (out_n) { out_n[0] = s->last_trace[0].n; out_n[1] = s->last_trace[1].n; }
   return s->dts.back();
 }
+// `mom_step!` with Function uBC / g (Flow.jl:156-167 with :69-73 and core.jl:201-219); null pointers fall back to
+// the constant uBC of the configuration / no acceleration.
+real wlo_mom_step_fn(void* h, wlo_fn ub, wlo_fn gf, wlo_fn dUdt, int* out_n) {
+  Sim* s = (Sim*)h;
+  real U[3] = {(real)s->cfg.uBC[0], (real)s->cfg.uBC[1], (real)s->cfg.uBC[2]};
+  mom_step(*s, U, nullptr, nullptr, ub, gf, dUdt);
+  if (out_n) { out_n[0] = s->last_trace[0].n; out_n[1] = s->last_trace[1].n; }
+  return s->dts.back();
+}
+// Flow constructor's `BC!(u,uBC,exitBC,perdir); exitBC!(u,u,0); u⁰ = copy(u)` (Flow.jl:141-142) for a Function uBC at t = 0
+void wlo_finish_ic_fn(void* h, wlo_fn ub) {
+  Sim* s = (Sim*)h;
+  BC_fn(s->g, s->u.data(), ub, s->cfg.exitBC != 0, s->per, (real)0);
+  exitBC(s->g, s->u.data(), s->u.data(), 0);
+  s->u0 = s->u;
+}
+// `apply!((i,x)->f(i,x,t), u)` core.jl:184-187: every index of every component
+void wlo_apply_fn(real* u, int D, const int* ng, wlo_fn f, real t) {
+  Grid g; g.init(D, ng);
+  for (int i = 0; i < D; ++i) {
+    real* ui = u + g.cells * i;
+    loop(g, whole(g), [&](long I, int x, int y, int z) { ui[I] = at_loc(f, i, x, y, z, t); });
+  }
+}
+void wlo_BC_fn(real* a, int D, const int* ng, wlo_fn ub, int saveexit, const int* per, real t) {
+  Grid g; g.init(D, ng); BC_fn(g, a, ub, saveexit != 0, per, t);
+}
+void wlo_accelerate_fn(real* r, int D, const int* ng, real t, wlo_fn gf, wlo_fn dUdt) {
+  Grid g; g.init(D, ng); accelerate_fn(g, r, t, gf, dUdt);
+}
 void wlo_get_trace(void* h, int which, int* n, float* rinf, float* r1, float* omega) {
   Trace& t = ((Sim*)h)->last_trace[which];
   *n = t.n;
@@ -1136,7 +1228,7 @@ void wlo_op_scale_u(void* h, real sc) { Sim* s = (Sim*)h; scale_u(s->g, s->u.dat
 void wlo_op_project(void* h, real w) {
   Sim* s = (Sim*)h;
   real U[3] = {(real)s->cfg.uBC[0], (real)s->cfg.uBC[1], (real)s->cfg.uBC[2]};
-  mom_project(*s, w, U, &s->last_trace[0]);
+  mom_project(*s, w, BCSpec{U, nullptr, 0}, &s->last_trace[0]);
 }
 void wlo_op_residual(void* h, int l) { residual(((Sim*)h)->ml.lv[l]); }
 void wlo_op_jacobi(void* h, int l) { Jacobi(((Sim*)h)->ml.lv[l]); }

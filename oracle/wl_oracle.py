@@ -197,6 +197,14 @@ def load(dtype=np.float32, fast_path=None):
     lib.wlo_viscous_force_csg.argtypes = [C.c_void_p, NP, C.c_int, DP]
     lib.wlo_force_moment_csg.argtypes = [C.c_void_p, NP, C.c_int, DP, C.c_int, DP]
     lib.wlo_measure_point_csg.argtypes = [NP, C.c_int, C.c_int, RP, R, RP, RP, RP]
+    FN = C.CFUNCTYPE(R, C.c_int, RP, R)
+    lib.FN = FN
+    lib.wlo_mom_step_fn.restype = R
+    lib.wlo_mom_step_fn.argtypes = [C.c_void_p, FN, FN, FN, C.POINTER(C.c_int)]
+    lib.wlo_finish_ic_fn.argtypes = [C.c_void_p, FN]
+    lib.wlo_BC_fn.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), FN, C.c_int, C.POINTER(C.c_int), R]
+    lib.wlo_accelerate_fn.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), R, FN, FN]
+    lib.wlo_apply_fn.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), FN, R]
     _LIBS[key] = lib
     return lib
 
@@ -211,8 +219,15 @@ class OracleSim:
 
     def __init__(self, dims, uBC, L=1.0, *, dt=0.25, nu=0.0, U=None, eps=1.0, perdir=(), exitBC=False,
                  scheme="quick", body=None, u0=None, dtype=np.float32, maxlevels=10, tol=2e-3,
-                 itmx=32, lib=None, build_poisson=True):
+                 itmx=32, lib=None, build_poisson=True, g=None, dUdt=None):
+        """`uBC` may be a function `(i,x,t)` (then `U` is required, WaterLily.jl:98, and `dUdt(i,x,t)` is its time
+        derivative, which the reference takes by ForwardDiff); `g(i,x,t)` is the acceleration field (Flow.jl:69-73)."""
         self.lib = lib or load(dtype)
+        self.uBC_fn = uBC if callable(uBC) else None
+        self.g_fn, self.dUdt_fn = g, dUdt
+        if self.uBC_fn is not None:
+            assert U is not None, "`U` must be specified if `uBC` is a Function"
+            uBC = (0.0,) * len(dims)
         self.dtype = np.float32 if self.lib.real is C.c_float else np.float64
         self.D = len(dims)
         self.dims = tuple(int(n) for n in dims)
@@ -230,6 +245,11 @@ class OracleSim:
         self.n = []
         if u0 is not None:
             self.apply_ic(u0)
+        elif self.uBC_fn is not None:                                  # ic_function(uBC) = (i,x)->uBC(i,x,0)
+            u = self.field("u")
+            ng = (C.c_int * 3)(*([n + 2 for n in self.dims] + [1] * (3 - self.D)))
+            self.lib.wlo_apply_fn(u.ctypes.data, self.D, ng, self._cb(self.uBC_fn), 0.0)
+            self.lib.wlo_finish_ic_fn(self.h, self._cb(self.uBC_fn))
         self._measure(0.0)
         self.nlevels = 0
         if build_poisson:
@@ -275,9 +295,22 @@ class OracleSim:
         u = self.field("u")
         for i in range(self.D):
             u[i][...] = np.broadcast_to(np.asarray(fn(i + 1, self.loc(i + 1)), dtype=self.dtype), u[i].shape)
+        if self.uBC_fn is not None and U is None:
+            self.lib.wlo_finish_ic_fn(self.h, self._cb(self.uBC_fn))
+            return
         U = self.uBC if U is None else U
         arr = (self.lib.real * 3)(*(list(U) + [0.0] * (3 - self.D)))
         self.lib.wlo_finish_ic(self.h, arr)
+
+    def _cb(self, fn):
+        """ctypes thunk for `f(i,x,t)`; None -> null pointer.  Kept alive on the instance."""
+        if fn is None:
+            return self.lib.FN()
+        cache = self.__dict__.setdefault("_cbs", {})
+        if fn not in cache:
+            D, T = self.D, self.dtype
+            cache[fn] = self.lib.FN(lambda i, x, t: float(fn(i, [T(x[k]) for k in range(D)], T(t))))
+        return cache[fn]
 
     # ---- time stepping
     def time(self):
@@ -303,10 +336,14 @@ class OracleSim:
     def mom_step(self, U1=None, acc0=None, acc1=None):
         def arr(v):
             if v is None:
-                return None
+                return self.lib.FN()
             return (self.lib.real * 3)(*(list(v) + [0.0] * (3 - len(v))))
         n = (C.c_int * 2)()
-        dt = self.lib.wlo_mom_step(self.h, arr(U1), arr(acc0), arr(acc1), n)
+        if self.uBC_fn is not None or self.g_fn is not None:
+            assert U1 is None and acc0 is None and acc1 is None
+            dt = self.lib.wlo_mom_step_fn(self.h, self._cb(self.uBC_fn), self._cb(self.g_fn), self._cb(self.dUdt_fn), n)
+        else:
+            dt = self.lib.wlo_mom_step(self.h, arr(U1), arr(acc0), arr(acc1), n)
         self.dts.append(self.dtype(dt))
         self.n += [n[0], n[1]]
         return dt

@@ -231,3 +231,27 @@ def test_meanflow_two_restatements():
         t.append(t[-1] + dt)
     assert np.array_equal(mf.P, P.T) and np.array_equal(mf.U, U.T) and np.array_equal(mf.UU, UU.T)
     assert np.abs(mf.uu()).max() > 0 and [float(x) for x in mf.t] == [float(x) for x in t]
+
+
+# ------------------------------------------------------------------------------------------ Function uBC / g
+@pytest.mark.parametrize("shape,perdir,saveexit", [((7, 6), (), False), ((7, 6), (2,), True), ((5, 6, 4), (3,), False),
+                                                   ((5, 6, 4), (), True)])
+def test_bc_and_accelerate_functions_two_restatements(shape, perdir, saveexit):
+    """BC!(a,uBC::Function,...) (core.jl:201-219) and accelerate!(r,t,g,U) (Flow.jl:69-73) by both restatements."""
+    from test_oracle_fnbc import accel_fn, bc_fn
+    D = len(shape)
+    rng = np.random.default_rng(5)
+    ub = lambda i, x, t: np.float32(0.3 * i) + np.float32(0.1) * x[i % D] * x[(i + 1) % D] + t * x[0]
+    a = rng.standard_normal((D,) + shape[::-1]).astype(np.float32)
+    b = np.ascontiguousarray(a.T).copy()
+    bc_fn(a, ub, saveexit=saveexit, perdir=perdir, t=0.75)
+    r2.BC_fn(b, ub, saveexit, perdir, 0.75)
+    assert np.array_equal(a, b.T)
+    g = lambda i, x, t: np.float32(i) * x[0] - t
+    dU = lambda i, x, t: x[D - 1] * np.float32(0.5)
+    for gg, dd in ((g, None), (None, dU), (g, dU)):
+        a = rng.standard_normal((D,) + shape[::-1]).astype(np.float32)
+        b = np.ascontiguousarray(a.T).copy()
+        accel_fn(a, 0.5, gg, dd)
+        r2.accelerate_fn(b, 0.5, gg, dd)
+        assert np.array_equal(a, b.T)
