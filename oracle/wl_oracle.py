@@ -336,7 +336,7 @@ class OracleSim:
     def mom_step(self, U1=None, acc0=None, acc1=None):
         def arr(v):
             if v is None:
-                return self.lib.FN()
+                return None
             return (self.lib.real * 3)(*(list(v) + [0.0] * (3 - len(v))))
         n = (C.c_int * 2)()
         if self.uBC_fn is not None or self.g_fn is not None:
