@@ -108,3 +108,25 @@ def test_npz_checkpoint(tmp_path):
     assert sim1._dts == sim2._dts and sim2.device_dt == float(sim1._dts[-1])
     with pytest.raises(ValueError):
         wio.load(StubSim((6, 5, 6)), fname="sim1.ckpt", dir=str(tmp_path))
+
+
+def test_slab_pieces_reassemble(tmp_path):
+    """Slab-parallel output: each rank writes its slab as one piece of the whole extent and rank 0 the .pvti index;
+    read back, the pieces give the global arrays (adjacent pieces share one point plane)."""
+    os.chdir(tmp_path)
+    nranks, dims = 2, (6, 5, 8)
+    glob = StubSim(dims, seed=7)
+    w = [wio.VTKWriter("slab", dir="OUT") for _ in range(nranks)]
+    for r in range(nranks):
+        s = StubSim(dims, seed=7)
+        s.rank, s.nranks, s.dims = r, nranks, dims
+        k0, n = waterlily_jl_b200.slab_range(r, nranks, dims[-1])
+        s.f = {k: np.ascontiguousarray(v[..., k0:k0 + n + 2, :, :]) for k, v in glob.f.items()}
+        path = w[r].save(s)
+        w[r].close(rank=r)
+    assert path == "OUT/slab_000000.pvti" and sorted(os.listdir("OUT")) == ["slab_000000.pvti", "slab_000000_r000.vti", "slab_000000_r001.vti"]
+    assert wio.slab_piece(0, 2, 8) == (0, 6, 0) and wio.slab_piece(1, 2, 8) == (5, 5, 1)
+    grid, data = wio.read_pvti(path)
+    assert grid == glob.f["p"].shape
+    assert np.array_equal(data["Pressure"], glob.f["p"]) and np.array_equal(data["Velocity"], glob.f["u"])
+    assert [f for _, f in wio._read_pvd("slab.pvd")] == ["OUT/slab_000000.pvti"]

@@ -20,7 +20,7 @@ import re
 import numpy as np
 
 __all__ = ["save", "load", "save_meanflow", "load_meanflow", "VTKWriter", "load_pvd", "write_vti", "read_vti",
-           "default_attrib"]
+           "write_pvti", "read_pvti", "slab_piece", "default_attrib"]
 
 
 # ------------------------------------------------------------------------------------------------ JLD2 pair
@@ -69,11 +69,12 @@ def load_meanflow(meanflow, fname="WaterLilyMean.npz", dir="./"):
 
 
 # ------------------------------------------------------------------------------------------------ .vti files
-def write_vti(path, point_data, grid=None):
+def write_vti(path, point_data, grid=None, whole_nz=None, k0=0):
     """One ImageData file on the point grid 1:nx × 1:ny (× 1:nz).  `point_data` maps a name to an array shaped
     `grid` = (nz, ny, nx) / (ny, nx) for scalars or (ncomp,) + grid for vectors; vectors are written components-first
     per point (`components_first`, ext/WaterLilyWriteVTKExt.jl:71).  Raw appended binary, UInt64 block headers, no
-    compression.  Without `grid` the lowest-rank array defines it."""
+    compression.  Without `grid` the lowest-rank array defines it.  `whole_nz`/`k0` place the file as one piece
+    (planes k0 .. k0+nz-1) of a taller whole extent: the slab of one rank (see `write_pvti`)."""
     point_data = {k: np.ascontiguousarray(a, np.float32) for k, a in point_data.items()}
     if grid is None:
         grid = min((a.shape for a in point_data.values()), key=len)
@@ -89,10 +90,14 @@ def write_vti(path, point_data, grid=None):
         arrays.append((name, ncomp, flat))
     n = list(grid[::-1]) + [1] * (3 - len(grid))              # nx, ny, nz
     extent = " ".join(f"0 {k - 1}" for k in n)
+    piece = extent
+    if whole_nz is not None:
+        piece = f"0 {n[0] - 1} 0 {n[1] - 1} {k0} {k0 + n[2] - 1}"
+        extent = f"0 {n[0] - 1} 0 {n[1] - 1} 0 {whole_nz - 1}"
     head = ['<?xml version="1.0"?>',
             '<VTKFile type="ImageData" version="1.0" byte_order="LittleEndian" header_type="UInt64">',
             f'  <ImageData WholeExtent="{extent}" Origin="1 1 1" Spacing="1 1 1">',
-            f'    <Piece Extent="{extent}">', '      <PointData>']
+            f'    <Piece Extent="{piece}">', '      <PointData>']
     offset = 0
     for name, ncomp, flat in arrays:
         head.append(f'        <DataArray type="Float32" Name="{name}" NumberOfComponents="{ncomp}" '
@@ -115,7 +120,7 @@ def read_vti(path):
     mark = raw.index(b'<AppendedData encoding="raw">')
     head = raw[:mark].decode()
     blob = raw[raw.index(b"_", mark) + 1:]
-    ext = [int(x) for x in re.search(r'WholeExtent="([^"]+)"', head).group(1).split()]
+    ext = [int(x) for x in re.search(r'<Piece Extent="([^"]+)"', head).group(1).split()]
     n = [ext[2 * k + 1] - ext[2 * k] + 1 for k in range(3)]   # nx, ny, nz
     grid = tuple(n[::-1]) if n[2] > 1 else (n[1], n[0])
     out = {}
@@ -124,6 +129,46 @@ def read_vti(path):
         nbytes = int(np.frombuffer(blob[off:off + 8], "<u8")[0])
         a = np.frombuffer(blob[off + 8:off + 8 + nbytes], "<f4")
         out[name] = a.reshape(grid).copy() if ncomp == 1 else np.moveaxis(a.reshape(grid + (ncomp,)), -1, 0).copy()
+    return grid, out
+
+
+def slab_piece(rank, nranks, nz_global):
+    """Point planes of the GLOBAL grid (0 .. nz_global+1, ghosts included) that rank `rank` writes, as
+    (first plane, number of planes, planes to drop at the start of its local array).  Every rank holds its interior
+    planes plus one ghost plane per side; neighbouring pieces share one point plane (the upper ghost plane of the lower
+    rank), which parallel ImageData needs to leave no gap between pieces."""
+    n = nz_global // nranks
+    k_off = rank * n
+    drop = 0 if rank == 0 else 1
+    return k_off + drop, n + 2 - drop, drop
+
+
+def write_pvti(path, pieces, names, nx, ny, whole_nz):
+    """Parallel ImageData index: `pieces` = [(file, k0, nz)], `names` = {array name: ncomp}."""
+    ext = f"0 {nx - 1} 0 {ny - 1} 0 {whole_nz - 1}"
+    lines = ['<?xml version="1.0"?>', '<VTKFile type="PImageData" version="1.0" byte_order="LittleEndian" header_type="UInt64">',
+             f'  <PImageData WholeExtent="{ext}" GhostLevel="0" Origin="1 1 1" Spacing="1 1 1">', '    <PPointData>']
+    lines += [f'      <PDataArray type="Float32" Name="{k}" NumberOfComponents="{c}"/>' for k, c in names.items()]
+    lines += ['    </PPointData>']
+    lines += [f'    <Piece Extent="0 {nx - 1} 0 {ny - 1} {k0} {k0 + nz - 1}" Source="{os.path.basename(f)}"/>' for f, k0, nz in pieces]
+    lines += ['  </PImageData>', '</VTKFile>', '']
+    with open(path, "w") as fh:
+        fh.write("\n".join(lines))
+    return path
+
+
+def read_pvti(path):
+    """Assemble the global arrays from a `.pvti` and its pieces: (grid, {name: array})."""
+    text = open(path).read()
+    ext = [int(x) for x in re.search(r'WholeExtent="([^"]+)"', text).group(1).split()]
+    grid = (ext[5] + 1, ext[3] + 1, ext[1] + 1)
+    out = {}
+    for m in re.finditer(r'<Piece Extent="([^"]+)" Source="([^"]+)"', text):
+        e = [int(x) for x in m.group(1).split()]
+        _, data = read_vti(os.path.join(os.path.dirname(path), m.group(2)))
+        for name, a in data.items():
+            full = out.setdefault(name, np.zeros(a.shape[:-3] + grid, np.float32))
+            full[..., e[4]:e[5] + 1, :, :] = a
     return grid, out
 
 
@@ -151,13 +196,32 @@ class VTKWriter:
 
     def save(self, sim):
         k = self.count[0]
-        path = os.path.join(self.dir_name, "%s_%06i.vti" % (self.fname, k))
-        write_vti(path, {name: fn(sim) for name, fn in self.output_attrib.items()}, grid=sim.field_shape("p"))
+        data = {name: np.asarray(fn(sim), np.float32) for name, fn in self.output_attrib.items()}
+        grid = tuple(sim.field_shape("p"))
+        nranks = getattr(sim, "nranks", 1)
+        if nranks == 1:
+            path = os.path.join(self.dir_name, "%s_%06i.vti" % (self.fname, k))
+            write_vti(path, data, grid=grid)
+        else:
+            # slab decomposition: every rank writes its own piece, nothing is gathered;
+            # rank 0 adds the .pvti index and owns the collection file
+            nz_g = sim.dims[-1]
+            k0, nz, drop = slab_piece(sim.rank, nranks, nz_g)
+            piece = os.path.join(self.dir_name, "%s_%06i_r%03i.vti" % (self.fname, k, sim.rank))
+            write_vti(piece, {n_: a[..., drop:, :, :] for n_, a in data.items()}, grid=(nz,) + grid[1:], whole_nz=nz_g + 2, k0=k0)
+            path = os.path.join(self.dir_name, "%s_%06i.pvti" % (self.fname, k))
+            if sim.rank == 0:
+                pieces = [(os.path.join(self.dir_name, "%s_%06i_r%03i.vti" % (self.fname, k, r)),) + slab_piece(r, nranks, nz_g)[:2]
+                          for r in range(nranks)]
+                write_pvti(path, pieces, {n_: (1 if a.shape == grid else a.shape[0]) for n_, a in data.items()},
+                           grid[-1], grid[-2], nz_g + 2)
         self.count[0] = k + 1
         self.entries.append((round(float(sim.sim_time()), 4), path))
         return path
 
-    def close(self):
+    def close(self, rank=0):
+        if rank != 0:                                      # slab runs: rank 0 writes the collection
+            return
         lines = ['<?xml version="1.0"?>', '<VTKFile type="Collection" version="1.0" byte_order="LittleEndian">',
                  '  <Collection>']
         lines += [f'    <DataSet timestep="{t!r}" part="0" file="{f}"/>' for t, f in self.entries]
