@@ -71,9 +71,9 @@ def test_vti_round_trip_and_layout(tmp_path, dims):
     assert np.array_equal(first[len(dims):], sim.f["u"][(slice(None),) + idx1])
 
 
-def test_writer_collection_and_restart(tmp_path):
+def test_writer_collection_and_restart(tmp_path, monkeypatch):
     """vtkWriter / save! / close and load!(sim, Val(:pvd)) (test/test_ioext.jl:11-26)."""
-    os.chdir(tmp_path)
+    monkeypatch.chdir(tmp_path)
     sim = StubSim((6, 5, 4), seed=1)
     w = wio.VTKWriter("run", dir="TEST_DIR")
     w.save(sim)
@@ -110,10 +110,10 @@ def test_npz_checkpoint(tmp_path):
         wio.load(StubSim((6, 5, 6)), fname="sim1.ckpt", dir=str(tmp_path))
 
 
-def test_slab_pieces_reassemble(tmp_path):
+def test_slab_pieces_reassemble(tmp_path, monkeypatch):
     """Slab-parallel output: each rank writes its slab as one piece of the whole extent and rank 0 the .pvti index;
     read back, the pieces give the global arrays (adjacent pieces share one point plane)."""
-    os.chdir(tmp_path)
+    monkeypatch.chdir(tmp_path)
     nranks, dims = 2, (6, 5, 8)
     glob = StubSim(dims, seed=7)
     w = [wio.VTKWriter("slab", dir="OUT") for _ in range(nranks)]

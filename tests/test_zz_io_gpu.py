@@ -23,9 +23,9 @@ def sphere_sim(wl, D, L=16):
 
 
 @pytest.mark.parametrize("D", [2, 3])
-def test_vtk_restart(wl, D, tmp_path):
+def test_vtk_restart(wl, D, tmp_path, monkeypatch):
     from waterlily_jl_b200 import io as wio
-    os.chdir(tmp_path)
+    monkeypatch.chdir(tmp_path)
     sim = sphere_sim(wl, D)
     wr = wio.VTKWriter(f"test_vtk_reader_{D}", dir="TEST_DIR")
     sim.sim_step(1.0)
