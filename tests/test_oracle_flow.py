@@ -158,3 +158,46 @@ def test_sim_time_stop():
     assert sim.sim_time() == 0
     sim.sim_step(0.1, remeasure=False)
     assert sim.sim_time() >= 0.1 > float(np.sum(sim.dts[:-2])) * sim.U / sim.L
+
+
+def test_metrics_moments_and_viscous_known_answers():
+    """test/test_metrics.jl:41-64: zero velocity gives zero viscous force and moment; a hydrostatic pressure field has no
+    moment about the disc/sphere centre; a uniform-gradient or pure-shear velocity gives no net viscous force on a
+    closed surface."""
+    N = 32
+    for D in (2, 3):
+        dims = (N - 2,) * D
+        c = (N / 2,) * D
+        sim = wo.OracleSim(dims, (0.0,) * D, dtype=np.float64, nu=1.0, build_poisson=False,
+                           body=wo.make_body("sphere", c, N // 4))
+        u, p = sim.field("u"), sim.field("p")
+        u[...] = 0
+        assert np.all(sim.viscous_force(0.0) == 0) and np.all(sim.moment(c, True, 0.0) == 0)
+        p[...] = np.broadcast_to(sim.loc(0)[1], p.shape)                        # apply!(x->x[2], p)
+        m = sim.moment(c, False, 0.0)
+        assert np.all(np.abs(m) < 1e-9 * np.pi * (N / 4) ** D), m
+        for fld in (lambda i: sim.loc(i + 1)[i], lambda i: sim.loc(i + 1)[(i + 1) % D]):   # x[i] ; x[i%D+1]
+            for i in range(D):
+                u[i][...] = np.broadcast_to(fld(i), u[i].shape)
+            f = sim.viscous_force(0.0)
+            assert np.all(np.abs(f) < 1e-9 * N ** (D - 1)), f
+
+
+def test_meanflow_of_a_steady_boundary_layer():
+    """test/test_metrics.jl:66-92: the parabolic-inflow boundary-layer flow (a Function uBC) is steady, so the running
+    averages equal the instantaneous fields to √eps; uu(); time bookkeeping; reset!."""
+    L = 32
+    prof = lambda i, x, t: np.float32(4.0 * (((x[1] + 0.5) / (2 * L)) - ((x[1] + 0.5) / (2 * L)) ** 2)) if i == 1 else 0.0
+    sim = wo.OracleSim((L, L), prof, L, nu=0.001, U=1)
+    mf = wo.MeanFlow(sim, uu_stats=True)
+    for t in np.arange(0, 10.0001, 0.1):
+        sim.sim_step(t)
+        mf.update()
+    tol = float(np.sqrt(np.finfo(np.float32).eps))
+    u, p = sim.field("u"), sim.field("p")
+    assert np.allclose(u, mf.U, rtol=0, atol=tol) and np.allclose(p, mf.P, rtol=0, atol=tol)
+    for i in range(2):
+        for j in range(2):
+            assert np.allclose(u[i] * u[j], mf.UU[j][i], rtol=0, atol=tol)
+            assert np.allclose(mf.UU[j][i] - mf.U[i] * mf.U[j], mf.uu()[j][i], rtol=0, atol=tol)
+    assert np.float32(sim.time()) == np.float32(mf.time())
