@@ -125,3 +125,21 @@ def test_measure_csg_two_restatements(dims, mk, exitBC, perdir):
     for nm in ("V", "mu0", "mu1"):
         a, c = sim.field(nm), fl[nm].T
         assert np.allclose(a, c, rtol=0, atol=5e-6), (nm, np.abs(a - c).max())
+
+
+@pytest.mark.parametrize("exitBC", [True, False])
+def test_rotating_plate_simulation(exitBC):
+    """test/test_simulation.jl:32-36 ("non-uniform V doesn't break"): a plate (capsule of half-length radius-2 and
+    thickness radius 2) under `rotate(x,t) = R(t/radius+1)·(x − 2radius)`, i.e. a RigidMap with θ(t) = t/radius+1 and
+    ω = 1/radius, impulsively started in still fluid: two Poisson solves of < 5 iterations and 0.5 < Δt < 1."""
+    radius = 8
+    nu = radius / 250
+    theta = lambda t: np.float32(t / radius + 1)
+    plate = L("capsule", (2 * radius, 2 * radius), theta(0.0), radius=2, minor=radius - 2, axis=0, omega=1 / radius)
+    sim = wo.OracleSim((4 * radius, 4 * radius), (0.0, 0.0), radius, U=1, body=plate, nu=nu, exitBC=exitBC)
+    sim.body = sim.body.setmap(theta=theta(float(np.sum(sim.dts))))      # measure!(sim) at t = sum(Δt)
+    sim.sim_step()
+    assert len(sim.n) == 2 and all(n < 5 for n in sim.n), sim.n
+    assert 1 > sim.dts[-1] > 0.5, sim.dts
+    V = sim.field("V")
+    assert V.max() > 0.5 and abs(V.max() + V.min()) < 0.2                 # |V| = ω·r up to the plate tip, both senses
