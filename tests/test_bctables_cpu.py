@@ -1,0 +1,69 @@
+"""The table form of Function boundary data (waterlily.jl_b200/bctables.py) carries everything BC!/accelerate! need:
+applying the tables pass by pass (component outer, direction inner, like core.jl:203-218) reproduces the oracle's
+function-valued `BC!` and `accelerate!` bit for bit."""
+import numpy as np
+import pytest
+
+import waterlily_jl_b200  # noqa: F401
+from waterlily_jl_b200 import bctables as bt
+from test_oracle_fnbc import accel_fn, bc_fn
+
+
+def apply_tables(a, tables, saveexit, perdir):
+    """BC! driven by tables; `a` shaped (D, [nz,] ny, nx)."""
+    D = a.shape[0]
+    for i in range(D):
+        for j in range(D):
+            ax = D - 1 - j
+            v = np.moveaxis(a[i], ax, 0)                     # v[k] = plane k of direction j (a view)
+            if (j + 1) in perdir:
+                v[0] = v[-2]
+                v[-1] = v[1]
+            elif i == j:
+                tb = tables[i, j]
+                v[0], v[1] = tb["lo0"], tb["lo1"]
+                if not saveexit or i > 0:
+                    v[-1] = tb["hi"]
+            else:
+                tb = tables[i, j]
+                v[0] = v[1] + tb["dlo"]
+                v[-1] = v[-2] + tb["dhi"]
+
+
+CASES = [((7, 6), (), False), ((7, 6), (2,), True), ((5, 6, 4), (3,), False), ((5, 6, 4), (), True), ((5, 6, 4), (1, 2), False)]
+
+
+@pytest.mark.parametrize("dims,perdir,saveexit", CASES)
+def test_tables_reproduce_function_bc(dims, perdir, saveexit):
+    D = len(dims)
+    rng = np.random.default_rng(11)
+    ub = lambda i, x, t: np.float32(0.3 * i) + np.float32(0.1) * x[i % D] * x[(i + 1) % D] + t * x[0]
+    a = rng.standard_normal((D,) + tuple(n + 2 for n in dims[::-1])).astype(np.float32)
+    b = a.copy()
+    bc_fn(a, ub, saveexit=saveexit, perdir=perdir, t=0.75)
+    apply_tables(b, bt.bc_tables(ub, dims, 0.75, perdir), saveexit, perdir)
+    assert np.array_equal(a, b)
+    # a boundary value that does not vary along the tangential direction keeps the exact copy
+    const = lambda i, x, t: np.float32(1.0 if i == 1 else 0.5) + 0 * x[0]
+    tb = bt.bc_tables(const, dims, 0.0, perdir)
+    assert all(np.all(v["dlo"] == 0) and np.all(v["dhi"] == 0) for (i, j), v in tb.items() if i != j)
+
+
+def test_scalar_only_closures_and_acceleration():
+    dims = (6, 5)
+    ub = lambda i, x, t: t if i == 1 else (np.float32(0.25) * x[0] if x[1] > 2 else np.float32(0))   # Python `if`: not vectorisable
+    rng = np.random.default_rng(12)
+    a = rng.standard_normal((2, 7, 8)).astype(np.float32)
+    b = a.copy()
+    bc_fn(a, ub, t=0.5)
+    apply_tables(b, bt.bc_tables(ub, dims, 0.5), False, ())
+    assert np.array_equal(a, b)
+    g = lambda i, x, t: np.float32(i) * x[0] - t
+    dU = lambda i, x, t: x[1] * np.float32(0.5)
+    for gg, dd in ((g, None), (None, dU), (g, dU)):
+        r = rng.standard_normal((2, 7, 8)).astype(np.float32)
+        q = r.copy()
+        accel_fn(r, 0.5, gg, dd)
+        q += bt.accel_field(gg, dd, dims, 0.5)
+        assert np.array_equal(r, q)
+    assert bt.accel_field(None, None, dims, 0.0) is None
