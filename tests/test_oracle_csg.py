@@ -143,3 +143,41 @@ def test_rotating_plate_simulation(exitBC):
     assert 1 > sim.dts[-1] > 0.5, sim.dts
     V = sim.field("V")
     assert V.max() > 0.5 and abs(V.max() + V.min()) < 0.2                 # |V| = ω·r up to the plate tip, both senses
+
+
+def _random_body(rng, D, depth=0):
+    """A random SetBody tree of at most 8 postfix nodes over random RigidMap leaves."""
+    kinds = ["sphere", "cylinder", "torus", "capsule"] if D == 3 else ["circle", "capsule"]
+
+    def leaf():
+        k = kinds[rng.integers(len(kinds))]
+        v = lambda s: tuple(float(x) for x in rng.uniform(-s, s, D))
+        th = tuple(float(x) for x in rng.uniform(-1.5, 1.5, 3)) if D == 3 else float(rng.uniform(-3, 3))
+        om = tuple(float(x) for x in rng.uniform(-0.2, 0.2, 3)) if D == 3 else float(rng.uniform(-0.2, 0.2))
+        return L(k, v(2.0), th, xp=v(1.0), V=v(0.5), omega=om, radius=float(rng.uniform(1.0, 3.0)),
+                 minor=float(rng.uniform(0.3, 1.5)), axis=int(rng.integers(D)))
+    b = leaf()
+    while len(b.prog) < 6 and rng.random() < 0.7:
+        op = rng.integers(4)
+        b = -b if op == 3 else (b + leaf() if op == 0 else b & leaf() if op == 1 else b - leaf())
+    return b if len(b.prog) <= 8 else leaf()
+
+
+@pytest.mark.parametrize("D", [2, 3])
+def test_random_programs_two_restatements(D):
+    """Random trees × random points × both fastd² regimes: C++ stack machine vs the recursive Python restatement
+    (lexicographic tuple min/max, complement, the fastd² early return per leaf)."""
+    rng = np.random.default_rng(100 + D)
+    n_checked = 0
+    for _ in range(40):
+        body = _random_body(rng, D)
+        tree = _tree(body)
+        for _ in range(25):
+            x = [np.float32(v) for v in rng.uniform(-5, 5, D)]
+            for fd2 in (np.float32(9.0), np.float32(0.0), np.float32(np.inf)):
+                d, n, V = wo.measure_point_csg(body, x, fastd2=fd2)
+                d2, n2, V2 = r2.measure_set(tree, x, fd2)
+                assert np.isclose(d, d2, rtol=2e-6, atol=2e-6), (body.prog, x, d, d2)
+                assert np.allclose(n, n2, rtol=0, atol=5e-6) and np.allclose(V, V2, rtol=0, atol=5e-6), (body.prog, x)
+                n_checked += 1
+    assert n_checked == 40 * 25 * 3
