@@ -53,6 +53,22 @@ def cases():
     return out
 
 
+def widened_cases():
+    """Rows added after the first fixtures: name -> (runner(leaf ctor, Simulation ctor) -> sim, has body).
+    Frozen for the oracle here; the CUDA path is compared with the live oracle in tests/test_parity_gpu.py
+    (`test_csg_rigid_bodies`) until these fixtures have been run against it on the box."""
+    def rotating_annulus_with_capsule(leaf, Sim):
+        ring = leaf("circle", (14.0, 12.0), 0.3, radius=6.0, omega=0.05) - leaf("circle", (14.0, 12.0), 0.3, radius=3.0, omega=0.05)
+        body = ring + leaf("capsule", (22.0, 6.0), -0.4, radius=1.5, minor=3.0, axis=0, V=(0.0, 0.1))
+        sim = Sim((32, 24), (1.0, 0.0), 8.0, body=body, nu=0.05)
+        for n in range(6):
+            th = np.float32(0.3) + np.float32(0.05) * np.float32(sum(sim.flow_dts()))
+            sim.body = sim.body.setmap(theta=float(th))
+            sim.sim_step(remeasure=True)
+        return sim
+    return {"E_csg_annulus_capsule_32x24": rotating_annulus_with_capsule}
+
+
 def build(mod, make_body, kw):
     """Instantiate `mod.Simulation`-like object (oracle or CUDA mirror) from a case description."""
     kw = dict(kw)
@@ -76,6 +92,18 @@ def main():
         np.savez_compressed(path, u=sim.field("u"), p=sim.field("p"), dt=np.asarray(sim.dts, np.float32),
                             n=np.asarray(sim.n, np.int16), force=np.asarray(force, np.float64))
         print(name, os.path.getsize(path), "bytes", "n =", sim.n[-4:], "dt =", sim.dts[-1])
+    for name, run in widened_cases().items():
+        sim = run(wo.CsgBody.leaf, _OracleWithDts)
+        path = os.path.join(HERE, name + ".npz")
+        np.savez_compressed(path, u=sim.field("u"), p=sim.field("p"), dt=np.asarray(sim.dts, np.float32),
+                            n=np.asarray(sim.n, np.int16), force=np.asarray(sim.pressure_force(), np.float64),
+                            mu0=sim.field("mu0"), V=sim.field("V"))
+        print(name, os.path.getsize(path), "bytes", "n =", sim.n[-4:], "dt =", sim.dts[-1])
+
+
+class _OracleWithDts(wo.OracleSim):
+    def flow_dts(self):
+        return [float(x) for x in self.dts]
 
 
 if __name__ == "__main__":

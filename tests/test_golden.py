@@ -33,3 +33,11 @@ def test_oracle_reproduces_golden(name):
         sim.sim_step(remeasure=remeasure)
     force = sim.pressure_force() if body is not None else np.zeros(len(dims))
     compare(name, sim.field("u"), sim.field("p"), sim.dts, sim.n, force)
+
+
+@pytest.mark.parametrize("name", sorted(mg.widened_cases()))
+def test_oracle_reproduces_widened_golden(name):
+    sim = mg.widened_cases()[name](wo.CsgBody.leaf, mg._OracleWithDts)
+    compare(name, sim.field("u"), sim.field("p"), sim.dts, sim.n, sim.pressure_force())
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    assert float(np.abs(sim.field("mu0") - g["mu0"]).max()) <= 2e-6 and float(np.abs(sim.field("V") - g["V"]).max()) <= 2e-6
