@@ -11,7 +11,7 @@ the points the reference's `BC!` (src/core.jl:201-219) and `accelerate!` (src/Fl
 
 Each table is a numpy array shaped like the field with axis j removed, in the mirror's (z, y, x) order.  The tables are
 what a device-side BC!/accelerate! consumes (one upload per step when the data depend on t, once otherwise);
-`tests/test_bctables_cpu.py` shows that applying them pass by pass reproduces the oracle's `BC!`/`accelerate!` with
+`tests/test_bctables_cpu.py` shows that applying them pass by pass reproduces the CPU checker's `BC!`/`accelerate!` with
 functions bit for bit.  The device kernels that consume them are not built yet.
 """
 import numpy as np
