@@ -67,3 +67,60 @@ def test_scalar_only_closures_and_acceleration():
         q += bt.accel_field(gg, dd, dims, 0.5)
         assert np.array_equal(r, q)
     assert bt.accel_field(None, None, dims, 0.0) is None
+
+
+def resolve(a, tables, ci, c, saveexit, perdir):
+    """The per-cell form a fused device BC! needs (the constant-uBC kernel k_bc_vec already works this way): instead
+    of D² sequential passes, walk the passes BACKWARDS from the cell, collecting the tangential differences met on
+    the way, until a Dirichlet table value or an untouched cell is reached; then add the differences in pass order.
+    `c` is (x, y[, z]); arrays are indexed [z][y][x]."""
+    D = a.shape[0]
+    N = a.shape[1:][::-1]
+    c = list(c)
+    ds = []
+    at = lambda tb, dj: tb[tuple(c[d] for d in range(D - 1, -1, -1) if d != dj)]      # in-plane index, (z, y, x) order
+    base = None
+    for dj in range(D - 1, -1, -1):
+        x, n = c[dj], N[dj]
+        if (dj + 1) in perdir:
+            if x == 0:
+                c[dj] = n - 2
+            elif x == n - 1:
+                c[dj] = 1
+        elif ci == dj:
+            tb = tables[ci, dj]
+            if x <= 1:
+                base = at(tb["lo0"] if x == 0 else tb["lo1"], dj)
+                break
+            if x == n - 1 and not (saveexit and ci == 0):
+                base = at(tb["hi"], dj)
+                break
+        else:
+            tb = tables[ci, dj]
+            if x == 0:
+                ds.append(at(tb["dlo"], dj))
+                c[dj] = 1
+            elif x == n - 1:
+                ds.append(at(tb["dhi"], dj))
+                c[dj] = n - 2
+    if base is None:
+        base = a[(ci,) + tuple(c[::-1])]
+    for d in reversed(ds):                                   # lowest direction first, like the sequential passes
+        base = np.float32(base + d)
+    return base
+
+
+@pytest.mark.parametrize("dims,perdir,saveexit", CASES)
+def test_backward_walk_equals_sequential_passes(dims, perdir, saveexit):
+    D = len(dims)
+    rng = np.random.default_rng(13)
+    ub = lambda i, x, t: np.float32(0.3 * i) + np.float32(0.1) * x[i % D] * x[(i + 1) % D] + t * x[0]
+    a = rng.standard_normal((D,) + tuple(n + 2 for n in dims[::-1])).astype(np.float32)
+    tables = bt.bc_tables(ub, dims, 0.25, perdir)
+    seq = a.copy()
+    apply_tables(seq, tables, saveexit, perdir)
+    out = a.copy()
+    for ci in range(D):
+        for idx in np.ndindex(*a.shape[1:]):
+            out[(ci,) + idx] = resolve(a, tables, ci, idx[::-1], saveexit, perdir)
+    assert np.array_equal(out, seq)
