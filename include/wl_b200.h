@@ -138,6 +138,19 @@ int wl_nlevels(const wl_sim* s);
 int wl_finish_ic(wl_sim* s, const float uBC[3]);
 
 /* ---- body: measure!(flow,body;t,ϵ) (src/Body.jl:28-51)                                      */
+/* Function `uBC(i,x,t)` (src/core.jl:201-219; the Flow ctor and `mom_step!` call `BC!(a.u,a.uBC,a.exitBC,a.perdir,t)`,
+ * src/Flow.jl:141,195,209,231).  A closure cannot cross this boundary, so the caller samples it at the points BC!
+ * evaluates it at and hands over the table; every later BC! on the velocity (wl_finish_ic, wl_mom_step) uses it
+ * until it is replaced or cleared (tables == NULL).  Layout: for component ci (outer) and direction dj (inner),
+ * three planes over the other dims, ghosts included, lowest remaining dim fastest:
+ *   ci == dj: uBC at index 0, 1 and n-1 of dj;   ci != dj: uBC(I)-uBC(I+e_dj) at index 0, (unused), uBC(I)-uBC(I-e_dj)
+ *   at index n-1.  Periodic directions keep their (ignored) slots.  `wl_bc_table_size` gives the element count.
+ * STATUS: built and checked against the CPU restatement of the same table walk; NOT YET RUN on a B200 (its GPU test
+ * is gated behind WL_RUN_UNVERIFIED=1).  `∂ₜuBC` and `g(i,x,t)` in `accelerate!` (src/Flow.jl:69-73) are not wired:
+ * only boundary data that do not depend on t are complete.  Single GPU only. */
+int wl_bc_table_size(const wl_sim* s, size_t* count);
+int wl_set_bc_tables(wl_sim* s, const float* tables, size_t count);
+
 int wl_measure_body(wl_sim* s, const wl_body* body, double t, double eps);
 /* host-measured coefficients (values BEFORE the two BC! calls of Body.jl:49-50, which are applied here) */
 int wl_set_body_coeffs(wl_sim* s, const float* mu0, const float* mu1, const float* V, const float* sdf);

@@ -124,3 +124,63 @@ def test_backward_walk_equals_sequential_passes(dims, perdir, saveexit):
         for idx in np.ndindex(*a.shape[1:]):
             out[(ci,) + idx] = resolve(a, tables, ci, idx[::-1], saveexit, perdir)
     assert np.array_equal(out, seq)
+
+
+def resolve_flat(a, flat, ci, c, saveexit, per):
+    """`bc_resolve_tab` of wl_kernels_mom.cuh transliterated (same offsets, plane sizes and in-plane index) on the
+    packed array `wl_set_bc_tables` receives: checks the packing against the kernel's addressing."""
+    D = a.shape[0]
+    N = list(a.shape[1:][::-1]) + [1] * (3 - D)
+    psz = [N[0] * N[1] * N[2] // N[dj] if dj < D else 0 for dj in range(3)]
+    off, o = {}, 0
+    for i in range(D):
+        for j in range(D):
+            off[i * D + j] = o
+            o += 3 * psz[j]
+    c = list(c) + [0] * (3 - D)
+    ds, base, have = [], None, False
+    for dj in range(D - 1, -1, -1):
+        if have:
+            continue
+        x, n = c[dj], N[dj]
+        if per[dj]:
+            c[dj] = n - 2 if x == 0 else 1 if x == n - 1 else x
+            continue
+        ia, ib = (1 if dj == 0 else 0), (1 if dj == 2 else 2)
+        idx = c[ia] + (N[ia] * c[ib] if D == 3 else 0)
+        T, ps = off[ci * D + dj], psz[dj]
+        if ci == dj:
+            if x <= 1:
+                base, have = flat[T + (0 if x == 0 else ps) + idx], True
+            elif x == n - 1 and not (saveexit and ci == 0):
+                base, have = flat[T + 2 * ps + idx], True
+        else:
+            if x == 0:
+                ds.append(flat[T + idx]); c[dj] = 1
+            elif x == n - 1:
+                ds.append(flat[T + 2 * ps + idx]); c[dj] = n - 2
+    if not have:
+        base = a[(ci,) + tuple(c[:D][::-1])]
+    if len(ds) == 2:
+        base = np.float32(base + ds[1])
+    if len(ds) >= 1:
+        base = np.float32(base + ds[0])
+    return base
+
+
+@pytest.mark.parametrize("dims,perdir,saveexit", CASES)
+def test_packed_tables_match_kernel_addressing(dims, perdir, saveexit):
+    D = len(dims)
+    rng = np.random.default_rng(14)
+    ub = lambda i, x, t: np.float32(0.3 * i) + np.float32(0.1) * x[i % D] * x[(i + 1) % D] + t * x[0]
+    a = rng.standard_normal((D,) + tuple(n + 2 for n in dims[::-1])).astype(np.float32)
+    tables = bt.bc_tables(ub, dims, 0.25, perdir)
+    flat = bt.pack(tables, dims)
+    seq = a.copy()
+    apply_tables(seq, tables, saveexit, perdir)
+    per = [(d + 1) in perdir for d in range(3)]
+    out = a.copy()
+    for ci in range(D):
+        for idx in np.ndindex(*a.shape[1:]):
+            out[(ci,) + idx] = resolve_flat(a, flat, ci, idx[::-1], saveexit, per)
+    assert np.array_equal(out, seq)

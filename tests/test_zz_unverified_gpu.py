@@ -1,0 +1,64 @@
+"""GPU tests of entry points that were built after the round's GPU budget was spent: they have NOT been run on a B200
+yet and are therefore switched off unless WL_RUN_UNVERIFIED=1.  First thing to run next round:
+    WL_RUN_UNVERIFIED=1 python -m pytest tests/test_zz_unverified_gpu.py -m gpu -x -q
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import wl_oracle as wo
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(os.environ.get("WL_RUN_UNVERIFIED") != "1", reason="not yet run on a B200; set WL_RUN_UNVERIFIED=1")]
+
+
+@pytest.fixture(scope="module")
+def wl():
+    import __graft_entry__ as ge
+    ge.build()
+    import waterlily_jl_b200 as wl
+    return wl
+
+
+def profile(L):
+    return lambda i, x, t: (np.float32(4.0) * (((x[1] + np.float32(0.5)) / np.float32(2 * L)) - ((x[1] + np.float32(0.5)) / np.float32(2 * L)) ** 2)
+                            if i == 1 else 0 * x[0])
+
+
+@pytest.mark.parametrize("exitBC", [False, True])
+def test_boundary_layer_profile_tables(wl, exitBC):
+    """make_bl_flow (test/helper.jl:18-21, test/test_flow.jl:134-140): parabolic inflow as a Function uBC through
+    wl_set_bc_tables, CUDA vs oracle over 20 steps."""
+    L = 32
+    prof = profile(L)
+    sim = wl.Simulation((L, L), (0.0, 0.0), L, nu=0.001, U=1, exitBC=exitBC)
+    sim.set_bc_function(prof)
+    sim.apply_ic(lambda i, x: prof(i, x, np.float32(0)))
+    ref = wo.OracleSim((L, L), lambda i, x, t: float(prof(i, x, t)), L, nu=0.001, U=1, exitBC=exitBC)
+    assert np.array_equal(sim.flow.u, ref.field("u"))
+    for _ in range(20):
+        sim.sim_step()
+        ref.sim_step()
+    assert sim.pois.n == ref.n
+    assert np.allclose(sim.flow.Δt, ref.dts, rtol=2e-6)
+    assert float(np.abs(sim.flow.u - ref.field("u")).max()) <= 1e-6
+    u = sim.flow.u
+    assert np.allclose(u[0][:, 0], u[0][:, -1], rtol=float(np.sqrt(np.finfo(np.float32).eps)), atol=0) or exitBC
+
+
+def test_bc_tables_3d_kernel(wl):
+    """One BC! with a space-varying uBC on random data, 3D with a periodic direction: CUDA table kernel vs oracle BC_fn."""
+    from test_oracle_fnbc import bc_fn
+    dims = (8, 6, 4)
+    ub = lambda i, x, t: np.float32(0.3 * i) + np.float32(0.1) * x[i % 3] * x[(i + 1) % 3]
+    for perdir, exitBC in (((), False), ((3,), True), ((1, 2), False)):
+        sim = wl.Simulation(dims, (0.0, 0.0, 0.0), 4.0, U=1, perdir=perdir, exitBC=exitBC)
+        sim.set_bc_function(ub)
+        a = np.random.default_rng(3).standard_normal(sim.field_shape("u")).astype(np.float32)
+        sim.upload("u", a)
+        sim.debug_op(0)                                   # BC!(u, uBC, exitBC, perdir)
+        b = a.copy()
+        bc_fn(b, lambda i, x, t: float(ub(i, x, t)), saveexit=exitBC, perdir=perdir)
+        assert np.array_equal(sim.flow.u, b), (perdir, exitBC)
+        sim.set_bc_function(None)

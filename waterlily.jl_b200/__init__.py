@@ -33,7 +33,7 @@ KINDS = dict(none=0, sphere=1, circle=1, cylinder=2, torus=3)
 # symbols include/wl_b200.h declares (tests check the library exports every one of them)
 ABI_SYMBOLS = [
     "wl_create", "wl_destroy", "wl_last_error", "wl_version", "wl_field_dims", "wl_download",
-    "wl_upload", "wl_nlevels", "wl_finish_ic", "wl_measure_body", "wl_set_body_coeffs",
+    "wl_upload", "wl_nlevels", "wl_finish_ic", "wl_bc_table_size", "wl_set_bc_tables", "wl_measure_body", "wl_set_body_coeffs",
     "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_poisson_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
     "wl_cfl", "wl_pressure_force", "wl_viscous_force", "wl_force_moment", "wl_measure_csg", "wl_pressure_force_csg",
     "wl_viscous_force_csg", "wl_force_moment_csg", "wl_meanflow_init", "wl_meanflow_update", "wl_meanflow_copy_to_flow", "wl_sync", "wl_launch_count", "wl_enable_timing",
@@ -110,6 +110,8 @@ def load_library(path=None):
     lib.wl_nlevels.argtypes = [P]
     lib.wl_finish_ic.argtypes = [P, FP]
     lib.wl_measure_body.argtypes = [P, C.POINTER(WLBody), C.c_double, C.c_double]
+    lib.wl_bc_table_size.argtypes = [P, C.POINTER(C.c_size_t)]
+    lib.wl_set_bc_tables.argtypes = [P, C.c_void_p, C.c_size_t]
     lib.wl_set_body_coeffs.argtypes = [P, P, P, P, P]
     lib.wl_build_poisson.argtypes = [P]
     lib.wl_update_poisson.argtypes = [P]
@@ -425,6 +427,21 @@ class Simulation:
             u[i][...] = np.broadcast_to(np.asarray(fn(i + 1, self.loc(i + 1)), dtype=np.float32), shape[1:])
         self.upload("u", u)
         self._check(self.lib.wl_finish_ic(self.h, _v3f(self.uBC if U is None else U)))
+
+    def set_bc_function(self, uBC, t=0.0):
+        """Boundary data from a Function `uBC(i,x,t)` (src/core.jl:201-219), sampled on the host into the tables
+        `wl_set_bc_tables` takes; `None` returns to the constant tuple.  Data that depend on `t` must be re-sampled
+        by the caller before each step (at t₁ = sum(Δt)), and their `∂ₜuBC` term in `accelerate!` is not wired yet.
+        NOT YET RUN on a B200 (see include/wl_b200.h)."""
+        if uBC is None:
+            self._check(self.lib.wl_set_bc_tables(self.h, None, 0))
+            return
+        from . import bctables
+        flat = bctables.pack(bctables.bc_tables(uBC, self.dims, t, self.perdir), self.dims)
+        n = C.c_size_t()
+        self._check(self.lib.wl_bc_table_size(self.h, C.byref(n)))
+        assert flat.size == n.value, (flat.size, n.value)
+        self._check(self.lib.wl_set_bc_tables(self.h, flat.ctypes.data, flat.size))
 
     # ---- reference API
     def time(self):

@@ -79,3 +79,25 @@ def accel_field(g, dUdt, dims, t, dtype=np.float32):
         else:
             out[i] = _eval(g if g is not None else dUdt, i, x, t, full, dtype)
     return out
+
+
+def pack(tables, dims):
+    """The flat array `wl_set_bc_tables` takes (include/wl_b200.h): component outer, direction inner, three planes each
+    (`lo0, lo1, hi` or `dlo, 0, dhi`; zeros for periodic directions), every plane in (z, y, x)-minus-j C order."""
+    D = len(dims)
+    full = tuple(n + 2 for n in dims[::-1])
+    parts = []
+    for i in range(D):
+        for j in range(D):
+            shape = tuple(full[a] for a in range(D) if a != D - 1 - j)
+            tb = tables.get((i, j))
+            if tb is None:
+                planes = [np.zeros(shape, np.float32)] * 3
+            elif i == j:
+                planes = [tb["lo0"], tb["lo1"], tb["hi"]]
+            else:
+                planes = [tb["dlo"], np.zeros(shape, np.float32), tb["dhi"]]
+            for p in planes:
+                assert p.shape == shape, (p.shape, shape)
+                parts.append(np.ascontiguousarray(p, np.float32).ravel())
+    return np.concatenate(parts)

@@ -362,6 +362,7 @@ void wl_destroy(wl_sim* s) {
   if (s->dist.comm) ncclCommDestroy(s->dist.comm);
   if (s->d_redg) cudaFree(s->d_redg);
   if (s->stage) cudaFree(s->stage);
+  if (s->bc_tab) cudaFree(s->bc_tab);
   if (s->h_redg) cudaFreeHost(s->h_redg);
   for (size_t l = 0; l < s->lv.size(); ++l) {
     Level& v = s->lv[l];
@@ -485,6 +486,40 @@ static int measure_impl(wl_sim* s, const B& body, double eps, const char* what) 
   return check_async(s, what);
 }
 }  // extern "C++"
+
+int wl_bc_table_size(const wl_sim* s, size_t* count) {
+  if (!s || !count) return WL_ERR_INVALID;
+  const int N[3] = {s->lay.n0, s->lay.n1, s->D == 3 ? s->lay.n2 : 1};
+  size_t tot = 0;
+  for (int dj = 0; dj < s->D; ++dj) tot += (size_t)3 * s->D * ((size_t)N[0] * N[1] * N[2] / N[dj]);
+  *count = tot;
+  return WL_OK;
+}
+
+int wl_set_bc_tables(wl_sim* s, const float* tables, size_t count) {
+  if (!s) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  if (!tables) {                                      // back to the constant uBC of the configuration
+    WL_CUDA(s, cudaStreamSynchronize(s->st));
+    if (s->bc_tab) cudaFree(s->bc_tab);
+    s->bc_tab = nullptr;
+    return WL_OK;
+  }
+  if (s->dist.n > 1) return fail(s, WL_ERR_UNSUPPORTED, "boundary tables are not wired into the slab decomposition yet");
+  size_t want = 0;
+  wl_bc_table_size(s, &want);
+  if (count != want) return fail(s, WL_ERR_INVALID, "boundary tables have the wrong number of elements (wl_bc_table_size)");
+  const int N[3] = {s->lay.n0, s->lay.n1, s->D == 3 ? s->lay.n2 : 1};
+  int off = 0;
+  for (int dj = 0; dj < 3; ++dj) s->bc_psz[dj] = dj < s->D ? N[0] * N[1] * N[2] / N[dj] : 0;
+  for (int ci = 0; ci < s->D; ++ci)
+    for (int dj = 0; dj < s->D; ++dj) { s->bc_off[ci * s->D + dj] = off; off += 3 * s->bc_psz[dj]; }
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  if (!s->bc_tab) WL_CUDA(s, cudaMalloc(&s->bc_tab, want * sizeof(float)));
+  WL_CUDA(s, cudaMemcpyAsync(s->bc_tab, tables, want * sizeof(float), cudaMemcpyHostToDevice, s->st));
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  return WL_OK;
+}
 
 int wl_measure_body(wl_sim* s, const wl_body* body, double t, double eps) {
   if (!s || !body) return WL_ERR_INVALID;

@@ -86,6 +86,7 @@ struct wl_sim {
   bool p2p_gather = false;                            // reduction slots travel by k_gather_p2p instead of NCCL
   unsigned int gseq = 0;
   unsigned int cnt_lo = 0, cnt_hi = 0;                // halo arrival-counter totals per link
+  float* bc_tab = nullptr; int bc_off[9] = {0}; int bc_psz[3] = {0, 0, 0};   // Function-uBC tables (wl_set_bc_tables)
   unsigned int gs_seq_lo = 0, gs_seq_hi = 0;          // fused half-sweep pushes per link (k_gs_half_cx)
   bool p2p = false;
   unsigned int seq_lo = 0, seq_hi = 0;                // exchanges done on the lower / upper link
@@ -376,6 +377,17 @@ int gather_red(wl_sim* s) {
 
 // ---------------------------------------------------------------- boundary conditions
 void bc_vec(wl_sim* s, DevField& a, const float* U, bool saveexit, const Per* per = nullptr) {
+  if (U && s->bc_tab && &a == &s->u) {                 // Function uBC sampled into tables (wl_set_bc_tables)
+    BcTabArgs t;
+    t.l = a.lay; t.a = a.base; t.per = s->per; t.saveexit = saveexit ? 1 : 0; t.tab = s->bc_tab;
+    for (int q = 0; q < 9; ++q) t.off[q] = s->bc_off[q];
+    for (int d = 0; d < 3; ++d) t.psz[d] = s->bc_psz[d];
+    dim3 g, b;
+    plane_launch(a.lay, g, b);
+    g.z = 3 * s->D;
+    DISPATCH_D(s, k_bc_vec_tab, g, b, t);
+    return;
+  }
   BcArgs args;
   args.l = a.lay; args.a = a.base; args.per = per ? *per : s->per; args.saveexit = saveexit ? 1 : 0;
   for (int d = 0; d < 3; ++d) args.U.v[d] = U ? U[d] : 0.f;

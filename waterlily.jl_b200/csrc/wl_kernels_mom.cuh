@@ -210,6 +210,84 @@ __global__ void k_bc_vec(const BcArgs a) {
   }
 }
 
+// BC! with a Function uBC(i,x,t) (core.jl:201-219) sampled by the caller into tables (wl_set_bc_tables): per
+// (component ci, direction dj) three planes over the other dims (ghosts included, lowest remaining dim fastest):
+//   ci == dj: Dirichlet values at index 0, 1 and n-1;   ci != dj: uBC(I)-uBC(I±δ) at index 0, unused, at index n-1.
+// Same backward walk as bc_resolve; the tangential differences met on the way are added afterwards in pass order
+// (lowest direction first), which is what the reference's sequential passes compute.
+struct BcTabArgs {
+  Lay l;
+  float* a;
+  Per per;
+  int saveexit;
+  const float* tab;
+  int off[9];      // start of the 3 planes of pair ci*D+dj
+  int psz[3];      // plane size of direction dj
+};
+
+template <int D>
+__device__ __forceinline__ float bc_resolve_tab(const BcTabArgs& a, int ci, int c0, int c1, int c2) {
+  int c[3] = {c0, c1, c2};
+  const int N[3] = {a.l.n0, a.l.n1, a.l.n2};
+  float ds[2] = {0.f, 0.f};
+  int nd = 0;
+  float base = 0.f;
+  bool have = false;
+#pragma unroll
+  for (int dj = D - 1; dj >= 0; --dj) {
+    if (have) continue;
+    const int x = c[dj], n = N[dj];
+    if (a.per.p[dj]) {
+      if (x == 0) c[dj] = n - 2; else if (x == n - 1) c[dj] = 1;
+      continue;
+    }
+    const int ia = dj == 0 ? 1 : 0, ib = dj == 2 ? 1 : 2;       // in-plane dims, fast and slow
+    const int idx = c[ia] + (D == 3 ? N[ia] * c[ib] : 0);
+    const float* T = a.tab + a.off[ci * D + dj];
+    const int ps = a.psz[dj];
+    if (ci == dj) {
+      if (x <= 1) { base = T[(x == 0 ? 0 : ps) + idx]; have = true; }
+      else if (x == n - 1 && !(a.saveexit && ci == 0)) { base = T[2 * ps + idx]; have = true; }
+    } else {
+      if (x == 0) { ds[nd++] = T[idx]; c[dj] = 1; }
+      else if (x == n - 1) { ds[nd++] = T[2 * ps + idx]; c[dj] = n - 2; }
+    }
+  }
+  if (!have) base = a.a[a.l.cstride * ci + a.l.off(c[0], c[1], c[2])];
+  if (nd == 2) base = base + ds[1];
+  if (nd >= 1) base = base + ds[0];
+  return base;
+}
+
+// launch shape and written-cell rules of k_bc_vec
+template <int D>
+__global__ void k_bc_vec_tab(const BcTabArgs a) {
+  pdl_entry();
+  const int dj = blockIdx.z / 3, which = blockIdx.z % 3;
+  const Lay& l = a.l;
+  const int N[3] = {l.n0, l.n1, l.n2};
+  const int da = dj == 0 ? 1 : 0;
+  const int db = dj == 2 ? 1 : 2;
+  const int pa = blockIdx.x * blockDim.x + threadIdx.x;
+  const int pb = blockIdx.y * blockDim.y + threadIdx.y;
+  if (pa >= N[da] || (D == 3 ? pb >= N[db] : pb > 0)) return;
+  int c[3] = {0, 0, 0};
+  c[dj] = which == 0 ? 0 : which == 1 ? 1 : N[dj] - 1;
+  c[da] = pa;
+  if (D == 3) c[db] = pb;
+#pragma unroll
+  for (int ci = 0; ci < D; ++ci) {
+    if (which == 1 && (ci != dj || a.per.p[dj])) continue;
+    if (which == 2 && ci == dj && !a.per.p[dj] && a.saveexit && ci == 0) {
+      bool edge = false;
+      for (int d = 0; d < D; ++d) if (d != dj && (c[d] == 0 || c[d] == N[d] - 1)) edge = true;
+      if (!edge) continue;
+    }
+    const float v = bc_resolve_tab<D>(a, ci, c[0], c[1], c[2]);
+    a.a[l.cstride * ci + l.off(c[0], c[1], c[2])] = v;
+  }
+}
+
 // perBC! (core.jl:239-243) for one direction; launched once per periodic direction, in order.
 struct PerArgs { Lay l; float* a; int dj; };
 template <int D>
