@@ -334,7 +334,8 @@ class Simulation:
             raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: the B200 path is Float32 only")
         if callable(uBC) or callable(g):
             raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: Function uBC/g; use the uBC_t/dUdt arguments of "
-                                     "sim_step for space-uniform time-dependent boundary velocity")
+                                     "sim_step for space-uniform time-dependent boundary velocity, or "
+                                     "set_bc_function for steady space-varying boundary data")
         if scheme not in SCHEMES:
             raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: convective scheme must be quick, cds or vanLeer")
         self.lib = lib or load_library()
