@@ -88,7 +88,8 @@ typedef struct wl_body_node {
 enum wl_field {
   WL_U = 0, WL_U0 = 1, WL_F = 2, WL_P = 3, WL_SIGMA = 4, WL_V = 5, WL_MU0 = 6, WL_MU1 = 7,
   WL_X = 10, WL_R = 11, WL_EPS = 12, WL_Z = 13, WL_L = 14, WL_DIAG = 15, WL_IDIAG = 16,
-  WL_MEAN_P = 20, WL_MEAN_U = 21, WL_MEAN_UU = 22   /* MeanFlow.P/.U/.UU, after wl_meanflow_init */
+  WL_MEAN_P = 20, WL_MEAN_U = 21, WL_MEAN_UU = 22,  /* MeanFlow.P/.U/.UU, after wl_meanflow_init */
+  WL_ACCEL_T0 = 23, WL_ACCEL_T1 = 24                /* accelerate! fields, after wl_set_accel_field */
 };
 
 /* Per-step results: replaces `push!(a.Δt,CFL(a))` (src/Flow.jl:166), the two `push!(ml.n,nᵖ)`
@@ -150,6 +151,13 @@ int wl_finish_ic(wl_sim* s, const float uBC[3]);
  * only boundary data that do not depend on t are complete.  Single GPU only. */
 int wl_bc_table_size(const wl_sim* s, size_t* count);
 int wl_set_bc_tables(wl_sim* s, const float* tables, size_t count);
+
+/* `accelerate!(r,t,g,U)` (src/Flow.jl:69-73) with Function `g(i,x,t)` / `uBC(i,x,t)`: the caller samples
+ * `g + ∂ₜuBC` on every index of every component (layout of WL_F) at t₀ = sum(Δt)-Δt[end] (`which` = 0, predictor) and
+ * t₁ = sum(Δt) (`which` = 1, corrector) before wl_mom_step; the fields are added to the convective-diffusive right-hand
+ * side after the uniform term.  While fields are set the step runs its per-operator kernels (the fused K-MOM has no
+ * slot for them).  `field == NULL` clears both.  STATUS as wl_set_bc_tables: built, NOT YET RUN on a B200.  Single GPU. */
+int wl_set_accel_field(wl_sim* s, int which, const float* field, size_t count);
 
 int wl_measure_body(wl_sim* s, const wl_body* body, double t, double eps);
 /* host-measured coefficients (values BEFORE the two BC! calls of Body.jl:49-50, which are applied here) */

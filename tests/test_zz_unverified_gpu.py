@@ -62,3 +62,36 @@ def test_bc_tables_3d_kernel(wl):
         bc_fn(b, lambda i, x, t: float(ub(i, x, t)), saveexit=exitBC, perdir=perdir)
         assert np.array_equal(sim.flow.u, b), (perdir, exitBC)
         sim.set_bc_function(None)
+
+
+def test_constant_jerk_through_g(wl):
+    """test/test_flow.jl:120-131 in Float32: g(i,x,t) = (jerk·t, 0) as a sampled acceleration field, CUDA vs oracle."""
+    N, jerk = 8, 4.0
+    g = lambda i, x, t: (t * np.float32(jerk) + 0 * x[0]) if i == 1 else 0 * x[0]
+    kw = dict(nu=0.001, dt=0.001, perdir=(1,))
+    sim = wl.Simulation((N, N), (float(np.sqrt(N)), 0.0), N, **kw)
+    sim.set_accel_function(g)
+    ref = wo.OracleSim((N, N), (float(np.sqrt(N)), 0.0), N, g=lambda i, x, t: float(g(i, x, t)), **kw)
+    for _ in range(25):
+        sim.sim_step()
+        ref.sim_step()
+    assert sim.pois.n == ref.n and np.allclose(sim.flow.Δt, ref.dts, rtol=2e-6)
+    assert float(np.abs(sim.flow.u - ref.field("u")).max()) <= 2e-6 * np.sqrt(N)
+
+
+def test_rotating_frame_fields_3d_unfused(wl):
+    """Space- and time-varying g and ∂ₜuBC-like field in 3D (per-operator path while fields are set): CUDA vs oracle."""
+    dims = (16, 12, 8)
+    g = lambda i, x, t: np.float32(0.01) * x[i % 3] - np.float32(0.02) * t * x[(i + 1) % 3]
+    kw = dict(nu=0.01, perdir=(3,))
+    body = dict(kind="sphere", center=(6.0, 6.0, 4.0), radius=2.5)
+    sim = wl.Simulation(dims, (1.0, 0.0, 0.0), 5.0, body=wl.AutoBody(**body), **kw)
+    sim.set_accel_function(g)
+    ref = wo.OracleSim(dims, (1.0, 0.0, 0.0), 5.0, body=wo.make_body(**body), g=lambda i, x, t: float(g(i, x, t)), **kw)
+    for _ in range(4):
+        sim.sim_step(remeasure=False)
+        ref.sim_step(remeasure=False)
+    assert sim.pois.n == ref.n and np.allclose(sim.flow.Δt, ref.dts, rtol=2e-6)
+    assert float(np.abs(sim.flow.u - ref.field("u")).max()) <= 2e-6
+    sim.set_accel_function(None)                       # back on the fused path
+    sim.sim_step(remeasure=False)

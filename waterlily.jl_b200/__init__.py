@@ -26,14 +26,14 @@ _LIBNAME = os.path.join(_HERE, "libwaterlily_b200.so")
 
 WL_OK, WL_ERR_INVALID, WL_ERR_UNSUPPORTED, WL_ERR_CUDA, WL_ERR_NO_DEVICE = range(5)
 FIELDS = dict(u=0, u0=1, f=2, p=3, sigma=4, V=5, mu0=6, mu1=7,
-              x=10, r=11, eps=12, z=13, L=14, D=15, iD=16, mean_P=20, mean_U=21, mean_UU=22)
+              x=10, r=11, eps=12, z=13, L=14, D=15, iD=16, mean_P=20, mean_U=21, mean_UU=22, accel_t0=23, accel_t1=24)
 SCHEMES = dict(quick=0, cds=1, vanLeer=2)
 KINDS = dict(none=0, sphere=1, circle=1, cylinder=2, torus=3)
 
 # symbols include/wl_b200.h declares (tests check the library exports every one of them)
 ABI_SYMBOLS = [
     "wl_create", "wl_destroy", "wl_last_error", "wl_version", "wl_field_dims", "wl_download",
-    "wl_upload", "wl_nlevels", "wl_finish_ic", "wl_bc_table_size", "wl_set_bc_tables", "wl_measure_body", "wl_set_body_coeffs",
+    "wl_upload", "wl_nlevels", "wl_finish_ic", "wl_bc_table_size", "wl_set_bc_tables", "wl_set_accel_field", "wl_measure_body", "wl_set_body_coeffs",
     "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_poisson_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
     "wl_cfl", "wl_pressure_force", "wl_viscous_force", "wl_force_moment", "wl_measure_csg", "wl_pressure_force_csg",
     "wl_viscous_force_csg", "wl_force_moment_csg", "wl_meanflow_init", "wl_meanflow_update", "wl_meanflow_copy_to_flow", "wl_sync", "wl_launch_count", "wl_enable_timing",
@@ -112,6 +112,7 @@ def load_library(path=None):
     lib.wl_measure_body.argtypes = [P, C.POINTER(WLBody), C.c_double, C.c_double]
     lib.wl_bc_table_size.argtypes = [P, C.POINTER(C.c_size_t)]
     lib.wl_set_bc_tables.argtypes = [P, C.c_void_p, C.c_size_t]
+    lib.wl_set_accel_field.argtypes = [P, I, C.c_void_p, C.c_size_t]
     lib.wl_set_body_coeffs.argtypes = [P, P, P, P, P]
     lib.wl_build_poisson.argtypes = [P]
     lib.wl_update_poisson.argtypes = [P]
@@ -444,6 +445,20 @@ class Simulation:
         assert flat.size == n.value, (flat.size, n.value)
         self._check(self.lib.wl_set_bc_tables(self.h, flat.ctypes.data, flat.size))
 
+    def set_accel_function(self, g=None, dUdt=None):
+        """`g(i,x,t)` and `∂ₜuBC(i,x,t)` of `accelerate!` (src/Flow.jl:69-73) as Functions: sampled on the host on every
+        index at t₀ and t₁ before each `mom_step` of `sim_step` and uploaded (`wl_set_accel_field`); both None clears.
+        NOT YET RUN on a B200 (see include/wl_b200.h)."""
+        self._accel = None if (g is None and dUdt is None) else (g, dUdt)
+        if self._accel is None:
+            self._check(self.lib.wl_set_accel_field(self.h, 0, None, 0))
+
+    def _upload_accel(self, t0, t1):
+        from . import bctables
+        for which, t in ((0, t0), (1, t1)):
+            a = bctables.accel_field(self._accel[0], self._accel[1], self.dims, t)
+            self._check(self.lib.wl_set_accel_field(self.h, which, a.ctypes.data, a.size))
+
     # ---- reference API
     def time(self):
         """`time(flow)` = sum(Δt[1:end-1]) (src/Flow.jl:174)."""
@@ -504,6 +519,8 @@ class Simulation:
                 self.measure()
             t1 = float(np.sum(np.asarray(self._dts, np.float32), dtype=np.float32))
             t0 = float(np.float32(t1) - self._dts[-1])
+            if getattr(self, "_accel", None) is not None:
+                self._upload_accel(t0, t1)
             self.mom_step(None if uBC_t is None else uBC_t(t1),
                           None if dUdt is None else dUdt(t0), None if dUdt is None else dUdt(t1))
             steps += 1

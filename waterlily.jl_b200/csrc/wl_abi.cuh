@@ -372,6 +372,7 @@ void wl_destroy(wl_sim* s) {
   free_field(s->u); free_field(s->u0); free_field(s->f); free_field(s->p);
   free_field(s->sigma); free_field(s->V); free_field(s->mu0); free_field(s->mu1); free_field(s->w);
   free_field(s->mf_P); free_field(s->mf_U); free_field(s->mf_UU);
+  free_field(s->accf[0]); free_field(s->accf[1]);
   if (s->band_list) cudaFree(s->band_list);
   if (s->band_list2) cudaFree(s->band_list2);
   if (s->band_mark) cudaFree(s->band_mark);
@@ -521,6 +522,28 @@ int wl_set_bc_tables(wl_sim* s, const float* tables, size_t count) {
   return WL_OK;
 }
 
+int wl_set_accel_field(wl_sim* s, int which, const float* field, size_t count) {
+  if (!s || which < 0 || which > 1) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  if (!field) {
+    WL_CUDA(s, cudaStreamSynchronize(s->st));
+    free_field(s->accf[0]); free_field(s->accf[1]);
+    s->accf_on = false;
+    return WL_OK;
+  }
+  if (s->dist.n > 1) return fail(s, WL_ERR_UNSUPPORTED, "acceleration fields are not wired into the slab decomposition yet");
+  for (int w = 0; w < 2; ++w)
+    if (!s->accf[w].alloc) {
+      char* arena = s->arena; s->arena = nullptr;      // plain allocation, never peer-mapped
+      const int e = alloc_field(s, s->accf[w], s->lay, s->D);
+      s->arena = arena;
+      if (e) return e;
+    }
+  if (int e = xfer(s, WL_ACCEL_T0 + which, 0, const_cast<float*>(field), count, true)) return e;
+  s->accf_on = true;
+  return WL_OK;
+}
+
 int wl_measure_body(wl_sim* s, const wl_body* body, double t, double eps) {
   if (!s || !body) return WL_ERR_INVALID;
   if (body->kind == 0) return WL_OK;                 // NoBody: measure! is a no-op (Body.jl:83)
@@ -617,7 +640,7 @@ int wl_mom_step(wl_sim* s, const float* uBC_t1, const float* acc0, const float* 
   const float* U = uBC_t1 ? uBC_t1 : s->cfg.uBC;
   const bool ex = s->cfg.exitBC != 0;
   Trace tr[2];
-  const bool fused = s->D == 3 && !(s->cfg.flags & WL_FLAG_NO_FUSED);
+  const bool fused = s->D == 3 && !(s->cfg.flags & WL_FLAG_NO_FUSED) && !s->accf_on;
   if (fused && s->band_dirty) { if (int e = band_rebuild(s)) return e; }
   if (s->timing) cudaEventRecord(s->ev[0], s->st);
   if (fused) {
@@ -627,7 +650,7 @@ int wl_mom_step(wl_sim* s, const float* uBC_t1, const float* acc0, const float* 
   } else {
     WL_CUDA(s, cudaMemcpyAsync(s->u0.alloc, s->u.alloc, s->u.bytes, cudaMemcpyDeviceToDevice, s->st));   // u⁰ .= u
     ++s->launches;
-    mom_rhs(s, s->u0, acc0);
+    mom_rhs(s, s->u0, acc0, s->accf_on ? s->accf[0].base : nullptr);
     bdim(s, 0);
   }
   bc_vec(s, s->u, U, ex);
@@ -643,7 +666,7 @@ int wl_mom_step(wl_sim* s, const float* uBC_t1, const float* acc0, const float* 
     mom3(s, s->u, s->u0, s->w, 1, acc1);
     DevField t = s->u; s->u = s->w; s->w = t;
   } else {
-    mom_rhs(s, s->u, acc1);
+    mom_rhs(s, s->u, acc1, s->accf_on ? s->accf[1].base : nullptr);
     bdim(s, 1);
   }
   bc_vec(s, s->u, U, ex);

@@ -86,6 +86,8 @@ struct wl_sim {
   bool p2p_gather = false;                            // reduction slots travel by k_gather_p2p instead of NCCL
   unsigned int gseq = 0;
   unsigned int cnt_lo = 0, cnt_hi = 0;                // halo arrival-counter totals per link
+  DevField accf[2];                                   // accelerate! fields at t₀ / t₁ (wl_set_accel_field), else unallocated
+  bool accf_on = false;
   float* bc_tab = nullptr; int bc_off[9] = {0}; int bc_psz[3] = {0, 0, 0};   // Function-uBC tables (wl_set_bc_tables)
   unsigned int gs_seq_lo = 0, gs_seq_hi = 0;          // fused half-sweep pushes per link (k_gs_half_cx)
   bool p2p = false;
@@ -884,12 +886,13 @@ int poisson_solver(wl_sim* s, int itmx, int* n_out) {
 }
 
 // ---------------------------------------------------------------- momentum pieces
-void mom_rhs(wl_sim* s, DevField& uadv, const float* acc) {
+void mom_rhs(wl_sim* s, DevField& uadv, const float* acc, const float* accf = nullptr) {
   MomArgs a{};
   a.l = s->lay; a.ua = uadv.base; a.u0 = s->u0.base; a.V = s->V.base; a.f = s->f.base;
   a.per = s->per; a.nu = s->cfg.nu; a.dt = s->dt;
   for (int d = 0; d < 3; ++d) a.acc.v[d] = acc ? acc[d] : 0.f;
-  DISPATCH_DS(s, k_mom_rhs, grid_all(s->lay), blk(s->D), a);
+  if (accf) DISPATCH_DS(s, k_mom_rhs_acc, grid_all(s->lay), blk(s->D), a, accf);
+  else DISPATCH_DS(s, k_mom_rhs, grid_all(s->lay), blk(s->D), a);
 }
 // list of band cells for k_mom_patch; rebuilt when μ₁ changed (measure!, uploads)
 int band_rebuild(wl_sim* s) {
@@ -1129,6 +1132,9 @@ DevField* flow_field(wl_sim* s, int field, int level, Lay* lay) {
       case WL_MU1: f = &s->mu1; break;
       default: return nullptr;
     }
+  } else if (field == WL_ACCEL_T0 || field == WL_ACCEL_T1) {
+    f = &s->accf[field - WL_ACCEL_T0];
+    if (!f->alloc) return nullptr;
   } else if (field >= WL_MEAN_P && field <= WL_MEAN_UU) {
     f = field == WL_MEAN_P ? &s->mf_P : (field == WL_MEAN_U ? &s->mf_U : &s->mf_UU);
     if (!f->alloc) return nullptr;

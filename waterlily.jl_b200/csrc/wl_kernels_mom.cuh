@@ -63,8 +63,10 @@ struct MomArgs {
 // with r accumulated exactly in the reference's order (for j: +Φ_low, −Φ_up) and r==0 on cells
 // the reference never writes (any coordinate on the lower ghost).  One thread per cell.
 // f[I,ci] for ANY cell (ghosts included) straight from global memory, in the reference's order.
-template <int D, int S>
-__device__ __forceinline__ float rhs_f(const MomArgs& a, int ci, int c0, int c1, int c2) {
+// ACCF adds the caller's acceleration field (g(i,x,t)+∂ₜuBC(i,x,t) sampled on every index, wl_set_accel_field)
+// after the uniform term, as accelerate! does (Flow.jl:69-73); the default instantiation is unchanged.
+template <int D, int S, bool ACCF = false>
+__device__ __forceinline__ float rhs_f(const MomArgs& a, int ci, int c0, int c1, int c2, const float* accf = nullptr) {
   const Lay& l = a.l;
   const int o = l.off(c0, c1, c2);
   const int c[3] = {c0, c1, c2};
@@ -93,6 +95,7 @@ __device__ __forceinline__ float rhs_f(const MomArgs& a, int ci, int c0, int c1,
   }
   r += a.acc.v[ci];
   const long long oc = l.cstride * ci + o;
+  if (ACCF) r += accf[oc];
   return a.u0[oc] + a.dt * r - a.V[oc];
 }
 
@@ -107,6 +110,19 @@ __global__ void __launch_bounds__(256) k_mom_rhs(const MomArgs a) {
   const int o = l.off(i, j, k);
 #pragma unroll
   for (int ci = 0; ci < D; ++ci) a.f[l.cstride * ci + o] = rhs_f<D, S>(a, ci, i, j, k);
+}
+
+template <int D, int S>
+__global__ void __launch_bounds__(256) k_mom_rhs_acc(const MomArgs a, const float* accf) {
+  pdl_entry();
+  const Lay& l = a.l;
+  const int i = blockIdx.x * 32 + threadIdx.x - LPAD;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z : 0;
+  if (i < 0 || i >= l.n0 || j >= l.n1 || k >= l.n2) return;
+  const int o = l.off(i, j, k);
+#pragma unroll
+  for (int ci = 0; ci < D; ++ci) a.f[l.cstride * ci + o] = rhs_f<D, S, true>(a, ci, i, j, k, accf);
 }
 
 struct BdimArgs {
