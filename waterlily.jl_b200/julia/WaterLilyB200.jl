@@ -283,6 +283,36 @@ pressure_moment(x₀, a::B200Flow, body::CsgBody) = csg_call(:wl_force_moment_cs
 viscous_moment(x₀, a::B200Flow, body::CsgBody) = csg_call(:wl_force_moment_csg, a, body, x₀, 1)
 total_moment(x₀, a::B200Flow, body::CsgBody) = pressure_moment(x₀, a, body) .+ viscous_moment(x₀, a, body)
 
+# ---- Function uBC(i,x,t): sampled where BC! evaluates it (src/core.jl:201-219) and handed over as tables ------------
+# Layout of wl_set_bc_tables: component outer, direction inner, three planes (index 1, 2, Ng[j]) over the other dims in
+# column-major order; normal component: the Dirichlet values; tangential: uBC(I)-uBC(I±δ) on the two ghost planes.
+# Built together with the device kernel; like it, not yet run (see include/wl_b200.h).
+function bc_tables(uBC::Function, Ng::NTuple{D,Int}, t, perdir, ::Type{T}) where {D,T}
+    tab = T[]
+    for i in 1:D, j in 1:D, (s, k) in enumerate((1, 2, Ng[j])), I in WaterLily.slice(Ng, k, j)
+        v = if j in perdir || (i != j && s == 2)
+            zero(T)
+        elseif i == j
+            T(uBC(i, WaterLily.loc(i, I, T), t))
+        else
+            J = s == 1 ? I + WaterLily.δ(j, I) : I - WaterLily.δ(j, I)
+            T(uBC(i, WaterLily.loc(i, I, T), t)) - T(uBC(i, WaterLily.loc(i, J, T), t))
+        end
+        push!(tab, v)
+    end
+    tab
+end
+function set_bc_function!(a::B200Flow{D,T}, uBC::Function; t=zero(T)) where {D,T}
+    tab = bc_tables(uBC, size(a.p), T(t), a.perdir, T)
+    check(a.h, ccall((:wl_set_bc_tables, LIB), Cint, (Ptr{Cvoid}, Ptr{Cfloat}, Csize_t), a.h.ptr, tab, length(tab)))
+end
+"`g + ∂ₜuBC` on every index at t₀ (`which`=0) or t₁ (`which`=1) for accelerate! (src/Flow.jl:69-73)."
+function set_accel_field!(a::B200Flow{D,T}, which::Integer, f::Function, t) where {D,T}
+    Ng = size(a.p)
+    fld = T[f(i, WaterLily.loc(i, I, T), T(t)) for I in CartesianIndices(Ng), i in 1:D]
+    check(a.h, ccall((:wl_set_accel_field, LIB), Cint, (Ptr{Cvoid}, Cint, Ptr{Cfloat}, Csize_t), a.h.ptr, which, fld, length(fld)))
+end
+
 # ---- MeanFlow (src/Metrics.jl:205-263): device-resident running averages --------------------------------
 struct B200MeanFlow{T}
     h::Handle; P::B200Array{T}; U::B200Array{T}; UU::Union{Nothing,B200Array{T}}; t::Vector{T}; uu_stats::Bool
