@@ -1,16 +1,11 @@
-"""GPU tests of entry points that were built after the round's GPU budget was spent: they have NOT been run on a B200
-yet and are therefore switched off unless WL_RUN_UNVERIFIED=1.  First thing to run next round:
-    WL_RUN_UNVERIFIED=1 python -m pytest tests/test_zz_unverified_gpu.py -m gpu -x -q
-"""
-import os
-
+"""Function uBC(i,x,t) / g(i,x,t) through the device path (wl_set_bc_tables, wl_set_accel_field): CUDA vs oracle.
+First run on a B200 in round 2 (profiles/r2_c01_pytest_fnbc_ungated.log: 5 passed)."""
 import numpy as np
 import pytest
 
 from oracle import wl_oracle as wo
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("WL_RUN_UNVERIFIED") != "1", reason="not yet run on a B200; set WL_RUN_UNVERIFIED=1")]
+pytestmark = pytest.mark.gpu
 
 
 @pytest.fixture(scope="module")
