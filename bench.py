@@ -6,7 +6,9 @@ baseline timed beside it.
   python bench.py [--gpus N] [--steps K] [--warmup W] [--workload tgv|sphere|circle] [--impl reference]
 
 One "step" = one `sim_step!` (= one mom_step!; plus measure!+update! for remeasured bodies).
-Default workload: BASELINE.json configs[1], 3D Taylor-Green vortex 128^3, Float32, periodic.
+Default workload: BASELINE.json configs[2], the north_star's 1-GPU target: 3D static sphere Re=3700 on 512x256x256,
+Float32.  --gpus N (torchrun): the same slab on EVERY GPU, i.e. the grid z-extended to 512x256x(256 N) (weak scaling);
+at N=8 the line also carries configs[4] (TGV 1024^3 on 8 GPUs) as the sub-record "config_E".
 Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
 """
 import argparse
@@ -22,18 +24,18 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# Algorithmic HBM bytes per interior cell per launch of each kernel (Float32; every field the
-# kernel must consume read once, every field it must produce written once).
-B_ALG = {
-    # fused predictor/corrector: reads u(adv) D, u⁰ D(corr only), μ₀ D, V D, μ₁ D²; writes u D  
-    "k_mom": {3: (84 + 96) / 2, 2: (48 + 56) / 2},
-    # un-fused RHS kernel: reads u_adv D, u⁰ D (corrector: both), V D; writes f D
-    "k_mom_rhs": {3: (36 + 48) / 2, 2: (24 + 32) / 2},
-    "k_bdim": {3: (3 + 3 + 3 + 9 + 3) * 4 + 6, 2: (2 + 2 + 2 + 4 + 2) * 4 + 4},
-    "k_gs_half": {3: 4 * (1 + 0.5 + 3 + 0.5), 2: 4 * (1 + 0.5 + 2 + 0.5)},
-    "k_smooth": {3: 28, 2: 24},
-    "k_increment": {3: 4 * (1 + 1 + 1 + 3 + 1 + 1), 2: 4 * (1 + 1 + 1 + 2 + 1 + 1)},
+# Algorithmic HBM bytes per cell per launch (every field the phase must consume read once, every field it
+# must produce written once, Float32, D/iD recomputable from L) and the cells one thread block covers, per kernel.
+# Groups: the smoother is ONE algorithmic phase (K-SMOOTH, 28 B per cell of the level) however many kernels run it.
+B_ALG3 = {
+    "k_mom3": 90.0,          # (84 predictor + 96 corrector)/2: u_adv 3 (+u⁰ 3), μ₀ 3, V 3, μ₁ 9 read; u 3 written
+    "k_mom3_nobody": 30.0,   # body-free periodic variant <S,true,W>: no V, μ₀, μ₁ in the data it must read: (24+36)/2
+    "k_divres4": 36.0, "k_proj4": 44.0, "k_down4": 28.5, "k_up4": 28.5, "k_cfl4": 16.0,
+    "smoother": 28.0,
 }
+SMOOTHER_KERNELS = ("k_gs_half_c", "k_gs_pair", "k_incr4", "k_smooth_fused", "k_gs_half_cx")
+CELLS_PER_BLOCK = {"k_divres4": 1024, "k_proj4": 1024, "k_down4": 1024, "k_up4": 1024, "k_incr4": 1024, "k_cfl4": 1024}
+B_ALG2 = {"k_mom_rhs": (24 + 32) / 2}
 
 
 def tgv3d(i, x, k):
@@ -165,12 +167,14 @@ class ClockSampler:
         return out
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from `ncu --set full`
-# captures of these exact workloads on one GPU (summaries under profiles/): (bytes per launch, source)
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, from `ncu --set full` captures of these exact workloads on
+# one GPU (summaries under profiles/): {(workload, dims): (source, {kernel: bytes per launch})}
 NCU_TRAFFIC = {
-    # mean of the two captured launches (predictor, corrector)
-    ("tgv", (128, 128, 128)): ((32.50e6 + 0.21e6 + 58.01e6 + 4.11e6) / 2, "profiles/r1_v15_ncu_full_kmom3_tgv128.tsv (most of the 128^3 working set stays in the 126 MB L2)"),
-    ("sphere", (512, 256, 256)): ((1273.3e6 + 387.2e6 + 1678.3e6 + 389.9e6) / 2, "profiles/r1_v15_ncu_full_kmom3_sphere512.tsv"),
+    ("tgv", (128, 128, 128)): ("profiles/r1_v15_ncu_full_kmom3_tgv128.tsv (most of the 128^3 working set stays in the 126 MB L2)",
+                               {"k_mom3": (32.50e6 + 0.21e6 + 58.01e6 + 4.11e6) / 2}),
+    ("sphere", (512, 256, 256)): ("profiles/r1_v15_ncu_full_kmom3_sphere512.tsv, r1_v14_ncu_full_sphere512.tsv, r1_v16_ncu_full_mg4_sphere512.tsv (level-1 launches)",
+                                  {"k_mom3": (1273.3e6 + 387.2e6 + 1678.3e6 + 389.9e6) / 2, "k_divres4": 1221e6, "k_down4": 1117e6,
+                                   "k_up4": 1202e6, "k_proj4": 1440e6, "k_gs_half_c": 803e6}),
 }
 
 
@@ -199,8 +203,25 @@ def build_fast_oracle():
     return lib, "-O3 -march=native -fopenmp"
 
 
+def omp_all_cores():
+    """torch.distributed.run exports OMP_NUM_THREADS=1 to its workers: the CPU legs set the thread count themselves."""
+    n = os.cpu_count() or 1
+    try:
+        n = len(os.sched_getaffinity(0))
+    except Exception:
+        pass
+    os.environ["OMP_NUM_THREADS"] = str(n)
+    try:
+        import ctypes
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(n)
+    except Exception:
+        pass
+    return n
+
+
 def cpu_run(wname, size, steps, warmup):
     """Time the CPU restatement of the reference (oracle port) on all host cores."""
+    ncores = omp_all_cores()
     from oracle import wl_oracle as wo
     path, flags = build_fast_oracle()
     lib = wo.load(fast_path=path)
@@ -215,27 +236,134 @@ def cpu_run(wname, size, steps, warmup):
     dt = time.perf_counter() - t0
     cells = int(np.prod(dims))
     return dict(ns=dt / steps / cells * 1e9, ms_per_step=dt / steps * 1e3, n=list(sim.n[-2 * steps:]), desc=desc,
-                cores=os.cpu_count(), flags=flags, cells=cells)
+                cores=ncores, flags=flags, cells=cells, dims=dims)
 
 
 def reference_arm(args, rank):
     """`--impl reference`: the reference's own CPU path for this workload.  The reference is Julia and
     Julia is not installed (here or on the GPU box), so this times the oracle port (oracle/wl_oracle.cpp,
-    a loop-for-loop restatement) with all host threads.  Rank 0 only."""
+    a loop-for-loop restatement) with all host threads.  Rank 0 only.  At N > 1 the repo arm z-extends the grid
+    (weak scaling); the CPU sample stays the per-GPU grid -- the metric is per cell, the CPU cost per cell does not
+    depend on the z extent -- and `config` names the job the ratio is quoted for."""
     if rank != 0:
         return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     r = cpu_run(args.workload, args.size, args.steps, args.warmup)
+    job = workload(args.workload, args.size, world if args.scaling == "weak" else 1, args.nz)
     line = {
         "impl": "reference", "metric": "ns_per_cell_per_step", "value": r["ns"], "unit": "ns/cell/step",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
-        "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": r["desc"], "cells": r["cells"], "poisson_iters_per_step": float(np.mean(r["n"])) * 2},
+        "higher_is_better": False, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": job[0], "cells": int(np.prod(job[1])), "remeasure": job[6],
+                   "poisson_iters_per_step": float(np.mean(r["n"])) * 2},
         "cpu_baseline": {"value": r["ns"], "unit": "ns/cell/step", "cores": r["cores"], "kind": "port",
-                         "sample": f"{args.steps} full steps of the same workload after {args.warmup} warm-up, {r['flags']}"},
+                         "sample": f"{args.steps} full steps of {r['desc']} after {args.warmup} warm-up, oracle port {r['flags']}, "
+                                   f"{r['cores']} OpenMP threads" + ("" if world == 1 else " (the per-GPU slab of the job; per-cell metric)")},
         "e2e": {"value": r["ns"], "unit": "ns/cell/step", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def base_name(name):
+    """'(k_mom3<0, false, true>)' -> ('k_mom3', ['0','false','true'])"""
+    n = name.strip("()")
+    args = []
+    if "<" in n:
+        n, rest = n.split("<", 1)
+        args = [x.strip() for x in rest.rstrip(">").split(",")]
+    return n, args
+
+
+def kernel_table(prof, blocks, cells_gpu, nsteps, peak, ncu):
+    """Per-kernel rows from a live CUDA-event profile of whole steps on this rank: launches per step, average launch
+    time, algorithmic bytes of the work those launches did, achieved GB/s and its fraction of the measured peak.
+    Work size of the multigrid kernels (they run on several levels) = thread blocks launched x cells per block."""
+    rows, total = [], sum(ms for _, ms in prof.values())
+    sm_ms, sm_cells, sm_n = 0.0, 0, 0
+    for name, (n, ms) in prof.items():
+        kn, targs = base_name(name)
+        balg = work = None
+        if kn == "k_mom3":
+            nobody = len(targs) > 1 and targs[1] == "true"
+            balg = B_ALG3["k_mom3_nobody" if nobody else "k_mom3"]
+            work = cells_gpu * n
+        elif kn in CELLS_PER_BLOCK and kn in B_ALG3:
+            balg, work = B_ALG3[kn], blocks.get(name, 0) * CELLS_PER_BLOCK[kn]
+        if kn in SMOOTHER_KERNELS:
+            sm_ms += ms
+            sm_n += n
+            if kn in ("k_incr4", "k_smooth_fused", "k_gs_pair_incr"):   # runs once per smooth: its blocks count the cells smoothed
+                sm_cells += blocks.get(name, 0) * CELLS_PER_BLOCK.get(kn, 1024)
+        row = {"kernel": kn + ("<nobody>" if kn == "k_mom3" and balg == B_ALG3["k_mom3_nobody"] else ""),
+               "launches_per_step": n / nsteps, "avg_us": ms / n * 1e3, "share": ms / total if total else None,
+               "B_alg": balg, "achieved_GBps": None, "frac": None, "ncu_dram_bytes_per_launch": ncu.get(kn)}
+        if balg and work and ms > 0:
+            row["achieved_GBps"] = balg * work / (ms * 1e-3) / 1e9
+            row["frac"] = row["achieved_GBps"] / peak
+        rows.append(row)
+    if sm_ms > 0 and sm_cells > 0:
+        ach = B_ALG3["smoother"] * sm_cells / (sm_ms * 1e-3) / 1e9
+        rows.append({"kernel": "smoother group (" + "+".join(k for k in SMOOTHER_KERNELS if any(base_name(x)[0] == k for x in prof)) + ")",
+                     "launches_per_step": sm_n / nsteps, "avg_us": None, "share": sm_ms / total, "B_alg": B_ALG3["smoother"],
+                     "achieved_GBps": ach, "frac": ach / peak, "ncu_dram_bytes_per_launch": None,
+                     "us_per_smooth_of_the_fine_level": None})
+    rows.sort(key=lambda r: -(r["share"] or 0))
+    return rows
+
+
+def mgpu_parity(wl, dist, world, rank, local):
+    """N > 1: a small sphere run slab-decomposed over all ranks must equal the single-GPU run of the same global grid
+    (fields, Δt, Poisson iteration counts).  Returns "bit-exact" or the largest difference."""
+    dims, R = (64, 32, 8 * world if 8 * world >= 32 else 32), 4.0
+    while dims[2] % (2 * world) or dims[2] // world < 4:
+        dims = (dims[0], dims[1], dims[2] + 2 * world - dims[2] % (2 * world))
+    body = dict(kind="sphere", center=(15.0, 15.0, dims[2] / 2 - 1), radius=R)
+    kw = dict(nu=2 * R / 100, exitBC=True)
+    sim = wl.Simulation(dims, (1.0, 0.0, 0.0), 2 * R, body=wl.AutoBody(**body), device=local, comm=wl.make_slab_comm(), **kw)
+    for _ in range(3):
+        sim.sim_step(remeasure=False)
+    u, p = sim.gather("u"), sim.gather("p")
+    n, dts = list(sim.pois.n), [float(x) for x in sim.flow.Δt]
+    del sim
+    verdict = [None]
+    if rank == 0:
+        one = wl.Simulation(dims, (1.0, 0.0, 0.0), 2 * R, body=wl.AutoBody(**body), device=local, **kw)
+        for _ in range(3):
+            one.sim_step(remeasure=False)
+        u1, p1 = one.flow.u, one.flow.p
+        same = np.array_equal(u, u1) and np.array_equal(p, p1) and n == list(one.pois.n) and dts == [float(x) for x in one.flow.Δt]
+        if same:
+            verdict[0] = "bit-exact"
+        else:
+            verdict[0] = "max|du|=%.3e max|dp|=%.3e n %s vs %s" % (float(np.abs(u - u1).max()), float(np.abs(p - p1).max()), n, list(one.pois.n))
+        del one
+    dist.broadcast_object_list(verdict, src=0)
+    return verdict[0]
+
+
+def timed_steps(sim, steps, warmup, remeasure, barrier, dist, torch, prof_filter=None):
+    for _ in range(warmup):
+        sim.sim_step(remeasure=remeasure)
+    barrier()
+    l0 = sim.launch_count()
+    if prof_filter:
+        sim.prof_begin(prof_filter)
+    sim.event_record(0)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        sim.sim_step(remeasure=remeasure)
+    sim.event_record(1)
+    sim.sync()
+    wall = time.perf_counter() - t0
+    dev_ms = sim.event_elapsed_ms(0, 1)
+    prof = sim.prof_end() if prof_filter else {}
+    t_max = dev_ms
+    if dist is not None:
+        t = torch.tensor([dev_ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_max = float(t.item())
+    return t_max, dev_ms, wall, prof, sim.launch_count() - l0
 
 
 def main():
@@ -244,13 +372,14 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--workload", default="tgv")
+    ap.add_argument("--workload", default="sphere")
     ap.add_argument("--size", type=int, default=None)
     ap.add_argument("--nz", type=int, default=None, help="tgv: planes per GPU in the last dimension (default: size)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-config-e", action="store_true", help="N=8: skip the TGV 1024^3 sub-record")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N>1: weak = every GPU keeps the single-GPU grid (last dimension x N), strong = the same grid split N ways")
-    ap.add_argument("--breakdown", default=None, help="write a per-kernel CUDA-event breakdown (3 extra steps) here")
+    ap.add_argument("--breakdown", default=None, help="also write the per-kernel CUDA-event breakdown here (tsv)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -270,6 +399,8 @@ def main():
         dist.barrier()
     import waterlily_jl_b200 as wl
 
+    parity = mgpu_parity(wl, dist, world, rank, local) if world > 1 else None
+
     # N>1: ONE simulation, slab-decomposed along the last dimension, one rank per GPU
     desc, dims, uBC, L, kw, body, remeasure = workload(args.workload, args.size, world if args.scaling == "weak" else 1, args.nz)
     D = len(dims)
@@ -283,50 +414,59 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
-        sim.sim_step(remeasure=remeasure)
+    warm = max(args.warmup, 3)
+    peak, peak_src = measured_peak()
+    ncu_src, ncu = NCU_TRAFFIC.get((args.workload, tuple(dims)), (None, {})) if world == 1 else (None, {})
 
-    # ---- timed region: K steps, state resident in HBM, CUDA events on the launching stream
-    dom = "k_mom3" if D == 3 else "k_mom_rhs"
-    balg_key = "k_mom" if D == 3 else "k_mom_rhs"
-    clocks = ClockSampler(local)
-    barrier()
-    l0 = sim.launch_count()
-    sim.prof_begin(dom)
-    sim.event_record(0)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
+    # ---- per-kernel profile of 3 whole steps (every launch bracketed by CUDA events on the launching stream): picks
+    #      the dominant kernel and fills the per-kernel table.  Outside the timed region: events break launch overlap.
+    for _ in range(warm):
         sim.sim_step(remeasure=remeasure)
-    sim.event_record(1)
-    sim.sync()
-    wall = time.perf_counter() - t0
-    dev_ms = sim.event_elapsed_ms(0, 1)
-    prof = sim.prof_end()
-    launches = sim.launch_count() - l0
+    sim.prof_begin("")
+    sim.event_record(2)
+    for _ in range(3):
+        sim.sim_step(remeasure=remeasure)
+    sim.event_record(3)
+    allp = sim.prof_end()
+    blocks = dict(sim.prof_blocks)
+    prof_total_ms = sim.event_elapsed_ms(2, 3)
+    table = kernel_table(allp, blocks, cells // world, 3, peak, ncu) if D == 3 else []
+    dom_full = max(allp.items(), key=lambda kv: kv[1][1])[0]
+    dom = base_name(dom_full)[0]
+
+    # ---- timed region: K steps, state resident in HBM, CUDA events on the launching stream; only the dominant
+    #      kernel's launches carry their own events
+    clocks = ClockSampler(local)
+    t_max, dev_ms, wall, prof, launches = timed_steps(sim, args.steps, 0, remeasure, barrier, dist, torch, dom)
     clk = clocks.stop()
     n_iters = list(sim.pois.n[-2 * args.steps:])
-    t_max = dev_ms
-    if dist is not None:
-        t = torch.tensor([dev_ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        t_max = float(t.item())
     ms_per_step = t_max / args.steps
     value = t_max * 1e6 / args.steps / cells               # ns per cell per step, whole job
 
     # ---- roofline of the dominant kernel (live CUDA events inside the timed region)
-    peak, peak_src = measured_peak()
-    kn, kms = 0, 0.0
-    for name, (n, ms) in prof.items():
-        kn += n
-        kms += ms
-    balg = B_ALG[balg_key][D]
-    achieved = (balg * cells / world) / (kms / max(kn, 1) * 1e-3) / 1e9 if kn else None     # per GPU (rank 0's kernel)
-    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+    kn = sum(n for n, _ in prof.values())
+    kms = sum(ms for _, ms in prof.values())
+    row = next((r for r in table if r["kernel"].split("<")[0] == dom and r["B_alg"]), None)
+    if D == 3 and row is not None and kn:
+        work = row["B_alg"] * ((cells // world) * kn if dom == "k_mom3" else
+                               sum(sim.prof_blocks.get(nm, 0) for nm in prof) * CELLS_PER_BLOCK.get(dom, 1024))
+        achieved, balg = work / (kms * 1e-3) / 1e9, row["B_alg"]
+    elif D == 2 and kn:
+        balg = B_ALG2.get(dom)
+        achieved = balg * cells * kn / (kms * 1e-3) / 1e9 if balg else None
+    else:
+        achieved = balg = None
+    roofline = {"bound": "hbm", "kernel": dom_full.strip("()"), "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": (achieved / peak) if achieved else None,
-                "traffic": NCU_TRAFFIC.get((args.workload, tuple(dims)), (None, None))[0] if world == 1 else None,
-                "traffic_source": NCU_TRAFFIC.get((args.workload, tuple(dims)), (None, None))[1] if world == 1 else None,
+                "traffic": ncu.get(dom), "traffic_source": ncu_src if ncu.get(dom) else None,
                 "alg_bytes_per_cell": balg, "launches": kn, "avg_ms": kms / max(kn, 1), "peak_source": peak_src,
-                "share_of_step": kms / dev_ms}
+                "share_of_step": kms / dev_ms,
+                "chosen": "largest share of the step's kernel time in the live per-kernel profile (3 steps before the timed region)",
+                "whole_step": {"alg_bytes_per_cell": 340 + 97 * float(np.mean(n_iters)) * 2 if D == 3 else None,
+                               "achieved": ((340 + 97 * float(np.mean(n_iters)) * 2) * (cells // world) / (ms_per_step * 1e-3) / 1e9) if D == 3 else None},
+                "kernels": table}
+    if D == 3 and roofline["whole_step"]["achieved"]:
+        roofline["whole_step"]["frac"] = roofline["whole_step"]["achieved"] / peak
 
     # ---- e2e: the same step through the public API with HOST buffers (pinned): upload state, step, download
     shape_u, shape_p = sim.field_shape("u"), sim.field_shape("p")
@@ -353,49 +493,75 @@ def main():
            "h2d_bytes_per_step": int(hu.nbytes + hp.nbytes) * world, "d2h_bytes_per_step": int(hu.nbytes + hp.nbytes) * world,
            "steps": e2e_steps, "what": "upload u,p from pinned host + sim_step + download u,p"}
 
-    # ---- optional per-kernel breakdown (outside the timed region)
-    phases = None
-    if args.breakdown:                      # every rank steps (collective); rank 0 writes
+    if args.breakdown:
         sim.enable_timing(True)
         sim.sim_step(remeasure=remeasure)
         phases = [round(t * 1e3, 4) for t in sim.phase_times()[:5]]
         sim.enable_timing(False)
-        sim.prof_begin("")
-        sim.event_record(2)
-        for _ in range(3):
-            sim.sim_step(remeasure=remeasure)
-        sim.event_record(3)
-        allp = sim.prof_end()
-        tot = sim.event_elapsed_ms(2, 3)
         with open(args.breakdown if rank == 0 else os.devnull, "w") as f:
             f.write(f"# phases of one step [ms]: predictor {phases[0]}, project {phases[1]}, corrector {phases[2]}, "
                     f"project {phases[3]}, CFL {phases[4]}\n")
-            f.write(f"# {desc}; 3 steps, {tot:.3f} ms total with per-launch events (events add overhead)\n")
-            f.write("kernel\tlaunches\ttotal_ms\tavg_us\tshare_of_kernel_time\n")
+            f.write(f"# {desc}; 3 steps, {prof_total_ms:.3f} ms total with per-launch events (events add overhead)\n")
+            f.write("kernel\tlaunches\ttotal_ms\tavg_us\tshare_of_kernel_time\tblocks\n")
             ksum = sum(ms for _, ms in allp.values())
             for name, (n, ms) in sorted(allp.items(), key=lambda kv: -kv[1][1]):
-                f.write(f"{name}\t{n}\t{ms:.4f}\t{ms / n * 1e3:.2f}\t{ms / ksum:.3f}\n")
+                f.write(f"{name}\t{n}\t{ms:.4f}\t{ms / n * 1e3:.2f}\t{ms / ksum:.3f}\t{blocks.get(name, 0)}\n")
 
     halo = sim.halo_stats()
     halo_us = sim.halo_timing() if world > 1 else None
+    halo_transport = sim.halo_transport()
     nsteps_total = len(sim.pois.n) // 2
+    hu = hp = None
+    del sim
+
+    # ---- N = 8: BASELINE configs[4], TGV 1024^3 on 8 GPUs, against the same slab (1024x1024x128) on one GPU
+    config_e = None
+    if world == 8 and not args.no_config_e and args.workload == "sphere" and args.scaling == "weak":
+        d8 = workload("tgv", 1024, 8, 128)
+        s8 = wl.Simulation(d8[1], d8[2], d8[3], device=local, comm=wl.make_slab_comm(), **d8[4])
+        sim = s8
+        t8, _, _, _, _ = timed_steps(s8, 10, 3, False, barrier, dist, torch)
+        n8 = list(s8.pois.n[-20:])
+        del s8, sim
+        t1 = None
+        if rank == 0:                                  # the single-GPU reference point of the weak-scaling pair
+            d1 = workload("tgv", 1024, 1, 128)
+            s1 = wl.Simulation(d1[1], d1[2], d1[3], device=local, **d1[4])
+            for _ in range(3):
+                s1.sim_step()
+            s1.event_record(0)
+            for _ in range(10):
+                s1.sim_step()
+            s1.event_record(1)
+            s1.sync()
+            t1 = s1.event_elapsed_ms(0, 1)
+            del s1
+        dist.barrier()
+        if rank == 0:
+            config_e = {"workload": d8[0], "cells": int(np.prod(d8[1])), "steps": 10, "warmup": 3,
+                        "ms_per_step": t8 / 10, "ns_per_cell_per_step": t8 * 1e6 / 10 / int(np.prod(d8[1])),
+                        "single_gpu_same_slab": {"workload": workload("tgv", 1024, 1, 128)[0], "ms_per_step": t1 / 10},
+                        "weak_efficiency": (t1 / 10) / (t8 / 10), "poisson_iters_per_step": float(np.mean(n8)) * 2}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cpu_size = {"tgv": min(args.size or 128, 128), "sphere": 64, "cylinder": 64, "circle": None}[args.workload]
-        r = cpu_run(args.workload, cpu_size, 3, 1)
+        # the SAME workload on the host cores where ~10 steps take tens of seconds, else a reduced grid (per-cell figure)
+        cpu_size = {"tgv": min(args.size or 128, 256), "sphere": min(args.size or 256, 256), "cylinder": 64, "circle": None}[args.workload]
+        r = cpu_run(args.workload, cpu_size, 10, 1)
         big = r["cells"] != cells
         cpu = {"value": r["ns"], "unit": "ns/cell/step", "cores": r["cores"], "kind": "port",
-               "sample": f"3 steps of {r['desc']} after 1 warm-up, oracle port {r['flags']}" +
-                         (" (reduced grid, per-cell figure)" if big else "")}
+               "sample": f"10 steps of {r['desc']} after 1 warm-up, oracle port {r['flags']}, {r['cores']} OpenMP threads" +
+                         (" (reduced grid, per-cell figure)" if big else " (the same workload)")}
 
     if rank == 0:
         line = {
             "metric": "ns_per_cell_per_step", "value": value, "unit": "ns/cell/step", "n_gpus": world,
-            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": False,
+            "steps": args.steps, "warmup": warm + 3, "ms_per_step": ms_per_step, "higher_is_better": False,
             "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": desc, "cells": cells, "cells_per_gpu": cells // world, "remeasure": remeasure,
                        "parallelism": "single GPU" if world == 1 else
-                       f"{world} slabs along the last dimension, halo exchange by {sim.halo_transport()} ({halo[0] // max(1, nsteps_total)} exchanges, "
+                       f"{world} slabs along the last dimension ({'every GPU keeps the single-GPU grid: z-extended job' if args.scaling == 'weak' else 'the same grid split N ways'}), "
+                       f"halo exchange by {halo_transport} ({halo[0] // max(1, nsteps_total)} exchanges, "
                        f"{halo[1] / max(1, nsteps_total) / 1e6:.1f} MB sent per rank per step), coarse levels replicated",
                        "poisson_iters_per_step": float(np.mean(n_iters)) * 2,
                        "l2": "working set (%.0f MB per GPU) exceeds L2, no flush" % (30 * 4 * cells / world / 1e6)
@@ -403,6 +569,10 @@ def main():
             "halo_us_per_exchange": halo_us, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
             "wall_ms_per_step": wall / args.steps * 1e3,
         }
+        if parity is not None:
+            line["mgpu_parity"] = parity
+        if config_e is not None:
+            line["config_E"] = config_e
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()

@@ -185,6 +185,14 @@ int wl_cfl(wl_sim* s, float* dt);                       /* CFL(a) src/Flow.jl:23
 
 /* ---- pressure_force(sim) (src/Metrics.jl:116-133); clobbers flow.f like the reference        */
 int wl_pressure_force(wl_sim* s, const wl_body* body, double t, double out[3]);
+/* ---- pressure_force for a HOST-measured body (any `AutoBody(sdf,map)` closure; replaces `pressure_force(flow,body)`,
+ *      src/Metrics.jl:126-133, for bodies the library cannot evaluate itself): the caller evaluates
+ *      `nds(body,loc(0,I),t)` (:110-113) on the interior cells with |d| < 1 and hands over the non-zero entries --
+ *      idx = 0-based linear index into the (N1+2,N2+2[,N3+2]) scalar array, first dimension fastest (the local slab
+ *      on a slab-decomposed sim), w = D floats per entry.  wl_pressure_force_weights forms p[I]*w in Float32 and
+ *      sums in Float64 like the reference; the weights stay valid until replaced (moving bodies: every step). */
+int wl_set_force_weights(wl_sim* s, int64_t nnz, const int64_t* idx, const float* w);
+int wl_pressure_force_weights(wl_sim* s, double out[3]);
 /* ---- viscous_force(sim) (src/Metrics.jl:140-152): -2ν Σ S(I,u)·nds; clobbers flow.f like the reference.
  *      total_force(sim) (:159) is the sum of the two, formed by the caller.                     */
 int wl_viscous_force(wl_sim* s, const wl_body* body, double t, double out[3]);
@@ -224,7 +232,7 @@ int wl_last_phase_times(const wl_sim* s, double out[8]);
 
 /* ---- measurement hooks (bench.py): per-kernel CUDA-event timing on the launching stream.
  *      wl_prof_begin(filter): time every kernel whose name contains `filter` ("" = all) until
- *      wl_prof_end, which writes "<kernel>\t<launches>\t<total_ms>\n" lines into buf.
+ *      wl_prof_end, which writes "<kernel>\t<launches>\t<total_ms>\t<total_blocks>\n" lines into buf.
  *      wl_event_record / wl_event_elapsed_ms: events on the sim's own stream, slots 0..7.      */
 int wl_prof_begin(wl_sim* s, const char* filter);
 int wl_prof_end(wl_sim* s, char* buf, size_t buflen);

@@ -35,7 +35,7 @@ ABI_SYMBOLS = [
     "wl_create", "wl_destroy", "wl_last_error", "wl_version", "wl_field_dims", "wl_download",
     "wl_upload", "wl_nlevels", "wl_finish_ic", "wl_bc_table_size", "wl_set_bc_tables", "wl_set_accel_field", "wl_measure_body", "wl_set_body_coeffs",
     "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_poisson_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
-    "wl_cfl", "wl_pressure_force", "wl_viscous_force", "wl_force_moment", "wl_measure_csg", "wl_pressure_force_csg",
+    "wl_cfl", "wl_pressure_force", "wl_set_force_weights", "wl_pressure_force_weights", "wl_viscous_force", "wl_force_moment", "wl_measure_csg", "wl_pressure_force_csg",
     "wl_viscous_force_csg", "wl_force_moment_csg", "wl_meanflow_init", "wl_meanflow_update", "wl_meanflow_copy_to_flow", "wl_sync", "wl_launch_count", "wl_enable_timing",
     "wl_last_phase_times", "wl_debug_op", "wl_prof_begin", "wl_prof_end", "wl_event_record",
     "wl_event_elapsed_ms", "wl_create_slab", "wl_nccl_unique_id", "wl_slab_info", "wl_halo_stats", "wl_halo_transport", "wl_halo_timing",
@@ -124,6 +124,8 @@ def load_library(path=None):
     lib.wl_cfl.argtypes = [P, FP]
     lib.wl_pressure_force.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3)]
     lib.wl_viscous_force.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3)]
+    lib.wl_set_force_weights.argtypes = [P, C.c_int64, C.c_void_p, C.c_void_p]
+    lib.wl_pressure_force_weights.argtypes = [P, C.POINTER(C.c_double * 3)]
     lib.wl_force_moment.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3), I, C.POINTER(C.c_double * 3)]
     D3 = C.POINTER(C.c_double * 3)
     lib.wl_measure_csg.argtypes = [P, C.POINTER(WLNode), I, C.c_double]
@@ -270,6 +272,126 @@ def NoBody():
     return AutoBody("none")
 
 
+class ClosureBody:
+    """Any `AbstractBody` given by host code: `measure(x, t) -> (d, n, V)` (src/Body.jl:1-12), vectorised over numpy
+    coordinate arrays (x = D broadcastable arrays; d an array, n and V sequences of D arrays, Float32).  This is the
+    route an arbitrary `AutoBody(sdf,map)` closure takes through the C ABI: `measure!` (src/Body.jl:28-51) and
+    `nds` (src/Metrics.jl:110-113) run on the HOST (`host_measure`, `host_nds`), their results travel through
+    `wl_set_body_coeffs` / `wl_set_force_weights`; everything after that is the device path.  `from_sdf` builds the
+    contract from an sdf and its gradient the way `measure(::AutoBody)` does (src/AutoBody.jl:29-37, identity map)."""
+    kind = 1
+
+    def __init__(self, measure):
+        self.measure = measure
+
+    @classmethod
+    def from_sdf(cls, sdf, grad, vel=None):
+        def measure(x, t):
+            d = np.asarray(sdf(x, t), np.float32)
+            n = [np.asarray(g, np.float32) for g in grad(x, t)]
+            m = np.sqrt(sum(g * g for g in n), dtype=np.float32)
+            with np.errstate(invalid="ignore", divide="ignore"):
+                d = d / m
+                n = [g / m for g in n]
+            V = [np.zeros_like(d) for _ in n] if vel is None else [np.asarray(v, np.float32) + 0 * d for v in vel(x, t)]
+            return d, n, V
+        return cls(measure)
+
+
+def _kern0(d):
+    d64 = d.astype(np.float64)
+    return ((np.float32(1) + d + (np.sin(np.pi * d64) / np.pi).astype(np.float32)) / np.float32(2)).astype(np.float32)
+
+
+def _kern1(d):
+    d64 = d.astype(np.float64)
+    sp, cp = np.sin(np.pi * d64).astype(np.float32), np.cos(np.pi * d64).astype(np.float32)
+    pi = np.float32(np.pi)
+    return ((np.float32(1) - d * d) / np.float32(4) - (d * sp + (np.float32(1) + cp) / pi) / (np.float32(2) * pi)).astype(np.float32)
+
+
+def host_measure(body, dims, t=0.0, eps=1.0, k_offset=0, n_last=None):
+    """`measure!(flow, body; t, ϵ)` (src/Body.jl:28-48) on the host for a ClosureBody, BEFORE its two `BC!` calls (the
+    library applies them): returns (μ₀, μ₁, V, σ) in the mirror's array order.  `k_offset`/`n_last`: the slab of a
+    slab-decomposed sim."""
+    D = len(dims)
+    T = np.float32
+    n = [int(v) + 2 for v in dims]
+    if n_last is not None:
+        n[-1] = n_last + 2
+    full = tuple(n[::-1])
+
+    def loc(i):                                        # loc(i,I) src/core.jl:177 on 0-based indices; i = 0: cell centre
+        out = []
+        for d in range(D):
+            x = (np.arange(n[d]) + (k_offset if d == D - 1 else 0)).astype(T) - T(0.5) - (T(0.5) if i == d + 1 else T(0))
+            shp = [1] * D
+            shp[D - 1 - d] = n[d]
+            out.append(np.broadcast_to(x.reshape(shp), full))
+        return out
+    eps = T(eps)
+    d2 = (T(2) + eps) ** 2
+    inner = tuple(slice(1, -1) for _ in range(D))
+    mu0 = np.ones((D,) + full, T)
+    mu1 = np.zeros((D, D) + full, T)
+    V = np.zeros((D,) + full, T)
+    sig = np.zeros(full, T)
+    # measure_sdf! (src/Body.jl:73-75): σ = sdf at the cell centres of inside(σ), ghosts stay 0
+    dc = np.asarray(body.measure([a[inner] for a in loc(0)], T(t))[0], T)
+    sig[inner] = dc
+    band = np.zeros(full, bool)
+    band[inner] = dc * dc < d2
+    solid = np.zeros(full, bool)
+    solid[inner] = (~(dc * dc < d2)) & (dc < 0)
+    for i in range(D):
+        x = [a[band] for a in loc(i + 1)]
+        if x[0].size:
+            di, ni, Vi = body.measure(x, T(t))
+            di = np.asarray(di, T)
+            bad = np.zeros(di.shape, bool)
+            for g in ni:
+                bad |= np.isnan(np.asarray(g, T))
+            ni = [np.where(bad, T(0), np.asarray(g, T)) for g in ni]
+            Vi = [np.where(bad, T(0), np.asarray(v, T) + 0 * di) for v in Vi]
+            di = np.where(np.abs(di) <= T(0.5), di, np.copysign(di, sig[band]))      # sign consistency, Body.jl:36
+            V[i][band] = Vi[i]
+            q = di / eps
+            m0 = np.where(q < T(-1) + np.sqrt(np.spacing(np.abs(di)).astype(T)), T(0), _kern0(np.minimum(q, T(1))))
+            mu0[i][band] = m0
+            k1 = eps * _kern1(np.clip(q, T(-1), T(1)))
+            for j in range(D):
+                mu1[j, i][band] = k1 * ni[j]           # μ₁[I,i,j]: component i (slow-1), direction j (slowest)
+        mu0[i][solid] = 0
+    return mu0, mu1, V, sig
+
+
+def host_nds(body, dims, t=0.0, k_offset=0, n_last=None):
+    """`nds(body, loc(0,I), t)` (src/Metrics.jl:110-113) on the interior cells: (idx int64 [nnz], w float32 [nnz, D]) in
+    the layout `wl_set_force_weights` takes (entries with |d| >= 1 or a zero weight are dropped)."""
+    D = len(dims)
+    T = np.float32
+    n = [int(v) + 2 for v in dims]
+    if n_last is not None:
+        n[-1] = n_last + 2
+    full = tuple(n[::-1])
+    xs = []
+    for d in range(D):
+        x = (np.arange(n[d]) + (k_offset if d == D - 1 else 0)).astype(T) - T(0.5)
+        shp = [1] * D
+        shp[D - 1 - d] = n[d]
+        xs.append(np.broadcast_to(x.reshape(shp), full))
+    inner = np.zeros(full, bool)
+    inner[tuple(slice(1, -1) for _ in range(D))] = True
+    d, nn, _ = body.measure([a[inner] for a in xs], T(t))
+    d = np.asarray(d, T)
+    near = d * d <= T(1)                                # fastd² = 1: beyond it measure returns n = 0
+    kern = ((T(1) + np.cos(np.pi * np.clip(d, T(-1), T(1)).astype(np.float64)).astype(T)) / T(2)).astype(T)
+    w = np.stack([np.where(near & ~np.isnan(np.asarray(g, T)), np.asarray(g, T) * kern, T(0)) for g in nn], axis=-1).astype(T)
+    keep = np.any(w != 0, axis=-1)
+    idx = np.flatnonzero(inner.ravel())[keep].astype(np.int64)      # C order of (z,y,x) == first dimension fastest
+    return idx, np.ascontiguousarray(w[keep])
+
+
 class _Handle:
     def __init__(self, lib, h):
         self.lib, self.h = lib, h
@@ -330,13 +452,18 @@ class Simulation:
 
     def __init__(self, dims, uBC, L=1.0, *, dt=0.25, nu=0.0, U=None, eps=1.0, perdir=(), exitBC=False,
                  scheme="quick", body=None, u0=None, g=None, maxlevels=10, tol=2e-3, itmx=32, device=0,
-                 T=np.float32, lib=None, flags=0, comm=None):
+                 T=np.float32, lib=None, flags=0, comm=None, dUBCdt=None):
         if np.dtype(T) != np.float32:
             raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: the B200 path is Float32 only")
-        if callable(uBC) or callable(g):
-            raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: Function uBC/g; use the uBC_t/dUdt arguments of "
-                                     "sim_step for space-uniform time-dependent boundary velocity, or "
-                                     "set_bc_function for steady space-varying boundary data")
+        # Function uBC(i,x,t) / g(i,x,t) (src/Flow.jl:128,131): closures stay on the host and are SAMPLED into the
+        # boundary tables / acceleration fields the device path consumes (set_bc_function, set_accel_function), at
+        # t = 0 for the constructor's BC! and at t₁ / (t₀,t₁) before every mom_step (sim_step).  ∂ₜuBC of accelerate!
+        # (the reference differentiates uBC by AD, Flow.jl:72-73) is supplied by the caller as `dUBCdt(i,x,t)`.
+        bc_fn = uBC if callable(uBC) else None
+        if bc_fn is not None:
+            if U is None:
+                raise AssertionError("U must be specified if uBC is a Function")      # src/WaterLily.jl:99
+            uBC = (0.0,) * len(dims)
         if scheme not in SCHEMES:
             raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: convective scheme must be quick, cds or vanLeer")
         self.lib = lib or load_library()
@@ -371,8 +498,15 @@ class Simulation:
         self._dts = [np.float32(dt)]
         self._n = []
         self.last_info = None
+        self._bc_fn = self._accel = None
+        if bc_fn is not None:
+            self.set_bc_function(bc_fn, 0.0)
+            if u0 is None:
+                u0 = lambda i, x: bc_fn(i, x, np.float32(0))                              # ic_function(uBC)
         if u0 is not None:
             self.apply_ic(u0)
+        if callable(g) or dUBCdt is not None:
+            self.set_accel_function(g if callable(g) else None, dUBCdt)
         self._measure(0.0)                                                                      # measure!(flow,body;ϵ)
         self._check(self.lib.wl_build_poisson(self.h))                                        # pois_ctor(flow)
         self.nlevels = self.lib.wl_nlevels(self.h)
@@ -432,9 +566,10 @@ class Simulation:
 
     def set_bc_function(self, uBC, t=0.0):
         """Boundary data from a Function `uBC(i,x,t)` (src/core.jl:201-219), sampled on the host into the tables
-        `wl_set_bc_tables` takes; `None` returns to the constant tuple.  Data that depend on `t` must be re-sampled
-        by the caller before each step (at t₁ = sum(Δt)), and their `∂ₜuBC` term in `accelerate!` is not wired yet.
-        NOT YET RUN on a B200 (see include/wl_b200.h)."""
+        `wl_set_bc_tables` takes; `None` returns to the constant tuple.  The function is kept: `sim_step` re-samples
+        it at t₁ = sum(Δt) before every `mom_step`, the time all four `BC!` of a step use (src/Flow.jl:194,209,231).
+        Its `∂ₜuBC` term in `accelerate!` goes through `set_accel_function(dUdt=...)`."""
+        self._bc_fn = uBC
         if uBC is None:
             self._check(self.lib.wl_set_bc_tables(self.h, None, 0))
             return
@@ -445,10 +580,14 @@ class Simulation:
         assert flat.size == n.value, (flat.size, n.value)
         self._check(self.lib.wl_set_bc_tables(self.h, flat.ctypes.data, flat.size))
 
+    def _upload_bc(self, t):
+        from . import bctables
+        flat = bctables.pack(bctables.bc_tables(self._bc_fn, self.dims, t, self.perdir), self.dims)
+        self._check(self.lib.wl_set_bc_tables(self.h, flat.ctypes.data, flat.size))
+
     def set_accel_function(self, g=None, dUdt=None):
         """`g(i,x,t)` and `∂ₜuBC(i,x,t)` of `accelerate!` (src/Flow.jl:69-73) as Functions: sampled on the host on every
-        index at t₀ and t₁ before each `mom_step` of `sim_step` and uploaded (`wl_set_accel_field`); both None clears.
-        NOT YET RUN on a B200 (see include/wl_b200.h)."""
+        index at t₀ and t₁ before each `mom_step` of `sim_step` and uploaded (`wl_set_accel_field`); both None clears."""
         self._accel = None if (g is None and dUdt is None) else (g, dUdt)
         if self._accel is None:
             self._check(self.lib.wl_set_accel_field(self.h, 0, None, 0))
@@ -480,7 +619,11 @@ class Simulation:
         self._check(self.lib.wl_update_poisson(self.h))
 
     def _measure(self, t):
-        if isinstance(self.body, RigidBody):
+        if isinstance(self.body, ClosureBody):          # host measure! + upload (src/Body.jl:28-51)
+            nl = self.dims[-1] // self.nranks if (self.nranks > 1 and self.D == 3) else None
+            mu0, mu1, V, sdf = host_measure(self.body, self.dims, t, self.eps, self.k_offset, nl)
+            self._check(self.lib.wl_set_body_coeffs(self.h, mu0.ctypes.data, mu1.ctypes.data, V.ctypes.data, sdf.ctypes.data))
+        elif isinstance(self.body, RigidBody):
             arr, n = self.body.nodes()
             self._check(self.lib.wl_measure_csg(self.h, arr, n, float(self.eps)))
         else:
@@ -519,7 +662,11 @@ class Simulation:
                 self.measure()
             t1 = float(np.sum(np.asarray(self._dts, np.float32), dtype=np.float32))
             t0 = float(np.float32(t1) - self._dts[-1])
-            if getattr(self, "_accel", None) is not None:
+            if self._bc_fn is not None:
+                if uBC_t is not None:
+                    raise WaterLilyB200Error("WL_ERR_INVALID: a Function uBC (set_bc_function) and uBC_t are mutually exclusive")
+                self._upload_bc(t1)
+            if self._accel is not None:
                 self._upload_accel(t0, t1)
             self.mom_step(None if uBC_t is None else uBC_t(t1),
                           None if dUdt is None else dUdt(t0), None if dUdt is None else dUdt(t1))
@@ -555,7 +702,12 @@ class Simulation:
         """`pressure_force(sim)` (src/Metrics.jl:116-133)."""
         out = (C.c_double * 3)()
         t = self.time() if t is None else t
-        if isinstance(self.body, RigidBody):
+        if isinstance(self.body, ClosureBody):          # host nds (src/Metrics.jl:110-113) -> sparse weights -> device sum
+            nl = self.dims[-1] // self.nranks if (self.nranks > 1 and self.D == 3) else None
+            idx, w = host_nds(self.body, self.dims, t, self.k_offset, nl)
+            self._check(self.lib.wl_set_force_weights(self.h, idx.size, idx.ctypes.data, w.ctypes.data))
+            self._check(self.lib.wl_pressure_force_weights(self.h, C.byref(out)))
+        elif isinstance(self.body, RigidBody):
             arr, n = self.body.nodes()
             self._check(self.lib.wl_pressure_force_csg(self.h, arr, n, C.byref(out)))
         else:
@@ -564,6 +716,8 @@ class Simulation:
 
     def viscous_force(self, t=None):
         """`viscous_force(sim)` (src/Metrics.jl:140-152)."""
+        if isinstance(self.body, ClosureBody):
+            raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: viscous_force for a host-measured body")
         out = (C.c_double * 3)()
         t = self.time() if t is None else t
         if isinstance(self.body, RigidBody):
@@ -575,6 +729,8 @@ class Simulation:
 
     def moment(self, x0, viscous=False, t=None):
         """`pressure_moment(x₀,sim)` / `viscous_moment(x₀,sim)` (src/Metrics.jl:168-192)."""
+        if isinstance(self.body, ClosureBody):
+            raise WaterLilyB200Error("WL_ERR_UNSUPPORTED: moments for a host-measured body")
         out = (C.c_double * 3)()
         t = self.time() if t is None else t
         xx = (C.c_double * 3)(*(list(x0) + [0.0] * (3 - len(x0))))
@@ -600,13 +756,15 @@ class Simulation:
         self._check(self.lib.wl_prof_begin(self.h, filt.encode()))
 
     def prof_end(self):
-        """-> {kernel name: (launches, total_ms)} measured with CUDA events on the launching stream."""
+        """-> {kernel name: (launches, total_ms)} measured with CUDA events on the launching stream
+        (`self.prof_blocks[name]` = thread blocks launched, the work size behind those times)."""
         buf = C.create_string_buffer(1 << 16)
         self.lib.wl_prof_end(self.h, buf, len(buf))
-        out = {}
+        out, self.prof_blocks = {}, {}
         for line in buf.value.decode().splitlines():
-            name, n, ms = line.split("\t")
+            name, n, ms, blocks = line.split("\t")
             out[name] = (int(n), float(ms))
+            self.prof_blocks[name] = int(blocks)
         return out
 
     def event_record(self, slot):

@@ -363,6 +363,8 @@ void wl_destroy(wl_sim* s) {
   if (s->d_redg) cudaFree(s->d_redg);
   if (s->stage) cudaFree(s->stage);
   if (s->bc_tab) cudaFree(s->bc_tab);
+  if (s->fw_off) cudaFree(s->fw_off);
+  if (s->fw_w) cudaFree(s->fw_w);
   if (s->h_redg) cudaFreeHost(s->h_redg);
   for (size_t l = 0; l < s->lv.size(); ++l) {
     Level& v = s->lv[l];
@@ -736,6 +738,47 @@ int wl_pressure_force(wl_sim* s, const wl_body* body, double t, double out[3]) {
   if (!s || !body || !out) return WL_ERR_INVALID;
   return pressure_force_impl(s, body_at(body, s->D, (float)t), out, "wl_pressure_force");
 }
+// nds weights of a host-measured body (src/Metrics.jl:110-113,126-133): idx = linear index into the reference's
+// (n0,n1[,n2]) scalar array (first dimension fastest, 0-based), w = D floats per entry
+int wl_set_force_weights(wl_sim* s, int64_t nnz, const int64_t* idx, const float* w) {
+  if (!s || nnz < 0 || (nnz > 0 && (!idx || !w))) return WL_ERR_INVALID;
+  cudaSetDevice(s->device);
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  if (s->fw_off) cudaFree(s->fw_off);
+  if (s->fw_w) cudaFree(s->fw_w);
+  s->fw_off = nullptr; s->fw_w = nullptr; s->fw_n = -1;
+  if (nnz > 0x7fffffff) return fail(s, WL_ERR_INVALID, "too many force weights");
+  const Lay& l = s->lay;
+  std::vector<int> off((size_t)nnz);
+  const long long per = (long long)l.n0 * l.n1 * l.n2;
+  for (int64_t q = 0; q < nnz; ++q) {
+    const long long g = idx[q];
+    if (g < 0 || g >= per) return fail(s, WL_ERR_INVALID, "force weight index outside the scalar field");
+    const int i = (int)(g % l.n0), j = (int)((g / l.n0) % l.n1), k = (int)(g / ((long long)l.n0 * l.n1));
+    off[q] = l.off(i, j, k);
+  }
+  if (nnz > 0) {
+    WL_CUDA(s, cudaMalloc(&s->fw_off, sizeof(int) * (size_t)nnz));
+    WL_CUDA(s, cudaMalloc(&s->fw_w, sizeof(float) * (size_t)nnz * s->D));
+    WL_CUDA(s, cudaMemcpy(s->fw_off, off.data(), sizeof(int) * (size_t)nnz, cudaMemcpyHostToDevice));
+    WL_CUDA(s, cudaMemcpy(s->fw_w, w, sizeof(float) * (size_t)nnz * s->D, cudaMemcpyHostToDevice));
+  }
+  s->fw_n = (int)nnz;
+  return WL_OK;
+}
+int wl_pressure_force_weights(wl_sim* s, double out[3]) {
+  if (!s || !out) return WL_ERR_INVALID;
+  if (s->fw_n < 0) return fail(s, WL_ERR_INVALID, "wl_set_force_weights has not been called");
+  cudaSetDevice(s->device);
+  const int nb = std::max(1, std::min((s->fw_n + 255) / 256, 592));
+  for (int c = 0; c < s->D; ++c) {
+    ForceWArgs a{s->p.base, s->fw_off, s->fw_w, s->fw_n, s->D, c, s->redw, s->d_red + 3 + c};
+    LAUNCH(s, k_force_w, dim3(nb), dim3(256), a);
+  }
+  if (int e = fetch_red(s)) return e;
+  for (int c = 0; c < 3; ++c) out[c] = c < s->D ? s->h_red[3 + c].sum : 0.0;
+  return check_async(s, "wl_pressure_force_weights");
+}
 int wl_viscous_force(wl_sim* s, const wl_body* body, double t, double out[3]) {
   if (!s || !body || !out) return WL_ERR_INVALID;
   return viscous_force_impl(s, body_at(body, s->D, (float)t), out, "wl_viscous_force");
@@ -833,13 +876,13 @@ int wl_prof_begin(wl_sim* s, const char* filter) {
   s->prof_filter = filter ? filter : "";
   return WL_OK;
 }
-// Writes one line per kernel: "<name>\t<launches>\t<total_ms>\n"; returns the number of kernels.
+// Writes one line per kernel: "<name>\t<launches>\t<total_ms>\t<total_blocks>\n"; returns the number of kernels.
 int wl_prof_end(wl_sim* s, char* buf, size_t buflen) {
   if (!s) return WL_ERR_INVALID;
   cudaSetDevice(s->device);
   cudaStreamSynchronize(s->st);
   s->prof_on = false;
-  struct Acc { const char* name; long n; double ms; };
+  struct Acc { const char* name; long n; double ms; long long blocks; };
   std::vector<Acc> acc;
   for (auto& r : s->recs) {
     float ms = 0.f;
@@ -847,13 +890,13 @@ int wl_prof_end(wl_sim* s, char* buf, size_t buflen) {
     s->evpool.push_back(r.a); s->evpool.push_back(r.b);
     size_t i = 0;
     for (; i < acc.size(); ++i) if (acc[i].name == r.name || !strcmp(acc[i].name, r.name)) break;
-    if (i == acc.size()) acc.push_back({r.name, 0, 0.0});
-    acc[i].n++; acc[i].ms += ms;
+    if (i == acc.size()) acc.push_back({r.name, 0, 0.0, 0});
+    acc[i].n++; acc[i].ms += ms; acc[i].blocks += r.blocks;
   }
   s->recs.clear();
   std::string out;
   char line[256];
-  for (auto& a : acc) { snprintf(line, sizeof line, "%s\t%ld\t%.6f\n", a.name, a.n, a.ms); out += line; }
+  for (auto& a : acc) { snprintf(line, sizeof line, "%s\t%ld\t%.6f\t%lld\n", a.name, a.n, a.ms, a.blocks); out += line; }
   if (buf && buflen) { strncpy(buf, out.c_str(), buflen - 1); buf[buflen - 1] = 0; }
   return (int)acc.size();
 }

@@ -65,7 +65,7 @@ struct Dist {
   long long min_cells = 1 << 20;           // ... and so are levels with at most this many cells in total
 };
 
-struct ProfRec { const char* name; cudaEvent_t a, b; };
+struct ProfRec { const char* name; cudaEvent_t a, b; long long blocks; };
 
 }  // namespace
 
@@ -109,6 +109,7 @@ struct wl_sim {
   int band_cap2 = 0, band_epoch = 0;
   bool band_dirty = false;
   bool band_from_measure = false;   // k_measure appended the band cells itself: only the count has to be checked
+  int* fw_off = nullptr; float* fw_w = nullptr; int fw_n = -1;   // pressure_force weights of a host-measured body (wl_set_force_weights)
   bool free_flow = true;      // V ≡ 0, μ₀ ≡ 1, μ₁ ≡ 0 as the constructor left them (no measure!, no upload of them)
   std::vector<Level> lv;
   cudaStream_t st = nullptr;
@@ -232,17 +233,18 @@ inline bool prof_pre(wl_sim* s, const char* name, cudaEvent_t* a, cudaEvent_t* b
   cudaEventRecord(*a, s->st);
   return true;
 }
-inline void prof_post(wl_sim* s, const char* name, cudaEvent_t a, cudaEvent_t b) {
+inline void prof_post(wl_sim* s, const char* name, cudaEvent_t a, cudaEvent_t b, const dim3& g = dim3(0)) {
   cudaEventRecord(b, s->st);
-  s->recs.push_back({name, a, b});
+  s->recs.push_back({name, a, b, (long long)g.x * g.y * g.z});
 }
 
 #define LAUNCH(s, kern, g, b, ...)                         \
   do {                                                     \
     cudaEvent_t pa_, pb_;                                  \
     const bool prof_ = prof_pre(s, #kern, &pa_, &pb_);     \
-    launch_pdl((s)->st, g, b, kern, __VA_ARGS__);          \
-    if (prof_) prof_post(s, #kern, pa_, pb_);              \
+    const dim3 g_ = (g);                                   \
+    launch_pdl((s)->st, g_, b, kern, __VA_ARGS__);         \
+    if (prof_) prof_post(s, #kern, pa_, pb_, g_);          \
     ++(s)->launches;                                       \
   } while (0)
 

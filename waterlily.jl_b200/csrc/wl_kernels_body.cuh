@@ -462,6 +462,21 @@ __global__ void __launch_bounds__(256) k_sum_all(const SumArgs a) {
   block_reduce_finish(s, -INFINITY, a.w, a.out);
 }
 
+// pressure_force for a HOST-measured body (an arbitrary AutoBody closure cannot cross the C ABI): the caller
+// evaluates nds(body,loc(0,I),t) = n·kern(clamp(d,-1,1)) (src/Metrics.jl:110-113) on the cells with |d| < 1 and
+// uploads them as a sparse list; df[I,c] = p[I]·w[I,c] is formed in Float32 as the reference's `@loop` does
+// (:130) and summed in Float64 (:131).  One launch per component (the block reduction owns the tickets).
+struct ForceWArgs { const float* p; const int* off; const float* w; int nnz, D, comp; RedWork rw; Red* out; };
+__global__ void __launch_bounds__(256) k_force_w(const ForceWArgs a) {
+  pdl_entry();
+  double s = 0.0;
+  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < a.nnz; q += gridDim.x * blockDim.x) {
+    const float df = a.p[a.off[q]] * a.w[(size_t)q * a.D + a.comp];
+    s += (double)df;
+  }
+  block_reduce_finish(s, -INFINITY, a.rw, a.out);
+}
+
 // ---------------------------------------------------------------- host <-> device repacking
 // The C ABI moves fields in the reference's dense layout (n0,n1,n2[,comp]); one contiguous DMA to or
 // from a packed device buffer plus this kernel replaces a strided cudaMemcpy2D per component (whose

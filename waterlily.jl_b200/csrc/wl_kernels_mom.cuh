@@ -93,9 +93,10 @@ __device__ __forceinline__ float rhs_f(const MomArgs& a, int ci, int c0, int c1,
         r -= face_flux<S>(ui, uj, o + st[dj], st[ci], st[dj], cu, Nu, pj, a.nu);
     }
   }
-  r += a.acc.v[ci];
   const long long oc = l.cstride * ci + o;
-  if (ACCF) r += accf[oc];
+  // accelerate! adds g + ∂ₜU as ONE term (Flow.jl:73): uniform part and sampled field are summed first
+  if (ACCF) r += a.acc.v[ci] + accf[oc];
+  else r += a.acc.v[ci];
   return a.u0[oc] + a.dt * r - a.V[oc];
 }
 
