@@ -90,9 +90,11 @@ def measure_loop(ref, sdf, grad, eps=1.0):
     sig = np.zeros(ref.field("sigma").shape, T)
     d2 = T((2 + eps) ** 2)
 
-    def meas(x):
+    def meas(x, fastd2):                                # measure(::AutoBody) src/AutoBody.jl:29-37, identity map
         xa = [np.array([v], T) for v in x]
         d = T(sdf(xa, 0)[0])
+        if d * d > fastd2:
+            return d, np.zeros(D, T)
         g = np.array([gg[0] for gg in grad(xa, 0)], T)
         if np.isnan(g).any():
             return d, np.zeros(D, T)
@@ -102,13 +104,13 @@ def measure_loop(ref, sdf, grad, eps=1.0):
         I = tuple(v + 1 for v in I)                      # 0-based interior index, x fastest LAST in this tuple order
         a = I[::-1]                                      # array index (z, y, x)
         xc = [T(I[d]) - T(0.5) for d in range(D)]
-        d, _ = meas(xc)
+        d = T(sdf([np.array([v], T) for v in xc], 0)[0])  # measure_sdf!: the raw sdf
         sig[a] = d
         if d * d < d2:
             for i in range(D):
                 xi = list(xc)
                 xi[i] = xi[i] - T(0.5)
-                di, ni = meas(xi)
+                di, ni = meas(xi, d2)
                 di = di if abs(di) <= 0.5 else T(np.copysign(di, d))
                 mu0[(i,) + a] = ref.lib.wlo_mu0(di, eps)
                 for j in range(D):
@@ -178,10 +180,12 @@ def test_moving_closure_body_remeasure(wl):
     c0, Vb, R = np.float32([10.3, 11.7, 8.2]), np.float32([0.5, 0.0, 0.0]), np.float32(4.1)   # no cell sits on the band edge
     lib_body = wl.AutoBody("sphere", tuple(c0), float(R), vel=tuple(Vb))
 
-    def measure(x, t):
+    def measure(x, t, fastd2=np.inf):
         c = [cc + vv * np.float32(t) for cc, vv in zip(c0, Vb)]
         q = np.sqrt(sum((xx - cc) ** 2 for xx, cc in zip(x, c)))
-        return (q - R).astype(np.float32), [((xx - cc) / q).astype(np.float32) for xx, cc in zip(x, c)], [vv + 0 * q for vv in Vb]
+        d = (q - R).astype(np.float32)
+        near = d * d <= np.float32(fastd2)                          # measure(::AutoBody) returns n = V = 0 beyond fastd²
+        return d, [np.where(near, (xx - cc) / q, 0).astype(np.float32) for xx, cc in zip(x, c)], [np.where(near, vv, 0).astype(np.float32) for vv in Vb]
     a = wl.Simulation(dims, (0.0, 0.0, 0.0), 8.0, body=lib_body, nu=0.05, U=1.0)
     b = wl.Simulation(dims, (0.0, 0.0, 0.0), 8.0, body=wl.ClosureBody(measure), nu=0.05, U=1.0)
     for _ in range(3):

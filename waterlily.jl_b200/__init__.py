@@ -273,29 +273,37 @@ def NoBody():
 
 
 class ClosureBody:
-    """Any `AbstractBody` given by host code: `measure(x, t) -> (d, n, V)` (src/Body.jl:1-12), vectorised over numpy
-    coordinate arrays (x = D broadcastable arrays; d an array, n and V sequences of D arrays, Float32).  This is the
-    route an arbitrary `AutoBody(sdf,map)` closure takes through the C ABI: `measure!` (src/Body.jl:28-51) and
-    `nds` (src/Metrics.jl:110-113) run on the HOST (`host_measure`, `host_nds`), their results travel through
+    """Any `AbstractBody` given by host code: `measure(x, t, fastd2) -> (d, n, V)` (src/Body.jl:1-12), vectorised over
+    numpy coordinate arrays (x = D broadcastable arrays; d an array, n and V sequences of D arrays, Float32; where
+    d² > fastd2 a fast method may return n = V = 0, as `measure(::AutoBody)` does).  Optional `sdf(x, t)` = the distance
+    alone (`sdf(body,x,t)`, src/Body.jl:66-68; default `measure(...)[0]`).  This is the route an arbitrary
+    `AutoBody(sdf,map)` closure takes through the C ABI: `measure!` (src/Body.jl:28-51) and `nds`
+    (src/Metrics.jl:110-113) run on the HOST (`host_measure`, `host_nds`), their results travel through
     `wl_set_body_coeffs` / `wl_set_force_weights`; everything after that is the device path.  `from_sdf` builds the
-    contract from an sdf and its gradient the way `measure(::AutoBody)` does (src/AutoBody.jl:29-37, identity map)."""
+    contract from an sdf and its gradient exactly as `measure(::AutoBody)` does (src/AutoBody.jl:29-37, identity map)."""
     kind = 1
 
-    def __init__(self, measure):
+    def __init__(self, measure, sdf=None):
         self.measure = measure
+        self.sdf = sdf if sdf is not None else (lambda x, t: measure(x, t, np.float32(0))[0])
 
     @classmethod
     def from_sdf(cls, sdf, grad, vel=None):
-        def measure(x, t):
-            d = np.asarray(sdf(x, t), np.float32)
+        def measure(x, t, fastd2=np.inf):
+            d = np.asarray(sdf(x, t), np.float32) + np.float32(0) * x[0]
+            far = d * d > np.float32(fastd2)                         # AutoBody.jl:31: return (d, 0, 0) un-normalised
             n = [np.asarray(g, np.float32) for g in grad(x, t)]
+            bad = np.zeros(d.shape, bool)
+            for g in n:
+                bad = bad | np.isnan(g)                              # AutoBody.jl:33: non-differentiable points
             m = np.sqrt(sum(g * g for g in n), dtype=np.float32)
+            skip = far | bad
             with np.errstate(invalid="ignore", divide="ignore"):
-                d = d / m
-                n = [g / m for g in n]
-            V = [np.zeros_like(d) for _ in n] if vel is None else [np.asarray(v, np.float32) + 0 * d for v in vel(x, t)]
+                d = np.where(skip, d, d / m)
+                n = [np.where(skip, np.float32(0), g / m) for g in n]
+            V = [np.zeros_like(d) for _ in n] if vel is None else [np.where(skip, np.float32(0), np.asarray(v, np.float32) + 0 * d) for v in vel(x, t)]
             return d, n, V
-        return cls(measure)
+        return cls(measure, lambda x, t: np.asarray(sdf(x, t), np.float32) + np.float32(0) * x[0])
 
 
 def _kern0(d):
@@ -337,7 +345,7 @@ def host_measure(body, dims, t=0.0, eps=1.0, k_offset=0, n_last=None):
     V = np.zeros((D,) + full, T)
     sig = np.zeros(full, T)
     # measure_sdf! (src/Body.jl:73-75): σ = sdf at the cell centres of inside(σ), ghosts stay 0
-    dc = np.asarray(body.measure([a[inner] for a in loc(0)], T(t))[0], T)
+    dc = np.asarray(body.sdf([a[inner] for a in loc(0)], T(t)), T)
     sig[inner] = dc
     band = np.zeros(full, bool)
     band[inner] = dc * dc < d2
@@ -346,7 +354,7 @@ def host_measure(body, dims, t=0.0, eps=1.0, k_offset=0, n_last=None):
     for i in range(D):
         x = [a[band] for a in loc(i + 1)]
         if x[0].size:
-            di, ni, Vi = body.measure(x, T(t))
+            di, ni, Vi = body.measure(x, T(t), d2)
             di = np.asarray(di, T)
             bad = np.zeros(di.shape, bool)
             for g in ni:
@@ -382,9 +390,9 @@ def host_nds(body, dims, t=0.0, k_offset=0, n_last=None):
         xs.append(np.broadcast_to(x.reshape(shp), full))
     inner = np.zeros(full, bool)
     inner[tuple(slice(1, -1) for _ in range(D))] = True
-    d, nn, _ = body.measure([a[inner] for a in xs], T(t))
+    d, nn, _ = body.measure([a[inner] for a in xs], T(t), T(1))
     d = np.asarray(d, T)
-    near = d * d <= T(1)                                # fastd² = 1: beyond it measure returns n = 0
+    near = np.ones(d.shape, bool)                       # (fastd² = 1: beyond it the body's measure returns n = 0 itself)
     kern = ((T(1) + np.cos(np.pi * np.clip(d, T(-1), T(1)).astype(np.float64)).astype(T)) / T(2)).astype(T)
     w = np.stack([np.where(near & ~np.isnan(np.asarray(g, T)), np.asarray(g, T) * kern, T(0)) for g in nn], axis=-1).astype(T)
     keep = np.any(w != 0, axis=-1)

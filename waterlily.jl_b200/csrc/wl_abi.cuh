@@ -16,7 +16,7 @@ int build_levels(wl_sim* s) {
     Level& v = s->lv[l];
     free_field(v.L); free_field(v.x); free_field(v.z);
   }
-  for (auto& v : s->lv) { free_field(v.r); free_field(v.eps); free_field(v.Dg); free_field(v.iD); }
+  for (auto& v : s->lv) { free_field(v.r); free_field(v.eps); free_field(v.Dg); free_field(v.iD); free_field(v.tmp); }
   s->lv.clear();
   s->lv.reserve(s->cfg.maxlevels + 2);
   s->lv.emplace_back();
@@ -38,6 +38,7 @@ int build_levels(wl_sim* s) {
     if (int e = alloc_field(s, l0.eps, s->lay, 1)) return e;
     if (int e = alloc_field(s, l0.Dg, s->lay, 1)) return e;
     if (int e = alloc_field(s, l0.iD, s->lay, 1)) return e;
+    if (int e = alloc_field(s, l0.tmp, s->lay, 1)) return e;
     if (int e = set_diag_h(s, l0)) return e;
   }
   auto anydiv = [&]() {
@@ -76,6 +77,7 @@ int build_levels(wl_sim* s) {
     if (int e = alloc_field(s, co.eps, co.lay, 1)) return e;
     if (int e = alloc_field(s, co.Dg, co.lay, 1)) return e;
     if (int e = alloc_field(s, co.iD, co.lay, 1)) return e;
+    if (int e = alloc_field(s, co.tmp, co.lay, 1)) return e;
     if (int e = restrictL(s, s->lv[s->lv.size() - 2], co)) return e;
     if (int e = set_diag_h(s, co)) return e;
   }
@@ -90,7 +92,7 @@ size_t plan_arena_bytes(wl_sim* s) {
   const int D = s->D;
   size_t tot = ARENA_HDR;                                               // flags, gather tables
   tot += fld(s->lay, D) * 6 + fld(s->lay, 1) * 2 + fld(s->lay, D * D);   // u,u0,f,V,mu0,w ; p,sigma ; mu1
-  tot += fld(s->lay, 1) * 4;                                            // level 0: r, eps, D, iD
+  tot += fld(s->lay, 1) * 5;                                            // level 0: r, eps, D, iD, tmp
   int gn[3] = {s->lay.n0, s->lay.n1, s->dist.nzg + 2};
   bool fdist = true;
   int nzf = s->lay.n2 - 2;
@@ -108,7 +110,7 @@ size_t plan_arena_bytes(wl_sim* s) {
     }
     fdist = cdist;
     const Lay l = make_lay(D, ng);
-    tot += fld(l, D) + fld(l, 1) * 6;
+    tot += fld(l, D) + fld(l, 1) * 7;
     ++nlev;
   }
   return tot + tot / 64 + (1 << 20);
@@ -369,7 +371,7 @@ void wl_destroy(wl_sim* s) {
   for (size_t l = 0; l < s->lv.size(); ++l) {
     Level& v = s->lv[l];
     if (v.owns) { free_field(v.L); free_field(v.x); free_field(v.z); }
-    free_field(v.r); free_field(v.eps); free_field(v.Dg); free_field(v.iD);
+    free_field(v.r); free_field(v.eps); free_field(v.Dg); free_field(v.iD); free_field(v.tmp);
   }
   free_field(s->u); free_field(s->u0); free_field(s->f); free_field(s->p);
   free_field(s->sigma); free_field(s->V); free_field(s->mu0); free_field(s->mu1); free_field(s->w);
