@@ -55,7 +55,7 @@ typedef struct wl_config {
 
 #define WL_FLAG_NO_GRAPHS 1   /* disable CUDA-graph replay of the V-cycle (debugging) */
 #define WL_FLAG_NO_FUSED 2    /* 3D: use the un-fused K-RHS + K-BDIM kernels (materialises flow.f) */
-#define WL_FLAG_FUSED_SMOOTH 4 /* 3D: single-kernel smoother (ϵ kept in shared memory); experimental */
+#define WL_FLAG_FUSED_SMOOTH 4 /* 3D: K-GS2, two red-black sweeps per pass (wl_kernels_gs2.cuh); bit-identical, opt-in: slower for now */
 
 /* Parametric AutoBody: primitive sdf composed with map(x,t) = x - centre(t),
  * centre(t) = center + vel*t + acc*t^2 + amp*sin(omega*t)  (src/AutoBody.jl:1-37).

@@ -20,7 +20,6 @@
 #include "wl_kernels_mg2.cuh"
 #include "wl_kernels_mom.cuh"
 #include "wl_kernels_mom3.cuh"
-#include "wl_kernels_smooth.cuh"
 #include "wl_kernels_mg4.cuh"
 #include "wl_kernels_gs2.cuh"
 #include "wl_kernels_pcg.cuh"
@@ -568,53 +567,12 @@ void fold_partials_to(wl_sim* s, const dim3& g, Red* out) {
   LAUNCH(s, k_fold_partials, dim3(1), dim3(1024), fa);
 }
 
-// K-SMOOTH applies when no reference quirk outside its model is in play: 3D, even last dimension
-// (half_rangek sweeps every plane), even interior extent in periodic directions (colours continue
-// across the seam), and extents that the 5-cell halo cannot wrap twice.
-bool smooth_fusable(wl_sim* s, const Level& p) {
-  // opt-in (WL_FLAG_FUSED_SMOOTH or WL_FUSED_SMOOTH=1): bit-identical to the per-sweep kernels but, at
-  // ~620 issued instructions per thread and plane, not yet faster than them
-  static int env = -1;
-  if (env < 0) env = getenv("WL_FUSED_SMOOTH") ? 1 : 0;
-  if (!(env || (s->cfg.flags & WL_FLAG_FUSED_SMOOTH)) || s->D != 3 || p.dist) return false;
-  const Lay& l = p.lay;
-  if (l.n2 % 2 != 0 || l.n0 - 2 < 8 || l.n1 - 2 < 8 || l.n2 - 2 < 8) return false;
-  for (int d = 0; d < 3; ++d) if (p.per.p[d] && (l.n(d) - 2) % 2 != 0) return false;
-  return true;
-}
-int smooth_fused(wl_sim* s, Level& p, float w, Red* norms) {
-  static bool attr = false;
-  if (!attr) {
-    cudaFuncSetAttribute(k_smooth_fused<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SfSmem));
-    attr = true;
-  }
-  const Lay& l = p.lay;
-  SmoothFArgs a{};
-  a.p = levdev(p); a.rn = p.eps.base; a.per = p.per; a.omega = w;
-  a.w = s->redw; a.out = norms ? norms : s->d_red; a.want_norms = norms ? 1 : 0;
-  a.zh = 0; a.seam_zlo = a.seam_zhi = 0;
-  const int gx = (l.n0 - 2 + SF_TX - 1) / SF_TX, gy = (l.n1 - 2 + SF_TY - 1) / SF_TY;
-  int KZ = l.n2 - 2;
-  while (KZ > SF_MAXKZ) KZ = (KZ + 1) / 2;
-  // every z-chunk recomputes 10 warm-up planes: chunks of >= 32 planes, and only as many as fill the GPU once
-  while (KZ > 32 && (long long)gx * gy * ((l.n2 - 2 + KZ - 1) / KZ) < 148 * 2) KZ = (KZ + 1) / 2;
-  a.KZ = KZ;
-  dim3 g(gx, gy, (l.n2 - 2 + KZ - 1) / KZ);
-  {
-    cudaEvent_t pa_, pb_;
-    const bool prof_ = prof_pre(s, "k_smooth_fused<3>", &pa_, &pb_);
-    k_smooth_fused<3><<<g, SF_NT, sizeof(SfSmem), s->st>>>(a);
-    if (prof_) prof_post(s, "k_smooth_fused<3>", pa_, pb_);
-    ++s->launches;
-  }
-  std::swap(p.r, p.eps);                           // the new residual was staged in the idle ϵ array
-  return WL_OK;
-}
 // K-GS2 (wl_kernels_gs2.cuh): the four colour sweeps as two passes.  Single-GPU levels that the 4-cells-per-thread
 // kernels serve (row length a multiple of 4) with an even last dimension (half_rangek then sweeps every plane).
+// Opt-in (WL_FLAG_FUSED_SMOOTH): bit-identical to the per-sweep kernels and at the traffic goal (27 + 32 B/cell instead of
+// 4 x 24), but issue-bound and slower for now (profiles/r2_smoother_experiments.md).
 bool pair_ok(wl_sim* s, const Level& p) {
-  static const bool on = getenv("WL_GS_PAIR") != nullptr;      // opt-in: measured slower than the L2-blocked sweeps
-  return on && s->D == 3 && !p.dist && p.tmp.alloc && use_vec4(p.lay) && p.lay.n2 % 2 == 0 && p.lay.n2 >= 4;
+  return (s->cfg.flags & WL_FLAG_FUSED_SMOOTH) && s->D == 3 && !p.dist && p.tmp.alloc && use_vec4(p.lay) && p.lay.n2 % 2 == 0 && p.lay.n2 >= 4;
 }
 void gs_pairs(wl_sim* s, Level& p) {
   const Lay& l = p.lay;
@@ -652,73 +610,7 @@ void gs_pairs(wl_sim* s, Level& p) {
   }
   std::swap(p.eps, p.tmp);
 }
-// ---- L2-blocked post-smoothing.  The four colour sweeps and the increment each stream the whole level (24-32 B per
-// cell and pass) although every pass only needs the previous pass on the neighbouring planes.  A level much larger
-// than the 126 MB L2 is therefore processed in slabs of planes whose working set (r, x, ϵ, iD, L) fits the L2, each
-// stage one plane behind the previous one (K-UP, sweep 1..4, increment: stage q on plane p after stage q-1 on planes
-// p-1..p+1): HBM sees the fields once per smooth instead of once per pass, the rest is L2 traffic.  Same kernels on
-// plane ranges, same arithmetic, reduction slots of the full launch: bit-identical.  A periodic last dimension keeps
-// its stale-ghost semantics: K-UP serves the last two planes first (the sweeps read their ϵ image below plane 1) and
-// the increment of planes 1-2 (which wrap-reads the final ϵ of the top plane) runs last.
-bool l2_blocked(wl_sim* s, const Level& p) {
-  static const bool off = getenv("WL_NO_L2_BLOCK") != nullptr;
-  static const long long min_cells = getenv("WL_L2_BLOCK_MIN_CELLS") ? atoll(getenv("WL_L2_BLOCK_MIN_CELLS")) : 6000000;
-  if (off || s->D != 3 || p.dist || !use_vec4(p.lay) || (p.lay.n2 - 2) % 2 != 0 || blk(3).z != 2) return false;
-  if (smooth_fusable(s, p) || pair_ok(s, p)) return false;
-  return (long long)(p.lay.n0 - 2) * (p.lay.n1 - 2) * (p.lay.n2 - 2) >= min_cells && p.lay.n2 - 2 >= 8;
-}
-int l2_slab_planes(const Lay& l) {
-  static const int mb = getenv("WL_L2_SLAB_MB") ? atoi(getenv("WL_L2_SLAB_MB")) : 48;
-  static const int planes = getenv("WL_L2_SLAB_PLANES") ? atoi(getenv("WL_L2_SLAB_PLANES")) : 0;   // tests: force thin slabs
-  long long S = planes > 0 ? planes : ((long long)mb << 20) / (7LL * l.plane * 4);
-  S = S < 4 ? 4 : S;
-  return (int)(S & ~1LL);
-}
-int smooth_blocked(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready, const UpArgs* up) {
-  const Lay& l = p.lay;
-  const int nz = l.n2 - 2, S = l2_slab_planes(l);
-  const bool pz = p.per.p[2] != 0;
-  SmArgs a{levdev(p), p.per, w, 0, s->redw, norms ? norms : s->d_red, norms ? 1 : 0};
-  a.w.finish = 0;
-  if (!eps_ready && !up) DISPATCH_D(s, k_eps_init_g, grid_inside(l), blk(s->D), a);
-  LevArgs g = lev_args(s, p);
-  dim3 gg = grid_inside(l);
-  gg.x = (l.n0 - 2 + 2 * blk(3).x - 1) / (2 * blk(3).x);
-  const dim3 gq = grid_quads(l);
-  auto zrange = [](int lo, int hi) { return ZRange{(lo - 1) / 2, lo, hi}; };
-  auto nzb = [](int lo, int hi) { return (unsigned)((hi - 1) / 2 - (lo - 1) / 2 + 1); };
-  UpArgs u{};
-  if (up) u = *up;
-  auto run_up = [&](int lo, int hi) {
-    if (lo > hi) return;
-    u.zr = zrange(lo, hi);
-    LAUNCH(s, k_up4, dim3(gq.x, gq.y, nzb(lo, hi)), dim3(32, 4, 2), u);
-  };
-  auto run_incr = [&](int lo, int hi) {
-    if (lo > hi) return;
-    a.zr = zrange(lo, hi);
-    LAUNCH(s, k_incr4, dim3(gq.x, gq.y, nzb(lo, hi)), dim3(32, 4, 2), a);
-  };
-  const int up_top = (up && pz) ? nz - 2 : nz;               // planes nz-1, nz of a periodic level go first
-  if (up && pz) run_up(nz - 1, nz);
-  for (int a0 = 1; a0 - 4 <= nz; a0 += S) {
-    const int b0 = a0 + S;                                    // base planes a0 .. b0-1
-    if (up) run_up(a0 == 1 ? 1 : a0 + 1, std::min(up_top, b0));
-    for (int k0 = 1; k0 <= 4; ++k0) {
-      const int lo = std::max(1, a0 - (k0 - 1)), hi = std::min(nz, b0 - 1 - (k0 - 1));
-      if (lo > hi) continue;
-      g.k0 = k0; g.zr = zrange(lo, hi);
-      LAUNCH(s, k_gs_half_c<3>, dim3(gg.x, gg.y, nzb(lo, hi)), blk(3), g);
-    }
-    run_incr(std::max(pz ? 3 : 1, a0 - 4), std::min(nz, b0 - 5));
-  }
-  if (pz) run_incr(1, 2);
-  if (norms) fold_partials_to(s, gq, norms);
-  return WL_OK;
-}
-int smooth2(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready = false, const UpArgs* up = nullptr) {
-  if (l2_blocked(s, p)) return smooth_blocked(s, p, w, norms, eps_ready, up);
-  if (smooth_fusable(s, p)) return smooth_fused(s, p, w, norms);
+int smooth2(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready = false) {
   SmArgs a{levdev(p), p.per, w, 0, s->redw, norms ? norms : s->d_red, norms ? 1 : 0};
   if (pair_ok(s, p)) {
     gs_pairs(s, p);
@@ -816,8 +708,7 @@ void coarse_block(wl_sim* s, size_t first, float w) {
 }
 // first: the top level's residual still needs its mean removed; K-DOWN does it on the fly and leaves the
 // norms of the shifted residual in slot 10
-// up_out: the caller's smoother is L2-blocked and runs K-UP itself as the first stage of its slab pipeline
-int vcycle(wl_sim* s, size_t l, float w, bool first = false, UpArgs* up_out = nullptr) {
+int vcycle(wl_sim* s, size_t l, float w, bool first = false) {
   if (s->cfg.flags & WL_FLAG_NO_FUSED) { vcycle_v1(s, l, w); return WL_OK; }
   Level &fine = s->lv[l], &coarse = s->lv[l + 1];
   const bool gather = fine.dist && !coarse.dist;
@@ -850,10 +741,8 @@ int vcycle(wl_sim* s, size_t l, float w, bool first = false, UpArgs* up_out = nu
     coarse_block(s, l + 1, w);
   } else {
     const bool deeper = l + 2 < s->lv.size();
-    UpArgs upc{};
-    const bool defer = deeper && l2_blocked(s, coarse);
-    if (deeper) { if (int e = vcycle(s, l + 1, w, false, defer ? &upc : nullptr)) return e; }
-    if (int e = smooth2(s, coarse, w, nullptr, deeper, defer ? &upc : nullptr)) return e;
+    if (deeper) { if (int e = vcycle(s, l + 1, w)) return e; }
+    if (int e = smooth2(s, coarse, w, nullptr, deeper)) return e;
   }
   if (coarse.dist) { if (int e = halo(s, coarse.x, 1)) return e; }     // K-UP prolongates the neighbours' coarse cells too
   else if (gather && s->per_glob.p[2]) {                               // rank windows read the wrap planes as ghosts
@@ -862,8 +751,7 @@ int vcycle(wl_sim* s, size_t l, float w, bool first = false, UpArgs* up_out = nu
     plane_launch(coarse.lay, g, b);
     DISPATCH_D(s, k_perbc, g, b, pa);
   }
-  UpArgs u{levdev(fine), levdev_window(s, fine, coarse), fine.per, w, s->redw, s->d_red, 0, (smooth_fusable(s, fine) || pair_ok(s, fine)) ? 0 : 1};
-  if (up_out) { *up_out = u; return WL_OK; }
+  UpArgs u{levdev(fine), levdev_window(s, fine, coarse), fine.per, w, s->redw, s->d_red, 0, pair_ok(s, fine) ? 0 : 1};
   if (use_vec4(fine.lay)) LAUNCH(s, k_up4, grid_quads(fine.lay), dim3(32, 4, 2), u);
   else DISPATCH_D(s, k_up, grid_inside(fine.lay), blk(s->D), u);
   return WL_OK;
@@ -926,10 +814,8 @@ int mlp_solver(wl_sim* s, Trace* tr, bool residual_done = false) {
       a.in = red_in(s, 7); a.out = s->d_red + 1; // slot 7 stays zero: no shift, norms only
       DISPATCH_D(s, k_shift_norms, grid_tiles(p.lay, false), blk(s->D), a);
     } else {
-      UpArgs up0{};
-      const bool defer = fused && l2_blocked(s, p);
-      if (int e = vcycle(s, 0, w, lazy && np == 0, defer ? &up0 : nullptr)) return e;
-      if (fused) { if (int e = smooth2(s, p, w, s->d_red + 1, true, defer ? &up0 : nullptr)) return e; }
+      if (int e = vcycle(s, 0, w, lazy && np == 0)) return e;
+      if (fused) { if (int e = smooth2(s, p, w, s->d_red + 1, true)) return e; }
       else smooth(s, p, w, s->d_red + 1);
     }
     if (int e = fetch_red(s)) return e;

@@ -60,11 +60,6 @@ inline Lay make_lay(int D, const int* ng, int zpad = 0) {
 // boundary variant applies there and p[2] is 0.  kz0: global index of local plane k==0.
 struct Per { int p[3]; int zlo, zhi; int kz0; };
 struct Vec3 { float v[3]; };
-// A launch restricted to planes k_lo..k_hi of the last dimension (L2-blocked sweeps): zb0 = index of the launch's
-// first block in z, so that block <-> cell mapping and reduction slots equal those of the full launch.  All zero
-// (aggregate default) = the whole level.
-struct ZRange { int zb0, k_lo, k_hi; };
-__device__ __forceinline__ bool zr_has(const ZRange& z, int k) { return z.k_hi == 0 || (k >= z.k_lo && k <= z.k_hi); }
 
 // ---- deterministic block reduction helpers (warp shuffle -> smem -> thread 0)
 __device__ __forceinline__ double warp_sum(double v) {
@@ -166,7 +161,7 @@ __device__ __forceinline__ void fold_partials(const double* psum, const float* p
 
 // Reduction in two launches for kernels with ~10^5 blocks: every block leaves one partial
 // (block_reduce_partial, no fence, no atomic), k_fold_partials folds them in index order.
-__device__ __forceinline__ void block_reduce_partial(double s, float m, const RedWork w, int bid = -1) {
+__device__ __forceinline__ void block_reduce_partial(double s, float m, const RedWork w) {
   __shared__ double ssum[32];
   __shared__ float smax[32];
   const int tid = linear_tid();
@@ -179,7 +174,7 @@ __device__ __forceinline__ void block_reduce_partial(double s, float m, const Re
     s = lane < nw ? ssum[lane] : 0.0;
     m = lane < nw ? smax[lane] : -INFINITY;
     s = warp_sum(s); m = warp_max(m);
-    if (lane == 0) { const int b = bid >= 0 ? bid : linear_bid(); w.psum[b] = s; w.pmax[b] = m; }
+    if (lane == 0) { const int b = linear_bid(); w.psum[b] = s; w.pmax[b] = m; }
   }
 }
 struct FoldArgs { RedWork w; int n; Red* out; };

@@ -21,7 +21,6 @@ struct LevArgs {
   RedIn in;          // residual sum input (k_shift_norms)
   long long ncells;  // interior cells of the GLOBAL level (mean of the residual)
   int want_norms;
-  ZRange zr;         // k_gs_half_c: planes of this launch (zero = all)
 };
 
 #define WL_INTERIOR_IJK(D, l)                                                   \
@@ -196,9 +195,9 @@ __global__ void __launch_bounds__(256) k_gs_half_c(const LevArgs a) {
   pdl_entry();
   const Lay& l = a.l;
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
-  const int k = D == 3 ? (blockIdx.z + a.zr.zb0) * blockDim.z + threadIdx.z + 1 : 0;
+  const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;
   const int i = 1 + 2 * (blockIdx.x * blockDim.x + threadIdx.x) + ((j + k + D + a.k0) & 1);
-  if (i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && (k > l.n2 - 2 || !zr_has(a.zr, k)))) return;
+  if (i > l.n0 - 2 || j > l.n1 - 2 || (D == 3 && k > l.n2 - 2)) return;
   const int nl = D == 3 ? l.n2 : l.n1;
   const int cl = D == 3 ? k : j;
   if (cl > 2 * (nl / 2) - 2) return;

@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(256) k_down(const DownArgs a) {
 // ---------------------------------------------------------------- K-UP
 // write_eps: the smoother of this level always follows (MultiLevelPoisson.jl:97-100,115), so K-UP also
 // leaves its first statement ϵ = r·iD (+ periodic images, Poisson.jl:142-143) behind
-struct UpArgs { LevDev f, c; Per per; float omega; RedWork w; Red* out; int want_norms; int write_eps; ZRange zr; };
+struct UpArgs { LevDev f, c; Per per; float omega; RedWork w; Red* out; int want_norms; int write_eps; };
 template <int D>
 __global__ void __launch_bounds__(256) k_up(const UpArgs a) {
   pdl_entry();
@@ -344,7 +344,6 @@ struct SmArgs {
   LevDev p; Per per; float omega; int k0; RedWork w; Red* out; int want_norms;
   // k_incr4 after fused half sweeps (k_gs_half_cx): arrival flags the boundary slabs wait for
   unsigned int* wflag; unsigned int wait_seq_lo, wait_seq_hi; int wait_lo, wait_hi;
-  ZRange zr;         // k_incr4: planes of this launch (zero = all)
 };
 template <int D>
 __global__ void __launch_bounds__(256) k_eps_init_g(const SmArgs a) {

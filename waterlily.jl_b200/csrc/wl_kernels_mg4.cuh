@@ -46,12 +46,6 @@ inline bool vec4_ok(const Lay& l) { return l.D == 3 && (l.n0 - 2) % 4 == 0 && l.
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;                      \
   const int k = blockIdx.z * blockDim.z + threadIdx.z + 1;                      \
   const bool inb = !(i > l.n0 - 2 || j > l.n1 - 2 || k > l.n2 - 2);
-// the same for a launch over a range of planes (ZRange)
-#define WL_QUAD_FROM_BLOCK_ZR(l, zr)                                            \
-  const int i = 1 + 4 * (blockIdx.x * blockDim.x + threadIdx.x);                \
-  const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;                      \
-  const int k = (blockIdx.z + (zr).zb0) * blockDim.z + threadIdx.z + 1;         \
-  const bool inb = !(i > l.n0 - 2 || j > l.n1 - 2 || k > l.n2 - 2) && zr_has(zr, k);
 
 // y/z neighbour offsets of the quad's row (wrapped across periodic seams) and the x offsets of the
 // cell left of the quad / right of it
@@ -80,7 +74,7 @@ __global__ void __launch_bounds__(256) k_incr4(const SmArgs a) {
       __syncthreads();
     }
   }
-  WL_QUAD_FROM_BLOCK_ZR(l, a.zr)
+  WL_QUAD_FROM_BLOCK(l)
   double s1 = 0.0; float m = -INFINITY;
   if (inb) {
     const int o = l.off(i, j, k);
@@ -112,10 +106,7 @@ __global__ void __launch_bounds__(256) k_incr4(const SmArgs a) {
     st4(a.p.r + o, rn);
     st4(a.p.x + o, xn);
   }
-  if (a.want_norms) {
-    if (a.w.finish) block_reduce_finish(s1, m, a.w, a.out);
-    else block_reduce_partial(s1, m, a.w, blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * (blockIdx.z + a.zr.zb0)));
-  }
+  if (a.want_norms) { if (a.w.finish) block_reduce_finish(s1, m, a.w, a.out); else block_reduce_partial(s1, m, a.w); }
 }
 
 // ---------------------------------------------------------------- red-black half sweep, 8 cells per thread (4 updated)
@@ -313,7 +304,7 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_up4(const UpArgs a) {
   pdl_entry();
   const Lay& l = a.f.l;
   const Lay& lc = a.c.l;
-  WL_QUAD_FROM_BLOCK_ZR(l, a.zr)
+  WL_QUAD_FROM_BLOCK(l)
   if (!inb) return;
   const int o = l.off(i, j, k);
   const bool cx = a.c.c[0] != 0, cy = a.c.c[1] != 0, cz = a.c.c[2] != 0;
