@@ -325,7 +325,7 @@ def mgpu_parity(wl, dist, world, rank, local):
         sim.sim_step(remeasure=False)
     u, p = sim.gather("u"), sim.gather("p")
     n, dts = list(sim.pois.n), [float(x) for x in sim.flow.Δt]
-    del sim
+    sim.close()                                       # collective: every rank, here
     verdict = [None]
     if rank == 0:
         one = wl.Simulation(dims, (1.0, 0.0, 0.0), 2 * R, body=wl.AutoBody(**body), device=local, **kw)
@@ -337,7 +337,7 @@ def mgpu_parity(wl, dist, world, rank, local):
             verdict[0] = "bit-exact"
         else:
             verdict[0] = "max|du|=%.3e max|dp|=%.3e n %s vs %s" % (float(np.abs(u - u1).max()), float(np.abs(p - p1).max()), n, list(one.pois.n))
-        del one
+        one.close()
     dist.broadcast_object_list(verdict, src=0)
     return verdict[0]
 
@@ -512,7 +512,7 @@ def main():
     halo_transport = sim.halo_transport()
     nsteps_total = len(sim.pois.n) // 2
     hu = hp = None
-    del sim
+    sim.close()
 
     # ---- N = 8: BASELINE configs[4], TGV 1024^3 on 8 GPUs, against the same slab (1024x1024x128) on one GPU
     config_e = None
@@ -522,7 +522,7 @@ def main():
         sim = s8
         t8, _, _, _, _ = timed_steps(s8, 10, 3, False, barrier, dist, torch)
         n8 = list(s8.pois.n[-20:])
-        del s8, sim
+        s8.close()
         t1 = None
         if rank == 0:                                  # the single-GPU reference point of the weak-scaling pair
             d1 = workload("tgv", 1024, 1, 128)
@@ -535,7 +535,7 @@ def main():
             s1.event_record(1)
             s1.sync()
             t1 = s1.event_elapsed_ms(0, 1)
-            del s1
+            s1.close()
         dist.barrier()
         if rank == 0:
             config_e = {"workload": d8[0], "cells": int(np.prod(d8[1])), "steps": 10, "warmup": 3,

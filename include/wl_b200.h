@@ -53,7 +53,7 @@ typedef struct wl_config {
   int32_t flags;        /* WL_FLAG_*                                                 */
 } wl_config;
 
-#define WL_FLAG_NO_GRAPHS 1   /* disable CUDA-graph replay of the V-cycle (debugging) */
+/* (flag bit 1 is unused: round 1 reserved it for a CUDA-graph replay that was never built) */
 #define WL_FLAG_NO_FUSED 2    /* 3D: use the un-fused K-RHS + K-BDIM kernels (materialises flow.f) */
 #define WL_FLAG_FUSED_SMOOTH 4 /* 3D: K-GS2, two red-black sweeps per pass (wl_kernels_gs2.cuh); bit-identical, opt-in: slower for now */
 

@@ -404,10 +404,14 @@ class _Handle:
     def __init__(self, lib, h):
         self.lib, self.h = lib, h
 
+    def close(self):
+        if self.h:
+            self.lib.wl_destroy(self.h)
+            self.h = None
+
     def __del__(self):
         try:
-            if self.h:
-                self.lib.wl_destroy(self.h)
+            self.close()
         except Exception:
             pass
 
@@ -522,6 +526,13 @@ class Simulation:
         self.pois = B200Poisson(self)
 
     # ---- plumbing
+    def close(self):
+        """`wl_destroy` now.  On a slab-decomposed run destruction is COLLECTIVE (the ranks meet once before the peer
+        mappings go away): call it on every rank at the same point of the program instead of leaving it to the garbage
+        collector (`sim.flow` / `sim.pois` refer back to the simulation, so `del sim` alone does not free it)."""
+        self._handle.close()
+        self.h = None
+
     def _check(self, rc):
         if rc != WL_OK:
             msg = self.lib.wl_last_error(self.h).decode()

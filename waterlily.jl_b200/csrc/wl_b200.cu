@@ -86,7 +86,6 @@ struct wl_sim {
   char* peer_all[P2P_MAXRANKS] = {};                  // every rank's arena (own included) when nranks <= P2P_MAXRANKS
   bool p2p_gather = false;                            // reduction slots travel by k_gather_p2p instead of NCCL
   unsigned int gseq = 0;
-  unsigned int cnt_lo = 0, cnt_hi = 0;                // halo arrival-counter totals per link
   DevField accf[2];                                   // accelerate! fields at t₀ / t₁ (wl_set_accel_field), else unallocated
   bool accf_on = false;
   float* bc_tab = nullptr; int bc_off[9] = {0}; int bc_psz[3] = {0, 0, 0};   // Function-uBC tables (wl_set_bc_tables)
@@ -110,6 +109,8 @@ struct wl_sim {
   int band_cap2 = 0, band_epoch = 0;
   bool band_dirty = false;
   bool band_from_measure = false;   // k_measure appended the band cells itself: only the count has to be checked
+  std::map<const float*, CUtensorMap> tmaps;       // 4-D tensor maps of the vector fields K-MOM fetches by TMA, keyed by allocation
+  int tma_ok = -1;                                 // -1 not probed, 0 unavailable (encoder missing / WL_NO_TMA), 1 in use
   int* fw_off = nullptr; float* fw_w = nullptr; int fw_n = -1;   // pressure_force weights of a host-measured body (wl_set_force_weights)
   bool free_flow = true;      // V ≡ 0, μ₀ ≡ 1, μ₁ ≡ 0 as the constructor left them (no measure!, no upload of them)
   std::vector<Level> lv;
@@ -167,14 +168,7 @@ int alloc_field(wl_sim* s, DevField& f, const Lay& lay, int ncomp) {
 }
 void free_field(DevField& f) { if (f.alloc && !f.in_arena) cudaFree(f.alloc); f.alloc = f.base = nullptr; f.in_arena = false; }
 
-dim3 blk(int D) {
-  static int bx = 0, by = 4, bz = 2;
-  if (!bx) {   // WL_BLK3="bx,by,bz" overrides the 3D interior tile (experiments); bx*by*bz must be 256, by and bz even (K-DOWN keeps the children of a coarse cell in one block)
-    bx = 32;
-    if (const char* e = getenv("WL_BLK3")) { int a, b, c; if (sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a * b * c == 256 && a % 32 == 0 && b % 2 == 0 && c % 2 == 0) { bx = a; by = b; bz = c; } }
-  }
-  return D == 3 ? dim3(bx, by, bz) : dim3(32, 8, 1);
-}
+dim3 blk(int D) { return D == 3 ? dim3(32, 4, 2) : dim3(32, 8, 1); }   // even extents: K-DOWN keeps the children of a coarse cell in one block
 dim3 grid_inside(const Lay& l) {
   dim3 b = blk(l.D);
   return dim3((l.n0 - 2 + b.x - 1) / b.x, (l.n1 - 2 + b.y - 1) / b.y, l.D == 3 ? (l.n2 - 2 + b.z - 1) / b.z : 1);
@@ -247,6 +241,16 @@ inline void prof_post(wl_sim* s, const char* name, cudaEvent_t a, cudaEvent_t b,
     launch_pdl((s)->st, g_, b, kern, __VA_ARGS__);         \
     if (prof_) prof_post(s, #kern, pa_, pb_, g_);          \
     ++(s)->launches;                                       \
+  } while (0)
+
+#define LAUNCH_SMEM(s, kern, g, b, smem, ...)                          \
+  do {                                                                \
+    cudaEvent_t pa_, pb_;                                             \
+    const bool prof_ = prof_pre(s, #kern, &pa_, &pb_);                \
+    const dim3 g_ = (g);                                              \
+    launch_pdl_smem((s)->st, g_, b, smem, kern, __VA_ARGS__);         \
+    if (prof_) prof_post(s, #kern, pa_, pb_, g_);                     \
+    ++(s)->launches;                                                  \
   } while (0)
 
 #define DISPATCH_D(s, kern, g, b, ...)                                    \
@@ -331,16 +335,11 @@ int halo(wl_sim* s, const DevField& f, int depth, bool wrap = true, bool idle = 
     a.nb_hi = reinterpret_cast<unsigned int*>(s->peer_hi);
     a.use_lo = use_lo; a.use_hi = use_hi;
     // (a link that closes a periodic ring sat out the exchanges between the sweeps: it keeps its handshake)
-    const bool skip = idle && !getenv_flag("WL_HALO_ALWAYS_READY");
-    a.skip_lo = skip && !d.lo_wrap; a.skip_hi = skip && !d.hi_wrap;
+    a.skip_lo = idle && !d.lo_wrap; a.skip_hi = idle && !d.hi_wrap;
     if (use_lo) a.seq_lo = ++s->seq_lo;
     if (use_hi) a.seq_hi = ++s->seq_hi;
     long long nb = ((long long)cnt * a.nseg + 2047) / 2048;
     nb = nb < 1 ? 1 : (nb > 296 ? 296 : nb);
-    // both ends of a link run this exchange with the same segment count and size, hence the same grid
-    a.counters = getenv_flag("WL_HALO_COUNTERS") ? 1 : 0;
-    if (use_lo) a.cnt_lo = (s->cnt_lo += (unsigned)nb);
-    if (use_hi) a.cnt_hi = (s->cnt_hi += (unsigned)nb);
     LAUNCH(s, k_halo_p2p, dim3((unsigned)nb), dim3(256), a);
     return WL_OK;
   }
@@ -554,14 +553,10 @@ bool use_vec4(const Lay& l) {
 dim3 grid_quads(const Lay& l, int cells_per_thread = 4) {
   return dim3((l.n0 - 2 + 32 * cells_per_thread - 1) / (32 * cells_per_thread), (l.n1 - 2 + 3) / 4, (l.n2 - 2 + 1) / 2);
 }
-// WL_FINISH_MAX=n: grids of up to n blocks finish their reduction in the kernel (two-level ticket) instead
-// of leaving block partials to a k_fold_partials launch.  Off by default: with dependent launches the
-// extra 1-block kernel is cheaper than a fence + atomic in every block (TGV 128³: 0.301 vs 0.314, sphere
-// 512x256²: 0.182 vs 0.189 ns/cell/step).
-inline bool finish_in_kernel(const dim3& g) {
-  static const long long lim = getenv("WL_FINISH_MAX") ? atoll(getenv("WL_FINISH_MAX")) : 0;
-  return (long long)g.x * g.y * g.z <= lim;
-}
+// Reductions of the vectorised kernels: every block leaves one partial, a 1-block k_fold_partials launch folds them in
+// index order (with dependent launches that is cheaper than a fence + atomic ticket in every block: TGV 128³ 0.301 vs
+// 0.314, sphere 512x256² 0.182 vs 0.189 ns/cell/step, round 1).
+inline bool finish_in_kernel(const dim3&) { return false; }
 void fold_partials_to(wl_sim* s, const dim3& g, Red* out) {
   FoldArgs fa{s->redw, (int)(g.x * g.y * g.z), out};
   LAUNCH(s, k_fold_partials, dim3(1), dim3(1024), fa);
@@ -580,7 +575,6 @@ void gs_pairs(wl_sim* s, Level& p) {
   const long long bxy = (long long)((l.n0 - 2 + G2_XS - 1) / G2_XS) * ((l.n1 - 2 + G2_TY - 1) / G2_TY);
   const int nz = l.n2 - 2;
   {                                                   // chunk length: whole waves of 2 blocks per SM, 3 extra planes per chunk
-    static const int kz_env = getenv("WL_GS2_KZ") ? atoi(getenv("WL_GS2_KZ")) : 0;
     long long best = -1;
     for (int n = 1; n <= (nz + 3) / 4; ++n) {
       const int kz = (nz + n - 1) / n;
@@ -588,7 +582,6 @@ void gs_pairs(wl_sim* s, Level& p) {
       const long long cost = ((bxy * chunks + 295) / 296) * (kz + 3);
       if (best < 0 || cost < best) { best = cost; g.KZ = kz; }
     }
-    if (kz_env >= 2) g.KZ = kz_env;
   }
   const dim3 grid((l.n0 - 2 + G2_XS - 1) / G2_XS, (l.n1 - 2 + G2_TY - 1) / G2_TY, (nz + g.KZ - 1) / g.KZ), blk2(32, G2_NR);
   static bool attr = false;
@@ -627,13 +620,10 @@ int smooth2(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready = false) {
   dim3 gg = grid_inside(p.lay);
   gg.x = (p.lay.n0 - 2 + 2 * blk(s->D).x - 1) / (2 * blk(s->D).x);   // colour-compacted: a thread per x-pair
   const bool v4 = use_vec4(p.lay);
-  // k_gs8 (8 cells per thread) measured no faster than the colour-compacted scalar sweep: opt-in only
-  static const bool gs8 = getenv("WL_GS8") != nullptr;
-  const bool v8 = gs8 && v4 && (p.lay.n0 - 2) % 8 == 0;
   // slab interfaces: exchange fused into the sweeps (k_gs_half_cx) when the planes can be pushed to peers
   const Dist& d = s->dist;
   const bool link_lo = d.lo >= 0 && !d.lo_wrap, link_hi = d.hi >= 0 && !d.hi_wrap;
-  const bool fuse = p.dist && s->p2p && p.eps.in_arena && s->D == 3 && v4 && !v8 && blk(3).z == 2 &&
+  const bool fuse = p.dist && s->p2p && p.eps.in_arena && s->D == 3 && v4 && blk(3).z == 2 &&
                     (link_lo || link_hi) && !getenv_flag("WL_NO_GS_FUSE");
   GsLink x{};
   if (fuse) {
@@ -656,8 +646,7 @@ int smooth2(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready = false) {
       if (k0 == 4 && (d.lo_wrap || d.hi_wrap)) { if (int e = halo(s, p.eps, 1, true, false, true)) return e; }
       continue;
     }
-    if (v8) LAUNCH(s, k_gs8, grid_quads(p.lay, 8), dim3(32, 4, 2), g);
-    else DISPATCH_D(s, k_gs_half_c, gg, blk(s->D), g);
+    DISPATCH_D(s, k_gs_half_c, gg, blk(s->D), g);
     if (p.dist) { if (int e = halo(s, p.eps, 1, k0 == 4, true)) return e; }
   }
   if (fuse) {
@@ -679,31 +668,8 @@ void coarse_block(wl_sim* s, size_t first, float w) {
   CoarseArgs a{};
   for (size_t l = 0; l < s->lv.size() && l < (size_t)WL_MAXLEV; ++l) a.lv[l] = levdev(s->lv[l]);
   a.first = (int)first; a.nlev = (int)s->lv.size(); a.per = s->per_glob; a.omega = w;
-  // optionally stage the smallest levels in shared memory (WL_COARSE_SMEM_KB > 0).  Measured slower than
-  // leaving them in L2 (52 -> 75 µs on the 18³..4³ tail of a 128³ grid: the recursion itself drops to 35 µs,
-  // but launch + descriptor setup cost 7 µs and the generic staging copies 33 µs; the recursion is bound by
-  // the instruction issue of one SM on the largest staged level and by ~40 dependent phases, not by memory).
-  static const int budget_kb = getenv("WL_COARSE_SMEM_KB") ? atoi(getenv("WL_COARSE_SMEM_KB")) : 0;
-  const size_t budget = (size_t)std::min(std::max(budget_kb, 0), 200) * 1024;
-  int from = a.nlev;
-  while (from > a.first && coarse_smem_bytes(a, s->D, from - 1) <= budget) --from;
-  a.stage_from = from;
-  const size_t smem = coarse_smem_bytes(a, s->D, from);
-  if (from < a.nlev) {
-    static bool attr = false;
-    if (!attr) {
-      cudaFuncSetAttribute(k_coarse_sm<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-      cudaFuncSetAttribute(k_coarse_sm<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-      attr = true;
-    }
-    cudaEvent_t pa_, pb_;
-    const bool prof_ = prof_pre(s, "k_coarse_sm", &pa_, &pb_);
-    if (s->D == 3) launch_pdl_smem(s->st, dim3(1), dim3(1024), smem, k_coarse_sm<3>, a);
-    else launch_pdl_smem(s->st, dim3(1), dim3(1024), smem, k_coarse_sm<2>, a);
-    if (prof_) prof_post(s, "k_coarse_sm", pa_, pb_);
-    ++s->launches;
-    return;
-  }
+  // (staging the smallest levels in shared memory measured slower than leaving them in L2 -- 52 -> 75 µs on the 18³..4³
+  //  tail of a 128³ grid: the recursion is bound by ~40 dependent phases and one SM's instruction issue; removed in round 2)
   DISPATCH_D(s, k_coarse, dim3(1), dim3(1024), a);
 }
 // first: the top level's residual still needs its mean removed; K-DOWN does it on the fly and leaves the
@@ -953,9 +919,49 @@ int band_rebuild(wl_sim* s) {
   s->band_dirty = false;
   return WL_OK;
 }
+// 4-D tensor map (x+3, y, z+zpad, component) over the padded device array of a 3-component field, for the TMA tile
+// loads of K-MOM: base = alloc + 28 floats (16-byte aligned; element i sits at x = i + 3), rows of `pitch` floats.
+// The encoder comes from the driver through the runtime (no libcuda link); nullptr when it is not available.
+const CUtensorMap* tensor_map(wl_sim* s, const DevField& f, int box_x, int box_y) {
+  typedef CUresult (*Encode)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                             const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                             CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static Encode enc = nullptr;
+  if (s->tma_ok < 0) {
+    s->tma_ok = 0;
+    if (!getenv("WL_NO_TMA")) {
+      void* fn = nullptr;
+      cudaDriverEntryPointQueryResult qr;
+      if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) == cudaSuccess && fn &&
+          qr == cudaDriverEntryPointSuccess) { enc = (Encode)fn; s->tma_ok = 1; }
+      else cudaGetLastError();
+    }
+  }
+  if (s->tma_ok != 1) return nullptr;
+  const float* key = f.alloc + (box_x == 32 ? 1 : 0);     // two box shapes per allocation (tile / own-cell operands)
+  auto it = s->tmaps.find(key);
+  if (it != s->tmaps.end()) return &it->second;
+  const Lay& l = f.lay;
+  CUtensorMap tm;
+  const cuuint64_t dims[4] = {(cuuint64_t)l.pitch, (cuuint64_t)l.n1, (cuuint64_t)(l.n2 + 2 * l.zpad), 3};
+  const cuuint64_t strides[3] = {(cuuint64_t)l.pitch * 4, (cuuint64_t)l.plane * 4, (cuuint64_t)l.cstride * 4};
+  const cuuint32_t box[4] = {(cuuint32_t)box_x, (cuuint32_t)box_y, 1, 3}, es[4] = {1, 1, 1, 1};
+  const CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)(f.alloc + LPAD - 3), dims, strides, box, es,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { s->tma_ok = 0; return nullptr; }
+  return &(s->tmaps[key] = tm);
+}
 // K-MOM (3D fused): out = new velocity from ua (advecting) and u0
 void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, const float* acc) {
   Mom3Args a{};
+  {
+    const CUtensorMap* t0 = tensor_map(s, ua, M3_TW, M3_TH);
+    const CUtensorMap* t1 = tensor_map(s, u0, 32, M3_TY - 1);
+    const CUtensorMap* t2 = tensor_map(s, s->V, 32, M3_TY - 1);
+    const CUtensorMap* t3 = tensor_map(s, s->mu0, 32, M3_TY - 1);
+    if (t0 && t1 && t2 && t3) { a.use_tma = 1; a.tm_ua = *t0; a.tm_u0 = *t1; a.tm_V = *t2; a.tm_m0 = *t3; }
+  }
   a.l = s->lay; a.ua = ua.base; a.u0 = u0.base; a.V = s->V.base; a.mu0 = s->mu0.base; a.un = out.base;
   a.per = s->per; a.nu = s->cfg.nu; a.dt = s->dt; a.corrector = corrector;
   for (int d = 0; d < 3; ++d) a.acc.v[d] = acc ? acc[d] : 0.f;
@@ -966,8 +972,7 @@ void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, c
   }
   // 32-column tiles (the block's last row supplies lane 31's upper x faces); WL_M3_W32=0 selects the 31-column
   // tiling.  Measured (profiles/r1_v14_kmom_march_sweep.tsv): TGV 128³ 67.3 -> 58.7 us, sphere 512x256² 810 -> 795 us.
-  static const bool w32 = !(getenv("WL_M3_W32") != nullptr && atoi(getenv("WL_M3_W32")) == 0);
-  const int bw = w32 ? 32 : 31;
+  const int bw = 32;
   // march length: the chunk count that minimises waves x (planes per chunk + ~4 planes of pipeline fill and
   // the extra flux plane), a wave being 2 blocks on each of the 148 SMs (measured on 128³ and 512x256²:
   // a grid just under a whole number of waves beats a finer split by up to 8%)
@@ -985,33 +990,34 @@ void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, c
       if (best < 0 || cost < best) { best = cost; a.KZ = kz; }
     }
   }
-  { static const int kz_env = getenv("WL_M3_KZ") ? atoi(getenv("WL_M3_KZ")) : 0; if (kz_env >= 2) a.KZ = kz_env; }
   dim3 g((l.n0 - 2 + bw - 1) / bw, (l.n1 - 2 + M3_TY - 2) / (M3_TY - 1), (l.n2 - 2 + a.KZ - 1) / a.KZ);
   dim3 b(32, M3_TY, 1);
   const int sc = s->cfg.scheme;
   // body-free, fully periodic flow: V ≡ 0 and μ₀ ≡ 1 everywhere, the kernel need not read them
   static const bool nb_off = getenv("WL_NO_NOBODY") != nullptr;
   const bool nb = !nb_off && s->free_flow && s->per_glob.p[0] && s->per_glob.p[1] && s->per_glob.p[2];
-#define WL_MOM3_LAUNCH(NB, W)                                        \
-  do {                                                               \
-    if (sc == 0) LAUNCH(s, (k_mom3<0, NB, W>), g, b, a);             \
-    else if (sc == 1) LAUNCH(s, (k_mom3<1, NB, W>), g, b, a);        \
-    else LAUNCH(s, (k_mom3<2, NB, W>), g, b, a);                     \
+  static bool attr = false;
+  if (!attr) {                                                       // Mom3Smem exceeds the 48 KB static limit
+#define WL_MOM3_ATTR(S_, NB, W) cudaFuncSetAttribute(k_mom3<S_, NB, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Mom3Smem))
+    WL_MOM3_ATTR(0, false, true); WL_MOM3_ATTR(0, true, true); WL_MOM3_ATTR(1, false, true); WL_MOM3_ATTR(1, true, true);
+    WL_MOM3_ATTR(2, false, true); WL_MOM3_ATTR(2, true, true);
+#undef WL_MOM3_ATTR
+    attr = true;
+  }
+#define WL_MOM3_LAUNCH(NB, W)                                                                \
+  do {                                                                                       \
+    if (sc == 0) LAUNCH_SMEM(s, (k_mom3<0, NB, W>), g, b, sizeof(Mom3Smem), a);              \
+    else if (sc == 1) LAUNCH_SMEM(s, (k_mom3<1, NB, W>), g, b, sizeof(Mom3Smem), a);         \
+    else LAUNCH_SMEM(s, (k_mom3<2, NB, W>), g, b, sizeof(Mom3Smem), a);                      \
   } while (0)
-  if (nb) { if (w32) WL_MOM3_LAUNCH(true, true); else WL_MOM3_LAUNCH(true, false); }
-  else { if (w32) WL_MOM3_LAUNCH(false, true); else WL_MOM3_LAUNCH(false, false); }
+  if (nb) WL_MOM3_LAUNCH(true, true); else WL_MOM3_LAUNCH(false, true);
 #undef WL_MOM3_LAUNCH
   PatchArgs pa{};
   pa.m.l = s->lay; pa.m.ua = ua.base; pa.m.u0 = u0.base; pa.m.V = s->V.base; pa.m.f = nullptr;
   pa.m.per = s->per; pa.m.nu = s->cfg.nu; pa.m.dt = s->dt; pa.m.acc = a.acc;
   pa.mu0 = s->mu0.base; pa.mu1 = s->mu1.base; pa.un = out.base;
   pa.list = s->band_list; pa.count = s->band_count; pa.cap = s->band_cap; pa.corrector = corrector;
-  static const bool patch1 = getenv("WL_PATCH_1PASS") != nullptr;      // the one-warp-per-cell kernel
-  if (s->band_cap > 0 && (patch1 || !s->band_list2)) {
-    if (sc == 0) LAUNCH(s, k_mom_patch<0>, dim3(1184), dim3(128), pa);
-    else if (sc == 1) LAUNCH(s, k_mom_patch<1>, dim3(1184), dim3(128), pa);
-    else LAUNCH(s, k_mom_patch<2>, dim3(1184), dim3(128), pa);
-  } else if (s->band_cap > 0) {
+  if (s->band_cap > 0 && s->band_list2) {
     pa.m.f = s->f.base;
     if (sc == 0) LAUNCH(s, k_patch_f<0>, dim3(1184), dim3(128), pa, s->band_list2, s->band_count2, s->band_cap2);
     else if (sc == 1) LAUNCH(s, k_patch_f<1>, dim3(1184), dim3(128), pa, s->band_list2, s->band_count2, s->band_cap2);
@@ -1061,8 +1067,7 @@ int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
 }
 int cfl(wl_sim* s, float* out) {
   CflArgs a{s->lay, s->u.base, s->sigma.base, s->redw, s->d_red + 2, s->per.zlo, s->per.zhi};
-  static const bool scalar_cfl = getenv("WL_SCALAR_CFL") != nullptr;
-  if (use_vec4(s->lay) && !scalar_cfl) {                          // all rows and planes, ghosts included
+  if (use_vec4(s->lay)) {                          // all rows and planes, ghosts included
     const dim3 g((s->lay.n0 - 2 + 127) / 128, (s->lay.n1 + 3) / 4, (s->lay.n2 + 1) / 2);
     a.w.finish = finish_in_kernel(g) ? 1 : 0;
     LAUNCH(s, k_cfl4, g, dim3(32, 4, 2), a);

@@ -27,9 +27,7 @@ struct HaloP2PArgs {
   unsigned int* nb_lo;                 // lower neighbour's flag block (I am ITS upper neighbour: slots 1 and 3)
   unsigned int* nb_hi;                 // upper neighbour's flag block (slots 0 and 2)
   unsigned int seq_lo, seq_hi;
-  unsigned int cnt_lo, cnt_hi;         // arrival-counter totals after this exchange ([6] from lower, [7] from upper)
   int use_lo, use_hi;
-  int counters;                        // completion by remote release-adds (WL_HALO_COUNTERS=1) instead of ticket + done
                                        // flags: measured slower (TGV 128³ x2: 1.12 vs 1.04 ms/step), kept for reference
   int skip_lo, skip_hi;                // per link: the caller proved the ghost planes idle (see halo() in wl_b200.cu)
 };
@@ -103,26 +101,8 @@ __global__ void __launch_bounds__(256) k_halo_p2p(const HaloP2PArgs a) {
       for (long long e = gt; e < a.cnt; e += stride) dst[e] = src[e];
     }
   }
-  // Completion: one release-add per block on the RECEIVER's arrival counter (the barrier orders the block's
-  // stores before thread 0's release, which is cumulative), no local ticket and no second fence.  The
-  // counters are cumulative over the run; block 0 waits until its own have reached the totals the
-  // neighbours will have added (they run the same exchange with the same grid).
   __syncthreads();
-  if (a.counters) {
-    if (tid != 0) return;
-    if (a.use_lo) red_release_sys_add(a.nb_lo + 7, 1u);
-    if (a.use_hi) red_release_sys_add(a.nb_hi + 6, 1u);
-    if (blockIdx.x != 0) return;
-    const unsigned long long t_copied = wl_now_ns();
-    if (a.use_lo) wait_flag(a.my + 6, a.cnt_lo, a.my + 5);
-    if (a.use_hi) wait_flag(a.my + 7, a.cnt_hi, a.my + 5);
-    const unsigned long long t_done = wl_now_ns();
-    atomicAdd(stat + 1, t_copied - t_ready);
-    atomicAdd(stat + 2, t_done - t_copied);
-    atomicAdd(stat + 3, 1ull);
-    return;
-  }
-  // default: one system-scope fence per block, a local ticket, and the last block raises the done flags
+  // completion: one system-scope fence per block, a local ticket, and the last block raises the done flags
   __shared__ int last;
   if (tid == 0) __threadfence_system();
   if (tid == 0) last = atomicAdd(a.my + 4, 1u) == gridDim.x - 1;

@@ -433,7 +433,6 @@ constexpr int WL_MAXLEV = 12;
 struct CoarseArgs {
   LevDev lv[WL_MAXLEV];
   int first, nlev;     // levels first..nlev-1 are processed here
-  int stage_from;      // k_coarse_sm: levels stage_from..nlev-1 live in shared memory
   Per per;
   float omega;
 };
@@ -543,65 +542,6 @@ template <int D>
 __global__ void __launch_bounds__(1024) k_coarse(const CoarseArgs a) {
   pdl_entry();
   coarse_body<D>(a.lv, a.first, a.nlev, a.per, a.omega);
-}
-
-// The same with every array of the levels first..nlev-1 staged in SHARED memory in a dense layout: the
-// ~40 phases of the recursion are separated by __syncthreads only, instead of a round trip to L2 each
-// (57 -> ~12 µs for the 18³..4³ tail of a 128³ grid).  L, iD, r, x are copied in (ghosts included), x, r, ϵ
-// are copied back, so the data surface sees exactly what the global-memory version leaves.
-inline size_t coarse_smem_bytes(const CoarseArgs& a, int D, int from) {
-  size_t cells = 0;
-  for (int l = from; l < a.nlev; ++l) cells += (size_t)a.lv[l].l.n0 * a.lv[l].l.n1 * a.lv[l].l.n2;
-  return cells * (D + 4) * sizeof(float);
-}
-template <int D>
-__global__ void __launch_bounds__(1024) k_coarse_sm(const CoarseArgs a) {
-  pdl_entry();
-  extern __shared__ __align__(16) float csm[];
-  __shared__ LevDev slv[WL_MAXLEV];
-  if (threadIdx.x == 0) {
-    float* p = csm;
-    for (int l = a.first; l < a.stage_from; ++l) slv[l] = a.lv[l];
-    for (int l = a.stage_from; l < a.nlev; ++l) {
-      LevDev d = a.lv[l];
-      const int n = d.l.n0 * d.l.n1 * d.l.n2;
-      d.l.pitch = d.l.n0; d.l.plane = d.l.n0 * d.l.n1; d.l.cstride = n;
-      d.L = p; p += n * D;
-      d.iD = p; p += n;
-      d.x = p; p += n;
-      d.r = p; p += n;
-      d.eps = p; p += n;
-      slv[l] = d;
-    }
-  }
-  __syncthreads();
-  for (int l = a.stage_from; l < a.nlev; ++l) {
-    const LevDev g = a.lv[l];
-    const LevDev s = slv[l];
-    const int n0 = g.l.n0, n01 = g.l.n0 * g.l.n1, n = n01 * g.l.n2;
-    const float in01 = 1.0f / (float)n01, in0 = 1.0f / (float)n0;
-    for (int q = threadIdx.x; q < n; q += blockDim.x) {
-      const int k = (int)(((float)q + 0.5f) * in01), r = q - k * n01, j = (int)(((float)r + 0.5f) * in0), i = r - j * n0;
-      const int o = g.l.off(i, j, k);
-#pragma unroll
-      for (int d = 0; d < D; ++d) const_cast<float*>(s.L)[n * d + q] = g.L[g.l.cstride * d + o];
-      const_cast<float*>(s.iD)[q] = g.iD[o];
-      s.x[q] = g.x[o]; s.r[q] = g.r[o]; s.eps[q] = g.eps[o];
-    }
-  }
-  __syncthreads();
-  coarse_body<D>(slv, a.first, a.nlev, a.per, a.omega);
-  for (int l = a.stage_from; l < a.nlev; ++l) {
-    const LevDev g = a.lv[l];
-    const LevDev s = slv[l];
-    const int n0 = g.l.n0, n01 = g.l.n0 * g.l.n1, n = n01 * g.l.n2;
-    const float in01 = 1.0f / (float)n01, in0 = 1.0f / (float)n0;
-    for (int q = threadIdx.x; q < n; q += blockDim.x) {
-      const int k = (int)(((float)q + 0.5f) * in01), r = q - k * n01, j = (int)(((float)r + 0.5f) * in0), i = r - j * n0;
-      const int o = g.l.off(i, j, k);
-      g.x[o] = s.x[q]; g.r[o] = s.r[q]; g.eps[o] = s.eps[q];
-    }
-  }
 }
 
 }  // namespace wl

@@ -109,54 +109,6 @@ __global__ void __launch_bounds__(256) k_incr4(const SmArgs a) {
   if (a.want_norms) { if (a.w.finish) block_reduce_finish(s1, m, a.w, a.out); else block_reduce_partial(s1, m, a.w); }
 }
 
-// ---------------------------------------------------------------- red-black half sweep, 8 cells per thread (4 updated)
-// gauss_rb (Poisson.jl:124-128) over half_rangek (:130-132).  The thread rewrites its two quads whole:
-// the cells of the other colour get back the value that was read (nobody writes them in this sweep).
-__global__ void __launch_bounds__(256) k_gs8(const LevArgs a) {
-  pdl_entry();
-  const Lay& l = a.l;
-  const int i = 1 + 8 * (blockIdx.x * blockDim.x + threadIdx.x);
-  const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
-  const int k = blockIdx.z * blockDim.z + threadIdx.z + 1;
-  if (i > l.n0 - 2 || j > l.n1 - 2 || k > l.n2 - 2) return;
-  if (k > 2 * (l.n2 / 2) - 2) return;
-  const int b = (j + k + 3 + a.k0) & 1;                            // updated cells: q = b, b+2, b+4, b+6
-  const int o = l.off(i, j, k);
-  const float* Lx = a.L; const float* Ly = a.L + l.cstride; const float* Lz = a.L + 2 * l.cstride;
-  const int pitch = l.pitch, plane = l.plane;
-  float lx[9], ly0[8], ly1[8], lz0[8], lz1[8], e[10], eym[8], eyp[8], ezm[8], ezp[8], r[8];
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    const int oh = o + 4 * h;
-    const F4 t0 = ld4g(Lx + oh), t1 = ld4g(Ly + oh), t2 = ld4g(Ly + oh + pitch), t3 = ld4g(Lz + oh), t4 = ld4g(Lz + oh + plane);
-    const F4 t5 = ld4(a.eps + oh), t6 = ld4(a.eps + oh - pitch), t7 = ld4(a.eps + oh + pitch),
-             t8 = ld4(a.eps + oh - plane), t9 = ld4(a.eps + oh + plane), ta = ld4(a.r + oh);
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      lx[4 * h + q] = t0.v[q]; ly0[4 * h + q] = t1.v[q]; ly1[4 * h + q] = t2.v[q]; lz0[4 * h + q] = t3.v[q]; lz1[4 * h + q] = t4.v[q];
-      e[1 + 4 * h + q] = t5.v[q]; eym[4 * h + q] = t6.v[q]; eyp[4 * h + q] = t7.v[q]; ezm[4 * h + q] = t8.v[q]; ezp[4 * h + q] = t9.v[q];
-      r[4 * h + q] = ta.v[q];
-    }
-  }
-  lx[8] = __ldg(Lx + o + 8);
-  e[0] = a.eps[o - 1]; e[9] = a.eps[o + 8];                        // ghosts as they are (stale under periodic BCs)
-#pragma unroll
-  for (int p = 0; p < 4; ++p) {
-#pragma unroll
-    for (int bb = 0; bb < 2; ++bb) {
-      if (bb != b) continue;
-      const int q = 2 * p + bb;
-      float s = r[q], dg = 0.f;
-      dg -= lx[q] + lx[q + 1];   s -= e[q] * lx[q] + e[q + 2] * lx[q + 1];
-      dg -= ly0[q] + ly1[q];     s -= eym[q] * ly0[q] + eyp[q] * ly1[q];
-      dg -= lz0[q] + lz1[q];     s -= ezm[q] * lz0[q] + ezp[q] * lz1[q];
-      e[1 + q] = s * inv_or_zero(dg);
-    }
-  }
-  st4(a.eps + o, F4{{e[1], e[2], e[3], e[4]}});
-  st4(a.eps + o + 4, F4{{e[5], e[6], e[7], e[8]}});
-}
-
 // ---------------------------------------------------------------- CFL (Flow.jl:234-244), 4 cells per thread
 // Same cells, same per-cell expression and the same "whole-array maximum" as k_cfl: rows and planes
 // 0..N-1 are all visited, a thread on a ghost row takes the maximum of the σ already stored there (zeros

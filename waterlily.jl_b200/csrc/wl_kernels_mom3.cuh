@@ -21,6 +21,8 @@
 // algorithmic B/cell); the few cells in the body band are recomputed afterwards by k_mom_patch
 // from the exact reference formula, f-neighbours on ghost rows included (Flow.jl:20-26,179).
 #pragma once
+#include <cuda.h>          // CUtensorMap (type only: the encoder is fetched through cudaGetDriverEntryPoint, no libcuda link)
+
 #include <type_traits>
 
 #include "wl_kernels_mom.cuh"
@@ -103,6 +105,10 @@ struct Mom3Args {
   Vec3 acc;
   int corrector;
   int KZ;
+  // TMA (cp.async.bulk.tensor): 4-D maps (x+3, y, z+zpad, component) over the padded device arrays of the advecting
+  // velocity, u⁰, V and μ₀; blocks whose tile lies inside the array take their planes with ONE bulk copy per operand
+  int use_tma;
+  alignas(64) CUtensorMap tm_ua, tm_u0, tm_V, tm_m0;
 };
 
 constexpr int M3_TY = 8;
@@ -123,15 +129,41 @@ constexpr int M3_TW = 36;                       // tile row pitch: columns i0-2 
 constexpr int M3_TH = M3_TY + 3;                // tile rows      j0-2 .. j0+TY
 constexpr int M3_TILE = M3_TW * M3_TH;          // floats per component per plane
 constexpr int M3_RING = 4;
+constexpr int M3_SLOT = ((3 * M3_TILE * 4 + 127) / 128) * 32;   // floats per ring slot: [3][M3_TILE] padded to 128 bytes (TMA)
+constexpr int M3_FIN = 32 * (M3_TY - 1);        // own-cell operands of one component and plane: the block's output rows
 
-struct Mom3Smem {
-  float ring[M3_RING][3][M3_TILE];
+struct alignas(128) Mom3Smem {
+  float ring[M3_RING][M3_SLOT];    // slot = plane & 3; component c of the tile at c * M3_TILE
+  float fin[3][9][M3_FIN];         // u⁰, V, μ₀ of the thread's own cell, staged two planes ahead (slot = plane % 3)
   float shy[2][3][M3_TY][32];
   float shx[2][3][M3_TY];          // W32: x-face fluxes of the column right of the block, per row
-#ifndef WL_M3_FIN_LDG
-  float fin[2][9][32 * M3_TY];     // u⁰, V, μ₀ of the thread's own cell, staged two planes ahead (slot = plane & 1)
-#endif
+  unsigned long long mbar[M3_RING];   // TMA: one transaction barrier per ring slot
 };
+
+// ---- TMA + mbarrier primitives (sm_90+; SASS: UTMALDG / SYNCS)
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned mb, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(mb), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(unsigned mb, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(mb), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned mb, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WL_MBAR_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra WL_MBAR_DONE;\n"
+      "bra WL_MBAR_WAIT;\n"
+      "WL_MBAR_DONE:\n"
+      "}\n" ::"r"(mb), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(unsigned dst, const CUtensorMap* tm, int c0, int c1, int c2, int c3, unsigned mb) {
+  asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];\n"
+               ::"r"(dst), "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(mb) : "memory");
+}
 
 // NB ("no body"): the host knows V ≡ 0 and μ₀ ≡ 1 on every cell (no body was ever measured or uploaded
 // and every direction is periodic, so BC!(μ₀,0) left no zero faces): then f - V = f and V + μ₀·f = f
@@ -174,9 +206,36 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   const bool has_b = pb < M3_TILE;
   const int ga = fold(i0 - 2 + pa % M3_TW, N0, p0) + pitch * fold(j0 - 2 + pa / M3_TW, N1, p1);
   const int gb = has_b ? fold(i0 - 2 + pb % M3_TW, N0, p0) + pitch * fold(j0 - 2 + pb / M3_TW, N1, p1) : 0;
+  // TMA: the block's tile lies inside the array (every FAST block of a non-periodic direction; periodic ones except
+  // those whose halo columns/rows wrap), so one elected thread fetches a plane of the three components with ONE bulk
+  // tensor copy, and the own-cell operands of the finalisation with one more per field; completion is counted on the
+  // ring slot's mbarrier.  Other blocks keep the per-thread cp.async staging below.
+  const bool tma = FAST && a.use_tma && i0 - 2 >= 0 && i0 + 33 <= N0 - 1 && j0 - 2 >= 0 && j0 + M3_TY <= N1 - 1;
+  auto plane_of = [&](int kp) { return p2 ? (kp > N2 - 1 ? min(kp - (N2 - 2), N2 - 1) : kp) : min(kp, khi); };
+  // ring plane kp (+ the finalisation operands of plane kf, or kf < 0) on the mbarrier of slot kp & 3
+  auto stage_tma = [&](int kp, int kf) {
+    const unsigned mb = smem_u32(&sm.mbar[kp & (M3_RING - 1)]);
+    constexpr unsigned ring_bytes = 3 * M3_TILE * 4, fin_bytes = 3 * M3_FIN * 4;
+    mbar_expect_tx(mb, ring_bytes + (kf >= 0 ? (NB ? 1u : 3u) * fin_bytes : 0u));
+    tma_load_4d(smem_u32(sm.ring[kp & (M3_RING - 1)]), &a.tm_ua, i0 - 2 + 3, j0 - 2, plane_of(kp) + l.zpad, 0, mb);
+    if (kf >= 0) {
+      float* dst = sm.fin[kf % 3][0];
+      tma_load_4d(smem_u32(dst), &a.tm_u0, i0 + 3, j0, kf + l.zpad, 0, mb);
+      if (!NB) {
+        tma_load_4d(smem_u32(dst + 3 * M3_FIN), &a.tm_V, i0 + 3, j0, kf + l.zpad, 0, mb);
+        tma_load_4d(smem_u32(dst + 6 * M3_FIN), &a.tm_m0, i0 + 3, j0, kf + l.zpad, 0, mb);
+      }
+    }
+  };
+  unsigned phase = 0;                             // parity bit per ring slot
+  auto wait_tma = [&](int kp) {
+    const int sl = kp & (M3_RING - 1);
+    mbar_wait(smem_u32(&sm.mbar[sl]), (phase >> sl) & 1u);
+    phase ^= 1u << sl;
+  };
   auto stage = [&](int kp) {
-    const int kc = p2 ? (kp > N2 - 1 ? min(kp - (N2 - 2), N2 - 1) : kp) : min(kp, khi);
-    float(*slot)[M3_TILE] = sm.ring[kp & (M3_RING - 1)];
+    const int kc = plane_of(kp);
+    float(*slot)[M3_TILE] = reinterpret_cast<float(*)[M3_TILE]>(sm.ring[kp & (M3_RING - 1)]);
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
       cp_async4(&slot[c][pa], U[c] + ga + plane * kc);
@@ -184,26 +243,24 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
     }
   };
   const int tc = (ty + 2) * M3_TW + lane + 2;     // own position in the tile
-#ifndef WL_M3_FIN_LDG
   // Operands of the finalisation (u⁰, V, μ₀ of the own cell): ncu showed 9 % of the kernel's stall samples on
-  // the first use of these loads although they were issued a whole plane of flux arithmetic earlier.  They now
-  // travel by cp.async too, two planes ahead and without holding registers; each thread reads back what it
-  // staged itself, so its own wait_group is the only synchronisation.
+  // the first use of these loads although they were issued a whole plane of flux arithmetic earlier.  They
+  // travel asynchronously too, two planes ahead and without holding registers (cp.async path: each thread reads
+  // back what it staged itself, so its own wait_group is the only synchronisation).
   const bool fin_thread = out_ij && ty < M3_TY - 1;
   auto stage_fin = [&](int kp) {
     if (!fin_thread) return;
     const int o = oij + plane * kp;
-    float* dst = &sm.fin[kp & 1][0][tid];
+    float* dst = &sm.fin[kp % 3][0][tid];
 #pragma unroll
     for (int ci = 0; ci < 3; ++ci) {
-      cp_async4(dst + ci * (32 * M3_TY), a.u0c[ci] + o);
+      cp_async4(dst + ci * M3_FIN, a.u0c[ci] + o);
       if (!NB) {
-        cp_async4(dst + (3 + ci) * (32 * M3_TY), a.Vc[ci] + o);
-        cp_async4(dst + (6 + ci) * (32 * M3_TY), a.m0c[ci] + o);
+        cp_async4(dst + (3 + ci) * M3_FIN, a.Vc[ci] + o);
+        cp_async4(dst + (6 + ci) * M3_FIN, a.m0c[ci] + o);
       }
     }
   };
-#endif
   // W32: lane = 7·c + r of the last row evaluates the x face of component c at column i0+32, row j0+r
   const bool xact = W32 && ty == M3_TY - 1 && lane < 3 * (M3_TY - 1);
   const int xr = lane % (M3_TY - 1), xc = min(lane / (M3_TY - 1), 2);
@@ -212,12 +269,20 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   const int kxX = (FAST || p0) ? 0 : (i0 + 32 == N0 - 1 ? 3 : 0);
   float xprev = 0.f;                              // u_x(i0+32, j0+xr) one plane below
 
-  stage(k0); stage(k0 + 1);
-#ifndef WL_M3_FIN_LDG
-  if (k0 <= kend - 1) stage_fin(k0);
-#endif
-  cp_async_commit();
-  stage(k0 + 2); cp_async_commit();
+  if (tma) {
+    if (tid == 0) {
+#pragma unroll
+      for (int q = 0; q < M3_RING; ++q) mbar_init(smem_u32(&sm.mbar[q]), 1);
+      mbar_fence_init();
+    }
+    __syncthreads();
+    if (tid == 0) { stage_tma(k0, k0 <= kend - 1 ? k0 : -1); stage_tma(k0 + 1, -1); stage_tma(k0 + 2, -1); }
+  } else {
+    stage(k0); stage(k0 + 1);
+    if (k0 <= kend - 1) stage_fin(k0);
+    cp_async_commit();
+    stage(k0 + 2); cp_async_commit();
+  }
   float w[3][4];   // own column: planes k-2, k-1, k, k+1
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
@@ -225,12 +290,12 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
     w[c][1] = U[c][oij + plane * (k0 - 1)];
   }
   if (xact) xprev = U[0][fold(i0 + 32, N0, p0) + pitch * fold(j0 + xr, N1, p1) + plane * (k0 - 1)];
-  cp_async_wait<1>();
+  if (tma) { wait_tma(k0); wait_tma(k0 + 1); } else cp_async_wait<1>();
   __syncthreads();
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    w[c][2] = sm.ring[k0 & (M3_RING - 1)][c][tc];
-    w[c][3] = sm.ring[(k0 + 1) & (M3_RING - 1)][c][tc];
+    w[c][2] = sm.ring[k0 & (M3_RING - 1)][c * M3_TILE + tc];
+    w[c][3] = sm.ring[(k0 + 1) & (M3_RING - 1)][c * M3_TILE + tc];
   }
   float pend[3] = {0.f, 0.f, 0.f};
 
@@ -243,21 +308,15 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
     constexpr bool TOP = decltype(top_tag)::value;
     const bool lastp = ZIN ? false : k == kend;
     const int kz = (ZIN || p2) ? 0 : (k == 1 ? (a.per.zlo ? 0 : 1) : (k == N2 - 1 ? (a.per.zhi ? 0 : 3) : 0));
-    if (!lastp) { stage(k + 3); cp_async_commit(); }
-    // operands of the finalisation of cell k-1: issued now, consumed after the fluxes
+    if (!lastp) {
+      if (tma) { if (tid == 0) stage_tma(k + 3, k + 1 <= kend - 1 ? k + 1 : -1); }
+      else { stage(k + 3); cp_async_commit(); }
+    }
+    // operands of the finalisation of cell k-1: staged two planes ago, consumed after the fluxes
     float fu0[3], fV[3], fm0[3];
     const int opv = oij + plane * (k - 1);
     const bool fin = !TOP && k > k0 && out_ij;
-#ifdef WL_M3_FIN_LDG
-    if (fin) {
-#pragma unroll
-      for (int ci = 0; ci < 3; ++ci) {
-        fu0[ci] = a.u0c[ci][opv];
-        if (!NB) { fV[ci] = a.Vc[ci][opv]; fm0[ci] = a.m0c[ci][opv]; }
-      }
-    }
-#endif
-    float(*cur)[M3_TILE] = sm.ring[k & (M3_RING - 1)];
+    float(*cur)[M3_TILE] = reinterpret_cast<float(*)[M3_TILE]>(sm.ring[k & (M3_RING - 1)]);
     float nb[3][3][3];   // nb[c][d][m2,m1,p1]
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
@@ -300,7 +359,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
         Fxu[ci] = __shfl_down_sync(0xffffffffu, F[ci][0], 1);
         sm.shy[buf][ci][ty][lane] = F[ci][1];
       }
-      cp_async_wait<1>();                                    // plane k+2 has landed (k+3 may be in flight)
+      if (tma) wait_tma(k + 2); else cp_async_wait<1>();     // plane k+2 has landed (k+3 may be in flight)
       __syncthreads();
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) Fyu[ci] = sm.shy[buf][ci][min(ty + 1, M3_TY - 1)][lane];
@@ -309,18 +368,16 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
         for (int ci = 0; ci < 3; ++ci) Fxu[ci] = sm.shx[buf][ci][min(ty, M3_TY - 2)];
       }
     }
-#ifndef WL_M3_FIN_LDG
-    if (lastp) cp_async_wait<0>();                           // no wait_group above on the last plane
+    if (lastp && !tma) cp_async_wait<0>();                   // no wait_group above on the last plane
     if (fin) {
-      const float* src = &sm.fin[(k - 1) & 1][0][tid];
+      const float* src = &sm.fin[(k - 1) % 3][0][tid];
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) {
-        fu0[ci] = src[ci * (32 * M3_TY)];
-        if (!NB) { fV[ci] = src[(3 + ci) * (32 * M3_TY)]; fm0[ci] = src[(6 + ci) * (32 * M3_TY)]; }
+        fu0[ci] = src[ci * M3_FIN];
+        if (!NB) { fV[ci] = src[(3 + ci) * M3_FIN]; fm0[ci] = src[(6 + ci) * M3_FIN]; }
       }
     }
-    if (!TOP && k + 1 <= kend - 1) stage_fin(k + 1);        // joins the group committed at the top of the next plane
-#endif
+    if (!tma && !TOP && k + 1 <= kend - 1) stage_fin(k + 1);  // joins the group committed at the top of the next plane
     if (fin) {                                               // finalise cell (i,j,k-1)
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) {
@@ -337,7 +394,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
       }
     }
     if (!lastp) {
-      float(*nxt)[M3_TILE] = sm.ring[(k + 2) & (M3_RING - 1)];
+      float(*nxt)[M3_TILE] = reinterpret_cast<float(*)[M3_TILE]>(sm.ring[(k + 2) & (M3_RING - 1)]);
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) {
         float r = F[ci][0];
@@ -364,9 +421,10 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
 }
 
 template <int S, bool NB, bool W32>
-__global__ void __launch_bounds__(32 * M3_TY, 2) k_mom3(const Mom3Args a) {
+__global__ void __launch_bounds__(32 * M3_TY, 2) k_mom3(const __grid_constant__ Mom3Args a) {
   pdl_entry();
-  __shared__ Mom3Smem sm;
+  extern __shared__ __align__(128) unsigned char m3_raw[];
+  Mom3Smem& sm = *reinterpret_cast<Mom3Smem*>(m3_raw);
   // FAST: every thread of the block sits on an ordinary cell with ordinary faces (in a periodic direction
   // that is every block whose last lane / row still lies inside the array)
   const int px = a.per.p[0] ? 1 : 0, py = a.per.p[1] ? 1 : 0;
@@ -380,9 +438,7 @@ __global__ void __launch_bounds__(32 * M3_TY, 2) k_mom3(const Mom3Args a) {
   else mom3_body_async<S, false, NB, W32>(a, sm);
 }
 
-// ---- band cells (any μ₁ ≠ 0): exact BDIM with μddn, Flow.jl:20-26,176-180.
-// One warp per band cell: lane = 7·ci + nbr evaluates f[I+δ(nbr), ci] (nbr 0 centre, 1/2 ±x, 3/4 ±y,
-// 5/6 ±z) from global memory with the general per-cell routine; the centre lanes then gather.
+// ---- band cells (any μ₁ ≠ 0): exact BDIM with μddn, Flow.jl:20-26,176-180 (two passes, below).
 struct PatchArgs {
   MomArgs m;           // ua, u0, V, per, nu, dt, acc (m.f unused)
   const float* mu0;
@@ -393,41 +449,12 @@ struct PatchArgs {
   int cap;
   int corrector;
 };
-template <int S>
-__global__ void __launch_bounds__(128) k_mom_patch(const PatchArgs a) {
-  pdl_entry();
-  const Lay& l = a.m.l;
-  const int n = min(*a.count, a.cap);
-  const int lane = threadIdx.x & 31;
-  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
-  const int ci = min(lane / 7, 2), nbr = lane % 7;
-  const int e = nbr == 0 ? 0 : ((nbr & 1) ? 1 : -1), d = nbr == 0 ? 0 : (nbr - 1) >> 1;
-  for (int q = wid; q < n; q += nw) {
-    const int o = a.list[q];
-    const int k = o / l.plane, rem = o - k * l.plane, j = rem / l.pitch, i = rem - j * l.pitch;
-    float fv = 0.f;
-    if (lane < 21) fv = rhs_f<3, S>(a.m, ci, i + (d == 0 ? e : 0), j + (d == 1 ? e : 0), k + (d == 2 ? e : 0));
-    float s = 0.f;
-#pragma unroll
-    for (int dj = 0; dj < 3; ++dj) {
-      const float fp = __shfl_sync(0xffffffffu, fv, ci * 7 + 1 + 2 * dj);
-      const float fm = __shfl_sync(0xffffffffu, fv, ci * 7 + 2 + 2 * dj);
-      if (lane < 21 && nbr == 0) s += a.mu1[l.cstride * (ci + 3 * dj) + o] * (fp - fm);
-    }
-    if (lane < 21 && nbr == 0) {
-      const long long oc = l.cstride * ci + o;
-      const float X = s / 2.f + a.m.V[oc] + a.mu0[oc] * fv;
-      a.un[oc] = a.corrector ? (a.m.ua[oc] + X) * 0.5f : X;
-    }
-  }
-}
-
-// ---- band patch in two passes (default).  The one-warp-per-cell kernel above evaluates every f value up to
-// seven times (a band cell and its six neighbours are mostly band cells themselves): 141 us per call on the
-// sphere of config C, 521 us on the cylinder of config D.  Here the cells whose f is needed -- the band and its
+// ---- band patch in two passes.  (A one-warp-per-cell kernel evaluated every f value up to seven times -- a band
+// cell and its six neighbours are mostly band cells themselves: 141 us per call on the sphere of config C, 521 us
+// on the cylinder of config D; removed in round 2.)  Here the cells whose f is needed -- the band and its
 // face neighbours, de-duplicated once per measure! into `list2` -- get f[I,ci] exactly once (K-PATCH-F, one thread
 // per cell and component, written to the otherwise idle flow.f), then one thread per band cell and component
-// applies μddn (K-PATCH-APPLY).  Same rhs_f, same summation order: bit-identical to k_mom_patch.
+// applies μddn (K-PATCH-APPLY).  Same rhs_f, same summation order as the reference: bit-identical.
 struct Band2Args { Lay l; const int* list; const int* count; int cap; int* mark; int epoch; int* list2; int* count2; int cap2; };
 __global__ void __launch_bounds__(256) k_band_nbrs(const Band2Args a) {
   pdl_entry();

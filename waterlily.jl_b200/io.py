@@ -5,7 +5,11 @@ reference's extensions work on `Array(flow.p)` / `copyto!(flow.p, ...)`.
 
 * `save` / `load`                 : `save!(fname, sim)` / `load!(sim; fname)`   (ext/WaterLilyJLD2Ext.jl:11-49).
   The container is `.npz` instead of JLD2 (no HDF5 writer in this image); the payload is the same three
-  entries `p`, `u`, `Δt`, arrays in the mirror's own (component, z, y, x) order.
+  entries `p`, `u` and the Δt vector (stored under the key `dt`), arrays in the mirror's own (component, z, y, x)
+  order.  On a slab-decomposed run every rank stores / restores ITS slab in `fname.rNNNofMMM`.
+* These are the mirror's OWN formats: `read_vti` parses what `write_vti` writes (uncompressed raw-appended ImageData) and
+  rejects anything else with a clear error; files written by the reference's JLD2 / WriteVTK extensions are read by
+  those extensions, which work unchanged on `B200Array` (Julia side).
 * `save_meanflow` / `load_meanflow`: the `MeanFlow` pair of the same extension (:24-31, :57-69).
 * `VTKWriter` + `load_pvd`        : `vtkWriter` / `save!(w, sim)` / `close(w)` (ext/WaterLilyWriteVTKExt.jl:27-71) and
   `load!(sim, Val(:pvd))` (ext/WaterLilyReadVTKExt.jl:22-43): one ImageData `.vti` per save on the `1:n` point grid
@@ -24,9 +28,14 @@ __all__ = ["save", "load", "save_meanflow", "load_meanflow", "VTKWriter", "load_
 
 
 # ------------------------------------------------------------------------------------------------ JLD2 pair
+def _slab_name(fname, sim):
+    n = getattr(sim, "nranks", 1)
+    return fname if n == 1 else "%s.r%03iof%03i" % (fname, sim.rank, n)
+
+
 def save(fname, sim, dir="./"):
-    """`save!(fname, sim; dir)`: pressure, velocity and the Δt vector."""
-    path = os.path.join(dir, fname)
+    """`save!(fname, sim; dir)`: pressure, velocity and the Δt vector (every rank its own slab file on several GPUs)."""
+    path = os.path.join(dir, _slab_name(fname, sim))
     with open(path, "wb") as fh:                       # a file handle keeps numpy from appending ".npz"
         np.savez(fh, p=sim.download("p"), u=sim.download("u"), dt=np.asarray(sim.flow.Δt, np.float32))
     return path
@@ -34,7 +43,7 @@ def save(fname, sim, dir="./"):
 
 def load(sim, fname="WaterLily.npz", dir="./"):
     """`load!(sim; fname, dir)`: p and u are overwritten, Δt is replaced (empty! + push!)."""
-    with np.load(os.path.join(dir, fname)) as obj:
+    with np.load(os.path.join(dir, _slab_name(fname, sim))) as obj:
         p, u, dt = obj["p"], obj["u"], obj["dt"]
     if tuple(p.shape) != tuple(sim.field_shape("p")):
         raise ValueError("Simulation size does not match the size of the stored simulation.")
@@ -117,6 +126,9 @@ def read_vti(path):
     """Inverse of `write_vti`: (grid shape as (nz, ny, nx) or (ny, nx), {name: array}) with vectors components-first
     in the leading axis again (`components_last` of the reader ext, in this mirror's axis order)."""
     raw = open(path, "rb").read()
+    if b'<AppendedData encoding="raw">' not in raw or b"compressor=" in raw[:4096]:
+        raise ValueError(f"{path}: only the uncompressed raw-appended ImageData layout written by write_vti is supported "
+                         "(files from WriteVTK.jl are compressed / base64: read them with the reference's ReadVTK extension)")
     mark = raw.index(b'<AppendedData encoding="raw">')
     head = raw[:mark].decode()
     blob = raw[raw.index(b"_", mark) + 1:]
@@ -224,7 +236,8 @@ class VTKWriter:
             return
         lines = ['<?xml version="1.0"?>', '<VTKFile type="Collection" version="1.0" byte_order="LittleEndian">',
                  '  <Collection>']
-        lines += [f'    <DataSet timestep="{t!r}" part="0" file="{f}"/>' for t, f in self.entries]
+        base = os.path.dirname(os.path.abspath(self.fname + ".pvd"))          # DataSet paths are relative to the .pvd
+        lines += [f'    <DataSet timestep="{t!r}" part="0" file="{os.path.relpath(os.path.abspath(f), base)}"/>' for t, f in self.entries]
         lines += ['  </Collection>', '</VTKFile>', '']
         with open(self.fname + ".pvd", "w") as fh:
             fh.write("\n".join(lines))
@@ -233,9 +246,18 @@ class VTKWriter:
 def load_pvd(sim, fname="WaterLily.pvd", attrib=None, pressure="Pressure", velocity="Velocity"):
     """`load!(sim, Val(:pvd); fname, attrib)` (ext/WaterLilyReadVTKExt.jl:22-43): restart from the last file of the
     collection, set Δt[end] to the stored time (in flow units) and push CFL; returns a writer that appends."""
-    entries = _read_pvd(fname)
+    base = os.path.dirname(os.path.abspath(fname))
+    entries = [(t, os.path.relpath(f if os.path.isabs(f) else os.path.join(base, f))) for t, f in _read_pvd(fname)]
     t_last, f_last = entries[-1]
-    grid, data = read_vti(f_last)
+    if f_last.endswith(".pvti"):                           # written by a slab-decomposed run: reassemble, then take this rank's slab
+        grid, data = read_pvti(f_last)
+        n = getattr(sim, "nranks", 1)
+        if n > 1:
+            from . import slab_of
+            data = {k: slab_of(a, sim.rank, n) for k, a in data.items()}
+            grid = data[pressure].shape
+    else:
+        grid, data = read_vti(f_last)
     if tuple(grid) != tuple(sim.field_shape("p")):
         raise ValueError("The dimensions of the simulation do not match the dimensions of the vtk file.")
     sim.upload("p", data[pressure])

@@ -112,7 +112,8 @@ struct B200Flow{D,T} <: AbstractFlow{D,T}
     h::Handle
     u::B200Array{T}; u⁰::B200Array{T}; f::B200Array{T}; p::B200Array{T}; σ::B200Array{T}
     V::B200Array{T}; μ₀::B200Array{T}; μ₁::B200Array{T}
-    uBC::NTuple{D,T}; Δt::Vector{T}; ν::T; g::Nothing; exitBC::Bool; perdir::NTuple
+    uBC::Union{NTuple{D,T},Function}; Δt::Vector{T}; ν::T; g::Union{Function,Nothing}; exitBC::Bool; perdir::NTuple
+    koff::Int                                        # global index of the slab's first plane (0 on one GPU)
 end
 const SCHEME = Dict(WaterLily.quick => 0, WaterLily.cds => 1, WaterLily.vanLeer => 2)
 
@@ -131,10 +132,13 @@ returned flow holds this rank's slab: arrays have `N[end]÷nranks+2` planes and 
 function B200Flow(N::NTuple{D}, uBC; Δt=0.25, ν=0., g=nothing, u0=nothing, uλ=nothing, perdir=(), exitBC=false,
                   λ=WaterLily.quick, T=Float32, mem=Array, device=0, comm=nothing) where D
     T == Float32 || error("WL_ERR_UNSUPPORTED: the B200 path is Float32 only")
-    (uBC isa Function || g isa Function) && error("WL_ERR_UNSUPPORTED: Function uBC / g cannot cross the C ABI")
     haskey(SCHEME, λ) || error("WL_ERR_UNSUPPORTED: λ must be quick, cds or vanLeer")
+    # A Function uBC(i,x,t) / g(i,x,t) stays on the host: it is SAMPLED into the boundary tables / acceleration fields
+    # the device path consumes (set_bc_function!, set_accel_field!) -- at t = 0 here, at t₁ / (t₀,t₁) in every mom_step!.
+    ubc0 = uBC isa Function ? ntuple(_ -> 0f0, D) : Float32.(uBC)
+    (uBC isa Function && !isnothing(comm) && comm[2] > 1) && error("WL_ERR_UNSUPPORTED: Function uBC on a slab-decomposed run")
     cfg = Ref(WLConfig(D, pad3(Int32.(N), Int32(0)), ntuple(i -> Int32(i in perdir), 3), exitBC, SCHEME[λ], ν, Δt,
-                       pad3(Float32.(uBC), 0f0), 10, 2f-3, 32, device, 0))
+                       pad3(ubc0, 0f0), 10, 2f-3, 32, device, 0))
     out = Ref{Ptr{Cvoid}}(C_NULL)
     koff = 0
     if isnothing(comm) || comm[2] == 1
@@ -151,14 +155,18 @@ function B200Flow(N::NTuple{D}, uBC; Δt=0.25, ν=0., g=nothing, u0=nothing, uλ
     arr(f, dims) = B200Array{T,length(dims)}(h, Int32(f), Int32(0), dims)
     flow = B200Flow{D,T}(h, arr(FIELD.u, (Ng..., D)), arr(FIELD.u⁰, (Ng..., D)), arr(FIELD.f, (Ng..., D)),
                          arr(FIELD.p, Ng), arr(FIELD.σ, Ng), arr(FIELD.V, (Ng..., D)), arr(FIELD.μ₀, (Ng..., D)),
-                         arr(FIELD.μ₁, (Ng..., D, D)), T.(uBC), T[Δt], T(ν), nothing, exitBC, perdir)
+                         arr(FIELD.μ₁, (Ng..., D, D)), uBC isa Function ? uBC : T.(uBC), T[Δt], T(ν), g, exitBC, perdir, koff)
     u0 = isnothing(u0) ? uλ : u0
+    if uBC isa Function
+        set_bc_function!(flow, uBC; t=zero(T))         # BC!(u,uBC,exitBC,perdir) of the constructor, t = 0 (Flow.jl:141)
+        isnothing(u0) && (u0 = (i, x) -> uBC(i, x, zero(T)))               # ic_function(uBC)
+    end
     if !isnothing(u0)                                  # apply!(u0,u) on the host, then BC!/exitBC!/u⁰ on the device
         host = Array{T}(undef, Ng..., D)
         shift(x) = x .+ ntuple(d -> d == D ? T(koff) : zero(T), D)        # slab origin in the global grid
         u0 isa Function ? WaterLily.apply!((i, x) -> u0(i, shift(x)), host) : WaterLily.apply!((i, x) -> u0[i], host)
         copyto!(flow.u, host)
-        check(h, ccall((:wl_finish_ic, LIB), Cint, (Ptr{Cvoid}, Ref{NTuple{3,Float32}}), h.ptr, Ref(pad3(Float32.(uBC), 0f0))))
+        check(h, ccall((:wl_finish_ic, LIB), Cint, (Ptr{Cvoid}, Ref{NTuple{3,Float32}}), h.ptr, Ref(pad3(ubc0, 0f0))))
     end
     flow
 end
@@ -189,9 +197,26 @@ end
 function mom_step!(a::B200Flow{D,T}, b::B200Poisson; udf=nothing, kwargs...) where {D,T}
     isnothing(udf) || error("WL_ERR_UNSUPPORTED: udf hooks cannot cross the C ABI")
     ccall((:wl_set_dt, LIB), Cint, (Ptr{Cvoid}, Cfloat), a.h.ptr, a.Δt[end])
+    t₁ = sum(a.Δt); t₀ = t₁ - a.Δt[end]                 # Flow.jl:157
+    if a.uBC isa Function                               # all four BC! of the step use t₁ (Flow.jl:194,209,231)
+        set_bc_function!(a, a.uBC; t=t₁)
+    end
+    if a.g isa Function || a.uBC isa Function           # accelerate!(r,t,g,uBC): g + ∂ₜuBC by AD, as Flow.jl:69-73
+        acc(i, x, t) = (a.g isa Function ? a.g(i, x, t) : zero(T)) +
+                       (a.uBC isa Function ? WaterLily.derivative(τ -> a.uBC(i, x, τ), t) : zero(T))
+        set_accel_field!(a, 0, acc, t₀); set_accel_field!(a, 1, acc, t₁)
+    end
     info = Ref{WLStepInfo}()
     check(a.h, ccall((:wl_mom_step, LIB), Cint, (Ptr{Cvoid}, Ptr{Cfloat}, Ptr{Cfloat}, Ptr{Cfloat}, Ref{WLStepInfo}),
                      a.h.ptr, C_NULL, C_NULL, C_NULL, info))
+    # the solver trace the reference writes with @log (Flow.jl:159,163, MultiLevelPoisson.jl:112,117): same lines, same order
+    for (q, tag) in enumerate(("p", "c"))
+        WaterLily.@log tag
+        for it in 0:info[].trace_len[q]-1
+            k = 34 * (q - 1) + it + 1
+            WaterLily.@log ", $it, $(info[].rinf[k]), $(info[].r1[k]), $(info[].omega[k])\n"
+        end
+    end
     push!(b.n, info[].n_pred, info[].n_corr)            # MultiLevelPoisson.jl:127
     push!(a.Δt, info[].dt_next)                         # Flow.jl:166
 end
@@ -207,11 +232,39 @@ function measure!(a::B200Flow{D,T}, body::AbstractBody; t=zero(T), ϵ=1) where {
         check(a.h, ccall((:wl_measure_csg, LIB), Cint, (Ptr{Cvoid}, Ptr{WLNode}, Cint, Cdouble), a.h.ptr, nd, length(nd), ϵ))
         return
     end
-    host = WaterLily.Flow(size(a.p) .- 2, a.uBC; T, perdir=a.perdir, exitBC=a.exitBC)
+    host = WaterLily.Flow(size(a.p) .- 2, ntuple(_ -> zero(T), D); T, perdir=a.perdir, exitBC=a.exitBC)
     fill!(host.V, 0); fill!(host.μ₀, 1); fill!(host.μ₁, 0)
-    WaterLily.measure!(host, body; t, ϵ)               # includes the two BC! calls; the library re-applies them (idempotent)
+    WaterLily.measure!(host, shifted(body, a.koff, Val(D)); t, ϵ)   # includes the two BC! calls; the library re-applies them (idempotent)
     check(a.h, ccall((:wl_set_body_coeffs, LIB), Cint, (Ptr{Cvoid}, Ptr{Float32}, Ptr{Float32}, Ptr{Float32}, Ptr{Float32}),
                      a.h.ptr, host.μ₀, host.μ₁, host.V, host.σ))
+end
+"A body seen from a slab whose first plane is global plane `koff`: the same body with `x[D] += koff`."
+struct ShiftedBody{B<:AbstractBody,D} <: AbstractBody; body::B; koff::Int; end
+shifted(b::AbstractBody, koff, ::Val{D}) where D = koff == 0 ? b : ShiftedBody{typeof(b),D}(b, koff)
+WaterLily.measure(s::ShiftedBody{B,D}, x, t; kw...) where {B,D} =
+    WaterLily.measure(s.body, x .+ ntuple(d -> d == D ? eltype(x)(s.koff) : zero(eltype(x)), D), t; kw...)
+WaterLily.sdf(s::ShiftedBody{B,D}, x, t=0; kw...) where {B,D} =
+    WaterLily.sdf(s.body, x .+ ntuple(d -> d == D ? eltype(x)(s.koff) : zero(eltype(x)), D), t; kw...)
+
+"""
+`pressure_force(flow, body)` for ANY `AbstractBody` (src/Metrics.jl:116-133): `nds(body, loc(0,I), t)` is evaluated by the
+reference's own code on the host over the interior cells, the non-zero entries travel through `wl_set_force_weights`, and
+the device forms `p[I]·nds` in Float32 and sums in Float64 as the reference does.  Library bodies (`B200Body`, `B200Rigid`
+trees) have device-side methods below and never come here.
+"""
+function pressure_force(a::B200Flow{D,T}, body::AbstractBody) where {D,T}
+    Ng = size(a.p); b = shifted(body, a.koff, Val(D)); t = time(a)
+    idx = Int64[]; w = T[]
+    lin = LinearIndices(Ng)
+    for I in WaterLily.inside(Ng)
+        n = WaterLily.nds(b, WaterLily.loc(0, I, T), t)
+        iszero(n) && continue
+        push!(idx, lin[I] - 1); append!(w, n)           # 0-based, first dimension fastest; D weights per entry
+    end
+    check(a.h, ccall((:wl_set_force_weights, LIB), Cint, (Ptr{Cvoid}, Int64, Ptr{Int64}, Ptr{Cfloat}), a.h.ptr, length(idx), idx, w))
+    out = Ref(ntuple(_ -> 0.0, 3))
+    check(a.h, ccall((:wl_pressure_force_weights, LIB), Cint, (Ptr{Cvoid}, Ref{NTuple{3,Float64}}), a.h.ptr, out))
+    collect(out[][1:D])
 end
 update!(b::B200Poisson) = check(b.h, ccall((:wl_update_poisson, LIB), Cint, (Ptr{Cvoid},), b.h.ptr))
 function solver!(b::B200Poisson; kw...)
@@ -266,7 +319,11 @@ viscous_moment(x₀, a::B200Flow, body::B200Body) = force_moment(x₀, a, body, 
 total_moment(x₀, a::B200Flow, body::B200Body) = pressure_moment(x₀, a, body) .+ viscous_moment(x₀, a, body)
 
 function csg_call(sym, a::B200Flow{D}, body, extra...) where D
-    nd = nodes(body); nd === nothing && error("force metrics on the device need library primitives (B200Rigid leaves)")
+    nd = nodes(body)
+    if nd === nothing                                     # a tree with a non-library leaf: the host-weights route
+        sym === :wl_pressure_force_csg && return invoke(pressure_force, Tuple{B200Flow,AbstractBody}, a, body)
+        error("WL_ERR_UNSUPPORTED: viscous force and moments need library primitives (B200Rigid leaves)")
+    end
     out = Ref(ntuple(_ -> 0.0, 3))
     sym === :wl_force_moment_csg ?
         check(a.h, ccall((:wl_force_moment_csg, LIB), Cint, (Ptr{Cvoid}, Ptr{WLNode}, Cint, Ref{NTuple{3,Float64}}, Cint, Ref{NTuple{3,Float64}}),
@@ -286,7 +343,7 @@ total_moment(x₀, a::B200Flow, body::CsgBody) = pressure_moment(x₀, a, body) 
 # ---- Function uBC(i,x,t): sampled where BC! evaluates it (src/core.jl:201-219) and handed over as tables ------------
 # Layout of wl_set_bc_tables: component outer, direction inner, three planes (index 1, 2, Ng[j]) over the other dims in
 # column-major order; normal component: the Dirichlet values; tangential: uBC(I)-uBC(I±δ) on the two ghost planes.
-# Built together with the device kernel; like it, not yet run (see include/wl_b200.h).
+# (The ctypes mirror's `bctables.py` is the executable twin of this function: tests/test_bctables_cpu.py, tests/test_fnbc_gpu.py.)
 function bc_tables(uBC::Function, Ng::NTuple{D,Int}, t, perdir, ::Type{T}) where {D,T}
     tab = T[]
     for i in 1:D, j in 1:D, (s, k) in enumerate((1, 2, Ng[j])), I in WaterLily.slice(Ng, k, j)
