@@ -125,7 +125,12 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
 
-constexpr int M3_TW = 36;                       // tile row pitch: columns i0-2 .. i0+33
+constexpr int M3_X0 = 4;                        // tile column of cell i0.  The stencil needs columns i0-2 .. i0+33; the tile starts two
+                                                // columns earlier because a TMA box must start on a 16-byte boundary of its row (measured on
+                                                // B200: an innermost coordinate that is not a multiple of 4 floats raises "illegal instruction",
+                                                // scripts/r2/tma_probe.cu), and cell i0-4 = 32·bx-3 is the nearest such column (layout: cell 1
+                                                // of every row is 128-byte aligned)
+constexpr int M3_TW = 40;                       // tile row pitch: columns i0-4 .. i0+35
 constexpr int M3_TH = M3_TY + 3;                // tile rows      j0-2 .. j0+TY
 constexpr int M3_TILE = M3_TW * M3_TH;          // floats per component per plane
 constexpr int M3_RING = 4;
@@ -204,20 +209,23 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   // staging duty of this thread: tile positions tid and tid+256
   const int pa = tid, pb = tid + 32 * M3_TY;
   const bool has_b = pb < M3_TILE;
-  const int ga = fold(i0 - 2 + pa % M3_TW, N0, p0) + pitch * fold(j0 - 2 + pa / M3_TW, N1, p1);
-  const int gb = has_b ? fold(i0 - 2 + pb % M3_TW, N0, p0) + pitch * fold(j0 - 2 + pb / M3_TW, N1, p1) : 0;
+  const int ga = fold(i0 - M3_X0 + pa % M3_TW, N0, p0) + pitch * fold(j0 - 2 + pa / M3_TW, N1, p1);
+  const int gb = has_b ? fold(i0 - M3_X0 + pb % M3_TW, N0, p0) + pitch * fold(j0 - 2 + pb / M3_TW, N1, p1) : 0;
   // TMA: the block's tile lies inside the array (every FAST block of a non-periodic direction; periodic ones except
   // those whose halo columns/rows wrap), so one elected thread fetches a plane of the three components with ONE bulk
   // tensor copy, and the own-cell operands of the finalisation with one more per field; completion is counted on the
   // ring slot's mbarrier.  Other blocks keep the per-thread cp.async staging below.
-  const bool tma = FAST && a.use_tma && i0 - 2 >= 0 && i0 + 33 <= N0 - 1 && j0 - 2 >= 0 && j0 + M3_TY <= N1 - 1;
+  // (columns of the box left of cell 0 or right of the row's pitch are never used: they hold the neighbouring row's
+  //  padding or the zero fill of an out-of-bounds box; the columns the stencil reads, i0-2 .. i0+33, must be real cells)
+  const bool tma = FAST && a.use_tma && i0 - 2 >= 0 && i0 + 33 <= N0 - 1 && i0 + 33 + 3 <= pitch - 1 &&
+                   j0 - 2 >= 0 && j0 + M3_TY <= N1 - 1;
   auto plane_of = [&](int kp) { return p2 ? (kp > N2 - 1 ? min(kp - (N2 - 2), N2 - 1) : kp) : min(kp, khi); };
   // ring plane kp (+ the finalisation operands of plane kf, or kf < 0) on the mbarrier of slot kp & 3
   auto stage_tma = [&](int kp, int kf) {
     const unsigned mb = smem_u32(&sm.mbar[kp & (M3_RING - 1)]);
     constexpr unsigned ring_bytes = 3 * M3_TILE * 4, fin_bytes = 3 * M3_FIN * 4;
     mbar_expect_tx(mb, ring_bytes + (kf >= 0 ? (NB ? 1u : 3u) * fin_bytes : 0u));
-    tma_load_4d(smem_u32(sm.ring[kp & (M3_RING - 1)]), &a.tm_ua, i0 - 2 + 3, j0 - 2, plane_of(kp) + l.zpad, 0, mb);
+    tma_load_4d(smem_u32(sm.ring[kp & (M3_RING - 1)]), &a.tm_ua, i0 - M3_X0 + 3, j0 - 2, plane_of(kp) + l.zpad, 0, mb);
     if (kf >= 0) {
       float* dst = sm.fin[kf % 3][0];
       tma_load_4d(smem_u32(dst), &a.tm_u0, i0 + 3, j0, kf + l.zpad, 0, mb);
@@ -242,7 +250,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
       if (has_b) cp_async4(&slot[c][pb], U[c] + gb + plane * kc);
     }
   };
-  const int tc = (ty + 2) * M3_TW + lane + 2;     // own position in the tile
+  const int tc = (ty + 2) * M3_TW + lane + M3_X0;     // own position in the tile
   // Operands of the finalisation (u⁰, V, μ₀ of the own cell): ncu showed 9 % of the kernel's stall samples on
   // the first use of these loads although they were issued a whole plane of flux arithmetic earlier.  They
   // travel asynchronously too, two planes ahead and without holding registers (cp.async path: each thread reads
@@ -264,7 +272,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   // W32: lane = 7·c + r of the last row evaluates the x face of component c at column i0+32, row j0+r
   const bool xact = W32 && ty == M3_TY - 1 && lane < 3 * (M3_TY - 1);
   const int xr = lane % (M3_TY - 1), xc = min(lane / (M3_TY - 1), 2);
-  const int pX = (xr + 2) * M3_TW + 34;           // tile position of (i0+32, j0+xr)
+  const int pX = (xr + 2) * M3_TW + M3_X0 + 32;          // tile position of (i0+32, j0+xr)
   const int pA = xc == 0 ? pX - 1 : pX - M3_TW;   // the other operand of the advecting mean (xc == 2: previous plane)
   const int kxX = (FAST || p0) ? 0 : (i0 + 32 == N0 - 1 ? 3 : 0);
   float xprev = 0.f;                              // u_x(i0+32, j0+xr) one plane below
