@@ -183,6 +183,23 @@ int wl_get_dt(const wl_sim* s, float* dt);
 int wl_set_dt(wl_sim* s, float dt);
 int wl_cfl(wl_sim* s, float* dt);                       /* CFL(a) src/Flow.jl:234-237 */
 
+/* ---- allocation-free CFL.  NO COUNTERPART IN THE REFERENCE: added for callers
+ *      that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ *      Computes what wl_cfl computes -- Δt = min(10, 1/(max_I flux_out(I,u) + 5ν)), src/Flow.jl:234-244, the maximum
+ *      taken over the interior cells and the zero of the lower ghost cells -- but needs no wl_sim and allocates
+ *      nothing: its reduction scratch is a file-scope `static __device__` array (1 MiB + 256 B on every GPU that
+ *      loads the library, held until exit).  The call makes no cudaMalloc / cudaFree / allocating library call; it
+ *      enqueues one 4-byte memset and one kernel on `cuda_stream` (a cudaStream_t; NULL = the legacy default stream)
+ *      and returns without synchronising.  The first call on each device resolves the array's device address
+ *      (cudaGetSymbolAddress): make one warm-up call per device before capturing a graph.
+ *        u_dev   device pointer, Float32, the reference's dense layout (n[0], n[1][, n[2]], D), ghosts included
+ *        n       extents INCLUDING the two ghost cells per direction (n[2] ignored for D == 2)
+ *        dt_dev  device pointer to one float (output)
+ *      LIMIT: (n[1]-2)·(n[2]-2) <= 262144 interior rows (e.g. 512x512x512 cells); larger grids return WL_ERR_INVALID
+ *      with the limit in wl_last_error(NULL).  All calls on a GPU SHARE the array, which keeps the previous call's
+ *      contents (the call clears what must start at zero): calls that overlap on one GPU race -- serialise them.   */
+int wl_cfl_noalloc(const float* u_dev, int32_t D, const int32_t n[3], float nu, float* dt_dev, void* cuda_stream);
+
 /* ---- pressure_force(sim) (src/Metrics.jl:116-133); clobbers flow.f like the reference        */
 int wl_pressure_force(wl_sim* s, const wl_body* body, double t, double out[3]);
 /* ---- pressure_force for a HOST-measured body (any `AutoBody(sdf,map)` closure; replaces `pressure_force(flow,body)`,

@@ -1178,3 +1178,4 @@ inline bool divisible(int N) { return N % 2 == 0 && N > 4; }
 }  // namespace
 
 #include "wl_abi.cuh"
+#include "wl_noalloc.cuh"
