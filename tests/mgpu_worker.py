@@ -80,6 +80,8 @@ def run_case(wl, name, comm, dev):
     out["halo"] = slab.halo_stats()
     out["transport"] = slab.halo_transport()
     out["ok"] = bool(ok)
+    slab.close()               # collective: every rank, at the same point (never left to the garbage collector)
+    one.close()
     return out
 
 
