@@ -517,6 +517,7 @@ def main():
             for name, (n, ms) in sorted(allp.items(), key=lambda kv: -kv[1][1]):
                 f.write(f"{name}\t{n}\t{ms:.4f}\t{ms / n * 1e3:.2f}\t{ms / ksum:.3f}\t{blocks.get(name, 0)}\n")
 
+    tiles = sim.tile_classes(0) if D == 3 else (0, 0, 0)
     halo = sim.halo_stats()
     halo_us = sim.halo_timing() if world > 1 else None
     halo_transport = sim.halo_transport()
@@ -574,6 +575,10 @@ def main():
                        f"halo exchange by {halo_transport} ({halo[0] // max(1, nsteps_total)} exchanges, "
                        f"{halo[1] / max(1, nsteps_total) / 1e6:.1f} MB sent per rank per step), coarse levels replicated",
                        "poisson_iters_per_step": float(np.mean(n_iters)) * 2,
+                       "pattern_tiles_level1": {"general": tiles[0], "constants": tiles[1], "constants_with_boundary": tiles[2],
+                                                "note": "tiles (128x4x2 cells) on which the pressure kernels use the body-free coefficient pattern "
+                                                        "instead of loading L / iD (12-20 of their 24-36 algorithmic B/cell): B_alg in "
+                                                        "roofline.kernels keeps SURVEY's figure, so their achieved GB/s is an upper bound of the DRAM rate"},
                        "l2": "working set (%.0f MB per GPU) exceeds L2, no flush" % (30 * 4 * cells / world / 1e6)
                              if cells / world > 1.5e6 else "fits L2"},
             "halo_us_per_exchange": halo_us, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,

@@ -240,6 +240,12 @@ int wl_meanflow_copy_to_flow(wl_sim* s);
  *      the reference); wl_sync waits for all queued device work.                               */
 int wl_sync(wl_sim* s);
 
+/* ---- measurement: how many 128x4x2-cell tiles of multigrid level `level` the last update! classified as
+ *      0 general (coefficients L, iD loaded), 1 body-free (the pressure kernels use the level's constants instead of
+ *      loading L / iD), 2 body-free next to a boundary or slab interface (constants with the boundary faces zeroed).
+ *      Same values either way: results do not depend on the classes.                */
+int wl_tile_classes(wl_sim* s, int32_t level, int64_t counts[3]);
+
 /* ---- counters for benchmarks: kernels launched by this sim since creation, and per-phase
  *      device time of the last step when enabled by wl_enable_timing.                         */
 int64_t wl_launch_count(const wl_sim* s);

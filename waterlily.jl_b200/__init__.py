@@ -35,7 +35,7 @@ ABI_SYMBOLS = [
     "wl_create", "wl_destroy", "wl_last_error", "wl_version", "wl_field_dims", "wl_download",
     "wl_upload", "wl_nlevels", "wl_finish_ic", "wl_bc_table_size", "wl_set_bc_tables", "wl_set_accel_field", "wl_measure_body", "wl_set_body_coeffs",
     "wl_build_poisson", "wl_update_poisson", "wl_solver", "wl_poisson_solver", "wl_mom_step", "wl_get_dt", "wl_set_dt",
-    "wl_cfl", "wl_cfl_noalloc", "wl_pressure_force", "wl_set_force_weights", "wl_pressure_force_weights", "wl_viscous_force", "wl_force_moment", "wl_measure_csg", "wl_pressure_force_csg",
+    "wl_cfl", "wl_cfl_noalloc", "wl_tile_classes", "wl_pressure_force", "wl_set_force_weights", "wl_pressure_force_weights", "wl_viscous_force", "wl_force_moment", "wl_measure_csg", "wl_pressure_force_csg",
     "wl_viscous_force_csg", "wl_force_moment_csg", "wl_meanflow_init", "wl_meanflow_update", "wl_meanflow_copy_to_flow", "wl_sync", "wl_launch_count", "wl_enable_timing",
     "wl_last_phase_times", "wl_debug_op", "wl_prof_begin", "wl_prof_end", "wl_event_record",
     "wl_event_elapsed_ms", "wl_create_slab", "wl_nccl_unique_id", "wl_slab_info", "wl_halo_stats", "wl_halo_transport", "wl_halo_timing",
@@ -122,6 +122,7 @@ def load_library(path=None):
     lib.wl_get_dt.argtypes = [P, FP]
     lib.wl_set_dt.argtypes = [P, F]
     lib.wl_cfl.argtypes = [P, FP]
+    lib.wl_tile_classes.argtypes = [P, I, C.POINTER(C.c_int64 * 3)]
     lib.wl_cfl_noalloc.argtypes = [P, I, C.POINTER(I * 3), F, P, P]     # device pointers and a cudaStream_t: plain addresses
     lib.wl_pressure_force.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3)]
     lib.wl_viscous_force.argtypes = [P, C.POINTER(WLBody), C.c_double, C.POINTER(C.c_double * 3)]
@@ -823,6 +824,12 @@ class Simulation:
         parts = [None] * self.nranks
         dist.all_gather_object(parts, a, group=group)
         return join_slabs(parts)
+
+    def tile_classes(self, level=0):
+        """(general, constants, constants + boundary) tile counts of a multigrid level (`wl_tile_classes`)."""
+        out = (C.c_int64 * 3)()
+        self._check(self.lib.wl_tile_classes(self.h, int(level), C.byref(out)))
+        return tuple(int(x) for x in out)
 
     def launch_count(self):
         return int(self.lib.wl_launch_count(self.h))

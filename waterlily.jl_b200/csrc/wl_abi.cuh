@@ -16,7 +16,11 @@ int build_levels(wl_sim* s) {
     Level& v = s->lv[l];
     free_field(v.L); free_field(v.x); free_field(v.z);
   }
-  for (auto& v : s->lv) { free_field(v.r); free_field(v.eps); free_field(v.Dg); free_field(v.iD); free_field(v.tmp); }
+  for (auto& v : s->lv) {
+    free_field(v.r); free_field(v.eps); free_field(v.Dg); free_field(v.iD); free_field(v.tmp);
+    if (v.ucore) cudaFree(v.ucore);
+    if (v.uflag) cudaFree(v.uflag);
+  }
   s->lv.clear();
   s->lv.reserve(s->cfg.maxlevels + 2);
   s->lv.emplace_back();
@@ -68,6 +72,11 @@ int build_levels(wl_sim* s) {
     }
     c.lay = make_lay(s->D, ng);
     c.owns = true;
+    for (int i = 0; i < 3; ++i) {                       // restrictL (MultiLevelPoisson.jl:20-26) of a body-free fine level
+      float v = f.lu[i];
+      for (int d = 0; d < s->D; ++d) if (d != i && c.c[d]) v = v + v;
+      c.lu[i] = (i < s->D && c.c[i]) ? v / 2.f : v;
+    }
     s->lv.push_back(c);
     Level& co = s->lv.back();
     if (int e = alloc_field(s, co.L, co.lay, s->D)) return e;
@@ -372,6 +381,8 @@ void wl_destroy(wl_sim* s) {
     Level& v = s->lv[l];
     if (v.owns) { free_field(v.L); free_field(v.x); free_field(v.z); }
     free_field(v.r); free_field(v.eps); free_field(v.Dg); free_field(v.iD); free_field(v.tmp);
+    if (v.ucore) cudaFree(v.ucore);
+    if (v.uflag) cudaFree(v.uflag);
   }
   free_field(s->u); free_field(s->u0); free_field(s->f); free_field(s->p);
   free_field(s->sigma); free_field(s->V); free_field(s->mu0); free_field(s->mu1); free_field(s->w);
@@ -453,6 +464,9 @@ static int xfer(wl_sim* s, int field, int level, float* host, size_t count, bool
   WL_CUDA(s, cudaStreamSynchronize(s->st));
   if (up && field == WL_MU1) { s->band_dirty = true; s->band_from_measure = false; }
   if (up && (field == WL_MU1 || field == WL_MU0 || field == WL_V)) s->free_flow = false;
+  // the uniform-coefficient tile flags describe L as of the last update!: a changed L switches them off until the next one
+  if (up && field == WL_MU0 && !s->lv.empty()) s->lv[0].uvalid = false;
+  if (up && (field == WL_L || field == WL_DIAG || field == WL_IDIAG) && level >= 0 && level < (int)s->lv.size()) s->lv[level].uvalid = false;
   return WL_OK;
 }
 int wl_download(wl_sim* s, int field, int level, float* host, size_t count) { return xfer(s, field, level, host, count, false); }
@@ -484,6 +498,7 @@ static int measure_impl(wl_sim* s, const B& body, double eps, const char* what) 
   }
   DISPATCH_DB(s, k_measure, B, grid_all(s->lay), blk(s->D), a);
   s->band_dirty = true; s->free_flow = false;
+  if (!s->lv.empty()) s->lv[0].uvalid = false;          // μ₀ ≡ L changed: flags come back with update!
   bc_vec(s, s->mu0, nullptr, false);
   bc_vec(s, s->V, nullptr, s->cfg.exitBC != 0);
   if (int e = halo(s, s->mu0, 1)) return e;
@@ -624,6 +639,21 @@ int wl_poisson_solver(wl_sim* s, int32_t itmx, int32_t* n_iter) {
   WL_CUDA(s, cudaStreamSynchronize(s->st));
   if (n_iter) *n_iter = n;
   return check_async(s, "wl_poisson_solver");
+}
+
+// pattern-tile classes of a level (TileFlags, wl_common.cuh): counts[c] = tiles of class c (0 general, 1 constants,
+// 2 constants with boundary faces); all zero when the level has no classes (2D, rows not a multiple of 4, invalidated)
+int wl_tile_classes(wl_sim* s, int32_t level, int64_t counts[3]) {
+  if (!s || !counts || level < 0 || level >= (int)s->lv.size()) return WL_ERR_INVALID;
+  counts[0] = counts[1] = counts[2] = 0;
+  const Level& p = s->lv[level];
+  if (!p.uvalid || !p.uflag) return WL_OK;
+  cudaSetDevice(s->device);
+  std::vector<unsigned char> h((size_t)p.unx * p.uny * p.unz);
+  WL_CUDA(s, cudaStreamSynchronize(s->st));
+  WL_CUDA(s, cudaMemcpy(h.data(), p.uflag, h.size(), cudaMemcpyDeviceToHost));
+  for (unsigned char c : h) counts[c < 3 ? c : 0]++;
+  return WL_OK;
 }
 
 int wl_get_dt(const wl_sim* s, float* dt) { if (!s || !dt) return WL_ERR_INVALID; *dt = s->dt; return WL_OK; }

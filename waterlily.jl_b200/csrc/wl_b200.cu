@@ -43,6 +43,10 @@ struct Level {
   Lay lay{};
   DevField L, x, z, r, eps, Dg, iD;
   DevField tmp;              // second ϵ buffer of the paired sweeps (K-GS2 cannot update ϵ in place)
+  unsigned char* ucore = nullptr; unsigned char* uflag = nullptr;   // pattern-tile classes (TileFlags, wl_common.cuh)
+  int unx = 0, uny = 0, unz = 0;
+  bool uvalid = false;       // classes match the level's current L (set by set_diag_h, cleared by uploads / measure!)
+  float lu[3] = {1.f, 1.f, 1.f};   // the level's body-free face coefficient per direction (restrictL of all-ones)
   bool owns = false;
   int c[3] = {0, 0, 0};
   // multi-GPU: a level is either DISTRIBUTED (each rank holds its slab; `per` marks the interfaces
@@ -426,11 +430,21 @@ int exitbc(wl_sim* s, DevField& u, DevField& u0, float dt) {
 }
 
 // ---------------------------------------------------------------- multigrid pieces
+TileFlags tile_flags(const Level& p) {
+  static const bool off = getenv("WL_NO_TILE_FLAGS") != nullptr;      // A/B switch: every tile takes the general path
+  TileFlags t{nullptr, 0, 0, {p.lu[0], p.lu[1], p.lu[2]}, 0.f};
+  float dg = 0.f;                                                    // set_diag! on an all-pattern interior cell
+  dg -= p.lu[0] + p.lu[0]; dg -= p.lu[1] + p.lu[1]; dg -= p.lu[2] + p.lu[2];
+  t.idu = dg == 0.f ? 0.f : 1.f / dg;
+  if (p.uvalid && p.uflag && !off) { t.f = p.uflag; t.nx = p.unx; t.ny = p.uny; }
+  return t;
+}
 LevArgs lev_args(wl_sim* s, Level& p) {
   LevArgs a{};
   a.l = p.lay; a.L = p.L.base; a.x = p.x.base; a.r = p.r.base; a.eps = p.eps.base; a.z = p.z.base;
   a.omega = 1.f; a.k0 = 0; a.w = s->redw; a.out = s->d_red; a.in = red_in(s, 0); a.want_norms = 0;
   a.ncells = p.ncells;
+  a.uf = tile_flags(p); a.per = p.per;
   return a;
 }
 void set_diag(wl_sim* s, Level& p) {
@@ -498,6 +512,23 @@ int restrictL(wl_sim* s, Level& fi, Level& co) {
 // set_diag! + the halo of iD that the fused kernels read at neighbour cells
 int set_diag_h(wl_sim* s, Level& p) {
   set_diag(s, p);
+  // pattern-tile classes of the level (its L, ghosts and slab halos included, is final here)
+  p.uvalid = false;
+  if (s->D == 3 && vec4_ok(p.lay)) {
+    const int nx = (p.lay.n0 - 2 + UT_X - 1) / UT_X, ny = (p.lay.n1 - 2 + UT_Y - 1) / UT_Y, nz = (p.lay.n2 - 2 + UT_Z - 1) / UT_Z;
+    if (!p.uflag || nx != p.unx || ny != p.uny || nz != p.unz) {
+      if (p.ucore) cudaFree(p.ucore);
+      if (p.uflag) cudaFree(p.uflag);
+      p.ucore = p.uflag = nullptr;
+      WL_CUDA(s, cudaMalloc(&p.ucore, (size_t)nx * ny * nz));
+      WL_CUDA(s, cudaMalloc(&p.uflag, (size_t)nx * ny * nz));
+      p.unx = nx; p.uny = ny; p.unz = nz;
+    }
+    TileArgs t{p.lay, p.L.base, p.ucore, p.uflag, nx, ny, nz, p.per, {p.lu[0], p.lu[1], p.lu[2]}};
+    LAUNCH(s, k_tile_core, dim3(nx, ny, nz), dim3(256), t);
+    LAUNCH(s, k_tile_class, dim3((unsigned)std::min((nx * ny * nz + 255) / 256, 1184)), dim3(256), t);
+    p.uvalid = true;
+  }
   if (p.dist) return halo(s, p.iD, 1);
   return WL_OK;
 }
@@ -518,6 +549,7 @@ LevDev levdev(const Level& p) {
   LevDev d{};
   d.l = p.lay; d.L = p.L.base; d.iD = p.iD.base; d.x = p.x.base; d.r = p.r.base; d.eps = p.eps.base;
   for (int q = 0; q < 3; ++q) d.c[q] = p.c[q];
+  d.uf = tile_flags(p);
   return d;
 }
 // the rank's window into a REPLICATED coarse level as seen from the DISTRIBUTED level above it:
@@ -1038,7 +1070,7 @@ int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
   if (!(s->cfg.flags & WL_FLAG_NO_FUSED)) {
     Level& p0 = s->lv[0];
     const float dt = w * s->dt;
-    DivResArgs d{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, p0.r.base, s->per, dt, s->redw, s->d_red + 0};
+    DivResArgs d{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, p0.r.base, s->per, dt, s->redw, s->d_red + 0, tile_flags(p0)};
     if (use_vec4(s->lay)) {
       const dim3 gq = grid_quads(s->lay);
       d.w.finish = finish_in_kernel(gq) ? 1 : 0;
@@ -1050,7 +1082,7 @@ int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
     std::swap(s->p, p0.eps); p0.x = s->p;                       // scaled x lives in the former ϵ buffer
     if (int e = mlp_solver(s, tr, true)) return e;
     if (int e = halo(s, p0.x, 1)) return e;                     // the solver's final perBC!(x) across slabs
-    ProjArgs2 q{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, s->per, dt};
+    ProjArgs2 q{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, s->per, dt, tile_flags(p0)};
     if (use_vec4(s->lay)) LAUNCH(s, k_proj4, grid_quads(s->lay), dim3(32, 4, 2), q);
     else DISPATCH_D(s, k_proj, grid_inside(s->lay), blk(s->D), q);
     std::swap(s->p, p0.eps); p0.x = s->p;                       // (K-PROJ also wrote p's interface ghost planes)

@@ -61,6 +61,28 @@ inline Lay make_lay(int D, const int* ng, int zpad = 0) {
 struct Per { int p[3]; int zlo, zhi; int kz0; };
 struct Vec3 { float v[3]; };
 
+// Pattern tiles (pressure side).  Away from bodies the face coefficients L of a level follow a pattern known without
+// reading them: L_d = lu[d] (1 on the finest level, the restricted constant 2^k... on coarser ones), except 0 on the faces
+// of a physical non-periodic boundary (BC!(L,0): indices 0, 1 and N-1 of the normal component, core.jl:208-212); then
+// iD = 1/-(sum of the six faces).  The pressure kernels would otherwise re-read those values from HBM in every pass
+// (12-20 of their 24-36 B/cell).  update!/build classify each 128x4x2-cell tile (= one block of the 4-cells-per-thread
+// kernels): every cell of the tile AND of its neighbouring tiles matches the pattern -> class 1 (no boundary, no slab
+// interface next to the tile: all values are the constants lu / idu) or class 2 (boundary or interface tile: L is
+// synthesised with index compares, iD of neighbour cells is still loaded); else class 0 (general path, loads).
+// Same values, same operations: bit-identical.  f == nullptr: no classes for this level (2D, rows not a multiple of 4,
+// switched off by an upload until the next update!).
+struct TileFlags { const unsigned char* f; int nx, ny; float lu[3]; float idu; };
+constexpr int UT_X = 128, UT_Y = 4, UT_Z = 2;
+__device__ __forceinline__ int tile_class(const TileFlags& t, int tx, int ty, int tz) {
+  return t.f == nullptr ? 0 : t.f[tx + t.nx * (ty + t.ny * tz)];
+}
+// is index c of direction d a face the boundary pattern zeroes (normal component only)?
+__device__ __forceinline__ bool pattern_zero(const Per& per, int d, int c, int n) {
+  if (per.p[d]) return false;
+  const bool lo_phys = !(d == 2 && per.zlo), hi_phys = !(d == 2 && per.zhi);
+  return (lo_phys && c <= 1) || (hi_phys && c == n - 1);
+}
+
 // ---- deterministic block reduction helpers (warp shuffle -> smem -> thread 0)
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll

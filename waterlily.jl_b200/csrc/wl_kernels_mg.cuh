@@ -21,6 +21,8 @@ struct LevArgs {
   RedIn in;          // residual sum input (k_shift_norms)
   long long ncells;  // interior cells of the GLOBAL level (mean of the residual)
   int want_norms;
+  TileFlags uf;      // pattern tiles (k_gs_half_c, k_gs_half_cx)
+  Per per;           // ... and the level's boundary kinds, for their class-2 path
 };
 
 #define WL_INTERIOR_IJK(D, l)                                                   \
@@ -205,10 +207,17 @@ __global__ void __launch_bounds__(256) k_gs_half_c(const LevArgs a) {
   const int st[3] = {1, l.pitch, l.plane};
   float lo[3], hi[3], em[3], ep[3];
   const float r0 = a.r[o];
+  // a block covers 64 x 4 x 2 cells: half a tile in x.  Pattern tiles: the coefficients are known without loading them
+  const int cls = D == 3 ? tile_class(a.uf, blockIdx.x >> 1, blockIdx.y, blockIdx.z) : 0;
+  const int c3[3] = {i, j, k}, N3[3] = {l.n0, l.n1, l.n2};
 #pragma unroll
   for (int q = 0; q < D; ++q) {                      // every load before the first use: one memory round trip
     const float* Lq = a.L + l.cstride * q;
-    lo[q] = Lq[o]; hi[q] = Lq[o + st[q]];
+    if (cls == 1) { lo[q] = a.uf.lu[q]; hi[q] = a.uf.lu[q]; }
+    else if (cls == 2) {
+      lo[q] = pattern_zero(a.per, q, c3[q], N3[q]) ? 0.f : a.uf.lu[q];
+      hi[q] = pattern_zero(a.per, q, c3[q] + 1, N3[q]) ? 0.f : a.uf.lu[q];
+    } else { lo[q] = Lq[o]; hi[q] = Lq[o + st[q]]; }
     em[q] = a.eps[o - st[q]]; ep[q] = a.eps[o + st[q]];
   }
   float s = r0, dg = 0.f;
@@ -218,6 +227,70 @@ __global__ void __launch_bounds__(256) k_gs_half_c(const LevArgs a) {
     s -= em[q] * lo[q] + ep[q] * hi[q];
   }
   a.eps[o] = s * inv_or_zero(dg);
+}
+
+// ---- pattern-tile classification (see TileFlags in wl_common.cuh).  Stage 1: core[t] = every cell of tile t -- its
+// interior cells, plus the ghost / halo row, column or plane next to a tile at the end of a direction, which the
+// kernels read as upper faces -- holds the pattern value in all three components.  Stage 2: class[t] = 0 unless t and
+// its 26 neighbours (wrapped across periodic directions, absent beyond the end of the others) are all core tiles;
+// then 2 if the tile touches the end of a non-periodic direction (physical boundary or slab interface), else 1.
+struct TileArgs { Lay l; const float* L; unsigned char* core; unsigned char* cls; int nx, ny, nz; Per per; float lu[3]; };
+__global__ void __launch_bounds__(256) k_tile_core(const TileArgs a) {
+  pdl_entry();
+  const Lay& l = a.l;
+  const int N[3] = {l.n0, l.n1, l.n2};
+  const int t3[3] = {(int)blockIdx.x, (int)blockIdx.y, (int)blockIdx.z}, nt[3] = {a.nx, a.ny, a.nz}, ts[3] = {UT_X, UT_Y, UT_Z};
+  int lo[3], hi[3];                                    // index range of the tile, widened to the UPPER ghost at the end of a
+#pragma unroll                                         // direction (read as the upper face of the last cell; nothing reads a
+  for (int d = 0; d < 3; ++d) {                        // lower ghost or a ghost's tangential components)
+    lo[d] = 1 + ts[d] * t3[d]; hi[d] = min(lo[d] + ts[d] - 1, N[d] - 2);
+    if (t3[d] == nt[d] - 1) hi[d] = N[d] - 1;
+  }
+  const int ex = hi[0] - lo[0] + 1, ey = hi[1] - lo[1] + 1, ez = hi[2] - lo[2] + 1;
+  int bad = 0;
+  for (int q = threadIdx.x; q < ex * ey * ez; q += blockDim.x) {
+    const int c[3] = {lo[0] + q % ex, lo[1] + (q / ex) % ey, lo[2] + q / (ex * ey)};
+    const int o = l.off(c[0], c[1], c[2]);
+    int ng = 0, g = -1;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) if (c[d] == N[d] - 1) { ++ng; g = d; }
+    if (ng > 1) continue;                              // edges and corners of the array: never read
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      if (ng == 1 && d != g) continue;                 // upper ghost: only its normal component is an upper face
+      const float want = pattern_zero(a.per, d, c[d], N[d]) ? 0.f : a.lu[d];
+      bad |= a.L[l.cstride * d + o] != want;
+    }
+  }
+  bad = __syncthreads_or(bad);
+  if (threadIdx.x == 0) a.core[blockIdx.x + a.nx * (blockIdx.y + a.ny * blockIdx.z)] = bad ? 0 : 1;
+}
+__global__ void __launch_bounds__(256) k_tile_class(const TileArgs a) {
+  pdl_entry();
+  const int nt = a.nx * a.ny * a.nz;
+  const int n[3] = {a.nx, a.ny, a.nz};
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < nt; t += gridDim.x * blockDim.x) {
+    const int c[3] = {t % a.nx, (t / a.nx) % a.ny, t / (a.nx * a.ny)};
+    int ok = 1, edge = 0;
+    // (the last TWO tiles of a direction: a partial last tile can be one cell thick, and then the tile before it has a
+    //  boundary-adjacent cell -- whose iD is not the constant -- as its neighbour)
+#pragma unroll
+    for (int d = 0; d < 3; ++d) edge |= !a.per.p[d] && (c[d] == 0 || c[d] >= n[d] - 2);
+    for (int dz = -1; dz <= 1 && ok; ++dz)
+      for (int dy = -1; dy <= 1 && ok; ++dy)
+        for (int dx = -1; dx <= 1 && ok; ++dx) {
+          int q[3] = {c[0] + dx, c[1] + dy, c[2] + dz};
+          bool absent = false;
+#pragma unroll
+          for (int d = 0; d < 3; ++d) {
+            if (q[d] < 0 || q[d] >= n[d]) {
+              if (a.per.p[d]) q[d] = q[d] < 0 ? n[d] - 1 : 0; else absent = true;
+            }
+          }
+          if (!absent) ok = a.core[q[0] + a.nx * (q[1] + a.ny * q[2])];
+        }
+    a.cls[t] = (unsigned char)(ok ? (edge ? 2 : 1) : 0);
+  }
 }
 
 // The half sweep with the slab-interface exchange FUSED in (multi-GPU, peer-mapped arenas; host side in
@@ -258,10 +331,16 @@ __global__ void __launch_bounds__(256) k_gs_half_cx(const LevArgs a, const GsLin
     const int st[3] = {1, l.pitch, l.plane};
     float lo[3], hi[3], em[3], ep[3];
     const float r0 = a.r[o];
+    const int cls = tile_class(a.uf, blockIdx.x >> 1, blockIdx.y, zb);
+    const int c3[3] = {i, j, k}, N3[3] = {l.n0, l.n1, l.n2};
 #pragma unroll
     for (int q = 0; q < D; ++q) {
       const float* Lq = a.L + l.cstride * q;
-      lo[q] = Lq[o]; hi[q] = Lq[o + st[q]];
+      if (cls == 1) { lo[q] = a.uf.lu[q]; hi[q] = a.uf.lu[q]; }
+      else if (cls == 2) {
+        lo[q] = pattern_zero(a.per, q, c3[q], N3[q]) ? 0.f : a.uf.lu[q];
+        hi[q] = pattern_zero(a.per, q, c3[q] + 1, N3[q]) ? 0.f : a.uf.lu[q];
+      } else { lo[q] = Lq[o]; hi[q] = Lq[o + st[q]]; }
       em[q] = a.eps[o - st[q]]; ep[q] = a.eps[o + st[q]];
     }
     float s = r0, dg = 0.f;

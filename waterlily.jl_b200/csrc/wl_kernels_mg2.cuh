@@ -26,6 +26,7 @@ struct LevDev {
   float* r;
   float* eps;
   int c[3];          // coarsening mask from the next finer level to this one
+  TileFlags uf;      // uniform-coefficient tiles of this level (4-cells-per-thread kernels)
 };
 
 // offsets of the lower/upper neighbour in direction d for an INTERIOR cell, wrapped when periodic.
@@ -124,7 +125,7 @@ __device__ __forceinline__ float multA_w(const Lay& l, const float* __restrict__
 // pointers) because neighbours still read the unscaled x.  Non-periodic ghosts of every scalar work
 // array are zero for the whole run, periodic ghosts are rewritten by whoever needs them, so the
 // buffers are interchangeable.
-struct DivResArgs { Lay l; const float* u; const float* x; float* xs; const float* L; float* r; Per per; float dt; RedWork w; Red* out; };
+struct DivResArgs { Lay l; const float* u; const float* x; float* xs; const float* L; float* r; Per per; float dt; RedWork w; Red* out; TileFlags uf; };
 template <int D>
 __global__ void __launch_bounds__(256) k_divres(const DivResArgs a) {
   pdl_entry();
@@ -397,7 +398,7 @@ __global__ void __launch_bounds__(256) k_increment_w(const SmArgs a) {
 // ---------------------------------------------------------------- K-PROJ
 // u[I,i] -= L[I,i]·(x[I]-x[I-δᵢ]) for all i (after the solver's final perBC!(x): wrap-read), and the
 // unscaled pressure p = x/dt with its periodic images, written to the spare buffer (host swaps).
-struct ProjArgs2 { Lay l; float* u; const float* x; float* pn; const float* L; Per per; float dt; };
+struct ProjArgs2 { Lay l; float* u; const float* x; float* pn; const float* L; Per per; float dt; TileFlags uf; };
 template <int D>
 __global__ void __launch_bounds__(256) k_proj(const ProjArgs2 a) {
   pdl_entry();

@@ -11,6 +11,8 @@
 // multiples of 32 floats, so a thread whose first cell is i = 1+4m loads aligned float4s.  The
 // kernels require (n0-2) % 4 == 0; other levels use the scalar kernels.
 #pragma once
+#include <type_traits>
+
 #include "wl_kernels_mg2.cuh"
 
 // resident blocks per SM the register allocation is held to.  K-UP fits 64 registers without spilling (50 %
@@ -38,6 +40,48 @@ __device__ __forceinline__ F4 ld4(const float* p) {            // data other thr
 __device__ __forceinline__ void st4(float* p, const F4& a) {
   *reinterpret_cast<float4*>(p) = make_float4(a.v[0], a.v[1], a.v[2], a.v[3]);
 }
+// ---- face coefficients of a quad by tile class (TileFlags, wl_common.cuh): 0 loaded, 1 the level's constants, 2 the
+// constants with the boundary faces zeroed by index compares.  ly*/lz* are the same for the quad's four cells in
+// classes 1 and 2, so the compiler keeps scalars there.
+struct QuadL { F4 lx, ly0, ly1, lz0, lz1; float lx4; };
+template <int CLS>
+__device__ __forceinline__ QuadL quad_coeffs(const float* L, const Lay& l, const Per& per, const TileFlags& t, int o, int i, int j, int k) {
+  QuadL q;
+  if (CLS == 0) {
+    const float* Lx = L; const float* Ly = L + l.cstride; const float* Lz = L + 2 * l.cstride;
+    q.lx = ld4g(Lx + o); q.lx4 = __ldg(Lx + o + 4);
+    q.ly0 = ld4g(Ly + o); q.ly1 = ld4g(Ly + o + l.pitch); q.lz0 = ld4g(Lz + o); q.lz1 = ld4g(Lz + o + l.plane);
+  } else {
+    auto f = [&](int d, int c, int n) { return (CLS == 2 && pattern_zero(per, d, c, n)) ? 0.f : t.lu[d]; };
+#pragma unroll
+    for (int c = 0; c < 4; ++c) q.lx.v[c] = f(0, i + c, l.n0);
+    q.lx4 = f(0, i + 4, l.n0);
+    const float a0 = f(1, j, l.n1), a1 = f(1, j + 1, l.n1), b0 = f(2, k, l.n2), b1 = f(2, k + 1, l.n2);
+    q.ly0 = F4{{a0, a0, a0, a0}}; q.ly1 = F4{{a1, a1, a1, a1}}; q.lz0 = F4{{b0, b0, b0, b0}}; q.lz1 = F4{{b1, b1, b1, b1}};
+  }
+  return q;
+}
+// iD of the quad's own cells: loaded, the level's constant, or inv_or_zero(diag) of the synthesised faces (set_diag!'s
+// own expression, Poisson.jl:43-55: the same operands in the same order, so the same bits as the stored value)
+template <int CLS>
+__device__ __forceinline__ F4 quad_iD(const float* iD, const QuadL& q, const TileFlags& t, int o) {
+  if (CLS == 0) return ld4g(iD + o);
+  if (CLS == 1) return F4{{t.idu, t.idu, t.idu, t.idu}};
+  F4 d;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    float dg = 0.f;
+    dg -= q.lx.v[c] + (c < 3 ? q.lx.v[c < 3 ? c + 1 : 3] : q.lx4); dg -= q.ly0.v[c] + q.ly1.v[c]; dg -= q.lz0.v[c] + q.lz1.v[c];
+    d.v[c] = inv_or_zero(dg);
+  }
+  return d;
+}
+#define WL_CLASS_DISPATCH(cls, body)                                              \
+  do {                                                                            \
+    if ((cls) == 1) body(std::integral_constant<int, 1>{});                       \
+    else if ((cls) == 2) body(std::integral_constant<int, 2>{});                  \
+    else body(std::integral_constant<int, 0>{});                                  \
+  } while (0)
 inline bool vec4_ok(const Lay& l) { return l.D == 3 && (l.n0 - 2) % 4 == 0 && l.n0 - 2 >= 8; }
 
 // thread -> first cell of its quad; blockDim = (32,4,2) covers 128 x 4 x 2 cells
@@ -76,13 +120,13 @@ __global__ void __launch_bounds__(256) k_incr4(const SmArgs a) {
   }
   WL_QUAD_FROM_BLOCK(l)
   double s1 = 0.0; float m = -INFINITY;
-  if (inb) {
+  auto body = [&](auto tag) {
+    constexpr int CLS = decltype(tag)::value;
     const int o = l.off(i, j, k);
     int oxm, oxp, oym, oyp, ozm, ozp;
     quad_nbr(l, a.per, i, j, k, oxm, oxp, oym, oyp, ozm, ozp);
-    const float* Lx = a.p.L; const float* Ly = a.p.L + l.cstride; const float* Lz = a.p.L + 2 * l.cstride;
-    const F4 lx = ld4g(Lx + o); const float lx4 = __ldg(Lx + o + 4);
-    const F4 ly0 = ld4g(Ly + o), ly1 = ld4g(Ly + o + l.pitch), lz0 = ld4g(Lz + o), lz1 = ld4g(Lz + o + l.plane);
+    const QuadL ql = quad_coeffs<CLS>(a.p.L, l, a.per, a.p.uf, o, i, j, k);
+    const F4 &lx = ql.lx, &ly0 = ql.ly0, &ly1 = ql.ly1, &lz0 = ql.lz0, &lz1 = ql.lz1; const float lx4 = ql.lx4;
     const F4 e = ld4(a.p.eps + o), eym = ld4(a.p.eps + o + oym), eyp = ld4(a.p.eps + o + oyp),
              ezm = ld4(a.p.eps + o + ozm), ezp = ld4(a.p.eps + o + ozp);
     const float exm = a.p.eps[o + oxm], exp_ = a.p.eps[o + oxp];
@@ -105,7 +149,8 @@ __global__ void __launch_bounds__(256) k_incr4(const SmArgs a) {
     }
     st4(a.p.r + o, rn);
     st4(a.p.x + o, xn);
-  }
+  };
+  if (inb) WL_CLASS_DISPATCH(tile_class(a.p.uf, blockIdx.x, blockIdx.y, blockIdx.z), body);
   if (a.want_norms) { if (a.w.finish) block_reduce_finish(s1, m, a.w, a.out); else block_reduce_partial(s1, m, a.w); }
 }
 
@@ -161,16 +206,16 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_divres4(const DivResArgs
   const Lay& l = a.l;
   WL_QUAD_FROM_BLOCK(l)
   double s = 0.0;
-  if (inb) {
+  auto body = [&](auto tag) {
+    constexpr int CLS = decltype(tag)::value;
     const int o = l.off(i, j, k);
     int oxm, oxp, oym, oyp, ozm, ozp;
     quad_nbr(l, a.per, i, j, k, oxm, oxp, oym, oyp, ozm, ozp);
     const float* ux = a.u; const float* uy = a.u + l.cstride; const float* uz = a.u + 2 * l.cstride;
-    const float* Lx = a.L; const float* Ly = a.L + l.cstride; const float* Lz = a.L + 2 * l.cstride;
     const F4 u0 = ld4g(ux + o); const float u04 = __ldg(ux + o + 4);
     const F4 v0 = ld4g(uy + o), v1 = ld4g(uy + o + l.pitch), w0 = ld4g(uz + o), w1 = ld4g(uz + o + l.plane);
-    const F4 lx = ld4g(Lx + o); const float lx4 = __ldg(Lx + o + 4);
-    const F4 ly0 = ld4g(Ly + o), ly1 = ld4g(Ly + o + l.pitch), lz0 = ld4g(Lz + o), lz1 = ld4g(Lz + o + l.plane);
+    const QuadL ql = quad_coeffs<CLS>(a.L, l, a.per, a.uf, o, i, j, k);
+    const F4 &lx = ql.lx, &ly0 = ql.ly0, &ly1 = ql.ly1, &lz0 = ql.lz0, &lz1 = ql.lz1; const float lx4 = ql.lx4;
     const F4 x = ld4g(a.x + o), xym = ld4g(a.x + o + oym), xyp = ld4g(a.x + o + oyp),
              xzm = ld4g(a.x + o + ozm), xzp = ld4g(a.x + o + ozp);
     const float xxm = __ldg(a.x + o + oxm), xxp = __ldg(a.x + o + oxp);
@@ -197,7 +242,8 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_divres4(const DivResArgs
     }
     st4(a.r + o, rr);
     st4(a.xs + o, xs);
-  }
+  };
+  if (inb) WL_CLASS_DISPATCH(tile_class(a.uf, blockIdx.x, blockIdx.y, blockIdx.z), body);
   if (a.w.finish) block_reduce_finish(s, -INFINITY, a.w, a.out);
   else block_reduce_partial(s, -INFINITY, a.w);
 }
@@ -215,7 +261,16 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_proj4(const ProjArgs2 a)
   const float xxm = __ldg(a.x + o + oxm);
   float* ux = a.u; float* uy = a.u + l.cstride; float* uz = a.u + 2 * l.cstride;
   const F4 u0 = ld4(ux + o), v0 = ld4(uy + o), w0 = ld4(uz + o);
-  const F4 lx = ld4g(a.L + o), ly = ld4g(a.L + l.cstride + o), lz = ld4g(a.L + 2 * l.cstride + o);
+  F4 lx, ly, lz;                                        // lower faces only (Flow.jl:228)
+  const int cls = tile_class(a.uf, blockIdx.x, blockIdx.y, blockIdx.z);
+  if (cls == 0) { lx = ld4g(a.L + o); ly = ld4g(a.L + l.cstride + o); lz = ld4g(a.L + 2 * l.cstride + o); }
+  else {
+    auto f = [&](int d, int c, int n) { return (cls == 2 && pattern_zero(a.per, d, c, n)) ? 0.f : a.uf.lu[d]; };
+#pragma unroll
+    for (int c = 0; c < 4; ++c) lx.v[c] = f(0, i + c, l.n0);
+    const float a0 = f(1, j, l.n1), b0 = f(2, k, l.n2);
+    ly = F4{{a0, a0, a0, a0}}; lz = F4{{b0, b0, b0, b0}};
+  }
   F4 un, vn, wn, pn;
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
@@ -275,12 +330,13 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_up4(const UpArgs a) {
   const F4 e = row(cj, ck), eym = row(dn(cy, jm), ck), eyp = row(dn(cy, jp), ck), ezm = row(cj, dn(cz, km)), ezp = row(cj, dn(cz, kp));
   const float* pc = a.c.x + lc.pitch * cj + lc.plane * ck;
   const float exm = __ldg(pc + dn(cx, im)), exp_ = __ldg(pc + dn(cx, ip));
-  const float* Lx = a.f.L; const float* Ly = a.f.L + l.cstride; const float* Lz = a.f.L + 2 * l.cstride;
-  const F4 lx = ld4g(Lx + o); const float lx4 = __ldg(Lx + o + 4);
-  const F4 ly0 = ld4g(Ly + o), ly1 = ld4g(Ly + o + l.pitch), lz0 = ld4g(Lz + o), lz1 = ld4g(Lz + o + l.plane);
+  auto body = [&](auto tag) {
+  constexpr int CLS = decltype(tag)::value;
+  const QuadL ql = quad_coeffs<CLS>(a.f.L, l, a.per, a.f.uf, o, i, j, k);
+  const F4 &lx = ql.lx, &ly0 = ql.ly0, &ly1 = ql.ly1, &lz0 = ql.lz0, &lz1 = ql.lz1; const float lx4 = ql.lx4;
   const F4 r0 = ld4(a.f.r + o), x0 = ld4(a.f.x + o);
   F4 d0{{0.f, 0.f, 0.f, 0.f}};
-  if (a.write_eps) d0 = ld4g(a.f.iD + o);
+  if (a.write_eps) d0 = quad_iD<CLS>(a.f.iD, ql, a.f.uf, o);
   F4 rn, xn, en;
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
@@ -308,6 +364,8 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_up4(const UpArgs a) {
       for (int q = 0; q < 4; ++q) store_images<3>(a.f.eps, l, a.per, i + q, j, k, en.v[q]);
     }
   }
+  };
+  WL_CLASS_DISPATCH(tile_class(a.f.uf, blockIdx.x, blockIdx.y, blockIdx.z), body);
 }
 
 // ---------------------------------------------------------------- K-DOWN, 4 cells per thread (see k_down)
@@ -326,19 +384,25 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_down4(const DownArgs a) 
     if (fabsf(mean) > 2.f * 1.1920929e-07f) sh = mean;
   }
   F4 rn{{0.f, 0.f, 0.f, 0.f}};
-  if (inb) {
+  auto body = [&](auto tag) {
+    constexpr int CLS = decltype(tag)::value;
     const int o = l.off(i, j, k);
     int oxm, oxp, oym, oyp, ozm, ozp;
     quad_nbr(l, a.per, i, j, k, oxm, oxp, oym, oyp, ozm, ozp);
-    const float* Lx = a.f.L; const float* Ly = a.f.L + l.cstride; const float* Lz = a.f.L + 2 * l.cstride;
-    const F4 lx = ld4g(Lx + o); const float lx4 = __ldg(Lx + o + 4);
-    const F4 ly0 = ld4g(Ly + o), ly1 = ld4g(Ly + o + l.pitch), lz0 = ld4g(Lz + o), lz1 = ld4g(Lz + o + l.plane);
+    const QuadL ql = quad_coeffs<CLS>(a.f.L, l, a.per, a.f.uf, o, i, j, k);
+    const F4 &lx = ql.lx, &ly0 = ql.ly0, &ly1 = ql.ly1, &lz0 = ql.lz0, &lz1 = ql.lz1; const float lx4 = ql.lx4;
     F4 r = ld4g(a.f.r + o), rym = ld4g(a.f.r + o + oym), ryp = ld4g(a.f.r + o + oyp), rzm = ld4g(a.f.r + o + ozm),
        rzp = ld4g(a.f.r + o + ozp);
     float rxm = __ldg(a.f.r + o + oxm), rxp = __ldg(a.f.r + o + oxp);
-    const F4 d = ld4g(a.f.iD + o), dym = ld4g(a.f.iD + o + oym), dyp = ld4g(a.f.iD + o + oyp), dzm = ld4g(a.f.iD + o + ozm),
-             dzp = ld4g(a.f.iD + o + ozp);
-    const float dxm = __ldg(a.f.iD + o + oxm), dxp = __ldg(a.f.iD + o + oxp);
+    // iD of the quad and of its six neighbours: class 1 -- the tile AND its neighbouring tiles hold the constants and no
+    // boundary is near, so every one of them is idu; class 2 (boundary / interface tiles) loads the neighbours' values
+    const F4 d = quad_iD<CLS>(a.f.iD, ql, a.f.uf, o);
+    F4 dym = d, dyp = d, dzm = d, dzp = d;
+    float dxm = d.v[0], dxp = d.v[0];
+    if (CLS != 1) {
+      dym = ld4g(a.f.iD + o + oym); dyp = ld4g(a.f.iD + o + oyp); dzm = ld4g(a.f.iD + o + ozm); dzp = ld4g(a.f.iD + o + ozp);
+      dxm = __ldg(a.f.iD + o + oxm); dxp = __ldg(a.f.iD + o + oxp);
+    }
     const F4 x0 = ld4(a.f.x + o);
     if (sh != 0.f) {
       // ghost neighbours of non-periodic directions are not shifted by the reference, but their iD and
@@ -368,7 +432,8 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_down4(const DownArgs a) 
     }
     st4(a.f.eps + o, rn);          // neighbours still read r: the new residual is staged in ϵ (host swaps the pointers)
     st4(a.f.x + o, xn);
-  }
+  };
+  if (inb) WL_CLASS_DISPATCH(tile_class(a.f.uf, blockIdx.x, blockIdx.y, blockIdx.z), body);
   {
     float* t = &tile[threadIdx.z][threadIdx.y][4 * threadIdx.x];
     t[0] = rn.v[0]; t[1] = rn.v[1]; t[2] = rn.v[2]; t[3] = rn.v[3];
