@@ -516,6 +516,13 @@ def main():
             ksum = sum(ms for _, ms in allp.values())
             for name, (n, ms) in sorted(allp.items(), key=lambda kv: -kv[1][1]):
                 f.write(f"{name}\t{n}\t{ms:.4f}\t{ms / n * 1e3:.2f}\t{ms / ksum:.3f}\t{blocks.get(name, 0)}\n")
+            sim.prof_begin("@")                      # one more step, one line per (kernel, grid size) = per multigrid level
+            sim.sim_step(remeasure=remeasure)
+            lev = sim.prof_end()
+            f.write("# one step, per (kernel, blocks per launch): the multigrid levels apart\n")
+            f.write("kernel@blocks\tlaunches\ttotal_ms\tavg_us\n")
+            for name, (n, ms) in sorted(lev.items(), key=lambda kv: -kv[1][1]):
+                f.write(f"{name}\t{n}\t{ms:.4f}\t{ms / n * 1e3:.2f}\n")
 
     tiles = sim.tile_classes(0) if D == 3 else (0, 0, 0)
     halo = sim.halo_stats()

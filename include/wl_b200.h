@@ -255,7 +255,8 @@ int wl_last_phase_times(const wl_sim* s, double out[8]);
 
 /* ---- measurement hooks (bench.py): per-kernel CUDA-event timing on the launching stream.
  *      wl_prof_begin(filter): time every kernel whose name contains `filter` ("" = all) until
- *      wl_prof_end, which writes "<kernel>\t<launches>\t<total_ms>\t<total_blocks>\n" lines into buf.
+ *      wl_prof_end, which writes "<kernel>\t<launches>\t<total_ms>\t<total_blocks>\n" lines into buf.  A filter that starts
+ *      with '@' ("@", "@k_down") reports one line per (kernel, grid size) as "<kernel>@<blocks>", i.e. per multigrid level.
  *      wl_event_record / wl_event_elapsed_ms: events on the sim's own stream, slots 0..7.      */
 int wl_prof_begin(wl_sim* s, const char* filter);
 int wl_prof_end(wl_sim* s, char* buf, size_t buflen);

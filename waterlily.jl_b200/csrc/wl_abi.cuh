@@ -674,12 +674,12 @@ int wl_mom_step(wl_sim* s, const float* uBC_t1, const float* acc0, const float* 
   const float* U = uBC_t1 ? uBC_t1 : s->cfg.uBC;
   const bool ex = s->cfg.exitBC != 0;
   Trace tr[2];
-  const bool fused = s->D == 3 && !(s->cfg.flags & WL_FLAG_NO_FUSED) && !s->accf_on;
+  const bool fused = s->D == 3 && !(s->cfg.flags & WL_FLAG_NO_FUSED);
   if (fused && s->band_dirty) { if (int e = band_rebuild(s)) return e; }
   if (s->timing) cudaEventRecord(s->ev[0], s->st);
   if (fused) {
     // predictor: u⁰ .= u is a buffer rotation; K-MOM writes the new u into the work buffer
-    mom3(s, s->u, s->u, s->w, 0, acc0);
+    mom3(s, s->u, s->u, s->w, 0, acc0, s->accf_on ? s->accf[0].base : nullptr);
     DevField old0 = s->u0; s->u0 = s->u; s->u = s->w; s->w = old0;
   } else {
     WL_CUDA(s, cudaMemcpyAsync(s->u0.alloc, s->u.alloc, s->u.bytes, cudaMemcpyDeviceToDevice, s->st));   // u⁰ .= u
@@ -697,7 +697,7 @@ int wl_mom_step(wl_sim* s, const float* uBC_t1, const float* acc0, const float* 
   // corrector
   ghost_phi(s);
   if (fused) {
-    mom3(s, s->u, s->u0, s->w, 1, acc1);
+    mom3(s, s->u, s->u0, s->w, 1, acc1, s->accf_on ? s->accf[1].base : nullptr);
     DevField t = s->u; s->u = s->w; s->w = t;
   } else {
     mom_rhs(s, s->u, acc1, s->accf_on ? s->accf[1].base : nullptr);
@@ -905,7 +905,8 @@ int wl_debug_op(wl_sim* s, int op, int level, float arg) {
 int wl_prof_begin(wl_sim* s, const char* filter) {
   if (!s) return WL_ERR_INVALID;
   s->prof_on = true;
-  s->prof_filter = filter ? filter : "";
+  s->prof_split = filter && filter[0] == '@';                  // "@…": one line per (kernel, grid size), i.e. per multigrid level
+  s->prof_filter = filter ? filter + (s->prof_split ? 1 : 0) : "";
   return WL_OK;
 }
 // Writes one line per kernel: "<name>\t<launches>\t<total_ms>\t<total_blocks>\n"; returns the number of kernels.
@@ -921,14 +922,19 @@ int wl_prof_end(wl_sim* s, char* buf, size_t buflen) {
     cudaEventElapsedTime(&ms, r.a, r.b);
     s->evpool.push_back(r.a); s->evpool.push_back(r.b);
     size_t i = 0;
-    for (; i < acc.size(); ++i) if (acc[i].name == r.name || !strcmp(acc[i].name, r.name)) break;
+    for (; i < acc.size(); ++i)
+      if ((acc[i].name == r.name || !strcmp(acc[i].name, r.name)) && (!s->prof_split || acc[i].blocks == r.blocks * acc[i].n)) break;
     if (i == acc.size()) acc.push_back({r.name, 0, 0.0, 0});
     acc[i].n++; acc[i].ms += ms; acc[i].blocks += r.blocks;
   }
   s->recs.clear();
   std::string out;
   char line[256];
-  for (auto& a : acc) { snprintf(line, sizeof line, "%s\t%ld\t%.6f\t%lld\n", a.name, a.n, a.ms, a.blocks); out += line; }
+  for (auto& a : acc) {
+    if (s->prof_split) snprintf(line, sizeof line, "%s@%lld\t%ld\t%.6f\t%lld\n", a.name, a.blocks / a.n, a.n, a.ms, a.blocks);
+    else snprintf(line, sizeof line, "%s\t%ld\t%.6f\t%lld\n", a.name, a.n, a.ms, a.blocks);
+    out += line;
+  }
   if (buf && buflen) { strncpy(buf, out.c_str(), buflen - 1); buf[buflen - 1] = 0; }
   return (int)acc.size();
 }

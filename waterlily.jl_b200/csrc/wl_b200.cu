@@ -131,7 +131,7 @@ struct wl_sim {
   double phase_s[8] = {};
   int status = WL_OK;
   // profiling hooks
-  bool prof_on = false;
+  bool prof_on = false, prof_split = false;
   std::string prof_filter;
   std::vector<cudaEvent_t> evpool;
   std::vector<ProfRec> recs;
@@ -591,7 +591,7 @@ dim3 grid_quads(const Lay& l, int cells_per_thread = 4) {
 inline bool finish_in_kernel(const dim3&) { return false; }
 void fold_partials_to(wl_sim* s, const dim3& g, Red* out) {
   FoldArgs fa{s->redw, (int)(g.x * g.y * g.z), out};
-  LAUNCH(s, k_fold_partials, dim3(1), dim3(1024), fa);
+  LAUNCH(s, k_fold_partials, dim3((unsigned)((fa.n + FOLD_CHUNK - 1) / FOLD_CHUNK)), dim3(1024), fa);
 }
 
 // K-GS2 (wl_kernels_gs2.cuh): the four colour sweeps as two passes.  Single-GPU levels that the 4-cells-per-thread
@@ -985,7 +985,7 @@ const CUtensorMap* tensor_map(wl_sim* s, const DevField& f, int box_x, int box_y
   return &(s->tmaps[key] = tm);
 }
 // K-MOM (3D fused): out = new velocity from ua (advecting) and u0
-void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, const float* acc) {
+void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, const float* acc, const float* accf = nullptr) {
   Mom3Args a{};
   {
     const CUtensorMap* t0 = tensor_map(s, ua, M3_TW, M3_TH);
@@ -1001,6 +1001,7 @@ void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, c
   for (int c = 0; c < 3; ++c) {
     const long long oc = l.cstride * c;
     a.uac[c] = a.ua + oc; a.u0c[c] = a.u0 + oc; a.Vc[c] = a.V + oc; a.m0c[c] = a.mu0 + oc; a.unc[c] = a.un + oc;
+    a.accfc[c] = accf ? accf + oc : nullptr;
   }
   // 32-column tiles (the block's last row supplies lane 31's upper x faces); WL_M3_W32=0 selects the 31-column
   // tiling.  Measured (profiles/r1_v14_kmom_march_sweep.tsv): TGV 128³ 67.3 -> 58.7 us, sphere 512x256² 810 -> 795 us.
@@ -1047,7 +1048,7 @@ void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, c
   PatchArgs pa{};
   pa.m.l = s->lay; pa.m.ua = ua.base; pa.m.u0 = u0.base; pa.m.V = s->V.base; pa.m.f = nullptr;
   pa.m.per = s->per; pa.m.nu = s->cfg.nu; pa.m.dt = s->dt; pa.m.acc = a.acc;
-  pa.mu0 = s->mu0.base; pa.mu1 = s->mu1.base; pa.un = out.base;
+  pa.mu0 = s->mu0.base; pa.mu1 = s->mu1.base; pa.un = out.base; pa.accf = accf;
   pa.list = s->band_list; pa.count = s->band_count; pa.cap = s->band_cap; pa.corrector = corrector;
   if (s->band_cap > 0 && s->band_list2) {
     pa.m.f = s->f.base;

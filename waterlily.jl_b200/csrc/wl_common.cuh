@@ -200,13 +200,32 @@ __device__ __forceinline__ void block_reduce_partial(double s, float m, const Re
   }
 }
 struct FoldArgs { RedWork w; int n; Red* out; };
+constexpr int FOLD_CHUNK = 4096;   // partials per block of k_fold_partials (one block when n <= FOLD_CHUNK)
+// gridDim.x = ceil(n / FOLD_CHUNK) blocks fold one contiguous chunk each into psum[n + b]; the last one to finish
+// (ticket 0) folds those in index order: the result does not depend on which block that is.
 __global__ void __launch_bounds__(1024) k_fold_partials(const FoldArgs a) {
   pdl_entry();
   __shared__ double ssum[32];
   __shared__ float smax[32];
+  __shared__ int last;
   double s; float m;
-  fold_partials(a.w.psum, a.w.pmax, 0, a.n, ssum, smax, s, m);
-  if (threadIdx.x == 0) { a.out->sum = s; a.out->maxv = m; }
+  if (gridDim.x == 1) {
+    fold_partials(a.w.psum, a.w.pmax, 0, a.n, ssum, smax, s, m);
+    if (threadIdx.x == 0) { a.out->sum = s; a.out->maxv = m; }
+    return;
+  }
+  const int b = blockIdx.x, base = b * FOLD_CHUNK;
+  fold_partials(a.w.psum, a.w.pmax, base, min(FOLD_CHUNK, a.n - base), ssum, smax, s, m);
+  if (threadIdx.x == 0) {
+    a.w.psum[a.n + b] = s; a.w.pmax[a.n + b] = m;
+    __threadfence();
+    last = atomicAdd(&a.w.ticket[0], 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  fold_partials(a.w.psum, a.w.pmax, a.n, (int)gridDim.x, ssum, smax, s, m);
+  if (threadIdx.x == 0) { a.out->sum = s; a.out->maxv = m; a.w.ticket[0] = 0u; }
 }
 
 // Call from ALL threads of the block (contains __syncthreads).  `out` receives the result.

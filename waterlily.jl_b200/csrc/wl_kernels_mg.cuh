@@ -196,6 +196,10 @@ template <int D>
 __global__ void __launch_bounds__(256) k_gs_half_c(const LevArgs a) {
   pdl_entry();
   const Lay& l = a.l;
+  // a block covers 64 x 4 x 2 cells: half a tile in x.  Pattern tiles: the coefficients are known without loading them.
+  // The class byte is fetched first and the loads every class needs are issued before the branch on it (one memory
+  // round trip, not two in a row).
+  const int cls = D == 3 ? tile_class(a.uf, blockIdx.x >> 1, blockIdx.y, blockIdx.z) : 0;
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
   const int k = D == 3 ? blockIdx.z * blockDim.z + threadIdx.z + 1 : 0;
   const int i = 1 + 2 * (blockIdx.x * blockDim.x + threadIdx.x) + ((j + k + D + a.k0) & 1);
@@ -207,18 +211,21 @@ __global__ void __launch_bounds__(256) k_gs_half_c(const LevArgs a) {
   const int st[3] = {1, l.pitch, l.plane};
   float lo[3], hi[3], em[3], ep[3];
   const float r0 = a.r[o];
-  // a block covers 64 x 4 x 2 cells: half a tile in x.  Pattern tiles: the coefficients are known without loading them
-  const int cls = D == 3 ? tile_class(a.uf, blockIdx.x >> 1, blockIdx.y, blockIdx.z) : 0;
-  const int c3[3] = {i, j, k}, N3[3] = {l.n0, l.n1, l.n2};
 #pragma unroll
-  for (int q = 0; q < D; ++q) {                      // every load before the first use: one memory round trip
-    const float* Lq = a.L + l.cstride * q;
-    if (cls == 1) { lo[q] = a.uf.lu[q]; hi[q] = a.uf.lu[q]; }
-    else if (cls == 2) {
+  for (int q = 0; q < D; ++q) { em[q] = a.eps[o - st[q]]; ep[q] = a.eps[o + st[q]]; }
+  const int c3[3] = {i, j, k}, N3[3] = {l.n0, l.n1, l.n2};
+  if (cls == 1) {
+#pragma unroll
+    for (int q = 0; q < D; ++q) { lo[q] = a.uf.lu[q]; hi[q] = a.uf.lu[q]; }
+  } else if (cls == 2) {
+#pragma unroll
+    for (int q = 0; q < D; ++q) {
       lo[q] = pattern_zero(a.per, q, c3[q], N3[q]) ? 0.f : a.uf.lu[q];
       hi[q] = pattern_zero(a.per, q, c3[q] + 1, N3[q]) ? 0.f : a.uf.lu[q];
-    } else { lo[q] = Lq[o]; hi[q] = Lq[o + st[q]]; }
-    em[q] = a.eps[o - st[q]]; ep[q] = a.eps[o + st[q]];
+    }
+  } else {
+#pragma unroll
+    for (int q = 0; q < D; ++q) { const float* Lq = a.L + l.cstride * q; lo[q] = Lq[o]; hi[q] = Lq[o + st[q]]; }
   }
   float s = r0, dg = 0.f;
 #pragma unroll
@@ -330,18 +337,23 @@ __global__ void __launch_bounds__(256) k_gs_half_cx(const LevArgs a, const GsLin
     const int o = l.off(i, j, k);
     const int st[3] = {1, l.pitch, l.plane};
     float lo[3], hi[3], em[3], ep[3];
-    const float r0 = a.r[o];
     const int cls = tile_class(a.uf, blockIdx.x >> 1, blockIdx.y, zb);
-    const int c3[3] = {i, j, k}, N3[3] = {l.n0, l.n1, l.n2};
+    const float r0 = a.r[o];
 #pragma unroll
-    for (int q = 0; q < D; ++q) {
-      const float* Lq = a.L + l.cstride * q;
-      if (cls == 1) { lo[q] = a.uf.lu[q]; hi[q] = a.uf.lu[q]; }
-      else if (cls == 2) {
+    for (int q = 0; q < D; ++q) { em[q] = a.eps[o - st[q]]; ep[q] = a.eps[o + st[q]]; }   // before the branch on cls
+    const int c3[3] = {i, j, k}, N3[3] = {l.n0, l.n1, l.n2};
+    if (cls == 1) {
+#pragma unroll
+      for (int q = 0; q < D; ++q) { lo[q] = a.uf.lu[q]; hi[q] = a.uf.lu[q]; }
+    } else if (cls == 2) {
+#pragma unroll
+      for (int q = 0; q < D; ++q) {
         lo[q] = pattern_zero(a.per, q, c3[q], N3[q]) ? 0.f : a.uf.lu[q];
         hi[q] = pattern_zero(a.per, q, c3[q] + 1, N3[q]) ? 0.f : a.uf.lu[q];
-      } else { lo[q] = Lq[o]; hi[q] = Lq[o + st[q]]; }
-      em[q] = a.eps[o - st[q]]; ep[q] = a.eps[o + st[q]];
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < D; ++q) { const float* Lq = a.L + l.cstride * q; lo[q] = Lq[o]; hi[q] = Lq[o + st[q]]; }
     }
     float s = r0, dg = 0.f;
 #pragma unroll

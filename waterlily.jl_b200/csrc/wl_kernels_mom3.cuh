@@ -103,6 +103,7 @@ struct Mom3Args {
   Per per;
   float nu, dt;
   Vec3 acc;
+  const float* accfc[3];  // accelerate! field g(i,x,t)+∂ₜuBC(i,x,t) per component (wl_set_accel_field), or all null
   int corrector;
   int KZ;
   // TMA (cp.async.bulk.tensor): 4-D maps (x+3, y, z+zpad, component) over the padded device arrays of the advecting
@@ -390,7 +391,9 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
 #pragma unroll
       for (int ci = 0; ci < 3; ++ci) {
         float r = pend[ci] - F[ci][2];
-        r += a.acc.v[ci];
+        // accelerate! (Flow.jl:69-73): uniform part and sampled field are ONE term, summed first (as rhs_f does)
+        if (a.accfc[0]) r += a.acc.v[ci] + a.accfc[ci][opv];
+        else r += a.acc.v[ci];
         float X;
         if (NB) {
           X = fu0[ci] + a.dt * r;                            // f - 0, then 0 + 1·f
@@ -449,6 +452,7 @@ __global__ void __launch_bounds__(32 * M3_TY, 2) k_mom3(const __grid_constant__ 
 // ---- band cells (any μ₁ ≠ 0): exact BDIM with μddn, Flow.jl:20-26,176-180 (two passes, below).
 struct PatchArgs {
   MomArgs m;           // ua, u0, V, per, nu, dt, acc (m.f unused)
+  const float* accf;   // accelerate! field of this phase or null
   const float* mu0;
   const float* mu1;
   float* un;
@@ -485,7 +489,7 @@ __global__ void __launch_bounds__(128) k_patch_f(const PatchArgs a, const int* l
   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < 3 * n; t += gridDim.x * blockDim.x) {
     const int ci = t / n, o = list2[t - ci * n];
     const int k = o / l.plane, rem = o - k * l.plane, j = rem / l.pitch, i = rem - j * l.pitch;
-    a.m.f[l.cstride * ci + o] = rhs_f<3, S>(a.m, ci, i, j, k);
+    a.m.f[l.cstride * ci + o] = a.accf ? rhs_f<3, S, true>(a.m, ci, i, j, k, a.accf) : rhs_f<3, S>(a.m, ci, i, j, k);
   }
 }
 __global__ void __launch_bounds__(128) k_patch_apply(const PatchArgs a) {
