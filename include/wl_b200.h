@@ -146,17 +146,18 @@ int wl_finish_ic(wl_sim* s, const float uBC[3]);
  * three planes over the other dims, ghosts included, lowest remaining dim fastest:
  *   ci == dj: uBC at index 0, 1 and n-1 of dj;   ci != dj: uBC(I)-uBC(I+e_dj) at index 0, (unused), uBC(I)-uBC(I-e_dj)
  *   at index n-1.  Periodic directions keep their (ignored) slots.  `wl_bc_table_size` gives the element count.
- * STATUS: built and checked against the CPU restatement of the same table walk; NOT YET RUN on a B200 (its GPU test
- * is gated behind WL_RUN_UNVERIFIED=1).  `∂ₜuBC` and `g(i,x,t)` in `accelerate!` (src/Flow.jl:69-73) are not wired:
- * only boundary data that do not depend on t are complete.  Single GPU only. */
+ * On a slab-decomposed sim every rank passes the tables of ITS slab (local plane indices, global coordinates); the planes
+ * of the last direction are only read on the ranks that own a physical end.  `∂ₜuBC` and `g(i,x,t)` of `accelerate!`
+ * go through wl_set_accel_field.  GPU parity: tests/test_fnbc_gpu.py, tests/test_fullsize_gpu.py, tests/mgpu_worker.py. */
 int wl_bc_table_size(const wl_sim* s, size_t* count);
 int wl_set_bc_tables(wl_sim* s, const float* tables, size_t count);
 
 /* `accelerate!(r,t,g,U)` (src/Flow.jl:69-73) with Function `g(i,x,t)` / `uBC(i,x,t)`: the caller samples
  * `g + ∂ₜuBC` on every index of every component (layout of WL_F) at t₀ = sum(Δt)-Δt[end] (`which` = 0, predictor) and
  * t₁ = sum(Δt) (`which` = 1, corrector) before wl_mom_step; the fields are added to the convective-diffusive right-hand
- * side after the uniform term.  While fields are set the step runs its per-operator kernels (the fused K-MOM has no
- * slot for them).  `field == NULL` clears both.  STATUS as wl_set_bc_tables: built, NOT YET RUN on a B200.  Single GPU. */
+ * side after the uniform term (3D: a slot of the fused K-MOM and of its band patch; 2D: the per-operator K-RHS).
+ * `field == NULL` clears both.  Slab-decomposed sims pass their slab of the field (no exchange is needed: only the
+ * cell's own value is read). */
 int wl_set_accel_field(wl_sim* s, int which, const float* field, size_t count);
 
 int wl_measure_body(wl_sim* s, const wl_body* body, double t, double eps);
@@ -172,7 +173,8 @@ int wl_solver(wl_sim* s, int32_t* n_iter, int32_t* trace_len, float* rinf, float
 /* ---- stand-alone single-level solver: `solver!(p::Poisson;tol,itmx)` with the Jacobi-preconditioned
  *      `pcg!(p;it=6)` smoother (src/Poisson.jl:166-186,212-223) on level 1 (x = p, z = σ, L = μ₀), for
  *      users who pass `pois_ctor = flow->Poisson(flow.p,flow.μ₀,flow.σ)`.  tol comes from the config.
- *      Single GPU (WL_ERR_UNSUPPORTED on a slab-decomposed sim).                                 */
+ *      On a slab-decomposed sim the dot products are global (`perdot`, src/Poisson.jl:150-157): per-rank partial sums
+ *      folded in rank order, identical on every rank.                                            */
 int wl_poisson_solver(wl_sim* s, int32_t itmx, int32_t* n_iter);
 
 /* ---- time step: mom_step! (src/Flow.jl:156-167).  uBC_t1 = boundary velocity at t₁ (NULL: cfg.uBC);

@@ -48,7 +48,21 @@ CASES = {
     "torus": lambda: dict(dims=(48, 32, 32), uBC=(1.0, 0.0, 0.0), L=8.0, kw=dict(nu=0.05, scheme="vanLeer"),
                           body=dict(kind="torus", axis=0, center=(20, 15, 15), radius=6.0, minor=2.0),
                           remeasure=False, steps=4),
+    # the stand-alone Poisson/pcg! solver on slabs (perdot = gathered partial sums), after two ordinary steps
+    "pcg": lambda: dict(dims=(32, 32, 32), uBC=(1.0, 0.0, 0.0), L=8.0, kw=dict(nu=8.0 / 100),
+                        body=dict(kind="sphere", center=(12, 15, 15), radius=4.0), remeasure=False, steps=2, pcg=True),
+    # Function uBC(i,x,t) varying along the decomposed direction + its ∂ₜ in accelerate!: every rank samples its own slab
+    # of the tables at global coordinates (physical z ends on the first / last rank, interfaces in between)
+    "fn_ubc": lambda: dict(dims=(32, 24, 16), uBC=_ubc, L=8.0, kw=dict(nu=0.02, U=1.0, dt=0.1, dUBCdt=_dub),
+                           body=dict(kind="sphere", center=(10, 11, 7.5), radius=3.0), remeasure=False, steps=6),
+    # acceleration field g(i,x,t) through K-MOM's field slot, periodic last dimension (wrap link between the end ranks)
+    "fn_g": lambda: dict(dims=(32, 24, 16), uBC=(1.0, 0.0, 0.0), L=8.0, kw=dict(nu=0.02, perdir=(3,), g=_g),
+                         body=dict(kind="sphere", center=(10, 11, 8.0), radius=3.0), remeasure=False, steps=5),
 }
+_T = np.float32
+_ubc = lambda i, x, t: (_T(1) + _T(0.2) * t + _T(0.01) * x[1] + _T(0.005) * x[2]) if i == 1 else _T(0) * x[0] * t
+_dub = lambda i, x, t: (_T(0.2) + _T(0) * x[1] * t) if i == 1 else _T(0) * x[0] * t
+_g = lambda i, x, t: _T(0.01) * x[i % 3] - _T(0.02) * t * x[(i + 1) % 3]
 
 
 def run_case(wl, name, comm, dev):
@@ -76,6 +90,24 @@ def run_case(wl, name, comm, dev):
         f1, f2 = one.pressure_force(), slab.pressure_force()
         out["force_err"] = float(np.abs(f1 - f2).max() / max(1.0, np.abs(f1).max()))
         ok = ok and out["force_err"] <= 1e-6
+    if c.get("pcg"):
+        # stand-alone solver!(p::Poisson) with pcg! (src/Poisson.jl:166-186,212-223) on the stepped state: a smooth,
+        # zero-mean source in σ, x = 0.  The dot products are `perdot` sums over the slabs (Poisson.jl:150-157); CG
+        # amplifies their last-bit differences, so x agrees to the solver's tolerance, not to rounding
+        shp = one.field_shape("sigma")
+        zz, yy, xx = np.meshgrid(*(np.arange(m, dtype=np.float32) for m in shp), indexing="ij")
+        src = (np.sin(0.3 * xx) * np.cos(0.2 * yy) * np.sin(0.25 * zz + 0.4)).astype(np.float32)
+        inner = (slice(1, -1),) * 3
+        src[inner] -= src[inner].mean(dtype=np.float64).astype(np.float32)
+        zero = np.zeros(shp, np.float32)
+        one.upload("sigma", src); one.upload("p", zero)
+        slab.upload("sigma", wl.slab_of(src, rank, n)); slab.upload("p", wl.slab_of(zero, rank, n))
+        n1, n2 = one.poisson_solver(200), slab.poisson_solver(200)
+        ref = wl.slab_of(one.flow.p, rank, n)
+        got = slab.flow.p
+        out["pcg_n"] = [n1, n2]
+        out["pcg_err"] = float(np.abs(got - ref)[1:-1].max() / max(1e-30, float(np.abs(ref).max())))
+        ok = ok and abs(n1 - n2) <= 1 + n1 // 50 and n1 > 0 and out["pcg_err"] <= 1e-3
     slab.sync()
     out["halo"] = slab.halo_stats()
     out["transport"] = slab.halo_transport()

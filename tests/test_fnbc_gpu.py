@@ -74,8 +74,8 @@ def test_constant_jerk_through_g(wl):
     assert float(np.abs(sim.flow.u - ref.field("u")).max()) <= 2e-6 * np.sqrt(N)
 
 
-def test_rotating_frame_fields_3d_unfused(wl):
-    """Space- and time-varying g and ∂ₜuBC-like field in 3D (per-operator path while fields are set): CUDA vs oracle."""
+def test_rotating_frame_fields_3d(wl):
+    """Space- and time-varying g in 3D through the fused K-MOM's field slot (and the band patch's): CUDA vs oracle."""
     dims = (16, 12, 8)
     g = lambda i, x, t: np.float32(0.01) * x[i % 3] - np.float32(0.02) * t * x[(i + 1) % 3]
     kw = dict(nu=0.01, perdir=(3,))
@@ -88,5 +88,5 @@ def test_rotating_frame_fields_3d_unfused(wl):
         ref.sim_step(remeasure=False)
     assert sim.pois.n == ref.n and np.allclose(sim.flow.Δt, ref.dts, rtol=2e-6)
     assert float(np.abs(sim.flow.u - ref.field("u")).max()) <= 2e-6
-    sim.set_accel_function(None)                       # back on the fused path
+    sim.set_accel_function(None)                       # fields cleared: the uniform term alone again
     sim.sim_step(remeasure=False)

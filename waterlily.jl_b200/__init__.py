@@ -595,15 +595,23 @@ class Simulation:
             self._check(self.lib.wl_set_bc_tables(self.h, None, 0))
             return
         from . import bctables
-        flat = bctables.pack(bctables.bc_tables(uBC, self.dims, t, self.perdir), self.dims)
+        kw = self._slab_kw()
+        flat = bctables.pack(bctables.bc_tables(uBC, self.dims, t, self.perdir, **kw), self.dims, kw.get("n_last"))
         n = C.c_size_t()
         self._check(self.lib.wl_bc_table_size(self.h, C.byref(n)))
         assert flat.size == n.value, (flat.size, n.value)
         self._check(self.lib.wl_set_bc_tables(self.h, flat.ctypes.data, flat.size))
 
+    def _slab_kw(self):
+        """This rank's slab for the host-side samplers: {} on one GPU, else its plane offset and plane count."""
+        if self.nranks > 1 and self.D == 3:
+            return dict(k_offset=self.k_offset, n_last=self.dims[-1] // self.nranks)
+        return {}
+
     def _upload_bc(self, t):
         from . import bctables
-        flat = bctables.pack(bctables.bc_tables(self._bc_fn, self.dims, t, self.perdir), self.dims)
+        kw = self._slab_kw()
+        flat = bctables.pack(bctables.bc_tables(self._bc_fn, self.dims, t, self.perdir, **kw), self.dims, kw.get("n_last"))
         self._check(self.lib.wl_set_bc_tables(self.h, flat.ctypes.data, flat.size))
 
     def set_accel_function(self, g=None, dUdt=None):
@@ -616,7 +624,7 @@ class Simulation:
     def _upload_accel(self, t0, t1):
         from . import bctables
         for which, t in ((0, t0), (1, t1)):
-            a = bctables.accel_field(self._accel[0], self._accel[1], self.dims, t)
+            a = bctables.accel_field(self._accel[0], self._accel[1], self.dims, t, **self._slab_kw())
             self._check(self.lib.wl_set_accel_field(self.h, which, a.ctypes.data, a.size))
 
     # ---- reference API

@@ -525,7 +525,6 @@ int wl_set_bc_tables(wl_sim* s, const float* tables, size_t count) {
     s->bc_tab = nullptr;
     return WL_OK;
   }
-  if (s->dist.n > 1) return fail(s, WL_ERR_UNSUPPORTED, "boundary tables are not wired into the slab decomposition yet");
   size_t want = 0;
   wl_bc_table_size(s, &want);
   if (count != want) return fail(s, WL_ERR_INVALID, "boundary tables have the wrong number of elements (wl_bc_table_size)");
@@ -550,7 +549,6 @@ int wl_set_accel_field(wl_sim* s, int which, const float* field, size_t count) {
     s->accf_on = false;
     return WL_OK;
   }
-  if (s->dist.n > 1) return fail(s, WL_ERR_UNSUPPORTED, "acceleration fields are not wired into the slab decomposition yet");
   for (int w = 0; w < 2; ++w)
     if (!s->accf[w].alloc) {
       char* arena = s->arena; s->arena = nullptr;      // plain allocation, never peer-mapped
@@ -632,7 +630,6 @@ int wl_solver(wl_sim* s, int32_t* n_iter, int32_t* trace_len, float* rinf, float
 
 int wl_poisson_solver(wl_sim* s, int32_t itmx, int32_t* n_iter) {
   if (!s || s->lv.empty() || itmx < 0) return WL_ERR_INVALID;
-  if (s->dist.n > 1) return fail(s, WL_ERR_UNSUPPORTED, "the stand-alone Poisson/pcg! solver is single-GPU");
   cudaSetDevice(s->device);
   int n = 0;
   if (int e = poisson_solver(s, itmx, &n)) return e;
@@ -895,7 +892,7 @@ int wl_debug_op(wl_sim* s, int op, int level, float arg) {
     case 7: exitbc(s, s->u, s->u0, s->dt); break;
     case 8: ghost_phi(s); mom_rhs(s, s->u, nullptr); bdim(s, 1); break;
     case 9: cudaMemcpyAsync(s->u0.alloc, s->u.alloc, s->u.bytes, cudaMemcpyDeviceToDevice, s->st); break;
-    case 10: if (s->lv.empty() || s->dist.n > 1) return WL_ERR_INVALID; if (int e = pcg(s, s->lv[0], (int)arg)) return e; break;
+    case 10: if (s->lv.empty()) return WL_ERR_INVALID; if (int e = pcg(s, s->lv[0], (int)arg)) return e; break;
     default: return fail(s, WL_ERR_INVALID, "unknown debug op");
   }
   WL_CUDA(s, cudaStreamSynchronize(s->st));

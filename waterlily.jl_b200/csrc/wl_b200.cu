@@ -839,7 +839,9 @@ int mlp_solver(wl_sim* s, Trace* tr, bool residual_done = false) {
   return WL_OK;
 }
 
-// pcg!(p;it=6) (Poisson.jl:166-186): host control flow of the reference, one read-back per dot product
+// pcg!(p;it=6) (Poisson.jl:166-186): host control flow of the reference, one read-back per dot product.  On slabs the
+// dot products are the reference's `perdot` (Poisson.jl:150-157): every rank's partial sum is gathered and folded in
+// rank order by fetch_red, so all ranks take the same branches
 int pcg(wl_sim* s, Level& p, int it = 6) {
   const float epsT = 1.1920929e-07f;
   PcgArgs a{p.lay, p.L.base, p.iD.base, p.x.base, p.r.base, p.eps.base, p.z.base, 0.f, 0, s->redw, s->d_red + 11};
@@ -850,6 +852,7 @@ int pcg(wl_sim* s, Level& p, int it = 6) {
   if (std::fabs(rho) < 10 * epsT) return WL_OK;
   for (int i = 1; i <= it; ++i) {
     perbc(s, p.lay, p.eps.base, &p.per);
+    if (p.dist) { if (int e = halo(s, p.eps, 1)) return e; }   // the search direction's interface planes
     DISPATCH_D(s, k_pcg_mult, g, b, a);
     if (int e = fetch_red(s)) return e;
     const float alpha = rho / (float)s->h_red[11].sum;
@@ -868,15 +871,17 @@ int pcg(wl_sim* s, Level& p, int it = 6) {
 }
 
 // stand-alone solver!(p::Poisson;tol,itmx) (Poisson.jl:212-223) on level 1: residual!, then pcg! until
-// Σ|r| < (tol/10)·N and max|r| < tol; single GPU only
+// Σ|r| < (tol/10)·N and max|r| < tol
 int poisson_solver(wl_sim* s, int itmx, int* n_out) {
   Level& p = s->lv[0];
   const double tol = s->cfg.tol;
   const double r1tol = (tol / 10) * (double)p.ncells, rinftol = tol;
   LevArgs a = lev_args(s, p);
   perbc(s, p.lay, p.x.base, &p.per);
+  if (p.dist) { if (int e = halo(s, p.x, 1)) return e; }
   a.out = s->d_red + 0;
   DISPATCH_D(s, k_residual, grid_inside(p.lay), blk(s->D), a);
+  if (int e = gather_red(s)) return e;
   a.in = red_in(s, 0); a.out = s->d_red + 1;
   DISPATCH_D(s, k_shift_norms, grid_tiles(p.lay, false), blk(s->D), a);
   int np = 0;
@@ -891,6 +896,7 @@ int poisson_solver(wl_sim* s, int itmx, int* n_out) {
     if ((double)r1 < r1tol && (double)rinf < rinftol) break;
   }
   perbc(s, p.lay, p.x.base, &p.per);
+  if (p.dist) { if (int e = halo(s, p.x, 1)) return e; }
   if (n_out) *n_out = np;
   return WL_OK;
 }
@@ -1031,19 +1037,23 @@ void mom3(wl_sim* s, DevField& ua, DevField& u0, DevField& out, int corrector, c
   const bool nb = !nb_off && s->free_flow && s->per_glob.p[0] && s->per_glob.p[1] && s->per_glob.p[2];
   static bool attr = false;
   if (!attr) {                                                       // Mom3Smem exceeds the 48 KB static limit
-#define WL_MOM3_ATTR(S_, NB, W) cudaFuncSetAttribute(k_mom3<S_, NB, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Mom3Smem))
+#define WL_MOM3_ATTR(S_, NB, F) cudaFuncSetAttribute(k_mom3<S_, NB, true, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Mom3Smem))
+    WL_MOM3_ATTR(0, false, false); WL_MOM3_ATTR(0, true, false); WL_MOM3_ATTR(1, false, false); WL_MOM3_ATTR(1, true, false);
+    WL_MOM3_ATTR(2, false, false); WL_MOM3_ATTR(2, true, false);
     WL_MOM3_ATTR(0, false, true); WL_MOM3_ATTR(0, true, true); WL_MOM3_ATTR(1, false, true); WL_MOM3_ATTR(1, true, true);
     WL_MOM3_ATTR(2, false, true); WL_MOM3_ATTR(2, true, true);
 #undef WL_MOM3_ATTR
     attr = true;
   }
-#define WL_MOM3_LAUNCH(NB, W)                                                                \
+  // NB: body-free variant; F: with the caller's acceleration field (a separate instantiation: the hot variant pays nothing)
+#define WL_MOM3_LAUNCH(NB, F)                                                                 \
   do {                                                                                       \
-    if (sc == 0) LAUNCH_SMEM(s, (k_mom3<0, NB, W>), g, b, sizeof(Mom3Smem), a);              \
-    else if (sc == 1) LAUNCH_SMEM(s, (k_mom3<1, NB, W>), g, b, sizeof(Mom3Smem), a);         \
-    else LAUNCH_SMEM(s, (k_mom3<2, NB, W>), g, b, sizeof(Mom3Smem), a);                      \
+    if (sc == 0) LAUNCH_SMEM(s, (k_mom3<0, NB, true, F>), g, b, sizeof(Mom3Smem), a);        \
+    else if (sc == 1) LAUNCH_SMEM(s, (k_mom3<1, NB, true, F>), g, b, sizeof(Mom3Smem), a);   \
+    else LAUNCH_SMEM(s, (k_mom3<2, NB, true, F>), g, b, sizeof(Mom3Smem), a);                \
   } while (0)
-  if (nb) WL_MOM3_LAUNCH(true, true); else WL_MOM3_LAUNCH(false, true);
+  if (accf) { if (nb) WL_MOM3_LAUNCH(true, true); else WL_MOM3_LAUNCH(false, true); }
+  else { if (nb) WL_MOM3_LAUNCH(true, false); else WL_MOM3_LAUNCH(false, false); }
 #undef WL_MOM3_LAUNCH
   PatchArgs pa{};
   pa.m.l = s->lay; pa.m.ua = ua.base; pa.m.u0 = u0.base; pa.m.V = s->V.base; pa.m.f = nullptr;

@@ -263,7 +263,6 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_proj4(const ProjArgs2 a)
   const Lay& l = a.l;
   WL_QUAD_FROM_BLOCK(l)
   if (!inb) return;
-  const int cls = tile_class(a.uf, blockIdx.x, blockIdx.y, blockIdx.z);
   const int o = l.off(i, j, k);
   int oxm, oxp, oym, oyp, ozm, ozp;
   quad_nbr(l, a.per, i, j, k, oxm, oxp, oym, oyp, ozm, ozp);
@@ -272,6 +271,7 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_proj4(const ProjArgs2 a)
   float* ux = a.u; float* uy = a.u + l.cstride; float* uz = a.u + 2 * l.cstride;
   const F4 u0 = ld4(ux + o), v0 = ld4(uy + o), w0 = ld4(uz + o);
   F4 lx, ly, lz;                                        // lower faces only (Flow.jl:228)
+  const int cls = tile_class(a.uf, blockIdx.x, blockIdx.y, blockIdx.z);
   if (cls == 0) { lx = ld4g(a.L + o); ly = ld4g(a.L + l.cstride + o); lz = ld4g(a.L + 2 * l.cstride + o); }
   else {
     auto f = [&](int d, int c, int n) { return (cls == 2 && pattern_zero(a.per, d, c, n)) ? 0.f : a.uf.lu[d]; };
@@ -322,7 +322,6 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_up4(const UpArgs a) {
   const Lay& lc = a.c.l;
   WL_QUAD_FROM_BLOCK(l)
   if (!inb) return;
-  const int cls = tile_class(a.f.uf, blockIdx.x, blockIdx.y, blockIdx.z);   // first: see k_incr4
   const int o = l.off(i, j, k);
   const bool cx = a.c.c[0] != 0, cy = a.c.c[1] != 0, cz = a.c.c[2] != 0;
   // coarse coordinates of the row and of its (periodically wrapped) neighbours: down(I,c) MLP.jl:7
@@ -340,11 +339,11 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_up4(const UpArgs a) {
   const F4 e = row(cj, ck), eym = row(dn(cy, jm), ck), eyp = row(dn(cy, jp), ck), ezm = row(cj, dn(cz, km)), ezp = row(cj, dn(cz, kp));
   const float* pc = a.c.x + lc.pitch * cj + lc.plane * ck;
   const float exm = __ldg(pc + dn(cx, im)), exp_ = __ldg(pc + dn(cx, ip));
-  const F4 r0 = ld4(a.f.r + o), x0 = ld4(a.f.x + o);
   auto body = [&](auto tag) {
   constexpr int CLS = decltype(tag)::value;
   const QuadL ql = quad_coeffs<CLS>(a.f.L, l, a.per, a.f.uf, o, i, j, k);
   const F4 &lx = ql.lx, &ly0 = ql.ly0, &ly1 = ql.ly1, &lz0 = ql.lz0, &lz1 = ql.lz1; const float lx4 = ql.lx4;
+  const F4 r0 = ld4(a.f.r + o), x0 = ld4(a.f.x + o);
   F4 d0{{0.f, 0.f, 0.f, 0.f}};
   if (a.write_eps) d0 = quad_iD<CLS>(a.f.iD, ql, a.f.uf, o);
   F4 rn, xn, en;
@@ -375,7 +374,7 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_up4(const UpArgs a) {
     }
   }
   };
-  WL_CLASS_DISPATCH(cls, body);
+  WL_CLASS_DISPATCH(tile_class(a.f.uf, blockIdx.x, blockIdx.y, blockIdx.z), body);
 }
 
 // ---------------------------------------------------------------- K-DOWN, 4 cells per thread (see k_down)
@@ -394,19 +393,16 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_down4(const DownArgs a) 
     if (fabsf(mean) > 2.f * 1.1920929e-07f) sh = mean;
   }
   F4 rn{{0.f, 0.f, 0.f, 0.f}};
-  const int cls = tile_class(a.f.uf, blockIdx.x, blockIdx.y, blockIdx.z);   // first: see k_incr4
-  if (inb) {
-  const int o = l.off(i, j, k);
-  int oxm, oxp, oym, oyp, ozm, ozp;
-  quad_nbr(l, a.per, i, j, k, oxm, oxp, oym, oyp, ozm, ozp);
-  F4 r = ld4g(a.f.r + o), rym = ld4g(a.f.r + o + oym), ryp = ld4g(a.f.r + o + oyp), rzm = ld4g(a.f.r + o + ozm),
-     rzp = ld4g(a.f.r + o + ozp);
-  float rxm = __ldg(a.f.r + o + oxm), rxp = __ldg(a.f.r + o + oxp);
-  const F4 x0 = ld4(a.f.x + o);
   auto body = [&](auto tag) {
     constexpr int CLS = decltype(tag)::value;
+    const int o = l.off(i, j, k);
+    int oxm, oxp, oym, oyp, ozm, ozp;
+    quad_nbr(l, a.per, i, j, k, oxm, oxp, oym, oyp, ozm, ozp);
     const QuadL ql = quad_coeffs<CLS>(a.f.L, l, a.per, a.f.uf, o, i, j, k);
     const F4 &lx = ql.lx, &ly0 = ql.ly0, &ly1 = ql.ly1, &lz0 = ql.lz0, &lz1 = ql.lz1; const float lx4 = ql.lx4;
+    F4 r = ld4g(a.f.r + o), rym = ld4g(a.f.r + o + oym), ryp = ld4g(a.f.r + o + oyp), rzm = ld4g(a.f.r + o + ozm),
+       rzp = ld4g(a.f.r + o + ozp);
+    float rxm = __ldg(a.f.r + o + oxm), rxp = __ldg(a.f.r + o + oxp);
     // iD of the quad and of its six neighbours: class 1 -- the tile AND its neighbouring tiles hold the constants and no
     // boundary is near, so every one of them is idu; class 2 (boundary / interface tiles) loads the neighbours' values
     const F4 d = quad_iD<CLS>(a.f.iD, ql, a.f.uf, o);
@@ -416,6 +412,7 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_down4(const DownArgs a) 
       dym = ld4g(a.f.iD + o + oym); dyp = ld4g(a.f.iD + o + oyp); dzm = ld4g(a.f.iD + o + ozm); dzp = ld4g(a.f.iD + o + ozp);
       dxm = __ldg(a.f.iD + o + oxm); dxp = __ldg(a.f.iD + o + oxp);
     }
+    const F4 x0 = ld4(a.f.x + o);
     if (sh != 0.f) {
       // ghost neighbours of non-periodic directions are not shifted by the reference, but their iD and
       // the face coefficient towards them are 0: they contribute a (signed) zero either way
@@ -445,8 +442,7 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_down4(const DownArgs a) 
     st4(a.f.eps + o, rn);          // neighbours still read r: the new residual is staged in ϵ (host swaps the pointers)
     st4(a.f.x + o, xn);
   };
-  WL_CLASS_DISPATCH(cls, body);
-  }
+  if (inb) WL_CLASS_DISPATCH(tile_class(a.f.uf, blockIdx.x, blockIdx.y, blockIdx.z), body);
   {
     float* t = &tile[threadIdx.z][threadIdx.y][4 * threadIdx.x];
     t[0] = rn.v[0]; t[1] = rn.v[1]; t[2] = rn.v[2]; t[3] = rn.v[3];

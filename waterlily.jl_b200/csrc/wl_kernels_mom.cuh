@@ -254,6 +254,7 @@ __device__ __forceinline__ float bc_resolve_tab(const BcTabArgs& a, int ci, int 
   for (int dj = D - 1; dj >= 0; --dj) {
     if (have) continue;
     const int x = c[dj], n = N[dj];
+    const bool lo_if = dj == 2 && a.per.zlo, hi_if = dj == 2 && a.per.zhi;   // slab interface: no pass writes there
     if (a.per.p[dj]) {
       if (x == 0) c[dj] = n - 2; else if (x == n - 1) c[dj] = 1;
       continue;
@@ -263,11 +264,11 @@ __device__ __forceinline__ float bc_resolve_tab(const BcTabArgs& a, int ci, int 
     const float* T = a.tab + a.off[ci * D + dj];
     const int ps = a.psz[dj];
     if (ci == dj) {
-      if (x <= 1) { base = T[(x == 0 ? 0 : ps) + idx]; have = true; }
-      else if (x == n - 1 && !(a.saveexit && ci == 0)) { base = T[2 * ps + idx]; have = true; }
+      if (x <= 1 && !lo_if) { base = T[(x == 0 ? 0 : ps) + idx]; have = true; }
+      else if (x == n - 1 && !hi_if && !(a.saveexit && ci == 0)) { base = T[2 * ps + idx]; have = true; }
     } else {
-      if (x == 0) { ds[nd++] = T[idx]; c[dj] = 1; }
-      else if (x == n - 1) { ds[nd++] = T[2 * ps + idx]; c[dj] = n - 2; }
+      if (x == 0 && !lo_if) { ds[nd++] = T[idx]; c[dj] = 1; }
+      else if (x == n - 1 && !hi_if) { ds[nd++] = T[2 * ps + idx]; c[dj] = n - 2; }
     }
   }
   if (!have) base = a.a[a.l.cstride * ci + a.l.off(c[0], c[1], c[2])];
@@ -283,6 +284,7 @@ __global__ void k_bc_vec_tab(const BcTabArgs a) {
   const int dj = blockIdx.z / 3, which = blockIdx.z % 3;
   const Lay& l = a.l;
   const int N[3] = {l.n0, l.n1, l.n2};
+  if (dj == 2 && (which == 2 ? a.per.zhi : a.per.zlo)) return;   // slab interface: filled by the halo exchange
   const int da = dj == 0 ? 1 : 0;
   const int db = dj == 2 ? 1 : 2;
   const int pa = blockIdx.x * blockDim.x + threadIdx.x;

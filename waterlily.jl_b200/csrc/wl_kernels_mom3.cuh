@@ -103,7 +103,7 @@ struct Mom3Args {
   Per per;
   float nu, dt;
   Vec3 acc;
-  const float* accfc[3];  // accelerate! field g(i,x,t)+∂ₜuBC(i,x,t) per component (wl_set_accel_field), or all null
+  const float* accfc[3];  // accelerate! field g(i,x,t)+∂ₜuBC(i,x,t) per component (wl_set_accel_field): read by the ACCF variant
   int corrector;
   int KZ;
   // TMA (cp.async.bulk.tensor): 4-D maps (x+3, y, z+zpad, component) over the padded device arrays of the advecting
@@ -179,7 +179,7 @@ __device__ __forceinline__ void tma_load_4d(unsigned dst, const CUtensorMap* tm,
 // those 3x7 faces at column i0+32 -- the same expression on the same staged values as lane 0 of the next
 // block -- and hands them over through shared memory.  Power-of-two grids then tile exactly (128 = 4x32
 // instead of 5x31 columns) and every lane of the seven output rows produces a cell.
-template <int S, bool FAST, bool NB, bool W32>
+template <int S, bool FAST, bool NB, bool W32, bool ACCF>
 __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm) {
   const Lay& l = a.l;
   const int lane = threadIdx.x, ty = threadIdx.y, tid = lane + 32 * ty;
@@ -392,7 +392,7 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
       for (int ci = 0; ci < 3; ++ci) {
         float r = pend[ci] - F[ci][2];
         // accelerate! (Flow.jl:69-73): uniform part and sampled field are ONE term, summed first (as rhs_f does)
-        if (a.accfc[0]) r += a.acc.v[ci] + a.accfc[ci][opv];
+        if (ACCF) r += a.acc.v[ci] + a.accfc[ci][opv];
         else r += a.acc.v[ci];
         float X;
         if (NB) {
@@ -431,7 +431,9 @@ __device__ __forceinline__ void mom3_body_async(const Mom3Args& a, Mom3Smem& sm)
   cp_async_wait<0>();
 }
 
-template <int S, bool NB, bool W32>
+// ACCF: with the caller's acceleration field -- a separate instantiation, because even a uniform branch on a null
+// pointer in the finalisation cost the hot variant 6 % (777 vs 730 us, profiles/r2_c17_*)
+template <int S, bool NB, bool W32, bool ACCF>
 __global__ void __launch_bounds__(32 * M3_TY, 2) k_mom3(const __grid_constant__ Mom3Args a) {
   pdl_entry();
   extern __shared__ __align__(128) unsigned char m3_raw[];
@@ -445,8 +447,8 @@ __global__ void __launch_bounds__(32 * M3_TY, 2) k_mom3(const __grid_constant__ 
                            : ((int)blockIdx.x >= 1 - px && 1 + 31 * (int)blockIdx.x + 31 <= a.l.n0 - 2 + px);
   const bool inner = inner_x &&
                      (int)blockIdx.y >= 1 - py && 1 + (M3_TY - 1) * (int)blockIdx.y + (M3_TY - 1) <= a.l.n1 - 2 + py;
-  if (inner) mom3_body_async<S, true, NB, W32>(a, sm);
-  else mom3_body_async<S, false, NB, W32>(a, sm);
+  if (inner) mom3_body_async<S, true, NB, W32, ACCF>(a, sm);
+  else mom3_body_async<S, false, NB, W32, ACCF>(a, sm);
 }
 
 // ---- band cells (any μ₁ ≠ 0): exact BDIM with μddn, Flow.jl:20-26,176-180 (two passes, below).

@@ -136,7 +136,6 @@ function B200Flow(N::NTuple{D}, uBC; Δt=0.25, ν=0., g=nothing, u0=nothing, uλ
     # A Function uBC(i,x,t) / g(i,x,t) stays on the host: it is SAMPLED into the boundary tables / acceleration fields
     # the device path consumes (set_bc_function!, set_accel_field!) -- at t = 0 here, at t₁ / (t₀,t₁) in every mom_step!.
     ubc0 = uBC isa Function ? ntuple(_ -> 0f0, D) : Float32.(uBC)
-    (uBC isa Function && !isnothing(comm) && comm[2] > 1) && error("WL_ERR_UNSUPPORTED: Function uBC on a slab-decomposed run")
     cfg = Ref(WLConfig(D, pad3(Int32.(N), Int32(0)), ntuple(i -> Int32(i in perdir), 3), exitBC, SCHEME[λ], ν, Δt,
                        pad3(ubc0, 0f0), 10, 2f-3, 32, device, 0))
     out = Ref{Ptr{Cvoid}}(C_NULL)
@@ -359,14 +358,17 @@ function bc_tables(uBC::Function, Ng::NTuple{D,Int}, t, perdir, ::Type{T}) where
     end
     tab
 end
+"A Function of (i,x,t) seen from a slab whose first plane is global plane `koff`: local indices, global coordinates."
+slab_fn(f::Function, koff, ::Val{D}, ::Type{T}) where {D,T} =
+    koff == 0 ? f : (i, x, t) -> f(i, x .+ ntuple(d -> d == D ? T(koff) : zero(T), D), t)
 function set_bc_function!(a::B200Flow{D,T}, uBC::Function; t=zero(T)) where {D,T}
-    tab = bc_tables(uBC, size(a.p), T(t), a.perdir, T)
+    tab = bc_tables(slab_fn(uBC, a.koff, Val(D), T), size(a.p), T(t), a.perdir, T)
     check(a.h, ccall((:wl_set_bc_tables, LIB), Cint, (Ptr{Cvoid}, Ptr{Cfloat}, Csize_t), a.h.ptr, tab, length(tab)))
 end
 "`g + ∂ₜuBC` on every index at t₀ (`which`=0) or t₁ (`which`=1) for accelerate! (src/Flow.jl:69-73)."
 function set_accel_field!(a::B200Flow{D,T}, which::Integer, f::Function, t) where {D,T}
-    Ng = size(a.p)
-    fld = T[f(i, WaterLily.loc(i, I, T), T(t)) for I in CartesianIndices(Ng), i in 1:D]
+    Ng = size(a.p); fs = slab_fn(f, a.koff, Val(D), T)
+    fld = T[fs(i, WaterLily.loc(i, I, T), T(t)) for I in CartesianIndices(Ng), i in 1:D]
     check(a.h, ccall((:wl_set_accel_field, LIB), Cint, (Ptr{Cvoid}, Cint, Ptr{Cfloat}, Csize_t), a.h.ptr, which, fld, length(fld)))
 end
 
