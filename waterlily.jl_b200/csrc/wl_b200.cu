@@ -432,10 +432,13 @@ int exitbc(wl_sim* s, DevField& u, DevField& u0, float dt) {
 // ---------------------------------------------------------------- multigrid pieces
 TileFlags tile_flags(const Level& p) {
   static const bool off = getenv("WL_NO_TILE_FLAGS") != nullptr;      // A/B switch: every tile takes the general path
-  TileFlags t{nullptr, 0, 0, {p.lu[0], p.lu[1], p.lu[2]}, 0.f};
+  TileFlags t{nullptr, 0, 0, {p.lu[0], p.lu[1], p.lu[2]}, 0.f, 0.f};
   float dg = 0.f;                                                    // set_diag! on an all-pattern interior cell
   dg -= p.lu[0] + p.lu[0]; dg -= p.lu[1] + p.lu[1]; dg -= p.lu[2] + p.lu[2];
   t.idu = dg == 0.f ? 0.f : 1.f / dg;
+  float d1 = 0.f;                                                    // ... and on one next to an x boundary: (0 + lu) or
+  d1 -= p.lu[0]; d1 -= p.lu[1] + p.lu[1]; d1 -= p.lu[2] + p.lu[2];   // (lu + 0) is lu exactly
+  t.idx1 = d1 == 0.f ? 0.f : 1.f / d1;
   if (p.uvalid && p.uflag && !off) { t.f = p.uflag; t.nx = p.unx; t.ny = p.uny; }
   return t;
 }

@@ -68,10 +68,17 @@ struct Vec3 { float v[3]; };
 // (12-20 of their 24-36 B/cell).  update!/build classify each 128x4x2-cell tile (= one block of the 4-cells-per-thread
 // kernels): every cell of the tile AND of its neighbouring tiles matches the pattern -> class 1 (no boundary, no slab
 // interface next to the tile: all values are the constants lu / idu) or class 2 (boundary or interface tile: L is
-// synthesised with index compares, iD of neighbour cells is still loaded); else class 0 (general path, loads).
+// synthesised with index compares, iD of neighbour cells is still loaded; rows that touch no y/z boundary -- all but
+// the first and last of the array -- only need two selects on the x ends and the constant idx1); else class 0
+// (general path, loads).
 // Same values, same operations: bit-identical.  f == nullptr: no classes for this level (2D, rows not a multiple of 4,
 // switched off by an upload until the next update!).
-struct TileFlags { const unsigned char* f; int nx, ny; float lu[3]; float idu; };
+struct TileFlags {
+  const unsigned char* f; int nx, ny;
+  float lu[3];
+  float idu;    // iD of a cell whose six faces hold the pattern constants
+  float idx1;   // iD of a cell whose lower OR upper x face is a boundary face (0) and the other five hold the constants
+};
 constexpr int UT_X = 128, UT_Y = 4, UT_Z = 2;
 __device__ __forceinline__ int tile_class(const TileFlags& t, int tx, int ty, int tz) {
   return t.f == nullptr ? 0 : t.f[tx + t.nx * (ty + t.ny * tz)];

@@ -188,6 +188,53 @@ __global__ void __launch_bounds__(256) k_gs_half(const LevArgs a) {
   a.eps[o] = s * inv_or_zero(dg);
 }
 
+// The update of one cell, ϵ = (r - Σ L·ϵ_nb)·iD (Poisson.jl:142-147), by tile class.  The arithmetic on ϵ is the same in
+// every branch; what differs is where L and iD = inv_or_zero(-ΣL) come from: loaded (class 0), the level's constants
+// (class 1: idu is that expression evaluated once on the host), or constants with the boundary faces zeroed (class 2).
+// In class 2 a row that touches no y/z boundary -- a warp-uniform test -- needs only two selects for the x ends, and its
+// iD is idu or idx1 (one zero x face; 0 + lu == lu + 0 == lu, so one constant serves both ends).
+template <int D>
+__device__ __forceinline__ float gs_update(const LevArgs& a, int cls, int i, int j, int k, int o, float r0,
+                                           const float (&em)[3], const float (&ep)[3]) {
+  const Lay& l = a.l;
+  float lo[3], hi[3];
+  if (D == 3 && cls == 1) {
+    float s = r0;
+#pragma unroll
+    for (int q = 0; q < 3; ++q) s -= em[q] * a.uf.lu[q] + ep[q] * a.uf.lu[q];
+    return s * a.uf.idu;
+  }
+  const int c3[3] = {i, j, k}, N3[3] = {l.n0, l.n1, l.n2};
+  if (D == 3 && cls == 2) {
+    const bool yz_plain = !(pattern_zero(a.per, 1, j, l.n1) || pattern_zero(a.per, 1, j + 1, l.n1) ||
+                            pattern_zero(a.per, 2, k, l.n2) || pattern_zero(a.per, 2, k + 1, l.n2));
+    if (yz_plain) {
+      const bool z0 = pattern_zero(a.per, 0, i, l.n0), z1 = pattern_zero(a.per, 0, i + 1, l.n0);
+      float s = r0;
+      s -= em[0] * (z0 ? 0.f : a.uf.lu[0]) + ep[0] * (z1 ? 0.f : a.uf.lu[0]);
+      s -= em[1] * a.uf.lu[1] + ep[1] * a.uf.lu[1];
+      s -= em[2] * a.uf.lu[2] + ep[2] * a.uf.lu[2];
+      return s * ((z0 || z1) ? a.uf.idx1 : a.uf.idu);
+    }
+#pragma unroll
+    for (int q = 0; q < D; ++q) {
+      lo[q] = pattern_zero(a.per, q, c3[q], N3[q]) ? 0.f : a.uf.lu[q];
+      hi[q] = pattern_zero(a.per, q, c3[q] + 1, N3[q]) ? 0.f : a.uf.lu[q];
+    }
+  } else {
+    const int st[3] = {1, l.pitch, l.plane};
+#pragma unroll
+    for (int q = 0; q < D; ++q) { const float* Lq = a.L + l.cstride * q; lo[q] = Lq[o]; hi[q] = Lq[o + st[q]]; }
+  }
+  float s = r0, dg = 0.f;
+#pragma unroll
+  for (int q = 0; q < D; ++q) {
+    dg -= lo[q] + hi[q];
+    s -= em[q] * lo[q] + ep[q] * hi[q];
+  }
+  return s * inv_or_zero(dg);
+}
+
 // The same half sweep with the threads COMPACTED onto the colour being updated: thread tx owns the
 // x-pair (2tx+1, 2tx+2) of its row and updates the member of the sweep's colour, so every lane of a
 // warp does work (the one-thread-per-cell version idles half of them and is issue-bound).
@@ -209,31 +256,11 @@ __global__ void __launch_bounds__(256) k_gs_half_c(const LevArgs a) {
   if (cl > 2 * (nl / 2) - 2) return;
   const int o = l.off(i, j, k);
   const int st[3] = {1, l.pitch, l.plane};
-  float lo[3], hi[3], em[3], ep[3];
+  float em[3] = {0.f, 0.f, 0.f}, ep[3] = {0.f, 0.f, 0.f};
   const float r0 = a.r[o];
 #pragma unroll
   for (int q = 0; q < D; ++q) { em[q] = a.eps[o - st[q]]; ep[q] = a.eps[o + st[q]]; }
-  const int c3[3] = {i, j, k}, N3[3] = {l.n0, l.n1, l.n2};
-  if (cls == 1) {
-#pragma unroll
-    for (int q = 0; q < D; ++q) { lo[q] = a.uf.lu[q]; hi[q] = a.uf.lu[q]; }
-  } else if (cls == 2) {
-#pragma unroll
-    for (int q = 0; q < D; ++q) {
-      lo[q] = pattern_zero(a.per, q, c3[q], N3[q]) ? 0.f : a.uf.lu[q];
-      hi[q] = pattern_zero(a.per, q, c3[q] + 1, N3[q]) ? 0.f : a.uf.lu[q];
-    }
-  } else {
-#pragma unroll
-    for (int q = 0; q < D; ++q) { const float* Lq = a.L + l.cstride * q; lo[q] = Lq[o]; hi[q] = Lq[o + st[q]]; }
-  }
-  float s = r0, dg = 0.f;
-#pragma unroll
-  for (int q = 0; q < D; ++q) {
-    dg -= lo[q] + hi[q];
-    s -= em[q] * lo[q] + ep[q] * hi[q];
-  }
-  a.eps[o] = s * inv_or_zero(dg);
+  a.eps[o] = gs_update<D>(a, cls, i, j, k, o, r0, em, ep);
 }
 
 // ---- pattern-tile classification (see TileFlags in wl_common.cuh).  Stage 1: core[t] = every cell of tile t -- its
@@ -279,10 +306,14 @@ __global__ void __launch_bounds__(256) k_tile_class(const TileArgs a) {
   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < nt; t += gridDim.x * blockDim.x) {
     const int c[3] = {t % a.nx, (t / a.nx) % a.ny, t / (a.nx * a.ny)};
     int ok = 1, edge = 0;
-    // (the last TWO tiles of a direction: a partial last tile can be one cell thick, and then the tile before it has a
-    //  boundary-adjacent cell -- whose iD is not the constant -- as its neighbour)
+    // a tile is an edge tile if it holds a boundary-adjacent cell (index 1 or N-2: the first and the last tile of a
+    // direction) or has one as a neighbour: the tile before the last when the last one is a single cell thick
+    const int N3[3] = {a.l.n0, a.l.n1, a.l.n2}, ts[3] = {UT_X, UT_Y, UT_Z};
 #pragma unroll
-    for (int d = 0; d < 3; ++d) edge |= !a.per.p[d] && (c[d] == 0 || c[d] >= n[d] - 2);
+    for (int d = 0; d < 3; ++d) {
+      const int last_thick = (N3[d] - 2) - ts[d] * (n[d] - 1);
+      edge |= !a.per.p[d] && (c[d] == 0 || c[d] == n[d] - 1 || (c[d] == n[d] - 2 && last_thick == 1));
+    }
     for (int dz = -1; dz <= 1 && ok; ++dz)
       for (int dy = -1; dy <= 1 && ok; ++dy)
         for (int dx = -1; dx <= 1 && ok; ++dx) {
@@ -336,32 +367,12 @@ __global__ void __launch_bounds__(256) k_gs_half_cx(const LevArgs a, const GsLin
   if (i <= l.n0 - 2 && j <= l.n1 - 2 && k <= l.n2 - 2 && k <= 2 * (l.n2 / 2) - 2) {
     const int o = l.off(i, j, k);
     const int st[3] = {1, l.pitch, l.plane};
-    float lo[3], hi[3], em[3], ep[3];
     const int cls = tile_class(a.uf, blockIdx.x >> 1, blockIdx.y, zb);
     const float r0 = a.r[o];
+    float em[3], ep[3];
 #pragma unroll
     for (int q = 0; q < D; ++q) { em[q] = a.eps[o - st[q]]; ep[q] = a.eps[o + st[q]]; }   // before the branch on cls
-    const int c3[3] = {i, j, k}, N3[3] = {l.n0, l.n1, l.n2};
-    if (cls == 1) {
-#pragma unroll
-      for (int q = 0; q < D; ++q) { lo[q] = a.uf.lu[q]; hi[q] = a.uf.lu[q]; }
-    } else if (cls == 2) {
-#pragma unroll
-      for (int q = 0; q < D; ++q) {
-        lo[q] = pattern_zero(a.per, q, c3[q], N3[q]) ? 0.f : a.uf.lu[q];
-        hi[q] = pattern_zero(a.per, q, c3[q] + 1, N3[q]) ? 0.f : a.uf.lu[q];
-      }
-    } else {
-#pragma unroll
-      for (int q = 0; q < D; ++q) { const float* Lq = a.L + l.cstride * q; lo[q] = Lq[o]; hi[q] = Lq[o + st[q]]; }
-    }
-    float s = r0, dg = 0.f;
-#pragma unroll
-    for (int q = 0; q < D; ++q) {
-      dg -= lo[q] + hi[q];
-      s -= em[q] * lo[q] + ep[q] * hi[q];
-    }
-    const float v = s * inv_or_zero(dg);
+    const float v = gs_update<D>(a, cls, i, j, k, o, r0, em, ep);
     a.eps[o] = v;
     if (x.push_lo && k == 1) x.peer_lo[o + l.plane * (l.n2 - 2)] = v;
     if (x.push_hi && k == l.n2 - 2) x.peer_hi[o - l.plane * (l.n2 - 2)] = v;

@@ -43,14 +43,25 @@ __device__ __forceinline__ void st4(float* p, const F4& a) {
 // ---- face coefficients of a quad by tile class (TileFlags, wl_common.cuh): 0 loaded, 1 the level's constants, 2 the
 // constants with the boundary faces zeroed by index compares.  ly*/lz* are the same for the quad's four cells in
 // classes 1 and 2, so the compiler keeps scalars there.
-struct QuadL { F4 lx, ly0, ly1, lz0, lz1; float lx4; };
+// (class 2: a row that touches no y/z boundary -- warp-uniform -- has the plain constants everywhere except the quad's
+//  first lower / last upper x face at the ends of the row: `xq` = 1 + (first face zero) + 2·(last face zero), 0 = general)
+struct QuadL { F4 lx, ly0, ly1, lz0, lz1; float lx4; int xq; };
 template <int CLS>
 __device__ __forceinline__ QuadL quad_coeffs(const float* L, const Lay& l, const Per& per, const TileFlags& t, int o, int i, int j, int k) {
   QuadL q;
+  q.xq = 0;
   if (CLS == 0) {
     const float* Lx = L; const float* Ly = L + l.cstride; const float* Lz = L + 2 * l.cstride;
     q.lx = ld4g(Lx + o); q.lx4 = __ldg(Lx + o + 4);
     q.ly0 = ld4g(Ly + o); q.ly1 = ld4g(Ly + o + l.pitch); q.lz0 = ld4g(Lz + o); q.lz1 = ld4g(Lz + o + l.plane);
+  } else if (CLS == 2 && !(pattern_zero(per, 1, j, l.n1) || pattern_zero(per, 1, j + 1, l.n1) ||
+                           pattern_zero(per, 2, k, l.n2) || pattern_zero(per, 2, k + 1, l.n2))) {
+    const bool z0 = pattern_zero(per, 0, i, l.n0), z4 = pattern_zero(per, 0, i + 4, l.n0);
+    q.xq = 1 + (z0 ? 1 : 0) + (z4 ? 2 : 0);
+    q.lx = F4{{z0 ? 0.f : t.lu[0], t.lu[0], t.lu[0], t.lu[0]}};
+    q.lx4 = z4 ? 0.f : t.lu[0];
+    q.ly0 = q.ly1 = F4{{t.lu[1], t.lu[1], t.lu[1], t.lu[1]}};
+    q.lz0 = q.lz1 = F4{{t.lu[2], t.lu[2], t.lu[2], t.lu[2]}};
   } else {
     auto f = [&](int d, int c, int n) { return (CLS == 2 && pattern_zero(per, d, c, n)) ? 0.f : t.lu[d]; };
 #pragma unroll
@@ -67,6 +78,7 @@ template <int CLS>
 __device__ __forceinline__ F4 quad_iD(const float* iD, const QuadL& q, const TileFlags& t, int o) {
   if (CLS == 0) return ld4g(iD + o);
   if (CLS == 1) return F4{{t.idu, t.idu, t.idu, t.idu}};
+  if (q.xq) return F4{{((q.xq - 1) & 1) ? t.idx1 : t.idu, t.idu, t.idu, ((q.xq - 1) & 2) ? t.idx1 : t.idu}};   // xq-1 = z0 + 2·z4
   F4 d;
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
@@ -105,7 +117,7 @@ __device__ __forceinline__ void quad_nbr(const Lay& l, const Per& per, int i, in
 
 // ---------------------------------------------------------------- increment! (Poisson.jl:100-104), 4 cells per thread
 // perBC!(ϵ) folded into wrap-reads as in k_increment_w; L₁/L∞ partials per block (k_fold_partials folds them)
-__global__ void __launch_bounds__(256) k_incr4(const SmArgs a) {
+__global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_incr4(const SmArgs a) {
   pdl_entry();
   const Lay& l = a.p.l;
   if (a.wait_lo | a.wait_hi) {                         // ϵ ghost planes pushed by the neighbours' last half sweep
