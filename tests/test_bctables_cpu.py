@@ -184,3 +184,32 @@ def test_packed_tables_match_kernel_addressing(dims, perdir, saveexit):
         for idx in np.ndindex(*a.shape[1:]):
             out[(ci,) + idx] = resolve_flat(a, flat, ci, idx[::-1], saveexit, per)
     assert np.array_equal(out, seq)
+
+
+@pytest.mark.parametrize("nranks", [2, 4])
+def test_slab_tables_are_slices_of_the_global_tables(nranks):
+    """A rank of a slab-decomposed run samples ITS slab (local plane indices, global coordinates, `k_offset`/`n_last`):
+    the x- and y-normal tables and the acceleration field must be the corresponding z-slices of the global ones, and the
+    z-normal tables of the first / last rank must equal the global lower / upper planes (interface ranks never read theirs)."""
+    T = np.float32
+    dims = (10, 6, 8)
+    ub = lambda i, x, t: T(0.3 * i) + T(0.1) * x[i % 3] * x[(i + 1) % 3] + T(0.01) * t * x[2]
+    g = lambda i, x, t: T(0.01) * x[i % 3] - T(0.02) * t * x[(i + 1) % 3]
+    t = 0.7
+    glob = bt.bc_tables(ub, dims, t)
+    gacc = bt.accel_field(g, None, dims, t)
+    nl = dims[2] // nranks
+    for r in range(nranks):
+        k0 = r * nl
+        loc = bt.bc_tables(ub, dims, t, k_offset=k0, n_last=nl)
+        acc = bt.accel_field(g, None, dims, t, k_offset=k0, n_last=nl)
+        assert np.array_equal(acc, gacc[:, k0:k0 + nl + 2])
+        for (i, j), tb in loc.items():
+            for name, plane in tb.items():
+                want = glob[i, j][name]
+                if j < 2:                                  # planes over (z, ·): the slab's z range, ghosts included
+                    assert np.array_equal(plane, want[k0:k0 + nl + 2]), (r, i, j, name)
+                elif (r == 0 and name in ("lo0", "lo1", "dlo")) or (r == nranks - 1 and name in ("hi", "dhi")):
+                    assert np.array_equal(plane, want), (r, i, j, name)
+        flat = bt.pack(loc, dims, nl)
+        assert flat.size == sum(3 * 3 * (np.prod([10 + 2, 6 + 2, nl + 2]) // n) for n in (10 + 2, 6 + 2, nl + 2))
