@@ -33,6 +33,7 @@ B_ALG3 = {
     "k_divres4": 36.0, "k_proj4": 44.0, "k_down4": 28.5, "k_up4": 28.5, "k_cfl4": 16.0,
     "smoother": 28.0,
 }
+SPLIT_KERNELS = ("k_divres4", "k_down4")
 SMOOTHER_KERNELS = ("k_gs_half_c", "k_gs_pair", "k_incr4", "k_smooth_fused", "k_gs_half_cx")
 CELLS_PER_BLOCK = {"k_divres4": 1024, "k_proj4": 1024, "k_down4": 1024, "k_up4": 1024, "k_incr4": 1024, "k_cfl4": 1024}
 B_ALG2 = {"k_mom_rhs": (24 + 32) / 2}
@@ -281,7 +282,20 @@ def kernel_table(prof, blocks, cells_gpu, nsteps, peak, ncu):
     Work size of the multigrid kernels (they run on several levels) = thread blocks launched x cells per block."""
     rows, total = [], sum(ms for _, ms in prof.values())
     sm_ms, sm_cells, sm_n = 0.0, 0, 0
+    # K-DIVRES and K-DOWN run as two launches per call (<1>: the whole grid of tiles, classes 1/3; <2>: the class-0/2 tile
+    # list): one row per kernel, time of both launches, work = the grid of the first
+    def is_list_launch(name):
+        kn, targs = base_name(name)
+        return kn in SPLIT_KERNELS and targs[:1] == ["2"]
+    merged = {name: v for name, v in prof.items() if not is_list_launch(name)}
     for name, (n, ms) in prof.items():
+        if is_list_launch(name):
+            first = next((x for x in merged if base_name(x)[0] == base_name(name)[0] and base_name(x)[1][:1] == ["1"]), None)
+            if first is None:
+                merged[name] = (n, ms)
+            else:
+                merged[first] = (merged[first][0], merged[first][1] + ms)
+    for name, (n, ms) in merged.items():
         kn, targs = base_name(name)
         balg = work = None
         if kn == "k_mom3":

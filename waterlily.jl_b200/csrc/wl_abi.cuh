@@ -20,6 +20,8 @@ int build_levels(wl_sim* s) {
     free_field(v.r); free_field(v.eps); free_field(v.Dg); free_field(v.iD); free_field(v.tmp);
     if (v.ucore) cudaFree(v.ucore);
     if (v.uflag) cudaFree(v.uflag);
+    if (v.ulist) cudaFree(v.ulist);
+    if (v.ucount) cudaFree(v.ucount);
   }
   s->lv.clear();
   s->lv.reserve(s->cfg.maxlevels + 2);
@@ -383,6 +385,8 @@ void wl_destroy(wl_sim* s) {
     free_field(v.r); free_field(v.eps); free_field(v.Dg); free_field(v.iD); free_field(v.tmp);
     if (v.ucore) cudaFree(v.ucore);
     if (v.uflag) cudaFree(v.uflag);
+    if (v.ulist) cudaFree(v.ulist);
+    if (v.ucount) cudaFree(v.ucount);
   }
   free_field(s->u); free_field(s->u0); free_field(s->f); free_field(s->p);
   free_field(s->sigma); free_field(s->V); free_field(s->mu0); free_field(s->mu1); free_field(s->w);
@@ -649,7 +653,7 @@ int wl_tile_classes(wl_sim* s, int32_t level, int64_t counts[3]) {
   std::vector<unsigned char> h((size_t)p.unx * p.uny * p.unz);
   WL_CUDA(s, cudaStreamSynchronize(s->st));
   WL_CUDA(s, cudaMemcpy(h.data(), p.uflag, h.size(), cudaMemcpyDeviceToHost));
-  for (unsigned char c : h) counts[c < 3 ? c : 0]++;
+  for (unsigned char c : h) counts[c == 3 ? 2 : (c < 3 ? c : 0)]++;          // class 3 (x end only) is a boundary class
   return WL_OK;
 }
 

@@ -44,6 +44,7 @@ struct Level {
   DevField L, x, z, r, eps, Dg, iD;
   DevField tmp;              // second ϵ buffer of the paired sweeps (K-GS2 cannot update ϵ in place)
   unsigned char* ucore = nullptr; unsigned char* uflag = nullptr;   // pattern-tile classes (TileFlags, wl_common.cuh)
+  int* ulist = nullptr; int* ucount = nullptr; int ulist_n = 0;      // class-0/2 tiles: ids, device counter, count on the host
   int unx = 0, uny = 0, unz = 0;
   bool uvalid = false;       // classes match the level's current L (set by set_diag_h, cleared by uploads / measure!)
   float lu[3] = {1.f, 1.f, 1.f};   // the level's body-free face coefficient per direction (restrictL of all-ones)
@@ -432,14 +433,14 @@ int exitbc(wl_sim* s, DevField& u, DevField& u0, float dt) {
 // ---------------------------------------------------------------- multigrid pieces
 TileFlags tile_flags(const Level& p) {
   static const bool off = getenv("WL_NO_TILE_FLAGS") != nullptr;      // A/B switch: every tile takes the general path
-  TileFlags t{nullptr, 0, 0, {p.lu[0], p.lu[1], p.lu[2]}, 0.f, 0.f};
+  TileFlags t{nullptr, 0, 0, nullptr, {p.lu[0], p.lu[1], p.lu[2]}, 0.f, 0.f};
   float dg = 0.f;                                                    // set_diag! on an all-pattern interior cell
   dg -= p.lu[0] + p.lu[0]; dg -= p.lu[1] + p.lu[1]; dg -= p.lu[2] + p.lu[2];
   t.idu = dg == 0.f ? 0.f : 1.f / dg;
   float d1 = 0.f;                                                    // ... and on one next to an x boundary: (0 + lu) or
   d1 -= p.lu[0]; d1 -= p.lu[1] + p.lu[1]; d1 -= p.lu[2] + p.lu[2];   // (lu + 0) is lu exactly
   t.idx1 = d1 == 0.f ? 0.f : 1.f / d1;
-  if (p.uvalid && p.uflag && !off) { t.f = p.uflag; t.nx = p.unx; t.ny = p.uny; }
+  if (p.uvalid && p.uflag && !off) { t.f = p.uflag; t.nx = p.unx; t.ny = p.uny; t.list = p.ulist; }
   return t;
 }
 LevArgs lev_args(wl_sim* s, Level& p) {
@@ -522,14 +523,22 @@ int set_diag_h(wl_sim* s, Level& p) {
     if (!p.uflag || nx != p.unx || ny != p.uny || nz != p.unz) {
       if (p.ucore) cudaFree(p.ucore);
       if (p.uflag) cudaFree(p.uflag);
-      p.ucore = p.uflag = nullptr;
+      if (p.ulist) cudaFree(p.ulist);
+      if (p.ucount) cudaFree(p.ucount);
+      p.ucore = p.uflag = nullptr; p.ulist = p.ucount = nullptr;
       WL_CUDA(s, cudaMalloc(&p.ucore, (size_t)nx * ny * nz));
       WL_CUDA(s, cudaMalloc(&p.uflag, (size_t)nx * ny * nz));
+      WL_CUDA(s, cudaMalloc(&p.ulist, sizeof(int) * (size_t)nx * ny * nz));
+      WL_CUDA(s, cudaMalloc(&p.ucount, sizeof(int)));
       p.unx = nx; p.uny = ny; p.unz = nz;
     }
-    TileArgs t{p.lay, p.L.base, p.ucore, p.uflag, nx, ny, nz, p.per, {p.lu[0], p.lu[1], p.lu[2]}};
+    TileArgs t{p.lay, p.L.base, p.ucore, p.uflag, nx, ny, nz, p.per, {p.lu[0], p.lu[1], p.lu[2]}, p.ulist, p.ucount};
     LAUNCH(s, k_tile_core, dim3(nx, ny, nz), dim3(256), t);
     LAUNCH(s, k_tile_class, dim3((unsigned)std::min((nx * ny * nz + 255) / 256, 1184)), dim3(256), t);
+    LAUNCH(s, k_tile_list, dim3(1), dim3(1024), t);
+    // the number of class-0/2 tiles sizes the second launch of the split kernels: one small read-back per update!
+    WL_CUDA(s, cudaMemcpyAsync(&p.ulist_n, p.ucount, sizeof(int), cudaMemcpyDeviceToHost, s->st));
+    WL_CUDA(s, cudaStreamSynchronize(s->st));
     p.uvalid = true;
   }
   if (p.dist) return halo(s, p.iD, 1);
@@ -596,6 +605,24 @@ void fold_partials_to(wl_sim* s, const dim3& g, Red* out) {
   FoldArgs fa{s->redw, (int)(g.x * g.y * g.z), out};
   LAUNCH(s, k_fold_partials, dim3((unsigned)((fa.n + FOLD_CHUNK - 1) / FOLD_CHUNK)), dim3(1024), fa);
 }
+
+// K-DIVRES / K-DOWN as two launches when the level has tile classes (see split_tile in wl_kernels_mg4.cuh): the lean
+// instantiation over the grid of tiles, then the general one over the class-0/2 list.  WL_NO_SPLIT: one launch (A/B).
+inline bool split_ok(const Level& p) {
+  static const bool off = getenv("WL_NO_SPLIT") != nullptr;
+  // (below ~16 k tiles the second launch costs what the leaner first one saves: measured on the 256x128x128 level)
+  static const long long min_tiles = getenv("WL_SPLIT_MIN_TILES") ? atoll(getenv("WL_SPLIT_MIN_TILES")) : 16384;
+  return !off && p.uvalid && p.uflag && p.ulist && tile_flags(p).f != nullptr && (long long)p.unx * p.uny * p.unz >= min_tiles;
+}
+#define LAUNCH_SPLIT(s, kern, level, grid, args)                                            \
+  do {                                                                                      \
+    if (split_ok(level)) {                                                                  \
+      LAUNCH(s, kern<1>, grid, dim3(32, 4, 2), args);                                       \
+      if ((level).ulist_n > 0) LAUNCH(s, kern<2>, dim3((unsigned)(level).ulist_n), dim3(32, 4, 2), args); \
+    } else {                                                                                \
+      LAUNCH(s, kern<0>, grid, dim3(32, 4, 2), args);                                       \
+    }                                                                                       \
+  } while (0)
 
 // K-GS2 (wl_kernels_gs2.cuh): the four colour sweeps as two passes.  Single-GPU levels that the 4-cells-per-thread
 // kernels serve (row length a multiple of 4) with an even last dimension (half_rangek then sweeps every plane).
@@ -722,7 +749,7 @@ int vcycle(wl_sim* s, size_t l, float w, bool first = false) {
       if (use_vec4(fine.lay) && coarse.c[0] && coarse.c[1] && coarse.c[2]) {
         const dim3 gq = grid_quads(fine.lay);
         a.w.finish = finish_in_kernel(gq) ? 1 : 0;
-        LAUNCH(s, k_down4, gq, dim3(32, 4, 2), a);
+        LAUNCH_SPLIT(s, k_down4, fine, gq, a);
         if (first && !a.w.finish) fold_partials_to(s, gq, s->d_red + 10);
       } else {
         DISPATCH_D(s, k_down, dim3((unsigned)nt), blk(s->D), a);
@@ -1088,7 +1115,7 @@ int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
     if (use_vec4(s->lay)) {
       const dim3 gq = grid_quads(s->lay);
       d.w.finish = finish_in_kernel(gq) ? 1 : 0;
-      LAUNCH(s, k_divres4, gq, dim3(32, 4, 2), d);
+      LAUNCH_SPLIT(s, k_divres4, p0, gq, d);
       if (!d.w.finish) fold_partials_to(s, gq, s->d_red + 0);
     } else {
       DISPATCH_D(s, k_divres, grid_tiles(s->lay, false), blk(s->D), d);

@@ -73,8 +73,12 @@ struct Vec3 { float v[3]; };
 // (general path, loads).
 // Same values, same operations: bit-identical.  f == nullptr: no classes for this level (2D, rows not a multiple of 4,
 // switched off by an upload until the next update!).
+// Class 3 = a class-2 tile whose only boundary is an x end: every row of it (and of its y/z neighbours) is a plain row,
+// so a kernel compiled for classes 1 and 3 alone needs no coefficient or iD arrays at all -- K-DIVRES and K-DOWN run as
+// two launches, that lean one over the whole grid (class 0/2 blocks leave at once) and the general one over `list`.
 struct TileFlags {
   const unsigned char* f; int nx, ny;
+  const int* list;   // linear tile ids of the class-0 and class-2 tiles, ascending (the "list" launch of the split kernels), or null
   float lu[3];
   float idu;    // iD of a cell whose six faces hold the pattern constants
   float idx1;   // iD of a cell whose lower OR upper x face is a boundary face (0) and the other five hold the constants
@@ -190,7 +194,7 @@ __device__ __forceinline__ void fold_partials(const double* psum, const float* p
 
 // Reduction in two launches for kernels with ~10^5 blocks: every block leaves one partial
 // (block_reduce_partial, no fence, no atomic), k_fold_partials folds them in index order.
-__device__ __forceinline__ void block_reduce_partial(double s, float m, const RedWork w) {
+__device__ __forceinline__ void block_reduce_partial(double s, float m, const RedWork w, int bid = -1) {
   __shared__ double ssum[32];
   __shared__ float smax[32];
   const int tid = linear_tid();
@@ -203,7 +207,7 @@ __device__ __forceinline__ void block_reduce_partial(double s, float m, const Re
     s = lane < nw ? ssum[lane] : 0.0;
     m = lane < nw ? smax[lane] : -INFINITY;
     s = warp_sum(s); m = warp_max(m);
-    if (lane == 0) { const int b = linear_bid(); w.psum[b] = s; w.pmax[b] = m; }
+    if (lane == 0) { const int b = bid >= 0 ? bid : linear_bid(); w.psum[b] = s; w.pmax[b] = m; }
   }
 }
 struct FoldArgs { RedWork w; int n; Red* out; };

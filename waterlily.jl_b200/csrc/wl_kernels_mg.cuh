@@ -205,7 +205,7 @@ __device__ __forceinline__ float gs_update(const LevArgs& a, int cls, int i, int
     return s * a.uf.idu;
   }
   const int c3[3] = {i, j, k}, N3[3] = {l.n0, l.n1, l.n2};
-  if (D == 3 && cls == 2) {
+  if (D == 3 && cls >= 2) {
     const bool yz_plain = !(pattern_zero(a.per, 1, j, l.n1) || pattern_zero(a.per, 1, j + 1, l.n1) ||
                             pattern_zero(a.per, 2, k, l.n2) || pattern_zero(a.per, 2, k + 1, l.n2));
     if (yz_plain) {
@@ -265,10 +265,11 @@ __global__ void __launch_bounds__(256) k_gs_half_c(const LevArgs a) {
 
 // ---- pattern-tile classification (see TileFlags in wl_common.cuh).  Stage 1: core[t] = every cell of tile t -- its
 // interior cells, plus the ghost / halo row, column or plane next to a tile at the end of a direction, which the
-// kernels read as upper faces -- holds the pattern value in all three components.  Stage 2: class[t] = 0 unless t and
-// its 26 neighbours (wrapped across periodic directions, absent beyond the end of the others) are all core tiles;
+// kernels read as upper faces -- holds the pattern value in all three components (and the same for its first / last 32
+// columns alone).  Stage 2: class[t] = 0 unless t and its 26 neighbours (wrapped across periodic directions, absent beyond
+// the end of the others; of a neighbour to the left or right only the 32 columns next to t) hold the pattern;
 // then 2 if the tile touches the end of a non-periodic direction (physical boundary or slab interface), else 1.
-struct TileArgs { Lay l; const float* L; unsigned char* core; unsigned char* cls; int nx, ny, nz; Per per; float lu[3]; };
+struct TileArgs { Lay l; const float* L; unsigned char* core; unsigned char* cls; int nx, ny, nz; Per per; float lu[3]; int* list; int* count; };
 __global__ void __launch_bounds__(256) k_tile_core(const TileArgs a) {
   pdl_entry();
   const Lay& l = a.l;
@@ -293,11 +294,13 @@ __global__ void __launch_bounds__(256) k_tile_core(const TileArgs a) {
     for (int d = 0; d < 3; ++d) {
       if (ng == 1 && d != g) continue;                 // upper ghost: only its normal component is an upper face
       const float want = pattern_zero(a.per, d, c[d], N[d]) ? 0.f : a.lu[d];
-      bad |= a.L[l.cstride * d + o] != want;
+      if (a.L[l.cstride * d + o] != want) bad |= 1 | (c[0] < lo[0] + 32 ? 2 : 0) | (c[0] > hi[0] - 32 ? 4 : 0);
     }
   }
-  bad = __syncthreads_or(bad);
-  if (threadIdx.x == 0) a.core[blockIdx.x + a.nx * (blockIdx.y + a.ny * blockIdx.z)] = bad ? 0 : 1;
+  // bit 0: the whole tile holds the pattern; bits 1, 2: its first / last 32 columns do -- what an x neighbour needs of it
+  // (the kernels reach one cell, and that cell's faces, beyond a tile: a 128-cell-wide halo in x would be wasteful)
+  const int b0 = __syncthreads_or(bad & 1), b1 = __syncthreads_or(bad & 2), b2 = __syncthreads_or(bad & 4);
+  if (threadIdx.x == 0) a.core[blockIdx.x + a.nx * (blockIdx.y + a.ny * blockIdx.z)] = (b0 ? 0 : 1) | (b1 ? 0 : 2) | (b2 ? 0 : 4);
 }
 __global__ void __launch_bounds__(256) k_tile_class(const TileArgs a) {
   pdl_entry();
@@ -305,14 +308,16 @@ __global__ void __launch_bounds__(256) k_tile_class(const TileArgs a) {
   const int n[3] = {a.nx, a.ny, a.nz};
   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < nt; t += gridDim.x * blockDim.x) {
     const int c[3] = {t % a.nx, (t / a.nx) % a.ny, t / (a.nx * a.ny)};
-    int ok = 1, edge = 0;
+    int ok = 1, edge = 0, edge_yz = 0;
     // a tile is an edge tile if it holds a boundary-adjacent cell (index 1 or N-2: the first and the last tile of a
     // direction) or has one as a neighbour: the tile before the last when the last one is a single cell thick
     const int N3[3] = {a.l.n0, a.l.n1, a.l.n2}, ts[3] = {UT_X, UT_Y, UT_Z};
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
       const int last_thick = (N3[d] - 2) - ts[d] * (n[d] - 1);
-      edge |= !a.per.p[d] && (c[d] == 0 || c[d] == n[d] - 1 || (c[d] == n[d] - 2 && last_thick == 1));
+      const int e = !a.per.p[d] && (c[d] == 0 || c[d] == n[d] - 1 || (c[d] == n[d] - 2 && last_thick == 1));
+      edge |= e;
+      if (d > 0) edge_yz |= e;
     }
     for (int dz = -1; dz <= 1 && ok; ++dz)
       for (int dy = -1; dy <= 1 && ok; ++dy)
@@ -325,10 +330,33 @@ __global__ void __launch_bounds__(256) k_tile_class(const TileArgs a) {
               if (a.per.p[d]) q[d] = q[d] < 0 ? n[d] - 1 : 0; else absent = true;
             }
           }
-          if (!absent) ok = a.core[q[0] + a.nx * (q[1] + a.ny * q[2])];
+          if (!absent) ok = a.core[q[0] + a.nx * (q[1] + a.ny * q[2])] & (dx == 0 ? 1 : (dx < 0 ? 4 : 2));
         }
-    a.cls[t] = (unsigned char)(ok ? (edge ? 2 : 1) : 0);
+    a.cls[t] = (unsigned char)(ok ? (edge ? (edge_yz ? 2 : 3) : 1) : 0);
   }
+}
+
+// The class-0/2 tiles in ascending order (the second launch of the split kernels walks them: neighbours in the list are
+// neighbours in memory).  One block: every thread counts its contiguous chunk, the block scans the counts, every thread
+// writes its chunk's ids from its offset.
+__global__ void __launch_bounds__(1024) k_tile_list(const TileArgs a) {
+  pdl_entry();
+  __shared__ int cnt[1024];
+  const int nt = a.nx * a.ny * a.nz, per = (nt + 1023) / 1024;
+  const int t0 = min(nt, (int)threadIdx.x * per), t1 = min(nt, t0 + per);
+  int c = 0;
+  for (int t = t0; t < t1; ++t) c += (a.cls[t] == 0 || a.cls[t] == 2);
+  cnt[threadIdx.x] = c;
+  __syncthreads();
+  for (int off = 1; off < 1024; off <<= 1) {                       // inclusive scan
+    const int v = threadIdx.x >= off ? cnt[threadIdx.x - off] : 0;
+    __syncthreads();
+    cnt[threadIdx.x] += v;
+    __syncthreads();
+  }
+  int o = cnt[threadIdx.x] - c;
+  for (int t = t0; t < t1; ++t) if (a.cls[t] == 0 || a.cls[t] == 2) a.list[o++] = t;
+  if (threadIdx.x == 1023) *a.count = cnt[1023];
 }
 
 // The half sweep with the slab-interface exchange FUSED in (multi-GPU, peer-mapped arenas; host side in

@@ -54,6 +54,14 @@ __device__ __forceinline__ QuadL quad_coeffs(const float* L, const Lay& l, const
     const float* Lx = L; const float* Ly = L + l.cstride; const float* Lz = L + 2 * l.cstride;
     q.lx = ld4g(Lx + o); q.lx4 = __ldg(Lx + o + 4);
     q.ly0 = ld4g(Ly + o); q.ly1 = ld4g(Ly + o + l.pitch); q.lz0 = ld4g(Lz + o); q.lz1 = ld4g(Lz + o + l.plane);
+  } else if (CLS == 3) {
+    // a tile whose only boundary is an x end (the split kernels' first launch): two selects, constants otherwise
+    const bool z0 = pattern_zero(per, 0, i, l.n0), z4 = pattern_zero(per, 0, i + 4, l.n0);
+    q.xq = 1 + (z0 ? 1 : 0) + (z4 ? 2 : 0);
+    q.lx = F4{{z0 ? 0.f : t.lu[0], t.lu[0], t.lu[0], t.lu[0]}};
+    q.lx4 = z4 ? 0.f : t.lu[0];
+    q.ly0 = q.ly1 = F4{{t.lu[1], t.lu[1], t.lu[1], t.lu[1]}};
+    q.lz0 = q.lz1 = F4{{t.lu[2], t.lu[2], t.lu[2], t.lu[2]}};
   } else if (CLS == 2 && !(pattern_zero(per, 1, j, l.n1) || pattern_zero(per, 1, j + 1, l.n1) ||
                            pattern_zero(per, 2, k, l.n2) || pattern_zero(per, 2, k + 1, l.n2))) {
     const bool z0 = pattern_zero(per, 0, i, l.n0), z4 = pattern_zero(per, 0, i + 4, l.n0);
@@ -63,7 +71,7 @@ __device__ __forceinline__ QuadL quad_coeffs(const float* L, const Lay& l, const
     q.ly0 = q.ly1 = F4{{t.lu[1], t.lu[1], t.lu[1], t.lu[1]}};
     q.lz0 = q.lz1 = F4{{t.lu[2], t.lu[2], t.lu[2], t.lu[2]}};
   } else {
-    auto f = [&](int d, int c, int n) { return (CLS == 2 && pattern_zero(per, d, c, n)) ? 0.f : t.lu[d]; };
+    auto f = [&](int d, int c, int n) { return (CLS >= 2 && pattern_zero(per, d, c, n)) ? 0.f : t.lu[d]; };
 #pragma unroll
     for (int c = 0; c < 4; ++c) q.lx.v[c] = f(0, i + c, l.n0);
     q.lx4 = f(0, i + 4, l.n0);
@@ -78,7 +86,7 @@ template <int CLS>
 __device__ __forceinline__ F4 quad_iD(const float* iD, const QuadL& q, const TileFlags& t, int o) {
   if (CLS == 0) return ld4g(iD + o);
   if (CLS == 1) return F4{{t.idu, t.idu, t.idu, t.idu}};
-  if (q.xq) return F4{{((q.xq - 1) & 1) ? t.idx1 : t.idu, t.idu, t.idu, ((q.xq - 1) & 2) ? t.idx1 : t.idu}};   // xq-1 = z0 + 2·z4
+  if (CLS == 3 || q.xq) return F4{{((q.xq - 1) & 1) ? t.idx1 : t.idu, t.idu, t.idu, ((q.xq - 1) & 2) ? t.idx1 : t.idu}};   // xq-1 = z0 + 2·z4
   F4 d;
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
@@ -91,7 +99,7 @@ __device__ __forceinline__ F4 quad_iD(const float* iD, const QuadL& q, const Til
 #define WL_CLASS_DISPATCH(cls, body)                                              \
   do {                                                                            \
     if ((cls) == 1) body(std::integral_constant<int, 1>{});                       \
-    else if ((cls) == 2) body(std::integral_constant<int, 2>{});                  \
+    else if ((cls) >= 2) body(std::integral_constant<int, 2>{});                  \
     else body(std::integral_constant<int, 0>{});                                  \
   } while (0)
 inline bool vec4_ok(const Lay& l) { return l.D == 3 && (l.n0 - 2) % 4 == 0 && l.n0 - 2 >= 8; }
@@ -102,6 +110,36 @@ inline bool vec4_ok(const Lay& l) { return l.D == 3 && (l.n0 - 2) % 4 == 0 && l.
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;                      \
   const int k = blockIdx.z * blockDim.z + threadIdx.z + 1;                      \
   const bool inb = !(i > l.n0 - 2 || j > l.n1 - 2 || k > l.n2 - 2);
+
+// The split kernels (K-DIVRES, K-DOWN).  MODE 0: one launch over the grid of tiles, every class.  MODE 1: the same grid,
+// compiled for classes 1 and 3 only (constants + x-end selects: no coefficient or iD arrays, 56 instead of 77-80
+// registers, one more resident block per SM); blocks of class 0 / 2 tiles leave at once.  MODE 2: a 1-D launch over
+// TileFlags::list, the class 0 / 2 tiles, with the general code.  (Serving the y/z boundary tiles from the lean
+// instantiation too -- iD from a 27-entry table -- was measured: it slows the common rows more than the shorter list
+// saves, profiles/r2_c28_*.)  A tile's reduction partial is stored at the tile's linear index in every mode, so the
+// folded sums do not depend on the split.
+template <int MODE>
+__device__ __forceinline__ bool split_tile(const TileFlags& uf, int& bx, int& by, int& bz, int& cls) {
+  if (MODE == 2) {
+    const int t = uf.list[blockIdx.x];
+    bx = t % uf.nx; by = (t / uf.nx) % uf.ny; bz = t / (uf.nx * uf.ny);
+  } else {
+    bx = blockIdx.x; by = blockIdx.y; bz = blockIdx.z;
+  }
+  cls = tile_class(uf, bx, by, bz);
+  return !(MODE == 1 && (cls == 0 || cls == 2));
+}
+#define WL_QUAD_FROM_TILE(l, bx, by, bz)                                        \
+  const int i = 1 + 4 * ((bx) * blockDim.x + threadIdx.x);                      \
+  const int j = (by) * blockDim.y + threadIdx.y + 1;                            \
+  const int k = (bz) * blockDim.z + threadIdx.z + 1;                            \
+  const bool inb = !(i > l.n0 - 2 || j > l.n1 - 2 || k > l.n2 - 2);
+#define WL_SPLIT_DISPATCH(MODE, cls, body)                                        \
+  do {                                                                            \
+    if (MODE == 1) body(std::integral_constant<int, 3>{});                        \
+    else if (MODE == 2) { if ((cls) == 2) body(std::integral_constant<int, 2>{}); else body(std::integral_constant<int, 0>{}); } \
+    else WL_CLASS_DISPATCH(cls, body);                                            \
+  } while (0)
 
 // y/z neighbour offsets of the quad's row (wrapped across periodic seams) and the x offsets of the
 // cell left of the quad / right of it
@@ -219,12 +257,14 @@ __global__ void __launch_bounds__(256) k_cfl4(const CflArgs a) {
 }
 
 // ---------------------------------------------------------------- K-DIVRES, 4 cells per thread (see k_divres)
-__global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_divres4(const DivResArgs a) {
+template <int MODE>
+__global__ void __launch_bounds__(256, MODE == 1 ? WL_MG4_MINB_A : WL_MG4_MINB_B) k_divres4(const DivResArgs a) {
   pdl_entry();
   const Lay& l = a.l;
-  WL_QUAD_FROM_BLOCK(l)
+  int bx, by, bz, cls;                                                    // class first: see k_incr4
+  if (!split_tile<MODE>(a.uf, bx, by, bz, cls)) return;
+  WL_QUAD_FROM_TILE(l, bx, by, bz)
   double s = 0.0;
-  const int cls = tile_class(a.uf, blockIdx.x, blockIdx.y, blockIdx.z);   // first: see k_incr4
   if (inb) {
   const int o = l.off(i, j, k);
   int oxm, oxp, oym, oyp, ozm, ozp;
@@ -263,10 +303,10 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_divres4(const DivResArgs
     st4(a.r + o, rr);
     st4(a.xs + o, xs);
   };
-  WL_CLASS_DISPATCH(cls, body);
+  WL_SPLIT_DISPATCH(MODE, cls, body);
   }
-  if (a.w.finish) block_reduce_finish(s, -INFINITY, a.w, a.out);
-  else block_reduce_partial(s, -INFINITY, a.w);
+  if (MODE == 0 && a.w.finish) block_reduce_finish(s, -INFINITY, a.w, a.out);
+  else block_reduce_partial(s, -INFINITY, a.w, MODE == 0 ? -1 : bx + a.uf.nx * (by + a.uf.ny * bz));
 }
 
 // ---------------------------------------------------------------- K-PROJ, 4 cells per thread (see k_proj)
@@ -286,7 +326,7 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_proj4(const ProjArgs2 a)
   const int cls = tile_class(a.uf, blockIdx.x, blockIdx.y, blockIdx.z);
   if (cls == 0) { lx = ld4g(a.L + o); ly = ld4g(a.L + l.cstride + o); lz = ld4g(a.L + 2 * l.cstride + o); }
   else {
-    auto f = [&](int d, int c, int n) { return (cls == 2 && pattern_zero(a.per, d, c, n)) ? 0.f : a.uf.lu[d]; };
+    auto f = [&](int d, int c, int n) { return (cls >= 2 && pattern_zero(a.per, d, c, n)) ? 0.f : a.uf.lu[d]; };
 #pragma unroll
     for (int c = 0; c < 4; ++c) lx.v[c] = f(0, i + c, l.n0);
     const float a0 = f(1, j, l.n1), b0 = f(2, k, l.n2);
@@ -392,12 +432,15 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_up4(const UpArgs a) {
 // ---------------------------------------------------------------- K-DOWN, 4 cells per thread (see k_down)
 // Jacobi! (ϵ=r·iD, perBC!, increment! with ω=1) + restrict! + fill!(coarse.x,0), for levels coarsened
 // in every direction.  blockDim (32,4,2): the block's 128x4x2 cells are the children of 64x2x1 coarse cells.
-__global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_down4(const DownArgs a) {
+template <int MODE>
+__global__ void __launch_bounds__(256, MODE == 1 ? WL_MG4_MINB_A : WL_MG4_MINB_B) k_down4(const DownArgs a) {
   pdl_entry();
   __shared__ float tile[2][4][128];
   const Lay& l = a.f.l;
   const Lay& lc = a.c.l;
-  WL_QUAD_FROM_BLOCK(l)
+  int bx, by, bz, cls;
+  if (!split_tile<MODE>(a.f.uf, bx, by, bz, cls)) return;              // (block-uniform: no thread is left at the barrier)
+  WL_QUAD_FROM_TILE(l, bx, by, bz)
   double s1 = 0.0; float mx = -INFINITY;
   float sh = 0.f;                                                      // residual mean to remove (first cycle only)
   if (a.first) {
@@ -416,11 +459,19 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_down4(const DownArgs a) 
        rzp = ld4g(a.f.r + o + ozp);
     float rxm = __ldg(a.f.r + o + oxm), rxp = __ldg(a.f.r + o + oxp);
     // iD of the quad and of its six neighbours: class 1 -- the tile AND its neighbouring tiles hold the constants and no
-    // boundary is near, so every one of them is idu; class 2 (boundary / interface tiles) loads the neighbours' values
+    // boundary is near, so every one of them is idu; class 3 -- an x end is the only boundary near, see below; class 2
+    // (y/z boundary or interface tiles) loads the neighbours'
     const F4 d = quad_iD<CLS>(a.f.iD, ql, a.f.uf, o);
     F4 dym = d, dyp = d, dzm = d, dzp = d;
-    float dxm = d.v[0], dxp = d.v[0];
-    if (CLS != 1) {
+    float dxm = a.f.uf.idu, dxp = a.f.uf.idu;
+    if (CLS == 3) {
+      // a neighbour beyond a boundary face is a ghost cell (iD 0: set_diag! never writes it); any other neighbour row has
+      // the quad's x pattern and its own count of y/z boundary faces
+      // the y/z neighbours sit at the same x as the quad's cells and have their iD (dym..dzp were initialised with d); the
+      // x neighbours are a plain cell or the ghost cell beyond the boundary face (iD 0: set_diag! never writes it)
+      if ((ql.xq - 1) & 1) dxm = 0.f;
+      if ((ql.xq - 1) & 2) dxp = 0.f;
+    } else if (CLS != 1) {
       dym = ld4g(a.f.iD + o + oym); dyp = ld4g(a.f.iD + o + oyp); dzm = ld4g(a.f.iD + o + ozm); dzp = ld4g(a.f.iD + o + ozp);
       dxm = __ldg(a.f.iD + o + oxm); dxp = __ldg(a.f.iD + o + oxp);
     }
@@ -454,7 +505,7 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_down4(const DownArgs a) 
     st4(a.f.eps + o, rn);          // neighbours still read r: the new residual is staged in ϵ (host swaps the pointers)
     st4(a.f.x + o, xn);
   };
-  if (inb) WL_CLASS_DISPATCH(tile_class(a.f.uf, blockIdx.x, blockIdx.y, blockIdx.z), body);
+  if (inb) WL_SPLIT_DISPATCH(MODE, cls, body);
   {
     float* t = &tile[threadIdx.z][threadIdx.y][4 * threadIdx.x];
     t[0] = rn.v[0]; t[1] = rn.v[1]; t[2] = rn.v[2]; t[3] = rn.v[3];
@@ -476,7 +527,10 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_down4(const DownArgs a) 
       a.c.x[oc + p] = 0.f;                                             // fill!(coarse.x,0)  MLP.jl:94
     }
   }
-  if (a.first) { if (a.w.finish) block_reduce_finish(s1, mx, a.w, a.out); else block_reduce_partial(s1, mx, a.w); }
+  if (a.first) {
+    if (MODE == 0 && a.w.finish) block_reduce_finish(s1, mx, a.w, a.out);
+    else block_reduce_partial(s1, mx, a.w, MODE == 0 ? -1 : bx + a.f.uf.nx * (by + a.f.uf.ny * bz));
+  }
 }
 
 }  // namespace wl
