@@ -15,10 +15,15 @@
 
 #include "wl_kernels_mg2.cuh"
 
-// resident blocks per SM the register allocation is held to.  K-UP fits 64 registers without spilling (50 %
-// occupancy instead of 37.5 %; ncu showed it latency-bound, 60 % DRAM at 32 % warps active): 54.7 -> 51.2 us
-// per launch averaged over the levels of config C.  K-PROJ is already DRAM-bound (no gain), K-DOWN and
-// K-DIVRES would spill 40-80 bytes (measured 40 % and 4 % slower): they keep the 3-block allocation
+// Resident blocks per SM the register allocation is held to (second __launch_bounds__ argument).  These kernels live
+// for one memory round trip, so what they gain from more warps in flight outweighs a few spilled bytes -- measured per
+// kernel on the sphere grid (profiles/r2_c34_*, r2_c35_*, r2_c36_*; level-1 launch, us):
+//   k_proj4   3 blocks (70 regs) 206 | 4 (64) 180 | 5 (48, 8 B spilled) 170      -> 5
+//   k_up4     4 (64) 168 | 5 (48, 32 B spilled) 161                              -> 5
+//   k_down4<1> (lean instantiation)  4 (56) 158 | 5 (43) 138 | 6 (40) 127        -> 6
+//   k_divres4<1>                     4 (56) 158 | 5 (48, 32 B spilled) 174       -> 4
+//   k_incr4   4 (64) 148 | 5 (48, 72 B spilled) 150                              -> 4
+// The general instantiations (k_down4<0/2>, k_divres4<0/2>) need 77-80 registers and spill when held to 64: 3 blocks.
 #ifndef WL_MG4_MINB_A
 #define WL_MG4_MINB_A 4
 #endif
@@ -310,7 +315,7 @@ __global__ void __launch_bounds__(256, MODE == 1 ? WL_MG4_MINB_A : WL_MG4_MINB_B
 }
 
 // ---------------------------------------------------------------- K-PROJ, 4 cells per thread (see k_proj)
-__global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_proj4(const ProjArgs2 a) {
+__global__ void __launch_bounds__(256, 5) k_proj4(const ProjArgs2 a) {
   pdl_entry();
   const Lay& l = a.l;
   WL_QUAD_FROM_BLOCK(l)
@@ -368,7 +373,7 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_B) k_proj4(const ProjArgs2 a)
 
 // ---------------------------------------------------------------- K-UP, 4 cells per thread (see k_up)
 // prolongate! + perBC! + increment!(ω) (+ ϵ = r·iD for the smoother that follows).  Any coarsening mask.
-__global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_up4(const UpArgs a) {
+__global__ void __launch_bounds__(256, 5) k_up4(const UpArgs a) {
   pdl_entry();
   const Lay& l = a.f.l;
   const Lay& lc = a.c.l;
@@ -433,7 +438,7 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_up4(const UpArgs a) {
 // Jacobi! (ϵ=r·iD, perBC!, increment! with ω=1) + restrict! + fill!(coarse.x,0), for levels coarsened
 // in every direction.  blockDim (32,4,2): the block's 128x4x2 cells are the children of 64x2x1 coarse cells.
 template <int MODE>
-__global__ void __launch_bounds__(256, MODE == 1 ? WL_MG4_MINB_A : WL_MG4_MINB_B) k_down4(const DownArgs a) {
+__global__ void __launch_bounds__(256, MODE == 1 ? 6 : WL_MG4_MINB_B) k_down4(const DownArgs a) {
   pdl_entry();
   __shared__ float tile[2][4][128];
   const Lay& l = a.f.l;
