@@ -173,9 +173,11 @@ class ClockSampler:
 NCU_TRAFFIC = {
     ("tgv", (128, 128, 128)): ("profiles/r1_v15_ncu_full_kmom3_tgv128.tsv (most of the 128^3 working set stays in the 126 MB L2)",
                                {"k_mom3": (32.50e6 + 0.21e6 + 58.01e6 + 4.11e6) / 2}),
-    ("sphere", (512, 256, 256)): ("profiles/r1_v15_ncu_full_kmom3_sphere512.tsv, r1_v14_ncu_full_sphere512.tsv, r1_v16_ncu_full_mg4_sphere512.tsv (level-1 launches)",
-                                  {"k_mom3": (1273.3e6 + 387.2e6 + 1678.3e6 + 389.9e6) / 2, "k_divres4": 1221e6, "k_down4": 1117e6,
-                                   "k_up4": 1202e6, "k_proj4": 1440e6, "k_gs_half_c": 803e6}),
+    # k_mom3: predictor launch of this round (1269 + 386 MB; round 1: 1273 + 387) and the corrector launch of round 1 (1678 + 390 MB:
+    # it also reads u0); pressure kernels: this round's level-1 launches with pattern tiles (k_down4: the one-launch form)
+    ("sphere", (512, 256, 256)): ("profiles/r2_c15_ncu_kmom3_kdown4.txt, r2_c34_launch_bounds_ab.md (k_proj4, k_incr4, k_gs_half_c), r1_v15_ncu_full_kmom3_sphere512.tsv (corrector launch)",
+                                  {"k_mom3": (1269.2e6 + 386.5e6 + 1678.3e6 + 389.9e6) / 2, "k_down4": 431.4e6 + 263.7e6,
+                                   "k_proj4": 560.4e6 + 480.2e6, "k_incr4": 428.0e6 + 220.7e6, "k_gs_half_c": 289.2e6 + 90.5e6}),
 }
 
 
