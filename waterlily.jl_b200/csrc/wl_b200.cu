@@ -557,11 +557,22 @@ void vcycle_v1(wl_sim* s, size_t l, float w) {
 }
 
 // ---- v2: fused kernels (wl_kernels_mg2.cuh)
+// L2 prefetch distance of the 4-cells-per-thread kernels (pf4, wl_kernels_mg4.cuh): ~1.5 waves of blocks (5 resident per
+// SM) in planes (a block layer is 2 planes thick); off on levels that fit the L2 anyway.  WL_PREFETCH=<planes> overrides.
+int prefetch_planes(const Lay& l) {
+  static const int env = getenv("WL_PREFETCH") ? atoi(getenv("WL_PREFETCH")) : -1;
+  if (l.D != 3 || !vec4_ok(l)) return 0;
+  const long long per_layer = (long long)((l.n0 - 2 + 127) / 128) * ((l.n1 - 2 + 3) / 4), layers = (l.n2 - 2 + 1) / 2;
+  if (per_layer * layers < 148 * 5 * 4) return 0;
+  if (env >= 0) return env;
+  return (int)std::min<long long>(16, 2 * ((148 * 5 * 3 / 2 + per_layer - 1) / per_layer));
+}
 LevDev levdev(const Level& p) {
   LevDev d{};
   d.l = p.lay; d.L = p.L.base; d.iD = p.iD.base; d.x = p.x.base; d.r = p.r.base; d.eps = p.eps.base;
   for (int q = 0; q < 3; ++q) d.c[q] = p.c[q];
   d.uf = tile_flags(p);
+  d.pf = prefetch_planes(p.lay);
   return d;
 }
 // the rank's window into a REPLICATED coarse level as seen from the DISTRIBUTED level above it:
@@ -695,6 +706,13 @@ int smooth2(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready = false) {
     x.my = reinterpret_cast<unsigned int*>(s->arena);
     x.nb_lo = reinterpret_cast<unsigned int*>(s->peer_lo);
     x.nb_hi = reinterpret_cast<unsigned int*>(s->peer_hi);
+  }
+  {
+    // prefetch distance: ~1.5 waves of blocks (8 resident per SM) expressed in planes of 2-plane block layers
+    static const int pf_env = getenv("WL_PREFETCH") ? atoi(getenv("WL_PREFETCH")) : -1;
+    const long long per_layer = (long long)gg.x * gg.y;
+    g.pf = pf_env >= 0 ? pf_env : (per_layer > 0 ? (int)std::min<long long>(16, 2 * ((148 * 8 * 3 / 2 + per_layer - 1) / per_layer)) : 0);
+    if (per_layer * gg.z < 148 * 8 * 2) g.pf = 0;            // small levels live in L2 anyway
   }
   for (int k0 = 1; k0 <= 4; ++k0) {
     g.k0 = k0;
@@ -1111,7 +1129,7 @@ int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
   if (!(s->cfg.flags & WL_FLAG_NO_FUSED)) {
     Level& p0 = s->lv[0];
     const float dt = w * s->dt;
-    DivResArgs d{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, p0.r.base, s->per, dt, s->redw, s->d_red + 0, tile_flags(p0)};
+    DivResArgs d{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, p0.r.base, s->per, dt, s->redw, s->d_red + 0, tile_flags(p0), prefetch_planes(s->lay)};
     if (use_vec4(s->lay)) {
       const dim3 gq = grid_quads(s->lay);
       d.w.finish = finish_in_kernel(gq) ? 1 : 0;

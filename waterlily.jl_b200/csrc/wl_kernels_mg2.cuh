@@ -27,6 +27,7 @@ struct LevDev {
   float* eps;
   int c[3];          // coarsening mask from the next finer level to this one
   TileFlags uf;      // uniform-coefficient tiles of this level (4-cells-per-thread kernels)
+  int pf;            // 4-cells-per-thread kernels: planes ahead whose lines are prefetched into L2 (0 = off), see pf4()
 };
 
 // offsets of the lower/upper neighbour in direction d for an INTERIOR cell, wrapped when periodic.
@@ -125,7 +126,7 @@ __device__ __forceinline__ float multA_w(const Lay& l, const float* __restrict__
 // pointers) because neighbours still read the unscaled x.  Non-periodic ghosts of every scalar work
 // array are zero for the whole run, periodic ghosts are rewritten by whoever needs them, so the
 // buffers are interchangeable.
-struct DivResArgs { Lay l; const float* u; const float* x; float* xs; const float* L; float* r; Per per; float dt; RedWork w; Red* out; TileFlags uf; };
+struct DivResArgs { Lay l; const float* u; const float* x; float* xs; const float* L; float* r; Per per; float dt; RedWork w; Red* out; TileFlags uf; int pf; };
 template <int D>
 __global__ void __launch_bounds__(256) k_divres(const DivResArgs a) {
   pdl_entry();

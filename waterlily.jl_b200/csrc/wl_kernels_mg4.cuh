@@ -109,6 +109,11 @@ __device__ __forceinline__ F4 quad_iD(const float* iD, const QuadL& q, const Til
   } while (0)
 inline bool vec4_ok(const Lay& l) { return l.D == 3 && (l.n0 - 2) % 4 == 0 && l.n0 - 2 >= 8; }
 
+// These kernels live for one memory round trip and blocks are issued in z order: a thread asks for the 16 bytes its
+// counterpart `pf` planes further on (a block ~1.5 waves later) will load, so that those loads hit L2 (a warp's requests
+// fall on four lines).  Measured on the half sweep: 97 -> 91 us (profiles/r2_c38_*).
+__device__ __forceinline__ void pf4(const float* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // thread -> first cell of its quad; blockDim = (32,4,2) covers 128 x 4 x 2 cells
 #define WL_QUAD_FROM_BLOCK(l)                                                   \
   const int i = 1 + 4 * (blockIdx.x * blockDim.x + threadIdx.x);                \
@@ -187,6 +192,7 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_incr4(const SmArgs a) {
            ezm = ld4(a.p.eps + o + ozm), ezp = ld4(a.p.eps + o + ozp);
   const float exm = a.p.eps[o + oxm], exp_ = a.p.eps[o + oxp];
   const F4 r0 = ld4(a.p.r + o), x0 = ld4(a.p.x + o);
+  if (a.p.pf > 0 && k + a.p.pf <= l.n2 - 2) { const int q = o + a.p.pf * l.plane; pf4(a.p.eps + q); pf4(a.p.r + q); pf4(a.p.x + q); }
   auto body = [&](auto tag) {
     constexpr int CLS = decltype(tag)::value;
     const QuadL ql = quad_coeffs<CLS>(a.p.L, l, a.per, a.p.uf, o, i, j, k);
@@ -280,6 +286,7 @@ __global__ void __launch_bounds__(256, MODE == 1 ? WL_MG4_MINB_A : WL_MG4_MINB_B
   const F4 x = ld4g(a.x + o), xym = ld4g(a.x + o + oym), xyp = ld4g(a.x + o + oyp),
            xzm = ld4g(a.x + o + ozm), xzp = ld4g(a.x + o + ozp);
   const float xxm = __ldg(a.x + o + oxm), xxp = __ldg(a.x + o + oxp);
+  if (a.pf > 0 && k + a.pf <= l.n2 - 2) { const int q = o + a.pf * l.plane; pf4(ux + q); pf4(uy + q); pf4(uz + q); pf4(a.x + q); }
   auto body = [&](auto tag) {
     constexpr int CLS = decltype(tag)::value;
     const QuadL ql = quad_coeffs<CLS>(a.L, l, a.per, a.uf, o, i, j, k);
@@ -327,6 +334,8 @@ __global__ void __launch_bounds__(256, 5) k_proj4(const ProjArgs2 a) {
   const float xxm = __ldg(a.x + o + oxm);
   float* ux = a.u; float* uy = a.u + l.cstride; float* uz = a.u + 2 * l.cstride;
   const F4 u0 = ld4(ux + o), v0 = ld4(uy + o), w0 = ld4(uz + o);
+  // (no pf4 here: K-PROJ streams 16 B/cell in and 16 B/cell out at 97 % of the bandwidth; prefetching its four inputs made
+  //  it 7 % slower, profiles/r2_c39_*)
   F4 lx, ly, lz;                                        // lower faces only (Flow.jl:228)
   const int cls = tile_class(a.uf, blockIdx.x, blockIdx.y, blockIdx.z);
   if (cls == 0) { lx = ld4g(a.L + o); ly = ld4g(a.L + l.cstride + o); lz = ld4g(a.L + 2 * l.cstride + o); }
@@ -396,6 +405,7 @@ __global__ void __launch_bounds__(256, 5) k_up4(const UpArgs a) {
   const F4 e = row(cj, ck), eym = row(dn(cy, jm), ck), eyp = row(dn(cy, jp), ck), ezm = row(cj, dn(cz, km)), ezp = row(cj, dn(cz, kp));
   const float* pc = a.c.x + lc.pitch * cj + lc.plane * ck;
   const float exm = __ldg(pc + dn(cx, im)), exp_ = __ldg(pc + dn(cx, ip));
+  if (a.f.pf > 0 && k + a.f.pf <= l.n2 - 2) { const int q = o + a.f.pf * l.plane; pf4(a.f.r + q); pf4(a.f.x + q); }
   auto body = [&](auto tag) {
   constexpr int CLS = decltype(tag)::value;
   const QuadL ql = quad_coeffs<CLS>(a.f.L, l, a.per, a.f.uf, o, i, j, k);
@@ -510,6 +520,7 @@ __global__ void __launch_bounds__(256, MODE == 1 ? 6 : WL_MG4_MINB_B) k_down4(co
     st4(a.f.eps + o, rn);          // neighbours still read r: the new residual is staged in ϵ (host swaps the pointers)
     st4(a.f.x + o, xn);
   };
+  if (inb && a.f.pf > 0 && k + a.f.pf <= l.n2 - 2) { const int q = l.off(i, j, k) + a.f.pf * l.plane; pf4(a.f.r + q); pf4(a.f.x + q); }
   if (inb) WL_SPLIT_DISPATCH(MODE, cls, body);
   {
     float* t = &tile[threadIdx.z][threadIdx.y][4 * threadIdx.x];
