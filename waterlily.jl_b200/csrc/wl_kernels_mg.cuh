@@ -407,6 +407,10 @@ __global__ void __launch_bounds__(256) k_gs_half_cx(const LevArgs a, const GsLin
     float em[3], ep[3];
 #pragma unroll
     for (int q = 0; q < D; ++q) { em[q] = a.eps[o - st[q]]; ep[q] = a.eps[o + st[q]]; }   // before the branch on cls
+    if (a.pf > 0 && k + a.pf <= l.n2 - 2) {                // as in k_gs_half_c (after the two boundary layers z runs upwards)
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(a.r + o + a.pf * l.plane));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(a.eps + o + a.pf * l.plane));
+    }
     const float v = gs_update<D>(a, cls, i, j, k, o, r0, em, ep);
     a.eps[o] = v;
     if (x.push_lo && k == 1) x.peer_lo[o + l.plane * (l.n2 - 2)] = v;
