@@ -608,10 +608,9 @@ bool use_vec4(const Lay& l) {
 dim3 grid_quads(const Lay& l, int cells_per_thread = 4) {
   return dim3((l.n0 - 2 + 32 * cells_per_thread - 1) / (32 * cells_per_thread), (l.n1 - 2 + 3) / 4, (l.n2 - 2 + 1) / 2);
 }
-// Reductions of the vectorised kernels: every block leaves one partial, a 1-block k_fold_partials launch folds them in
+// Reductions of the vectorised kernels: every block leaves one partial, a k_fold_partials launch folds them in
 // index order (with dependent launches that is cheaper than a fence + atomic ticket in every block: TGV 128³ 0.301 vs
 // 0.314, sphere 512x256² 0.182 vs 0.189 ns/cell/step, round 1).
-inline bool finish_in_kernel(const dim3&) { return false; }
 void fold_partials_to(wl_sim* s, const dim3& g, Red* out) {
   FoldArgs fa{s->redw, (int)(g.x * g.y * g.z), out};
   LAUNCH(s, k_fold_partials, dim3((unsigned)((fa.n + FOLD_CHUNK - 1) / FOLD_CHUNK)), dim3(1024), fa);
@@ -682,9 +681,8 @@ int smooth2(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready = false) {
     gs_pairs(s, p);
     a.p = levdev(p);                                  // ϵ now lives in the other buffer
     const dim3 gq = grid_quads(p.lay);
-    a.w.finish = finish_in_kernel(gq) ? 1 : 0;
     LAUNCH(s, k_incr4, gq, dim3(32, 4, 2), a);
-    if (norms && !a.w.finish) fold_partials_to(s, gq, norms);
+    if (norms) fold_partials_to(s, gq, norms);
     return WL_OK;
   }
   if (!eps_ready) DISPATCH_D(s, k_eps_init_g, grid_inside(p.lay), blk(s->D), a);   // else K-UP left ϵ = r·iD behind
@@ -735,9 +733,8 @@ int smooth2(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready = false) {
   }
   if (v4) {
     const dim3 gq = grid_quads(p.lay);
-    a.w.finish = finish_in_kernel(gq) ? 1 : 0;
     LAUNCH(s, k_incr4, gq, dim3(32, 4, 2), a);
-    if (norms && !a.w.finish) fold_partials_to(s, gq, norms);
+    if (norms) fold_partials_to(s, gq, norms);
   } else {
     DISPATCH_D(s, k_increment_w, grid_tiles(p.lay, false), blk(s->D), a);
   }
@@ -766,9 +763,8 @@ int vcycle(wl_sim* s, size_t l, float w, bool first = false) {
       const long long nt = (long long)g3.x * g3.y * g3.z;
       if (use_vec4(fine.lay) && coarse.c[0] && coarse.c[1] && coarse.c[2]) {
         const dim3 gq = grid_quads(fine.lay);
-        a.w.finish = finish_in_kernel(gq) ? 1 : 0;
         LAUNCH_SPLIT(s, k_down4, fine, gq, a);
-        if (first && !a.w.finish) fold_partials_to(s, gq, s->d_red + 10);
+        if (first) fold_partials_to(s, gq, s->d_red + 10);
       } else {
         DISPATCH_D(s, k_down, dim3((unsigned)nt), blk(s->D), a);
         if (first) fold_partials_to(s, dim3((unsigned)nt), s->d_red + 10);
@@ -1132,9 +1128,8 @@ int mom_project(wl_sim* s, float w, const float* U, Trace* tr) {
     DivResArgs d{s->lay, s->u.base, s->p.base, p0.eps.base, s->mu0.base, p0.r.base, s->per, dt, s->redw, s->d_red + 0, tile_flags(p0), prefetch_planes(s->lay)};
     if (use_vec4(s->lay)) {
       const dim3 gq = grid_quads(s->lay);
-      d.w.finish = finish_in_kernel(gq) ? 1 : 0;
       LAUNCH_SPLIT(s, k_divres4, p0, gq, d);
-      if (!d.w.finish) fold_partials_to(s, gq, s->d_red + 0);
+      fold_partials_to(s, gq, s->d_red + 0);
     } else {
       DISPATCH_D(s, k_divres, grid_tiles(s->lay, false), blk(s->D), d);
     }
@@ -1160,9 +1155,8 @@ int cfl(wl_sim* s, float* out) {
   CflArgs a{s->lay, s->u.base, s->sigma.base, s->redw, s->d_red + 2, s->per.zlo, s->per.zhi};
   if (use_vec4(s->lay)) {                          // all rows and planes, ghosts included
     const dim3 g((s->lay.n0 - 2 + 127) / 128, (s->lay.n1 + 3) / 4, (s->lay.n2 + 1) / 2);
-    a.w.finish = finish_in_kernel(g) ? 1 : 0;
     LAUNCH(s, k_cfl4, g, dim3(32, 4, 2), a);
-    if (!a.w.finish) fold_partials_to(s, g, s->d_red + 2);
+    fold_partials_to(s, g, s->d_red + 2);
   } else {
     DISPATCH_D(s, k_cfl, grid_tiles(s->lay, true), blk(s->D), a);
   }

@@ -129,8 +129,6 @@ struct RedWork {
   double* psum;          // [maxblocks]
   float* pmax;           // [maxblocks]
   unsigned int* ticket;  // zero before and after every use
-  int finish;            // vectorised kernels: 1 = the last block folds (block_reduce_finish), 0 = leave the block
-                         // partials to a k_fold_partials launch (grids too large for the ticket round trips)
 };
 
 __device__ __forceinline__ int linear_tid() {

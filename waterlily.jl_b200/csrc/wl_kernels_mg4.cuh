@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(256, WL_MG4_MINB_A) k_incr4(const SmArgs a) {
   };
   WL_CLASS_DISPATCH(cls, body);
   }
-  if (a.want_norms) { if (a.w.finish) block_reduce_finish(s1, m, a.w, a.out); else block_reduce_partial(s1, m, a.w); }
+  if (a.want_norms) block_reduce_partial(s1, m, a.w);           // folded by k_fold_partials
 }
 
 // ---------------------------------------------------------------- CFL (Flow.jl:234-244), 4 cells per thread
@@ -263,8 +263,7 @@ __global__ void __launch_bounds__(256) k_cfl4(const CflArgs a) {
       for (int q = 0; q < 4; ++q) m = fmaxf(m, sg.v[q]);
     }
   }
-  if (a.w.finish) block_reduce_finish(0.0, m, a.w, a.out);
-  else block_reduce_partial(0.0, m, a.w);
+  block_reduce_partial(0.0, m, a.w);
 }
 
 // ---------------------------------------------------------------- K-DIVRES, 4 cells per thread (see k_divres)
@@ -317,8 +316,7 @@ __global__ void __launch_bounds__(256, MODE == 1 ? WL_MG4_MINB_A : WL_MG4_MINB_B
   };
   WL_SPLIT_DISPATCH(MODE, cls, body);
   }
-  if (MODE == 0 && a.w.finish) block_reduce_finish(s, -INFINITY, a.w, a.out);
-  else block_reduce_partial(s, -INFINITY, a.w, MODE == 0 ? -1 : bx + a.uf.nx * (by + a.uf.ny * bz));
+  block_reduce_partial(s, -INFINITY, a.w, MODE == 0 ? -1 : bx + a.uf.nx * (by + a.uf.ny * bz));
 }
 
 // ---------------------------------------------------------------- K-PROJ, 4 cells per thread (see k_proj)
@@ -544,8 +542,7 @@ __global__ void __launch_bounds__(256, MODE == 1 ? 6 : WL_MG4_MINB_B) k_down4(co
     }
   }
   if (a.first) {
-    if (MODE == 0 && a.w.finish) block_reduce_finish(s1, mx, a.w, a.out);
-    else block_reduce_partial(s1, mx, a.w, MODE == 0 ? -1 : bx + a.f.uf.nx * (by + a.f.uf.ny * bz));
+    block_reduce_partial(s1, mx, a.w, MODE == 0 ? -1 : bx + a.f.uf.nx * (by + a.f.uf.ny * bz));
   }
 }
 
