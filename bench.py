@@ -34,7 +34,7 @@ B_ALG3 = {
     "smoother": 28.0,
 }
 SPLIT_KERNELS = ("k_divres4", "k_down4")
-SMOOTHER_KERNELS = ("k_gs_half_c", "k_gs_pair", "k_incr4", "k_smooth_fused", "k_gs_half_cx")
+SMOOTHER_KERNELS = ("k_gs_half_c2", "k_gs_half_c", "k_gs_pair", "k_incr4", "k_smooth_fused", "k_gs_half_cx")
 CELLS_PER_BLOCK = {"k_divres4": 1024, "k_proj4": 1024, "k_down4": 1024, "k_up4": 1024, "k_incr4": 1024, "k_cfl4": 1024}
 B_ALG2 = {"k_mom_rhs": (24 + 32) / 2}
 

@@ -1,6 +1,6 @@
 """The run-time A/B switches of the library ("Run-time switches") select slower paths that must produce the
 SAME bits as the default: K-MOM by cp.async instead of TMA, pressure kernels without pattern tiles, one-cell-per-thread
-pressure kernels, plain launches, the body-free K-MOM variant off, K-DIVRES / K-DOWN as one launch or as two on every level.  The switches are read once per process, so every
+pressure kernels, plain launches, the body-free K-MOM variant off, K-DIVRES / K-DOWN as one launch or as two on every level, the half sweep with one or two rows per thread.  The switches are read once per process, so every
 variant runs in its own process (tests/variant_worker.py) and the digests of u, p, Δt and pois.n are compared."""
 import os
 import subprocess
@@ -10,13 +10,13 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-SWITCHES = ["WL_NO_TMA", "WL_NO_TILE_FLAGS", "WL_NO_VEC4", "WL_NO_PDL", "WL_NO_NOBODY", "WL_NO_SPLIT", "WL_SPLIT_MIN_TILES"]
+SWITCHES = ["WL_NO_TMA", "WL_NO_TILE_FLAGS", "WL_NO_VEC4", "WL_NO_PDL", "WL_NO_NOBODY", "WL_NO_SPLIT", "WL_SPLIT_MIN_TILES", "WL_NO_GS_C2", "WL_GS_C2_MIN_BLOCKS"]
 
 
 def digest(case, switch=None):
     env = {k: v for k, v in os.environ.items() if k not in SWITCHES}
     if switch:
-        env[switch] = "1"            # (WL_SPLIT_MIN_TILES=1: K-DIVRES / K-DOWN as two launches on every level, however small)
+        env[switch] = "1"            # (WL_SPLIT_MIN_TILES=1, WL_GS_C2_MIN_BLOCKS=1: the large-level forms of K-DIVRES / K-DOWN / the half sweep on every level)
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "variant_worker.py"), case], capture_output=True, text=True,
                        timeout=300, env=env, cwd=ROOT)
     lines = [l for l in r.stdout.splitlines() if l.startswith("DIGEST")]

@@ -724,6 +724,14 @@ int smooth2(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready = false) {
       if (k0 == 4 && (d.lo_wrap || d.hi_wrap)) { if (int e = halo(s, p.eps, 1, true, false, true)) return e; }
       continue;
     }
+    // two rows per thread (k_gs_half_c2): same tiles, half the y threads, four planes per block; levels of a few dozen
+    // blocks keep the one-cell kernel (more, smaller blocks fill the GPU better there).  WL_NO_GS_C2 / WL_GS_C2_MIN_BLOCKS: A/B
+    static const bool c2_off = getenv("WL_NO_GS_C2") != nullptr;
+    static const long long c2_min = getenv("WL_GS_C2_MIN_BLOCKS") ? atoll(getenv("WL_GS_C2_MIN_BLOCKS")) : 2048;
+    if (!c2_off && s->D == 3 && !p.dist && blk(3).y == 4 && blk(3).z == 2 && (long long)gg.x * gg.y * gg.z >= c2_min) {
+      LAUNCH(s, k_gs_half_c2, dim3(gg.x, gg.y, (gg.z + 1) / 2), dim3(32, 2, 4), g);
+      continue;
+    }
     DISPATCH_D(s, k_gs_half_c, gg, blk(s->D), g);
     if (p.dist) { if (int e = halo(s, p.eps, 1, k0 == 4, true)) return e; }
   }

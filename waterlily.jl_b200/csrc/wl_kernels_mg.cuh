@@ -270,6 +270,44 @@ __global__ void __launch_bounds__(256) k_gs_half_c(const LevArgs a) {
   a.eps[o] = gs_update<D>(a, cls, i, j, k, o, r0, em, ep);
 }
 
+// The half sweep with TWO cells per thread: rows j and j+2 of one tile (same colour, same x, same tile class), so that
+// indices, bounds, colour and the class byte -- 72 of the one-cell kernel's ~120 instructions, ncu profiles/r2_c47_* -- are
+// paid once per two updates.  With the L2 prefetch in place the sweep is bound by instruction issue (80 %), not by
+// latency.  Block (32,2,4) = 64 x 4 x 4 cells: half a tile in x, two tile layers in z; a warp is one row pair.
+// Same per-cell arithmetic (gs_update): bit-identical.  3D, non-distributed levels.  Level-1 launch on the sphere grid:
+// 91.7 -> 83.0 us; four cells per thread (rows j, j+2 on planes k, k+2) measured 85.3 us (profiles/r2_c48_*).
+__global__ void __launch_bounds__(256) k_gs_half_c2(const LevArgs a) {
+  pdl_entry();
+  const Lay& l = a.l;
+  const int k = 1 + 4 * blockIdx.z + threadIdx.z;
+  const int cls = tile_class(a.uf, blockIdx.x >> 1, blockIdx.y, (k - 1) >> 1);
+  const int j = 1 + 4 * blockIdx.y + threadIdx.y;                    // second row: j + 2
+  const int i = 1 + 2 * (blockIdx.x * blockDim.x + threadIdx.x) + ((j + k + 3 + a.k0) & 1);
+  if (i > l.n0 - 2 || j > l.n1 - 2 || k > l.n2 - 2 || k > 2 * (l.n2 / 2) - 2) return;
+  const bool two = j + 2 <= l.n1 - 2;
+  const int o = l.off(i, j, k), o2 = o + 2 * l.pitch;
+  const float* e = a.eps + o;
+  const float* r = a.r + o;
+  float em[3], ep[3], fm[3], fp[3];
+  const float r0 = r[0];
+  em[0] = e[-1]; ep[0] = e[1]; em[1] = e[-l.pitch]; ep[1] = e[l.pitch]; em[2] = e[-l.plane]; ep[2] = e[l.plane];
+  float r1 = 0.f;
+  if (two) {
+    const float* e2 = e + 2 * l.pitch;
+    r1 = r[2 * l.pitch];
+    fm[0] = e2[-1]; fp[0] = e2[1]; fm[1] = ep[1]; fp[1] = e2[l.pitch]; fm[2] = e2[-l.plane]; fp[2] = e2[l.plane];
+  }
+  const int pfd = a.pf;
+  if (pfd > 0 && k + pfd <= l.n2 - 2) {
+    const float* pe = e + (long long)pfd * l.plane;
+    const float* pr = r + (long long)pfd * l.plane;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(pe)); asm volatile("prefetch.global.L2 [%0];" ::"l"(pr));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(pe + 2 * l.pitch)); asm volatile("prefetch.global.L2 [%0];" ::"l"(pr + 2 * l.pitch));
+  }
+  a.eps[o] = gs_update<3>(a, cls, i, j, k, o, r0, em, ep);
+  if (two) a.eps[o2] = gs_update<3>(a, cls, i, j + 2, k, o2, r1, fm, fp);
+}
+
 // ---- pattern-tile classification (see TileFlags in wl_common.cuh).  Stage 1: core[t] = every cell of tile t -- its
 // interior cells, plus the ghost / halo row, column or plane next to a tile at the end of a direction, which the
 // kernels read as upper faces -- holds the pattern value in all three components (and the same for its first / last 32
