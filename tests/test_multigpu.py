@@ -29,11 +29,11 @@ def test_slab_run_equals_single_gpu(nproc):
     lines = [l for l in r.stdout.splitlines() if l.startswith("MGPU")]
     assert r.returncode == 0 and "MGPU_RESULT PASS" in r.stdout, "\n".join(lines[-20:]) + r.stderr[-3000:]
     if nproc == 2:
-        # once more with K-DIVRES / K-DOWN forced into their two-launch form on every (also distributed) level: by default
-        # only levels with >= 16 k tiles take it, which these small grids never reach
+        # once more with the large-level forms forced on every (also distributed) level -- K-DIVRES / K-DOWN as two launches,
+        # the half sweeps with two rows per thread: by default only levels these small grids never reach take them
         cmd2 = cmd[:cmd.index(os.path.join(ROOT, "tests", "mgpu_worker.py")) + 1] + ["sphere", "cylinder", "tgv32"]
         cmd2[cmd2.index("--master-port") + 1] = str(29560 + nproc)
-        r = subprocess.run(cmd2, capture_output=True, text=True, timeout=420, cwd=ROOT, env=dict(os.environ, WL_SPLIT_MIN_TILES="1"))
+        r = subprocess.run(cmd2, capture_output=True, text=True, timeout=420, cwd=ROOT, env=dict(os.environ, WL_SPLIT_MIN_TILES="1", WL_GS_C2_MIN_BLOCKS="1"))
         lines = [l for l in r.stdout.splitlines() if l.startswith("MGPU")]
         assert r.returncode == 0 and "MGPU_RESULT PASS" in r.stdout, "\n".join(lines[-20:]) + r.stderr[-3000:]
 

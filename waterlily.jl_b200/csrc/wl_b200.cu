@@ -720,7 +720,10 @@ int smooth2(wl_sim* s, Level& p, float w, Red* norms, bool eps_ready = false) {
       x.push_lo = link_lo; x.push_hi = link_hi;
       if (link_lo) x.push_seq_lo = ++s->gs_seq_lo;
       if (link_hi) x.push_seq_hi = ++s->gs_seq_hi;
-      LAUNCH(s, k_gs_half_cx<3>, gg, blk(3), g, x);
+      static const bool cx2_off = getenv("WL_NO_GS_C2") != nullptr;
+      static const long long cx2_min = getenv("WL_GS_C2_MIN_BLOCKS") ? atoll(getenv("WL_GS_C2_MIN_BLOCKS")) : 2048;
+      if (!cx2_off && (long long)gg.x * gg.y * gg.z >= cx2_min) LAUNCH(s, (k_gs_half_cx<3, true>), gg, dim3(32, 2, 2), g, x);
+      else LAUNCH(s, k_gs_half_cx<3>, gg, blk(3), g, x);
       if (k0 == 4 && (d.lo_wrap || d.hi_wrap)) { if (int e = halo(s, p.eps, 1, true, false, true)) return e; }
       continue;
     }

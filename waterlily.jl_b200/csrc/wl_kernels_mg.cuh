@@ -419,7 +419,9 @@ struct GsLink {
   unsigned int push_seq_lo, push_seq_hi, wait_seq_lo, wait_seq_hi;
   int push_lo, push_hi, wait_lo, wait_hi;
 };
-template <int D>
+// TWO: a thread takes rows j and j+2 of its tile, as in k_gs_half_c2 (block (32,2,2) on the same grid of 64 x 4 x 2-cell
+// blocks, so the layer order, the tickets and the flags are those of the one-row form).
+template <int D, bool TWO = false>
 __global__ void __launch_bounds__(256) k_gs_half_cx(const LevArgs a, const GsLink x) {
   pdl_entry();
   const Lay& l = a.l;
@@ -434,25 +436,38 @@ __global__ void __launch_bounds__(256) k_gs_half_cx(const LevArgs a, const GsLin
     }
     __syncthreads();
   }
-  const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  constexpr int NR = TWO ? 2 : 1;
+  const int jb = (TWO ? 4 * blockIdx.y : blockIdx.y * blockDim.y) + threadIdx.y + 1;
   const int k = zb * blockDim.z + threadIdx.z + 1;
-  const int i = 1 + 2 * (blockIdx.x * blockDim.x + threadIdx.x) + ((j + k + D + a.k0) & 1);
-  if (i <= l.n0 - 2 && j <= l.n1 - 2 && k <= l.n2 - 2 && k <= 2 * (l.n2 / 2) - 2) {
-    const int o = l.off(i, j, k);
+  const int i = 1 + 2 * (blockIdx.x * blockDim.x + threadIdx.x) + ((jb + k + D + a.k0) & 1);   // rows jb, jb+2: same colour
+  if (i <= l.n0 - 2 && jb <= l.n1 - 2 && k <= l.n2 - 2 && k <= 2 * (l.n2 / 2) - 2) {
     const int st[3] = {1, l.pitch, l.plane};
-    const int cls = tile_class(a.uf, blockIdx.x >> 1, blockIdx.y, zb);
-    const float r0 = a.r[o];
-    float em[3], ep[3];
+    const int cls = tile_class(a.uf, blockIdx.x >> 1, TWO ? blockIdx.y : (jb - 1) >> 2, zb);
+    int o[NR]; bool on[NR]; float r0[NR], em[NR][3], ep[NR][3];
 #pragma unroll
-    for (int q = 0; q < D; ++q) { em[q] = a.eps[o - st[q]]; ep[q] = a.eps[o + st[q]]; }   // before the branch on cls
-    if (a.pf > 0 && k + a.pf <= l.n2 - 2) {                // as in k_gs_half_c (after the two boundary layers z runs upwards)
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(a.r + o + a.pf * l.plane));
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(a.eps + o + a.pf * l.plane));
+    for (int q = 0; q < NR; ++q) {
+      on[q] = jb + 2 * q <= l.n1 - 2;
+      o[q] = l.off(i, jb + 2 * q, k);
+      if (!on[q]) continue;
+      r0[q] = a.r[o[q]];
+#pragma unroll
+      for (int d = 0; d < D; ++d) { em[q][d] = a.eps[o[q] - st[d]]; ep[q][d] = a.eps[o[q] + st[d]]; }   // before the branch on cls
     }
-    const float v = gs_update<D>(a, cls, i, j, k, o, r0, em, ep);
-    a.eps[o] = v;
-    if (x.push_lo && k == 1) x.peer_lo[o + l.plane * (l.n2 - 2)] = v;
-    if (x.push_hi && k == l.n2 - 2) x.peer_hi[o - l.plane * (l.n2 - 2)] = v;
+    if (a.pf > 0 && k + a.pf <= l.n2 - 2) {                // as in k_gs_half_c (after the two boundary layers z runs upwards)
+#pragma unroll
+      for (int q = 0; q < NR; ++q) {
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.r + o[q] + a.pf * l.plane));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.eps + o[q] + a.pf * l.plane));
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < NR; ++q) {
+      if (!on[q]) continue;
+      const float v = gs_update<D>(a, cls, i, jb + 2 * q, k, o[q], r0[q], em[q], ep[q]);
+      a.eps[o[q]] = v;
+      if (x.push_lo && k == 1) x.peer_lo[o[q] + l.plane * (l.n2 - 2)] = v;
+      if (x.push_hi && k == l.n2 - 2) x.peer_hi[o[q] - l.plane * (l.n2 - 2)] = v;
+    }
   }
   const bool sig_lo = lo_blk && x.push_lo, sig_hi = hi_blk && x.push_hi;
   if (sig_lo || sig_hi) {
