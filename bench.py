@@ -34,6 +34,9 @@ B_ALG3 = {
     "smoother": 28.0,
 }
 SPLIT_KERNELS = ("k_divres4", "k_down4")
+# B_alg of these counts the L / iD loads that pattern tiles (classes 1-3) skip: their fraction is an upper bound, not a DRAM rate.
+PATTERN_KERNELS = ("k_divres4", "k_proj4", "k_down4", "k_up4")
+PATTERN_NOTE = "B_alg counts L/iD loads that pattern tiles skip: upper bound of the DRAM rate, may exceed 1"
 SMOOTHER_KERNELS = ("k_gs_half_c2", "k_gs_half_c", "k_gs_pair", "k_incr4", "k_smooth_fused", "k_gs_half_cx")
 CELLS_PER_BLOCK = {"k_divres4": 1024, "k_proj4": 1024, "k_down4": 1024, "k_up4": 1024, "k_incr4": 1024, "k_cfl4": 1024}
 B_ALG2 = {"k_mom_rhs": (24 + 32) / 2}
@@ -317,6 +320,8 @@ def kernel_table(prof, blocks, cells_gpu, nsteps, peak, ncu):
         if balg and work and ms > 0:
             row["achieved_GBps"] = balg * work / (ms * 1e-3) / 1e9
             row["frac"] = row["achieved_GBps"] / peak
+            if kn in PATTERN_KERNELS:
+                row["frac_note"] = PATTERN_NOTE
         rows.append(row)
     if sm_ms > 0 and sm_cells > 0:
         ach = B_ALG3["smoother"] * sm_cells / (sm_ms * 1e-3) / 1e9
