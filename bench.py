@@ -314,7 +314,10 @@ def kernel_table(prof, blocks, cells_gpu, nsteps, peak, ncu):
             sm_n += n
             if kn in ("k_incr4", "k_smooth_fused", "k_gs_pair_incr"):   # runs once per smooth: its blocks count the cells smoothed
                 sm_cells += blocks.get(name, 0) * CELLS_PER_BLOCK.get(kn, 1024)
-        row = {"kernel": kn + ("<nobody>" if kn == "k_mom3" and balg == B_ALG3["k_mom3_nobody"] else ""),
+        label = kn + ("<nobody>" if kn == "k_mom3" and balg == B_ALG3["k_mom3_nobody"] else "")
+        if kn in SPLIT_KERNELS and targs[:1] == ["0"]:
+            label += " (one launch: levels below the split threshold)"
+        row = {"kernel": label,
                "launches_per_step": n / nsteps, "avg_us": ms / n * 1e3, "share": ms / total if total else None,
                "B_alg": balg, "achieved_GBps": None, "frac": None, "ncu_dram_bytes_per_launch": ncu.get(kn)}
         if balg and work and ms > 0:
@@ -475,7 +478,7 @@ def main():
     # ---- roofline of the dominant kernel (live CUDA events inside the timed region)
     kn = sum(n for n, _ in prof.values())
     kms = sum(ms for _, ms in prof.values())
-    row = next((r for r in table if r["kernel"].split("<")[0] == dom and r["B_alg"]), None)
+    row = next((r for r in table if r["kernel"].split("<")[0].split(" (")[0] == dom and r["B_alg"]), None)
     if D == 3 and row is not None and kn:
         work = row["B_alg"] * ((cells // world) * kn if dom == "k_mom3" else
                                sum(sim.prof_blocks.get(nm, 0) for nm in prof) * CELLS_PER_BLOCK.get(dom, 1024))
