@@ -255,7 +255,7 @@ function pressure_force(a::B200Flow{D,T}, body::AbstractBody) where {D,T}
     Ng = size(a.p); b = shifted(body, a.koff, Val(D)); t = time(a)
     idx = Int64[]; w = T[]
     lin = LinearIndices(Ng)
-    for I in WaterLily.inside(Ng)
+    for I in WaterLily.inside(a.p)                      # `inside` takes the array (src/core.jl:47); B200Array has `size`
         n = WaterLily.nds(b, WaterLily.loc(0, I, T), t)
         iszero(n) && continue
         push!(idx, lin[I] - 1); append!(w, n)           # 0-based, first dimension fastest; D weights per entry
@@ -388,11 +388,11 @@ function update!(m::B200MeanFlow{T}, flow::B200Flow) where T
     check(m.h, ccall((:wl_meanflow_update, LIB), Cint, (Ptr{Cvoid}, Cfloat), m.h.ptr, ε))
     push!(m.t, m.t[end] + dt)
 end
-function reset!(m::B200MeanFlow{T}; t_init=0.0) where T
+function WaterLily.reset!(m::B200MeanFlow{T}; t_init=0.0) where T      # WaterLily's own generic (src/Metrics.jl:229), not exported
     check(m.h, ccall((:wl_meanflow_init, LIB), Cint, (Ptr{Cvoid}, Cint), m.h.ptr, m.uu_stats))
     empty!(m.t); push!(m.t, T(t_init))
 end
-copy!(flow::B200Flow, m::B200MeanFlow) = check(m.h, ccall((:wl_meanflow_copy_to_flow, LIB), Cint, (Ptr{Cvoid},), m.h.ptr))
+WaterLily.copy!(flow::B200Flow, m::B200MeanFlow) = check(m.h, ccall((:wl_meanflow_copy_to_flow, LIB), Cint, (Ptr{Cvoid},), m.h.ptr))
 
 "Drop-in constructor: WaterLily's own `Simulation` with the two factories swapped."
 B200Simulation(dims, uBC, L; device=0, kw...) =
