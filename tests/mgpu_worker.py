@@ -51,6 +51,9 @@ CASES = {
     # the stand-alone Poisson/pcg! solver on slabs (perdot = gathered partial sums), after two ordinary steps
     "pcg": lambda: dict(dims=(32, 32, 32), uBC=(1.0, 0.0, 0.0), L=8.0, kw=dict(nu=8.0 / 100),
                         body=dict(kind="sphere", center=(12, 15, 15), radius=4.0), remeasure=False, steps=2, pcg=True),
+    # slab-parallel output (io.VTKWriter): one .vti piece per rank + rank 0's .pvti index, read back = the single-GPU fields
+    "vtk": lambda: dict(dims=(32, 32, 32), uBC=(1.0, 0.0, 0.0), L=8.0, kw=dict(nu=8.0 / 100),
+                        body=dict(kind="sphere", center=(12, 15, 15), radius=4.0), remeasure=False, steps=2, vtk=True),
     # Function uBC(i,x,t) varying along the decomposed direction + its ∂ₜ in accelerate!: every rank samples its own slab
     # of the tables at global coordinates (physical z ends on the first / last rank, interfaces in between)
     "fn_ubc": lambda: dict(dims=(32, 24, 16), uBC=_ubc, L=8.0, kw=dict(nu=0.02, U=1.0, dt=0.1, dUBCdt=_dub),
@@ -108,6 +111,25 @@ def run_case(wl, name, comm, dev):
         out["pcg_n"] = [n1, n2]
         out["pcg_err"] = float(np.abs(got - ref)[1:-1].max() / max(1e-30, float(np.abs(ref).max())))
         ok = ok and abs(n1 - n2) <= 1 + n1 // 50 and n1 > 0 and out["pcg_err"] <= 1e-3
+    if c.get("vtk"):
+        import tempfile
+        import torch.distributed as dist
+        from waterlily_jl_b200 import io as wio
+        box = [tempfile.mkdtemp(prefix="wl_vtk_") if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        cwd = os.getcwd()
+        os.chdir(box[0])                                   # `fname` is a name, not a path (as in the reference's vtkWriter)
+        w = wio.VTKWriter("slab", dir="OUT")
+        path = w.save(slab)
+        w.close(rank=rank)
+        dist.barrier()                                     # all pieces on disk before anyone reads the index
+        grid, data = wio.read_pvti(path)
+        out["vtk_files"] = sorted(os.listdir("OUT"))
+        out["vtk_err"] = max(float(np.abs(data["Pressure"] - one.flow.p).max()), float(np.abs(data["Velocity"] - one.flow.u).max()))
+        ok = ok and tuple(grid) == tuple(one.field_shape("p")) and out["vtk_err"] <= 1e-6 and len(out["vtk_files"]) == n + 1
+        ok = ok and [f for _, f in wio._read_pvd("slab.pvd")] == ["OUT/slab_000000.pvti"] if rank == 0 else ok
+        dist.barrier()
+        os.chdir(cwd)
     slab.sync()
     out["halo"] = slab.halo_stats()
     out["transport"] = slab.halo_transport()

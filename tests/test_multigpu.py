@@ -22,7 +22,7 @@ def test_slab_run_equals_single_gpu(nproc):
     import torch
     if torch.cuda.device_count() < nproc:
         pytest.skip(f"needs {nproc} GPUs")
-    cases = ["tgv32", "sphere", "sphere_exit", "cylinder", "torus", "fn_ubc", "fn_g", "pcg"] if nproc == 2 else ["tgv_32x32x64", "sphere64"]
+    cases = ["tgv32", "sphere", "sphere_exit", "cylinder", "torus", "fn_ubc", "fn_g", "pcg", "vtk"] if nproc == 2 else ["tgv_32x32x64", "sphere64"]
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(29530 + nproc), os.path.join(ROOT, "tests", "mgpu_worker.py")] + cases
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=420, cwd=ROOT)
