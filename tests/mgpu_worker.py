@@ -128,6 +128,23 @@ def run_case(wl, name, comm, dev):
         out["vtk_err"] = max(float(np.abs(data["Pressure"] - one.flow.p).max()), float(np.abs(data["Velocity"] - one.flow.u).max()))
         ok = ok and tuple(grid) == tuple(one.field_shape("p")) and out["vtk_err"] <= 1e-6 and len(out["vtk_files"]) == n + 1
         ok = ok and [f for _, f in wio._read_pvd("slab.pvd")] == ["OUT/slab_000000.pvti"] if rank == 0 else ok
+        # restart from the collection (load_pvd: last file, Δt[end] from the stored time, push CFL): the slab run takes its
+        # slab of the reassembled arrays, the single-GPU run the whole of them; one more step must agree again
+        slab.upload("p", np.zeros(slab.field_shape("p"), np.float32))
+        slab.upload("u", np.zeros(slab.field_shape("u"), np.float32))
+        wio.load_pvd(slab, "slab.pvd")
+        wio.load_pvd(one, "slab.pvd")
+        r_err = 0.0
+        for step in range(2):
+            for f in ("u", "p"):
+                d = np.abs(getattr(slab.flow, f) - wl.slab_of(getattr(one.flow, f), rank, n))[..., 1:-1, :, :]
+                r_err = max(r_err, float(d.max()))
+            if step == 0:
+                one.sim_step(remeasure=False)
+                slab.sim_step(remeasure=False)
+        out["vtk_restart_err"] = r_err
+        out["vtk_restart_dt"] = [float(x) for x in slab.flow.Δt[-2:]]
+        ok = ok and r_err <= 1e-6 and [float(x) for x in one.flow.Δt] == [float(x) for x in slab.flow.Δt]
         dist.barrier()
         os.chdir(cwd)
     slab.sync()
